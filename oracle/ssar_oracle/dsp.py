@@ -1,0 +1,161 @@
+"""Oracle: framing, STFT-family transforms and per-frame spectral features (torch CPU, fp32).
+
+TEST INFRASTRUCTURE (see package docstring).  Written as explicit framing + rFFT rather than torch.stft so the
+restatement is independent of the op the reference happens to call.
+"""
+from __future__ import annotations
+
+import math
+
+import numpy as np
+import torch
+
+
+# ----------------------------------------------------------------------------------------------
+# framing / transforms
+# ----------------------------------------------------------------------------------------------
+def reflect_pad(y: torch.Tensor, p: int) -> torch.Tensor:
+    """torch.nn.functional.pad(mode="reflect") on the last axis: edge sample not repeated."""
+    if p == 0:
+        return y
+    left = y[..., 1 : p + 1].flip(-1)
+    right = y[..., -p - 1 : -1].flip(-1)
+    return torch.cat([left, y, right], dim=-1)
+
+
+def frames(y: torch.Tensor, n_fft: int, hop: int) -> torch.Tensor:
+    """[..., N] -> [..., 1 + N//hop, n_fft] centred, reflect-padded frames (torch.stft center=True)."""
+    return reflect_pad(y, n_fft // 2).unfold(-1, n_fft, hop)
+
+
+def hann_periodic(n: int) -> torch.Tensor:
+    """torch.hann_window(n) (periodic): 0.5 - 0.5 cos(2 pi k / n)."""
+    return torch.hann_window(n, dtype=torch.float32)
+
+
+def stft(y, n_fft=2048, hop_length=1024, window="hann"):
+    """ssar/features/rosa/spectral.py:10-21 -> complex64 [F, 1 + N//hop] (or [B, F, T+1])."""
+    fr = frames(y.float(), n_fft, hop_length)
+    if window is not None:
+        fr = fr * (hann_periodic(n_fft) if isinstance(window, str) else window)
+    return torch.fft.rfft(fr, dim=-1).transpose(-1, -2)
+
+
+def istft(spec, n_fft=2048, hop_length=1024, window="hann", length=None):
+    """ssar/features/rosa/spectral.py:24-32 (torch.istft semantics): irfft per frame, window, overlap-add,
+    divide by the summed squared window, drop n_fft/2 from the start, trim / zero-pad to `length`."""
+    w = hann_periodic(n_fft) if isinstance(window, str) else (torch.ones(n_fft) if window is None else window)
+    fr = torch.fft.irfft(spec.transpose(-1, -2), n=n_fft, dim=-1) * w  # [T, n_fft]
+    T = fr.shape[-2]
+    total = n_fft + hop_length * (T - 1)
+    out = torch.zeros(total, dtype=torch.float32)
+    env = torch.zeros(total, dtype=torch.float32)
+    idx = (torch.arange(T)[:, None] * hop_length + torch.arange(n_fft)[None, :]).reshape(-1)
+    out.index_add_(0, idx, fr.reshape(-1))
+    env.index_add_(0, idx, (w * w).repeat(T))
+    start = n_fft // 2
+    end = total - n_fft // 2 if length is None else start + length
+    out, env = out[start:end], env[start:end]
+    out = out / env
+    if length is not None and out.shape[0] < length:
+        out = torch.nn.functional.pad(out, (0, length - out.shape[0]))
+    return out
+
+
+def spectrogram(y, n_fft=2048, hop_length=1024, power=1, window="hann"):
+    """rosa/spectral.py:59-62: last STFT frame dropped -> [F, N//hop]."""
+    if hop_length is None:
+        hop_length = n_fft // 4
+    return stft(y, n_fft, hop_length, window)[..., :-1].abs() ** power
+
+
+# ----------------------------------------------------------------------------------------------
+# mel
+# ----------------------------------------------------------------------------------------------
+F_SP = 200.0 / 3
+MIN_LOG_HZ = 1000.0
+MIN_LOG_MEL = MIN_LOG_HZ / F_SP
+LOGSTEP = np.log(6.4) / 27.0
+
+
+def hz_to_mel(f):
+    """rosa/convert.py:15-41 (Slaney)."""
+    f = torch.as_tensor(f, dtype=torch.float32)
+    lin = f / F_SP
+    return torch.where(f >= MIN_LOG_HZ, MIN_LOG_MEL + torch.log(f / MIN_LOG_HZ) / LOGSTEP, lin)
+
+
+def mel_to_hz(m):
+    """rosa/convert.py:44-66."""
+    m = torch.as_tensor(m, dtype=torch.float32)
+    return torch.where(m >= MIN_LOG_MEL, MIN_LOG_HZ * torch.exp(LOGSTEP * (m - MIN_LOG_MEL)), F_SP * m)
+
+
+def mel_basis(sr, n_fft, n_mels=128, fmin=0.0, fmax=None):
+    """rosa/spectral.py:73-110: triangular, area-normalised filters [n_mels, 1 + n_fft/2]."""
+    fmax = float(sr) / 2 if fmax is None else fmax
+    fftfreqs = torch.linspace(0, float(sr) / 2, 1 + n_fft // 2)
+    edges = mel_to_hz(torch.linspace(float(hz_to_mel(fmin)), float(hz_to_mel(fmax)), n_mels + 2))
+    width = torch.diff(edges)
+    ramps = edges[:, None] - fftfreqs[None, :]
+    W = torch.zeros(n_mels, 1 + n_fft // 2)
+    for i in range(n_mels):
+        W[i] = torch.clamp(torch.minimum(-ramps[i] / width[i], ramps[i + 2] / width[i + 1]), min=0)
+    return W * (2.0 / (edges[2:] - edges[:-2]))[:, None]
+
+
+def melspectrogram(y, sr, n_fft=2048, hop_length=1024, power=2.0, fmax=None):
+    """rosa/spectral.py:65-70."""
+    return mel_basis(sr, n_fft, fmax=fmax) @ spectrogram(y, n_fft, hop_length, power)
+
+
+def power_to_db(x, top_db=80.0):
+    """rosa/convert.py:7-12 with ref_value = 1, amin = 1e-10."""
+    amin = torch.tensor(1e-10)
+    db = 10.0 * torch.log10(torch.maximum(amin, x))
+    db = db - 10.0 * torch.log10(torch.maximum(amin, torch.ones(())))
+    if top_db is not None:
+        db = torch.maximum(db, db.max() - top_db)
+    return db
+
+
+def dct_ortho(x):
+    """rosa/spectral.py:35-56 with norm="ortho", over the last axis (restated as the explicit cosine sum)."""
+    N = x.shape[-1]
+    n = torch.arange(N, dtype=torch.float64)
+    k = torch.arange(N, dtype=torch.float64)[:, None]
+    D = torch.cos(math.pi * k * (2 * n + 1) / (2 * N))
+    D[0] /= math.sqrt(N)
+    D[1:] *= math.sqrt(2.0 / N)
+    return (x.double() @ D.T).float()
+
+
+# ----------------------------------------------------------------------------------------------
+# per-frame features
+# ----------------------------------------------------------------------------------------------
+def rms(y, sr=None, frame_length=2048, hop_length=1024):
+    """features/audio.py:31-37 -> [T, 1]."""
+    fr = frames(y.float(), frame_length, hop_length)[:-1]
+    return torch.sqrt(torch.mean(fr.abs() ** 2, dim=1)).unsqueeze(-1)
+
+
+def onset_strength(y, sr, hop_length=1024, n_fft=2048, aggregate="mean"):
+    """rosa/beat.py:10-23: mel (fmax 11025) -> dB -> positive first difference -> mean/median over bands ->
+    shifted right by 1 + n_fft // (2 hop) frames, truncated to T."""
+    S = power_to_db(melspectrogram(y, sr, n_fft=n_fft, hop_length=hop_length, fmax=11025.0).abs())
+    flux = torch.clamp(S[:, 1:] - S[:, :-1], min=0)
+    env = flux.mean(dim=0) if aggregate == "mean" else flux.median(dim=0).values
+    shift = 1 + n_fft // (2 * hop_length)
+    return torch.cat([torch.zeros(shift), env])[: S.shape[1]]
+
+
+def mfcc(y, sr, n_mfcc=20):
+    """features/audio.py:60-65 -> [T, n_mfcc]."""
+    S = power_to_db(melspectrogram(y, sr))
+    return dct_ortho(S.T)[:, :n_mfcc]
+
+
+def spectral_flatness(y, sr=None, n_fft=2048, hop_length=1024, amin=1e-10, power=2.0):
+    """features/audio.py:126-133 -> [T, 1]."""
+    S = torch.clamp(spectrogram(y, n_fft, hop_length, power=1.0) ** power, min=amin)
+    return (torch.exp(torch.mean(torch.log(S), dim=0)) / torch.mean(S, dim=0)).unsqueeze(-1)

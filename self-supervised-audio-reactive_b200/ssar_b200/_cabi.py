@@ -1,0 +1,103 @@
+"""ctypes binding of `libssar_b200.so` (the C ABI declared in `include/ssar_b200.h`).
+
+There is deliberately NO fallback: if the library is missing or a tensor is not a CUDA tensor the call raises.
+PyTorch is used for device memory, streams and `torch.distributed` only.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import torch
+
+LIB_PATH = Path(__file__).resolve().parent / "libssar_b200.so"
+
+_lib = None
+launch_count = 0  # number of C-ABI kernel entry points invoked (bench.py reports it as gpu_launches)
+
+
+class SsarError(RuntimeError):
+    pass
+
+
+class Filterbank(C.Structure):
+    _fields_ = [
+        ("n_bands", C.c_int), ("on_power", C.c_int),
+        ("start", C.c_void_p), ("count", C.c_void_p), ("offset", C.c_void_p), ("weights", C.c_void_p),
+        ("out", C.c_void_p), ("ld", C.c_longlong), ("max_key", C.c_void_p),
+    ]
+
+
+class Projection(C.Structure):
+    _fields_ = [
+        ("n_rows", C.c_int),
+        ("start", C.c_void_p), ("count", C.c_void_p), ("offset", C.c_void_p), ("weights", C.c_void_p),
+        ("out", C.c_void_p), ("ld", C.c_longlong), ("scale", C.c_float),
+    ]
+
+
+class FramesArgs(C.Structure):
+    _fields_ = [
+        ("x", C.c_void_p), ("n_samples", C.c_longlong), ("clip_stride", C.c_longlong),
+        ("n_clips", C.c_int), ("n_fft", C.c_int), ("hop", C.c_int), ("n_frames", C.c_int),
+        ("window", C.c_void_p), ("twiddle", C.c_void_p),
+        ("out_complex", C.c_void_p), ("ldc", C.c_longlong),
+        ("out_spec", C.c_void_p), ("lds", C.c_longlong), ("spec_power", C.c_int),
+        ("out_rms", C.c_void_p), ("out_flatness", C.c_void_p),
+        ("fb", Filterbank * 2), ("proj", Projection),
+    ]
+
+
+def lib():
+    """Loads the library once; raises (never falls back) when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise SsarError(
+                f"{LIB_PATH} not found: build the CUDA library first (python -m ssar_b200._build or "
+                "__graft_entry__.build()). ssar_b200 has no CPU or PyTorch fallback."
+            )
+        _lib = C.CDLL(str(LIB_PATH))
+        _lib.ssar_last_error.restype = C.c_char_p
+        if _lib.ssar_abi_version() != 1:
+            raise SsarError("libssar_b200.so ABI version mismatch; rebuild")
+    return _lib
+
+
+def ptr(t):
+    """Device pointer of a contiguous CUDA tensor (None -> NULL)."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise SsarError("ssar_b200 kernels need CUDA tensors (no CPU fallback)")
+    return C.c_void_p(t.data_ptr())
+
+
+def stream_ptr():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def call(name: str, *args):
+    """Invoke a C-ABI entry point on the current CUDA stream and raise on a non-zero status."""
+    global launch_count
+    fn = getattr(lib(), name)
+    rc = fn(*args, stream_ptr())
+    launch_count += 1
+    if rc != 0:
+        raise SsarError(f"{name} failed ({rc}): {lib().ssar_last_error().decode()}")
+
+
+def i32(v):
+    return C.c_int(int(v))
+
+
+def i64(v):
+    return C.c_longlong(int(v))
+
+
+def f32(v):
+    return C.c_float(float(v))
+
+
+def f64(v):
+    return C.c_double(float(v))

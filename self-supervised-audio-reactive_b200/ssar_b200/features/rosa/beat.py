@@ -1,0 +1,36 @@
+"""Mirror of ssar/features/rosa/beat.py (onset strength; plp lives further down once the tempogram path is in)."""
+from __future__ import annotations
+
+import torch
+
+from ... import ops, plan
+
+
+def _aggregate_name(aggregate):
+    if aggregate is torch.mean or aggregate == "mean":
+        return "mean"
+    if aggregate is torch.median or aggregate == "median":
+        return "median"
+    # the reference's plp passes a lambda wrapping torch.median (rosa/beat.py:42-44)
+    name = getattr(aggregate, "__name__", "")
+    if "median" in name:
+        return "median"
+    probe = aggregate(torch.tensor([[1.0, 2.0, 4.0, 8.0]]), axis=1)
+    return "median" if float(probe.flatten()[0]) == 2.0 else "mean"
+
+
+def onset_mel(y, sr, hop_length=1024, n_fft=2048):
+    """mel(fmax=11025) power spectrogram + per-clip running max, frame-major [B,T,128] (one fused launch)."""
+    n = y.shape[-1]
+    bank = plan.mel_bank(float(sr), int(n_fft), 128, 0.0, 11025.0, str(y.device))
+    out = ops.frames_fft(y, n_fft, hop_length, n // hop_length, torch.hann_window, banks=[(bank, True, True)])
+    return out["bank0"], out["bank0_max"]
+
+
+def onset_strength(y, sr, hop_length=1024, n_fft=2048, aggregate=torch.mean):
+    """rosa/beat.py:10-23 -> [T] (or [B,T])."""
+    squeeze = y.dim() == 1
+    m, mk = onset_mel(y, sr, hop_length, n_fft)
+    pad_width = 1 + n_fft // (2 * hop_length)
+    env = ops.onset_flux(m, mk, pad_width, _aggregate_name(aggregate))
+    return env[0] if squeeze else env

@@ -1,0 +1,90 @@
+"""Generates the committed golden fixtures by running the UNMODIFIED reference (/root/reference) on CPU.
+
+Run in the build container only:  python tests/golden/make_golden.py [group ...]
+Each group writes tests/golden/<group>.npz holding the seeded synthetic inputs' parameters and the reference's
+outputs.  Inputs are regenerated from `ssar_b200.synth.synth_clip` (deterministic), so only outputs are stored.
+"""
+from __future__ import annotations
+
+import sys
+from pathlib import Path
+
+import numpy as np
+import torch
+
+HERE = Path(__file__).resolve().parent
+ROOT = HERE.parent.parent
+sys.path.insert(0, str(HERE))
+sys.path.insert(0, str(ROOT / "self-supervised-audio-reactive_b200"))
+
+from ref_loader import load_reference  # noqa: E402
+from ssar_b200.synth import synth_clip  # noqa: E402
+
+SR = 24576
+
+
+def save(group, **arrays):
+    out = {}
+    for k, v in arrays.items():
+        if torch.is_tensor(v):
+            v = v.detach().cpu().numpy()
+        out[k] = np.asarray(v)
+    np.savez_compressed(HERE / f"{group}.npz", **out)
+    print(group, {k: v.shape for k, v in out.items()})
+
+
+def g_spectral(ref):
+    """short ragged clip: frame placement + spectra (n_fft 2048 and the CQT-style rectangular 1024)."""
+    n = 8192 + 100
+    x = synth_clip(n, SR, 0)
+    D = ref.spectral.stft(x)
+    save(
+        "spectral_short", n=n, sr=SR,
+        stft_re=D.real, stft_im=D.imag,
+        spec_p1=ref.spectral.spectrogram(x, power=1),
+        spec_p2_hop512=ref.spectral.spectrogram(x, hop_length=512, power=2),
+        stft_rect1024_re=ref.spectral.stft(x, n_fft=1024, hop_length=256, window=None).real,
+        stft_rect1024_im=ref.spectral.stft(x, n_fft=1024, hop_length=256, window=None).imag,
+        mel_basis_sum=ref.spectral.mel(SR, 2048).sum(1),
+        mel_basis_11025_sum=ref.spectral.mel(SR, 2048, fmax=11025.0).sum(1),
+    )
+
+
+def g_frame_features(ref):
+    """2 s (+300 samples) clip: mel / onset / rms / mfcc / flatness at both hops used by the configs."""
+    n = SR * 2 + 300
+    x = synth_clip(n, SR, 1)
+    med = lambda *a, **k: torch.median(*a, **k).values
+    save(
+        "frame_features", n=n, sr=SR, clip_index=1,
+        mel=ref.spectral.melspectrogram(x, SR),
+        mel_hop512=ref.spectral.melspectrogram(x, SR, hop_length=512),
+        onset=ref.beat.onset_strength(x, SR),
+        onset_hop512=ref.beat.onset_strength(x, SR, hop_length=512),
+        onset_median=ref.beat.onset_strength(x, SR, aggregate=med),
+        rms=ref.audio.rms(x, SR),
+        rms_hop512=ref.audio.rms(x, SR, hop_length=512),
+        mfcc=ref.audio.mfcc(x, SR),
+        flatness=ref.audio.spectral_flatness(x, SR),
+    )
+    # 44.1 kHz variant of BASELINE config 2 (n_fft 2048, hop 512)
+    n2 = 44100 + 77
+    x2 = synth_clip(n2, 44100, 2)
+    save(
+        "frame_features_44k", n=n2, sr=44100, clip_index=2,
+        spec_p2=ref.spectral.spectrogram(x2, 2048, 512, power=2)[::8],
+        mel=ref.spectral.melspectrogram(x2, 44100, 2048, 512),
+        onset=ref.beat.onset_strength(x2, 44100, 512, 2048),
+        rms=ref.audio.rms(x2, 44100, 2048, 512),
+    )
+
+
+GROUPS = {"spectral": g_spectral, "frame_features": g_frame_features}
+
+if __name__ == "__main__":
+    torch.manual_seed(0)
+    ref = load_reference()
+    names = sys.argv[1:] or list(GROUPS)
+    with torch.inference_mode():
+        for name in names:
+            GROUPS[name](ref)
