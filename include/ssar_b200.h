@@ -130,6 +130,40 @@ int ssar_minmax_keys(const float* x, int n_clips, long long n_per_clip, uint32_t
 int ssar_rms_frames(const float* x, long long n_samples, long long clip_stride, int n_clips,
                     int frame_length, int hop, int n_frames, float* out, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * HPSS, inverse STFT, IIR band splits, resampling
+ * ---------------------------------------------------------------------------------------------- */
+
+/* rosa/spectral.py:145-161 hpss on a complex STFT [n_clips, n_frames, ld] (complex, frame-major): 31-tap medians
+ * along time / frequency (features/processing.py:74-84, reflect padding) + soft masks (rosa/spectral.py:120-142,
+ * power 2, margin).  Either output may be NULL.  Outputs have the input's layout. */
+int ssar_hpss(const float* stft, int n_clips, int n_frames, int n_bins, long long ld, float margin_harm,
+              float margin_perc, float* out_harm, float* out_perc, void* stream);
+
+/* torch.istft (rosa/spectral.py:24-32), step 1: per-frame inverse real FFT times the synthesis window.
+ * spec: complex [n_clips, n_frames, ld]; frames: [n_clips, n_frames, n_fft]. n_fft 1024 or 2048. */
+int ssar_irfft_frames(const float* spec, long long ld, int n_clips, int n_frames, int n_fft,
+                      const float* window, const float* twiddle, float* frames, void* stream);
+
+/* torch.istft step 2: overlap-add of `frames`, division by the summed squared window, drop n_fft/2 leading
+ * samples, produce `length` samples per clip (zeros past the covered range). out: [n_clips, length]. */
+int ssar_overlap_add(const float* frames, const float* window, int n_clips, int n_frames, int n_fft, int hop,
+                     long long length, float* out, void* stream);
+
+/* torchaudio lfilter for one biquad (features/processing.py:141-150): coefficients already divided by a0.
+ * scratch: ssar_biquad_scratch_bytes(n_clips, n_samples) bytes of device memory.  y must not alias x. */
+long long ssar_biquad_scratch_bytes(int n_clips, long long n_samples);
+int ssar_biquad(const float* x, long long n_samples, long long stride_x, int n_clips, float b0, float b1,
+                float b2, float a1, float a2, int clamp, float* y, long long stride_y, void* scratch,
+                void* stream);
+
+/* torchaudio.functional.resample (supervised/data.py:63; rosa/constantq.py:83) with banded polyphase taps:
+ * taps [max_taps, newf] tap-major, first [newf] = index of the first kept tap of each phase in torchaudio's
+ * dense kernel; y[j] = post_scale * sum_k taps[k][j % newf] * xpad[(j / newf) * orig + first + k]. */
+int ssar_resample(const float* x, long long n_in, long long stride_in, int n_clips, const float* taps,
+                  const int* first, int orig, int newf, int width, int max_taps, float post_scale, float* y,
+                  long long n_out, long long stride_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

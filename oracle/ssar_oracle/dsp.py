@@ -159,3 +159,117 @@ def spectral_flatness(y, sr=None, n_fft=2048, hop_length=1024, amin=1e-10, power
     """features/audio.py:126-133 -> [T, 1]."""
     S = torch.clamp(spectrogram(y, n_fft, hop_length, power=1.0) ** power, min=amin)
     return (torch.exp(torch.mean(torch.log(S), dim=0)) / torch.mean(S, dim=0)).unsqueeze(-1)
+
+
+# ----------------------------------------------------------------------------------------------
+# harmonic / percussive separation
+# ----------------------------------------------------------------------------------------------
+def median_filter_1d(S, k, dim):
+    """features/processing.py:74-84 restricted to a 1-D window: reflect pad k//2, sliding window, torch.median
+    (= lower median; exact middle for odd k), here via a full sort."""
+    h = k // 2
+    S = S.transpose(dim, -1)
+    win = reflect_pad(S, h).unfold(-1, k, 1)
+    out = torch.sort(win, dim=-1).values[..., (k - 1) // 2]
+    return out.transpose(dim, -1)
+
+
+def softmask(X, X_ref, power=2.0, split_zeros=False):
+    """rosa/spectral.py:120-142."""
+    Z = torch.maximum(X, X_ref)
+    bad = Z < torch.finfo(torch.float32).tiny
+    Z = torch.where(bad, torch.ones(()), Z)
+    m, r = (X / Z) ** power, (X_ref / Z) ** power
+    mask = m / (m + r)
+    return torch.where(bad, torch.full((), 0.5 if split_zeros else 0.0), mask)
+
+
+def hpss(D, ks=31, power=2.0, margin=1.0):
+    """rosa/spectral.py:145-161 on a complex STFT [F, T]."""
+    S = D.abs()
+    phase = torch.exp(1j * torch.angle(D))
+    harm = median_filter_1d(S, ks, dim=1)   # along time
+    perc = median_filter_1d(S, ks, dim=0)   # along frequency
+    split = margin == 1
+    mh = softmask(harm, perc * margin, power, split)
+    mp = softmask(perc, harm * margin, power, split)
+    return (S * mh) * phase, (S * mp) * phase
+
+
+def harmonic(y, margin=8.0):
+    """features/audio.py:13-17."""
+    return istft(hpss(stft(y), margin=margin)[0], length=len(y))
+
+
+def percussive(y, margin=8.0):
+    """features/audio.py:20-24."""
+    return istft(hpss(stft(y), margin=margin)[1], length=len(y))
+
+
+# ----------------------------------------------------------------------------------------------
+# IIR band splits and resampling (third-party torchaudio algorithms restated; torchaudio is unpinned by env.yaml)
+# ----------------------------------------------------------------------------------------------
+def biquad_design(kind, sr, fc, Q=0.707):
+    """torchaudio lowpass_biquad / highpass_biquad: RBJ cookbook, coefficient arithmetic in fp32."""
+    w0 = torch.tensor(2 * math.pi * fc / sr, dtype=torch.float32)
+    w0 = 2 * math.pi * torch.tensor(fc, dtype=torch.float32) / sr
+    alpha = torch.sin(w0) / 2 / torch.tensor(Q, dtype=torch.float32)
+    c = torch.cos(w0)
+    if kind == "low":
+        b = [(1 - c) / 2, 1 - c, (1 - c) / 2]
+    else:
+        b = [(1 + c) / 2, -1 - c, (1 + c) / 2]
+    a = [1 + alpha, -2 * c, 1 - alpha]
+    return np.array([float(v / a[0]) for v in b], np.float32), np.array([float(v / a[0]) for v in a], np.float32)
+
+
+def lfilter_clamped(x, b, a):
+    """torchaudio lfilter(clamp=True): direct-form recurrence from a zero state, output clamped to [-1, 1]."""
+    from scipy.signal import lfilter
+
+    y = lfilter(b.astype(np.float64), a.astype(np.float64), x.numpy().astype(np.float64))
+    return torch.from_numpy(np.clip(y, -1.0, 1.0).astype(np.float32))
+
+
+def low_pass(x, sr, fmax=200):
+    """features/processing.py:141-142."""
+    return lfilter_clamped(x, *biquad_design("low", sr, fmax))
+
+
+def high_pass(x, sr, fmin=4000):
+    """features/processing.py:149-150."""
+    return lfilter_clamped(x, *biquad_design("high", sr, fmin))
+
+
+def mid_pass(x, sr, fmin=200, fmax=4000):
+    """features/processing.py:145-146 (high-pass at fmax, then low-pass at fmin — as written in the reference)."""
+    return low_pass(high_pass(x, sr, fmax), sr, fmin)
+
+
+def sinc_resample_kernel(orig, new, method="hann", zeros=6, rolloff=0.99, beta=14.769656459379492):
+    """torchaudio _get_sinc_resample_kernel (fp32, as reached from resample(fp32 waveform))."""
+    base = min(orig, new) * rolloff
+    width = math.ceil(zeros * orig / base)
+    idx = torch.arange(-width, width + orig, dtype=torch.float32)[None] / orig
+    t = (torch.arange(0, -new, -1, dtype=torch.float32)[:, None] / new + idx) * base
+    t = t.clamp(-zeros, zeros)
+    if method == "hann":
+        win = torch.cos(t * math.pi / zeros / 2) ** 2
+    else:
+        bt = torch.tensor(float(beta))
+        win = torch.i0(bt * torch.sqrt(1 - (t / zeros) ** 2)) / torch.i0(bt)
+    t = t * math.pi
+    k = torch.where(t == 0, torch.ones(()), torch.sin(t) / t) * win * (base / orig)
+    return k, width
+
+
+def resample(x, orig_freq, new_freq, method="hann"):
+    """torchaudio.functional.resample (supervised/data.py:63, rosa/constantq.py:83)."""
+    g = math.gcd(int(orig_freq), int(new_freq))
+    orig, new = int(orig_freq) // g, int(new_freq) // g
+    k, width = sinc_resample_kernel(orig, new, method)
+    n = x.shape[-1]
+    xp = torch.nn.functional.pad(x.float()[None, None], (width, width + orig))
+    y = torch.nn.functional.conv1d(xp, k[:, None], stride=orig)  # [1, new, blocks]
+    y = y[0].T.reshape(-1)
+    return y[: math.ceil(new * n / orig)]

@@ -14,6 +14,7 @@ LIB_PATH = Path(__file__).resolve().parent / "libssar_b200.so"
 
 _lib = None
 launch_count = 0  # number of C-ABI kernel entry points invoked (bench.py reports it as gpu_launches)
+event_log = None  # optional {entry point name: [(start_event, stop_event), ...]} filled by call()
 
 
 class SsarError(RuntimeError):
@@ -59,6 +60,7 @@ def lib():
             )
         _lib = C.CDLL(str(LIB_PATH))
         _lib.ssar_last_error.restype = C.c_char_p
+        _lib.ssar_biquad_scratch_bytes.restype = C.c_longlong
         if _lib.ssar_abi_version() != 1:
             raise SsarError("libssar_b200.so ABI version mismatch; rebuild")
     return _lib
@@ -81,7 +83,15 @@ def call(name: str, *args):
     """Invoke a C-ABI entry point on the current CUDA stream and raise on a non-zero status."""
     global launch_count
     fn = getattr(lib(), name)
-    rc = fn(*args, stream_ptr())
+    log = event_log.get(name) if event_log else None
+    if log is not None:  # bench.py: CUDA events on the launching stream around exactly this launch
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        rc = fn(*args, stream_ptr())
+        e1.record()
+        log.append((e0, e1))
+    else:
+        rc = fn(*args, stream_ptr())
     launch_count += 1
     if rc != 0:
         raise SsarError(f"{name} failed ({rc}): {lib().ssar_last_error().decode()}")

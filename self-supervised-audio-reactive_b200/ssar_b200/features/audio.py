@@ -7,6 +7,33 @@ from .. import ops, plan
 from .rosa.beat import onset_strength  # noqa: F401  (re-exported like the reference)
 
 
+def hpss_waveforms(audio, margin=8.0, want_harm=True, want_perc=True, n_fft=2048, hop_length=1024):
+    """stft -> hpss masks -> istft for both components with ONE forward STFT and ONE median pass.
+
+    The reference runs the whole chain twice (harmonic(audio), percussive(audio)); the two results only differ in
+    which mask is applied, so sharing the STFT and the medians is exact."""
+    squeeze = audio.dim() == 1
+    n = audio.shape[-1]
+    D = ops.frames_fft(audio, n_fft, hop_length, 1 + n // hop_length, torch.hann_window, want_complex=True)["complex"]
+    h, p = ops.hpss(D, float(margin), want_harm, want_perc)
+    yh = ops.istft(h, n_fft, hop_length, torch.hann_window, n) if want_harm else None
+    yp = ops.istft(p, n_fft, hop_length, torch.hann_window, n) if want_perc else None
+    if squeeze:
+        yh = yh[0] if yh is not None else None
+        yp = yp[0] if yp is not None else None
+    return yh, yp
+
+
+def harmonic(audio, margin=8.0):
+    """features/audio.py:13-17."""
+    return hpss_waveforms(audio, margin, True, False)[0]
+
+
+def percussive(audio, margin=8.0):
+    """features/audio.py:20-24."""
+    return hpss_waveforms(audio, margin, False, True)[1]
+
+
 def rms(y, sr, frame_length=2048, hop_length=1024, center=True, pad_mode="reflect"):
     """features/audio.py:31-37 -> [T,1]: sqrt(mean(x^2)) over reflect-padded frames, last frame dropped."""
     if not center or pad_mode != "reflect":

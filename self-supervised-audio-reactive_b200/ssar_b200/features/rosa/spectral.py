@@ -73,3 +73,34 @@ def mel_frequencies(n_mels=128, fmin=0.0, fmax=11025.0, htk=False, device="cpu")
     lo = plan.hz_to_mel_f32(torch.tensor(float(fmin)))
     hi = plan.hz_to_mel_f32(torch.tensor(float(fmax)))
     return plan.mel_to_hz_f32(torch.linspace(float(lo), float(hi), n_mels)).to(device)
+
+
+def _fm(spec):
+    """reference-layout complex [F,T] / [B,F,T] -> frame-major real view [B,T,F,2] (copies only if needed)"""
+    squeeze = spec.dim() == 2
+    if squeeze:
+        spec = spec[None]
+    fm = torch.view_as_real(spec.transpose(1, 2).contiguous())
+    return fm, squeeze
+
+
+def istft(spec, n_fft=2048, hop_length=1024, center=True, window=torch.hann_window, length=None):
+    """rosa/spectral.py:24-32 (torch.istft, center=True).  spec: complex [F, T] or [B, F, T]."""
+    if not center:
+        raise NotImplementedError("istft: only center=True is built")
+    fm, squeeze = _fm(spec)
+    out = ops.istft(fm, n_fft, hop_length, window, length)
+    return out[0] if squeeze else out
+
+
+def hpss(S, ks=31, power=2.0, margin=1.0):
+    """rosa/spectral.py:145-161 on a complex STFT [F, T] -> (harmonic, percussive) complex STFTs."""
+    if ks != 31 or power != 2.0:
+        raise NotImplementedError("hpss: only ks=31, power=2 (the reference's only use) is built")
+    if not torch.is_complex(S):
+        raise NotImplementedError("hpss: complex STFT input expected")
+    fm, squeeze = _fm(S)
+    h, p = ops.hpss(fm, float(margin))
+    h = _ft(torch.view_as_complex(h), squeeze)
+    p = _ft(torch.view_as_complex(p), squeeze)
+    return h, p

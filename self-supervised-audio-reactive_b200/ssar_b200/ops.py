@@ -170,6 +170,54 @@ def power_to_db(x: torch.Tensor, n_clips: int = 1, top_db: float | None = 80.0, 
     return out
 
 
+def hpss(stft_fm: torch.Tensor, margin: float = 1.0, want_harm: bool = True, want_perc: bool = True):
+    """stft_fm: frame-major complex STFT as real view [B, T1, F, 2].  Returns (harm, perc) in the same layout."""
+    B, T1, F, _ = stft_fm.shape
+    h = torch.empty_like(stft_fm) if want_harm else None
+    p = torch.empty_like(stft_fm) if want_perc else None
+    cabi.call("ssar_hpss", ptr(stft_fm), i32(B), i32(T1), i32(F), i64(F), f32(margin), f32(margin), ptr(h), ptr(p))
+    return h, p
+
+
+def istft(spec_fm: torch.Tensor, n_fft: int, hop: int, window=torch.hann_window, length: int | None = None):
+    """spec_fm: frame-major complex [B, T1, F, 2] -> waveform [B, length] (torch.istft semantics, center=True)."""
+    B, T1, F, _ = spec_fm.shape
+    dev = spec_fm.device
+    if length is None:
+        length = hop * (T1 - 1)
+    win = plan.window_tensor(window, n_fft, dev)
+    frames = torch.empty(B, T1, n_fft, dtype=torch.float32, device=dev)
+    cabi.call("ssar_irfft_frames", ptr(spec_fm), i64(F), i32(B), i32(T1), i32(n_fft), ptr(win),
+              ptr(plan.twiddle(n_fft, str(dev))), ptr(frames))
+    out = torch.empty(B, length, dtype=torch.float32, device=dev)
+    cabi.call("ssar_overlap_add", ptr(frames), ptr(win), i32(B), i32(T1), i32(n_fft), i32(hop), i64(length), ptr(out))
+    return out
+
+
+def biquad(x: torch.Tensor, coeffs, clamp: bool = True):
+    """x [B, N]; coeffs = (b0, b1, b2, a1, a2) already normalised by a0 (torchaudio lfilter semantics)."""
+    x, _ = _as_batch(x)
+    B, N = x.shape
+    y = torch.empty(B, N, dtype=torch.float32, device=x.device)
+    nbytes = cabi.lib().ssar_biquad_scratch_bytes(C.c_int(B), C.c_longlong(N))
+    scratch = torch.empty(max(int(nbytes), 8), dtype=torch.uint8, device=x.device)
+    b0, b1, b2, a1, a2 = coeffs
+    cabi.call("ssar_biquad", ptr(x), i64(N), i64(x.stride(0)), i32(B), f32(b0), f32(b1), f32(b2), f32(a1), f32(a2),
+              i32(1 if clamp else 0), ptr(y), i64(N), ptr(scratch))
+    return y
+
+
+def resample(x: torch.Tensor, rp, post_scale: float = 1.0):
+    """x [B, N] -> [B, ceil(new*N/orig)] with a `plan.ResamplePlan`."""
+    x, _ = _as_batch(x)
+    B, N = x.shape
+    n_out = -((-rp.new * N) // rp.orig)
+    y = torch.empty(B, n_out, dtype=torch.float32, device=x.device)
+    cabi.call("ssar_resample", ptr(x), i64(N), i64(x.stride(0)), i32(B), ptr(rp.taps), ptr(rp.first), i32(rp.orig),
+              i32(rp.new), i32(rp.width), i32(rp.max_taps), f32(post_scale), ptr(y), i64(n_out), i64(n_out))
+    return y
+
+
 def frames_rms(x: torch.Tensor, frame_length: int, hop: int, n_frames: int):
     """features/audio.py:31-37 -> [B, n_frames]."""
     x, _ = _as_batch(x)

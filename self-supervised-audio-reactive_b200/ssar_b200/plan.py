@@ -143,3 +143,83 @@ def dct_matrix(n_out: int, n_in: int, device) -> torch.Tensor:
     d[0] *= 1.0 / np.sqrt(n_in)
     d[1:] *= np.sqrt(2.0 / n_in)
     return torch.from_numpy(d.astype(np.float32)).to(_dev(device))
+
+
+# ------------------------------------------------------------------------------------------------
+# torchaudio-style windowed-sinc resampling taps (algorithm of torchaudio.functional._get_sinc_resample_kernel,
+# third-party / unpinned by the reference; evaluated in fp32 exactly like `resample(waveform_fp32, ...)` does)
+# ------------------------------------------------------------------------------------------------
+@dataclass(frozen=True)
+class ResamplePlan:
+    orig: int
+    new: int
+    width: int
+    max_taps: int
+    taps: torch.Tensor   # fp32 [max_taps, new] (tap-major)
+    first: torch.Tensor  # int32 [new]
+
+
+def sinc_kernel_cpu(orig: int, new: int, method: str = "sinc_interp_hann", lowpass_filter_width: int = 6,
+                    rolloff: float = 0.99, beta: float = 14.769656459379492):
+    """Dense [new, 2*width+orig] fp32 kernel + width, same fp32 op order as torchaudio."""
+    base_freq = min(orig, new) * rolloff
+    width = math.ceil(lowpass_filter_width * orig / base_freq)
+    idx = torch.arange(-width, width + orig, dtype=torch.float32)[None, :] / orig
+    t = torch.arange(0, -new, -1, dtype=torch.float32)[:, None] / new + idx
+    t *= base_freq
+    t = t.clamp_(-lowpass_filter_width, lowpass_filter_width)
+    if method in ("sinc_interp_hann", "sinc_interpolation"):
+        window = torch.cos(t * math.pi / lowpass_filter_width / 2) ** 2
+    elif method in ("sinc_interp_kaiser", "kaiser_window"):
+        b = torch.tensor(float(beta))
+        window = torch.i0(b * torch.sqrt(1 - (t / lowpass_filter_width) ** 2)) / torch.i0(b)
+    else:
+        raise ValueError(method)
+    t *= math.pi
+    scale = base_freq / orig
+    k = torch.where(t == 0, torch.tensor(1.0), t.sin() / t)
+    k *= window * scale
+    inside = (t.abs() < lowpass_filter_width * math.pi)  # un-clamped region; the clamped tail is ~1e-20
+    return k, width, inside
+
+
+@functools.lru_cache(maxsize=None)
+def resample_plan(orig_freq: int, new_freq: int, method: str, device) -> ResamplePlan:
+    if int(orig_freq) != orig_freq or int(new_freq) != new_freq:
+        raise ValueError("Frequencies must be whole numbers (torchaudio raises on fractional rates)")
+    g = math.gcd(int(orig_freq), int(new_freq))
+    orig, new = int(orig_freq) // g, int(new_freq) // g
+    k, width, inside = sinc_kernel_cpu(orig, new, method)
+    kw = k.shape[1]
+    if kw <= 64:  # small kernels (the /2 kaiser decimator: 28 taps) keep every tap, clamped tail included
+        inside = torch.ones_like(inside)
+    any_in = inside.any(dim=1)
+    first = torch.where(any_in, inside.float().argmax(dim=1), torch.zeros(new, dtype=torch.long))
+    last = torch.where(any_in, kw - 1 - inside.flip(1).float().argmax(dim=1), torch.zeros(new, dtype=torch.long))
+    max_taps = int((last - first + 1).max())
+    cols = first[:, None] + torch.arange(max_taps)[None, :]
+    valid = cols <= last[:, None]
+    taps = torch.where(valid, k.gather(1, cols.clamp(max=kw - 1)), torch.zeros(()))
+    dev = _dev(device)
+    return ResamplePlan(orig, new, width, max_taps, taps.T.contiguous().to(dev), first.to(torch.int32).to(dev))
+
+
+def biquad_coeffs(kind: str, sample_rate, cutoff_freq, Q: float = 0.707):
+    """torchaudio lowpass_biquad / highpass_biquad coefficient design in fp32 tensors, normalised by a0."""
+    cutoff = torch.as_tensor(cutoff_freq, dtype=torch.float32)
+    Qt = torch.as_tensor(Q, dtype=torch.float32)
+    w0 = 2 * math.pi * cutoff / sample_rate
+    alpha = torch.sin(w0) / 2 / Qt
+    if kind == "low":
+        b0 = (1 - torch.cos(w0)) / 2
+        b1 = 1 - torch.cos(w0)
+    elif kind == "high":
+        b0 = (1 + torch.cos(w0)) / 2
+        b1 = -1 - torch.cos(w0)
+    else:
+        raise ValueError(kind)
+    b2 = b0
+    a0 = 1 + alpha
+    a1 = -2 * torch.cos(w0)
+    a2 = 1 - alpha
+    return tuple(float(v) for v in (b0 / a0, b1 / a0, b2 / a0, a1 / a0, a2 / a0))

@@ -79,7 +79,28 @@ def g_frame_features(ref):
     )
 
 
-GROUPS = {"spectral": g_spectral, "frame_features": g_frame_features}
+def g_hpss_filters(ref):
+    """HPSS waveforms, biquad band splits and the entry resampler on short clips."""
+    n = SR * 2 + 300
+    x = synth_clip(n, SR, 3)
+    D = ref.spectral.stft(x)
+    H, P = ref.spectral.hpss(D, margin=8.0)
+    save(
+        "hpss_filters", n=n, sr=SR, clip_index=3,
+        hpss_h_abs=H.abs()[::4], hpss_p_abs=P.abs()[::4],
+        harmonic=ref.audio.harmonic(x), percussive=ref.audio.percussive(x),
+        low=ref.processing.low_pass(x, SR), mid=ref.processing.mid_pass(x, SR), high=ref.processing.high_pass(x, SR),
+    )
+    import torchaudio
+
+    n2 = 44100 + 17
+    x2 = synth_clip(n2, 44100, 4)
+    y2 = torchaudio.functional.resample(x2, 44100, SR)
+    y3 = torchaudio.functional.resample(y2, SR, SR / 2, resampling_method="kaiser_window")
+    save("resample", n=n2, clip_index=4, to24576=y2, half_kaiser=y3)
+
+
+GROUPS = {"spectral": g_spectral, "frame_features": g_frame_features, "hpss_filters": g_hpss_filters}
 
 if __name__ == "__main__":
     torch.manual_seed(0)

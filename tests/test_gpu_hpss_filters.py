@@ -1,0 +1,90 @@
+"""GPU parity: HPSS (31-tap medians + soft masks), ISTFT, biquad scan, polyphase resampler."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN, rel_l2
+from ssar_b200.synth import synth_clip
+from ssar_oracle import dsp
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+
+
+def load(name):
+    return {k: torch.from_numpy(np.asarray(v)) for k, v in np.load(GOLDEN / f"{name}.npz").items()}
+
+
+def test_hpss_masks_and_waveforms_vs_golden():
+    from ssar_b200.features import audio
+    from ssar_b200.features.rosa import spectral
+
+    g = load("hpss_filters")
+    sr = int(g["sr"])
+    x = synth_clip(int(g["n"]), sr, int(g["clip_index"]))
+    xd = x.cuda()
+    H, P = spectral.hpss(spectral.stft(xd), margin=8.0)
+    assert rel_l2(H.abs()[::4], g["hpss_h_abs"]) < TOL and rel_l2(P.abs()[::4], g["hpss_p_abs"]) < TOL
+    Ho, Po = dsp.hpss(dsp.stft(x), margin=8.0)
+    assert rel_l2(torch.view_as_real(H.cpu().contiguous()), torch.view_as_real(Ho.contiguous())) < TOL
+    assert rel_l2(torch.view_as_real(P.cpu().contiguous()), torch.view_as_real(Po.contiguous())) < TOL
+    yh, yp = audio.harmonic(xd), audio.percussive(xd)
+    assert tuple(yh.shape) == tuple(x.shape)
+    assert rel_l2(yh, g["harmonic"]) < TOL and rel_l2(yp, g["percussive"]) < TOL
+    # margin 1 exercises the split_zeros branch (rosa/spectral.py:158)
+    H1, P1 = spectral.hpss(spectral.stft(xd), margin=1.0)
+    H1o, P1o = dsp.hpss(dsp.stft(x), margin=1.0)
+    assert rel_l2(H1.abs(), H1o.abs()) < TOL and rel_l2(P1.abs(), P1o.abs()) < TOL
+
+
+def test_istft_roundtrip_and_batch():
+    from ssar_b200.features.rosa import spectral
+
+    xs = torch.stack([synth_clip(24576 + 123, 24576, i) for i in range(3)]).cuda()
+    D = spectral.stft(xs)
+    y = spectral.istft(D, length=xs.shape[-1])
+    assert tuple(y.shape) == tuple(xs.shape) and rel_l2(y, xs) < 1e-5
+    # 1024-point path with hop 1 (the PLP configuration, rosa/beat.py:69)
+    e = synth_clip(1500, 24, 5).abs().cuda()
+    De = spectral.stft(e, n_fft=1024, hop_length=1)
+    ye = spectral.istft(De, n_fft=1024, hop_length=1, length=1500)
+    ref = dsp.istft(dsp.stft(e.cpu(), 1024, 1), 1024, 1, length=1500)
+    assert rel_l2(ye, ref) < TOL and rel_l2(ye, e) < 1e-4
+
+
+def test_biquads_vs_golden_and_long_clip():
+    from ssar_b200.features import processing
+
+    g = load("hpss_filters")
+    sr = int(g["sr"])
+    x = synth_clip(int(g["n"]), sr, int(g["clip_index"]))
+    xd = x.cuda()
+    assert rel_l2(processing.low_pass(xd, sr), g["low"]) < TOL
+    assert rel_l2(processing.high_pass(xd, sr), g["high"]) < TOL
+    assert rel_l2(processing.mid_pass(xd, sr), g["mid"]) < TOL
+    # long clip (many chunks per scan thread), batched, odd length, includes clamping
+    xs = torch.stack([synth_clip(24576 * 60 + 37, 24576, i) for i in (6, 7)]) * 1.5
+    for fn, ofn in [(processing.low_pass, dsp.low_pass), (processing.high_pass, dsp.high_pass)]:
+        y = fn(xs.cuda(), 24576)
+        assert float(y.abs().max()) <= 1.0
+        for b in range(2):
+            assert rel_l2(y[b], ofn(xs[b], 24576)) < TOL
+    # 44.1 kHz, 200 Hz low-pass: pole radius closer to 1 (slow decay across chunk boundaries)
+    x44 = synth_clip(44100 * 20 + 5, 44100, 8)
+    assert rel_l2(processing.low_pass(x44.cuda(), 44100, 60), dsp.low_pass(x44, 44100, 60)) < TOL
+
+
+def test_resample_vs_golden():
+    from ssar_b200.resampling import resample
+
+    g = load("resample")
+    x = synth_clip(int(g["n"]), 44100, int(g["clip_index"]))
+    y = resample(x.cuda(), 44100, 24576)
+    assert tuple(y.shape) == tuple(g["to24576"].shape)
+    assert rel_l2(y, g["to24576"]) < 1e-5
+    y2 = resample(g["to24576"].cuda(), 24576, 12288, "kaiser_window")
+    assert tuple(y2.shape) == tuple(g["half_kaiser"].shape) and rel_l2(y2, g["half_kaiser"]) < 1e-5
+    xs = torch.stack([synth_clip(50001, 48000, i) for i in (1, 2)])
+    yb = resample(xs.cuda(), 48000, 24576)
+    for b in range(2):
+        assert rel_l2(yb[b], dsp.resample(xs[b], 48000, 24576)) < 1e-5

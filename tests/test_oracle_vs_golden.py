@@ -61,3 +61,26 @@ def test_istft_roundtrip():
     assert y.shape == x.shape and rel_l2(y, x) < 1e-6
     assert rel_l2(y, torch.istft(torch.stft(x, 2048, 1024, window=torch.hann_window(2048), return_complex=True),
                                  2048, 1024, window=torch.hann_window(2048), length=len(x))) < 1e-6
+
+
+def test_hpss_and_filters():
+    g = load("hpss_filters")
+    sr = int(g["sr"])
+    x = synth_clip(int(g["n"]), sr, int(g["clip_index"]))
+    H, P = dsp.hpss(dsp.stft(x), margin=8.0)
+    assert rel_l2(H.abs()[::4], g["hpss_h_abs"]) < TOL and rel_l2(P.abs()[::4], g["hpss_p_abs"]) < TOL
+    assert rel_l2(dsp.harmonic(x), g["harmonic"]) < 5e-6
+    assert rel_l2(dsp.percussive(x), g["percussive"]) < 5e-6
+    assert rel_l2(dsp.low_pass(x, sr), g["low"]) < 1e-5
+    assert rel_l2(dsp.high_pass(x, sr), g["high"]) < 1e-5
+    assert rel_l2(dsp.mid_pass(x, sr), g["mid"]) < 1e-5
+
+
+def test_resample():
+    g = load("resample")
+    x = synth_clip(int(g["n"]), 44100, int(g["clip_index"]))
+    y = dsp.resample(x, 44100, 24576)
+    assert y.shape == g["to24576"].shape  # ceil(2048 * N / 3675): exact length
+    assert rel_l2(y, g["to24576"]) < TOL
+    y2 = dsp.resample(g["to24576"], 24576, 12288, method="kaiser")
+    assert y2.shape == g["half_kaiser"].shape and rel_l2(y2, g["half_kaiser"]) < TOL
