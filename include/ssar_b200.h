@@ -70,6 +70,10 @@ typedef struct {
     float* out;             /* complex [n_clips, n_frames, ld] (re, im) */
     long long ld;           /* in complex elements */
     float scale;
+    const int* clip_slot;   /* optional [n_clips]: clip c uses table rows [clip_slot[c]*n_rows, +n_rows) (start/count/
+                               offset hold n_slots*n_rows entries) - the per-clip tuned CQT bases */
+    const float* row_scale; /* optional: out[row] *= row_scale[slot*row_scale_ld + row] (CQT 1/sqrt(filter length)) */
+    long long row_scale_ld;
 } ssar_projection;
 
 typedef struct {
@@ -163,6 +167,101 @@ int ssar_biquad(const float* x, long long n_samples, long long stride_x, int n_c
 int ssar_resample(const float* x, long long n_in, long long stride_in, int n_clips, const float* taps,
                   const int* first, int orig, int newf, int width, int max_taps, float post_scale, float* y,
                   long long n_out, long long stride_out, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Tuning estimate, chroma, CENS, tonnetz
+ * ---------------------------------------------------------------------------------------------- */
+
+/* rosa/pitch.py:27-83 piptrack on a magnitude spectrogram [n_clips, n_frames, ld] (n_bins valid bins): per frame,
+ * local maxima above threshold * column max inside bins [k_lo, k_hi), parabolic interpolation.  pitch / mag:
+ * dense [n_clips, n_frames, k_hi - k_lo] slots, zero where there is no peak. */
+int ssar_piptrack(const float* mag_spec, long long ld, int n_clips, int n_frames, int n_bins, int k_lo, int k_hi,
+                  float threshold, float sr, int n_fft, float* pitch, float* mag, void* stream);
+
+/* rosa/pitch.py:9-24 + :98-120 estimate_tuning tail: threshold = lower median of mag[pitch > 0]; histogram (n_hist bins
+ * with the n_hist + 1 `edges` of torch.linspace(-0.5, 0.5, n_hist + 1)) of the bins_per_octave residuals of the
+ * pitches with mag >= threshold; tuning_idx[clip] = arg-max bin, tuning_val[clip] = edges[arg-max]. */
+int ssar_tuning_from_peaks(const float* pitch, const float* mag, int n_clips, long long n_per_clip,
+                           const float* edges, int n_hist, float bins_per_octave, int* tuning_idx,
+                           float* tuning_val, void* stream);
+
+/* rosa/spectral.py:286-325 chroma_cqt (norm=False) and, with quantize != 0, the first half of chroma_cens
+ * (:264-271): |cqt| [n_clips, n_frames, ldc] complex -> fold bins onto chroma_of_bin[n_bins] classes -> (L1 norm ->
+ * spline map with the natural-cubic-spline table (knots[n_knots], a, b, c, d [n_knots-1]; c, d used as written in
+ * :192-202) -> sigmoid staircase step_h * (floor(w-.5) + ...)).  out: [n_clips, n_frames, n_chroma]. */
+int ssar_chroma_from_cqt(const float* cqt, long long ldc, int n_clips, int n_frames, int n_bins,
+                         const int* chroma_of_bin, int n_chroma, int quantize, const float* knots,
+                         const float* sa, const float* sb, const float* sc, const float* sd, int n_knots,
+                         float step_h, float step_alpha, float* out, void* stream);
+
+/* rosa/spectral.py:273-280: correlation along time with window[win_len] (already normalised), zero "same" padding,
+ * then (l2_normalize) division by the per-frame L2 norm.  q, out: [n_clips, n_frames, n_chroma]. */
+int ssar_cens_smooth(const float* q, int n_clips, int n_frames, int n_chroma, const float* window, int win_len,
+                     int l2_normalize, float* out, void* stream);
+
+/* features/audio.py:48-57 tonnetz: out[row] = phi[n_out, n_chroma] @ (chroma[row] / ||chroma[row]||_1) */
+int ssar_tonnetz(const float* chroma, long long n_rows, int n_chroma, const float* phi, int n_out, float* out,
+                 void* stream);
+
+/* features/audio.py:72-123 spectral_contrast, step 1: per (frame, band) mean of the band_q smallest (valley) and
+ * largest (peak) magnitudes of bins [band_start, band_start + band_count) of mag [n_clips, n_frames, ld]; the
+ * clip-global maxima of both are merged into keys (ssar_fill_u32 them with the key of -inf first).
+ * peak, valley: [n_clips, n_frames, n_bands]. band_q <= 32 and <= band_count; max_count = max(band_count). */
+int ssar_contrast_bands(const float* mag, long long ld, int n_clips, int n_frames, int n_bands,
+                        const int* band_start, const int* band_count, const int* band_q, int max_count,
+                        float* peak, float* valley, uint32_t* peak_key, uint32_t* valley_key, void* stream);
+
+/* step 2: out = power_to_db(peak) - power_to_db(valley) (each floored at its own clip maximum - top_db), or
+ * peak - valley when linear != 0 (features/audio.py:120-123) */
+int ssar_contrast_finish(const float* peak, const float* valley, const uint32_t* peak_key,
+                         const uint32_t* valley_key, int n_clips, long long n_per_clip, int linear, float top_db,
+                         float* out, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Post-processing of feature matrices [n_clips, n_frames, n_cols] (time-major, columns contiguous)
+ * ---------------------------------------------------------------------------------------------- */
+
+/* features/processing.py:10-48 gaussian_filter along time of [n_clips, n_frames, inner]: weights [2*radius+1] are
+ * the normalised taps (built by the host exactly like :21-24); mode 0 circular (default), 1 reflect, 2 replicate;
+ * radius > n_frames reproduces the short-sequence branch (:30-35: mode-pad by n_frames, then replicate). */
+int ssar_gauss1d(const float* x, int n_clips, int n_frames, long long inner, const float* weights, int radius,
+                 int mode, float* out, void* stream);
+
+/* per-(clip, column) minimum / maximum -> [n_clips, n_cols] (either output may be NULL) */
+int ssar_col_minmax(const float* x, int n_clips, int n_frames, int n_cols, float* min_out, float* max_out,
+                    void* stream);
+
+/* per-(clip, column) quantile by radix select (exact order statistics).
+ *   subset 0: all non-NaN values; 1: strict interior local maxima (features/processing.py:107-115)
+ *   interp 0: torch.quantile "linear" (:117,125,129,137); 3: efficient_quantile midpoint
+ *             (ssar/analysis/efficient_quantile/efficient_quantile.cpp:72-75, wrapper __init__.py:5-6)
+ *   pre_sub/pre_div [n_clips, n_cols] or NULL: select on (x - pre_sub) / pre_div (emphasize, :133-137)
+ *   count_out [n_clips, n_cols] or NULL: size of the subset (0 -> out = NaN; the host raises like torch) */
+int ssar_col_quantile(const float* x, int n_clips, int n_frames, int n_cols, int subset, double q, int interp,
+                      const float* pre_sub, const float* pre_div, float* out, int* count_out, void* stream);
+
+/* torch.clamp by per-(clip, column) bounds [n_clips, n_cols] (features/processing.py:117,124-129) */
+int ssar_clamp_cols(const float* x, int n_clips, int n_frames, int n_cols, const float* lo, const float* hi,
+                    float* out, void* stream);
+
+/* features/processing.py:52-55 normalize over each whole clip: (x - min) / ((max - min) + eps); keys from
+ * ssar_minmax_keys */
+int ssar_normalize(const float* x, int n_clips, long long n_per_clip, const uint32_t* min_key,
+                   const uint32_t* max_key, float eps, float* out, void* stream);
+
+/* features/processing.py:132-138 emphasize; col_min/col_max from ssar_col_minmax; scratch: 2*n_clips*n_cols floats */
+int ssar_emphasize(const float* x, int n_clips, int n_frames, int n_cols, const float* col_min,
+                   const float* col_max, float strength, double q, float* scratch, float* out, void* stream);
+
+/* features/processing.py:88-89 spectral_flux: out[t] = x[t+1] - x[t] with a zero row appended */
+int ssar_spectral_flux(const float* x, int n_clips, int n_frames, long long inner, float* out, void* stream);
+
+/* features/processing.py:92: out[row] = sum_j 0.5 * (x + |x|) */
+int ssar_hwr_rowsum(const float* x, long long n_rows, int inner, float* out, void* stream);
+
+/* ssar/supervised/data.py:317-319 dataset statistics: accumulates (count, sum, sum of squares) per column in fp64
+ * into stats[3, n_cols] (caller zeroes it; all-reduce it over ranks, then mean = s/n, std = sqrt(ss/n - mean^2)) */
+int ssar_feature_stats(const float* x, long long n_rows, int n_cols, double* stats, void* stream);
 
 #ifdef __cplusplus
 }

@@ -161,6 +161,34 @@ def spectral_flatness(y, sr=None, n_fft=2048, hop_length=1024, amin=1e-10, power
     return (torch.exp(torch.mean(torch.log(S), dim=0)) / torch.mean(S, dim=0)).unsqueeze(-1)
 
 
+def spectral_contrast(y, sr, n_fft=2048, hop_length=1024, fmin=200.0, n_bands=6, quantile=0.02, linear=False):
+    """features/audio.py:72-123 -> [T, n_bands + 1]: octave bands with edges 0, fmin, 2 fmin, ...; each band also
+    takes the bin just below its lower edge (k > 0), the top band everything above; all but the top band drop their
+    last bin; q = max(1, round(quantile * bins_in_band)) extremes are averaged."""
+    S = spectrogram(y, n_fft, hop_length, power=1)
+    freq = torch.linspace(0, float(sr) / 2, 1 + n_fft // 2)
+    edges = torch.cat([torch.zeros(1), fmin * 2.0 ** torch.arange(0, n_bands + 1)])
+    peak, valley = [], []
+    for k in range(n_bands + 1):
+        inside = torch.nonzero((freq >= edges[k]) & (freq <= edges[k + 1])).flatten()
+        lo, hi = int(inside[0]), int(inside[-1])
+        if k > 0:
+            lo -= 1
+        if k == n_bands:
+            hi = len(freq) - 1
+        n_in_band = hi - lo + 1
+        if k < n_bands:
+            hi -= 1
+        q = max(1, int(torch.round(torch.tensor(quantile * n_in_band))))
+        srt = torch.sort(S[lo : hi + 1], dim=0).values
+        valley.append(srt[:q].mean(0))
+        peak.append(srt[-q:].mean(0))
+    peak, valley = torch.stack(peak), torch.stack(valley)
+    if linear:
+        return (peak - valley).T
+    return (power_to_db(peak) - power_to_db(valley)).T
+
+
 # ----------------------------------------------------------------------------------------------
 # harmonic / percussive separation
 # ----------------------------------------------------------------------------------------------

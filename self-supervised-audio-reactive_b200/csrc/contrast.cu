@@ -1,0 +1,134 @@
+// Spectral contrast (ssar/features/audio.py:72-123): per frame and per octave band, the mean of the q smallest
+// (valley) and q largest (peak) magnitude bins, then power_to_db(peak) - power_to_db(valley) where each power_to_db
+// floors at its own clip-global maximum - 80 dB (rosa/convert.py:7-12).
+//
+// Kernel 1: one warp per (frame, band).  The band's bins are staged in a per-warp shared-memory slab; the q extremes
+//   are extracted by q rounds of warp arg-min / arg-max (q <= 32; 1..10 at the reference's settings), which is the
+//   partial selection the reference's full torch.sort is used for.  Peak / valley maxima per clip are folded into
+//   order-preserving keys with one atomic per warp.
+// Kernel 2: elementwise dB difference with the two clip-global floors.
+#include "common.cuh"
+
+namespace {
+
+constexpr int WARPS = 8;
+
+__device__ __forceinline__ void warp_arg_reduce(float& v, int& i, bool want_min) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, v, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, i, o);
+        const bool better = want_min ? (ov < v) : (ov > v);
+        if (better || (ov == v && oi < i)) {
+            v = ov;
+            i = oi;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(WARPS * 32) contrast_bands_kernel(
+    const float* __restrict__ mag, long long ld, long long n_rows, int n_frames, int nb, const int* __restrict__ start,
+    const int* __restrict__ count, const int* __restrict__ qn, int slab, float* __restrict__ peak,
+    float* __restrict__ valley, uint32_t* __restrict__ peak_key, uint32_t* __restrict__ valley_key) {
+    extern __shared__ float sm[];
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    float* s = sm + (size_t)w * slab;
+    const long long tasks = n_rows * nb;
+    for (long long task = (long long)blockIdx.x * WARPS + w; task < tasks; task += (long long)gridDim.x * WARPS) {
+        const long long row = task / nb;
+        const int band = (int)(task - row * nb);
+        const int st = __ldg(start + band), n = __ldg(count + band), q = __ldg(qn + band);
+        const float* src = mag + row * ld + st;
+        for (int i = l; i < n; i += 32) s[i] = __ldg(src + i);
+        __syncwarp();
+        float sums[2];
+#pragma unroll
+        for (int side = 0; side < 2; ++side) {  // 0: q smallest (valley), 1: q largest (peak)
+            const bool want_min = side == 0;
+            const float sentinel = want_min ? INFINITY : -INFINITY;
+            float acc = 0.f, keep_v = 0.f;
+            int keep_i = -1;
+            for (int r = 0; r < q; ++r) {
+                float best = sentinel;
+                int bi = 0x7fffffff;
+                for (int i = l; i < n; i += 32) {
+                    const float v = s[i];
+                    if (want_min ? (v < best) : (v > best)) {
+                        best = v;
+                        bi = i;
+                    }
+                }
+                warp_arg_reduce(best, bi, want_min);
+                acc += best;
+                if (l == r) {  // lane r remembers what round r removed so the slab can be restored
+                    keep_v = best;
+                    keep_i = bi;
+                }
+                if (l == 0 && bi != 0x7fffffff) s[bi] = sentinel;
+                __syncwarp();
+            }
+            if (keep_i >= 0 && keep_i != 0x7fffffff) s[keep_i] = keep_v;
+            __syncwarp();
+            sums[side] = acc / (float)q;
+        }
+        if (l == 0) {
+            valley[row * nb + band] = sums[0];
+            peak[row * nb + band] = sums[1];
+            const int clip = (int)(row / n_frames);
+            atomic_max_key(valley_key + clip, sums[0]);
+            atomic_max_key(peak_key + clip, sums[1]);
+        }
+        __syncwarp();
+    }
+}
+
+__device__ __forceinline__ float db10(float x) { return 10.0f * log10f(fmaxf(1e-10f, x)); }
+
+__global__ void contrast_finish_kernel(const float* __restrict__ peak, const float* __restrict__ valley,
+                                       const uint32_t* __restrict__ peak_key, const uint32_t* __restrict__ valley_key,
+                                       long long n_per_clip, int linear, float top_db, float* __restrict__ out) {
+    const int clip = blockIdx.y;
+    const float pf = db10(key2f(peak_key[clip])) - top_db, vf = db10(key2f(valley_key[clip])) - top_db;
+    const long long base = (long long)clip * n_per_clip;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_per_clip; i += (long long)gridDim.x * blockDim.x) {
+        const float p = peak[base + i], v = valley[base + i];
+        out[base + i] = linear ? (p - v) : (fmaxf(db10(p), pf) - fmaxf(db10(v), vf));
+    }
+}
+
+}  // namespace
+
+extern "C" int ssar_contrast_bands(const float* mag, long long ld, int n_clips, int n_frames, int n_bands,
+                                   const int* band_start, const int* band_count, const int* band_q, int max_count,
+                                   float* peak, float* valley, uint32_t* peak_key, uint32_t* valley_key, void* stream) {
+    if (n_clips == 0 || n_frames == 0 || n_bands == 0) return SSAR_OK;
+    SSAR_REQUIRE(mag && band_start && band_count && band_q && peak && valley && peak_key && valley_key,
+                 "contrast_bands: null pointer");
+    SSAR_REQUIRE(max_count > 0 && max_count <= 4096, "contrast_bands: band wider than 4096 bins");
+    const size_t smem = (size_t)WARPS * max_count * sizeof(float);
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(contrast_bands_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) {
+            ssar_set_error("contrast_bands: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+            return SSAR_ERR_CUDA;
+        }
+    }
+    const long long rows = (long long)n_clips * n_frames;
+    long long grid = (rows * n_bands + WARPS - 1) / WARPS;
+    if (grid > (long long)SSAR_NUM_SMS * 8) grid = (long long)SSAR_NUM_SMS * 8;
+    contrast_bands_kernel<<<(unsigned)grid, WARPS * 32, smem, (cudaStream_t)stream>>>(
+        mag, ld, rows, n_frames, n_bands, band_start, band_count, band_q, max_count, peak, valley, peak_key, valley_key);
+    return ssar_launch_status("contrast_bands");
+}
+
+extern "C" int ssar_contrast_finish(const float* peak, const float* valley, const uint32_t* peak_key,
+                                    const uint32_t* valley_key, int n_clips, long long n_per_clip, int linear,
+                                    float top_db, float* out, void* stream) {
+    if (n_clips == 0 || n_per_clip == 0) return SSAR_OK;
+    SSAR_REQUIRE(peak && valley && peak_key && valley_key && out, "contrast_finish: null pointer");
+    int gx = ssar_div_up(n_per_clip, 256);
+    if (gx > SSAR_NUM_SMS * 4) gx = SSAR_NUM_SMS * 4;
+    contrast_finish_kernel<<<dim3(gx, n_clips), 256, 0, (cudaStream_t)stream>>>(peak, valley, peak_key, valley_key,
+                                                                              n_per_clip, linear, top_db, out);
+    return ssar_launch_status("contrast_finish");
+}

@@ -171,9 +171,11 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
         // ---- epilogue 3: banded complex projection of the complex spectrum (CQT basis)
         if (a.proj.n_rows > 0) {
             const ssar_projection& pj = a.proj;
+            const int slot = (pj.clip_slot && active) ? __ldg(pj.clip_slot + clip) : 0;
+            const int rb = slot * pj.n_rows;
             for (int r = lt; r < pj.n_rows; r += TPF) {
-                const int st = __ldg(pj.start + r), cn = __ldg(pj.count + r);
-                const float2* __restrict__ w = reinterpret_cast<const float2*>(pj.weights) + __ldg(pj.offset + r);
+                const int st = __ldg(pj.start + rb + r), cn = __ldg(pj.count + rb + r);
+                const float2* __restrict__ w = reinterpret_cast<const float2*>(pj.weights) + __ldg(pj.offset + rb + r);
                 float2 acc = make_float2(0.f, 0.f);
                 for (int k = 0; k < cn; ++k) {
                     const float2 wk = __ldg(w + k);
@@ -183,9 +185,10 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
                     acc.y = fmaf(wk.x, X.y, acc.y);
                     acc.y = fmaf(wk.y, X.x, acc.y);
                 }
+                const float sc = pj.row_scale ? pj.scale * __ldg(pj.row_scale + slot * pj.row_scale_ld + r) : pj.scale;
                 if (active)
                     reinterpret_cast<float2*>(pj.out)[((long long)clip * a.n_frames + t) * pj.ld + r] =
-                        make_float2(acc.x * pj.scale, acc.y * pj.scale);
+                        make_float2(acc.x * sc, acc.y * sc);
             }
         }
         __syncthreads();  // the next iteration overwrites s / pw / red

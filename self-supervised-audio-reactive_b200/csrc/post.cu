@@ -1,0 +1,355 @@
+// Post-processing of per-frame feature matrices [clip, T, C] (time-major, C contiguous):
+// Gaussian temporal smoothing, min/max normalisation, per-column order statistics (radix select), percentile
+// clamps, emphasize, spectral flux, and the per-column (count, sum, sum of squares) statistics that feed the
+// cross-GPU mean/std all-reduce.
+// Replaces ssar/features/processing.py:10-48 (gaussian_filter), :52-55 (normalize), :58-61 (standardize),
+// :88-98 (spectral_flux, onset_envelope), :101-129 (percentile clamps), :132-138 (emphasize) and the dataset
+// statistics of ssar/supervised/data.py:317-319.
+#include "block_utils.cuh"
+#include "select.cuh"
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------------------------
+// gaussian_filter: out[b,t,j] = sum_k w[k] * x[b, idx(t + k - r), j]
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int pad_index(int v, int T, int radius, int mode) {
+    if (radius > T) v = min(max(v, -T), 2 * T - 1);  // outer replicate pad of the short-sequence branch (:30-35)
+    if (mode == 0) {  // circular
+        v %= T;
+        if (v < 0) v += T;
+    } else if (mode == 1) {  // reflect (edge not repeated)
+        if (v < 0) v = -v;
+        if (v >= T) v = 2 * (T - 1) - v;
+        v = min(max(v, 0), T - 1);
+    } else {  // replicate
+        v = min(max(v, 0), T - 1);
+    }
+    return v;
+}
+
+constexpr int G_TPT = 4;  // consecutive time steps per thread (register sliding window)
+
+__global__ void gauss1d_kernel(const float* __restrict__ x, int T, long long inner, const float* __restrict__ w,
+                               int radius, int mode, float* __restrict__ out) {
+    extern __shared__ float ws[];
+    const int taps = 2 * radius + 1;
+    for (int i = threadIdx.x; i < taps; i += blockDim.x) ws[i] = w[i];
+    __syncthreads();
+    const int clip = blockIdx.z;
+    const float* xc = x + (long long)clip * T * inner;
+    float* oc = out + (long long)clip * T * inner;
+    const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= inner) return;
+    const int t0 = blockIdx.y * G_TPT;
+    float acc[G_TPT];
+#pragma unroll
+    for (int o = 0; o < G_TPT; ++o) acc[o] = 0.f;
+    // input rows t0 - r .. t0 + G_TPT - 1 + r; row i contributes to output o with tap k = i - o (relative indices)
+    for (int i = 0; i < taps + G_TPT - 1; ++i) {
+        const float v = __ldg(xc + (long long)pad_index(t0 + i - radius, T, radius, mode) * inner + j);
+#pragma unroll
+        for (int o = 0; o < G_TPT; ++o) {
+            const int k = i - o;
+            if (k >= 0 && k < taps) acc[o] = fmaf(ws[k], v, acc[o]);
+        }
+    }
+#pragma unroll
+    for (int o = 0; o < G_TPT; ++o)
+        if (t0 + o < T) oc[(long long)(t0 + o) * inner + j] = acc[o];
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// per-(clip, column) min / max of [clip, T, C]
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void col_minmax_kernel(const float* __restrict__ x, int T, int C, float* __restrict__ mn_out,
+                                  float* __restrict__ mx_out) {
+    __shared__ float scratch[32];
+    const int col = blockIdx.x, clip = blockIdx.y;
+    const float* xc = x + (long long)clip * T * C + col;
+    float mn = INFINITY, mx = -INFINITY;
+    for (int t = threadIdx.x; t < T; t += blockDim.x) {
+        const float v = xc[(long long)t * C];
+        mn = fminf(mn, v);
+        mx = fmaxf(mx, v);
+    }
+    mn = block_min(mn, scratch);
+    mx = block_max(mx, scratch);
+    if (threadIdx.x == 0) {
+        if (mn_out) mn_out[clip * C + col] = mn;
+        if (mx_out) mx_out[clip * C + col] = mx;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// per-(clip, column) quantile by MSB radix select on order-preserving keys.  One CTA per (column, clip).
+//   subset 0: every non-NaN element;  subset 1: strict interior local maxima (processing.py:107-115)
+//   interp 0: torch.quantile "linear" (rank = float(q) * (n - 1) in fp32, torch.lerp in fp32)
+//   interp 3: efficient_quantile midpoint (rank = double(float(q)) * (n - 1), trunc / ceil neighbours, mean in fp64)
+//   pre-transform: v -> (v - sub[col]) / div[col] when sub != NULL (emphasize's rescale, processing.py:133-136)
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void col_quantile_kernel(const float* __restrict__ x, int T, int C, int subset, double q, int interp,
+                                    const float* __restrict__ pre_sub, const float* __restrict__ pre_div,
+                                    float* __restrict__ out, int* __restrict__ count_out) {
+    __shared__ uint32_t hist[256];
+    __shared__ uint32_t bcast[2];
+    __shared__ int s_count;
+    const int col = blockIdx.x, clip = blockIdx.y;
+    SelectCtx c;
+    c.xc = x + (long long)clip * T * C + col;
+    c.T = T;
+    c.C = C;
+    c.aux = nullptr;
+    c.subset = subset;
+    c.pre = pre_sub != nullptr;
+    c.sub = c.pre ? pre_sub[clip * C + col] : 0.f;
+    c.div = c.pre ? pre_div[clip * C + col] : 1.f;
+    if (threadIdx.x == 0) s_count = 0;
+    __syncthreads();
+    int local = 0;
+    for (int t = threadIdx.x; t < T; t += blockDim.x) {
+        float v;
+        local += sel_value(c, t, v) ? 1 : 0;
+    }
+    if (local) atomicAdd(&s_count, local);
+    __syncthreads();
+    const int n = s_count;
+    if (count_out && threadIdx.x == 0) count_out[clip * C + col] = n;
+    if (n == 0) {  // torch.quantile raises on an empty input; efficient_quantile returns NaN. The host mirrors that.
+        if (threadIdx.x == 0) out[clip * C + col] = __int_as_float(0x7fc00000);
+        return;
+    }
+    long long lo, hi;
+    float w32 = 0.f;
+    if (interp == 0) {
+        const float rank = (float)q * (float)(n - 1);
+        const float below = floorf(rank);
+        lo = (long long)below;
+        hi = (long long)ceilf(rank);
+        w32 = rank - below;
+    } else {
+        const double rank = (double)(float)q * (double)(n - 1);
+        lo = (long long)rank;
+        hi = (long long)ceil(rank);
+    }
+    const float vlo = key2f(radix_select(c, lo, hist, bcast));
+    const float vhi = hi == lo ? vlo : key2f(radix_select(c, hi, hist, bcast));
+    if (threadIdx.x == 0) {
+        float r;
+        if (interp == 0) {  // ATen lerp: w < 0.5 ? a + w (b - a) : b - (b - a)(1 - w)
+            const float d = vhi - vlo;
+            r = w32 < 0.5f ? vlo + w32 * d : vhi - d * (1.f - w32);
+        } else {
+            const double delta = hi > lo ? 0.5 : 0.0;
+            const double a = (double)vlo, b = (double)vhi;
+            r = (float)(delta < 0.5 ? a + delta * (b - a) : b - (b - a) * (1.0 - delta));
+        }
+        out[clip * C + col] = r;
+    }
+}
+
+// clamp [clip, T, C] by per-(clip, column) bounds (either may be NULL)
+__global__ void clamp_cols_kernel(const float* __restrict__ x, long long n_per_clip, int C, const float* __restrict__ lo,
+                                  const float* __restrict__ hi, float* __restrict__ out) {
+    const int clip = blockIdx.y;
+    const float* xc = x + (long long)clip * n_per_clip;
+    float* oc = out + (long long)clip * n_per_clip;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_per_clip; i += (long long)gridDim.x * blockDim.x) {
+        const int col = (int)(i % C);
+        float v = xc[i];
+        // torch.clamp(min, max): min applied first, then max; NaN propagates
+        if (lo) v = (v != v) ? v : fmaxf(v, lo[clip * C + col]);
+        if (hi) v = (v != v) ? v : fminf(v, hi[clip * C + col]);
+        oc[i] = v;
+    }
+}
+
+// normalize (processing.py:52-55): (x - min) / ((max - min) + 1e-8) over the whole clip; min/max as keys
+__global__ void normalize_kernel(const float* __restrict__ x, long long n_per_clip, const uint32_t* __restrict__ min_key,
+                                 const uint32_t* __restrict__ max_key, float eps, float* __restrict__ out) {
+    const int clip = blockIdx.y;
+    const float mn = key2f(min_key[clip]);
+    const float den = (key2f(max_key[clip]) - mn) + eps;
+    const float* xc = x + (long long)clip * n_per_clip;
+    float* oc = out + (long long)clip * n_per_clip;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_per_clip; i += (long long)gridDim.x * blockDim.x)
+        oc[i] = (xc[i] - mn) / den;
+}
+
+// emphasize (processing.py:132-138): xn = (x - min)/max' ; xn * (1 + tanh(s (xn - qv))) * max' + min
+__global__ void emphasize_kernel(const float* __restrict__ x, long long n_per_clip, int C, const float* __restrict__ mn,
+                                 const float* __restrict__ rng, const float* __restrict__ qv, float strength,
+                                 float* __restrict__ out) {
+    const int clip = blockIdx.y;
+    const float* xc = x + (long long)clip * n_per_clip;
+    float* oc = out + (long long)clip * n_per_clip;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_per_clip; i += (long long)gridDim.x * blockDim.x) {
+        const int col = clip * C + (int)(i % C);
+        const float m = mn[col], r = rng[col];
+        float v = (xc[i] - m) / r;
+        v = v * (1.f + tanhf(strength * (v - qv[col])));
+        oc[i] = v * r + m;
+    }
+}
+
+// per-column range = max(x - min) (== max - min in fp32) from separate min / max arrays
+__global__ void range_kernel(const float* __restrict__ mn, const float* __restrict__ mx, int n, float* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = mx[i] - mn[i];
+}
+
+// spectral_flux (processing.py:88-89): out[t] = x[t+1] - x[t], last row = 0 - x[T-1]
+__global__ void flux_kernel(const float* __restrict__ x, int T, long long inner, float* __restrict__ out) {
+    const int clip = blockIdx.y;
+    const long long n = (long long)T * inner;
+    const float* xc = x + clip * n;
+    float* oc = out + clip * n;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float nxt = (i + inner < n) ? xc[i + inner] : 0.f;
+        oc[i] = nxt - xc[i];
+    }
+}
+
+// half-wave rectified row sums (processing.py:92): u[t] = sum_j 0.5 (f + |f|)
+__global__ void hwr_rowsum_kernel(const float* __restrict__ x, long long rows, int inner, float* __restrict__ out) {
+    const int warps = blockDim.x >> 5, w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    for (long long r = (long long)blockIdx.x * warps + w; r < rows; r += (long long)gridDim.x * warps) {
+        float acc = 0.f;
+        for (int j = l; j < inner; j += 32) {
+            const float f = x[r * inner + j];
+            acc += 0.5f * (f + fabsf(f));
+        }
+        acc = warp_sum(acc);
+        if (l == 0) out[r] = acc;
+    }
+}
+
+// (count, sum, sum of squares) per column in fp64, atomically accumulated into stats[3, C] (zeroed by the caller).
+// rows = n_clips * T flattened (the statistic is over all windows and frames, supervised/data.py:317-319).
+__global__ void feature_stats_kernel(const float* __restrict__ x, long long rows, int C, double* __restrict__ stats) {
+    // blockDim = (32, 8): x = column lane, y = row lane
+    for (int col = blockIdx.x * 32 + threadIdx.x; col < C; col += gridDim.x * 32) {
+        double s = 0.0, ss = 0.0;
+        long long cnt = 0;
+        for (long long r = (long long)blockIdx.y * blockDim.y + threadIdx.y; r < rows; r += (long long)gridDim.y * blockDim.y) {
+            const double v = (double)x[r * C + col];
+            s += v;
+            ss += v * v;
+            ++cnt;
+        }
+        atomicAdd(&stats[col], (double)cnt);
+        atomicAdd(&stats[C + col], s);
+        atomicAdd(&stats[2 * C + col], ss);
+    }
+}
+
+}  // namespace
+
+#define ST(s) reinterpret_cast<cudaStream_t>(s)
+
+extern "C" int ssar_gauss1d(const float* x, int n_clips, int n_frames, long long inner, const float* weights, int radius,
+                            int mode, float* out, void* stream) {
+    if (n_clips == 0 || n_frames == 0 || inner == 0) return SSAR_OK;
+    SSAR_REQUIRE(x && weights && out, "gauss1d: null pointer");
+    SSAR_REQUIRE(x != out, "gauss1d: in-place filtering is not supported");
+    SSAR_REQUIRE(radius >= 0 && radius <= 3 * n_frames, "gauss1d: radius must be <= 3 * n_frames");
+    SSAR_REQUIRE(mode >= 0 && mode <= 2, "gauss1d: mode must be 0 (circular), 1 (reflect) or 2 (replicate)");
+    SSAR_REQUIRE(mode != 1 || radius < n_frames, "gauss1d: reflect padding needs radius < n_frames");
+    SSAR_REQUIRE((2 * radius + 1) * sizeof(float) <= 200 * 1024, "gauss1d: kernel too long");
+    SSAR_REQUIRE(n_clips <= 65535, "gauss1d: too many clips per launch");
+    const int threads = inner >= 128 ? 128 : (inner >= 64 ? 64 : 32);
+    dim3 grid((unsigned)((inner + threads - 1) / threads), (unsigned)((n_frames + G_TPT - 1) / G_TPT), n_clips);
+    SSAR_REQUIRE(grid.y <= 65535, "gauss1d: too many frames per launch");
+    const size_t smem = (2 * radius + 1) * sizeof(float);
+    if (smem > 48 * 1024) cudaFuncSetAttribute(gauss1d_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    gauss1d_kernel<<<grid, threads, smem, ST(stream)>>>(x, n_frames, inner, weights, radius, mode, out);
+    return ssar_launch_status("gauss1d");
+}
+
+extern "C" int ssar_col_minmax(const float* x, int n_clips, int n_frames, int n_cols, float* min_out, float* max_out,
+                               void* stream) {
+    if (n_clips == 0 || n_cols == 0) return SSAR_OK;
+    SSAR_REQUIRE(x && n_frames > 0, "col_minmax: null pointer or empty columns");
+    col_minmax_kernel<<<dim3(n_cols, n_clips), 256, 0, ST(stream)>>>(x, n_frames, n_cols, min_out, max_out);
+    return ssar_launch_status("col_minmax");
+}
+
+extern "C" int ssar_col_quantile(const float* x, int n_clips, int n_frames, int n_cols, int subset, double q, int interp,
+                                 const float* pre_sub, const float* pre_div, float* out, int* count_out, void* stream) {
+    if (n_clips == 0 || n_cols == 0) return SSAR_OK;
+    SSAR_REQUIRE(x && out, "col_quantile: null pointer");
+    SSAR_REQUIRE(q >= 0.0 && q <= 1.0, "col_quantile: q must be in [0, 1]");
+    SSAR_REQUIRE(subset == 0 || subset == 1, "col_quantile: subset must be 0 (all) or 1 (strict interior peaks)");
+    SSAR_REQUIRE(interp == 0 || interp == 3, "col_quantile: interp must be 0 (linear) or 3 (midpoint)");
+    SSAR_REQUIRE((pre_sub == nullptr) == (pre_div == nullptr), "col_quantile: pre_sub and pre_div go together");
+    SSAR_REQUIRE(n_clips <= 65535, "col_quantile: too many clips per launch");
+    const int threads = n_frames >= 4096 ? 512 : 256;
+    col_quantile_kernel<<<dim3(n_cols, n_clips), threads, 0, ST(stream)>>>(x, n_frames, n_cols, subset, q, interp, pre_sub,
+                                                                          pre_div, out, count_out);
+    return ssar_launch_status("col_quantile");
+}
+
+static inline dim3 flat_grid(long long n_per_clip, int n_clips) {
+    int gx = ssar_div_up(n_per_clip, 256 * 4);
+    if (gx > SSAR_NUM_SMS * 8) gx = SSAR_NUM_SMS * 8;
+    if (gx < 1) gx = 1;
+    return dim3(gx, n_clips);
+}
+
+extern "C" int ssar_clamp_cols(const float* x, int n_clips, int n_frames, int n_cols, const float* lo, const float* hi,
+                               float* out, void* stream) {
+    if (n_clips == 0 || n_frames == 0 || n_cols == 0) return SSAR_OK;
+    SSAR_REQUIRE(x && out, "clamp_cols: null pointer");
+    const long long n = (long long)n_frames * n_cols;
+    clamp_cols_kernel<<<flat_grid(n, n_clips), 256, 0, ST(stream)>>>(x, n, n_cols, lo, hi, out);
+    return ssar_launch_status("clamp_cols");
+}
+
+extern "C" int ssar_normalize(const float* x, int n_clips, long long n_per_clip, const uint32_t* min_key,
+                              const uint32_t* max_key, float eps, float* out, void* stream) {
+    if (n_clips == 0 || n_per_clip == 0) return SSAR_OK;
+    SSAR_REQUIRE(x && min_key && max_key && out, "normalize: null pointer");
+    normalize_kernel<<<flat_grid(n_per_clip, n_clips), 256, 0, ST(stream)>>>(x, n_per_clip, min_key, max_key, eps, out);
+    return ssar_launch_status("normalize");
+}
+
+extern "C" int ssar_emphasize(const float* x, int n_clips, int n_frames, int n_cols, const float* col_min,
+                              const float* col_max, float strength, double q, float* scratch, float* out, void* stream) {
+    if (n_clips == 0 || n_frames == 0 || n_cols == 0) return SSAR_OK;
+    SSAR_REQUIRE(x && col_min && col_max && scratch && out, "emphasize: null pointer");
+    const int nc = n_clips * n_cols;
+    float* rng = scratch;        // [n_clips * n_cols]
+    float* qv = scratch + nc;    // [n_clips * n_cols]
+    range_kernel<<<ssar_div_up(nc, 256), 256, 0, ST(stream)>>>(col_min, col_max, nc, rng);
+    int rc = ssar_col_quantile(x, n_clips, n_frames, n_cols, 0, q, 0, col_min, rng, qv, nullptr, stream);
+    if (rc != SSAR_OK) return rc;
+    const long long n = (long long)n_frames * n_cols;
+    emphasize_kernel<<<flat_grid(n, n_clips), 256, 0, ST(stream)>>>(x, n, n_cols, col_min, rng, qv, strength, out);
+    return ssar_launch_status("emphasize");
+}
+
+extern "C" int ssar_spectral_flux(const float* x, int n_clips, int n_frames, long long inner, float* out, void* stream) {
+    if (n_clips == 0 || n_frames == 0 || inner == 0) return SSAR_OK;
+    SSAR_REQUIRE(x && out && x != out, "spectral_flux: null pointer or aliasing");
+    flux_kernel<<<flat_grid((long long)n_frames * inner, n_clips), 256, 0, ST(stream)>>>(x, n_frames, inner, out);
+    return ssar_launch_status("spectral_flux");
+}
+
+extern "C" int ssar_hwr_rowsum(const float* x, long long n_rows, int inner, float* out, void* stream) {
+    if (n_rows == 0) return SSAR_OK;
+    SSAR_REQUIRE(x && out && inner > 0, "hwr_rowsum: null pointer");
+    int grid = ssar_div_up(n_rows, 8);
+    if (grid > SSAR_NUM_SMS * 8) grid = SSAR_NUM_SMS * 8;
+    hwr_rowsum_kernel<<<grid, 256, 0, ST(stream)>>>(x, n_rows, inner, out);
+    return ssar_launch_status("hwr_rowsum");
+}
+
+extern "C" int ssar_feature_stats(const float* x, long long n_rows, int n_cols, double* stats, void* stream) {
+    if (n_rows == 0 || n_cols == 0) return SSAR_OK;
+    SSAR_REQUIRE(x && stats, "feature_stats: null pointer");
+    int gy = ssar_div_up(n_rows, 8 * 64);
+    if (gy > SSAR_NUM_SMS * 2) gy = SSAR_NUM_SMS * 2;
+    if (gy < 1) gy = 1;
+    feature_stats_kernel<<<dim3(ssar_div_up(n_cols, 32), gy), dim3(32, 8), 0, ST(stream)>>>(x, n_rows, n_cols, stats);
+    return ssar_launch_status("feature_stats");
+}

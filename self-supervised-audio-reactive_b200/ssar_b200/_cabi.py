@@ -34,6 +34,7 @@ class Projection(C.Structure):
         ("n_rows", C.c_int),
         ("start", C.c_void_p), ("count", C.c_void_p), ("offset", C.c_void_p), ("weights", C.c_void_p),
         ("out", C.c_void_p), ("ld", C.c_longlong), ("scale", C.c_float),
+        ("clip_slot", C.c_void_p), ("row_scale", C.c_void_p), ("row_scale_ld", C.c_longlong),
     ]
 
 

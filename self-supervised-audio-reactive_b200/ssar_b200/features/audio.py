@@ -4,7 +4,9 @@ from __future__ import annotations
 import torch
 
 from .. import ops, plan
+from .processing import emphasize, gaussian_filter, normalize
 from .rosa.beat import onset_strength  # noqa: F401  (re-exported like the reference)
+from .rosa.spectral import chroma_cens
 
 
 def hpss_waveforms(audio, margin=8.0, want_harm=True, want_perc=True, n_fft=2048, hop_length=1024):
@@ -69,3 +71,36 @@ def spectral_flatness(y, sr, n_fft=2048, hop_length=1024, window=torch.hann_wind
     out = ops.frames_fft(y, n_fft, hop_length, y.shape[-1] // hop_length, window, want_flatness=True)["flatness"]
     out = out.unsqueeze(-1)
     return out[0] if squeeze else out
+
+
+def spectral_contrast(y, sr, n_fft=2048, hop_length=1024, window=torch.hann_window, center=True, pad_mode="reflect",
+                      fmin=200.0, n_bands=6, quantile=0.02, linear=False):
+    """features/audio.py:72-123 -> [T, n_bands + 1]."""
+    if not center or pad_mode != "reflect":
+        raise NotImplementedError("spectral_contrast: only center=True, pad_mode='reflect' is built")
+    squeeze = y.dim() == 1
+    mag = ops.frames_fft(y, n_fft, hop_length, y.shape[-1] // hop_length, window, spec_power=1)["spec"]
+    bands = plan.contrast_bands(float(sr), int(n_fft), float(fmin), int(n_bands), float(quantile), str(y.device))
+    out = ops.spectral_contrast(mag, bands, linear)
+    return out[0] if squeeze else out
+
+
+def onsets(audio, sr):
+    """features/audio.py:27-28 -> [T, 1]."""
+    return normalize(onset_strength(percussive(audio), sr).unsqueeze(-1))
+
+
+def drop_strength(audio, sr):
+    """features/audio.py:40-41 -> [T, 1]."""
+    return emphasize(gaussian_filter(rms(audio, sr), 10), strength=10, percentile=50).unsqueeze(1)
+
+
+def chromagram(audio, sr):
+    """features/audio.py:44-45 -> [T, 12] (note: HPSS is applied to whatever is passed in, as in the reference)."""
+    return chroma_cens(harmonic(audio), sr).transpose(-1, -2)
+
+
+def tonnetz(y, sr, chroma_fn=None):
+    """features/audio.py:48-57 -> [T, 6].  chroma_fn returns [12, T] like the reference's default lambda."""
+    chroma_tm = chromagram(y, sr) if chroma_fn is None else chroma_fn(y, sr).transpose(-1, -2)
+    return ops.tonnetz(chroma_tm)

@@ -104,3 +104,38 @@ def hpss(S, ks=31, power=2.0, margin=1.0):
     h = _ft(torch.view_as_complex(h), squeeze)
     p = _ft(torch.view_as_complex(p), squeeze)
     return h, p
+
+
+def chroma_cqt(y, sr, hop_length=1024, fmin=None, threshold=0.0, tuning=None, n_chroma=12, n_octaves=7, window=None,
+               bins_per_octave=36, norm=True):
+    """rosa/spectral.py:286-325 -> [n_chroma, T] (or [B, n_chroma, T])."""
+    from .constantq import _tuning_index
+
+    if fmin is not None or window is not None or n_octaves != 7 or bins_per_octave != 36:
+        raise NotImplementedError("chroma_cqt: only fmin=C1, 7 octaves x 36 bins, window=None is built")
+    if threshold is not None and threshold > 0.0:
+        raise NotImplementedError("chroma_cqt: threshold > 0 is not used by the reference path")
+    squeeze = y.dim() == 1
+    B = 1 if squeeze else y.shape[0]
+    C = ops.cqt(y, sr, hop_length, _tuning_index(tuning, B, y.device))
+    chroma = ops.chroma_from_cqt(C, bins_per_octave, n_chroma, quantize=False)
+    if norm:
+        chroma = chroma / chroma.flatten(1).max(dim=1).values[:, None, None]
+    return _ft(chroma, squeeze)
+
+
+def chroma_cens(y, sr, hop_length=1024, fmin=None, tuning=None, n_chroma=12, n_octaves=7, bins_per_octave=36,
+                window=None, win_len_smooth=41, smoothing_window=torch.hann_window):
+    """rosa/spectral.py:239-280 -> [12, T] (or [B, 12, T]): CQT chroma -> L1 -> soft quantiser -> Hann smoothing -> L2."""
+    from .constantq import _tuning_index
+
+    if fmin is not None or window is not None or n_octaves != 7 or bins_per_octave != 36:
+        raise NotImplementedError("chroma_cens: only fmin=C1, 7 octaves x 36 bins, window=None is built")
+    if smoothing_window is not torch.hann_window:
+        raise NotImplementedError("chroma_cens: only the Hann smoothing window is built")
+    squeeze = y.dim() == 1
+    B = 1 if squeeze else y.shape[0]
+    C = ops.cqt(y, sr, hop_length, _tuning_index(tuning, B, y.device))
+    q = ops.chroma_from_cqt(C, bins_per_octave, n_chroma, quantize=True)
+    win = plan.cens_window(int(win_len_smooth), str(y.device)) if win_len_smooth else None
+    return _ft(ops.cens_smooth(q, win, l2=True), squeeze)

@@ -48,15 +48,17 @@ def frames_fft(
     want_rms: bool = False,
     want_flatness: bool = False,
     banks=(),
-    projection=None,
-    projection_scale: float = 1.0,
+    proj: dict | None = None,
 ):
     """Framed real FFT + fused epilogues over a batch of clips.
 
     banks: up to two `(plan.Banded, on_power: bool, track_max: bool)`.
     Returns a dict with the requested outputs (frame-major):
       complex [B,T,F,2], spec [B,T,F], rms [B,T], flatness [B,T], bank{i} [B,T,n_bands], bank{i}_max uint32 key [B],
-      proj [B,T,n_rows,2]
+    proj: banded complex projection of the spectrum (the CQT response), a dict with
+      n_rows, start, count, offset, weights (device tables), out (complex-as-real tensor or view whose element
+      [b, t, r] sits at out.data_ptr + ((b*T + t)*ld + r) complex elements), ld, scale, and optionally
+      slots (int32 [B]: per-clip table slot), row_scale (fp32 [n_slots, row_scale_ld] view), row_scale_ld.
     """
     x, _ = _as_batch(x)
     B, N = x.shape
@@ -111,19 +113,20 @@ def frames_fft(
             out[f"bank{i}_max"] = mk
             fb.max_key = mk.data_ptr()
         keep.append(bank)
-    if projection is not None:
-        if projection.n_cols != F:
-            raise SsarError(f"projection has {projection.n_cols} columns, spectrum has {F} bins")
+    if proj is not None:
         pj = a.proj
-        pj.n_rows = projection.n_rows
-        pj.start, pj.count, pj.offset = (
-            projection.start.data_ptr(), projection.count.data_ptr(), projection.offset.data_ptr())
-        pj.weights = projection.weights.data_ptr()
-        o = torch.empty(B, n_frames, projection.n_rows, 2, dtype=torch.float32, device=dev)
-        out["proj"] = o
-        pj.out = o.data_ptr()
-        pj.ld = projection.n_rows
-        pj.scale = float(projection_scale)
+        pj.n_rows = int(proj["n_rows"])
+        pj.start, pj.count, pj.offset = proj["start"].data_ptr(), proj["count"].data_ptr(), proj["offset"].data_ptr()
+        pj.weights = proj["weights"].data_ptr()
+        pj.out = proj["out"].data_ptr()
+        pj.ld = int(proj["ld"])
+        pj.scale = float(proj.get("scale", 1.0))
+        if proj.get("slots") is not None:
+            pj.clip_slot = proj["slots"].data_ptr()
+        if proj.get("row_scale") is not None:
+            pj.row_scale = proj["row_scale"].data_ptr()
+            pj.row_scale_ld = int(proj["row_scale_ld"])
+        keep.append(proj)
     cabi.call("ssar_frames_fft", C.byref(a))
     return out
 
@@ -224,4 +227,208 @@ def frames_rms(x: torch.Tensor, frame_length: int, hop: int, n_frames: int):
     B, N = x.shape
     out = torch.empty(B, n_frames, dtype=torch.float32, device=x.device)
     cabi.call("ssar_rms_frames", ptr(x), i64(N), i64(x.stride(0)), i32(B), i32(frame_length), i32(hop), i32(n_frames), ptr(out))
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# post-processing (csrc/post.cu)
+# ------------------------------------------------------------------------------------------------
+PAD_MODES = {"circular": 0, "reflect": 1, "replicate": 2}
+
+
+def gauss1d(x: torch.Tensor, sigma: float, mode: str = "circular", batched: bool = False):
+    """Gaussian smoothing along time.  x: [T, inner...] or, with batched=True, [B, T, inner...] -> same shape."""
+    if not x.is_cuda:
+        raise SsarError("ssar_b200 needs CUDA tensors (no CPU fallback)")
+    x = x.contiguous().float()
+    n_clips, T = (x.shape[0], x.shape[1]) if batched else (1, x.shape[0])
+    inner = x.numel() // max(n_clips * T, 1)
+    radius = min(int(sigma * 4), 3 * T)
+    if mode not in PAD_MODES:
+        raise SsarError(f"gaussian_filter: unsupported padding mode {mode!r}")
+    w = plan.gaussian_taps(float(sigma), radius, str(x.device))
+    out = torch.empty_like(x)
+    cabi.call("ssar_gauss1d", ptr(x), i32(n_clips), i32(T), i64(inner), ptr(w), i32(radius), i32(PAD_MODES[mode]), ptr(out))
+    return out
+
+
+def col_minmax(x: torch.Tensor):
+    """x [B, T, C] -> (min [B, C], max [B, C])."""
+    B, T, Cc = x.shape
+    mn = torch.empty(B, Cc, dtype=torch.float32, device=x.device)
+    mx = torch.empty(B, Cc, dtype=torch.float32, device=x.device)
+    cabi.call("ssar_col_minmax", ptr(x), i32(B), i32(T), i32(Cc), ptr(mn), ptr(mx))
+    return mn, mx
+
+
+def col_quantile(x: torch.Tensor, q: float, subset: str = "all", interp: str = "linear", pre=None, want_count=False):
+    """x [B, T, C] contiguous -> per-(clip, column) quantile [B, C] (exact order statistics, radix select)."""
+    B, T, Cc = x.shape
+    out = torch.empty(B, Cc, dtype=torch.float32, device=x.device)
+    cnt = torch.empty(B, Cc, dtype=torch.int32, device=x.device) if want_count else None
+    ps, pd = (pre if pre is not None else (None, None))
+    cabi.call("ssar_col_quantile", ptr(x), i32(B), i32(T), i32(Cc), i32({"all": 0, "peaks": 1}[subset]), f64(q),
+              i32({"linear": 0, "midpoint": 3}[interp]), ptr(ps), ptr(pd), ptr(out), ptr(cnt))
+    return (out, cnt) if want_count else out
+
+
+def clamp_cols(x: torch.Tensor, lo=None, hi=None):
+    B, T, Cc = x.shape
+    out = torch.empty_like(x)
+    cabi.call("ssar_clamp_cols", ptr(x), i32(B), i32(T), i32(Cc), ptr(lo), ptr(hi), ptr(out))
+    return out
+
+
+def normalize(x: torch.Tensor, n_clips: int = 1, eps: float = 1e-8):
+    """(x - min) / ((max - min) + eps) with min/max over each clip's whole array."""
+    x = x.contiguous()
+    mn, mx = minmax_keys(x, n_clips)
+    out = torch.empty_like(x)
+    cabi.call("ssar_normalize", ptr(x), i32(n_clips), i64(x.numel() // max(n_clips, 1)), ptr(mn), ptr(mx), f32(eps), ptr(out))
+    return out
+
+
+def emphasize(x: torch.Tensor, strength: float, percentile: float):
+    B, T, Cc = x.shape
+    mn, mx = col_minmax(x)
+    scratch = torch.empty(2 * B * Cc, dtype=torch.float32, device=x.device)
+    out = torch.empty_like(x)
+    cabi.call("ssar_emphasize", ptr(x), i32(B), i32(T), i32(Cc), ptr(mn), ptr(mx), f32(strength), f64(percentile / 100),
+              ptr(scratch), ptr(out))
+    return out
+
+
+def spectral_flux(x: torch.Tensor, n_clips: int = 1):
+    x = x.contiguous()
+    T = x.shape[1] if n_clips > 1 else x.shape[0]
+    out = torch.empty_like(x)
+    cabi.call("ssar_spectral_flux", ptr(x), i32(n_clips), i32(T), i64(x.numel() // max(n_clips * T, 1)), ptr(out))
+    return out
+
+
+def hwr_rowsum(x: torch.Tensor):
+    """x [rows, inner] -> [rows]: sum of the half-wave rectified entries."""
+    rows, inner = x.shape
+    out = torch.empty(rows, dtype=torch.float32, device=x.device)
+    cabi.call("ssar_hwr_rowsum", ptr(x), i64(rows), i32(inner), ptr(out))
+    return out
+
+
+def feature_stats(x: torch.Tensor, stats: torch.Tensor | None = None):
+    """x [..., C] -> fp64 [3, C] = (count, sum, sum of squares) accumulated into `stats` (allocated if None)."""
+    Cc = x.shape[-1]
+    x = x.contiguous()
+    if stats is None:
+        stats = torch.zeros(3, Cc, dtype=torch.float64, device=x.device)
+    cabi.call("ssar_feature_stats", ptr(x), i64(x.numel() // Cc), i32(Cc), ptr(stats))
+    return stats
+
+
+def spectral_contrast(mag: torch.Tensor, bands, linear: bool = False, top_db: float = 80.0):
+    """mag [B, T, F] magnitude spectrogram (frame-major) -> contrast [B, T, n_bands+1] (features/audio.py:72-123)."""
+    B, T, F = mag.shape
+    dev = mag.device
+    peak = torch.empty(B, T, bands.n, dtype=torch.float32, device=dev)
+    valley = torch.empty_like(peak)
+    keys = torch.empty(2, B, dtype=torch.int32, device=dev)
+    fill_u32(keys, KEY_NEG_INF)
+    cabi.call("ssar_contrast_bands", ptr(mag), i64(F), i32(B), i32(T), i32(bands.n), ptr(bands.start), ptr(bands.count),
+              ptr(bands.q), i32(bands.max_count), ptr(peak), ptr(valley), ptr(keys[0]), ptr(keys[1]))
+    out = torch.empty_like(peak)
+    cabi.call("ssar_contrast_finish", ptr(peak), ptr(valley), ptr(keys[0]), ptr(keys[1]), i32(B), i64(T * bands.n),
+              i32(1 if linear else 0), f32(top_db), ptr(out))
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# tuning / chroma / tonnetz (csrc/tuning.cu, csrc/chroma.cu)
+# ------------------------------------------------------------------------------------------------
+def estimate_tuning(y: torch.Tensor, sr, n_fft: int = 2048, bins_per_octave: int = 12, threshold: float = 0.1,
+                    fmin: float = 150.0, fmax: float = 4000.0):
+    """rosa/pitch.py:9-24 for a batch [B, N] -> (tuning_idx int32 [B] in [0, 100], tuning_val fp32 [B])."""
+    y, _ = _as_batch(y)
+    B, N = y.shape
+    hop = n_fft // 4  # hop_length=None reaches torch.stft's default through rosa/spectral.py:59-62
+    T = N // hop
+    S = frames_fft(y, n_fft, hop, T, torch.hann_window, spec_power=1)["spec"]
+    k_lo, k_hi = plan.piptrack_bin_range(float(sr), n_fft, fmin, fmax)
+    R = k_hi - k_lo
+    pitch = torch.empty(B, T, R, dtype=torch.float32, device=y.device)
+    mag = torch.empty_like(pitch)
+    cabi.call("ssar_piptrack", ptr(S), i64(S.shape[2]), i32(B), i32(T), i32(S.shape[2]), i32(k_lo), i32(k_hi),
+              f32(threshold), f32(float(sr)), i32(n_fft), ptr(pitch), ptr(mag))
+    idx = torch.empty(B, dtype=torch.int32, device=y.device)
+    val = torch.empty(B, dtype=torch.float32, device=y.device)
+    edges = plan.tuning_edges(str(y.device))
+    cabi.call("ssar_tuning_from_peaks", ptr(pitch), ptr(mag), i32(B), i64(T * R), ptr(edges), i32(edges.numel() - 1),
+              f32(float(bins_per_octave)), ptr(idx), ptr(val))
+    return idx, val
+
+
+def chroma_from_cqt(C_fm: torch.Tensor, bins_per_octave: int = 36, n_chroma: int = 12, quantize: bool = False):
+    """C_fm: frame-major complex-as-real CQT [B, T, n_bins, 2] -> chroma [B, T, n_chroma] (optionally L1-normalised and
+    passed through the CENS soft quantiser)."""
+    B, T, nb, _ = C_fm.shape
+    dev = str(C_fm.device)
+    cmap = plan.chroma_map(nb, bins_per_octave, n_chroma, dev)
+    knots, sa, sb, sc, sd = plan.cens_spline(dev)
+    out = torch.empty(B, T, n_chroma, dtype=torch.float32, device=C_fm.device)
+    cabi.call("ssar_chroma_from_cqt", ptr(C_fm), i64(nb), i32(B), i32(T), i32(nb), ptr(cmap), i32(n_chroma),
+              i32(1 if quantize else 0), ptr(knots), ptr(sa), ptr(sb), ptr(sc), ptr(sd), i32(knots.numel()),
+              f32(0.25), f32(20.0), ptr(out))
+    return out
+
+
+def cens_smooth(q: torch.Tensor, window: torch.Tensor | None, l2: bool = True):
+    B, T, nc = q.shape
+    if window is None:
+        window = torch.ones(1, dtype=torch.float32, device=q.device)
+    out = torch.empty_like(q)
+    cabi.call("ssar_cens_smooth", ptr(q), i32(B), i32(T), i32(nc), ptr(window), i32(window.numel()), i32(1 if l2 else 0),
+              ptr(out))
+    return out
+
+
+def tonnetz(chroma: torch.Tensor):
+    """chroma [..., T, n_chroma] contiguous -> [..., T, 6]."""
+    chroma = chroma.contiguous()
+    nc = chroma.shape[-1]
+    out = torch.empty(chroma.shape[:-1] + (6,), dtype=torch.float32, device=chroma.device)
+    cabi.call("ssar_tonnetz", ptr(chroma), i64(chroma.numel() // nc), i32(nc), ptr(plan.tonnetz_phi(nc, str(chroma.device))),
+              i32(6), ptr(out))
+    return out
+
+
+def cqt(y: torch.Tensor, sr, hop_length: int = 1024, tuning_idx=None):
+    """rosa/constantq.py:13-115 for the reference's only configuration (C1, 7 octaves x 36 bins, filter_scale 1,
+    sparsity 0.01): returns the frame-major complex-as-real CQT [B, T, 252, 2] with 1/sqrt(length) applied.
+    tuning_idx: int32 [B] from estimate_tuning (None -> estimate, like tuning=None in chroma_cqt)."""
+    y, _ = _as_batch(y)
+    B, N = y.shape
+    n_oct, bpo = plan.CQT_N_OCTAVES, plan.CQT_BINS_PER_OCTAVE
+    if hop_length % (1 << (n_oct - 1)) != 0:
+        raise Exception("hop_length must be a positive integer multiple of 2^{0:d} for {1:d}-octave CQT/VQT".format(
+            n_oct - 1, n_oct))
+    if float(sr) / (1 << (n_oct - 1)) != int(float(sr) / (1 << (n_oct - 1))):
+        raise ValueError("Frequencies must be of integer type to ensure quality resampling computation.")
+    if tuning_idx is None:
+        tuning_idx, _ = estimate_tuning(y, sr, bins_per_octave=bpo)
+    tables = plan.cqt_tables(float(sr), str(y.device))
+    slots = tables.slots_for(tuning_idx.cpu().tolist())  # one small D2H sync per batch: the basis is data-dependent
+    # octave signals: y_i = resample(y_{i-1}, /2, kaiser) * sqrt(2)
+    sigs, hops = [y], [hop_length]
+    rp = plan.resample_plan(2, 1, "kaiser_window", str(y.device))
+    for i in range(1, n_oct):
+        sigs.append(resample(sigs[-1], rp, post_scale=float(torch.tensor(2.0).sqrt())))
+        hops.append(hops[-1] // 2)
+    T = min(s.shape[1] // h for s, h in zip(sigs, hops))
+    n_bins = n_oct * bpo
+    out = torch.empty(B, T, n_bins, 2, dtype=torch.float32, device=y.device)
+    for i, (s, h) in enumerate(zip(sigs, hops)):
+        col0 = n_bins - bpo * (i + 1)
+        # frames beyond T (octaves can be one frame longer) are simply not produced
+        proj = dict(n_rows=bpo, start=tables.start, count=tables.count, offset=tables.offset, weights=tables.weights,
+                    out=out[:, :, col0:], ld=n_bins, scale=float(2.0 ** i) ** 0.5, slots=slots,
+                    row_scale=tables.row_scale[:, col0:], row_scale_ld=n_bins)
+        frames_fft(s, plan.CQT_N_FFT, h, T, None, proj=proj)
     return out

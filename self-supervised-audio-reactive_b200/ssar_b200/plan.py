@@ -223,3 +223,257 @@ def biquad_coeffs(kind: str, sample_rate, cutoff_freq, Q: float = 0.707):
     a1 = -2 * torch.cos(w0)
     a2 = 1 - alpha
     return tuple(float(v) for v in (b0 / a0, b1 / a0, b2 / a0, a1 / a0, a2 / a0))
+
+
+@functools.lru_cache(maxsize=None)
+def gaussian_taps(sigma: float, radius: int, device) -> torch.Tensor:
+    """features/processing.py:21-24: exp(-0.5/sigma^2 * k^2) / sum over k in [-radius, radius], fp32 op order kept."""
+    k = torch.arange(-radius, radius + 1, dtype=torch.float32)
+    k = torch.exp(-0.5 / sigma ** 2 * k ** 2)
+    k = k / k.sum()
+    return k.to(_dev(device))
+
+
+@dataclass(frozen=True)
+class ContrastBands:
+    start: torch.Tensor  # int32 [n_bands + 1]
+    count: torch.Tensor
+    q: torch.Tensor
+    n: int
+    max_count: int
+
+
+@functools.lru_cache(maxsize=None)
+def contrast_bands(sr: float, n_fft: int, fmin: float, n_bands: int, quantile: float, device) -> ContrastBands:
+    """Bin ranges and extreme counts of features/audio.py:86-113, evaluated once with the same fp32 comparisons."""
+    freq = torch.linspace(0, float(sr) / 2, int(1 + n_fft // 2))
+    octa = torch.zeros(n_bands + 2)
+    octa[1:] = fmin * (2.0 ** torch.arange(0, n_bands + 1))
+    starts, counts, qs = [], [], []
+    for k, (f_low, f_high) in enumerate(zip(octa[:-1], octa[1:])):
+        band = torch.logical_and(freq >= f_low, freq <= f_high)
+        idx = band.nonzero().flatten()
+        if k > 0:
+            band[idx[0] - 1] = True
+        if k == n_bands:
+            band[idx[-1] + 1:] = True
+        bins = band.nonzero().flatten()
+        assert int(bins[-1] - bins[0]) + 1 == len(bins), "contrast band is not a contiguous bin range"
+        n_used = len(bins) - (1 if k < n_bands else 0)
+        q = int(torch.maximum(torch.round(torch.tensor(quantile) * band.sum()), torch.ones(())))
+        if q > n_used or q > 32:
+            raise ValueError(f"spectral_contrast: band {k} needs {q} extremes of {n_used} bins (limit 32)")
+        starts.append(int(bins[0]))
+        counts.append(n_used)
+        qs.append(q)
+    dev = _dev(device)
+    i32 = lambda v: torch.tensor(v, dtype=torch.int32, device=dev)
+    return ContrastBands(i32(starts), i32(counts), i32(qs), n_bands + 1, max(counts))
+
+
+# ------------------------------------------------------------------------------------------------
+# Constant-Q basis (rosa/constantq.py:118-164, 215-269) for every tuning the estimator can return.
+# estimate_tuning quantises to linspace(-0.5, 0.5, 101)[argmax of a 100-bin histogram] (rosa/pitch.py:115-120), so
+# only 100 distinct bases exist; one basis serves all octaves (sr and fmin halve together, exact in fp32).
+# ------------------------------------------------------------------------------------------------
+CQT_BINS_PER_OCTAVE = 36
+CQT_N_OCTAVES = 7
+CQT_N_FFT = 1024
+C1_HZ = 440.0 * 2.0 ** ((24 - 69) / 12.0)  # librosa.note_to_hz("C1"), rosa/convert.py:129-130
+
+
+def cqt_tuning_values() -> torch.Tensor:
+    return torch.linspace(-0.5, 0.5, 101)
+
+
+def cqt_fmin_tuned(tuning: torch.Tensor) -> torch.Tensor:
+    """rosa/constantq.py:48-58: C1 * 2^(tuning / bins_per_octave), fp32."""
+    return torch.tensor(C1_HZ).float() * 2.0 ** (tuning / CQT_BINS_PER_OCTAVE)
+
+
+def cqt_octave_basis_cpu(sr: float, tuning: torch.Tensor, sparsity: float = 0.01):
+    """Top-octave FFT basis [36, 513] complex64 (dense, sparsified entries zeroed) + all 252 filter lengths."""
+    bpo, n_bins = CQT_BINS_PER_OCTAVE, CQT_BINS_PER_OCTAVE * CQT_N_OCTAVES
+    alpha = 2.0 ** (1.0 / bpo) - 1.0
+    Q = 1.0 / alpha
+    fmin = cqt_fmin_tuned(tuning)
+    ratios = 2.0 ** (torch.arange(n_bins, dtype=torch.float) / bpo)
+    all_freqs = 1.0 * fmin * ratios                      # cqt_frequencies (tuning correction 2^0 = 1)
+    all_lengths = Q * sr / (fmin * ratios + 0.0 / alpha)  # constant_q_lengths over all bins (the final 1/sqrt(len))
+    fmin_t = torch.min(all_freqs[-bpo:])
+    freqs = fmin_t * ratios[:bpo]
+    lengths = Q * sr / (freqs + 0.0 / alpha)
+    n_fft = int(2.0 ** torch.ceil(torch.log2(lengths.max())))
+    rows = []
+    for ilen, freq in zip(lengths, freqs):
+        half = torch.div(ilen, 2, rounding_mode="floor")
+        phase = torch.arange(-half, half, dtype=torch.float) * 1j * 2 * torch.pi * freq / sr
+        sig = torch.exp(phase) * torch.hann_window(len(phase))
+        sig = sig / sig.norm(p=1, dim=0)
+        lpad = (n_fft - len(sig)) // 2
+        rows.append(torch.nn.functional.pad(sig, (lpad, n_fft - len(sig) - lpad)))
+    basis = torch.stack(rows) * (lengths[:, None] / float(n_fft))
+    fb = torch.fft.fft(basis, n=n_fft, dim=1)[:, : n_fft // 2 + 1]
+    # sparsify_rows: drop the smallest entries holding < `sparsity` of each row's L1 mass
+    mags = fb.abs()
+    srt = torch.sort(mags, dim=1).values
+    cum = torch.cumsum(srt / mags.sum(1, keepdim=True), dim=1)
+    thr_idx = torch.argmin((cum < sparsity).to(torch.uint8), dim=1)
+    thr = srt.gather(1, thr_idx[:, None])
+    fb = torch.where(mags >= thr, fb, torch.zeros((), dtype=fb.dtype))
+    return fb, n_fft, all_lengths
+
+
+def cqt_banded_cpu(sr: float, tuning_index: int):
+    """Banded form of one tuning's top-octave basis: (start[36], count[36], weights [nnz, 2] fp32, lengths[252])."""
+    fb, n_fft, lengths = cqt_octave_basis_cpu(float(sr), cqt_tuning_values()[tuning_index])
+    assert n_fft == CQT_N_FFT, f"CQT filters need n_fft={n_fft}; only {CQT_N_FFT} is built (sr={sr})"
+    nz = fb.abs() > 0
+    starts, counts, chunks = [], [], []
+    for r in range(fb.shape[0]):
+        idx = nz[r].nonzero().flatten()
+        s, c = int(idx[0]), int(idx[-1]) - int(idx[0]) + 1
+        starts.append(s)
+        counts.append(c)
+        chunks.append(torch.view_as_real(fb[r, s : s + c].contiguous()))
+    return starts, counts, torch.cat(chunks), lengths
+
+
+class CqtTables:
+    """Device tables of the tuned CQT bases, grown on demand: slot s holds the basis of tuning index `slot_tuning[s]`."""
+
+    def __init__(self, sr: float, device):
+        self.sr, self.device = float(sr), _dev(device)
+        self.slot_of = {}
+        self._starts, self._counts, self._offsets, self._weights, self._rscale = [], [], [], [], []
+        self._nnz = 0
+        self.start = self.count = self.offset = self.weights = self.row_scale = None
+
+    def slots_for(self, tuning_idx_host):
+        """tuning indices (host ints, one per clip) -> int32 device tensor of slots; uploads any new basis."""
+        grew = False
+        for ti in sorted(set(int(v) for v in tuning_idx_host)):
+            if ti in self.slot_of:
+                continue
+            st, cn, w, lengths = cqt_banded_cpu(self.sr, ti)
+            self.slot_of[ti] = len(self.slot_of)
+            self._starts += st
+            self._counts += cn
+            off = self._nnz
+            for c in cn:
+                self._offsets.append(off)
+                off += c
+            self._nnz = off
+            self._weights.append(w)
+            self._rscale.append(1.0 / torch.sqrt(lengths))  # V /= sqrt(lengths) (rosa/constantq.py:113)
+            grew = True
+        if grew:
+            i32 = lambda v: torch.tensor(v, dtype=torch.int32, device=self.device)
+            self.start, self.count, self.offset = i32(self._starts), i32(self._counts), i32(self._offsets)
+            self.weights = torch.cat(self._weights).contiguous().to(self.device)
+            self.row_scale = torch.stack(self._rscale).contiguous().to(self.device)  # [n_slots, 252]
+        return torch.tensor([self.slot_of[int(v)] for v in tuning_idx_host], dtype=torch.int32, device=self.device)
+
+
+@functools.lru_cache(maxsize=None)
+def cqt_tables(sr: float, device) -> CqtTables:
+    return CqtTables(sr, device)
+
+
+@functools.lru_cache(maxsize=None)
+def tuning_edges(device) -> torch.Tensor:
+    return cqt_tuning_values().to(_dev(device))
+
+
+def piptrack_bin_range(sr: float, n_fft: int, fmin: float = 150.0, fmax: float = 4000.0):
+    """rosa/pitch.py:44-66: bins with fmin <= fft_freqs < fmax (fp32 linspace comparison, contiguous)."""
+    fmax = min(fmax, float(sr) / 2)
+    freqs = torch.linspace(0, float(sr) / 2, int(1 + n_fft // 2))
+    m = ((max(fmin, 0) <= freqs) & (freqs < fmax)).nonzero().flatten()
+    return int(m[0]), int(m[-1]) + 1
+
+
+def chroma_map_cpu(n_input: int, bins_per_octave: int = 36, n_chroma: int = 12) -> torch.Tensor:
+    """rosa/convert.py:69-117 cq_to_chroma with fmin = C1, base_c=True, window=None as a class index per CQT bin.
+    C1 is MIDI 24 -> roll 0.  Bin j of every octave belongs to chroma ((j + n_merge // 2) // n_merge) % n_chroma."""
+    n_merge = bins_per_octave // n_chroma
+    assert n_merge * n_chroma == bins_per_octave
+    midi_0 = (12 * (math.log2(C1_HZ) - math.log2(440.0)) + 69) % 12
+    roll = int(round(midi_0 * (n_chroma / 12.0))) % n_chroma
+    j = torch.arange(n_input) % bins_per_octave
+    return ((((j + n_merge // 2) // n_merge) + roll) % n_chroma).to(torch.int32)
+
+
+@functools.lru_cache(maxsize=None)
+def chroma_map(n_input: int, bins_per_octave: int, n_chroma: int, device) -> torch.Tensor:
+    return chroma_map_cpu(n_input, bins_per_octave, n_chroma).to(_dev(device))
+
+
+def natural_cubic_spline_np(t: np.ndarray, y: np.ndarray):
+    """Natural cubic spline through (t, y) in the (a, b, two_c, three_d) parameterisation of torchcubicspline
+    (published algorithm; the package itself is un-vendored and unpinned): value = a + b f + (two_c / 2) f^2 +
+    (three_d / 3) f^3 upstream — the reference's own spline_eval uses two_c and three_d directly (rosa/spectral.py:200)."""
+    t, y = t.astype(np.float64), y.astype(np.float64)
+    n = len(t)
+    dt = np.diff(t)
+    dx = np.diff(y)
+    A = np.zeros((n, n))
+    rhs = np.zeros(n)
+    for i in range(n):
+        if i > 0:
+            A[i, i] += 2.0 / dt[i - 1]
+            A[i, i - 1] = 1.0 / dt[i - 1]
+            rhs[i] += 3.0 * dx[i - 1] / dt[i - 1] ** 2
+        if i < n - 1:
+            A[i, i] += 2.0 / dt[i]
+            A[i, i + 1] = 1.0 / dt[i]
+            rhs[i] += 3.0 * dx[i] / dt[i] ** 2
+    k = np.linalg.solve(A, rhs)
+    a = y[:-1]
+    b = k[:-1]
+    two_c = (6.0 * dx / dt - 4.0 * k[:-1] - 2.0 * k[1:]) / dt
+    three_d = (-6.0 * dx / dt + 3.0 * (k[:-1] + k[1:])) / dt ** 2
+    return a, b, two_c, three_d
+
+
+def cens_quantiser_knots():
+    """The 240 knots of rosa/spectral.py:164-188 (QUANT_STEPS 0.4/0.2/0.1/0.05 -> plateaus 0.5 .. 4.5)."""
+    steps = [0.4, 0.2, 0.1, 0.05]
+    p1, p2, p3, p4 = np.diff(list(reversed(steps + [0])))
+    xs = [
+        torch.linspace(-0.1, 0.025, 101)[:-1], torch.linspace(0.025, p1, 11)[:-1], torch.linspace(p1, p1 + p2, 11)[:-1],
+        torch.linspace(p1 + p2, p1 + p2 + p3, 11)[:-1], torch.linspace(p1 + p2 + p3, 0.5, 11)[:-1],
+        torch.linspace(0.5, 1.1, 100),
+    ]
+    ys = torch.cat((
+        0.5 * torch.ones(len(xs[0])), xs[1] / p1, (xs[2] - p1) / p2 + 1, (xs[3] - p1 - p2) / p3 + 2,
+        (xs[4] - p1 - p2 - p3) / p4 + 3, 4.5 * torch.ones(len(xs[5])),
+    ))
+    return torch.cat(xs).float(), ys.float()
+
+
+@functools.lru_cache(maxsize=None)
+def cens_spline(device):
+    xs, ys = cens_quantiser_knots()
+    a, b, c, d = natural_cubic_spline_np(xs.numpy(), ys.numpy())
+    dev = _dev(device)
+    f = lambda v: torch.from_numpy(np.asarray(v, dtype=np.float32)).to(dev)
+    return xs.to(dev), f(a), f(b), f(c), f(d)
+
+
+@functools.lru_cache(maxsize=None)
+def cens_window(win_len_smooth: int, device) -> torch.Tensor:
+    """rosa/spectral.py:274-275: periodic hann(win_len_smooth + 2) / sum."""
+    w = torch.hann_window(win_len_smooth + 2)
+    return (w / torch.sum(w)).to(_dev(device))
+
+
+@functools.lru_cache(maxsize=None)
+def tonnetz_phi(n_chroma: int, device) -> torch.Tensor:
+    """features/audio.py:50-55 (endpoint-inclusive linspace(0, 12, n_chroma) kept as written)."""
+    dim_map = torch.linspace(0, 12, n_chroma)
+    scale = torch.tensor([7.0 / 6, 7.0 / 6, 3.0 / 2, 3.0 / 2, 2.0 / 3, 2.0 / 3])
+    V = scale.reshape(-1, 1) * dim_map
+    V[::2] -= 0.5
+    R = torch.tensor([1, 1, 1, 1, 0.5, 0.5])
+    return (R[:, None] * torch.cos(torch.pi * V)).contiguous().to(_dev(device))

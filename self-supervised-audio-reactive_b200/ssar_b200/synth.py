@@ -64,3 +64,13 @@ def synth_batch_device(n_clips: int, n_samples: int, sr: int, device, first_inde
         x[idx] += 0.8
         out[i] = x / (1.05 * x.abs().max())
     return out
+
+
+def synth_features(n_frames: int, n_cols: int, seed: int = 0) -> torch.Tensor:
+    """Deterministic [T, C] feature-like matrix (smooth random walk + spikes, columns on different scales)."""
+    g = torch.Generator("cpu").manual_seed(9000 + seed)
+    walk = torch.randn(n_frames, n_cols, generator=g).cumsum(0) * 0.05
+    spikes = (torch.rand(n_frames, n_cols, generator=g) > 0.97).float() * torch.rand(n_frames, n_cols, generator=g) * 3
+    jitter = 0.3 * torch.randn(n_frames, n_cols, generator=g)
+    scale = torch.linspace(0.5, 20.0, n_cols)
+    return ((walk + spikes + jitter) * scale + torch.arange(n_cols) * 0.25).float()

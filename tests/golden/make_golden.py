@@ -18,7 +18,7 @@ sys.path.insert(0, str(HERE))
 sys.path.insert(0, str(ROOT / "self-supervised-audio-reactive_b200"))
 
 from ref_loader import load_reference  # noqa: E402
-from ssar_b200.synth import synth_clip  # noqa: E402
+from ssar_b200.synth import synth_clip, synth_features  # noqa: E402
 
 SR = 24576
 
@@ -100,7 +100,51 @@ def g_hpss_filters(ref):
     save("resample", n=n2, clip_index=4, to24576=y2, half_kaiser=y3)
 
 
-GROUPS = {"spectral": g_spectral, "frame_features": g_frame_features, "hpss_filters": g_hpss_filters}
+def g_post(ref):
+    """processing.py on a synthetic [T, C] feature matrix (+ short-sequence, 1-D, 3-D and 4-D gaussian cases)."""
+    P = ref.processing
+    x = synth_features(700, 7, 0)
+    x3 = synth_features(64, 6, 1).reshape(64, 2, 3)
+    x4 = synth_features(48, 8, 2).reshape(48, 2, 2, 2)
+    short = synth_features(10, 3, 3)
+    import contextlib, io
+
+    with contextlib.redirect_stdout(io.StringIO()):
+        g_short = P.gaussian_filter(short, 5.0)
+    save(
+        "post",
+        gauss_s2=P.gaussian_filter(x, 2.4), gauss_s10_reflect=P.gaussian_filter(x, 10, mode="reflect"),
+        gauss_1d=P.gaussian_filter(x[:, 0], 3), gauss_col1=P.gaussian_filter(x[:, :1], 3),
+        gauss_3d=P.gaussian_filter(x3, 1), gauss_4d=P.gaussian_filter(x4, 2), gauss_short=g_short,
+        normalize=P.normalize(x), standardize=P.standardize(x),
+        q25=P.quantile(x, 0.25), q975=P.quantile(x[:, 3].contiguous(), 0.975),
+        flux=P.spectral_flux(x), onset_env=P.onset_envelope(P.spectral_flux(x)),
+        clamp_peaks=P.clamp_peaks_percentile(x, 97.5), clamp_peaks_1d=P.clamp_peaks_percentile(x[:, 2], 90),
+        clamp_upper=P.clamp_upper_percentile(x, 95), clamp_lower=P.clamp_lower_percentile(x, 10),
+        emphasize=P.emphasize(x, 2, 75), emphasize_10_50=P.emphasize(x[:, :1], 10, 50),
+    )
+
+
+def g_chroma(ref):
+    """tuning estimate, CQT, chroma (cqt / cens), chromagram, tonnetz, spectral contrast on a 4 s ragged clip."""
+    n = SR * 4 + 300
+    x = synth_clip(n, SR, 5)
+    tun = ref.pitch.estimate_tuning(x, SR, bins_per_octave=36)
+    tun12 = ref.pitch.estimate_tuning(x, SR)
+    C = ref.constantq.cqt(x, SR, n_bins=252, bins_per_octave=36, tuning=None)
+    C0 = ref.constantq.cqt(x, SR, n_bins=252, bins_per_octave=36, tuning=0.0)
+    cens = ref.spectral.chroma_cens(x, SR)
+    save(
+        "chroma", n=n, sr=SR, clip_index=5, tuning36=tun, tuning12=tun12,
+        cqt_re=C.real, cqt_im=C.imag, cqt0_abs=C0.abs(),
+        chroma_cqt=ref.spectral.chroma_cqt(x, SR), cens=cens,
+        chromagram=ref.audio.chromagram(x, SR), tonnetz=ref.audio.tonnetz(x, SR),
+        tonnetz_of_cens=ref.audio.tonnetz(x, SR, chroma_fn=lambda a, sr: cens),
+        contrast=ref.audio.spectral_contrast(x, SR), contrast_linear=ref.audio.spectral_contrast(x, SR, linear=True),
+    )
+
+
+GROUPS = {"chroma": g_chroma, "post": g_post, "spectral": g_spectral, "frame_features": g_frame_features, "hpss_filters": g_hpss_filters}
 
 if __name__ == "__main__":
     torch.manual_seed(0)

@@ -1,0 +1,71 @@
+"""GPU parity: tuning estimate, CQT, chroma / CENS, tonnetz and spectral contrast vs goldens and the oracle."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN, rel_l2
+from ssar_b200.synth import synth_clip
+from ssar_oracle import cqt as ocqt
+from ssar_oracle import dsp
+
+pytestmark = pytest.mark.gpu
+
+TOL_CQT = 1e-4     # north-star tolerance on spectra / CQT magnitudes
+TOL_CHROMA = 1e-3  # north-star tolerance on chroma / tonnetz / contrast
+
+
+def load(name):
+    return {k: torch.from_numpy(np.asarray(v)) for k, v in np.load(GOLDEN / f"{name}.npz").items()}
+
+
+def test_chroma_chain_vs_golden():
+    from ssar_b200.features import audio
+    from ssar_b200.features.rosa import constantq, pitch, spectral
+
+    g = load("chroma")
+    sr = int(g["sr"])
+    x = synth_clip(int(g["n"]), sr, int(g["clip_index"])).cuda()
+    assert float(pitch.estimate_tuning(x, sr, bins_per_octave=36)) == float(g["tuning36"])
+    assert float(pitch.estimate_tuning(x, sr)) == float(g["tuning12"])
+    C = constantq.cqt(x, sr, n_bins=252, bins_per_octave=36, tuning=None)
+    assert tuple(C.shape) == tuple(g["cqt_re"].shape)
+    ref = torch.complex(g["cqt_re"], g["cqt_im"])
+    assert rel_l2(torch.view_as_real(C.cpu().resolve_conj()), torch.view_as_real(ref)) < TOL_CQT
+    C0 = constantq.cqt(x, sr, n_bins=252, bins_per_octave=36, tuning=0.0)
+    assert rel_l2(C0.abs(), g["cqt0_abs"]) < TOL_CQT
+    assert rel_l2(spectral.chroma_cqt(x, sr), g["chroma_cqt"]) < TOL_CHROMA
+    cens = spectral.chroma_cens(x, sr)
+    assert tuple(cens.shape) == tuple(g["cens"].shape)
+    assert rel_l2(cens, g["cens"]) < TOL_CHROMA
+    assert rel_l2(audio.chromagram(x, sr), g["chromagram"]) < TOL_CHROMA
+    assert rel_l2(audio.tonnetz(x, sr, chroma_fn=lambda a, s: cens), g["tonnetz_of_cens"]) < TOL_CHROMA
+    assert rel_l2(audio.tonnetz(x, sr), g["tonnetz"]) < 2e-3  # harmonic(harmonic(x)) chain: two ISTFTs deep
+    assert rel_l2(audio.spectral_contrast(x, sr), g["contrast"]) < TOL_CHROMA
+    assert rel_l2(audio.spectral_contrast(x, sr, linear=True), g["contrast_linear"]) < TOL_CHROMA
+
+
+def test_chroma_batched_other_tunings_vs_oracle():
+    """Batch of clips with different estimated tunings (per-clip basis slots) vs the oracle, 6 s clips."""
+    from ssar_b200 import ops
+    from ssar_b200.features.rosa import spectral
+
+    sr, n = 24576, 24576 * 6
+    xs = torch.stack([synth_clip(n, sr, i) for i in (0, 7, 11)])
+    idx, val = ops.estimate_tuning(xs.cuda(), sr, bins_per_octave=36)
+    cens = spectral.chroma_cens(xs.cuda(), sr)
+    for b in range(xs.shape[0]):
+        t_ref = ocqt.estimate_tuning(xs[b], sr, bins_per_octave=36)
+        assert float(val[b]) == float(t_ref), (b, float(val[b]), float(t_ref))
+        assert rel_l2(cens[b], ocqt.chroma_cens(xs[b], sr)) < TOL_CHROMA
+
+
+def test_contrast_full_length_properties():
+    """cfg24 length (T = 5760): shape, finiteness, and equality with the oracle on a strided subset of frames."""
+    from ssar_b200.features import audio
+
+    sr, n = 24576, 24576 * 240
+    x = synth_clip(n, sr, 2)
+    c = audio.spectral_contrast(x.cuda(), sr)
+    assert tuple(c.shape) == (5760, 7) and bool(torch.isfinite(c).all())
+    ref = dsp.spectral_contrast(x, sr)
+    assert rel_l2(c, ref) < TOL_CHROMA
