@@ -203,6 +203,12 @@ int ssar_cens_smooth(const float* q, int n_clips, int n_frames, int n_chroma, co
 int ssar_tonnetz(const float* chroma, long long n_rows, int n_chroma, const float* phi, int n_out, float* out,
                  void* stream);
 
+/* rosa/beat.py:54-66 plp, spectral step, IN PLACE on the Fourier tempogram (complex [n_clips, n_frames, ld], n_bins
+ * valid): zero outside bins [k_lo, k_hi) (the 60-180 BPM range), keep only the per-frame maxima of log1p(1e6 |X|),
+ * scale by 1 / (sqrt(tiny) + max |X|).  The caller follows with ssar_irfft_frames + ssar_overlap_add (hop 1). */
+int ssar_plp_peaks(float* tempogram, long long ld, int n_clips, int n_frames, int n_bins, int k_lo, int k_hi,
+                   void* stream);
+
 /* features/audio.py:72-123 spectral_contrast, step 1: per (frame, band) mean of the band_q smallest (valley) and
  * largest (peak) magnitudes of bins [band_start, band_start + band_count) of mag [n_clips, n_frames, ld]; the
  * clip-global maxima of both are merged into keys (ssar_fill_u32 them with the key of -inf first).

@@ -149,6 +149,23 @@ def onset_strength(y, sr, hop_length=1024, n_fft=2048, aggregate="mean"):
     return torch.cat([torch.zeros(shift), env])[: S.shape[1]]
 
 
+def plp(y, sr, hop_length=1024, win_length=1024, tempo_min=60, tempo_max=180):
+    """rosa/beat.py:41-75: median-aggregated onset envelope -> Fourier tempogram (hop 1) -> keep the per-frame peak bin
+    of the 60-180 BPM band at unit magnitude -> inverse STFT -> positive half -> min/max normalise."""
+    env = onset_strength(y, sr, hop_length, aggregate="median")
+    T = len(env)
+    win = min(T, win_length)
+    G = stft(env, win, 1)
+    bpm = torch.linspace(0, float(sr * 60 / float(hop_length)) / 2, 1 + win // 2)
+    G = torch.where(((bpm < tempo_min) | (bpm > tempo_max))[:, None], torch.zeros((), dtype=G.dtype), G)
+    strength = torch.log1p(1e6 * G.abs())
+    G = torch.where(strength < strength.max(0, keepdim=True).values, torch.zeros((), dtype=G.dtype), G)
+    G = G / (torch.finfo(torch.float32).tiny ** 0.5 + G.abs().max(0, keepdim=True).values)
+    p = istft(G, win, 1, length=T).clamp(min=0)
+    p = p - p.min()
+    return p / (p.max() + 1e-8)
+
+
 def mfcc(y, sr, n_mfcc=20):
     """features/audio.py:60-65 -> [T, n_mfcc]."""
     S = power_to_db(melspectrogram(y, sr))

@@ -5,7 +5,7 @@ import torch
 
 from .. import ops, plan
 from .processing import emphasize, gaussian_filter, normalize
-from .rosa.beat import onset_strength  # noqa: F401  (re-exported like the reference)
+from .rosa.beat import onset_strength, plp  # noqa: F401  (re-exported like the reference)
 from .rosa.spectral import chroma_cens
 
 
@@ -104,3 +104,8 @@ def tonnetz(y, sr, chroma_fn=None):
     """features/audio.py:48-57 -> [T, 6].  chroma_fn returns [12, T] like the reference's default lambda."""
     chroma_tm = chromagram(y, sr) if chroma_fn is None else chroma_fn(y, sr).transpose(-1, -2)
     return ops.tonnetz(chroma_tm)
+
+
+def pulse(audio, sr):
+    """features/audio.py:68-69 -> [T, 1]."""
+    return plp(percussive(audio), sr).unsqueeze(-1)

@@ -1,4 +1,4 @@
-"""Mirror of ssar/features/rosa/beat.py (onset strength; plp lives further down once the tempogram path is in)."""
+"""Mirror of ssar/features/rosa/beat.py (onset strength, Fourier tempogram, predominant local pulse)."""
 from __future__ import annotations
 
 import torch
@@ -34,3 +34,27 @@ def onset_strength(y, sr, hop_length=1024, n_fft=2048, aggregate=torch.mean):
     pad_width = 1 + n_fft // (2 * hop_length)
     env = ops.onset_flux(m, mk, pad_width, _aggregate_name(aggregate))
     return env[0] if squeeze else env
+
+
+def fourier_tempo_frequencies(sr, win_length=1024, hop_length=1024, device="cpu"):
+    """rosa/beat.py:26-30."""
+    rate = sr * 60 / float(hop_length)
+    return torch.linspace(0, float(rate) / 2, int(1 + win_length // 2), device=device)
+
+
+def fourier_tempogram(y=None, sr=22050, onset_envelope=None, hop_length=1024, win_length=1024, center=True,
+                      window=torch.hann_window):
+    """rosa/beat.py:33-38 -> complex [1 + win_length/2, T + 1]."""
+    from .spectral import stft
+
+    if onset_envelope is None:
+        onset_envelope = onset_strength(y=y, sr=sr, hop_length=hop_length)
+    return stft(onset_envelope, n_fft=win_length, hop_length=1, center=center, window=window)
+
+
+def plp(y, sr, hop_length=1024, win_length=1024, tempo_min=60, tempo_max=180):
+    """rosa/beat.py:41-75 -> [T] (or [B, T])."""
+    squeeze = y.dim() == 1
+    env = onset_strength(y, sr, hop_length=hop_length, aggregate="median")
+    out = ops.plp_from_onset(env, sr, hop_length, win_length, tempo_min, tempo_max)
+    return out[0] if squeeze else out

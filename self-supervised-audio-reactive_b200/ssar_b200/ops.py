@@ -432,3 +432,28 @@ def cqt(y: torch.Tensor, sr, hop_length: int = 1024, tuning_idx=None):
                     row_scale=tables.row_scale[:, col0:], row_scale_ld=n_bins)
         frames_fft(s, plan.CQT_N_FFT, h, T, None, proj=proj)
     return out
+
+
+def plp_from_onset(onset_env: torch.Tensor, sr, hop_length: int = 1024, win_length: int = 1024, tempo_min=60, tempo_max=180):
+    """rosa/beat.py:46-75 after the onset envelope: onset_env [B, T] -> pulse [B, T] (normalised per clip)."""
+    onset_env, _ = _as_batch(onset_env)
+    B, T = onset_env.shape
+    win = min(T, win_length)
+    if win not in (1024, 2048):
+        raise NotImplementedError(f"plp: tempogram window {win} (clip shorter than {win_length} frames) is not built; "
+                                  "only the full 1024-frame window is")
+    tg = frames_fft(onset_env, win, 1, T + 1, torch.hann_window, want_complex=True)["complex"]  # [B, T+1, F, 2]
+    F = win // 2 + 1
+    freqs = torch.linspace(0, float(sr * 60 / float(hop_length)) / 2, F)
+    keep = torch.ones(F, dtype=torch.bool)
+    if tempo_min is not None:
+        keep &= ~(freqs < tempo_min)
+    if tempo_max is not None:
+        keep &= ~(freqs > tempo_max)
+    idx = keep.nonzero().flatten()
+    k_lo, k_hi = (int(idx[0]), int(idx[-1]) + 1) if len(idx) else (0, 0)
+    cabi.call("ssar_plp_peaks", ptr(tg), i64(F), i32(B), i32(T + 1), i32(F), i32(k_lo), i32(k_hi))
+    pulse = istft(tg, win, 1, torch.hann_window, T)
+    zero = torch.zeros(B, 1, dtype=torch.float32, device=pulse.device)
+    pulse = clamp_cols(pulse.view(B, T, 1), zero, None).view(B, T)  # clamp(pulse, 0, pulse.max())
+    return normalize(pulse, B)

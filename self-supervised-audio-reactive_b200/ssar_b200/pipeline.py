@@ -32,3 +32,96 @@ def spectral_frontend(x: torch.Tensor, sr, n_fft: int = 2048, hop: int = 512, wa
     )
     onset = ops.onset_flux(out["bank1"], out["bank1_max"], 1 + n_fft // (2 * hop), "mean")
     return {"spec": out.get("spec"), "mel": out["bank0"], "onset": onset, "rms": out["rms"]}
+
+
+def hpss_pair(x: torch.Tensor, margin: float = 8.0, n_fft: int = 2048, hop: int = 1024, D=None):
+    """harmonic(x), percussive(x) (features/audio.py:13-24) from ONE forward STFT and ONE pair of median passes.
+    x [B, N] -> (harm [B, N], perc [B, N]).  Exact: the two reference calls differ only in the mask applied."""
+    n = x.shape[-1]
+    if D is None:
+        D = ops.frames_fft(x, n_fft, hop, 1 + n // hop, torch.hann_window, want_complex=True)["complex"]
+    h, p = ops.hpss(D, margin, True, True)
+    return ops.istft(h, n_fft, hop, torch.hann_window, n), ops.istft(p, n_fft, hop, torch.hann_window, n)
+
+
+def band_split(x: torch.Tensor, sr):
+    """low_pass(x), mid_pass(x), high_pass(x) (features/processing.py:141-150) with three biquad passes: mid_pass is
+    literally low_pass(high_pass(x, 4000), 200), and high_pass(x, 4000) is also high_pass's default."""
+    lo_c, hi_c = plan.biquad_coeffs("low", sr, 200), plan.biquad_coeffs("high", sr, 4000)
+    high = ops.biquad(x, hi_c, clamp=True)
+    return ops.biquad(x, lo_c, clamp=True), ops.biquad(high, lo_c, clamp=True), high
+
+
+def onset_pair(x: torch.Tensor, sr, hop: int = 1024, n_fft: int = 2048, want_median: bool = False):
+    """onset_strength(x) with mean aggregation (+ the median-aggregated envelope plp needs) from one mel pass."""
+    bank = plan.mel_bank(float(sr), n_fft, 128, 0.0, 11025.0, str(x.device))
+    out = ops.frames_fft(x, n_fft, hop, x.shape[-1] // hop, torch.hann_window, banks=[(bank, True, True)])
+    pad = 1 + n_fft // (2 * hop)
+    mean = ops.onset_flux(out["bank0"], out["bank0_max"], pad, "mean")
+    med = ops.onset_flux(out["bank0"], out["bank0_max"], pad, "median") if want_median else None
+    return mean, med
+
+
+def audio2features_batch(audio: torch.Tensor, sr, fps, clamp=True, smooth=True, emphasis=False):
+    """supervised/data.py:60-107 for a batch of mono clips [B, N] at `sr` -> [B, T, 59].
+
+    Same arithmetic per clip as the reference call sequence; work the reference repeats on identical inputs is done
+    once (harmonic/percussive share an STFT + medians; chromagram(audio_harm) is computed once for both the chroma and
+    the tonnetz columns; the three band filters share the 4 kHz high-pass; the audio STFT feeds mfcc, contrast,
+    flatness and the HPSS)."""
+    from .resampling import resample
+
+    if audio.dim() != 2:
+        raise ValueError("audio2features_batch expects [clips, samples]")
+    x = resample(audio, sr, fps * 1024)
+    sr = fps * 1024
+    B, N = x.shape
+    n_fft, hop = 2048, 1024
+    T = N // hop
+    dev = str(x.device)
+
+    # --- full-band per-frame features: one pass over the audio for mel(mfcc) / magnitude(contrast) / flatness / rms
+    mel_bank = plan.mel_bank(float(sr), n_fft, 128, 0.0, None, dev)
+    fa = ops.frames_fft(x, n_fft, hop, T, torch.hann_window, spec_power=1, want_flatness=True, want_rms=True,
+                        banks=[(mel_bank, True, True)])
+    mfcc = ops.mfcc_from_mel(fa["bank0"], fa["bank0_max"], plan.dct_matrix(20, 128, dev))
+    contrast = ops.spectral_contrast(fa["spec"], plan.contrast_bands(float(sr), n_fft, 200.0, 6, 0.02, dev))
+    flatness = fa["flatness"]
+
+    # --- harmonic / percussive separation (and the second separation chromagram() applies to audio_harm)
+    harm, perc = hpss_pair(x)
+    harm2 = hpss_pair(harm)[0]  # harmonic(audio_harm): features/audio.py:44-45 applied to data.py:68-69's argument
+    C = ops.cqt(harm2, sr, hop)
+    cens = ops.cens_smooth(ops.chroma_from_cqt(C, quantize=True), plan.cens_window(41, dev), l2=True)  # [B, T, 12]
+    ton = ops.tonnetz(cens)
+
+    # --- onset envelopes of the percussive part and its three bands; pulse
+    p_lo, p_mid, p_hi = band_split(perc, sr)
+    on, on_med = onset_pair(perc, sr, hop, n_fft, want_median=True)
+    on_lo, on_mid, on_hi = (onset_pair(b, sr, hop, n_fft)[0] for b in (p_lo, p_mid, p_hi))
+    pulse = ops.plp_from_onset(on_med, sr, hop)
+
+    # --- rms of the harmonic part and its bands; drop strength of the full signal and its bands
+    h_lo, h_mid, h_hi = band_split(harm, sr)
+    rms_h = [ops.frames_rms(s, n_fft, hop, T) for s in (harm, h_lo, h_mid, h_hi)]
+    a_lo, a_mid, a_hi = band_split(x, sr)
+    rms_a = torch.stack([fa["rms"]] + [ops.frames_rms(s, n_fft, hop, T) for s in (a_lo, a_mid, a_hi)], dim=-1)  # [B,T,4]
+    drop = ops.emphasize(ops.gauss1d(rms_a, 10, "circular", batched=True), 10, 50)
+
+    Tm = min(T, cens.shape[1])
+    cols = [mfcc[:, :Tm], cens[:, :Tm], ton[:, :Tm], contrast[:, :Tm]]
+    cols += [s[:, :Tm, None] for s in (flatness, on, on_lo, on_mid, on_hi, pulse, *rms_h)]
+    cols.append(drop[:, :Tm])
+    feats = torch.cat(cols, dim=2).contiguous()
+
+    if clamp:
+        thr, cnt = ops.col_quantile(feats, (100 - 2.5) / 100, "peaks", "linear", want_count=True)
+        feats = ops.clamp_cols(feats, None, thr)
+        feats = ops.clamp_cols(feats, ops.col_quantile(feats, 4 * 2.5 / 100), None)
+        if int(cnt.min()) == 0:  # torch.quantile raises on a column without interior peaks (processing.py:117)
+            raise RuntimeError("quantile() input tensor must be non-empty")
+    if smooth:
+        feats = ops.gauss1d(feats, 0.1 * fps, "circular", batched=True)
+    if emphasis:
+        feats = ops.emphasize(feats, 2, 75)
+    return feats

@@ -144,7 +144,22 @@ def g_chroma(ref):
     )
 
 
-GROUPS = {"chroma": g_chroma, "post": g_post, "spectral": g_spectral, "frame_features": g_frame_features, "hpss_filters": g_hpss_filters}
+def g_a2f(ref):
+    """plp / pulse / onsets / drop_strength on a 45 s clip (T = 1080 >= the 1024-frame tempogram window) and the
+    full audio2features [1080, 59] of a 45 s 44.1 kHz clip (supervised/data.py:60-107)."""
+    n = SR * 45 + 100
+    x = synth_clip(n, SR, 6)
+    x44 = synth_clip(44100 * 45 + 100, 44100, 8)
+    save(
+        "a2f", n=n, sr=SR, clip_index=6, n44=len(x44), clip_index44=8,
+        plp=ref.beat.plp(x, SR), pulse=ref.audio.pulse(x, SR), onsets=ref.audio.onsets(x, SR),
+        drop_strength=ref.audio.drop_strength(x, SR),
+        features=ref.data.audio2features(x44, 44100, 24),
+        features_raw=ref.data.audio2features(x44, 44100, 24, clamp=False, smooth=False),
+    )
+
+
+GROUPS = {"a2f": g_a2f, "chroma": g_chroma, "post": g_post, "spectral": g_spectral, "frame_features": g_frame_features, "hpss_filters": g_hpss_filters}
 
 if __name__ == "__main__":
     torch.manual_seed(0)
