@@ -29,6 +29,18 @@ def test_plp_onsets_drop_vs_golden():
     assert tuple(d.shape) == tuple(g["drop_strength"].shape) and rel_l2(d, g["drop_strength"]) < 1e-4
 
 
+def test_plp_exact_given_envelope():
+    """The PLP kernels reproduce the oracle to 1e-5 when fed the oracle's own onset envelope."""
+    from ssar_b200 import ops
+    from ssar_oracle import dsp
+
+    g = load("a2f")
+    sr = int(g["sr"])
+    x = synth_clip(int(g["n"]), sr, int(g["clip_index"]))
+    env = dsp.onset_strength(x, sr, aggregate="median")
+    assert rel_l2(ops.plp_from_onset(env.cuda()[None], sr)[0], dsp.plp(x, sr)) < 1e-5
+
+
 # per-column tolerance on the un-clamped, un-smoothed features: spectra-derived columns 1e-3 (north star: onset /
 # chroma class), everything measured as rel-L2 per column against the unmodified reference's output
 def test_audio2features_vs_golden():
@@ -41,11 +53,18 @@ def test_audio2features_vs_golden():
     worst = {}
     for j, name in enumerate(FEATURE_NAMES):
         worst[name] = rel_l2(raw[:, j], g["features_raw"][:, j])
-    bad = {k: v for k, v in worst.items() if v > 2e-3}
+    # pulse: plp keeps ONE arg-max tempogram bin per frame; a near-tie flips under the 1e-5 fp32 noise of the onset
+    # envelope (reference noise floor), which moves the pulse by O(1e-3).  The kernel itself is exact given the same
+    # envelope (test_plp_exact_given_envelope, 1e-5); through the chain the column is held to 1e-2.
+    tol = {name: 2e-3 for name in FEATURE_NAMES}
+    tol["pulse"] = 1e-2
+    bad = {k: v for k, v in worst.items() if v > tol[k]}
     assert not bad, bad
     f = audio2features(x, 44100, 24)
     assert tuple(f.shape) == (1080, 59)
     assert rel_l2(f, g["features"]) < 1e-3
+    keep = [j for j, n in enumerate(FEATURE_NAMES) if n != "pulse"]
+    assert rel_l2(f[:, keep], g["features"][:, keep]) < 1e-4
     # stereo input is averaged to mono first (supervised/data.py:61-62)
     f2 = audio2features(torch.stack([x, x]), 44100, 24)
     assert rel_l2(f2, f) < 1e-6
