@@ -269,6 +269,55 @@ int ssar_hwr_rowsum(const float* x, long long n_rows, int inner, float* out, voi
  * into stats[3, n_cols] (caller zeroes it; all-reduce it over ranks, then mean = s/n, std = sqrt(ss/n - mean^2)) */
 int ssar_feature_stats(const float* x, long long n_rows, int n_cols, double* stats, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Trajectory construction: latent sequences [T, num_ws, 512] and per-layer noise maps
+ * ---------------------------------------------------------------------------------------------- */
+
+/* out[t, n] = row_alpha[t] * out[t, n] + row_beta[t] * sum_k weights_{g(n)}[t, k] * basis[k, n] for n in
+ * [col_begin, col_end), g(n) = n / group_cols, weights_g = weights + g * group_stride (row stride ldw).
+ * row_alpha NULL = overwrite (0), row_beta NULL = 1.  Stands in for einsum("TN,NWL->TWL") and every merge of
+ * ssar/random/latent.py:35-78, the spline evaluation of :7-13, features/generate.py:167,181,216-218 and
+ * models/latent_n_noise2.py:150-161 (per-split weights = one group per split).
+ * col_begin and group_cols multiples of 128; basis / out rows 16-byte aligned. */
+int ssar_mix_gemm(const float* weights, long long ldw, long long group_stride, int group_cols,
+                  const float* basis, long long ldb, float* out, long long ldo, int n_rows, int n_basis,
+                  int col_begin, int col_end, const float* row_alpha, const float* row_beta, void* stream);
+
+/* weights[t, g, k] = alpha[t] * weights[t, g, k] + beta[t] * seq[t, k] for g in [g_begin, g_end): the average /
+ * modulate / overwrite merges of latent.py:68-78 applied to weight matrices [n_rows, n_groups, n_basis].
+ * alpha / beta NULL -> the scalars. */
+int ssar_weights_merge(float* weights, int n_rows, int n_groups, int n_basis, int g_begin, int g_end,
+                       const float* seq, const float* alpha, const float* beta, float alpha_scalar,
+                       float beta_scalar, void* stream);
+
+/* out[t, j] = mu[t] + sig[t] * x[t, j] (models/latent_n_noise2.py:163-176); mu / sig NULL -> 0 / 1 */
+int ssar_rows_affine(const float* x, long long n_rows, long long inner, const float* mu, const float* sig,
+                     float* out, void* stream);
+
+/* One op of a compiled noise program (ssar/random/noise.py:4-86).  Leaves write `cur` (or `acc` when to_acc != 0). */
+#define SSAR_NOISE_LOOP 0      /* noise [3,H,W], mod = idx [length], p0 = sigma / 50                    (:42-53) */
+#define SSAR_NOISE_BLEND 1     /* noise [2,M,H,W], mod [length, M]                                      (:11-24) */
+#define SSAR_NOISE_MULTIPLY 2  /* noise [M,H,W], mod [length, M]                                        (:27-39) */
+#define SSAR_NOISE_BUFFER 3    /* noise = precomputed [n_frames, H*W] for this batch                             */
+#define SSAR_NOISE_AVERAGE 4   /* acc = (acc + cur) / 2                                                 (:56-63) */
+#define SSAR_NOISE_MODULATE 5  /* mod [length]: acc = acc * mod + cur * (1 - mod)                       (:66-75) */
+#define SSAR_NOISE_SCALEBIAS 6 /* acc = p0 * acc + p1                                                   (:78-86) */
+typedef struct {
+    int kind;
+    int M;
+    int to_acc;
+    int reserved;
+    const float* noise;
+    const float* mod;
+    float p0, p1;
+} ssar_noise_op;
+
+/* Evaluates a program for frames [first_frame, first_frame + n_frames) -> out [n_frames, height * width].
+ * ops_device / ops_host: the same n_ops ops in device and host memory (the host copy is only validated);
+ * loop_scratch: (number of LOOP ops) * n_frames floats of device scratch (may be NULL without LOOP ops). */
+int ssar_noise_eval(const ssar_noise_op* ops_device, const ssar_noise_op* ops_host, int n_ops, int first_frame,
+                    int n_frames, int height, int width, float* loop_scratch, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,170 @@
+// Latent-trajectory kernels: feature-weighted sums of latent bases written straight into [T, num_ws, 512].
+//
+// Every latent sequence the reference builds is linear in the latent palette with time-varying scalar weights:
+//   einsum("TN,NWL->TWL") (ssar/random/latent.py:48, features/generate.py:167,216, models/latent_n_noise2.py:159),
+//   the 2-latent lerp (latent.py:45), segmentation gathers (latent.py:39-41), natural-cubic-spline loops
+//   (latent.py:7-13: sum_k B_k(t) y_k) and the Gaussian smoothing / average / modulate merges that follow them.
+// So the host keeps only the small weight matrices  A_g [T, K]  (one per layer group g) and this kernel does
+//   C[t, n] = alpha[t] * C[t, n] + beta[t] * sum_k A_{g(n)}[t, k] * B[k, n],     n = layer * 512 + l
+// once, with B = the palette [K, num_ws * 512] and g(n) = n / group_cols.
+//
+// Tiling: CTA = 64 rows x 128 columns, K in slabs of 16 staged in shared memory, 256 threads each owning an 8 x 4
+// register tile (float4 along n: coalesced 512-byte rows for B loads and C stores).  The op is bound by the C write
+// (36.9 kB per frame); K is small (<= a few hundred).
+#include "common.cuh"
+
+namespace {
+
+constexpr int BM = 64, BN = 128, BK = 16;
+constexpr int AS_LD = BM + 4;
+
+__global__ void __launch_bounds__(256) mix_gemm_kernel(const float* __restrict__ A, long long lda, long long group_stride,
+                                                       int group_cols, const float* __restrict__ B, long long ldb,
+                                                       float* __restrict__ C, long long ldc, int M, int K, int col0,
+                                                       int col1, const float* __restrict__ row_alpha,
+                                                       const float* __restrict__ row_beta) {
+    __shared__ __align__(16) float As[BK * AS_LD];
+    __shared__ __align__(16) float Bs[BK * BN];
+    const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
+    const int m0 = blockIdx.y * BM;
+    const int n0 = col0 + blockIdx.x * BN;
+    const float* Ag = A + (long long)(n0 / group_cols) * group_stride;
+
+    float acc[8][4];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+    for (int k0 = 0; k0 < K; k0 += BK) {
+        // A slab: 64 rows x 16 k (row-major in global) -> As[k][row]
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int idx = tid + i * 256;
+            const int r = idx >> 4, k = idx & 15;
+            const int m = m0 + r;
+            As[k * AS_LD + r] = (m < M && k0 + k < K) ? __ldg(Ag + (long long)m * lda + k0 + k) : 0.f;
+        }
+        // B slab: 16 k x 128 columns
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int idx = tid + i * 256;
+            const int k = idx >> 5, c4 = idx & 31;
+            const int n = n0 + c4 * 4;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (k0 + k < K && n + 3 < col1) v = __ldg(reinterpret_cast<const float4*>(B + (long long)(k0 + k) * ldb + n));
+            *reinterpret_cast<float4*>(&Bs[k * BN + c4 * 4]) = v;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < BK; ++k) {
+            const float4 b = *reinterpret_cast<const float4*>(&Bs[k * BN + tx * 4]);
+            const float4 a0 = *reinterpret_cast<const float4*>(&As[k * AS_LD + ty * 8]);
+            const float4 a1 = *reinterpret_cast<const float4*>(&As[k * AS_LD + ty * 8 + 4]);
+            const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                acc[i][0] = fmaf(a[i], b.x, acc[i][0]);
+                acc[i][1] = fmaf(a[i], b.y, acc[i][1]);
+                acc[i][2] = fmaf(a[i], b.z, acc[i][2]);
+                acc[i][3] = fmaf(a[i], b.w, acc[i][3]);
+            }
+        }
+        __syncthreads();
+    }
+
+    const int n = n0 + tx * 4;
+    if (n + 3 >= col1) return;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int m = m0 + ty * 8 + i;
+        if (m >= M) continue;
+        float4* dst = reinterpret_cast<float4*>(C + (long long)m * ldc + n);
+        float4 r = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+        if (row_beta) {
+            const float bt = __ldg(row_beta + m);
+            r.x *= bt; r.y *= bt; r.z *= bt; r.w *= bt;
+        }
+        if (row_alpha) {
+            const float al = __ldg(row_alpha + m);
+            const float4 old = *dst;
+            r.x = fmaf(al, old.x, r.x);
+            r.y = fmaf(al, old.y, r.y);
+            r.z = fmaf(al, old.z, r.z);
+            r.w = fmaf(al, old.w, r.w);
+        }
+        *dst = r;
+    }
+}
+
+// weights[t, g, k] = alpha[t] * weights[t, g, k] + beta[t] * S[t, k]   for g in [g0, g1)
+// (the average / modulate / overwrite merges of latent.py:68-78 applied to the weight matrices)
+__global__ void weights_merge_kernel(float* __restrict__ Wt, int T, int G, int K, int g0, int g1,
+                                     const float* __restrict__ S, const float* __restrict__ alpha,
+                                     const float* __restrict__ beta, float alpha_s, float beta_s) {
+    const long long n = (long long)T * (g1 - g0) * K;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const int k = (int)(i % K);
+        const long long r = i / K;
+        const int g = g0 + (int)(r % (g1 - g0));
+        const int t = (int)(r / (g1 - g0));
+        const float al = alpha ? alpha[t] : alpha_s, be = beta ? beta[t] : beta_s;
+        float* w = Wt + ((long long)t * G + g) * K + k;
+        *w = al * *w + be * S[(long long)t * K + k];
+    }
+}
+
+// out[t, j] = mu[t] + sig[t] * x[t, j]   (models/latent_n_noise2.py:169-174) — mu / sig may be NULL (0 / 1)
+__global__ void rows_affine_kernel(const float* __restrict__ x, long long rows, long long inner, const float* __restrict__ mu,
+                                   const float* __restrict__ sig, float* __restrict__ out) {
+    const long long n = rows * inner;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const long long t = i / inner;
+        const float m = mu ? mu[t] : 0.f, s = sig ? sig[t] : 1.f;
+        out[i] = m + s * x[i];
+    }
+}
+
+}  // namespace
+
+extern "C" int ssar_mix_gemm(const float* weights, long long ldw, long long group_stride, int group_cols,
+                             const float* basis, long long ldb, float* out, long long ldo, int n_rows, int n_basis,
+                             int col_begin, int col_end, const float* row_alpha, const float* row_beta, void* stream) {
+    if (n_rows == 0 || col_end <= col_begin) return SSAR_OK;
+    SSAR_REQUIRE(weights && basis && out, "mix_gemm: null pointer");
+    SSAR_REQUIRE(n_basis >= 0 && group_cols > 0, "mix_gemm: bad sizes");
+    SSAR_REQUIRE(col_begin % BN == 0 && (col_end - col_begin) % 4 == 0 && group_cols % BN == 0,
+                 "mix_gemm: col_begin and group_cols must be multiples of 128 and the column count a multiple of 4");
+    SSAR_REQUIRE((ldb % 4 == 0) && (ldo % 4 == 0) && ((uintptr_t)basis % 16 == 0) && ((uintptr_t)out % 16 == 0),
+                 "mix_gemm: basis / out rows must be 16-byte aligned");
+    dim3 grid(ssar_div_up(col_end - col_begin, BN), ssar_div_up(n_rows, BM));
+    SSAR_REQUIRE(grid.y <= 65535, "mix_gemm: too many rows per launch");
+    mix_gemm_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(weights, ldw, group_stride, group_cols, basis, ldb, out, ldo,
+                                                           n_rows, n_basis, col_begin, col_end, row_alpha, row_beta);
+    return ssar_launch_status("mix_gemm");
+}
+
+extern "C" int ssar_weights_merge(float* weights, int n_rows, int n_groups, int n_basis, int g_begin, int g_end,
+                                  const float* seq, const float* alpha, const float* beta, float alpha_scalar,
+                                  float beta_scalar, void* stream) {
+    if (n_rows == 0 || n_basis == 0 || g_end <= g_begin) return SSAR_OK;
+    SSAR_REQUIRE(weights && seq, "weights_merge: null pointer");
+    SSAR_REQUIRE(0 <= g_begin && g_end <= n_groups, "weights_merge: bad group range");
+    const long long n = (long long)n_rows * (g_end - g_begin) * n_basis;
+    int grid = ssar_div_up(n, 256);
+    if (grid > SSAR_NUM_SMS * 8) grid = SSAR_NUM_SMS * 8;
+    weights_merge_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(weights, n_rows, n_groups, n_basis, g_begin, g_end, seq,
+                                                                alpha, beta, alpha_scalar, beta_scalar);
+    return ssar_launch_status("weights_merge");
+}
+
+extern "C" int ssar_rows_affine(const float* x, long long n_rows, long long inner, const float* mu, const float* sig,
+                                float* out, void* stream) {
+    if (n_rows == 0 || inner == 0) return SSAR_OK;
+    SSAR_REQUIRE(x && out, "rows_affine: null pointer");
+    int grid = ssar_div_up(n_rows * inner, 256 * 4);
+    if (grid > SSAR_NUM_SMS * 8) grid = SSAR_NUM_SMS * 8;
+    if (grid < 1) grid = 1;
+    rows_affine_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, n_rows, inner, mu, sig, out);
+    return ssar_launch_status("rows_affine");
+}

@@ -50,6 +50,13 @@ class FramesArgs(C.Structure):
     ]
 
 
+class NoiseOp(C.Structure):
+    _fields_ = [
+        ("kind", C.c_int), ("M", C.c_int), ("to_acc", C.c_int), ("reserved", C.c_int),
+        ("noise", C.c_void_p), ("mod", C.c_void_p), ("p0", C.c_float), ("p1", C.c_float),
+    ]
+
+
 def lib():
     """Loads the library once; raises (never falls back) when it has not been built."""
     global _lib

@@ -457,3 +457,68 @@ def plp_from_onset(onset_env: torch.Tensor, sr, hop_length: int = 1024, win_leng
     zero = torch.zeros(B, 1, dtype=torch.float32, device=pulse.device)
     pulse = clamp_cols(pulse.view(B, T, 1), zero, None).view(B, T)  # clamp(pulse, 0, pulse.max())
     return normalize(pulse, B)
+
+
+# ------------------------------------------------------------------------------------------------
+# trajectory construction (csrc/traj_mix.cu, csrc/traj_noise.cu)
+# ------------------------------------------------------------------------------------------------
+def mix_gemm(weights: torch.Tensor, basis: torch.Tensor, out: torch.Tensor | None = None, group_cols: int | None = None,
+             col_begin: int = 0, col_end: int | None = None, row_alpha=None, row_beta=None):
+    """out[t, n] = row_alpha[t] * out[t, n] + row_beta[t] * sum_k weights[t, g(n), k] * basis[k, n].
+
+    weights: [T, K] (one group) or [T, G, K]; basis: [K, ...] flattened to [K, N]; out: [T, ...] with N elements per row
+    (allocated when None).  g(n) = n // group_cols (default N // G)."""
+    if not (weights.is_cuda and basis.is_cuda):
+        raise SsarError("ssar_b200 needs CUDA tensors (no CPU fallback)")
+    weights = weights.contiguous().float()
+    basis = basis.contiguous().float()
+    if weights.dim() == 2:
+        weights = weights[:, None, :]
+    T, G, K = weights.shape
+    if basis.shape[0] != K:
+        raise SsarError(f"mix_gemm: weights have {K} columns but the basis has {basis.shape[0]} rows")
+    N = basis.numel() // max(K, 1)
+    if out is None:
+        out = torch.empty((T,) + tuple(basis.shape[1:]), dtype=torch.float32, device=basis.device)
+    if not out.is_contiguous() or out.numel() != T * N:
+        raise SsarError("mix_gemm: out must be a contiguous [T, N] tensor")
+    if group_cols is None:
+        group_cols = N // G
+    if col_end is None:
+        col_end = N
+    cabi.call("ssar_mix_gemm", ptr(weights), i64(G * K), i64(K), i32(group_cols), ptr(basis), i64(N), ptr(out), i64(N),
+              i32(T), i32(K), i32(col_begin), i32(col_end), ptr(row_alpha), ptr(row_beta))
+    return out
+
+
+def weights_merge(weights: torch.Tensor, seq: torch.Tensor, g_begin: int, g_end: int, alpha, beta):
+    """In place: weights[:, g, :] = alpha * weights[:, g, :] + beta * seq for g in [g_begin, g_end); alpha / beta are
+    floats or [T] tensors."""
+    T, G, K = weights.shape
+    a_t, b_t = (alpha if torch.is_tensor(alpha) else None), (beta if torch.is_tensor(beta) else None)
+    cabi.call("ssar_weights_merge", ptr(weights), i32(T), i32(G), i32(K), i32(g_begin), i32(g_end), ptr(seq.contiguous()),
+              ptr(a_t), ptr(b_t), f32(0.0 if a_t is not None else alpha), f32(0.0 if b_t is not None else beta))
+    return weights
+
+
+def rows_affine(x: torch.Tensor, mu=None, sig=None):
+    """out[t, ...] = mu[t] + sig[t] * x[t, ...]."""
+    x = x.contiguous()
+    rows = x.shape[0]
+    out = torch.empty_like(x)
+    cabi.call("ssar_rows_affine", ptr(x), i64(rows), i64(x.numel() // max(rows, 1)), ptr(mu), ptr(sig), ptr(out))
+    return out
+
+
+def noise_eval(ops_list, i: int, b: int, height: int, width: int, device):
+    """Runs a compiled noise program (list of `_cabi.NoiseOp`) for frames [i, i + b) -> [b, height, width]."""
+    n = len(ops_list)
+    arr = (cabi.NoiseOp * n)(*ops_list)
+    host_bytes = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
+    dev_ops = host_bytes.to(device)
+    n_loops = sum(1 for o in ops_list if o.kind == 0)
+    scratch = torch.empty(max(n_loops * b, 1), dtype=torch.float32, device=device)
+    out = torch.empty(b, height, width, dtype=torch.float32, device=device)
+    cabi.call("ssar_noise_eval", ptr(dev_ops), C.cast(arr, C.c_void_p), i32(n), i32(i), i32(b), i32(height), i32(width),
+              ptr(scratch), ptr(out))
+    return out

@@ -477,3 +477,30 @@ def tonnetz_phi(n_chroma: int, device) -> torch.Tensor:
     V[::2] -= 0.5
     R = torch.tensor([1, 1, 1, 1, 0.5, 0.5])
     return (R[:, None] * torch.cos(torch.pi * V)).contiguous().to(_dev(device))
+
+
+def spline_loop_weights_cpu(n_knots: int, size: int, n_loops=1) -> torch.Tensor:
+    """Cardinal weights of ssar/random/latent.py:7-13: out[t] = sum_k W[t, k] y[k] for the natural cubic spline through
+    (y_0 .. y_{K-1}, y_0) on linspace(0, 1, K + 1), evaluated at linspace(0, n_loops, size) % 1 (upstream
+    torchcubicspline evaluate: index = clamp(bucketize(t) - 1), value = a + b f + two_c f^2 / 2 + three_d f^3 / 3).
+    The closing knot's weight is folded onto knot 0.  Returns fp32 [size, n_knots]."""
+    K1 = n_knots + 1
+    t_in = torch.linspace(0, 1, K1)
+    t_out = torch.linspace(0, n_loops, size) % 1
+    idx = (torch.bucketize(t_out, t_in) - 1).clamp(0, K1 - 2)
+    frac = (t_out - t_in[idx]).double().numpy()
+    idx = idx.numpy()
+    if K1 == 2:
+        t64 = t_in.double().numpy()
+        W = np.zeros((size, 2))
+        slope = 1.0 / (t64[1] - t64[0])
+        W[:, 0] = 1.0 - slope * frac
+        W[:, 1] = slope * frac
+    else:
+        eye = np.eye(K1)
+        coeffs = [natural_cubic_spline_np(t_in.numpy(), eye[k]) for k in range(K1)]
+        W = np.zeros((size, K1))
+        for k, (a, b, c2, d3) in enumerate(coeffs):
+            W[:, k] = a[idx] + (b[idx] + (0.5 * c2[idx] + d3[idx] * frac / 3.0) * frac) * frac
+    W[:, 0] += W[:, -1]
+    return torch.from_numpy(W[:, :-1].astype(np.float32))

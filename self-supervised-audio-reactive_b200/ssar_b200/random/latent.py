@@ -1,0 +1,100 @@
+"""Mirror of ssar/random/latent.py — latent-sequence construction as weight matrices + one mixing GEMM.
+
+Every sequence here is linear in the palette, so smoothing and merging act on small [T, K] weight matrices and the
+[T, 18, 512] tensor is touched once per call (`latent_patch`, in place like the reference) or once in total
+(`LatentWeights`, used by `Patch.forward`)."""
+from __future__ import annotations
+
+import torch
+
+from .. import ops, plan
+
+LAYER_SLICES = {"low": (0, 6), "mid": (6, 12), "high": (12, 18), "lowmid": (0, 12), "midhigh": (6, 18), "all": (0, 18)}
+
+
+def spline_loop_latents(y, size, n_loops=1):
+    """ssar/random/latent.py:7-13: y [K, W, L] -> [size, W, L]."""
+    W = plan.spline_loop_weights_cpu(len(y), int(size), n_loops).to(y.device)
+    return ops.mix_gemm(W, y)
+
+
+def sequence_weights(rng, n_frames, n_palette, segmentations, features, tempo, fps, patch_type, segments, loop_bars,
+                     seq_feat, seq_feat_weight, device):
+    """The sub-patch's sequence (latent.py:35-54) as (selection [K] long on the rng device, weights [T, K] on `device`)
+    with the Gaussian smoothing of :41 and :54 already applied to the weights (it commutes with the palette sum)."""
+    feature = seq_feat_weight * features[seq_feat]
+    segmentation = segmentations[(seq_feat, segments)]
+    permutation = torch.randperm(n_palette, generator=rng, device=rng.device)
+    if patch_type == "segmentation":
+        selection = permutation[:segments]
+        onehot = torch.zeros(n_frames, int(segments), dtype=torch.float32, device=device)
+        onehot[torch.arange(n_frames, device=device), segmentation.to(device).long()] = 1.0
+        S = ops.gauss1d(onehot, 5, "circular")
+    elif patch_type == "feature":
+        n_select = feature.shape[1]
+        if n_select == 1:
+            selection = permutation[:2]
+            f = feature.to(device).float().reshape(n_frames, 1)
+            S = torch.cat([f, 1 - f], dim=1)
+        else:
+            selection = permutation[:n_select]
+            S = feature.to(device).float()
+    elif patch_type == "loop":
+        selection = permutation[:segments]
+        n_loops = n_frames / fps / 60 / tempo / 4 / loop_bars
+        S = plan.spline_loop_weights_cpu(len(selection), n_frames, n_loops).to(device)
+    else:
+        raise ValueError(patch_type)
+    return selection, ops.gauss1d(S.contiguous(), 1, "circular")
+
+
+def merge_coefficients(features, merge_type, mod_feat, mod_feat_weight, n_frames, device):
+    """latent.py:68-78 as (alpha, beta): latents = alpha * latents + beta * sequence (floats or [T] tensors)."""
+    if merge_type == "average":
+        return 0.5, 0.5
+    if merge_type == "modulate":
+        m = (mod_feat_weight * features[mod_feat]).to(device).float().reshape(n_frames).contiguous()
+        return (1 - m).contiguous(), m
+    return 0.0, 1.0  # overwrite
+
+
+def latent_patch(rng, latents, palette, segmentations, features, tempo, fps, patch_type, segments, loop_bars, seq_feat,
+                 seq_feat_weight, mod_feat, mod_feat_weight, merge_type, merge_depth):
+    """ssar/random/latent.py:16-80 — modifies `latents` [T, W, L] IN PLACE (like the reference) and returns it."""
+    T, Wn, L = latents.shape
+    dev = latents.device
+    selection, S = sequence_weights(rng, T, len(palette), segmentations, features, tempo, fps, patch_type, segments,
+                                    loop_bars, seq_feat, seq_feat_weight, dev)
+    alpha, beta = merge_coefficients(features, merge_type, mod_feat, mod_feat_weight, T, dev)
+    lo, hi = LAYER_SLICES[merge_depth]
+    a_t = alpha if torch.is_tensor(alpha) else torch.full((T,), float(alpha), device=dev)
+    b_t = beta if torch.is_tensor(beta) else torch.full((T,), float(beta), device=dev)
+    ops.mix_gemm(S, palette[selection.to(palette.device)].to(dev), out=latents, col_begin=lo * L, col_end=min(hi, Wn) * L,
+                 row_alpha=a_t, row_beta=b_t)
+    return latents
+
+
+class LatentWeights:
+    """Accumulates a whole stack of sub-patches as weights [T, G, P] over the full palette (G layer groups of
+    `group_layers` layers) and renders [T, W, L] with ONE mixing GEMM."""
+
+    def __init__(self, n_frames, n_palette, n_layers=18, group_layers=6, device="cuda"):
+        self.T, self.P, self.Wn, self.gl = n_frames, n_palette, n_layers, group_layers
+        self.G = n_layers // group_layers
+        self.device = torch.device(device)
+        self.w = torch.zeros(self.T, self.G, self.P, dtype=torch.float32, device=self.device)
+
+    def _dense(self, selection, S):
+        D = torch.zeros(self.T, self.P, dtype=torch.float32, device=self.device)
+        D.index_add_(1, selection.to(self.device).long(), S)  # duplicates (the closing spline knot) accumulate
+        return D
+
+    def set_base(self, selection, S):
+        ops.weights_merge(self.w, self._dense(selection, S), 0, self.G, 0.0, 1.0)
+
+    def merge(self, selection, S, alpha, beta, merge_depth):
+        lo, hi = LAYER_SLICES[merge_depth]
+        ops.weights_merge(self.w, self._dense(selection, S), lo // self.gl, hi // self.gl, alpha, beta)
+
+    def render(self, palette):
+        return ops.mix_gemm(self.w, palette.to(self.device))

@@ -74,3 +74,29 @@ def synth_features(n_frames: int, n_cols: int, seed: int = 0) -> torch.Tensor:
     jitter = 0.3 * torch.randn(n_frames, n_cols, generator=g)
     scale = torch.linspace(0.5, 20.0, n_cols)
     return ((walk + spikes + jitter) * scale + torch.arange(n_cols) * 0.25).float()
+
+
+PATCH_FEATURE_DIMS = {"chromagram": 12, "tonnetz": 6, "mfcc": 20, "spectral_contrast": 7, "rms": 1, "drop_strength": 1,
+                      "onsets": 1, "spectral_flatness": 1}
+
+
+def synth_patch_inputs(n_frames: int, seed: int = 0, n_palette: int = 180):
+    """Deterministic inputs of `Patch` (SURVEY.md 8d cfg 4): normalised [T, C] features per name, random segmentations
+    randint(0, k, [T]) for k in {2,4,6,8,12,16} per feature name (+ "rosa"), and a latent palette [P, 18, 512]."""
+    feats = {}
+    for j, (name, c) in enumerate(PATCH_FEATURE_DIMS.items()):
+        f = synth_features(n_frames, c, 40 + 17 * seed + j)
+        f = f - f.min()
+        feats[name] = f / (f.max() + 1e-8)
+    g = torch.Generator("cpu").manual_seed(7000 + seed)
+    segs = {}
+    for name in list(PATCH_FEATURE_DIMS) + ["rosa"]:
+        for k in (2, 4, 6, 8, 12, 16):
+            segs[(name, k)] = torch.randint(0, k, (n_frames,), generator=g)
+    palette = torch.randn(n_palette, 18, 512, generator=torch.Generator("cpu").manual_seed(3000 + seed))
+    return feats, segs, palette
+
+
+def projection_matrix(n_in: int = 512, n_out: int = 8) -> torch.Tensor:
+    """Fixed random projection used to store compact fingerprints of [T, 18, 512] tensors in the golden fixtures."""
+    return torch.randn(n_in, n_out, generator=torch.Generator("cpu").manual_seed(555)) / n_in ** 0.5

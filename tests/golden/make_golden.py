@@ -18,7 +18,7 @@ sys.path.insert(0, str(HERE))
 sys.path.insert(0, str(ROOT / "self-supervised-audio-reactive_b200"))
 
 from ref_loader import load_reference  # noqa: E402
-from ssar_b200.synth import synth_clip, synth_features  # noqa: E402
+from ssar_b200.synth import projection_matrix, synth_clip, synth_features, synth_patch_inputs  # noqa: E402
 
 SR = 24576
 
@@ -159,7 +159,46 @@ def g_a2f(ref):
     )
 
 
-GROUPS = {"a2f": g_a2f, "chroma": g_chroma, "post": g_post, "spectral": g_spectral, "frame_features": g_frame_features, "hpss_filters": g_hpss_filters}
+def g_traj(ref):
+    """Patch(seed).forward latents / noise batches, spline loops, latent_patch, FixedLatentNoiseDecoder.
+    Full [T, 18, 512] tensors are stored as a fixed random projection (512 -> 8) plus a few whole frames."""
+    T = 600
+    R = projection_matrix()
+    out = {}
+    for seed in (42, 7):
+        feats, segs, palette = synth_patch_inputs(T, 0)
+        patch = ref.patch.Patch(feats, segs, 120.0, fps=24, seed=seed, device="cpu")
+        lat, noise = patch.forward(palette, downscale_factor=4)
+        out[f"lat_proj_{seed}"] = lat @ R
+        out[f"lat_frames_{seed}"] = lat[::120]
+        for j in (0, 3, 8, 12, 16):
+            nz = noise[j].forward(10, 7)
+            out[f"noise_{seed}_{j}"] = nz if nz.shape[-1] <= 64 else nz[:, ::8, ::8]
+        out[f"noise_tail_{seed}"] = noise[6].forward(T - 3, 32)
+        out[f"n_sub_{seed}"] = np.array([len(patch.latent_patches), len(patch.noise_patches)])
+    feats, segs, palette = synth_patch_inputs(T, 0)
+    out["spline_proj"] = ref.latent.spline_loop_latents(palette[:8], T, 1) @ R
+    out["spline_loops_proj"] = ref.latent.spline_loop_latents(palette[8:13], T, 2.37) @ R
+    # one explicit latent_patch of every kind on a fresh base (in place)
+    rng = torch.Generator("cpu").manual_seed(5)
+    lat = ref.latent.spline_loop_latents(palette[:6], T)
+    for kind, merge, depth, sf in (("segmentation", "average", "low", "mfcc"), ("feature", "modulate", "midhigh", "chromagram"),
+                                   ("feature", "modulate", "all", "onsets"), ("loop", "overwrite", "high", "tonnetz")):
+        lat = ref.latent.latent_patch(rng, lat, palette, segs, feats, 120.0, 24, kind, 6, 8, sf, 0.8, "rms", 0.9, merge, depth)
+    out["latent_patch_proj"] = lat @ R
+    # FixedLatentNoiseDecoder
+    torch.manual_seed(0)
+    dec = ref.lnn2.FixedLatentNoiseDecoder(palette[:9], hidden_size=3, n_latent_split=3, n_noise=4)
+    x = synth_features(2 * 300, 17, 77).abs().reshape(2, 300, 17) + 0.1
+    torch.manual_seed(0)
+    dl, dn = dec.forward(x)
+    out["dec_proj"] = dl @ R
+    for i, n in enumerate(dn):
+        out[f"dec_noise_{i}"] = n[:, ::10]
+    save("traj", **out)
+
+
+GROUPS = {"traj": g_traj, "a2f": g_a2f, "chroma": g_chroma, "post": g_post, "spectral": g_spectral, "frame_features": g_frame_features, "hpss_filters": g_hpss_filters}
 
 if __name__ == "__main__":
     torch.manual_seed(0)

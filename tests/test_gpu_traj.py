@@ -1,0 +1,99 @@
+"""GPU parity: trajectory kernels (mix GEMM, weight merges, noise programs, fixed decoder) vs reference goldens."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN, rel_l2
+from ssar_b200.synth import projection_matrix, synth_features, synth_patch_inputs
+
+pytestmark = pytest.mark.gpu
+T = 600
+TOL = 1e-4  # north-star fp32 tolerance class for sums of latents (summation order differs from the reference)
+
+
+def load(name):
+    return {k: torch.from_numpy(np.asarray(v)) for k, v in np.load(GOLDEN / f"{name}.npz").items()}
+
+
+def sub(nz):
+    return nz if nz.shape[-1] <= 64 else nz[:, ::8, ::8]
+
+
+def cuda_inputs():
+    feats, segs, palette = synth_patch_inputs(T, 0)
+    return {k: v.cuda() for k, v in feats.items()}, segs, palette.cuda()
+
+
+def test_patch_forward_vs_golden():
+    from ssar_b200.random.patch import Patch
+
+    g = load("traj")
+    R = projection_matrix().cuda()
+    for seed in (42, 7):
+        feats, segs, palette = cuda_inputs()
+        patch = Patch(feats, segs, 120.0, fps=24, seed=seed, device="cpu")  # CPU generator: same draws as the golden run
+        assert [len(patch.latent_patches), len(patch.noise_patches)] == g[f"n_sub_{seed}"].tolist()
+        lat, noise = patch.forward(palette, downscale_factor=4)
+        assert tuple(lat.shape) == (T, 18, 512) and len(noise) == 17
+        assert rel_l2(lat @ R, g[f"lat_proj_{seed}"]) < TOL
+        assert rel_l2(lat[::120], g[f"lat_frames_{seed}"]) < TOL
+        for j in (0, 3, 8, 12, 16):
+            nz = noise[j].forward(10, 7)
+            assert rel_l2(sub(nz), g[f"noise_{seed}_{j}"]) < TOL, j
+        tail = noise[6].forward(T - 3, 32)
+        assert tuple(tail.shape) == tuple(g[f"noise_tail_{seed}"].shape)
+        assert rel_l2(tail, g[f"noise_tail_{seed}"]) < TOL
+
+
+def test_spline_latent_patch_decoder_vs_golden():
+    from ssar_b200.models.latent_n_noise2 import FixedLatentNoiseDecoder
+    from ssar_b200.random import latent
+
+    g = load("traj")
+    R = projection_matrix().cuda()
+    feats, segs, palette = cuda_inputs()
+    assert rel_l2(latent.spline_loop_latents(palette[:8], T, 1) @ R, g["spline_proj"]) < TOL
+    assert rel_l2(latent.spline_loop_latents(palette[8:13], T, 2.37) @ R, g["spline_loops_proj"]) < TOL
+    rng = torch.Generator("cpu").manual_seed(5)
+    lat = latent.spline_loop_latents(palette[:6], T)
+    ptr0 = lat.data_ptr()
+    for kind, merge, depth, sf in (("segmentation", "average", "low", "mfcc"), ("feature", "modulate", "midhigh", "chromagram"),
+                                   ("feature", "modulate", "all", "onsets"), ("loop", "overwrite", "high", "tonnetz")):
+        lat = latent.latent_patch(rng, lat, palette, segs, feats, 120.0, 24, kind, 6, 8, sf, 0.8, "rms", 0.9, merge, depth)
+    assert lat.data_ptr() == ptr0  # in place, like the reference
+    assert rel_l2(lat @ R, g["latent_patch_proj"]) < TOL
+    x = (synth_features(2 * 300, 17, 77).abs().reshape(2, 300, 17) + 0.1).cuda()
+    torch.manual_seed(0)
+    draws = [torch.randn(2, 300, s, s).cuda() for s in (4, 8, 16, 32)]
+    dec = FixedLatentNoiseDecoder(palette[:9], hidden_size=3, n_latent_split=3, n_noise=4)
+    dl, dn = dec.forward(x, noise_draws=draws)
+    assert tuple(dl.shape) == (2, 300, 18, 512)
+    assert rel_l2(dl @ R, g["dec_proj"]) < TOL
+    for i, n in enumerate(dn):
+        assert tuple(n.shape) == (2, 300, 4 * 2 ** i, 4 * 2 ** i)
+        assert rel_l2(n[:, ::10], g[f"dec_noise_{i}"]) < TOL, i
+
+
+def test_patch_full_size_vs_oracle_frames():
+    """cfg 4 size (T = 5760): the single mixing GEMM equals the step-by-step oracle on a strided set of frames, and the
+    general noise-tree fallback (composite right child) equals direct evaluation."""
+    from ssar_b200.random import noise as N
+    from ssar_b200.random.patch import Patch
+    from ssar_oracle import traj
+
+    Tf = 5760
+    feats, segs, palette = synth_patch_inputs(Tf, 1)
+    lat_o, noise_o = traj.Patch(feats, segs, 120.0, seed=11).forward(palette, downscale_factor=4)
+    patch = Patch({k: v.cuda() for k, v in feats.items()}, segs, 120.0, seed=11, device="cpu")
+    lat, noise = patch.forward(palette.cuda(), downscale_factor=4)
+    assert tuple(lat.shape) == (Tf, 18, 512)
+    assert rel_l2(lat[::97], lat_o[::97]) < TOL
+    for j in (2, 9, 14):
+        assert rel_l2(noise[j].forward(4000, 32), noise_o[j](4000, 32)) < TOL, j
+    # composite right child -> BUFFER fallback
+    rng = torch.Generator("cpu").manual_seed(1)
+    a = N.Loop(rng, Tf, (16, 16), 2, 3.0, device="cuda")
+    b = N.ScaleBias(N.Multiply(rng, Tf, (16, 16), feats["mfcc"].cuda()), 0.5, 0.1)
+    tree = N.Average(a, b)
+    direct = (a.forward(5, 9) + b.forward(5, 9)) / 2
+    assert rel_l2(tree.forward(5, 9), direct) < 1e-6
