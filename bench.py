@@ -1,17 +1,21 @@
 #!/usr/bin/env python
 """bench.py — audio-seconds/second of the hot path on N B200s of one node (contract in the task statement).
 
-Default workload = BASELINE.json configs[1] ("cfg2"): STFT power spectrogram + mel + onset strength + RMS for
-64 synthetic 4-minute 44.1 kHz clips per GPU, n_fft 2048, hop 512.  A "step" is one pass over that batch.
+Workloads (a "step" is one pass over one batch of synthetic clips per GPU):
+  full (default) : BASELINE.json's metric "full features + latents": audio2features [T, 59] (resample, HPSS x2, CQT
+                   chroma, tonnetz, mfcc, contrast, flatness, 4 onset envelopes, PLP, 8 RMS / drop-strength columns,
+                   percentile clamps, Gaussian smoothing) + the Patch latent trajectory [T, 18, 512] for every clip;
+                   --clips 4-minute 44.1 kHz clips per GPU (configs[2] + configs[3] at the batch size of configs[1]).
+  cfg2           : configs[1]: STFT power spectrogram + mel + onset strength + RMS, 64 clips, n_fft 2048, hop 512.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg2]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload full|cfg2] [--clips B]
 
-value      : whole-job audio-s/s with the waveforms already resident in HBM (CUDA events, max over ranks)
-e2e        : same metric through the public API from pinned HOST buffers, H2D + D2H copies inside the timed region
-roofline   : the dominant kernel (frames_fft) timed live with CUDA events, algorithmic bytes / time vs measured HBM peak
+value       : whole-job audio-s/s with the waveforms already resident in HBM (CUDA events, max over ranks)
+e2e         : same metric through the public API from pinned HOST buffers, H2D + D2H copies inside the timed region
+roofline    : the dominant kernel of the step, timed live with CUDA events around each of its launches
 cpu_baseline: the CPU oracle port timed on this box's host cores on a bounded sample (rank 0, N=1 only)
---impl reference : times the CPU implementation of the same path (oracle port; the reference is Python and
-                   cannot travel to the GPU box) on the host cores, rank 0 only.
+--impl reference : times the CPU implementation of the same workload (oracle port: the reference is Python + torch and
+                   cannot travel to the GPU box; the port is pinned to it at 2e-7) on all host threads.
 """
 from __future__ import annotations
 
@@ -31,8 +35,16 @@ for p in (ROOT / "self-supervised-audio-reactive_b200", ROOT / "oracle"):
 
 import torch  # noqa: E402
 
-SR, DUR_S, CLIPS, N_FFT, HOP = 44100, 240, 64, 2048, 512
-WORKLOAD = f"cfg2: STFT+mel+onset+RMS, {CLIPS} clips x {DUR_S} s @44.1kHz per GPU, n_fft {N_FFT} hop {HOP}"
+SR, DUR_S, N_FFT, HOP2 = 44100, 240, 2048, 512
+FPS = 24
+DEFAULT_CLIPS = {"full": 32, "cfg2": 64}
+
+
+def workload_name(kind, clips):
+    if kind == "cfg2":
+        return f"cfg2: STFT+mel+onset+RMS, {clips} clips x {DUR_S} s @44.1kHz per GPU, n_fft {N_FFT} hop {HOP2}"
+    return (f"full: audio2features [5760,59] + Patch latents [5760,18,512], {clips} clips x {DUR_S} s @44.1kHz per GPU "
+            f"(resampled to {FPS * 1024} Hz, n_fft {N_FFT} hop 1024, {FPS} fps)")
 
 
 def measured_peaks():
@@ -93,67 +105,84 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def cpu_cfg2_pass(x, sr):
-    """One pass of the cfg2 path on CPU with the oracle port: spectrogram + mel + onset + rms."""
+# ------------------------------------------------------------------------------------------------
+# CPU arm (oracle port) — used by cpu_baseline and by --impl reference
+# ------------------------------------------------------------------------------------------------
+def cpu_pass(kind, x, sr):
     from ssar_oracle import dsp
 
-    S = dsp.spectrogram(x, N_FFT, HOP, power=2)
-    mel = dsp.mel_basis(sr, N_FFT) @ S
-    onset = dsp.onset_strength(x, sr, HOP, N_FFT)
-    rms = dsp.rms(x, sr, N_FFT, HOP)
-    return S, mel, onset, rms
+    if kind == "cfg2":
+        S = dsp.spectrogram(x, N_FFT, HOP2, power=2)
+        return S, dsp.mel_basis(sr, N_FFT) @ S, dsp.onset_strength(x, sr, HOP2, N_FFT), dsp.rms(x, sr, N_FFT, HOP2)
+    from ssar_b200.pipeline import PATCH_FEATURE_COLUMNS
+    from ssar_b200.synth import synth_patch_inputs
+    from ssar_oracle import features, post, traj
+
+    f = features.audio2features(x, sr, FPS)
+    _, segs, palette = synth_patch_inputs(f.shape[0], 0)
+    pf = {n: post.normalize(f[:, a:b]) for n, (a, b) in PATCH_FEATURE_COLUMNS.items()}
+    lat, _ = traj.Patch(pf, segs, 120.0, fps=FPS, seed=42).forward(palette, downscale_factor=4)
+    return f, lat
 
 
-def time_cpu_sample(sample_s: int, repeats: int = 1):
+def cpu_sample_seconds(kind):
+    return 60 if kind == "cfg2" else 45  # full: 45 s is the shortest clip whose PLP uses the full 1024-frame window
+
+
+def time_cpu(kind, steps, warmup):
     from ssar_b200.synth import synth_clip
 
-    x = synth_clip(SR * sample_s, SR, 0)
-    cpu_cfg2_pass(x[: SR * 2], SR)  # warm-up (thread pools, fft plans)
+    s = cpu_sample_seconds(kind)
+    x = synth_clip(SR * s, SR, 0)
+    for _ in range(warmup):
+        cpu_pass(kind, x, SR)
     t0 = time.perf_counter()
-    for _ in range(repeats):
-        cpu_cfg2_pass(x, SR)
-    dt = (time.perf_counter() - t0) / repeats
-    return sample_s / dt, dt
+    for _ in range(steps):
+        cpu_pass(kind, x, SR)
+    dt = (time.perf_counter() - t0) / steps
+    return s / dt, dt, s
 
 
 def run_reference(args, rank):
     if rank != 0:
         return
-    sample_s = 60
-    # warm-up + K timed steps, each step = one 60 s clip of the cfg2 workload on all host threads
-    from ssar_b200.synth import synth_clip
-
-    x = synth_clip(SR * sample_s, SR, 0)
-    for _ in range(max(1, min(args.warmup, 2))):
-        cpu_cfg2_pass(x, SR)
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        cpu_cfg2_pass(x, SR)
-    dt = (time.perf_counter() - t0) / args.steps
-    v = sample_s / dt
+    v, dt, s = time_cpu(args.workload, args.steps, max(1, min(args.warmup, 2)))
     cores = torch.get_num_threads()
-    sample = f"1 clip x {sample_s} s of the cfg2 workload per step (oracle port, torch-CPU fp32, {cores} threads)"
+    sample = (f"1 clip x {s} s of the workload per step (oracle port of the reference's torch-CPU code, fp32, "
+              f"{cores} threads)")
     print(json.dumps({
         "impl": "reference", "metric": "audio-sec/sec", "value": v, "unit": "audio-s/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "sample": sample},
+        "config": {"workload": workload_name(args.workload, args.clips), "sample": sample},
         "cpu_baseline": {"value": v, "unit": "audio-s/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
 
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+class EventLog(dict):
+    """cabi.event_log that records every entry point."""
+
+    def get(self, k, d=None):
+        return self.setdefault(k, [])
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cfg2")
-    ap.add_argument("--clips", type=int, default=CLIPS)
+    ap.add_argument("--workload", default="full", choices=["full", "cfg2"])
+    ap.add_argument("--clips", type=int, default=None)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
+    if args.clips is None:
+        args.clips = DEFAULT_CLIPS[args.workload]
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
@@ -165,8 +194,8 @@ def main():
     import torch.distributed as dist
 
     from ssar_b200 import _cabi as cabi
-    from ssar_b200.pipeline import spectral_frontend
-    from ssar_b200.synth import synth_batch_device
+    from ssar_b200 import ops, pipeline
+    from ssar_b200.synth import synth_batch_device, synth_patch_inputs
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
@@ -179,46 +208,77 @@ def main():
         torch.cuda.synchronize()
 
     B, n = args.clips, SR * DUR_S
-    T = n // HOP
+    kind = args.workload
     x = synth_batch_device(B, n, SR, dev, first_index=rank * B)
     audio_s_per_step = B * DUR_S  # per rank
+    stats = torch.zeros(3, 59, dtype=torch.float64, device=dev)
 
-    # kernel-level event log for the roofline (events recorded on the launching stream around the one launch)
-    cabi.event_log = {"ssar_frames_fft": []}
+    if kind == "cfg2":
+        T = n // HOP2
+
+        def step(xd):
+            return pipeline.spectral_frontend(xd, SR, N_FFT, HOP2)
+
+        def results(o):
+            return [o["mel"], o["onset"], o["rms"]]
+        d2h_note = "mel+onset+rms out to pinned host; the power spectrogram stays in HBM for downstream kernels"
+    else:
+        T = 5760
+        _, segs, palette = synth_patch_inputs(T, 0)
+        palette = palette.to(dev)
+
+        def step(xd):
+            feats, latents, _ = pipeline.features_and_latents(xd, SR, FPS, palette, segs)
+            # the one cross-clip reduction of the path: per-feature (count, sum, sum^2) for the dataset mean / std
+            stats.zero_()
+            ops.feature_stats(feats, stats)
+            if world > 1:
+                dist.all_reduce(stats)  # NCCL: 59 x 3 fp64
+            return {"feats": feats, "latents": latents}
+
+        def results(o):
+            # latents feed the generator on the device (maua StyleGAN2 wrapper); the host gets the features and a
+            # per-clip fingerprint of the latents
+            return [o["feats"], o["latents"].sum(dim=(1, 2, 3))]
+        d2h_note = "features [B,5760,59] + a per-clip latent checksum out to pinned host; latents stay in HBM for the generator"
+
     for _ in range(args.warmup):
-        out = spectral_frontend(x, SR, N_FFT, HOP)
+        out = step(x)
     barrier()
-    cabi.event_log["ssar_frames_fft"].clear()
+    cabi.event_log = EventLog()
     launches0 = cabi.launch_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local_rank) as clocks:
         barrier()
         ev0.record()
         for _ in range(args.steps):
-            out = spectral_frontend(x, SR, N_FFT, HOP)
+            out = step(x)
         ev1.record()
         barrier()
     ms = ev0.elapsed_time(ev1)
     launches = cabi.launch_count - launches0
-    k_ms = [a.elapsed_time(b) for a, b in cabi.event_log["ssar_frames_fft"]]
+    per_kernel = {}
+    for name, evs in cabi.event_log.items():
+        t_ms = sum(a.elapsed_time(b) for a, b, _ in evs)
+        nb = sum(c for _, _, c in evs if c is not None)
+        per_kernel[name] = (t_ms, nb, len(evs))
     cabi.event_log = None
-    kernel_ms = sum(k_ms) / max(len(k_ms), 1)
     t = torch.tensor([ms], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_max = float(t.item())
     value = audio_s_per_step * world * args.steps / (ms_max * 1e-3)
 
-    # ---- e2e: pinned host waveforms -> H2D -> kernels -> D2H of the feature tensors, chunked over two streams
+    # ---- e2e: pinned host waveforms -> H2D -> public API -> D2H of the results, chunked over two streams
     e2e = None
     if not args.no_e2e:
-        chunk = 8
+        del out
+        chunk = min(8, B)
         host_x = torch.empty(B, n, dtype=torch.float32, pin_memory=True)
         host_x.copy_(x)
-        del out
-        host_mel = torch.empty(B, T, 128, dtype=torch.float32, pin_memory=True)
-        host_onset = torch.empty(B, T, dtype=torch.float32, pin_memory=True)
-        host_rms = torch.empty(B, T, dtype=torch.float32, pin_memory=True)
+        probe = results(step(x[:chunk]))
+        host_out = [torch.empty((B,) + tuple(p.shape[1:]), dtype=p.dtype, pin_memory=True) for p in probe]
+        del probe
         streams = [torch.cuda.Stream(dev), torch.cuda.Stream(dev)]
 
         def e2e_step():
@@ -226,18 +286,15 @@ def main():
                 s = streams[ci % 2]
                 with torch.cuda.stream(s):
                     xd = host_x[c0 : c0 + chunk].to(dev, non_blocking=True)
-                    o = spectral_frontend(xd, SR, N_FFT, HOP)
-                    host_mel[c0 : c0 + chunk].copy_(o["mel"], non_blocking=True)
-                    host_onset[c0 : c0 + chunk].copy_(o["onset"], non_blocking=True)
-                    host_rms[c0 : c0 + chunk].copy_(o["rms"], non_blocking=True)
+                    for h, r in zip(host_out, results(step(xd))):
+                        h[c0 : c0 + chunk].copy_(r, non_blocking=True)
             for s in streams:
                 s.synchronize()
 
-        for _ in range(2):
-            e2e_step()
+        e2e_step()
         barrier()
         t0 = time.perf_counter()
-        e_steps = max(2, min(args.steps, 5))
+        e_steps = max(2, min(args.steps, 3))
         for _ in range(e_steps):
             e2e_step()
         barrier()
@@ -247,35 +304,37 @@ def main():
             dist.all_reduce(td, op=dist.ReduceOp.MAX)
         e2e = {
             "value": audio_s_per_step * world * e_steps / float(td.item()), "unit": "audio-s/s",
-            "h2d_bytes_per_step": B * n * 4, "d2h_bytes_per_step": B * T * (128 + 2) * 4,
-            "steps": e_steps, "note": "per rank: pinned host waveforms in, mel+onset+rms out to pinned host; "
-                                      "the power spectrogram stays in HBM for the downstream kernels",
+            "h2d_bytes_per_step": B * n * 4, "d2h_bytes_per_step": sum(h.numel() * h.element_size() for h in host_out),
+            "steps": e_steps, "note": "per rank: pinned host waveforms in, " + d2h_note,
         }
 
     if rank == 0:
         peak, peak_src = measured_peaks()
-        # algorithmic bytes of one frames_fft launch: waveform in + power spec + mel + rms out,
-        # plus the internal onset-mel [B,T,128] this design materialises is NOT counted (it is not compulsory)
-        alg_bytes = B * n * 4 + B * T * (1025 + 128 + 1) * 4
+        top = sorted(per_kernel.items(), key=lambda kv: -kv[1][0])
+        name, (k_ms, k_bytes, k_n) = top[0]
+        kernel_total = sum(v[0] for v in per_kernel.values())
         roof = {
-            "bound": "hbm", "kernel": "frames_fft_kernel<1024>", "achieved": alg_bytes / (kernel_ms * 1e-3) / 1e9,
+            "bound": "hbm", "kernel": name, "achieved": (k_bytes / (k_ms * 1e-3) / 1e9) if k_bytes else None,
             "peak": peak, "peak_source": peak_src, "unit": "GB/s", "traffic": None,
-            "kernel_ms": kernel_ms, "algorithmic_bytes": alg_bytes,
-            "share_of_step": kernel_ms * len(k_ms) / ms if ms > 0 else None,
+            "kernel_ms_per_step": k_ms / args.steps, "launches_per_step": k_n / args.steps,
+            "algorithmic_bytes_per_step": k_bytes / args.steps, "share_of_step": k_ms / ms if ms > 0 else None,
+            "all_kernels_share_of_step": kernel_total / ms if ms > 0 else None,
+            "top5_ms_per_step": {k: round(v[0] / args.steps, 3) for k, v in top[:5]},
         }
-        roof["frac"] = roof["achieved"] / peak
+        roof["frac"] = roof["achieved"] / peak if roof["achieved"] else None
         cpu = None
         if world == 1 and not args.no_cpu:
-            sample_s = 60
-            v, dt = time_cpu_sample(sample_s)
+            v, dt, s = time_cpu(kind, 1 if kind == "full" else 3, 1)
             cpu = {"value": v, "unit": "audio-s/s", "cores": torch.get_num_threads(), "kind": "port",
-                   "sample": f"1 clip x {sample_s} s of the cfg2 workload, oracle port (torch-CPU fp32), {dt:.2f} s"}
+                   "sample": f"1 clip x {s} s of the same workload, oracle port (torch-CPU fp32), {dt:.2f} s per pass"}
         print(json.dumps({
             "metric": "audio-sec/sec", "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "clips_per_gpu": B, "frames_per_clip": T, "l2": "inputs_exceed_l2 (2.7 GB/step)",
-                       "parallelism": f"clip-sharded x{world}, no data-path collective"},
+            "config": {"workload": workload_name(kind, B), "clips_per_gpu": B, "frames_per_clip": T,
+                       "l2": f"inputs_exceed_l2 ({B * n * 4 / 1e9:.2f} GB of waveforms per step)",
+                       "parallelism": f"clip-sharded x{world}; one NCCL all-reduce of 59x3 fp64 feature stats per step"
+                       if kind == "full" else f"clip-sharded x{world}, no data-path collective"},
             "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
         }))
     if world > 1:

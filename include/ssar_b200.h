@@ -173,15 +173,18 @@ int ssar_resample(const float* x, long long n_in, long long stride_in, int n_cli
  * ---------------------------------------------------------------------------------------------- */
 
 /* rosa/pitch.py:27-83 piptrack on a magnitude spectrogram [n_clips, n_frames, ld] (n_bins valid bins): per frame,
- * local maxima above threshold * column max inside bins [k_lo, k_hi), parabolic interpolation.  pitch / mag:
- * dense [n_clips, n_frames, k_hi - k_lo] slots, zero where there is no peak. */
+ * local maxima above threshold * column max inside bins [k_lo, k_hi), parabolic interpolation.  The (pitch, mag)
+ * pairs with pitch > 0 are appended to per-clip lists pitch / mag [n_clips, capacity] (unordered), count [n_clips]
+ * receives their number.  capacity >= ssar_piptrack_capacity(n_frames, k_lo, k_hi). */
+long long ssar_piptrack_capacity(int n_frames, int k_lo, int k_hi);
 int ssar_piptrack(const float* mag_spec, long long ld, int n_clips, int n_frames, int n_bins, int k_lo, int k_hi,
-                  float threshold, float sr, int n_fft, float* pitch, float* mag, void* stream);
+                  float threshold, float sr, int n_fft, long long capacity, float* pitch, float* mag, int* count,
+                  void* stream);
 
-/* rosa/pitch.py:9-24 + :98-120 estimate_tuning tail: threshold = lower median of mag[pitch > 0]; histogram (n_hist bins
- * with the n_hist + 1 `edges` of torch.linspace(-0.5, 0.5, n_hist + 1)) of the bins_per_octave residuals of the
- * pitches with mag >= threshold; tuning_idx[clip] = arg-max bin, tuning_val[clip] = edges[arg-max]. */
-int ssar_tuning_from_peaks(const float* pitch, const float* mag, int n_clips, long long n_per_clip,
+/* rosa/pitch.py:9-24 + :98-120 estimate_tuning tail: threshold = lower median of the tracked magnitudes; histogram
+ * (n_hist bins with the n_hist + 1 `edges` of torch.linspace(-0.5, 0.5, n_hist + 1)) of the bins_per_octave residuals
+ * of the pitches with mag >= threshold; tuning_idx[clip] = arg-max bin, tuning_val[clip] = edges[arg-max]. */
+int ssar_tuning_from_peaks(const float* pitch, const float* mag, int n_clips, long long capacity, const int* count,
                            const float* edges, int n_hist, float bins_per_octave, int* tuning_idx,
                            float* tuning_val, void* stream);
 

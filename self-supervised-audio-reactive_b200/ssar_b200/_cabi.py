@@ -69,6 +69,7 @@ def lib():
         _lib = C.CDLL(str(LIB_PATH))
         _lib.ssar_last_error.restype = C.c_char_p
         _lib.ssar_biquad_scratch_bytes.restype = C.c_longlong
+        _lib.ssar_piptrack_capacity.restype = C.c_longlong
         if _lib.ssar_abi_version() != 1:
             raise SsarError("libssar_b200.so ABI version mismatch; rebuild")
     return _lib
@@ -87,22 +88,27 @@ def stream_ptr():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
-def call(name: str, *args):
-    """Invoke a C-ABI entry point on the current CUDA stream and raise on a non-zero status."""
+def call(name: str, *args, nbytes=None):
+    """Invoke a C-ABI entry point on the current CUDA stream and raise on a non-zero status.
+    nbytes: algorithmic bytes of this launch (compulsory inputs + outputs), recorded for the roofline when timing."""
     global launch_count
     fn = getattr(lib(), name)
-    log = event_log.get(name) if event_log else None
+    log = event_log.get(name) if event_log is not None else None
     if log is not None:  # bench.py: CUDA events on the launching stream around exactly this launch
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         rc = fn(*args, stream_ptr())
         e1.record()
-        log.append((e0, e1))
+        log.append((e0, e1, nbytes))
     else:
         rc = fn(*args, stream_ptr())
     launch_count += 1
     if rc != 0:
         raise SsarError(f"{name} failed ({rc}): {lib().ssar_last_error().decode()}")
+
+
+def nbytes_of(*tensors):
+    return sum(t.numel() * t.element_size() for t in tensors if t is not None)
 
 
 def i32(v):

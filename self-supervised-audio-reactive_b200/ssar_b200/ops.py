@@ -127,7 +127,11 @@ def frames_fft(
             pj.row_scale = proj["row_scale"].data_ptr()
             pj.row_scale_ld = int(proj["row_scale_ld"])
         keep.append(proj)
-    cabi.call("ssar_frames_fft", C.byref(a))
+    outs = [v for v in out.values()] + ([proj["out"]] if proj is not None else [])
+    nb = cabi.nbytes_of(x) + sum(o.numel() * o.element_size() for o in outs if proj is None or o is not proj["out"])
+    if proj is not None:
+        nb += B * n_frames * int(proj["n_rows"]) * 8
+    cabi.call("ssar_frames_fft", C.byref(a), nbytes=nb)
     return out
 
 
@@ -178,7 +182,8 @@ def hpss(stft_fm: torch.Tensor, margin: float = 1.0, want_harm: bool = True, wan
     B, T1, F, _ = stft_fm.shape
     h = torch.empty_like(stft_fm) if want_harm else None
     p = torch.empty_like(stft_fm) if want_perc else None
-    cabi.call("ssar_hpss", ptr(stft_fm), i32(B), i32(T1), i32(F), i64(F), f32(margin), f32(margin), ptr(h), ptr(p))
+    cabi.call("ssar_hpss", ptr(stft_fm), i32(B), i32(T1), i32(F), i64(F), f32(margin), f32(margin), ptr(h), ptr(p),
+              nbytes=cabi.nbytes_of(stft_fm, h, p))
     return h, p
 
 
@@ -191,9 +196,10 @@ def istft(spec_fm: torch.Tensor, n_fft: int, hop: int, window=torch.hann_window,
     win = plan.window_tensor(window, n_fft, dev)
     frames = torch.empty(B, T1, n_fft, dtype=torch.float32, device=dev)
     cabi.call("ssar_irfft_frames", ptr(spec_fm), i64(F), i32(B), i32(T1), i32(n_fft), ptr(win),
-              ptr(plan.twiddle(n_fft, str(dev))), ptr(frames))
+              ptr(plan.twiddle(n_fft, str(dev))), ptr(frames), nbytes=cabi.nbytes_of(spec_fm, frames))
     out = torch.empty(B, length, dtype=torch.float32, device=dev)
-    cabi.call("ssar_overlap_add", ptr(frames), ptr(win), i32(B), i32(T1), i32(n_fft), i32(hop), i64(length), ptr(out))
+    cabi.call("ssar_overlap_add", ptr(frames), ptr(win), i32(B), i32(T1), i32(n_fft), i32(hop), i64(length), ptr(out),
+              nbytes=cabi.nbytes_of(frames, out))
     return out
 
 
@@ -206,7 +212,7 @@ def biquad(x: torch.Tensor, coeffs, clamp: bool = True):
     scratch = torch.empty(max(int(nbytes), 8), dtype=torch.uint8, device=x.device)
     b0, b1, b2, a1, a2 = coeffs
     cabi.call("ssar_biquad", ptr(x), i64(N), i64(x.stride(0)), i32(B), f32(b0), f32(b1), f32(b2), f32(a1), f32(a2),
-              i32(1 if clamp else 0), ptr(y), i64(N), ptr(scratch))
+              i32(1 if clamp else 0), ptr(y), i64(N), ptr(scratch), nbytes=cabi.nbytes_of(x, y))
     return y
 
 
@@ -217,7 +223,7 @@ def resample(x: torch.Tensor, rp, post_scale: float = 1.0):
     n_out = -((-rp.new * N) // rp.orig)
     y = torch.empty(B, n_out, dtype=torch.float32, device=x.device)
     cabi.call("ssar_resample", ptr(x), i64(N), i64(x.stride(0)), i32(B), ptr(rp.taps), ptr(rp.first), i32(rp.orig),
-              i32(rp.new), i32(rp.width), i32(rp.max_taps), f32(post_scale), ptr(y), i64(n_out), i64(n_out))
+              i32(rp.new), i32(rp.width), i32(rp.max_taps), f32(post_scale), ptr(y), i64(n_out), i64(n_out), nbytes=cabi.nbytes_of(x, y))
     return y
 
 
@@ -352,16 +358,17 @@ def estimate_tuning(y: torch.Tensor, sr, n_fft: int = 2048, bins_per_octave: int
     T = N // hop
     S = frames_fft(y, n_fft, hop, T, torch.hann_window, spec_power=1)["spec"]
     k_lo, k_hi = plan.piptrack_bin_range(float(sr), n_fft, fmin, fmax)
-    R = k_hi - k_lo
-    pitch = torch.empty(B, T, R, dtype=torch.float32, device=y.device)
+    cap = int(cabi.lib().ssar_piptrack_capacity(C.c_int(T), C.c_int(k_lo), C.c_int(k_hi)))
+    pitch = torch.empty(B, cap, dtype=torch.float32, device=y.device)
     mag = torch.empty_like(pitch)
+    count = torch.empty(B, dtype=torch.int32, device=y.device)
     cabi.call("ssar_piptrack", ptr(S), i64(S.shape[2]), i32(B), i32(T), i32(S.shape[2]), i32(k_lo), i32(k_hi),
-              f32(threshold), f32(float(sr)), i32(n_fft), ptr(pitch), ptr(mag))
+              f32(threshold), f32(float(sr)), i32(n_fft), i64(cap), ptr(pitch), ptr(mag), ptr(count))
     idx = torch.empty(B, dtype=torch.int32, device=y.device)
     val = torch.empty(B, dtype=torch.float32, device=y.device)
     edges = plan.tuning_edges(str(y.device))
-    cabi.call("ssar_tuning_from_peaks", ptr(pitch), ptr(mag), i32(B), i64(T * R), ptr(edges), i32(edges.numel() - 1),
-              f32(float(bins_per_octave)), ptr(idx), ptr(val))
+    cabi.call("ssar_tuning_from_peaks", ptr(pitch), ptr(mag), i32(B), i64(cap), ptr(count), ptr(edges),
+              i32(edges.numel() - 1), f32(float(bins_per_octave)), ptr(idx), ptr(val))
     return idx, val
 
 
@@ -487,7 +494,8 @@ def mix_gemm(weights: torch.Tensor, basis: torch.Tensor, out: torch.Tensor | Non
     if col_end is None:
         col_end = N
     cabi.call("ssar_mix_gemm", ptr(weights), i64(G * K), i64(K), i32(group_cols), ptr(basis), i64(N), ptr(out), i64(N),
-              i32(T), i32(K), i32(col_begin), i32(col_end), ptr(row_alpha), ptr(row_beta))
+              i32(T), i32(K), i32(col_begin), i32(col_end), ptr(row_alpha), ptr(row_beta),
+              nbytes=cabi.nbytes_of(weights, basis) + T * (col_end - col_begin) * 4 * (2 if row_alpha is not None else 1))
     return out
 
 

@@ -125,3 +125,33 @@ def audio2features_batch(audio: torch.Tensor, sr, fps, clamp=True, smooth=True, 
     if emphasis:
         feats = ops.emphasize(feats, 2, 75)
     return feats
+
+
+# column ranges of the [T, 59] feature matrix (supervised/data.py:32-51) used as `Patch` inputs (SURVEY.md 8d cfg 4)
+PATCH_FEATURE_COLUMNS = {"mfcc": (0, 20), "chromagram": (20, 32), "tonnetz": (32, 38), "spectral_contrast": (38, 45),
+                         "spectral_flatness": (45, 46), "onsets": (46, 47), "rms": (51, 52), "drop_strength": (55, 56)}
+
+
+def patch_features_from_matrix(feats: torch.Tensor):
+    """[T, 59] feature matrix of one clip -> dict of normalised [T, C] features in the shape `Patch` expects
+    (random/mir.py:44 ends in `normalize`: every entry lies in [0, 1])."""
+    return {name: ops.normalize(feats[:, a:b].contiguous(), 1) for name, (a, b) in PATCH_FEATURE_COLUMNS.items()}
+
+
+def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, segmentations, tempo=120.0, seed=42,
+                         rng_device="cpu"):
+    """The north-star unit for a batch of clips: waveforms [B, N] -> (features [B, T, 59], latents [B, T, 18, 512]).
+    Tempo and segmentations are inputs (random/mir.py:28-42 is CPU librosa / scipy work outside the path).
+    rng_device: where the Patch generator lives ("cpu" reproduces a CPU-seeded reference run bit for bit in its draws;
+    the reference's own default is the compute device, random/__init__.py:1-3)."""
+    from .random.patch import Patch
+
+    feats = audio2features_batch(audio, sr, fps)
+    B, T, _ = feats.shape
+    latents = torch.empty(B, T, palette.shape[1], palette.shape[2], dtype=torch.float32, device=feats.device)
+    noises = []
+    for b in range(B):
+        patch = Patch(patch_features_from_matrix(feats[b]), segmentations, tempo, fps=fps, seed=seed + b, device=rng_device)
+        _, noise = patch.forward(palette, downscale_factor=4, latents_out=latents[b])
+        noises.append(noise)
+    return feats, latents, noises

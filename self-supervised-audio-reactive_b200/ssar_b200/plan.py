@@ -479,6 +479,16 @@ def tonnetz_phi(n_chroma: int, device) -> torch.Tensor:
     return (R[:, None] * torch.cos(torch.pi * V)).contiguous().to(_dev(device))
 
 
+@functools.lru_cache(maxsize=64)
+def _cardinal_spline_coeffs(n_points: int):
+    """(a, b, two_c, three_d) [n_points, n_points - 1] of the natural cubic splines through the unit vectors on
+    linspace(0, 1, n_points) (fp64)."""
+    t_in = torch.linspace(0, 1, n_points).numpy()
+    eye = np.eye(n_points)
+    per_knot = [natural_cubic_spline_np(t_in, eye[k]) for k in range(n_points)]
+    return tuple(np.stack([c[j] for c in per_knot]) for j in range(4))
+
+
 def spline_loop_weights_cpu(n_knots: int, size: int, n_loops=1) -> torch.Tensor:
     """Cardinal weights of ssar/random/latent.py:7-13: out[t] = sum_k W[t, k] y[k] for the natural cubic spline through
     (y_0 .. y_{K-1}, y_0) on linspace(0, 1, K + 1), evaluated at linspace(0, n_loops, size) % 1 (upstream
@@ -488,19 +498,15 @@ def spline_loop_weights_cpu(n_knots: int, size: int, n_loops=1) -> torch.Tensor:
     t_in = torch.linspace(0, 1, K1)
     t_out = torch.linspace(0, n_loops, size) % 1
     idx = (torch.bucketize(t_out, t_in) - 1).clamp(0, K1 - 2)
-    frac = (t_out - t_in[idx]).double().numpy()
+    frac = (t_out - t_in[idx]).double().numpy()[:, None]
     idx = idx.numpy()
     if K1 == 2:
         t64 = t_in.double().numpy()
-        W = np.zeros((size, 2))
         slope = 1.0 / (t64[1] - t64[0])
-        W[:, 0] = 1.0 - slope * frac
-        W[:, 1] = slope * frac
+        W = np.concatenate([1.0 - slope * frac, slope * frac], axis=1)
     else:
-        eye = np.eye(K1)
-        coeffs = [natural_cubic_spline_np(t_in.numpy(), eye[k]) for k in range(K1)]
-        W = np.zeros((size, K1))
-        for k, (a, b, c2, d3) in enumerate(coeffs):
-            W[:, k] = a[idx] + (b[idx] + (0.5 * c2[idx] + d3[idx] * frac / 3.0) * frac) * frac
+        a, b, c2, d3 = _cardinal_spline_coeffs(K1)  # each [K1, K1 - 1]
+        W = a.T[idx] + (b.T[idx] + (0.5 * c2.T[idx] + d3.T[idx] * frac / 3.0) * frac) * frac
+    W = W.copy()
     W[:, 0] += W[:, -1]
     return torch.from_numpy(W[:, :-1].astype(np.float32))

@@ -96,5 +96,5 @@ class LatentWeights:
         lo, hi = LAYER_SLICES[merge_depth]
         ops.weights_merge(self.w, self._dense(selection, S), lo // self.gl, hi // self.gl, alpha, beta)
 
-    def render(self, palette):
-        return ops.mix_gemm(self.w, palette.to(self.device))
+    def render(self, palette, out=None):
+        return ops.mix_gemm(self.w, palette.to(self.device), out=out)

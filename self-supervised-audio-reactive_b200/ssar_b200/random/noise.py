@@ -29,9 +29,15 @@ class Noise:
         self.length = length
         self.size = size
 
-    def to(self, device):
+    def _own_to(self, device):
         for name in self._buffers:
-            setattr(self, name, getattr(self, name).to(device).float().contiguous())
+            t = getattr(self, name)
+            if t.device != torch.device(device) or t.dtype != torch.float32 or not t.is_contiguous():
+                setattr(self, name, t.to(device).float().contiguous())
+        return self
+
+    def to(self, device):
+        self._own_to(device)
         for child in ("left", "right", "base"):
             if hasattr(self, child):
                 getattr(self, child).to(device)
@@ -81,7 +87,7 @@ class Blend(Noise):
         super().__init__(length, size)
         self.noise = torch.randn((2, modulator.shape[1], size[0], size[1]), generator=rng, device=rng.device)
         self.modulator = modulator
-        self.to(modulator.device)
+        self._own_to(modulator.device)
 
     def _leaf(self, to_acc, i, b, keep):
         return _op(BLEND, self.noise, self.modulator, M=self.modulator.shape[1], to_acc=to_acc)
@@ -96,7 +102,7 @@ class Multiply(Noise):
         super().__init__(length, size)
         self.noise = torch.randn((modulator.shape[1], size[0], size[1]), generator=rng, device=rng.device)
         self.modulator = modulator
-        self.to(modulator.device)
+        self._own_to(modulator.device)
 
     def _leaf(self, to_acc, i, b, keep):
         return _op(MULTIPLY, self.noise, self.modulator, M=self.modulator.shape[1], to_acc=to_acc)
@@ -113,7 +119,7 @@ class Loop(Noise):
         self.noise = torch.randn((3, size[0], size[1]), generator=rng, device=rng.device)
         self.idx = torch.linspace(0, n_loops * 2 * torch.pi, length)
         if device is not None:
-            self.to(device)
+            self._own_to(device)
 
     def _leaf(self, to_acc, i, b, keep):
         return _op(LOOP, self.noise, self.idx, p0=self.sigma / 50, to_acc=to_acc)
@@ -141,7 +147,7 @@ class Modulate(Noise):
         super().__init__(left.length, left.size)
         self.left, self.right = left, right
         self.modulator = modulator.float().mean(1)
-        self.to(left.device)
+        self._own_to(left.device)
 
     def _emit(self, prog, i, b, keep):
         self.left._emit(prog, i, b, keep)

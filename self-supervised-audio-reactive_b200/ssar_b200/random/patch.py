@@ -104,8 +104,9 @@ class Patch:
             noise_std=skewnorm(self.rng, a=5, loc=0.666, scale=0.5).item(),
         )
 
-    def forward(self, latent_palette, downscale_factor=1, aspect_ratio=1):
-        """patch.py:108-133 -> (latents [T, 18, 512], list of 17 lazy noise modules)."""
+    def forward(self, latent_palette, downscale_factor=1, aspect_ratio=1, latents_out=None):
+        """patch.py:108-133 -> (latents [T, 18, 512], list of 17 lazy noise modules).
+        latents_out: optional preallocated contiguous [T, 18, 512] tensor to render into (batch pipelines)."""
         self.rng.manual_seed(self.seed)
         dev = latent_palette.device
         T, P = self.length, len(latent_palette)
@@ -119,7 +120,7 @@ class Patch:
                                       sp["segments"], sp["loop_bars"], sp["seq_feat"], sp["seq_feat_weight"], dev)
             alpha, beta = merge_coefficients(feats, sp["merge_type"], sp["mod_feat"], sp["mod_feat_weight"], T, dev)
             acc.merge(sel, S, alpha, beta, sp["merge_depth"])
-        latents = acc.render(latent_palette)
+        latents = acc.render(latent_palette, out=latents_out)
 
         noise = [
             Loop(rng=self.rng, length=self.length,
