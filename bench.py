@@ -178,6 +178,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="full", choices=["full", "cfg2"])
     ap.add_argument("--clips", type=int, default=None)
+    ap.add_argument("--rng", default="cuda", choices=["cpu", "cuda"], help="device of the per-clip Patch generator")
+    ap.add_argument("--workers", type=int, default=None, help="host threads building the per-clip patches")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
@@ -228,7 +230,8 @@ def main():
         palette = palette.to(dev)
 
         def step(xd):
-            feats, latents, _ = pipeline.features_and_latents(xd, SR, FPS, palette, segs)
+            feats, latents, _ = pipeline.features_and_latents(xd, SR, FPS, palette, segs, rng_device=args.rng,
+                                                              workers=args.workers)
             # the one cross-clip reduction of the path: per-feature (count, sum, sum^2) for the dataset mean / std
             stats.zero_()
             ops.feature_stats(feats, stats)
@@ -245,7 +248,6 @@ def main():
     for _ in range(args.warmup):
         out = step(x)
     barrier()
-    cabi.event_log = EventLog()
     launches0 = cabi.launch_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local_rank) as clocks:
@@ -257,11 +259,18 @@ def main():
         barrier()
     ms = ev0.elapsed_time(ev1)
     launches = cabi.launch_count - launches0
+    # per-kernel times: ONE extra (untimed) step with CUDA events around every launch of the C ABI, on the launching
+    # stream; kept out of the timed region because two event records per launch cost host time
+    cabi.event_log = EventLog()
+    workers_timed, args.workers = args.workers, 1  # one launching thread: events bracket exactly one kernel each
+    out = step(x)
+    barrier()
+    args.workers = workers_timed
     per_kernel = {}
     for name, evs in cabi.event_log.items():
-        t_ms = sum(a.elapsed_time(b) for a, b, _ in evs)
-        nb = sum(c for _, _, c in evs if c is not None)
-        per_kernel[name] = (t_ms, nb, len(evs))
+        t_ms = sum(a.elapsed_time(b) for a, b, _ in evs) * args.steps  # scaled to the timed region's step count
+        nb = sum(c for _, _, c in evs if c is not None) * args.steps
+        per_kernel[name] = (t_ms, nb, len(evs) * args.steps)
     cabi.event_log = None
     t = torch.tensor([ms], device=dev, dtype=torch.float64)
     if world > 1:
@@ -334,7 +343,9 @@ def main():
             "config": {"workload": workload_name(kind, B), "clips_per_gpu": B, "frames_per_clip": T,
                        "l2": f"inputs_exceed_l2 ({B * n * 4 / 1e9:.2f} GB of waveforms per step)",
                        "parallelism": f"clip-sharded x{world}; one NCCL all-reduce of 59x3 fp64 feature stats per step"
-                       if kind == "full" else f"clip-sharded x{world}, no data-path collective"},
+                       if kind == "full" else f"clip-sharded x{world}, no data-path collective",
+                       "patch_rng": args.rng if kind == "full" else None,
+                       "host_threads": (args.workers or pipeline.default_patch_workers(args.rng)) if kind == "full" else 1},
             "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
         }))
     if world > 1:

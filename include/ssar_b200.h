@@ -293,6 +293,24 @@ int ssar_weights_merge(float* weights, int n_rows, int n_groups, int n_basis, in
                        const float* seq, const float* alpha, const float* beta, float alpha_scalar,
                        float beta_scalar, void* stream);
 
+/* One latent sub-patch (ssar/random/latent.py:35-78) applied to weight matrices [n_rows, n_groups, n_basis] in place:
+ * raw[t, k] = src_scale * src[t * src_ld + k] (src_mode 0: einsum / spline / smoothed one-hot weights, :39-52) or
+ * (f, 1 - f) with f = src_scale * src[t * src_ld] (src_mode 1: the 2-latent lerp of :44-45, n_select == 2);
+ * S = circular Gaussian of raw along t with `taps` [2 * radius + 1] (:54; radius 0 = none);
+ * beta[t] = mod_scale * mod[t * mod_ld], alpha = 1 - beta when mod != NULL (modulate, :72-75), else the scalars
+ * (average 0.5 / 0.5, overwrite 0 / 1; alpha_scalar == 0 never reads the old weights);
+ * weights[t, g, p] = alpha * weights[t, g, p] + beta * (p == selection[k] ? S[t, k] : 0) for g in [g_begin, g_end).
+ * selection: n_select distinct int64 palette indices in device memory (the randperm prefix of :36). */
+int ssar_subpatch_merge(float* weights, int n_rows, int n_groups, int n_basis, int g_begin, int g_end,
+                        const long long* selection, int n_select, const float* src, long long src_ld, float src_scale,
+                        int src_mode, const float* taps, int radius, const float* mod, long long mod_ld,
+                        float mod_scale, float alpha_scalar, float beta_scalar, void* stream);
+
+/* out[t, k] = sum_i taps[i] * (labels[(t + i - radius) mod n_rows] == k): latent.py:39-41's one-hot gather followed by
+ * its circular Gaussian, as weights [n_rows, n_classes]. labels: int64 [n_rows] in device memory. */
+int ssar_onehot_gauss(const long long* labels, int n_rows, int n_classes, const float* taps, int radius, float* out,
+                      void* stream);
+
 /* out[t, j] = mu[t] + sig[t] * x[t, j] (models/latent_n_noise2.py:163-176); mu / sig NULL -> 0 / 1 */
 int ssar_rows_affine(const float* x, long long n_rows, long long inner, const float* mu, const float* sig,
                      float* out, void* stream);

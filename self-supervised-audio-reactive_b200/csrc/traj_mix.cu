@@ -110,7 +110,107 @@ __global__ void weights_merge_kernel(float* __restrict__ Wt, int T, int G, int K
         const int t = (int)(r / (g1 - g0));
         const float al = alpha ? alpha[t] : alpha_s, be = beta ? beta[t] : beta_s;
         float* w = Wt + ((long long)t * G + g) * K + k;
-        *w = al * *w + be * S[(long long)t * K + k];
+        *w = fmaf(al, *w, be * S[(long long)t * K + k]);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// One latent sub-patch (ssar/random/latent.py:35-78) applied to the weight matrices in ONE launch:
+//   raw[t, k]   = src_scale * src[t, k]                       (src_mode 0: einsum weights / spline weights / smoothed one-hots)
+//               = (f, 1 - f), f = src_scale * src[t, 0]       (src_mode 1: the 2-latent lerp of latent.py:44-45)
+//   S[t, k]     = sum_i taps[i] * raw[(t + i - radius) mod T, k]    (the circular sigma = 1 smoothing of latent.py:54)
+//   beta[t]     = mod_scale * mod[t] (alpha = 1 - beta) when mod != NULL, else the scalars
+//   W[t, g, sel[k]] = alpha * W[t, g, sel[k]] + beta * S[t, k],   W[t, g, p] = alpha * W[t, g, p] elsewhere,  g in [g0, g1)
+// Accumulation order of the taps equals gauss1d_kernel's (ascending tap index, fmaf), products that the reference
+// rounds separately (feature * weight, 1 - f, 1 - m) are rounded separately here (__fmul_rn / __fsub_rn).
+// CTA = SP_TT frames; the inverse selection map (palette column -> k) and the smoothed rows live in shared memory.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int SP_TT = 8;
+
+__device__ __forceinline__ float subpatch_raw(const float* __restrict__ src, long long ld, float scale, int mode, int t, int k) {
+    if (mode == 0) return __fmul_rn(scale, __ldg(src + (long long)t * ld + k));
+    const float f = __fmul_rn(scale, __ldg(src + (long long)t * ld));
+    return k == 0 ? f : __fsub_rn(1.f, f);
+}
+
+__global__ void __launch_bounds__(256) subpatch_merge_kernel(float* __restrict__ Wt, int T, int G, int P, int g0, int g1,
+                                                             const long long* __restrict__ sel, int K,
+                                                             const float* __restrict__ src, long long src_ld, float src_scale,
+                                                             int src_mode, const float* __restrict__ taps, int radius,
+                                                             const float* __restrict__ mod, long long mod_ld, float mod_scale,
+                                                             float alpha_s, float beta_s) {
+    extern __shared__ float sp_smem[];
+    float* S = sp_smem;                                   // [SP_TT][K]
+    float* ab = S + SP_TT * K;                            // [SP_TT][2]
+    int* inv = reinterpret_cast<int*>(ab + SP_TT * 2);    // [P]
+    const int t0 = blockIdx.x * SP_TT;
+    for (int p = threadIdx.x; p < P; p += blockDim.x) inv[p] = -1;
+    __syncthreads();
+    for (int k = threadIdx.x; k < K; k += blockDim.x) {
+        const long long p = sel[k];
+        if (p >= 0 && p < P) inv[(int)p] = k;
+    }
+    for (int i = threadIdx.x; i < SP_TT * K; i += blockDim.x) {
+        const int tt = i / K, k = i - tt * K;
+        const int t = t0 + tt;
+        float acc = 0.f;
+        if (t < T) {
+            if (radius == 0) {
+                acc = subpatch_raw(src, src_ld, src_scale, src_mode, t, k);
+            } else {
+                int ti = (t - radius) % T;
+                if (ti < 0) ti += T;
+                for (int j = 0; j <= 2 * radius; ++j) {
+                    acc = fmaf(__ldg(taps + j), subpatch_raw(src, src_ld, src_scale, src_mode, ti, k), acc);
+                    if (++ti == T) ti = 0;
+                }
+            }
+        }
+        S[i] = acc;
+    }
+    if (threadIdx.x < SP_TT) {
+        const int t = t0 + threadIdx.x;
+        float al = alpha_s, be = beta_s;
+        if (mod && t < T) {
+            be = __fmul_rn(mod_scale, __ldg(mod + (long long)t * mod_ld));
+            al = __fsub_rn(1.f, be);
+        }
+        ab[2 * threadIdx.x] = al;
+        ab[2 * threadIdx.x + 1] = be;
+    }
+    __syncthreads();
+    const int Gr = g1 - g0;
+    const bool overwrite = (mod == nullptr) && alpha_s == 0.f;
+    for (int i = threadIdx.x; i < SP_TT * Gr * P; i += blockDim.x) {
+        const int p = i % P;
+        const int r = i / P;
+        const int g = g0 + r % Gr;
+        const int tt = r / Gr;
+        const int t = t0 + tt;
+        if (t >= T) break;
+        const int k = inv[p];
+        const float s = k >= 0 ? S[tt * K + k] : 0.f;
+        float* w = Wt + ((long long)t * G + g) * P + p;
+        const float al = ab[2 * tt], be = ab[2 * tt + 1];
+        *w = overwrite ? be * s : fmaf(al, *w, be * s);
+    }
+}
+
+// out[t, k] = sum_i taps[i] * (labels[(t + i - radius) mod T] == k): the one-hot gather of latent.py:39-40 followed by
+// the circular Gaussian of :41, without materialising the one-hot matrix (same tap order as gauss1d_kernel).
+__global__ void onehot_gauss_kernel(const long long* __restrict__ labels, int T, int K, const float* __restrict__ taps,
+                                    int radius, float* __restrict__ out) {
+    const long long n = (long long)T * K;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const int t = (int)(i / K), k = (int)(i - (long long)t * K);
+        int ti = (t - radius) % T;
+        if (ti < 0) ti += T;
+        float acc = 0.f;
+        for (int j = 0; j <= 2 * radius; ++j) {
+            acc = fmaf(__ldg(taps + j), (__ldg(labels + ti) == k) ? 1.f : 0.f, acc);
+            if (++ti == T) ti = 0;
+        }
+        out[i] = acc;
     }
 }
 
@@ -156,6 +256,37 @@ extern "C" int ssar_weights_merge(float* weights, int n_rows, int n_groups, int 
     weights_merge_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(weights, n_rows, n_groups, n_basis, g_begin, g_end, seq,
                                                                 alpha, beta, alpha_scalar, beta_scalar);
     return ssar_launch_status("weights_merge");
+}
+
+extern "C" int ssar_subpatch_merge(float* weights, int n_rows, int n_groups, int n_basis, int g_begin, int g_end,
+                                   const long long* selection, int n_select, const float* src, long long src_ld,
+                                   float src_scale, int src_mode, const float* taps, int radius, const float* mod,
+                                   long long mod_ld, float mod_scale, float alpha_scalar, float beta_scalar, void* stream) {
+    if (n_rows == 0 || n_basis == 0 || g_end <= g_begin) return SSAR_OK;
+    SSAR_REQUIRE(weights && selection && src, "subpatch_merge: null pointer");
+    SSAR_REQUIRE(0 <= g_begin && g_end <= n_groups, "subpatch_merge: bad group range");
+    SSAR_REQUIRE(n_select > 0 && (src_mode == 0 || (src_mode == 1 && n_select == 2)),
+                 "subpatch_merge: src_mode 1 (lerp) needs exactly 2 selected latents");
+    SSAR_REQUIRE(radius >= 0 && (radius == 0 || taps), "subpatch_merge: taps required when radius > 0");
+    const size_t smem = ((size_t)SP_TT * n_select + SP_TT * 2 + n_basis) * sizeof(float);
+    SSAR_REQUIRE(smem <= 200 * 1024, "subpatch_merge: palette / selection too large for one CTA's shared memory");
+    if (smem > 48 * 1024)
+        cudaFuncSetAttribute(subpatch_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    subpatch_merge_kernel<<<ssar_div_up(n_rows, SP_TT), 256, smem, (cudaStream_t)stream>>>(
+        weights, n_rows, n_groups, n_basis, g_begin, g_end, selection, n_select, src, src_ld, src_scale, src_mode, taps,
+        radius, mod, mod_ld, mod_scale, alpha_scalar, beta_scalar);
+    return ssar_launch_status("subpatch_merge");
+}
+
+extern "C" int ssar_onehot_gauss(const long long* labels, int n_rows, int n_classes, const float* taps, int radius,
+                                 float* out, void* stream) {
+    if (n_rows == 0 || n_classes == 0) return SSAR_OK;
+    SSAR_REQUIRE(labels && out && (radius == 0 || taps), "onehot_gauss: null pointer");
+    SSAR_REQUIRE(radius >= 0, "onehot_gauss: bad radius");
+    int grid = ssar_div_up((long long)n_rows * n_classes, 256);
+    if (grid > SSAR_NUM_SMS * 8) grid = SSAR_NUM_SMS * 8;
+    onehot_gauss_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(labels, n_rows, n_classes, taps, radius, out);
+    return ssar_launch_status("onehot_gauss");
 }
 
 extern "C" int ssar_rows_affine(const float* x, long long n_rows, long long inner, const float* mu, const float* sig,

@@ -6,6 +6,7 @@ PyTorch is used for device memory, streams and `torch.distributed` only.
 from __future__ import annotations
 
 import ctypes as C
+import threading
 from pathlib import Path
 
 import torch
@@ -84,7 +85,15 @@ def ptr(t):
     return C.c_void_p(t.data_ptr())
 
 
+_count_lock = threading.Lock()
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def stream_ptr():
+    """torch's current stream on the current device as a raw cudaStream_t (the fast private accessor when present:
+    `torch.cuda.current_stream()` costs ~15 us per call, which matters at ~2 000 launches per step)."""
+    if _raw_stream is not None:
+        return C.c_void_p(_raw_stream(torch.cuda.current_device()))
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
@@ -102,7 +111,8 @@ def call(name: str, *args, nbytes=None):
         log.append((e0, e1, nbytes))
     else:
         rc = fn(*args, stream_ptr())
-    launch_count += 1
+    with _count_lock:  # patches of different clips are built by several host threads
+        launch_count += 1
     if rc != 0:
         raise SsarError(f"{name} failed ({rc}): {lib().ssar_last_error().decode()}")
 

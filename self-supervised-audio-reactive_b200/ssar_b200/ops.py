@@ -509,6 +509,35 @@ def weights_merge(weights: torch.Tensor, seq: torch.Tensor, g_begin: int, g_end:
     return weights
 
 
+def subpatch_merge(weights: torch.Tensor, g_begin: int, g_end: int, selection: torch.Tensor, src: torch.Tensor,
+                   src_scale: float = 1.0, lerp: bool = False, sigma: float = 1.0, mod: torch.Tensor | None = None,
+                   mod_scale: float = 1.0, alpha: float = 0.5, beta: float = 0.5):
+    """One latent sub-patch into weights [T, G, P] in place (see `ssar_subpatch_merge`).  selection: int64 [K] on the
+    GPU; src: [T, K] (or [T, >=1] with lerp=True: K = 2, S = (f, 1 - f)); sigma: circular Gaussian along time (0 = none);
+    mod: [T, >=1] modulation feature (alpha = 1 - mod_scale * mod, beta = mod_scale * mod) or None (scalars)."""
+    T, G, P = weights.shape
+    K = int(selection.numel())
+    if sigma:
+        radius = min(int(sigma * 4), 3 * T)
+        taps = plan.gaussian_taps(float(sigma), radius, str(weights.device))
+    else:
+        radius, taps = 0, None
+    cabi.call("ssar_subpatch_merge", ptr(weights), i32(T), i32(G), i32(P), i32(g_begin), i32(g_end), ptr(selection), i32(K),
+              ptr(src), i64(src.stride(0)), f32(src_scale), i32(1 if lerp else 0), ptr(taps), i32(radius), ptr(mod),
+              i64(mod.stride(0) if mod is not None else 0), f32(mod_scale), f32(alpha), f32(beta))
+    return weights
+
+
+def onehot_gauss(labels: torch.Tensor, n_classes: int, sigma: float):
+    """labels int64 [T] on the GPU -> circularly smoothed one-hot weights [T, n_classes] (latent.py:39-41)."""
+    T = labels.shape[0]
+    radius = min(int(sigma * 4), 3 * T)
+    taps = plan.gaussian_taps(float(sigma), radius, str(labels.device))
+    out = torch.empty(T, n_classes, dtype=torch.float32, device=labels.device)
+    cabi.call("ssar_onehot_gauss", ptr(labels), i32(T), i32(n_classes), ptr(taps), i32(radius), ptr(out))
+    return out
+
+
 def rows_affine(x: torch.Tensor, mu=None, sig=None):
     """out[t, ...] = mu[t] + sig[t] * x[t, ...]."""
     x = x.contiguous()

@@ -510,3 +510,17 @@ def spline_loop_weights_cpu(n_knots: int, size: int, n_loops=1) -> torch.Tensor:
     W = W.copy()
     W[:, 0] += W[:, -1]
     return torch.from_numpy(W[:, :-1].astype(np.float32))
+
+
+@functools.lru_cache(maxsize=256)
+def spline_loop_weights(n_knots: int, size: int, n_loops, device) -> torch.Tensor:
+    """`spline_loop_weights_cpu` cached on the device (the weights depend only on the knot count, length and loop count,
+    so every sub-patch / clip of a batch shares them).  Read-only: callers must not write into the result."""
+    return spline_loop_weights_cpu(n_knots, size, n_loops).to(_dev(device))
+
+
+@functools.lru_cache(maxsize=256)
+def loop_phase(n_loops, length: int, device) -> torch.Tensor:
+    """ssar/random/noise.py:49: linspace(0, n_loops * 2 pi, length), evaluated on the CPU like the reference (the
+    module is built on the default device and moved afterwards), cached on the device.  Read-only."""
+    return torch.linspace(0, n_loops * 2 * torch.pi, length).to(_dev(device))

@@ -76,25 +76,73 @@ def latent_patch(rng, latents, palette, segmentations, features, tempo, fps, pat
 
 class LatentWeights:
     """Accumulates a whole stack of sub-patches as weights [T, G, P] over the full palette (G layer groups of
-    `group_layers` layers) and renders [T, W, L] with ONE mixing GEMM."""
+    `group_layers` layers) and renders [T, W, L] with ONE mixing GEMM.  Each sub-patch is ONE kernel launch
+    (`ssar_subpatch_merge`: feature scaling, the sigma = 1 smoothing, the merge coefficients and the scatter of the
+    selected palette columns are fused), so a 20-sub-patch stack costs ~20 launches and no [T, 18, 512] traffic."""
 
     def __init__(self, n_frames, n_palette, n_layers=18, group_layers=6, device="cuda"):
         self.T, self.P, self.Wn, self.gl = n_frames, n_palette, n_layers, group_layers
         self.G = n_layers // group_layers
         self.device = torch.device(device)
-        self.w = torch.zeros(self.T, self.G, self.P, dtype=torch.float32, device=self.device)
+        self.w = torch.empty(self.T, self.G, self.P, dtype=torch.float32, device=self.device)
+        self._labels = {}
 
-    def _dense(self, selection, S):
-        D = torch.zeros(self.T, self.P, dtype=torch.float32, device=self.device)
-        D.index_add_(1, selection.to(self.device).long(), S)  # duplicates (the closing spline knot) accumulate
-        return D
+    def _sel(self, selection):
+        return selection.to(self.device, non_blocking=True)
 
     def set_base(self, selection, S):
-        ops.weights_merge(self.w, self._dense(selection, S), 0, self.G, 0.0, 1.0)
+        """weights = S scattered to the selected palette columns in every layer group (overwrites)."""
+        ops.subpatch_merge(self.w, 0, self.G, self._sel(selection), S, sigma=0, alpha=0.0, beta=1.0)
 
     def merge(self, selection, S, alpha, beta, merge_depth):
+        """Generic merge of an already smoothed sequence S [T, K] with float or [T] tensor coefficients."""
         lo, hi = LAYER_SLICES[merge_depth]
-        ops.weights_merge(self.w, self._dense(selection, S), lo // self.gl, hi // self.gl, alpha, beta)
+        if torch.is_tensor(alpha) or torch.is_tensor(beta):
+            D = torch.zeros(self.T, self.P, dtype=torch.float32, device=self.device)
+            D.index_add_(1, self._sel(selection).long(), S)
+            ops.weights_merge(self.w, D, lo // self.gl, hi // self.gl, alpha, beta)
+        else:
+            ops.subpatch_merge(self.w, lo // self.gl, hi // self.gl, self._sel(selection), S, sigma=0, alpha=float(alpha),
+                               beta=float(beta))
+
+    def labels(self, key, segmentation):
+        """Segmentation labels as int64 on the compute device, copied once per key."""
+        t = self._labels.get(key)
+        if t is None:
+            t = self._labels[key] = segmentation.to(self.device).long().contiguous()
+        return t
+
+    def apply_subpatch(self, rng, segmentations, features, tempo, fps, patch_type, segments, loop_bars, seq_feat,
+                       seq_feat_weight, mod_feat, mod_feat_weight, merge_type, merge_depth):
+        """latent.py:35-78 on the weights: same RNG draw (one randperm per sub-patch), same arithmetic per element."""
+        T, P = self.T, self.P
+        segmentation = segmentations[(seq_feat, segments)]  # looked up for every patch type, like latent.py:36
+        permutation = torch.randperm(P, generator=rng, device=rng.device)
+        lerp, scale = False, 1.0
+        if patch_type == "segmentation":
+            selection = permutation[:segments]
+            src = ops.onehot_gauss(self.labels((seq_feat, segments), segmentation), int(segments), 5)
+        elif patch_type == "feature":
+            feature = features[seq_feat]
+            scale = float(seq_feat_weight)
+            if feature.shape[1] == 1:
+                selection, src, lerp = permutation[:2], feature, True
+            else:
+                selection, src = permutation[: feature.shape[1]], feature
+        elif patch_type == "loop":
+            selection = permutation[:segments]
+            n_loops = T / fps / 60 / tempo / 4 / loop_bars
+            src = plan.spline_loop_weights(len(selection), T, n_loops, str(self.device))
+        else:
+            raise ValueError(patch_type)
+        lo, hi = LAYER_SLICES[merge_depth]
+        if merge_type == "modulate":
+            mod, mod_scale, alpha, beta = features[mod_feat], float(mod_feat_weight), 0.0, 0.0
+        else:
+            mod, mod_scale = None, 1.0
+            alpha, beta = (0.5, 0.5) if merge_type == "average" else (0.0, 1.0)
+        ops.subpatch_merge(self.w, lo // self.gl, hi // self.gl, self._sel(selection), src, src_scale=scale, lerp=lerp,
+                           sigma=1, mod=mod, mod_scale=mod_scale, alpha=alpha, beta=beta)
 
     def render(self, palette, out=None):
         return ops.mix_gemm(self.w, palette.to(self.device), out=out)

@@ -4,7 +4,7 @@ from __future__ import annotations
 
 import torch
 
-from .. import ops
+from .. import ops, plan
 from .._cabi import NoiseOp
 
 LOOP, BLEND, MULTIPLY, BUFFER, AVERAGE, MODULATE, SCALEBIAS = range(7)
@@ -38,6 +38,7 @@ class Noise:
 
     def to(self, device):
         self._own_to(device)
+        self.__dict__.pop("_child_device", None)
         for child in ("left", "right", "base"):
             if hasattr(self, child):
                 getattr(self, child).to(device)
@@ -47,10 +48,15 @@ class Noise:
     def device(self):
         for name in self._buffers:
             return getattr(self, name).device
-        for child in ("left", "right", "base"):
-            if hasattr(self, child):
-                return getattr(self, child).device
-        raise RuntimeError("noise module without buffers")
+        d = self.__dict__.get("_child_device")
+        if d is None:
+            for child in ("left", "right", "base"):
+                if hasattr(self, child):
+                    d = self._child_device = getattr(self, child).device
+                    break
+            else:
+                raise RuntimeError("noise module without buffers")
+        return d
 
     # ---- program compilation -------------------------------------------------------------------
     def _leaf(self, to_acc, i, b, keep):
@@ -117,9 +123,11 @@ class Loop(Noise):
         super().__init__(length, size)
         self.sigma = sigma
         self.noise = torch.randn((3, size[0], size[1]), generator=rng, device=rng.device)
-        self.idx = torch.linspace(0, n_loops * 2 * torch.pi, length)
         if device is not None:
+            self.idx = plan.loop_phase(n_loops, int(length), str(device))  # cached, read-only
             self._own_to(device)
+        else:
+            self.idx = torch.linspace(0, n_loops * 2 * torch.pi, length)
 
     def _leaf(self, to_acc, i, b, keep):
         return _op(LOOP, self.noise, self.idx, p0=self.sigma / 50, to_acc=to_acc)
@@ -143,11 +151,13 @@ class Modulate(Noise):
 
     _buffers = ("modulator",)
 
-    def __init__(self, left, right, modulator):
+    def __init__(self, left, right, modulator, _mean=None):
         super().__init__(left.length, left.size)
         self.left, self.right = left, right
-        self.modulator = modulator.float().mean(1)
-        self._own_to(left.device)
+        # _mean: modulator.mean(1) computed once by noise_patch for all the layers it wraps
+        self.modulator = modulator.float().mean(1) if _mean is None else _mean
+        if _mean is None:
+            self._own_to(left.device)
 
     def _emit(self, prog, i, b, keep):
         self.left._emit(prog, i, b, keep)
@@ -174,8 +184,48 @@ NOISE_LAYER_RANGES = {"low": range(0, 6), "mid": range(6, 12), "high": range(12,
 def noise_patch(rng, noise, features, tempo, fps, patch_type, loop_bars, seq_feat, seq_feat_weight, mod_feat,
                 mod_feat_weight, merge_type, merge_depth, noise_mean, noise_std):
     """ssar/random/noise.py:89-140 (same RNG draw order: one basis draw per wrapped layer, in layer order)."""
+    layers = NOISE_LAYER_RANGES[merge_depth]
+    if len(layers) == 0:
+        return noise
+    # everything that does not depend on the layer is computed once per sub-patch (the reference recomputes the scaled
+    # features and the modulator mean for each wrapped layer: same values)
+    dev = noise[layers[0]].device
+    feature = (seq_feat_weight * features[seq_feat]).to(dev)
+    if feature.dtype != torch.float32 or not feature.is_contiguous():
+        feature = feature.float().contiguous()
+    length = len(feature)
+    if merge_type == "modulate":
+        modulator = (mod_feat_weight * features[mod_feat]).to(dev)
+        mod_mean = modulator.float().mean(1).contiguous()
+    if patch_type == "loop":
+        n_loops = length / fps / 60 / tempo / 4 / loop_bars
+    for n in layers:
+        if noise[n].device != dev:  # mixed-device module lists: fall back to per-layer placement
+            return _noise_patch_per_layer(rng, noise, features, tempo, fps, patch_type, loop_bars, seq_feat, seq_feat_weight,
+                                          mod_feat, mod_feat_weight, merge_type, layers, noise_mean, noise_std, start=n)
+        if patch_type == "blend":
+            new_noise = Blend(rng=rng, length=length, size=noise[n].size, modulator=feature)
+        elif patch_type == "multiply":
+            new_noise = Multiply(rng=rng, length=length, size=noise[n].size, modulator=feature)
+        elif patch_type == "loop":
+            new_noise = Loop(rng=rng, length=length, size=noise[n].size, n_loops=n_loops, device=dev)
+        if merge_type == "average":
+            noise[n] = Average(left=noise[n], right=new_noise)
+        elif merge_type == "modulate":
+            noise[n] = Modulate(left=noise[n], right=new_noise, modulator=modulator, _mean=mod_mean)
+        else:
+            noise[n] = new_noise
+        noise[n] = ScaleBias(noise[n], scale=noise_std, bias=noise_mean)
+    return noise
+
+
+def _noise_patch_per_layer(rng, noise, features, tempo, fps, patch_type, loop_bars, seq_feat, seq_feat_weight, mod_feat,
+                           mod_feat_weight, merge_type, layers, noise_mean, noise_std, start):
+    """noise.py:89-140 layer by layer (each layer on its own device), from layer `start` of `layers` on."""
     feature = seq_feat_weight * features[seq_feat]
-    for n in NOISE_LAYER_RANGES[merge_depth]:
+    for n in layers:
+        if n < start:
+            continue
         dev = noise[n].device
         if patch_type == "blend":
             new_noise = Blend(rng=rng, length=len(feature), size=noise[n].size, modulator=feature.to(dev))

@@ -35,6 +35,97 @@ def skewnorm(rng, a, loc, scale, size=()):
     return loc + scale * torch.where(u0 >= 0, u1, -u1)
 
 
+class _Deferred:
+    """A draw whose value is still on the generator's device; `Patch._resolve` replaces it after ONE bulk copy."""
+
+    __slots__ = ("kind", "slot", "aux")
+
+    def __init__(self, kind, slot, aux=None):
+        self.kind, self.slot, self.aux = kind, slot, aux
+
+
+class _Sampler:
+    """Issues exactly the generator calls of patch.py:12-32 / :41-66 in the reference's order, but leaves the drawn
+    values on the generator's device and converts them to Python objects with one device-to-host copy at the end
+    (a CUDA generator otherwise costs one stream synchronisation per draw: ~400 per Patch)."""
+
+    def __init__(self, rng):
+        self.rng = rng
+        self.floats, self._n_floats = [], 0
+        self._uniform, self._weighted, self._host_probs = {}, {}, {}
+
+    def _probs(self, n_options, weights):
+        if weights is None:
+            p = self._uniform.get(n_options)
+            if p is None:
+                p = self._uniform[n_options] = torch.ones(n_options, device=self.rng.device) / n_options
+            return p
+        key = tuple(weights)
+        p = self._weighted.get(key)
+        if p is None:
+            p = self._weighted[key] = torch.tensor(weights, device=self.rng.device) / np.sum(weights)
+        return p
+
+    def choice(self, options, weights=None):
+        """random_choice (patch.py:12-20) with n = 1.  `Tensor.multinomial(1)` draws q ~ Exp(1) with ONE
+        `exponential_` call on a tensor shaped like the probabilities and returns argmax(p / q) (ATen
+        native/Distributions.cpp multinomial_out, the no-replacement fast path; its other ~10 ops are input checks).
+        Only that generator call is issued here; the fp32 division and the arg-max are done after the bulk copy.
+        tests: the sampler equals the eager `random_choice` path draw for draw (CPU and CUDA generators)."""
+        p = self._probs(len(options), weights)
+        self.floats.append(torch.empty_like(p).exponential_(1, generator=self.rng))
+        self._n_floats += len(options)
+        return _Deferred("choice", self._n_floats - len(options), (options, p, weights))
+
+    def randn(self, scale=1.0):
+        self.floats.append(torch.randn((), generator=self.rng, device=self.rng.device).reshape(1))
+        self._n_floats += 1
+        return _Deferred("randn", self._n_floats - 1, scale)
+
+    def skewnorm(self, a, loc, scale):
+        """skewnorm (patch.py:23-32): the two normal draws now, the fp32 arithmetic after the copy."""
+        self.floats.append(torch.randn((), generator=self.rng, device=self.rng.device).reshape(1))
+        self.floats.append(torch.randn((), generator=self.rng, device=self.rng.device).reshape(1))
+        self._n_floats += 2
+        return _Deferred("skewnorm", self._n_floats - 2, (a, loc, scale))
+
+    def resolve(self, tree):
+        floats = torch.cat(self.floats).cpu().numpy() if self.floats else None
+        f = np.float32
+
+        def host_probs(p, weights):
+            key = (p.shape[0], None if weights is None else tuple(weights))
+            h = self._host_probs.get(key)
+            if h is None:
+                h = self._host_probs[key] = p.cpu().numpy()
+            return h
+
+        def value(d):
+            if d.kind == "choice":
+                options, p, weights = d.aux
+                q = floats[d.slot : d.slot + len(options)]
+                return options[int(np.argmax(host_probs(p, weights) / q))]  # fp32 IEEE division, first maximum
+            if d.kind == "randn":
+                return float(floats[d.slot]) * d.aux
+            a, loc, scale = d.aux
+            u0, v = f(floats[d.slot]), f(floats[d.slot + 1])
+            dd = a / np.sqrt(1 + a ** 2)
+            # fp32 op by op, like the tensor expression d * u0 + v * sqrt(1 - d^2); loc + scale * where(u0 >= 0, u1, -u1)
+            u1 = f(f(dd) * u0) + f(v * f(np.sqrt(1 - dd ** 2)))
+            return float(f(loc) + f(f(scale) * (u1 if u0 >= 0 else -u1)))
+
+        def walk(o):
+            if isinstance(o, _Deferred):
+                return value(o)
+            if isinstance(o, dict):
+                return {k: walk(v) for k, v in o.items()}
+            if isinstance(o, list):
+                return [walk(v) for v in o]
+            return o
+
+        return walk(tree)
+
+
 class Patch:
     """patch.py:35-175.  `device`: where the generator lives (as in the reference); `compute_device`: where the
     trajectory tensors live (defaults to the palette's device at forward time)."""
@@ -50,18 +141,24 @@ class Patch:
         self.length = features[list(features.keys())[0]].shape[0]
         self.features = features
         self.segmentations = segmentations
-        self.num_base_latents = torch.randint(3, 15, size=(), generator=rng, device=rng.device).item()
-        self.sigma_base_noise = 1 + 9 * torch.rand((), generator=rng, device=rng.device).item()
-        self.loops_base_noise = random_choice(rng, [1, 2, 4, 8, 16, 32, 64])
+        sm = self._sampler = _Sampler(rng)
+        num_base_latents = torch.randint(3, 15, size=(), generator=rng, device=rng.device)
+        sigma_u = torch.rand((), generator=rng, device=rng.device)
+        loops_base_noise = sm.choice([1, 2, 4, 8, 16, 32, 64])
         self.ks = np.unique([k for (_, k) in segmentations]).tolist()
-        self.latent_patches = [
+        latent_patches = [
             self.random_latent_patch()
             for _ in range(torch.randint(min_subpatches, max_subpatches, size=(), generator=rng, device=rng.device))
         ]
-        self.noise_patches = [
+        noise_patches = [
             self.random_noise_patch()
             for _ in range(torch.randint(min_subpatches, max_subpatches, size=(), generator=rng, device=rng.device))
         ]
+        self.loops_base_noise, self.latent_patches, self.noise_patches = sm.resolve(
+            [loops_base_noise, latent_patches, noise_patches])
+        self.num_base_latents = num_base_latents.item()
+        self.sigma_base_noise = 1 + 9 * sigma_u.item()
+        self._sampler = None
 
     def update_intensity(self, val):
         """patch.py:68-75 (including the write of noise_std into latent_patches[p], as in the reference)."""
@@ -73,35 +170,45 @@ class Patch:
             self.noise_patches[p]["mod_feat_weight"] = skewnorm(self.rng, a=5, loc=val, scale=0.5).item()
             self.latent_patches[p]["noise_std"] = skewnorm(self.rng, a=5, loc=val, scale=0.5).item()
 
+    def _draws(self):
+        """Draw source for the config samplers: the deferred sampler while __init__ runs, eager draws afterwards."""
+        sm = getattr(self, "_sampler", None)
+        if sm is not None:
+            return sm.choice, (lambda a, loc, scale: sm.skewnorm(a, loc, scale)), sm.randn
+        rng = self.rng
+        return ((lambda options, weights=None: random_choice(rng, options, weights)),
+                (lambda a, loc, scale: skewnorm(rng, a=a, loc=loc, scale=scale).item()),
+                (lambda scale=1.0: torch.randn((), generator=rng, device=rng.device).item() * scale))
+
     def random_latent_patch(self):
+        """patch.py:77-91 (same draws in the same order)."""
+        choice, skew, _ = self._draws()
         return dict(
-            patch_type=random_choice(self.rng, ["segmentation", "feature", "loop"]),
-            segments=random_choice(self.rng, self.ks),
-            loop_bars=random_choice(self.rng, [4, 8, 16, 32], weights=[2, 2, 2, 1]),
-            seq_feat=random_choice(self.rng, ALLFEATS),
-            seq_feat_weight=skewnorm(self.rng, a=5, loc=0.666, scale=0.5).item(),
-            mod_feat=random_choice(self.rng, UNITFEATS),
-            mod_feat_weight=skewnorm(self.rng, a=5, loc=0.666, scale=0.5).item(),
-            merge_type=random_choice(self.rng, ["average", "modulate"], weights=[1, 3]),
-            merge_depth=random_choice(
-                self.rng, ["low", "mid", "high", "lowmid", "midhigh", "all"], weights=[3, 3, 3, 2, 2, 1]
-            ),
+            patch_type=choice(["segmentation", "feature", "loop"]),
+            segments=choice(self.ks),
+            loop_bars=choice([4, 8, 16, 32], weights=[2, 2, 2, 1]),
+            seq_feat=choice(ALLFEATS),
+            seq_feat_weight=skew(5, 0.666, 0.5),
+            mod_feat=choice(UNITFEATS),
+            mod_feat_weight=skew(5, 0.666, 0.5),
+            merge_type=choice(["average", "modulate"], weights=[1, 3]),
+            merge_depth=choice(["low", "mid", "high", "lowmid", "midhigh", "all"], weights=[3, 3, 3, 2, 2, 1]),
         )
 
     def random_noise_patch(self):
+        """patch.py:93-106 (same draws in the same order)."""
+        choice, skew, randn = self._draws()
         return dict(
-            patch_type=random_choice(self.rng, ["blend", "multiply", "loop"]),
-            loop_bars=random_choice(self.rng, [4, 8, 16, 32], weights=[2, 2, 2, 1]),
-            seq_feat=random_choice(self.rng, ALLFEATS),
-            seq_feat_weight=skewnorm(self.rng, a=5, loc=0.666, scale=0.5).item(),
-            mod_feat=random_choice(self.rng, UNITFEATS),
-            mod_feat_weight=skewnorm(self.rng, a=5, loc=0.666, scale=0.5).item(),
-            merge_type=random_choice(self.rng, ["average", "modulate"], weights=[1, 3]),
-            merge_depth=random_choice(
-                self.rng, ["low", "mid", "high", "lowmid", "midhigh", "all"], weights=[3, 3, 3, 2, 2, 1]
-            ),
-            noise_mean=torch.randn((), generator=self.rng, device=self.rng.device).item() * 0.5,
-            noise_std=skewnorm(self.rng, a=5, loc=0.666, scale=0.5).item(),
+            patch_type=choice(["blend", "multiply", "loop"]),
+            loop_bars=choice([4, 8, 16, 32], weights=[2, 2, 2, 1]),
+            seq_feat=choice(ALLFEATS),
+            seq_feat_weight=skew(5, 0.666, 0.5),
+            mod_feat=choice(UNITFEATS),
+            mod_feat_weight=skew(5, 0.666, 0.5),
+            merge_type=choice(["average", "modulate"], weights=[1, 3]),
+            merge_depth=choice(["low", "mid", "high", "lowmid", "midhigh", "all"], weights=[3, 3, 3, 2, 2, 1]),
+            noise_mean=randn(0.5),
+            noise_std=skew(5, 0.666, 0.5),
         )
 
     def forward(self, latent_palette, downscale_factor=1, aspect_ratio=1, latents_out=None):
@@ -110,16 +217,18 @@ class Patch:
         self.rng.manual_seed(self.seed)
         dev = latent_palette.device
         T, P = self.length, len(latent_palette)
-        feats = {k: v.to(dev) for k, v in self.features.items()}
+        feats = {}
+        for k, v in self.features.items():
+            v = v.to(dev)
+            if v.dtype != torch.float32 or v.dim() != 2 or v.stride(1) != 1:
+                v = v.float().reshape(T, -1).contiguous()
+            feats[k] = v
 
         base_selection = torch.randperm(P, generator=self.rng, device=self.rng.device)[: self.num_base_latents]
         acc = LatentWeights(T, P, latent_palette.shape[1], 6, dev)
-        acc.set_base(base_selection, plan.spline_loop_weights_cpu(len(base_selection), T, 1).to(dev))
+        acc.set_base(base_selection, plan.spline_loop_weights(len(base_selection), T, 1, str(dev)))
         for sp in self.latent_patches:
-            sel, S = sequence_weights(self.rng, T, P, self.segmentations, feats, self.tempo, self.fps, sp["patch_type"],
-                                      sp["segments"], sp["loop_bars"], sp["seq_feat"], sp["seq_feat_weight"], dev)
-            alpha, beta = merge_coefficients(feats, sp["merge_type"], sp["mod_feat"], sp["mod_feat_weight"], T, dev)
-            acc.merge(sel, S, alpha, beta, sp["merge_depth"])
+            acc.apply_subpatch(self.rng, self.segmentations, feats, self.tempo, self.fps, **sp)
         latents = acc.render(latent_palette, out=latents_out)
 
         noise = [

@@ -97,3 +97,86 @@ def test_patch_full_size_vs_oracle_frames():
     tree = N.Average(a, b)
     direct = (a.forward(5, 9) + b.forward(5, 9)) / 2
     assert rel_l2(tree.forward(5, 9), direct) < 1e-6
+
+
+def _eager_configs(features, segmentations, seed, device, min_subpatches=5, max_subpatches=20):
+    """patch.py:41-66 written with the eager helpers (`random_choice` = real Tensor.multinomial, tensor `skewnorm`)."""
+    from ssar_b200.random.mir import ALLFEATS, UNITFEATS
+    from ssar_b200.random.patch import random_choice, skewnorm
+
+    rng = torch.Generator(device)
+    rng.manual_seed(seed)
+    head = [torch.randint(3, 15, size=(), generator=rng, device=rng.device).item(),
+            1 + 9 * torch.rand((), generator=rng, device=rng.device).item(),
+            random_choice(rng, [1, 2, 4, 8, 16, 32, 64])]
+    ks = np.unique([k for (_, k) in segmentations]).tolist()
+    depth = (["low", "mid", "high", "lowmid", "midhigh", "all"], [3, 3, 3, 2, 2, 1])
+
+    def common(kinds, with_segments):
+        d = dict(patch_type=random_choice(rng, kinds))
+        if with_segments:
+            d["segments"] = random_choice(rng, ks)
+        d.update(loop_bars=random_choice(rng, [4, 8, 16, 32], weights=[2, 2, 2, 1]), seq_feat=random_choice(rng, ALLFEATS),
+                 seq_feat_weight=skewnorm(rng, a=5, loc=0.666, scale=0.5).item(), mod_feat=random_choice(rng, UNITFEATS),
+                 mod_feat_weight=skewnorm(rng, a=5, loc=0.666, scale=0.5).item(),
+                 merge_type=random_choice(rng, ["average", "modulate"], weights=[1, 3]),
+                 merge_depth=random_choice(rng, depth[0], weights=depth[1]))
+        return d
+
+    lat = [common(["segmentation", "feature", "loop"], True)
+           for _ in range(torch.randint(min_subpatches, max_subpatches, size=(), generator=rng, device=rng.device))]
+    noi = []
+    for _ in range(torch.randint(min_subpatches, max_subpatches, size=(), generator=rng, device=rng.device)):
+        d = common(["blend", "multiply", "loop"], False)
+        d["noise_mean"] = torch.randn((), generator=rng, device=rng.device).item() * 0.5
+        d["noise_std"] = skewnorm(rng, a=5, loc=0.666, scale=0.5).item()
+        noi.append(d)
+    return head, lat, noi
+
+
+def test_deferred_sampler_equals_eager_draws_cuda_generator():
+    """The deferred sampler (one exponential_ per choice, arithmetic after one bulk copy) reproduces the eager
+    multinomial / skewnorm draws of patch.py:12-32 on a CUDA (Philox) generator value for value."""
+    from ssar_b200.random.patch import Patch
+
+    feats, segs, _ = synth_patch_inputs(64, 0)
+    for seed in range(12):
+        p = Patch(feats, segs, 120.0, seed=seed, device="cuda")
+        head, lat, noi = _eager_configs(feats, segs, seed, "cuda")
+        assert [p.num_base_latents, p.sigma_base_noise, p.loops_base_noise] == head
+        assert p.latent_patches == lat and p.noise_patches == noi
+
+
+def test_subpatch_kernel_vs_separate_steps():
+    """ssar_subpatch_merge / ssar_onehot_gauss vs the unfused sequence (scale, gauss1d, index_add, weights_merge)."""
+    from ssar_b200 import ops
+
+    g = torch.Generator("cpu").manual_seed(3)
+    Tn, G, P = 601, 3, 180
+    w0 = torch.randn(Tn, G, P, generator=g).cuda()
+    mod = torch.rand(Tn, 1, generator=g).cuda()
+    for K, lerp, use_mod, (g0, g1) in [(12, False, True, (0, 2)), (2, True, False, (1, 3)), (20, False, False, (0, 3)),
+                                       (2, True, True, (2, 3))]:
+        sel = torch.randperm(P, generator=g)[:K].cuda()
+        src = torch.rand(Tn, 1 if lerp else K, generator=g).cuda()
+        scale, ms = 0.83, 1.21
+        f = scale * src
+        S = ops.gauss1d(torch.cat([f, 1 - f], 1) if lerp else f, 1, "circular")
+        D = torch.zeros(Tn, P, device="cuda").index_add_(1, sel, S)
+        if use_mod:
+            m = (ms * mod).reshape(Tn)
+            ref = ops.weights_merge(w0.clone(), D, g0, g1, (1 - m).contiguous(), m.contiguous())
+        else:
+            ref = ops.weights_merge(w0.clone(), D, g0, g1, 0.5, 0.5)
+        got = ops.subpatch_merge(w0.clone(), g0, g1, sel, src, src_scale=scale, lerp=lerp, sigma=1,
+                                 mod=mod if use_mod else None, mod_scale=ms, alpha=0.5, beta=0.5)
+        assert torch.equal(got, ref), (K, lerp, use_mod, float((got - ref).abs().max()))
+    labels = torch.randint(0, 6, (Tn,), generator=g).cuda()
+    onehot = torch.zeros(Tn, 6, device="cuda")
+    onehot[torch.arange(Tn, device="cuda"), labels] = 1.0
+    assert torch.equal(ops.onehot_gauss(labels, 6, 5), ops.gauss1d(onehot, 5, "circular"))
+    # overwrite mode never reads the old weights (NaN-poisoned buffer)
+    sel = torch.arange(5, device="cuda")
+    src = torch.rand(Tn, 5, generator=g).cuda()
+    out = ops.subpatch_merge(torch.full((Tn, G, P), float("nan"), device="cuda"), 0, G, sel, src, sigma=0, alpha=0.0, beta=1.0)
+    assert torch.equal(out[:, 1, :5], src) and float(out[:, :, 5:].abs().max()) == 0.0

@@ -53,3 +53,22 @@ def test_spline_latent_patch_decoder():
     assert rel_l2(dl @ R, g["dec_proj"]) < 2e-6
     for i, n in enumerate(dn):
         assert rel_l2(n[:, ::10], g[f"dec_noise_{i}"]) < 2e-6, i
+
+
+def test_product_sampler_equals_oracle_sampler_cpu_generator():
+    """ssar_b200's deferred Patch sampler (multinomial fast path restated as one exponential_ draw per choice) yields the
+    oracle's configs — which use the real Tensor.multinomial like patch.py:12-20 — value for value (CPU generator)."""
+    import torch
+    from ssar_b200.random.patch import Patch as ProductPatch
+    from ssar_oracle import traj
+
+    T = 64
+    dims = dict(chromagram=12, tonnetz=6, mfcc=20, spectral_contrast=7, rms=1, drop_strength=1, onsets=1, spectral_flatness=1)
+    feats = {k: torch.rand(T, c) for k, c in dims.items()}
+    segs = {(f, k): torch.randint(0, k, (T,)) for f in feats for k in (2, 4, 6, 8, 12, 16)}
+    for seed in range(40):
+        a, b = ProductPatch(feats, segs, 120.0, seed=seed, device="cpu"), traj.Patch(feats, segs, 120.0, seed=seed)
+        assert (a.num_base_latents, a.sigma_base_noise, a.loops_base_noise) == (b.num_base_latents, b.sigma_base_noise, b.loops_base_noise)
+        assert len(a.latent_patches) == len(b.latent_patches) and len(a.noise_patches) == len(b.noise_patches)
+        for x, y in zip(a.latent_patches + a.noise_patches, b.latent_patches + b.noise_patches):
+            assert all(x[k] == v for k, v in y.items())
