@@ -62,7 +62,12 @@ def onset_pair(x: torch.Tensor, sr, hop: int = 1024, n_fft: int = 2048, want_med
     return mean, med
 
 
-def audio2features_batch(audio: torch.Tensor, sr, fps, clamp=True, smooth=True, emphasis=False):
+def _check_peak_counts(cnt):
+    if int(cnt.min()) == 0:  # torch.quantile raises on a column without interior peaks (processing.py:117)
+        raise RuntimeError("quantile() input tensor must be non-empty")
+
+
+def audio2features_batch(audio: torch.Tensor, sr, fps, clamp=True, smooth=True, emphasis=False, deferred_checks=None):
     """supervised/data.py:60-107 for a batch of mono clips [B, N] at `sr` -> [B, T, 59].
 
     Same arithmetic per clip as the reference call sequence; work the reference repeats on identical inputs is done
@@ -118,8 +123,12 @@ def audio2features_batch(audio: torch.Tensor, sr, fps, clamp=True, smooth=True, 
         thr, cnt = ops.col_quantile(feats, (100 - 2.5) / 100, "peaks", "linear", want_count=True)
         feats = ops.clamp_cols(feats, None, thr)
         feats = ops.clamp_cols(feats, ops.col_quantile(feats, 4 * 2.5 / 100), None)
-        if int(cnt.min()) == 0:  # torch.quantile raises on a column without interior peaks (processing.py:117)
-            raise RuntimeError("quantile() input tensor must be non-empty")
+        # the reference raises when a column has no interior peak; reading the count back synchronises the stream, so a
+        # batched caller may collect the check and run it after it has queued the rest of its work
+        if deferred_checks is None:
+            _check_peak_counts(cnt)
+        else:
+            deferred_checks.append(lambda: _check_peak_counts(cnt))
     if smooth:
         feats = ops.gauss1d(feats, 0.1 * fps, "circular", batched=True)
     if emphasis:
@@ -194,29 +203,51 @@ def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, se
     workers: host threads building the per-clip patches (sampling + launches are independent per clip; torch releases
     the GIL inside its ops, so the generator draws of different clips overlap).  Every thread launches on the caller's
     current stream, so stream order with the feature kernels is kept."""
-    from .random.patch import Patch
+    from .random.patch import Patch, precapture_sampler_graphs
 
-    feats = audio2features_batch(audio, sr, fps)
-    B, T, _ = feats.shape
-    latents = torch.empty(B, T, palette.shape[1], palette.shape[2], dtype=torch.float32, device=feats.device)
-    pf_all = patch_features_batch(feats)
-    stream = torch.cuda.current_stream(feats.device)
-
-    # Patch sampling (patch.py:41-66) needs only the feature NAMES and shapes, and it synchronises a few times to read
-    # its draws back: run it on a side stream so those waits do not queue behind the feature kernels still running on
-    # the caller's stream (the host builds all the configs while the GPU computes the features).
-    def make(b):
-        with torch.cuda.device(feats.device), torch.cuda.stream(_side_stream(feats.device)):
-            return Patch({k: v[b] for k, v in pf_all.items()}, segmentations, tempo, fps=fps, seed=seed + b, device=rng_device)
-
-    def render(b, patch):
-        with torch.cuda.device(feats.device), torch.cuda.stream(stream):
-            return patch.forward(palette, downscale_factor=4, latents_out=latents[b])[1]
-
+    dev = audio.device
+    stream = torch.cuda.current_stream(dev)
+    if str(rng_device).startswith("cuda"):
+        with torch.cuda.device(dev):
+            precapture_sampler_graphs(dev, segmentations)  # no-op once captured
     workers = default_patch_workers(rng_device) if workers is None else int(workers)
+    checks = []
+
+    # 1) the feature kernels are queued by a helper thread: audio2features_batch blocks once on the clip tunings (the CQT
+    #    basis is data dependent) and torch releases the GIL while it waits, so this thread keeps working
+    def features_job():
+        with torch.cuda.device(dev), torch.cuda.stream(stream):
+            f = audio2features_batch(audio, sr, fps, deferred_checks=checks)
+            return f, patch_features_batch(f)
+
+    fut = _pool(max(workers, 1) + 1).submit(features_job)
+
+    # 2) meanwhile: patch sampling (patch.py:41-66) needs no feature values; it reads its draws back with a few stream
+    #    synchronisations, so it runs on a side stream where those waits do not queue behind the feature kernels
+    B = audio.shape[0]
+
+    def sample(b):
+        with torch.cuda.device(dev), torch.cuda.stream(_side_stream(dev)):
+            return Patch(None, segmentations, tempo, fps=fps, seed=seed + b, device=rng_device)
+
     if workers <= 1 or B == 1:
-        patches = [make(b) for b in range(B)]
-        noises = [render(b, p) for b, p in enumerate(patches)]
+        patches = [sample(b) for b in range(B)]
     else:
-        noises = list(_pool(workers).map(lambda b: render(b, make(b)), range(B)))
+        patches = list(_pool(workers + 1).map(sample, range(B)))
+    feats, pf_all = fut.result()
+    T = feats.shape[1]
+    latents = torch.empty(B, T, palette.shape[1], palette.shape[2], dtype=torch.float32, device=dev)
+
+    # 3) render: one fused launch per latent sub-patch + one mixing GEMM per clip, noise bases drawn per layer
+    def render(b):
+        with torch.cuda.device(dev), torch.cuda.stream(stream):
+            patches[b].bind({k: v[b] for k, v in pf_all.items()})
+            return patches[b].forward(palette, downscale_factor=4, latents_out=latents[b])[1]
+
+    if workers <= 1 or B == 1 or str(rng_device).startswith("cuda"):
+        noises = [render(b) for b in range(B)]
+    else:
+        noises = list(_pool(workers + 1).map(render, range(B)))
+    for check in checks:  # error behaviour of the reference (empty peak set), read back once everything is queued
+        check()
     return feats, latents, noises

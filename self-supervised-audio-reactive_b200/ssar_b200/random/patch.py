@@ -49,10 +49,10 @@ class _Sampler:
     values on the generator's device and converts them to Python objects with one device-to-host copy at the end
     (a CUDA generator otherwise costs one stream synchronisation per draw: ~400 per Patch)."""
 
-    def __init__(self, rng):
+    def __init__(self, rng, caches=None):
         self.rng = rng
         self.floats, self._n_floats = [], 0
-        self._uniform, self._weighted, self._host_probs = {}, {}, {}
+        self._uniform, self._weighted, self._host_probs = caches if caches is not None else ({}, {}, {})
 
     def _probs(self, n_options, weights):
         if weights is None:
@@ -89,8 +89,14 @@ class _Sampler:
         self._n_floats += 2
         return _Deferred("skewnorm", self._n_floats - 2, (a, loc, scale))
 
-    def resolve(self, tree):
-        floats = torch.cat(self.floats).cpu().numpy() if self.floats else None
+    def flat(self):
+        """All draws so far as one fp32 vector on the generator's device (slot order)."""
+        return torch.cat(self.floats)
+
+    def resolve(self, tree, floats=None):
+        """tree of `_Deferred` -> Python values; floats: host copy of `flat()` (fetched here when None)."""
+        if floats is None:
+            floats = self.flat().cpu().numpy() if self.floats else None
         f = np.float32
 
         def host_probs(p, weights):
@@ -126,6 +132,147 @@ class _Sampler:
         return walk(tree)
 
 
+DEPTHS = ["low", "mid", "high", "lowmid", "midhigh", "all"]
+
+
+def _latent_config(choice, skew, ks):
+    """patch.py:77-91 (draw order is part of the result)."""
+    return dict(
+        patch_type=choice(["segmentation", "feature", "loop"]),
+        segments=choice(ks),
+        loop_bars=choice([4, 8, 16, 32], weights=[2, 2, 2, 1]),
+        seq_feat=choice(ALLFEATS),
+        seq_feat_weight=skew(5, 0.666, 0.5),
+        mod_feat=choice(UNITFEATS),
+        mod_feat_weight=skew(5, 0.666, 0.5),
+        merge_type=choice(["average", "modulate"], weights=[1, 3]),
+        merge_depth=choice(DEPTHS, weights=[3, 3, 3, 2, 2, 1]),
+    )
+
+
+def _noise_config(choice, skew, randn):
+    """patch.py:93-106 (draw order is part of the result)."""
+    return dict(
+        patch_type=choice(["blend", "multiply", "loop"]),
+        loop_bars=choice([4, 8, 16, 32], weights=[2, 2, 2, 1]),
+        seq_feat=choice(ALLFEATS),
+        seq_feat_weight=skew(5, 0.666, 0.5),
+        mod_feat=choice(UNITFEATS),
+        mod_feat_weight=skew(5, 0.666, 0.5),
+        merge_type=choice(["average", "modulate"], weights=[1, 3]),
+        merge_depth=choice(DEPTHS, weights=[3, 3, 3, 2, 2, 1]),
+        noise_mean=randn(0.5),
+        noise_std=skew(5, 0.666, 0.5),
+    )
+
+
+class _GraphSampler:
+    """CUDA-generator fast path of the Patch sampler.  The draws of n consecutive latent (or noise) sub-patch configs are
+    a fixed sequence of ~11 n (14 n) tiny generator kernels; they are captured ONCE per n as a CUDA graph whose Philox
+    seed / offset are re-read from the generator at every replay (`CUDAGraph.register_generator_state`), so a replay
+    issues exactly the draws the eager sequence would issue from the generator's current state — one graph launch instead
+    of ~250 kernel launches + ~500 Python-level torch calls per Patch.  One shared generator per device is re-seeded per
+    Patch; the Patch's own generator is then set to the shared generator's final state."""
+
+    _instances = {}
+    _guard = __import__("threading").Lock()
+
+    @classmethod
+    def get(cls, device):
+        device = torch.device(device)
+        idx = device.index if device.index is not None else torch.cuda.current_device()
+        with cls._guard:
+            inst = cls._instances.get(idx)
+            if inst is None:
+                inst = cls._instances[idx] = cls(torch.device("cuda", idx))
+            return inst
+
+    def __init__(self, device):
+        self.device = device
+        self.rng = torch.Generator(device)
+        self.lock = __import__("threading").RLock()
+        self.caches = ({}, {}, {})
+        self.blocks = {}
+        self.capture_stream = None
+
+    def _build(self, kind, n, ks):
+        sm = _Sampler(self.rng, self.caches)
+        if kind == "latent":
+            tree = [_latent_config(sm.choice, sm.skewnorm, ks) for _ in range(n)]
+        else:
+            tree = [_noise_config(sm.choice, sm.skewnorm, sm.randn) for _ in range(n)]
+        return sm, tree, sm.flat()
+
+    def block(self, kind, n, ks):
+        """(graph, static flat output, deferred tree, sampler) for n consecutive configs; captured on first use with the
+        generator state preserved."""
+        key = (kind, int(n), tuple(ks))
+        blk = self.blocks.get(key)
+        if blk is None:
+            if n == 0:
+                blk = self.blocks[key] = (None, None, [], None)
+                return blk
+            state = self.rng.get_state()
+            if self.capture_stream is None:
+                self.capture_stream = torch.cuda.Stream(self.device)
+            cs = self.capture_stream
+            cs.wait_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(cs):
+                self._build(kind, n, ks)  # eager warm-up: fills the probability-tensor caches outside the graph
+            cs.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            graph.register_generator_state(self.rng)
+            with torch.cuda.graph(graph, stream=cs, capture_error_mode="thread_local"):
+                sm, tree, flat = self._build(kind, n, ks)
+            self.rng.set_state(state)
+            blk = self.blocks[key] = (graph, flat, tree, sm)
+        return blk
+
+    def sample(self, seed, ks, min_subpatches, max_subpatches):
+        """patch.py:41-66 -> (num_base_latents, sigma_base_noise, loops_base_noise, latent configs, noise configs, final
+        generator state)."""
+        rng, dev = self.rng, self.device
+        with self.lock:
+            rng.manual_seed(seed)
+            num_base = torch.randint(3, 15, size=(), generator=rng, device=dev)
+            sigma_u = torch.rand((), generator=rng, device=dev)
+            head = _Sampler(rng, self.caches)
+            loops = head.choice([1, 2, 4, 8, 16, 32, 64])
+            n_lat = int(torch.randint(min_subpatches, max_subpatches, size=(), generator=rng, device=dev))
+            g_l, flat_l, tree_l, sm_l = self.block("latent", n_lat, ks)
+            if g_l is not None:
+                g_l.replay()
+            n_noi = int(torch.randint(min_subpatches, max_subpatches, size=(), generator=rng, device=dev))
+            g_n, flat_n, tree_n, sm_n = self.block("noise", n_noi, ks)
+            if g_n is not None:
+                g_n.replay()
+            parts = [head.flat(), num_base.float().reshape(1), sigma_u.reshape(1)]
+            parts += [t for t in (flat_l, flat_n) if t is not None]
+            host = torch.cat(parts).cpu().numpy()  # the one bulk copy (static graph outputs are read before the next replay)
+            state = rng.get_state()
+        n_head = head._n_floats
+        o = n_head + 2
+        loops_v = head.resolve(loops, host[:n_head])
+        lat = sm_l.resolve(tree_l, host[o : o + flat_l.numel()]) if flat_l is not None else []
+        o += flat_l.numel() if flat_l is not None else 0
+        noi = sm_n.resolve(tree_n, host[o : o + flat_n.numel()]) if flat_n is not None else []
+        return int(host[n_head]), 1 + 9 * float(host[n_head + 1]), loops_v, lat, noi, state
+
+
+USE_SAMPLER_GRAPHS = True  # CUDA generators only; False = the eager deferred sampler
+
+
+def precapture_sampler_graphs(device, segmentations, min_subpatches=5, max_subpatches=20):
+    """Captures every sampler graph a Patch on `device` can need (one per sub-patch count) — call before starting other
+    host threads that launch CUDA work, so no capture happens while they run."""
+    gs = _GraphSampler.get(device)
+    ks = np.unique([k for (_, k) in segmentations]).tolist()
+    with gs.lock:
+        for n in range(min_subpatches, max_subpatches):
+            gs.block("latent", n, ks)
+            gs.block("noise", n, ks)
+
+
 class Patch:
     """patch.py:35-175.  `device`: where the generator lives (as in the reference); `compute_device`: where the
     trajectory tensors live (defaults to the palette's device at forward time)."""
@@ -138,14 +285,20 @@ class Patch:
         self.rng = rng
         self.fps = fps
         self.tempo = tempo
-        self.length = features[list(features.keys())[0]].shape[0]
         self.features = features
+        self.length = features[list(features.keys())[0]].shape[0] if features is not None else None
         self.segmentations = segmentations
+        self.ks = np.unique([k for (_, k) in segmentations]).tolist()
+        if rng.device.type == "cuda" and USE_SAMPLER_GRAPHS:
+            (self.num_base_latents, self.sigma_base_noise, self.loops_base_noise, self.latent_patches, self.noise_patches,
+             state) = _GraphSampler.get(rng.device).sample(seed, self.ks, min_subpatches, max_subpatches)
+            rng.set_state(state)
+            self._sampler = None
+            return
         sm = self._sampler = _Sampler(rng)
         num_base_latents = torch.randint(3, 15, size=(), generator=rng, device=rng.device)
         sigma_u = torch.rand((), generator=rng, device=rng.device)
         loops_base_noise = sm.choice([1, 2, 4, 8, 16, 32, 64])
-        self.ks = np.unique([k for (_, k) in segmentations]).tolist()
         latent_patches = [
             self.random_latent_patch()
             for _ in range(torch.randint(min_subpatches, max_subpatches, size=(), generator=rng, device=rng.device))
@@ -159,6 +312,13 @@ class Patch:
         self.num_base_latents = num_base_latents.item()
         self.sigma_base_noise = 1 + 9 * sigma_u.item()
         self._sampler = None
+
+    def bind(self, features):
+        """Attach the feature dict of a patch sampled with features=None (batched pipelines sample the configs — which
+        need no feature values — while the GPU is still computing the features)."""
+        self.features = features
+        self.length = features[list(features.keys())[0]].shape[0]
+        return self
 
     def update_intensity(self, val):
         """patch.py:68-75 (including the write of noise_std into latent_patches[p], as in the reference)."""
@@ -183,33 +343,12 @@ class Patch:
     def random_latent_patch(self):
         """patch.py:77-91 (same draws in the same order)."""
         choice, skew, _ = self._draws()
-        return dict(
-            patch_type=choice(["segmentation", "feature", "loop"]),
-            segments=choice(self.ks),
-            loop_bars=choice([4, 8, 16, 32], weights=[2, 2, 2, 1]),
-            seq_feat=choice(ALLFEATS),
-            seq_feat_weight=skew(5, 0.666, 0.5),
-            mod_feat=choice(UNITFEATS),
-            mod_feat_weight=skew(5, 0.666, 0.5),
-            merge_type=choice(["average", "modulate"], weights=[1, 3]),
-            merge_depth=choice(["low", "mid", "high", "lowmid", "midhigh", "all"], weights=[3, 3, 3, 2, 2, 1]),
-        )
+        return _latent_config(choice, skew, self.ks)
 
     def random_noise_patch(self):
         """patch.py:93-106 (same draws in the same order)."""
         choice, skew, randn = self._draws()
-        return dict(
-            patch_type=choice(["blend", "multiply", "loop"]),
-            loop_bars=choice([4, 8, 16, 32], weights=[2, 2, 2, 1]),
-            seq_feat=choice(ALLFEATS),
-            seq_feat_weight=skew(5, 0.666, 0.5),
-            mod_feat=choice(UNITFEATS),
-            mod_feat_weight=skew(5, 0.666, 0.5),
-            merge_type=choice(["average", "modulate"], weights=[1, 3]),
-            merge_depth=choice(["low", "mid", "high", "lowmid", "midhigh", "all"], weights=[3, 3, 3, 2, 2, 1]),
-            noise_mean=randn(0.5),
-            noise_std=skew(5, 0.666, 0.5),
-        )
+        return _noise_config(choice, skew, randn)
 
     def forward(self, latent_palette, downscale_factor=1, aspect_ratio=1, latents_out=None):
         """patch.py:108-133 -> (latents [T, 18, 512], list of 17 lazy noise modules).

@@ -131,7 +131,7 @@ def _eager_configs(features, segmentations, seed, device, min_subpatches=5, max_
         d["noise_mean"] = torch.randn((), generator=rng, device=rng.device).item() * 0.5
         d["noise_std"] = skewnorm(rng, a=5, loc=0.666, scale=0.5).item()
         noi.append(d)
-    return head, lat, noi
+    return head, lat, noi, rng.get_state()
 
 
 def test_deferred_sampler_equals_eager_draws_cuda_generator():
@@ -139,12 +139,20 @@ def test_deferred_sampler_equals_eager_draws_cuda_generator():
     multinomial / skewnorm draws of patch.py:12-32 on a CUDA (Philox) generator value for value."""
     from ssar_b200.random.patch import Patch
 
+    from ssar_b200.random import patch as patch_mod
+
     feats, segs, _ = synth_patch_inputs(64, 0)
-    for seed in range(12):
-        p = Patch(feats, segs, 120.0, seed=seed, device="cuda")
-        head, lat, noi = _eager_configs(feats, segs, seed, "cuda")
-        assert [p.num_base_latents, p.sigma_base_noise, p.loops_base_noise] == head
-        assert p.latent_patches == lat and p.noise_patches == noi
+    for graphs in (True, False):  # CUDA-graph replay of the draw sequence / eager deferred draws
+        patch_mod.USE_SAMPLER_GRAPHS = graphs
+        try:
+            for seed in range(12):
+                p = Patch(feats, segs, 120.0, seed=seed, device="cuda")
+                head, lat, noi, state = _eager_configs(feats, segs, seed, "cuda")
+                assert [p.num_base_latents, p.sigma_base_noise, p.loops_base_noise] == head, (graphs, seed)
+                assert p.latent_patches == lat and p.noise_patches == noi, (graphs, seed)
+                assert torch.equal(p.rng.get_state(), state), (graphs, seed)  # later draws continue identically
+        finally:
+            patch_mod.USE_SAMPLER_GRAPHS = True
 
 
 def test_subpatch_kernel_vs_separate_steps():
