@@ -1,52 +1,69 @@
 // Framed, windowed real FFT with fused epilogues (power/magnitude spectrum, complex spectrum, banded real
 // filterbanks such as mel, banded complex projections such as the CQT basis, RMS, spectral flatness).
 //
-// One launch covers every clip of a batch.  A CTA of 256 threads owns FPB = 256/TPF frames at a time and walks
-// the (clip, frame) list persistently; consecutive frames of one clip land in the same / neighbouring CTAs, so
-// the 4x (hop 512) or 2x (hop 1024) overlapped waveform reads are served by L1/L2 and HBM sees each sample once.
-// The spectrum of a frame lives only in shared memory: |X|^2 -> filterbanks happen before anything is written,
-// so the [frames, 1025] spectrogram never round-trips HBM unless the caller asks for it as an output.
-#include "fft_core.cuh"
+// v1: ONE WARP PER FRAME (two frames per warp for n_fft 1024).  Every lane holds 32 complex points in registers and the
+// 1024-point (512-point) complex transform of the packed real frame is two register-resident radix-32 (radix-32 + 2 x
+// radix-16) passes around one warp-private shared-memory transpose (fft_warp.cuh) — the frame loop has no
+// __syncthreads, only __syncwarp.  One launch covers every clip of a batch; warps walk the (clip, frame) list
+// persistently with neighbouring warps on neighbouring frames, so the 2x-4x overlapped waveform reads are served by
+// L1/L2 and HBM sees each sample once.  The spectrum of a frame lives only in shared memory: |X|^2 -> filterbanks happen
+// before anything is written, so the [frames, 1025] spectrogram never round-trips HBM unless it is a requested output.
+#include "fft_warp.cuh"
 
 namespace {
 
 template <int M>
-struct FramesSmem {
-    static constexpr int TPF = FftShape<M>::TPF;
-    static constexpr int FPB = 256 / TPF;
-    static constexpr int ZLEN = fft_padded_len(M);        // float2 per frame group
-    static constexpr int PLEN = ((M + 1 + 3) / 4) * 4;    // floats per frame group
-    static constexpr size_t bytes = (size_t)FPB * ZLEN * sizeof(float2) + (size_t)FPB * PLEN * sizeof(float) +
-                                    (size_t)FPB * 8 * sizeof(float);
+struct WarpFft {
+    static constexpr int N1 = (M == 1024) ? 32 : 16;   // lanes per frame (n1)
+    static constexpr int FPW = 32 / N1;                // frames per warp
+    static constexpr int TLD = N1 + 1;                 // padded row of the [k2][n1] transpose tile (float2)
+    static constexpr int ZF = 32 * TLD;                // float2 per frame buffer (>= M + 1)
+    static constexpr int WPB = 8;                      // warps per CTA
+    static constexpr int NJ = M / 32 + 1;              // spectrum bins per lane (k = lane + 32 j), last one only lane 0
+    static_assert(ZF >= M + 1, "frame buffer must hold M + 1 bins");
+    static size_t smem_bytes(bool window, bool separate_power) {
+        size_t b = (size_t)32 * N1 * sizeof(float2);                  // twiddle table [k2][n1]
+        if (window) b += (size_t)2 * M * sizeof(float);
+        b += (size_t)WPB * FPW * ZF * sizeof(float2);
+        if (separate_power) b += (size_t)WPB * FPW * (M + 4) * sizeof(float);
+        return b;
+    }
 };
 
 template <int M>
-__global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_args a, const long long total_frames) {
-    using L = FramesSmem<M>;
-    constexpr int TPF = L::TPF, FPB = L::FPB, N = 2 * M, NBINS = M + 1;
-    constexpr int WPF = TPF / 32;  // warps per frame group
+__global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_args a, const long long total_frames,
+                                                            const int separate_power) {
+    using L = WarpFft<M>;
+    constexpr int N1 = L::N1, FPW = L::FPW, TLD = L::TLD, ZF = L::ZF, N = 2 * M, NBINS = M + 1, NJ = L::NJ;
     extern __shared__ float4 smem_raw[];
-    float2* zall = reinterpret_cast<float2*>(smem_raw);
-    float* pall = reinterpret_cast<float*>(zall + FPB * L::ZLEN);
-    float* redall = pall + FPB * L::PLEN;
+    float2* twT = reinterpret_cast<float2*>(smem_raw);                 // [32][N1]: W_M^{n1 k2}
+    float* wins = reinterpret_cast<float*>(twT + 32 * N1);             // [2M] or absent
+    float2* zall = reinterpret_cast<float2*>(wins + (a.window ? N : 0));
+    float* pall = reinterpret_cast<float*>(zall + L::WPB * FPW * ZF);  // only with separate_power
 
-    const int g = threadIdx.x / TPF, lt = threadIdx.x % TPF;
-    const int wig = lt >> 5;  // warp index inside the frame group
-    float2* s = zall + g * L::ZLEN;
-    float* pw = pall + g * L::PLEN;
-    float* red = redall + g * 8;
-    const float2* __restrict__ tw = reinterpret_cast<const float2*>(a.twiddle);
-    const float* __restrict__ win = a.window;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int h = lane / N1, n1 = lane % N1;  // frame slot inside the warp, point index inside the frame
+    const float2* __restrict__ tw = reinterpret_cast<const float2*>(a.twiddle);  // exp(-2 pi i k / 2M), k in [0, 2M)
+
+    for (int i = threadIdx.x; i < 32 * N1; i += blockDim.x) {
+        const int k2 = i / N1, nn = i - k2 * N1;
+        twT[i] = __ldg(&tw[2 * nn * k2]);
+    }
+    if (a.window)
+        for (int i = threadIdx.x; i < N; i += blockDim.x) wins[i] = __ldg(a.window + i);
+    __syncthreads();
+
+    float2* zw = zall + (size_t)warp * FPW * ZF;  // this warp's frame buffers
     const bool need_pw = a.out_spec || a.out_flatness || a.fb[0].n_bands > 0 || a.fb[1].n_bands > 0;
 
-    for (long long base = (long long)blockIdx.x * FPB; base < total_frames; base += (long long)gridDim.x * FPB) {
-        const long long f = base + g;
+    for (long long fbase = ((long long)blockIdx.x * L::WPB + warp) * FPW; fbase < total_frames;
+         fbase += (long long)gridDim.x * L::WPB * FPW) {
+        // ------------------------------------------------------------------ load + window (lane: n = n1 + N1 r)
+        const long long f = fbase + h;
         const bool active = f < total_frames;
         const int clip = active ? (int)(f / a.n_frames) : 0;
         const int t = active ? (int)(f - (long long)clip * a.n_frames) : 0;
-
-        // ---- pass 1 (radix 16, Ns = 1): the 16 inputs of butterfly `lt` come straight from global memory
-        float2 v[16];
+        float2 v[32];
         float ss = 0.f;
         if (active) {
             const float* __restrict__ xc = a.x + (long long)clip * a.clip_stride;
@@ -54,162 +71,226 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
             const bool interior = start >= 0 && start + N <= a.n_samples;
             const bool vec = interior && ((((long long)clip * a.clip_stride + start) & 1LL) == 0) &&
                              ((reinterpret_cast<uintptr_t>(a.x) & 7) == 0);
+            if (vec) {
+                const float2* __restrict__ xp = reinterpret_cast<const float2*>(xc + start);
 #pragma unroll
-            for (int r = 0; r < 16; ++r) {
-                const int n = lt + r * (M / 16);
-                float x0, x1;
-                if (vec) {
-                    const float2 p = __ldg(reinterpret_cast<const float2*>(xc + start) + n);
-                    x0 = p.x;
-                    x1 = p.y;
-                } else if (interior) {
-                    x0 = __ldg(xc + start + 2 * n);
-                    x1 = __ldg(xc + start + 2 * n + 1);
-                } else {
-                    x0 = __ldg(xc + ssar_reflect(start + 2 * n, a.n_samples));
-                    x1 = __ldg(xc + ssar_reflect(start + 2 * n + 1, a.n_samples));
+                for (int r = 0; r < 32; ++r) v[r] = __ldg(xp + n1 + N1 * r);
+            } else if (interior) {
+#pragma unroll
+                for (int r = 0; r < 32; ++r) {
+                    const int n = n1 + N1 * r;
+                    v[r] = make_float2(__ldg(xc + start + 2 * n), __ldg(xc + start + 2 * n + 1));
                 }
-                ss = fmaf(x0, x0, ss);
-                ss = fmaf(x1, x1, ss);
-                if (win) {
-                    const float2 w = __ldg(reinterpret_cast<const float2*>(win) + n);
-                    x0 *= w.x;
-                    x1 *= w.y;
+            } else {
+#pragma unroll
+                for (int r = 0; r < 32; ++r) {
+                    const int n = n1 + N1 * r;
+                    v[r] = make_float2(__ldg(xc + ssar_reflect(start + 2 * n, a.n_samples)),
+                                       __ldg(xc + ssar_reflect(start + 2 * n + 1, a.n_samples)));
                 }
-                v[r] = make_float2(x0, x1);
+            }
+            if (a.out_rms) {
+#pragma unroll
+                for (int r = 0; r < 32; ++r) {
+                    ss = fmaf(v[r].x, v[r].x, ss);
+                    ss = fmaf(v[r].y, v[r].y, ss);
+                }
+            }
+            if (a.window) {
+                const float2* wp = reinterpret_cast<const float2*>(wins);
+#pragma unroll
+                for (int r = 0; r < 32; ++r) {
+                    const float2 w = wp[n1 + N1 * r];
+                    v[r].x *= w.x;
+                    v[r].y *= w.y;
+                }
             }
         } else {
 #pragma unroll
-            for (int r = 0; r < 16; ++r) v[r] = make_float2(0.f, 0.f);
+            for (int r = 0; r < 32; ++r) v[r] = make_float2(0.f, 0.f);
         }
-        stockham_finish<M, 16>(v, s, tw, lt, 1);
-        __syncthreads();
-        fft_tail_passes<M>(s, tw, lt);
 
-        // ---- untangle the packed real transform: X[k] = E + w^k O, X[M-k] = conj(E - w^k O)
-        for (int k = lt; k <= M / 2; k += TPF) {
-            const float2 zk = s[PADI(k)];
-            const float2 zm = s[PADI(k == 0 ? 0 : M - k)];
-            const float2 w = __ldg(&tw[k]);
-            const float2 e = make_float2(0.5f * (zk.x + zm.x), 0.5f * (zk.y - zm.y));
-            const float2 d = make_float2(zk.x - zm.x, zk.y + zm.y);
-            const float2 o = make_float2(0.5f * d.y, -0.5f * d.x);
-            const float2 wo = cmul(w, o);
-            s[PADI(k)] = cadd(e, wo);
-            s[PADI(M - k)] = cconj(csub(e, wo));
-        }
-        __syncthreads();
-
-        // ---- epilogue 1: complex / power / magnitude outputs, power tile for the filterbanks, flatness sums
-        float slog = 0.f, slin = 0.f;
+        // ------------------------------------------------------------------ pass 1: 32-point DFT over n2, twiddle, transpose
+        fft_dif_regs<32, false>(v);
         {
-            float2* oc = (active && a.out_complex)
-                             ? reinterpret_cast<float2*>(a.out_complex) + ((long long)clip * a.n_frames + t) * a.ldc
-                             : nullptr;
-            float* os = (active && a.out_spec) ? a.out_spec + ((long long)clip * a.n_frames + t) * a.lds : nullptr;
-            for (int k = lt; k < NBINS; k += TPF) {
-                const float2 X = s[PADI(k)];
-                if (oc) oc[k] = X;
-                if (need_pw) {
-                    const float p = fmaf(X.x, X.x, X.y * X.y);
-                    pw[k] = p;
-                    if (os) os[k] = (a.spec_power == 2) ? p : sqrtf(p);
-                    if (a.out_flatness) {
-                        const float pt = fmaxf(1e-10f, p);
-                        slog += logf(pt);
-                        slin += pt;
+            float2* tile = zw + h * ZF;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const int k2 = bitrev_const(i, 5);
+                float2 y = v[i];
+                if (k2 != 0) y = cmul(y, twT[k2 * N1 + n1]);
+                tile[k2 * TLD + n1] = y;
+            }
+        }
+        __syncwarp();
+
+        // ------------------------------------------------------------------ pass 2: DFT over n1, natural-order store
+        if constexpr (M == 1024) {
+            float2* tile = zw;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = tile[lane * TLD + i];
+            fft_dif_regs<32, false>(v);
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) tile[32 * bitrev_const(i, 5) + lane] = v[i];
+        } else {
+            float2* tile = zw + h * ZF;
+            float2 u0[16], u1[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                u0[i] = tile[n1 * TLD + i];
+                u1[i] = tile[(n1 + 16) * TLD + i];
+            }
+            fft_dif_regs<16, false>(u0);
+            fft_dif_regs<16, false>(u1);
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                tile[32 * bitrev_const(i, 4) + n1] = u0[i];
+                tile[32 * bitrev_const(i, 4) + n1 + 16] = u1[i];
+            }
+        }
+        __syncwarp();
+
+        // rms: sum of squares over the N1 lanes of each frame
+        if (a.out_rms) {
+#pragma unroll
+            for (int o = N1 / 2; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+            if (active && n1 == 0) a.out_rms[(long long)clip * a.n_frames + t] = sqrtf(ss / (float)N);
+        }
+
+        // ------------------------------------------------------------------ per frame: untangle + epilogues, 32 lanes wide
+#pragma unroll 1
+        for (int fs = 0; fs < FPW; ++fs) {
+            const long long ff = fbase + fs;
+            if (ff >= total_frames) break;  // warp-uniform
+            const int fclip = (int)(ff / a.n_frames);
+            const int ft = (int)(ff - (long long)fclip * a.n_frames);
+            const long long orow = (long long)fclip * a.n_frames + ft;
+            float2* z = zw + fs * ZF;
+
+            // untangle the packed real transform in place: X[k] = E + w^k O, X[M-k] = conj(E - w^k O)
+            for (int k = lane; k <= M / 2; k += 32) {
+                const float2 zk = z[k];
+                const float2 zm = z[k == 0 ? 0 : M - k];
+                const float2 w = __ldg(&tw[k]);
+                const float2 e = make_float2(0.5f * (zk.x + zm.x), 0.5f * (zk.y - zm.y));
+                const float2 d = make_float2(zk.x - zm.x, zk.y + zm.y);
+                const float2 o = make_float2(0.5f * d.y, -0.5f * d.x);
+                const float2 wo = cmul(w, o);
+                z[k] = cadd(e, wo);
+                z[M - k] = cconj(csub(e, wo));
+            }
+            __syncwarp();
+
+            // epilogue 1: complex / power / magnitude outputs, flatness sums; the power tile goes to shared memory
+            float* pw = separate_power ? pall + (size_t)(warp * FPW + fs) * (M + 4) : reinterpret_cast<float*>(z);
+            if (a.out_complex || need_pw) {
+                float2* oc = a.out_complex ? reinterpret_cast<float2*>(a.out_complex) + orow * a.ldc : nullptr;
+                float* os = a.out_spec ? a.out_spec + orow * a.lds : nullptr;
+                float pj[NJ];
+                float slog = 0.f, slin = 0.f;
+#pragma unroll
+                for (int j = 0; j < NJ; ++j) {
+                    const int k = lane + 32 * j;
+                    pj[j] = 0.f;
+                    if (k < NBINS) {
+                        const float2 X = z[k];
+                        if (oc) oc[k] = X;
+                        const float p = fmaf(X.x, X.x, X.y * X.y);
+                        pj[j] = p;
+                        if (os) os[k] = (a.spec_power == 2) ? p : sqrtf(p);
+                        if (a.out_flatness) {
+                            const float pt = fmaxf(1e-10f, p);
+                            slog += logf(pt);
+                            slin += pt;
+                        }
                     }
                 }
-            }
-        }
-        // group reductions (rms, flatness) through a tiny smem scratch
-        ss = warp_sum(ss);
-        slog = warp_sum(slog);
-        slin = warp_sum(slin);
-        if ((lt & 31) == 0) {
-            red[wig] = ss;
-            red[2 + wig] = slog;
-            red[4 + wig] = slin;
-        }
-        __syncthreads();
-        if (active && lt == 0) {
-            float r0 = red[0], r1 = red[2], r2 = red[4];
-            if (WPF == 2) {
-                r0 += red[1];
-                r1 += red[3];
-                r2 += red[5];
-            }
-            const long long o = (long long)clip * a.n_frames + t;
-            if (a.out_rms) a.out_rms[o] = sqrtf(r0 / (float)N);
-            if (a.out_flatness) a.out_flatness[o] = expf(r1 / (float)NBINS) / (r2 / (float)NBINS);
-        }
-
-        // ---- epilogue 2: banded real filterbanks on the shared power tile
+                if (a.out_flatness) {
+                    slog = warp_sum(slog);
+                    slin = warp_sum(slin);
+                    if (lane == 0) a.out_flatness[orow] = expf(slog / (float)NBINS) / (slin / (float)NBINS);
+                }
+                if (a.fb[0].n_bands > 0 || a.fb[1].n_bands > 0) {
+                    if (!separate_power) __syncwarp();  // every lane has read its bins: the tile may be overwritten
 #pragma unroll
-        for (int q = 0; q < 2; ++q) {
-            const ssar_filterbank& fb = a.fb[q];
-            if (fb.n_bands <= 0) continue;
-            float bmax = -INFINITY;
-            for (int b = lt; b < fb.n_bands; b += TPF) {
-                const int st = __ldg(fb.start + b), cn = __ldg(fb.count + b);
-                const float* __restrict__ w = fb.weights + __ldg(fb.offset + b);
-                float acc = 0.f;
-                if (fb.on_power) {
-                    for (int k = 0; k < cn; ++k) acc = fmaf(__ldg(w + k), pw[st + k], acc);
-                } else {
-                    for (int k = 0; k < cn; ++k) acc = fmaf(__ldg(w + k), sqrtf(pw[st + k]), acc);
+                    for (int j = 0; j < NJ; ++j) {
+                        const int k = lane + 32 * j;
+                        if (k < NBINS) pw[k] = pj[j];
+                    }
+                    __syncwarp();
                 }
-                if (active) fb.out[((long long)clip * a.n_frames + t) * fb.ld + b] = acc;
-                bmax = fmaxf(bmax, acc);
             }
-            if (fb.max_key) {
-                bmax = warp_max(bmax);
-                if (active && (lt & 31) == 0) atomic_max_key(fb.max_key + clip, bmax);
-            }
-        }
 
-        // ---- epilogue 3: banded complex projection of the complex spectrum (CQT basis)
-        if (a.proj.n_rows > 0) {
-            const ssar_projection& pj = a.proj;
-            const int slot = (pj.clip_slot && active) ? __ldg(pj.clip_slot + clip) : 0;
-            const int rb = slot * pj.n_rows;
-            for (int r = lt; r < pj.n_rows; r += TPF) {
-                const int st = __ldg(pj.start + rb + r), cn = __ldg(pj.count + rb + r);
-                const float2* __restrict__ w = reinterpret_cast<const float2*>(pj.weights) + __ldg(pj.offset + rb + r);
-                float2 acc = make_float2(0.f, 0.f);
-                for (int k = 0; k < cn; ++k) {
-                    const float2 wk = __ldg(w + k);
-                    const float2 X = s[PADI(st + k)];
-                    acc.x = fmaf(wk.x, X.x, acc.x);
-                    acc.x = fmaf(-wk.y, X.y, acc.x);
-                    acc.y = fmaf(wk.x, X.y, acc.y);
-                    acc.y = fmaf(wk.y, X.x, acc.y);
+            // epilogue 2: banded real filterbanks on the shared power tile
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const ssar_filterbank& fb = a.fb[q];
+                if (fb.n_bands <= 0) continue;
+                float bmax = -INFINITY;
+                for (int b = lane; b < fb.n_bands; b += 32) {
+                    const int st = __ldg(fb.start + b), cn = __ldg(fb.count + b);
+                    const float* __restrict__ w = fb.weights + __ldg(fb.offset + b);
+                    float acc = 0.f;
+                    if (fb.on_power) {
+                        for (int k = 0; k < cn; ++k) acc = fmaf(__ldg(w + k), pw[st + k], acc);
+                    } else {
+                        for (int k = 0; k < cn; ++k) acc = fmaf(__ldg(w + k), sqrtf(pw[st + k]), acc);
+                    }
+                    fb.out[orow * fb.ld + b] = acc;
+                    bmax = fmaxf(bmax, acc);
                 }
-                const float sc = pj.row_scale ? pj.scale * __ldg(pj.row_scale + slot * pj.row_scale_ld + r) : pj.scale;
-                if (active)
-                    reinterpret_cast<float2*>(pj.out)[((long long)clip * a.n_frames + t) * pj.ld + r] =
-                        make_float2(acc.x * sc, acc.y * sc);
+                if (fb.max_key) {
+                    bmax = warp_max(bmax);
+                    if (lane == 0) atomic_max_key(fb.max_key + fclip, bmax);
+                }
+            }
+
+            // epilogue 3: banded complex projection of the complex spectrum (CQT basis); needs z intact
+            if (a.proj.n_rows > 0) {
+                const ssar_projection& pjn = a.proj;
+                const int slot = pjn.clip_slot ? __ldg(pjn.clip_slot + fclip) : 0;
+                const int rb = slot * pjn.n_rows;
+                for (int r = lane; r < pjn.n_rows; r += 32) {
+                    const int st = __ldg(pjn.start + rb + r), cn = __ldg(pjn.count + rb + r);
+                    const float2* __restrict__ w = reinterpret_cast<const float2*>(pjn.weights) + __ldg(pjn.offset + rb + r);
+                    float2 acc = make_float2(0.f, 0.f);
+                    for (int k = 0; k < cn; ++k) {
+                        const float2 wk = __ldg(w + k);
+                        const float2 X = z[st + k];
+                        acc.x = fmaf(wk.x, X.x, acc.x);
+                        acc.x = fmaf(-wk.y, X.y, acc.x);
+                        acc.y = fmaf(wk.x, X.y, acc.y);
+                        acc.y = fmaf(wk.y, X.x, acc.y);
+                    }
+                    const float sc = pjn.row_scale ? pjn.scale * __ldg(pjn.row_scale + slot * pjn.row_scale_ld + r) : pjn.scale;
+                    reinterpret_cast<float2*>(pjn.out)[orow * pjn.ld + r] = make_float2(acc.x * sc, acc.y * sc);
+                }
             }
         }
-        __syncthreads();  // the next iteration overwrites s / pw / red
+        __syncwarp();  // the next iteration overwrites the frame buffers
     }
 }
 
 template <int M>
 int launch_frames(const ssar_frames_args& a, cudaStream_t st) {
-    using L = FramesSmem<M>;
+    using L = WarpFft<M>;
     const long long total = (long long)a.n_clips * a.n_frames;
     if (total == 0) return SSAR_OK;
-    cudaError_t e = cudaFuncSetAttribute(frames_fft_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::bytes);
+    const bool banks = a.fb[0].n_bands > 0 || a.fb[1].n_bands > 0;
+    const int separate_power = (banks && a.proj.n_rows > 0) ? 1 : 0;  // the projection needs the complex tile intact
+    const size_t smem = L::smem_bytes(a.window != nullptr, separate_power != 0);
+    cudaError_t e = cudaFuncSetAttribute(frames_fft_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) {
         ssar_set_error("frames_fft: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
         return SSAR_ERR_CUDA;
     }
-    const long long groups = (total + L::FPB - 1) / L::FPB;
-    // persistent grid: a multiple of the SM count, 4 CTAs per SM resident when shared memory allows
-    long long grid = (long long)SSAR_NUM_SMS * 4;
+    const long long groups = (total + L::WPB * L::FPW - 1) / (L::WPB * L::FPW);
+    // persistent grid: a multiple of the SM count, 2 CTAs of 8 warps per SM (registers: 128 per thread)
+    long long grid = (long long)SSAR_NUM_SMS * 2;
     if (groups < grid) grid = groups;
-    frames_fft_kernel<M><<<(unsigned)grid, 256, L::bytes, st>>>(a, total);
+    frames_fft_kernel<M><<<(unsigned)grid, 256, smem, st>>>(a, total, separate_power);
     return ssar_launch_status("frames_fft");
 }
 
