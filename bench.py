@@ -291,6 +291,13 @@ def main():
         streams = [torch.cuda.Stream(dev), torch.cuda.Stream(dev)]
 
         def e2e_step():
+            if kind == "full":
+                # the public call takes the pinned host batch: it stages chunk k + 1 on a copy stream while chunk k's
+                # feature kernels run, and renders chunk k's patches meanwhile (pipeline.features_and_latents)
+                for h, r in zip(host_out, results(step(host_x))):
+                    h.copy_(r, non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+                return
             for ci, c0 in enumerate(range(0, B, chunk)):
                 s = streams[ci % 2]
                 with torch.cuda.stream(s):

@@ -151,11 +151,12 @@ _POOLS = {}
 _SIDE_STREAMS = {}
 
 
-def _side_stream(device):
-    key = (torch.device(device).index, __import__("threading").get_ident())
+def _side_stream(device, purpose="sampler"):
+    key = (torch.device(device).index, __import__("threading").get_ident(), purpose)
     st = _SIDE_STREAMS.get(key)
     if st is None:
-        st = _SIDE_STREAMS[key] = torch.cuda.Stream(device)
+        # sampler: high priority, so its tiny generator kernels jump the queue of feature kernels
+        st = _SIDE_STREAMS[key] = torch.cuda.Stream(device, priority=-1 if purpose == "sampler" else 0)
     return st
 
 
@@ -195,59 +196,110 @@ def patch_features_batch(feats: torch.Tensor):
 
 
 def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, segmentations, tempo=120.0, seed=42,
-                         rng_device="cuda", workers=None):
+                         rng_device="cuda", workers=None, chunk=8):
     """The north-star unit for a batch of clips: waveforms [B, N] -> (features [B, T, 59], latents [B, T, 18, 512]).
     Tempo and segmentations are inputs (random/mir.py:28-42 is CPU librosa / scipy work outside the path).
     rng_device: where the Patch generator lives ("cpu" reproduces a CPU-seeded reference run bit for bit in its draws;
     the reference's own default is the compute device, random/__init__.py:1-3).
-    workers: host threads building the per-clip patches (sampling + launches are independent per clip; torch releases
-    the GIL inside its ops, so the generator draws of different clips overlap).  Every thread launches on the caller's
-    current stream, so stream order with the feature kernels is kept."""
+
+    Host pipeline (the step is bound by host launch work, not by the kernels): three threads on the caller's stream +
+    one side stream, all in stream order so no extra events are needed —
+      * feature thread: queues `audio2features_batch` for `chunk` clips at a time (it blocks once per chunk on the clip
+        tunings; torch releases the GIL while it waits);
+      * sampler thread(s): `Patch(...)` for every clip on a high-priority side stream (patch.py:41-66 needs no feature
+        values; its read-backs then never queue behind the feature kernels);
+      * calling thread: as soon as a chunk's features are queued, binds them to that chunk's patches and renders
+        (one fused launch per latent sub-patch, one mixing GEMM per clip, the noise-basis draws).
+    workers: sampler threads (CPU generators only: their large basis draws release the GIL; CUDA generators use one)."""
+    import queue
+    import threading
+
     from .random.patch import Patch, precapture_sampler_graphs
 
-    dev = audio.device
+    # `audio` may live in (pinned) HOST memory: the feature thread then stages it chunk by chunk on a copy stream, one
+    # chunk ahead of the kernels (input staging only — there is no CPU compute path)
+    dev = palette.device if not audio.is_cuda else audio.device
+    if dev.type != "cuda":
+        raise ops.SsarError("features_and_latents needs the palette (and the compute) on a CUDA device")
     stream = torch.cuda.current_stream(dev)
     if str(rng_device).startswith("cuda"):
         with torch.cuda.device(dev):
             precapture_sampler_graphs(dev, segmentations)  # no-op once captured
     workers = default_patch_workers(rng_device) if workers is None else int(workers)
-    checks = []
-
-    # 1) the feature kernels are queued by a helper thread: audio2features_batch blocks once on the clip tunings (the CQT
-    #    basis is data dependent) and torch releases the GIL while it waits, so this thread keeps working
-    def features_job():
-        with torch.cuda.device(dev), torch.cuda.stream(stream):
-            f = audio2features_batch(audio, sr, fps, deferred_checks=checks)
-            return f, patch_features_batch(f)
-
-    fut = _pool(max(workers, 1) + 1).submit(features_job)
-
-    # 2) meanwhile: patch sampling (patch.py:41-66) needs no feature values; it reads its draws back with a few stream
-    #    synchronisations, so it runs on a side stream where those waits do not queue behind the feature kernels
     B = audio.shape[0]
+    chunk = max(1, min(int(chunk), B))
+    bounds = [(c0, min(c0 + chunk, B)) for c0 in range(0, B, chunk)]
+    checks = []
+    pool = _pool(max(workers, 1) + 2)
+    ready_feats = queue.Queue()
 
-    def sample(b):
-        with torch.cuda.device(dev), torch.cuda.stream(_side_stream(dev)):
-            return Patch(None, segmentations, tempo, fps=fps, seed=seed + b, device=rng_device)
+    def features_job():
+        try:
+            with torch.cuda.device(dev), torch.cuda.stream(stream):
+                staged = None
+                if not audio.is_cuda:
+                    copy_stream = _side_stream(dev, "h2d")
 
-    if workers <= 1 or B == 1:
-        patches = [sample(b) for b in range(B)]
-    else:
-        patches = list(_pool(workers + 1).map(sample, range(B)))
-    feats, pf_all = fut.result()
-    T = feats.shape[1]
-    latents = torch.empty(B, T, palette.shape[1], palette.shape[2], dtype=torch.float32, device=dev)
+                    def stage(c0, c1):
+                        with torch.cuda.stream(copy_stream):
+                            xd = audio[c0:c1].to(dev, non_blocking=True)
+                            ev = torch.cuda.Event()
+                            ev.record(copy_stream)
+                        xd.record_stream(stream)
+                        return xd, ev
 
-    # 3) render: one fused launch per latent sub-patch + one mixing GEMM per clip, noise bases drawn per layer
-    def render(b):
-        with torch.cuda.device(dev), torch.cuda.stream(stream):
-            patches[b].bind({k: v[b] for k, v in pf_all.items()})
-            return patches[b].forward(palette, downscale_factor=4, latents_out=latents[b])[1]
+                    staged = stage(*bounds[0])
+                for ci, (c0, c1) in enumerate(bounds):
+                    if staged is not None:
+                        xd, ev = staged
+                        staged = stage(*bounds[ci + 1]) if ci + 1 < len(bounds) else None  # one chunk ahead
+                        stream.wait_event(ev)
+                    else:
+                        xd = audio[c0:c1]
+                    f = audio2features_batch(xd, sr, fps, deferred_checks=checks)
+                    ready_feats.put((c0, c1, f, patch_features_batch(f)))
+        except BaseException as e:  # surfaced by the calling thread
+            ready_feats.put(e)
 
-    if workers <= 1 or B == 1 or str(rng_device).startswith("cuda"):
-        noises = [render(b) for b in range(B)]
-    else:
-        noises = list(_pool(workers + 1).map(render, range(B)))
+    patches = [None] * B
+    sampled = [threading.Event() for _ in range(B)]
+    sample_error = []
+
+    def sample_job(indices):
+        try:
+            with torch.cuda.device(dev), torch.cuda.stream(_side_stream(dev)):
+                for b in indices:
+                    patches[b] = Patch(None, segmentations, tempo, fps=fps, seed=seed + b, device=rng_device)
+                    sampled[b].set()
+        except BaseException as e:
+            sample_error.append(e)
+            for ev in sampled:
+                ev.set()
+
+    futs = [pool.submit(features_job)]
+    n_samplers = 1 if str(rng_device).startswith("cuda") else max(1, workers)
+    for w in range(n_samplers):
+        futs.append(pool.submit(sample_job, list(range(w, B, n_samplers))))
+
+    feats_chunks, latents, noises = [], None, [None] * B
+    with torch.cuda.device(dev), torch.cuda.stream(stream):
+        for _ in bounds:
+            item = ready_feats.get()
+            if isinstance(item, BaseException):
+                raise item
+            c0, c1, f, pf = item
+            feats_chunks.append(f)
+            if latents is None:
+                latents = torch.empty(B, f.shape[1], palette.shape[1], palette.shape[2], dtype=torch.float32, device=dev)
+            for b in range(c0, c1):
+                sampled[b].wait()
+                if sample_error:
+                    raise sample_error[0]
+                patches[b].bind({k: v[b - c0] for k, v in pf.items()})
+                noises[b] = patches[b].forward(palette, downscale_factor=4, latents_out=latents[b])[1]
+        feats = feats_chunks[0] if len(feats_chunks) == 1 else torch.cat(feats_chunks, dim=0)
+    for fu in futs:
+        fu.result()
     for check in checks:  # error behaviour of the reference (empty peak set), read back once everything is queued
         check()
     return feats, latents, noises

@@ -242,3 +242,100 @@ def _noise_patch_per_layer(rng, noise, features, tempo, fps, patch_type, loop_ba
             noise[n] = new_noise
         noise[n] = ScaleBias(noise[n], scale=noise_std, bias=noise_mean)
     return noise
+
+
+class NoiseProgram(Noise):
+    """One layer's noise as the flat op list the module tree of noise.py:4-140 compiles to.  `Patch.forward` builds these
+    directly (the trees it makes are chains: every sub-patch wraps the layer's previous value with ONE new leaf and a
+    merge), which keeps the per-layer host cost at the generator draw plus a few list appends.  Same call surface as the
+    modules: `forward(i, b) -> [b, H, W]`, `.size`, `.length`, `.device`, `.to(device)`."""
+
+    def __init__(self, length, size, device):
+        super().__init__(length, size)
+        self._device = torch.device(device)
+        self.steps = []  # (kind, noise tensor | None, mod tensor | None, M, p0, p1, to_acc)
+
+    @property
+    def device(self):
+        return self._device
+
+    def to(self, device):
+        device = torch.device(device)
+        if device != self._device:
+            self.steps = [(k, n.to(device) if n is not None else None, m.to(device) if m is not None else None, M, p0, p1, ta)
+                          for (k, n, m, M, p0, p1, ta) in self.steps]
+            self._device = device
+        return self
+
+    def leaf(self, kind, noise, mod, M=0, p0=0.0, to_acc=0):
+        if to_acc:
+            self.steps.clear()  # a leaf into `acc` replaces the layer's history (merge_type other than average / modulate)
+        self.steps.append((kind, noise, mod, M, p0, 0.0, to_acc))
+
+    def merge(self, kind, mod=None, p0=0.0, p1=0.0):
+        self.steps.append((kind, None, mod, 0, p0, p1, 0))
+
+    def forward(self, i, b):
+        b = max(0, min(int(b), self.length - int(i)))
+        prog = [_op(k, noise=n, mod=m, M=M, p0=p0, p1=p1, to_acc=ta) for (k, n, m, M, p0, p1, ta) in self.steps]
+        return ops.noise_eval(prog, int(i), b, int(self.size[0]), int(self.size[1]), self._device)
+
+    __call__ = forward
+
+
+def base_noise_programs(rng, length, sizes, n_loops, sigma, device):
+    """patch.py:123-131: one `Loop` per layer (same draw per layer: randn(3, H, W))."""
+    progs = []
+    for size in sizes:
+        p = NoiseProgram(length, size, device)
+        noise = torch.randn((3, size[0], size[1]), generator=rng, device=rng.device)
+        if noise.device != p.device:
+            noise = noise.to(p.device)
+        p.leaf(LOOP, noise, plan.loop_phase(n_loops, int(length), str(device)), p0=sigma / 50, to_acc=1)
+        progs.append(p)
+    return progs
+
+
+def noise_patch_programs(rng, progs, features, tempo, fps, patch_type, loop_bars, seq_feat, seq_feat_weight, mod_feat,
+                         mod_feat_weight, merge_type, merge_depth, noise_mean, noise_std):
+    """ssar/random/noise.py:89-140 on `NoiseProgram`s: same generator draws (one basis per wrapped layer, in layer order),
+    same arithmetic (the kernel evaluates the same ops the module tree would emit)."""
+    layers = NOISE_LAYER_RANGES[merge_depth]
+    if len(layers) == 0:
+        return progs
+    dev = progs[layers[0]].device
+    feature = (seq_feat_weight * features[seq_feat]).to(dev)
+    if feature.dtype != torch.float32 or not feature.is_contiguous():
+        feature = feature.float().contiguous()
+    length, M = feature.shape[0], feature.shape[1]
+    mod_mean = None
+    if merge_type == "modulate":
+        mod_mean = (mod_feat_weight * features[mod_feat]).to(dev).float().mean(1).contiguous()
+    if patch_type == "loop":
+        phase = plan.loop_phase(length / fps / 60 / tempo / 4 / loop_bars, int(length), str(dev))
+    merged = merge_type in ("average", "modulate")
+    rdev = rng.device
+    for n in layers:
+        p = progs[n]
+        h, w = p.size
+        if patch_type == "blend":
+            noise = torch.randn((2, M, h, w), generator=rng, device=rdev)
+        elif patch_type == "multiply":
+            noise = torch.randn((M, h, w), generator=rng, device=rdev)
+        else:
+            noise = torch.randn((3, h, w), generator=rng, device=rdev)
+        if noise.device != dev:
+            noise = noise.to(dev)
+        to_acc = 0 if merged else 1
+        if patch_type == "blend":
+            p.leaf(BLEND, noise, feature, M=M, to_acc=to_acc)
+        elif patch_type == "multiply":
+            p.leaf(MULTIPLY, noise, feature, M=M, to_acc=to_acc)
+        else:
+            p.leaf(LOOP, noise, phase, p0=5 / 50, to_acc=to_acc)  # Loop's default sigma = 5 (noise.py:45)
+        if merge_type == "average":
+            p.merge(AVERAGE)
+        elif merge_type == "modulate":
+            p.merge(MODULATE, mod=mod_mean)
+        p.merge(SCALEBIAS, p0=noise_std, p1=noise_mean)
+    return progs

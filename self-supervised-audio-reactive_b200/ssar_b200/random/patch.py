@@ -12,7 +12,7 @@ import torch
 from . import DEVICE
 from .latent import LatentWeights, latent_patch, merge_coefficients, sequence_weights, spline_loop_latents  # noqa: F401
 from .mir import ALLFEATS, UNITFEATS
-from .noise import Loop, noise_patch
+from .noise import Loop, base_noise_programs, noise_patch, noise_patch_programs  # noqa: F401
 from .. import plan
 
 
@@ -370,14 +370,11 @@ class Patch:
             acc.apply_subpatch(self.rng, self.segmentations, feats, self.tempo, self.fps, **sp)
         latents = acc.render(latent_palette, out=latents_out)
 
-        noise = [
-            Loop(rng=self.rng, length=self.length,
-                 size=(round(aspect_ratio * size / downscale_factor), round(size / downscale_factor)),
-                 n_loops=self.loops_base_noise, sigma=self.sigma_base_noise, device=dev)
-            for size in [4, 8, 8, 16, 16, 32, 32, 64, 64, 128, 128, 256, 256, 512, 512, 1024, 1024]
-        ]
+        sizes = [(round(aspect_ratio * size / downscale_factor), round(size / downscale_factor))
+                 for size in [4, 8, 8, 16, 16, 32, 32, 64, 64, 128, 128, 256, 256, 512, 512, 1024, 1024]]
+        noise = base_noise_programs(self.rng, self.length, sizes, self.loops_base_noise, self.sigma_base_noise, dev)
         for sp in self.noise_patches:
-            noise = noise_patch(self.rng, noise, feats, self.tempo, self.fps, **sp)
+            noise = noise_patch_programs(self.rng, noise, feats, self.tempo, self.fps, **sp)
         return latents, noise
 
     __call__ = forward
