@@ -149,6 +149,13 @@ int ssar_hpss(const float* stft, int n_clips, int n_frames, int n_bins, long lon
 int ssar_irfft_frames(const float* spec, long long ld, int n_clips, int n_frames, int n_fft,
                       const float* window, const float* twiddle, float* frames, void* stream);
 
+/* torch.istft (rosa/spectral.py:24-32) for hop = n_fft / 2 and n_fft = 2048 in ONE kernel: inverse real FFT per frame,
+ * synthesis window, overlap-add, division by the summed squared window, centre trim — the [frames, n_fft] intermediate
+ * of ssar_irfft_frames + ssar_overlap_add is never written.  spec: frame-major complex [n_clips, n_frames, ld];
+ * out [n_clips, length] (length even, 8-byte aligned). */
+int ssar_istft_half_overlap(const float* spec, long long ld, int n_clips, int n_frames, int n_fft, const float* window,
+                            const float* twiddle, long long length, float* out, void* stream);
+
 /* torch.istft step 2: overlap-add of `frames`, division by the summed squared window, drop n_fft/2 leading
  * samples, produce `length` samples per clip (zeros past the covered range). out: [n_clips, length]. */
 int ssar_overlap_add(const float* frames, const float* window, int n_clips, int n_frames, int n_fft, int hop,

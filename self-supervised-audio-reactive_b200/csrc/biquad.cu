@@ -4,11 +4,13 @@
 //     v[n] = b0 x[n] + b1 x[n-1] + b2 x[n-2]          (coefficients already divided by a0)
 //     y[n] = v[n] - (a2 y[n-2] + a1 y[n-1]),  y[-1] = y[-2] = 0,  output clamped to [-1, 1] at the very end.
 //
-// Phase A: every chunk of L samples runs the recurrence from a ZERO state and keeps only its final state z_c.
-// Phase B: the true end-of-chunk states follow the affine recurrence S_c = A^L S_{c-1} + z_c (A = companion
-//          matrix); one CTA per clip scans it in fp64 (per-thread runs + Hillis-Steele over (P, q) pairs).
-// Phase C: every chunk re-runs the SAME fp32 recurrence from its true initial state S_{c-1} and writes clamp(y),
-//          so within a chunk the operation order is the sequential reference's.
+// Phase A: every chunk of L samples runs the recurrence from a ZERO state and keeps its final state z_c; the CTA (128
+//          chunks) also scans its z_c in fp64 and emits the zero-state end state of its whole span.
+// Phase B: the true end-of-span states follow the affine recurrence S_c = A^(128 L) S_{c-1} + Z_c (A = companion
+//          matrix); one CTA per clip scans the ~720 spans in fp64 (one element per thread, coalesced).
+// Phase C: every CTA rebuilds the true state entering each of its chunks (fp64 block scan of z_c + the state entering
+//          the span), then every chunk re-runs the SAME fp32 recurrence from that state and writes clamp(y), so within
+//          a chunk the operation order is the sequential reference's.
 // Chunks are staged through shared memory so global reads and writes stay coalesced.
 #include "common.cuh"
 
@@ -27,12 +29,61 @@ __device__ __forceinline__ float step(const Coef& c, float x0, float x1, float x
     return v - (c.a2 * y2 + c.a1 * y1);
 }
 
+struct M2 {
+    double a, b, c, d;  // [[a, b], [c, d]]
+};
+__device__ __forceinline__ M2 mm(const M2& x, const M2& y) {
+    return {x.a * y.a + x.b * y.c, x.a * y.b + x.b * y.d, x.c * y.a + x.d * y.c, x.c * y.b + x.d * y.d};
+}
+struct V2 {
+    double x, y;
+};
+__device__ __forceinline__ V2 mv(const M2& m, const V2& v) { return {m.a * v.x + m.b * v.y, m.c * v.x + m.d * v.y}; }
+
+// powers AL^(2^s), s = 0..7, of AL = A^L (A = companion matrix on (y[n-1], y[n-2])), in fp64
+struct ALPowers {
+    M2 p[8];
+};
+__device__ __forceinline__ ALPowers al_powers(double a1, double a2) {
+    ALPowers r;
+    M2 AL = {-a1, -a2, 1.0, 0.0};
+#pragma unroll
+    for (int i = 0; i < 6; ++i) AL = mm(AL, AL);  // L = 64 = 2^6
+    r.p[0] = AL;
+#pragma unroll
+    for (int i = 1; i < 8; ++i) r.p[i] = mm(r.p[i - 1], r.p[i - 1]);
+    return r;
+}
+
+// inclusive scan over the CTA's CPB chunks of q_j = sum_{i <= j} AL^(j - i) z_i (Hillis-Steele, fp64, shared memory)
+__device__ __forceinline__ V2 block_scan_states(V2 q, const ALPowers& pw, V2* sq) {
+    const int tid = threadIdx.x;
+    sq[tid] = q;
+    __syncthreads();
+#pragma unroll
+    for (int s = 0; s < 7; ++s) {  // CPB = 128 = 2^7
+        const int d = 1 << s;
+        V2 add = {0.0, 0.0};
+        if (tid >= d) add = mv(pw.p[s], sq[tid - d]);
+        __syncthreads();
+        q.x += add.x;
+        q.y += add.y;
+        sq[tid] = q;
+        __syncthreads();
+    }
+    return q;
+}
+
 template <bool WRITE>
 __global__ void __launch_bounds__(CPB) biquad_chunks_kernel(const float* __restrict__ x, long long n, long long stride_x,
                                                             Coef c, const float2* __restrict__ state_in,
                                                             float2* __restrict__ state_out, float* __restrict__ y,
-                                                            long long stride_y, long long n_chunks, int clamp) {
+                                                            long long stride_y, long long n_chunks, int clamp,
+                                                            V2* __restrict__ cta_z, const V2* __restrict__ cta_s,
+                                                            double a1d, double a2d) {
     __shared__ float tile[CPB * LDT];
+    __shared__ V2 sq[CPB];
+    const ALPowers pw = al_powers(a1d, a2d);
     const int clip = blockIdx.y;
     const float* xc = x + (long long)clip * stride_x;
     const long long tile0 = (long long)blockIdx.x * CPB * L;
@@ -42,16 +93,36 @@ __global__ void __launch_bounds__(CPB) biquad_chunks_kernel(const float* __restr
     }
     __syncthreads();
     const long long chunk = (long long)blockIdx.x * CPB + threadIdx.x;
+    float y1 = 0.f, y2 = 0.f;
+    if (WRITE) {
+        // true state entering every chunk of this CTA: S_j = AL^(j+1) S_in + sum_{i<=j} AL^(j-i) z_i (fp64), chunk j starts
+        // from S_{j-1}; S_in = the state entering the CTA from the carry kernel
+        V2 z = {0.0, 0.0};
+        if (chunk < n_chunks) {
+            const float2 zz = state_in[(long long)clip * n_chunks + chunk];
+            z = {(double)zz.x, (double)zz.y};
+        }
+        V2 S = block_scan_states(z, pw, sq);
+        V2 sin = {0.0, 0.0};
+        if (blockIdx.x > 0) sin = cta_s[(long long)clip * gridDim.x + blockIdx.x - 1];
+        V2 prop = sin;
+        const int e = threadIdx.x + 1;
+#pragma unroll
+        for (int b = 0; b < 8; ++b)
+            if (e & (1 << b)) prop = mv(pw.p[b], prop);
+        S.x += prop.x;
+        S.y += prop.y;
+        __syncthreads();
+        sq[threadIdx.x] = S;
+        __syncthreads();
+        const V2 init = threadIdx.x > 0 ? sq[threadIdx.x - 1] : sin;
+        y1 = (float)init.x;
+        y2 = (float)init.y;
+    }
     if (chunk < n_chunks) {
         const long long n0 = chunk * L;
         float x1 = n0 >= 1 ? __ldg(xc + n0 - 1) : 0.f;
         float x2 = n0 >= 2 ? __ldg(xc + n0 - 2) : 0.f;
-        float y1 = 0.f, y2 = 0.f;
-        if (WRITE && chunk > 0) {
-            const float2 s = state_in[(long long)clip * n_chunks + chunk - 1];
-            y1 = s.x;
-            y2 = s.y;
-        }
         float* row = tile + threadIdx.x * LDT;
 #pragma unroll 8
         for (int i = 0; i < L; ++i) {
@@ -65,6 +136,13 @@ __global__ void __launch_bounds__(CPB) biquad_chunks_kernel(const float* __restr
         }
         if (!WRITE) state_out[(long long)clip * n_chunks + chunk] = make_float2(y1, y2);
     }
+    if (!WRITE) {
+        // CTA aggregate: zero-state end state of the CTA's whole span (chunks past the end contribute zero)
+        V2 z = {0.0, 0.0};
+        if (chunk < n_chunks) z = {(double)y1, (double)y2};
+        const V2 q = block_scan_states(z, pw, sq);
+        if (threadIdx.x == CPB - 1) cta_z[(long long)clip * gridDim.x + blockIdx.x] = q;
+    }
     if (WRITE) {
         __syncthreads();
         float* yc = y + (long long)clip * stride_y;
@@ -75,29 +153,20 @@ __global__ void __launch_bounds__(CPB) biquad_chunks_kernel(const float* __restr
     }
 }
 
-struct M2 {
-    double a, b, c, d;  // [[a, b], [c, d]]
-};
-__device__ __forceinline__ M2 mm(const M2& x, const M2& y) {
-    return {x.a * y.a + x.b * y.c, x.a * y.b + x.b * y.d, x.c * y.a + x.d * y.c, x.c * y.b + x.d * y.d};
-}
-struct V2 {
-    double x, y;
-};
-__device__ __forceinline__ V2 mv(const M2& m, const V2& v) { return {m.a * v.x + m.b * v.y, m.c * v.x + m.d * v.y}; }
-
-// One CTA (1024 threads) per clip.  z (in): zero-state end states per chunk; s (out): true end states per chunk.
-__global__ void __launch_bounds__(1024) biquad_carry_kernel(const float2* __restrict__ z, float2* __restrict__ s,
+// One CTA (1024 threads) per clip over the per-CTA aggregates of the chunk kernel (n_chunks here = number of chunk-kernel
+// CTAs per clip, 720 for a 4-minute clip: one element per thread, coalesced).  z (in): zero-state end state of every
+// span of CPB chunks; s (out): true state at the end of every span.
+__global__ void __launch_bounds__(1024) biquad_carry_kernel(const V2* __restrict__ z, V2* __restrict__ s,
                                                             long long n_chunks, double a1, double a2) {
     __shared__ M2 sP[1024];
     __shared__ V2 sq[1024];
     const int clip = blockIdx.x, tid = threadIdx.x;
-    const float2* zc = z + (long long)clip * n_chunks;
-    float2* sc = s + (long long)clip * n_chunks;
-    // A = companion matrix on (y[n-1], y[n-2]);  AL = A^L by repeated squaring (L = 64 = 2^6)
+    const V2* zc = z + (long long)clip * n_chunks;
+    V2* sc = s + (long long)clip * n_chunks;
+    // A = companion matrix on (y[n-1], y[n-2]);  AL = A^(L * CPB) by repeated squaring (64 * 128 = 2^13)
     M2 AL = {-a1, -a2, 1.0, 0.0};
 #pragma unroll
-    for (int i = 0; i < 6; ++i) AL = mm(AL, AL);
+    for (int i = 0; i < 13; ++i) AL = mm(AL, AL);
     const long long run = (n_chunks + 1023) / 1024;
     const long long c0 = (long long)tid * run;
     long long c1 = c0 + run;
@@ -106,10 +175,10 @@ __global__ void __launch_bounds__(1024) biquad_carry_kernel(const float2* __rest
     M2 P = {1.0, 0.0, 0.0, 1.0};
     V2 q = {0.0, 0.0};
     for (long long c = c0; c < c1; ++c) {
-        const float2 zz = zc[c];
+        const V2 zz = zc[c];
         q = mv(AL, q);
-        q.x += (double)zz.x;
-        q.y += (double)zz.y;
+        q.x += zz.x;
+        q.y += zz.y;
         P = mm(AL, P);
     }
     sP[tid] = P;
@@ -135,11 +204,11 @@ __global__ void __launch_bounds__(1024) biquad_carry_kernel(const float2* __rest
     V2 S = {0.0, 0.0};
     if (tid > 0) S = sq[tid - 1];
     for (long long c = c0; c < c1; ++c) {
-        const float2 zz = zc[c];
+        const V2 zz = zc[c];
         S = mv(AL, S);
-        S.x += (double)zz.x;
-        S.y += (double)zz.y;
-        sc[c] = make_float2((float)S.x, (float)S.y);
+        S.x += zz.x;
+        S.y += zz.y;
+        sc[c] = S;
     }
 }
 
@@ -147,7 +216,8 @@ __global__ void __launch_bounds__(1024) biquad_carry_kernel(const float2* __rest
 
 extern "C" long long ssar_biquad_scratch_bytes(int n_clips, long long n_samples) {
     const long long n_chunks = (n_samples + L - 1) / L;
-    return 2LL * n_clips * n_chunks * (long long)sizeof(float2);
+    const long long n_ctas = (n_chunks + CPB - 1) / CPB;
+    return (long long)n_clips * n_chunks * (long long)sizeof(float2) + 16 + 2LL * n_clips * n_ctas * 16;
 }
 
 extern "C" int ssar_biquad(const float* x, long long n_samples, long long stride_x, int n_clips, float b0, float b1,
@@ -158,12 +228,18 @@ extern "C" int ssar_biquad(const float* x, long long n_samples, long long stride
     SSAR_REQUIRE(n_clips <= 65535, "biquad: too many clips per launch");
     cudaStream_t st = (cudaStream_t)stream;
     const long long n_chunks = (n_samples + L - 1) / L;
+    // scratch: z [n_clips, n_chunks] float2 | per-CTA aggregates [n_clips, n_ctas] double2 | per-CTA states, same shape
     float2* z = reinterpret_cast<float2*>(scratch);
-    float2* s = z + (long long)n_clips * n_chunks;
+    const long long n_ctas = (n_chunks + CPB - 1) / CPB;
+    V2* cz = reinterpret_cast<V2*>(reinterpret_cast<char*>(scratch) +
+                                   (((long long)n_clips * n_chunks * (long long)sizeof(float2) + 15) / 16) * 16);
+    V2* cs = cz + (long long)n_clips * n_ctas;
     const Coef c = {b0, b1, b2, a1, a2};
-    dim3 grid((unsigned)((n_chunks + CPB - 1) / CPB), n_clips);
-    biquad_chunks_kernel<false><<<grid, CPB, 0, st>>>(x, n_samples, stride_x, c, nullptr, z, nullptr, 0, n_chunks, 0);
-    biquad_carry_kernel<<<n_clips, 1024, 0, st>>>(z, s, n_chunks, (double)a1, (double)a2);
-    biquad_chunks_kernel<true><<<grid, CPB, 0, st>>>(x, n_samples, stride_x, c, s, nullptr, y, stride_y, n_chunks, clamp);
+    dim3 grid((unsigned)n_ctas, n_clips);
+    biquad_chunks_kernel<false><<<grid, CPB, 0, st>>>(x, n_samples, stride_x, c, nullptr, z, nullptr, 0, n_chunks, 0, cz,
+                                                     nullptr, (double)a1, (double)a2);
+    biquad_carry_kernel<<<n_clips, 1024, 0, st>>>(cz, cs, n_ctas, (double)a1, (double)a2);
+    biquad_chunks_kernel<true><<<grid, CPB, 0, st>>>(x, n_samples, stride_x, c, z, nullptr, y, stride_y, n_chunks, clamp,
+                                                    nullptr, cs, (double)a1, (double)a2);
     return ssar_launch_status("biquad");
 }

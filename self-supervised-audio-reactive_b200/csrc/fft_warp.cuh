@@ -74,3 +74,72 @@ __device__ __forceinline__ void fft_dif_regs(float2 (&v)[N]) {
         }
     }
 }
+
+// Geometry of the warp-per-frame transform of M complex points.
+template <int M>
+struct WarpFft {
+    static constexpr int N1 = (M == 1024) ? 32 : 16;   // lanes per frame (n1)
+    static constexpr int FPW = 32 / N1;                // frames per warp
+    static constexpr int TLD = N1 + 1;                 // padded row of the [k2][n1] transpose tile (float2)
+    static constexpr int ZF = 32 * TLD;                // float2 per frame buffer (>= M + 1)
+    static constexpr int WPB = 8;                      // warps per CTA
+    static constexpr int NJ = M / 32 + 1;              // spectrum bins per lane (k = lane + 32 j), last one only lane 0
+    static_assert(ZF >= M + 1, "frame buffer must hold M + 1 bins");
+};
+
+// twT[k2 * N1 + n1] = W_M^{n1 k2} from the global table tw[k] = exp(-2 pi i k / 2M); call with the whole CTA, then sync.
+template <int M>
+__device__ __forceinline__ void warp_fft_fill_twiddles(float2* twT, const float2* __restrict__ tw) {
+    constexpr int N1 = WarpFft<M>::N1;
+    for (int i = threadIdx.x; i < 32 * N1; i += blockDim.x) {
+        const int k2 = i / N1, nn = i - k2 * N1;
+        twT[i] = __ldg(&tw[2 * nn * k2]);
+    }
+}
+
+// Forward DFT of the warp's frame(s).  In: v[r] = z[n1 + N1 r] of the frame in slot h = lane / N1 (n1 = lane % N1).
+// Out: Z[k], k in [0, M), in natural order at zw[h * ZF + k].  Ends with a __syncwarp (results visible to the warp).
+template <int M>
+__device__ __forceinline__ void warp_fft_forward(float2 (&v)[32], float2* zw, const float2* twT, int lane) {
+    using L = WarpFft<M>;
+    constexpr int N1 = L::N1, TLD = L::TLD, ZF = L::ZF;
+    const int h = lane / N1, n1 = lane % N1;
+    fft_dif_regs<32, false>(v);
+    {
+        float2* tile = zw + h * ZF;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            const int k2 = bitrev_const(i, 5);
+            float2 y = v[i];
+            if (k2 != 0) y = cmul(y, twT[k2 * N1 + n1]);
+            tile[k2 * TLD + n1] = y;
+        }
+    }
+    __syncwarp();
+    if constexpr (M == 1024) {
+        float2* tile = zw;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = tile[lane * TLD + i];
+        fft_dif_regs<32, false>(v);
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) tile[32 * bitrev_const(i, 5) + lane] = v[i];
+    } else {
+        float2* tile = zw + h * ZF;
+        float2 u0[16], u1[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            u0[i] = tile[n1 * TLD + i];
+            u1[i] = tile[(n1 + 16) * TLD + i];
+        }
+        fft_dif_regs<16, false>(u0);
+        fft_dif_regs<16, false>(u1);
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            tile[32 * bitrev_const(i, 4) + n1] = u0[i];
+            tile[32 * bitrev_const(i, 4) + n1 + 16] = u1[i];
+        }
+    }
+    __syncwarp();
+}

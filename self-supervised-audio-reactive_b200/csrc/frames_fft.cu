@@ -13,22 +13,14 @@
 namespace {
 
 template <int M>
-struct WarpFft {
-    static constexpr int N1 = (M == 1024) ? 32 : 16;   // lanes per frame (n1)
-    static constexpr int FPW = 32 / N1;                // frames per warp
-    static constexpr int TLD = N1 + 1;                 // padded row of the [k2][n1] transpose tile (float2)
-    static constexpr int ZF = 32 * TLD;                // float2 per frame buffer (>= M + 1)
-    static constexpr int WPB = 8;                      // warps per CTA
-    static constexpr int NJ = M / 32 + 1;              // spectrum bins per lane (k = lane + 32 j), last one only lane 0
-    static_assert(ZF >= M + 1, "frame buffer must hold M + 1 bins");
-    static size_t smem_bytes(bool window, bool separate_power) {
-        size_t b = (size_t)32 * N1 * sizeof(float2);                  // twiddle table [k2][n1]
-        if (window) b += (size_t)2 * M * sizeof(float);
-        b += (size_t)WPB * FPW * ZF * sizeof(float2);
-        if (separate_power) b += (size_t)WPB * FPW * (M + 4) * sizeof(float);
-        return b;
-    }
-};
+size_t frames_smem_bytes(bool window, bool separate_power) {
+    using L = WarpFft<M>;
+    size_t b = (size_t)32 * L::N1 * sizeof(float2);                  // twiddle table [k2][n1]
+    if (window) b += (size_t)2 * M * sizeof(float);
+    b += (size_t)L::WPB * L::FPW * L::ZF * sizeof(float2);
+    if (separate_power) b += (size_t)L::WPB * L::FPW * (M + 4) * sizeof(float);
+    return b;
+}
 
 template <int M>
 __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_args a, const long long total_frames,
@@ -45,10 +37,7 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
     const int h = lane / N1, n1 = lane % N1;  // frame slot inside the warp, point index inside the frame
     const float2* __restrict__ tw = reinterpret_cast<const float2*>(a.twiddle);  // exp(-2 pi i k / 2M), k in [0, 2M)
 
-    for (int i = threadIdx.x; i < 32 * N1; i += blockDim.x) {
-        const int k2 = i / N1, nn = i - k2 * N1;
-        twT[i] = __ldg(&tw[2 * nn * k2]);
-    }
+    warp_fft_fill_twiddles<M>(twT, tw);
     if (a.window)
         for (int i = threadIdx.x; i < N; i += blockDim.x) wins[i] = __ldg(a.window + i);
     __syncthreads();
@@ -110,47 +99,8 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
             for (int r = 0; r < 32; ++r) v[r] = make_float2(0.f, 0.f);
         }
 
-        // ------------------------------------------------------------------ pass 1: 32-point DFT over n2, twiddle, transpose
-        fft_dif_regs<32, false>(v);
-        {
-            float2* tile = zw + h * ZF;
-#pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                const int k2 = bitrev_const(i, 5);
-                float2 y = v[i];
-                if (k2 != 0) y = cmul(y, twT[k2 * N1 + n1]);
-                tile[k2 * TLD + n1] = y;
-            }
-        }
-        __syncwarp();
-
-        // ------------------------------------------------------------------ pass 2: DFT over n1, natural-order store
-        if constexpr (M == 1024) {
-            float2* tile = zw;
-#pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = tile[lane * TLD + i];
-            fft_dif_regs<32, false>(v);
-            __syncwarp();
-#pragma unroll
-            for (int i = 0; i < 32; ++i) tile[32 * bitrev_const(i, 5) + lane] = v[i];
-        } else {
-            float2* tile = zw + h * ZF;
-            float2 u0[16], u1[16];
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                u0[i] = tile[n1 * TLD + i];
-                u1[i] = tile[(n1 + 16) * TLD + i];
-            }
-            fft_dif_regs<16, false>(u0);
-            fft_dif_regs<16, false>(u1);
-            __syncwarp();
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                tile[32 * bitrev_const(i, 4) + n1] = u0[i];
-                tile[32 * bitrev_const(i, 4) + n1 + 16] = u1[i];
-            }
-        }
-        __syncwarp();
+        // ------------------------------------------------------------------ the transform (fft_warp.cuh)
+        warp_fft_forward<M>(v, zw, twT, lane);
 
         // rms: sum of squares over the N1 lanes of each frame
         if (a.out_rms) {
@@ -280,7 +230,7 @@ int launch_frames(const ssar_frames_args& a, cudaStream_t st) {
     if (total == 0) return SSAR_OK;
     const bool banks = a.fb[0].n_bands > 0 || a.fb[1].n_bands > 0;
     const int separate_power = (banks && a.proj.n_rows > 0) ? 1 : 0;  // the projection needs the complex tile intact
-    const size_t smem = L::smem_bytes(a.window != nullptr, separate_power != 0);
+    const size_t smem = frames_smem_bytes<M>(a.window != nullptr, separate_power != 0);
     cudaError_t e = cudaFuncSetAttribute(frames_fft_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) {
         ssar_set_error("frames_fft: cudaFuncSetAttribute: %s", cudaGetErrorString(e));

@@ -194,6 +194,11 @@ def istft(spec_fm: torch.Tensor, n_fft: int, hop: int, window=torch.hann_window,
     if length is None:
         length = hop * (T1 - 1)
     win = plan.window_tensor(window, n_fft, dev)
+    if n_fft == 2048 and hop == 1024 and length % 2 == 0:  # the HPSS case: fused transform + overlap-add
+        out = torch.empty(B, length, dtype=torch.float32, device=dev)
+        cabi.call("ssar_istft_half_overlap", ptr(spec_fm), i64(F), i32(B), i32(T1), i32(n_fft), ptr(win),
+                  ptr(plan.twiddle(n_fft, str(dev))), i64(length), ptr(out), nbytes=cabi.nbytes_of(spec_fm, out))
+        return out
     frames = torch.empty(B, T1, n_fft, dtype=torch.float32, device=dev)
     cabi.call("ssar_irfft_frames", ptr(spec_fm), i64(F), i32(B), i32(T1), i32(n_fft), ptr(win),
               ptr(plan.twiddle(n_fft, str(dev))), ptr(frames), nbytes=cabi.nbytes_of(spec_fm, frames))

@@ -34,14 +34,17 @@ def spectral_frontend(x: torch.Tensor, sr, n_fft: int = 2048, hop: int = 512, wa
     return {"spec": out.get("spec"), "mel": out["bank0"], "onset": onset, "rms": out["rms"]}
 
 
-def hpss_pair(x: torch.Tensor, margin: float = 8.0, n_fft: int = 2048, hop: int = 1024, D=None):
+def hpss_pair(x: torch.Tensor, margin: float = 8.0, n_fft: int = 2048, hop: int = 1024, D=None, want_harm=True,
+              want_perc=True):
     """harmonic(x), percussive(x) (features/audio.py:13-24) from ONE forward STFT and ONE pair of median passes.
-    x [B, N] -> (harm [B, N], perc [B, N]).  Exact: the two reference calls differ only in the mask applied."""
+    x [B, N] -> (harm [B, N], perc [B, N]) (None for a part that is not wanted).  Exact: the two reference calls differ
+    only in the mask applied."""
     n = x.shape[-1]
     if D is None:
         D = ops.frames_fft(x, n_fft, hop, 1 + n // hop, torch.hann_window, want_complex=True)["complex"]
-    h, p = ops.hpss(D, margin, True, True)
-    return ops.istft(h, n_fft, hop, torch.hann_window, n), ops.istft(p, n_fft, hop, torch.hann_window, n)
+    h, p = ops.hpss(D, margin, want_harm, want_perc)
+    return (ops.istft(h, n_fft, hop, torch.hann_window, n) if want_harm else None,
+            ops.istft(p, n_fft, hop, torch.hann_window, n) if want_perc else None)
 
 
 def band_split(x: torch.Tensor, sr):
@@ -95,7 +98,7 @@ def audio2features_batch(audio: torch.Tensor, sr, fps, clamp=True, smooth=True, 
 
     # --- harmonic / percussive separation (and the second separation chromagram() applies to audio_harm)
     harm, perc = hpss_pair(x)
-    harm2 = hpss_pair(harm)[0]  # harmonic(audio_harm): features/audio.py:44-45 applied to data.py:68-69's argument
+    harm2 = hpss_pair(harm, want_perc=False)[0]  # harmonic(audio_harm): features/audio.py:44-45 applied to data.py:68-69's argument
     C = ops.cqt(harm2, sr, hop)
     cens = ops.cens_smooth(ops.chroma_from_cqt(C, quantize=True), plan.cens_window(41, dev), l2=True)  # [B, T, 12]
     ton = ops.tonnetz(cens)

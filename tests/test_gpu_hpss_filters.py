@@ -44,6 +44,15 @@ def test_istft_roundtrip_and_batch():
     D = spectral.stft(xs)
     y = spectral.istft(D, length=xs.shape[-1])
     assert tuple(y.shape) == tuple(xs.shape) and rel_l2(y, xs) < 1e-5
+    # even lengths take the fused transform + overlap-add kernel (n_fft 2048, hop 1024): whole hops, a ragged tail,
+    # a clip shorter than one run of blocks, and the oracle's torch.istft on the same spectrum
+    for n in (24576 * 3, 24576 * 2 + 1000, 4096 + 2, 1026):
+        xe = torch.stack([synth_clip(n, 24576, i) for i in range(2)]).cuda()
+        De = spectral.stft(xe)
+        ye = spectral.istft(De, length=n)
+        assert tuple(ye.shape) == (2, n) and rel_l2(ye, xe) < 1e-5, n
+        ref = dsp.istft(De[1].cpu(), 2048, 1024, length=n)
+        assert rel_l2(ye[1], ref) < 1e-5, n
     # 1024-point path with hop 1 (the PLP configuration, rosa/beat.py:69)
     e = synth_clip(1500, 24, 5).abs().cuda()
     De = spectral.stft(e, n_fft=1024, hop_length=1)
