@@ -4,18 +4,30 @@
 // (features/processing.py:74-84: 31-tap median along time -> "harm", along frequency -> "perc", reflect
 // padding, torch.median = exact 16th smallest of 31) + two softmask calls (:120-142, power 2, margin m).
 //
-// One CTA computes a 32-frame x 64-bin output tile from a (32+30) x (64+30) magnitude tile staged in shared
-// memory (magnitudes are computed on the fly from the complex input, so |D| never round-trips HBM).  Each
-// output needs two 31-element selections; both run as a register-resident Batcher odd-even merge network
-// (data-independent; the generated include keeps only the 152 compare-exchanges that can reach the median).
+// One CTA (512 threads) computes a 32-frame x 64-bin output tile from a (32+30) x (64+30) magnitude tile staged in
+// shared memory (magnitudes are computed on the fly from the complex input, so |D| never round-trips HBM).
+//
+// Selection with a SHARED CORE: four neighbouring outputs along the filter axis have windows [j, j+30], j = 0..3, of one
+// 34-element span; the 28 elements [3, 30] are common to all four.  One pruned Batcher network (select28_net.inc, 138
+// compare-exchanges, generated + self-checked by scripts/gen_select_net.py) leaves the core's sorted ranks 12..15 in
+// place; the median of window j is then the 4th smallest of those four and the window's 3 private elements (everything
+// below rank 12 of the core is below it, everything above rank 15 is above it): a 3-element sort and
+// min(max(a0,b2), max(a1,b1), max(a2,b0), a3).  41 compare-exchange equivalents per output instead of 152, and
+// 8.5 shared-memory loads instead of 31.
+//   phase 1: medians along time   — thread = (bin column, 4 frames), lanes along bins   -> Hs tile
+//   phase 2: medians along frequency — thread = (frame row, 4 bins), lanes along frames (odd row stride: conflict-free)
+//            + both soft masks -> gain tiles
+//   phase 3: coalesced pass: out = gain * D / |D|
 #include "common.cuh"
 
 namespace {
 
-constexpr int KS = 31, HALF = 15;
+constexpr int HALF = 15;
 constexpr int TT = 32, TF = 64;
 constexpr int ROWS = TT + 2 * HALF, COLS = TF + 2 * HALF;
-constexpr int LDS = COLS + 1;
+constexpr int LDS = COLS + 1;  // 95: odd
+constexpr int LDG = TF + 1;    // 65: odd
+constexpr int HP_THREADS = 512;
 
 __device__ __forceinline__ void cswap(float& a, float& b) {
     const float lo = fminf(a, b), hi = fmaxf(a, b);
@@ -23,14 +35,30 @@ __device__ __forceinline__ void cswap(float& a, float& b) {
     b = hi;
 }
 
-// 16th smallest of v[0..30] -> returned; pruned Batcher odd-even merge network (median31_net.inc, generated)
-__device__ __forceinline__ float median31(float (&v)[31]) {
+// 4th smallest of {a0 <= a1 <= a2 <= a3} U {x, y, z}
+__device__ __forceinline__ float fourth_of_4_plus_3(float a0, float a1, float a2, float a3, float x, float y, float z) {
+    cswap(x, y);
+    cswap(y, z);
+    cswap(x, y);
+    return fminf(fminf(fmaxf(a0, z), fmaxf(a1, y)), fminf(fmaxf(a2, x), a3));
+}
+
+// medians of the four 31-element windows [j, j+30] of the 34-element span s[0], s[stride], ..., s[33 * stride]
+__device__ __forceinline__ void median31_x4(const float* __restrict__ s, int stride, float (&out)[4]) {
+    float v[28];
+#pragma unroll
+    for (int k = 0; k < 28; ++k) v[k] = s[(k + 3) * stride];
+    const float x0 = s[0], x1 = s[stride], x2 = s[2 * stride];
+    const float y0 = s[31 * stride], y1 = s[32 * stride], y2 = s[33 * stride];
 #define CS(a, b) cswap(v[a], v[b]);
 #define MV(a, b) { float t_ = v[a]; v[a] = v[b]; v[b] = t_; }
-#include "median31_net.inc"
+#include "select28_net.inc"
 #undef CS
 #undef MV
-    return v[15];
+    out[0] = fourth_of_4_plus_3(v[12], v[13], v[14], v[15], x0, x1, x2);
+    out[1] = fourth_of_4_plus_3(v[12], v[13], v[14], v[15], x1, x2, y0);
+    out[2] = fourth_of_4_plus_3(v[12], v[13], v[14], v[15], x2, y0, y1);
+    out[3] = fourth_of_4_plus_3(v[12], v[13], v[14], v[15], y0, y1, y2);
 }
 
 __device__ __forceinline__ float softmask2(float X, float Xref, float split) {
@@ -42,15 +70,17 @@ __device__ __forceinline__ float softmask2(float X, float Xref, float split) {
     return m / (m + r);
 }
 
-__global__ void __launch_bounds__(256) hpss_kernel(const float2* __restrict__ D, int n_frames, int n_bins, long long ld,
-                                                   float margin_h, float margin_p, float2* __restrict__ out_h,
-                                                   float2* __restrict__ out_p) {
+__global__ void __launch_bounds__(HP_THREADS, 2) hpss_kernel(const float2* __restrict__ D, int n_frames, int n_bins,
+                                                             long long ld, float margin_h, float margin_p,
+                                                             float2* __restrict__ out_h, float2* __restrict__ out_p) {
     __shared__ float mag[ROWS * LDS];
+    __shared__ float gh[TT * LDG];  // harmonic medians, then harmonic gains
+    __shared__ float gp[TT * LDG];  // percussive gains
     const int clip = blockIdx.z;
     const int t0 = blockIdx.y * TT, f0 = blockIdx.x * TF;
     const float2* Dc = D + (long long)clip * n_frames * ld;
 
-    for (int i = threadIdx.x; i < ROWS * COLS; i += blockDim.x) {
+    for (int i = threadIdx.x; i < ROWS * COLS; i += HP_THREADS) {
         const int r = i / COLS, c = i - r * COLS;
         int t = t0 + r - HALF, f = f0 + c - HALF;
         // reflect; tiles hanging over the far edge read clamped (unused) positions
@@ -63,33 +93,44 @@ __global__ void __launch_bounds__(256) hpss_kernel(const float2* __restrict__ D,
     }
     __syncthreads();
 
-    for (int o = threadIdx.x; o < TT * TF; o += blockDim.x) {
+    {   // phase 1: median along time (window rows r .. r+30 at column c+15) -> harmonic-enhanced
+        const int c = threadIdx.x % TF, r = (threadIdx.x / TF) * 4;
+        float m[4];
+        median31_x4(mag + r * LDS + c + HALF, LDS, m);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) gh[(r + j) * LDG + c] = m[j];
+    }
+    __syncthreads();
+    {   // phase 2: median along frequency (row r+15, columns c .. c+30) -> percussive-enhanced; soft masks -> gains
+        const int r = threadIdx.x % TT, c = (threadIdx.x / TT) * 4;
+        float m[4];
+        median31_x4(mag + (r + HALF) * LDS + c, 1, m);
+        const float split = (margin_h == 1.f && margin_p == 1.f) ? 0.5f : 0.f;  // rosa/spectral.py:158
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float harm = gh[r * LDG + c + j], perc = m[j];
+            const float S = mag[(r + HALF) * LDS + c + j + HALF];
+            gh[r * LDG + c + j] = S * softmask2(harm, perc * margin_h, split);
+            gp[r * LDG + c + j] = S * softmask2(perc, harm * margin_p, split);
+        }
+    }
+    __syncthreads();
+    // phase 3: (S * mask) * exp(i angle(D)): phase = D / |D| (1 when |D| = 0); coalesced along bins
+    for (int o = threadIdx.x; o < TT * TF; o += HP_THREADS) {
         const int r = o / TF, c = o - r * TF;
         const int t = t0 + r, f = f0 + c;
         if (t >= n_frames || f >= n_bins) continue;
-        float v[31];
-        // median along time (window rows r .. r+30 at column c+15) -> harmonic-enhanced
-#pragma unroll
-        for (int k = 0; k < KS; ++k) v[k] = mag[(r + k) * LDS + c + HALF];
-        const float harm = median31(v);
-        // median along frequency (row r+15, columns c .. c+30) -> percussive-enhanced
-#pragma unroll
-        for (int k = 0; k < KS; ++k) v[k] = mag[(r + HALF) * LDS + c + k];
-        const float perc = median31(v);
-
         const long long idx = ((long long)clip * n_frames + t) * ld + f;
         const float2 z = __ldg(&D[idx]);
         const float S = mag[(r + HALF) * LDS + c + HALF];
-        const float split = (margin_h == 1.f && margin_p == 1.f) ? 0.5f : 0.f;  // rosa/spectral.py:158
-        // (S * mask) * exp(i angle(D)): phase = D / |D| (1 when |D| = 0)
         float2 ph = make_float2(1.f, 0.f);
         if (S > 0.f) ph = make_float2(z.x / S, z.y / S);
         if (out_h) {
-            const float g = S * softmask2(harm, perc * margin_h, split);
+            const float g = gh[r * LDG + c];
             out_h[idx] = make_float2(g * ph.x, g * ph.y);
         }
         if (out_p) {
-            const float g = S * softmask2(perc, harm * margin_p, split);
+            const float g = gp[r * LDG + c];
             out_p[idx] = make_float2(g * ph.x, g * ph.y);
         }
     }
@@ -104,7 +145,7 @@ extern "C" int ssar_hpss(const float* stft, int n_clips, int n_frames, int n_bin
     SSAR_REQUIRE(n_frames > HALF && n_bins > HALF, "hpss: reflect padding of 15 needs more than 15 frames and bins");
     SSAR_REQUIRE(n_clips <= 65535, "hpss: too many clips per launch");
     dim3 grid(ssar_div_up(n_bins, TF), ssar_div_up(n_frames, TT), n_clips);
-    hpss_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float2*>(stft), n_frames, n_bins, ld,
+    hpss_kernel<<<grid, HP_THREADS, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float2*>(stft), n_frames, n_bins, ld,
                                                        margin_harm, margin_perc, reinterpret_cast<float2*>(out_harm),
                                                        reinterpret_cast<float2*>(out_perc));
     return ssar_launch_status("hpss");
