@@ -71,6 +71,7 @@ def lib():
         _lib.ssar_last_error.restype = C.c_char_p
         _lib.ssar_biquad_scratch_bytes.restype = C.c_longlong
         _lib.ssar_piptrack_capacity.restype = C.c_longlong
+        _lib.ssar_mix_gemm_tc_scratch_bytes.restype = C.c_longlong
         if _lib.ssar_abi_version() != 1:
             raise SsarError("libssar_b200.so ABI version mismatch; rebuild")
     return _lib

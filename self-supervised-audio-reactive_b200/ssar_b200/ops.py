@@ -474,6 +474,9 @@ def plp_from_onset(onset_env: torch.Tensor, sr, hop_length: int = 1024, win_leng
 # ------------------------------------------------------------------------------------------------
 # trajectory construction (csrc/traj_mix.cu, csrc/traj_noise.cu)
 # ------------------------------------------------------------------------------------------------
+USE_TENSOR_CORE_MIX = True  # False: always the CUDA-core fp32 GEMM (ssar_mix_gemm)
+
+
 def mix_gemm(weights: torch.Tensor, basis: torch.Tensor, out: torch.Tensor | None = None, group_cols: int | None = None,
              col_begin: int = 0, col_end: int | None = None, row_alpha=None, row_beta=None):
     """out[t, n] = row_alpha[t] * out[t, n] + row_beta[t] * sum_k weights[t, g(n), k] * basis[k, n].
@@ -498,6 +501,14 @@ def mix_gemm(weights: torch.Tensor, basis: torch.Tensor, out: torch.Tensor | Non
         group_cols = N // G
     if col_end is None:
         col_end = N
+    # tensor-core path (tcgen05, fp16 x 3-term split, fp32-accurate): whole-row renders of up to 192 basis rows
+    if (USE_TENSOR_CORE_MIX and row_alpha is None and row_beta is None and col_begin == 0 and col_end == N and K <= 192
+            and T >= 128 and group_cols % 128 == 0 and N % group_cols == 0 and N // group_cols == G):
+        nb = int(cabi.lib().ssar_mix_gemm_tc_scratch_bytes(C.c_int(T), C.c_int(G), C.c_int(K), C.c_int(N)))
+        scratch = torch.empty(nb, dtype=torch.uint8, device=out.device)
+        cabi.call("ssar_mix_gemm_tc", ptr(weights), i64(G * K), i64(K), i32(group_cols), ptr(basis), i64(N), ptr(out), i64(N),
+                  i32(T), i32(K), i32(N), ptr(scratch), nbytes=cabi.nbytes_of(weights, basis) + T * N * 4)
+        return out
     cabi.call("ssar_mix_gemm", ptr(weights), i64(G * K), i64(K), i32(group_cols), ptr(basis), i64(N), ptr(out), i64(N),
               i32(T), i32(K), i32(col_begin), i32(col_end), ptr(row_alpha), ptr(row_beta),
               nbytes=cabi.nbytes_of(weights, basis) + T * (col_end - col_begin) * 4 * (2 if row_alpha is not None else 1))

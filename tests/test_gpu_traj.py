@@ -188,3 +188,27 @@ def test_subpatch_kernel_vs_separate_steps():
     src = torch.rand(Tn, 5, generator=g).cuda()
     out = ops.subpatch_merge(torch.full((Tn, G, P), float("nan"), device="cuda"), 0, G, sel, src, sigma=0, alpha=0.0, beta=1.0)
     assert torch.equal(out[:, 1, :5], src) and float(out[:, :, 5:].abs().max()) == 0.0
+
+
+def test_tensor_core_mix_vs_fp32_kernel_and_fp64():
+    """ssar_mix_gemm_tc (tcgen05, fp16 3-term split, TMA in / TMA out) against the CUDA-core fp32 kernel and an fp64
+    product: full-size render, ragged row counts (TMA clips the last row block), one group, K not a multiple of 64."""
+    from ssar_b200 import ops
+
+    g = torch.Generator("cpu").manual_seed(11)
+    try:
+        for Tn, G, K in [(5760, 3, 180), (333, 3, 192), (1000, 1, 64), (129, 3, 7), (4097, 2, 100)]:
+            W = (torch.rand(Tn, G, K, generator=g) * (torch.rand(Tn, G, K, generator=g) < 0.5)).cuda()
+            P = torch.randn(K, 18, 512, generator=g).cuda()
+            ops.USE_TENSOR_CORE_MIX = False
+            ref32 = ops.mix_gemm(W, P)
+            ops.USE_TENSOR_CORE_MIX = True
+            launches = __import__("ssar_b200._cabi", fromlist=["x"]).launch_count
+            out = torch.full((Tn + 3, 18, 512), float("nan"), device="cuda")  # guard rows: the kernel must not touch them
+            got = ops.mix_gemm(W, P, out=out[:Tn])
+            assert torch.isnan(out[Tn:]).all()
+            ref64 = torch.einsum("tgk,kgn->tgn", W.double(), P.reshape(K, G, -1).double()).reshape(Tn, 18, 512)
+            assert rel_l2(got.double(), ref64) < 5e-6, (Tn, G, K)
+            assert rel_l2(got, ref32) < 5e-6, (Tn, G, K)
+    finally:
+        ops.USE_TENSOR_CORE_MIX = True
