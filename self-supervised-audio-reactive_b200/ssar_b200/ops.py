@@ -146,7 +146,7 @@ def minmax_keys(x: torch.Tensor, n_clips: int = 1, want_min=True, want_max=True)
     if want_max:
         mx = torch.empty(n_clips, dtype=torch.int32, device=x.device)
         fill_u32(mx, KEY_NEG_INF)
-    cabi.call("ssar_minmax_keys", ptr(x), i32(n_clips), i64(n_per), ptr(mn), ptr(mx))
+    cabi.call("ssar_minmax_keys", ptr(x), i32(n_clips), i64(n_per), ptr(mn), ptr(mx), nbytes=cabi.nbytes_of(x))
     return mn, mx
 
 
@@ -155,7 +155,7 @@ def onset_flux(mel: torch.Tensor, max_key: torch.Tensor, pad_width: int, aggrega
     B, T, nb = mel.shape
     out = torch.empty(B, T, dtype=torch.float32, device=mel.device)
     cabi.call("ssar_onset_flux", ptr(mel), ptr(max_key), i32(B), i32(T), i32(nb), i32(pad_width),
-              i32({"mean": 0, "median": 1}[aggregate]), f32(top_db), ptr(out))
+              i32({"mean": 0, "median": 1}[aggregate]), f32(top_db), ptr(out), nbytes=cabi.nbytes_of(mel, out))
     return out
 
 
@@ -163,7 +163,8 @@ def mfcc_from_mel(mel: torch.Tensor, max_key: torch.Tensor, dct: torch.Tensor, t
     B, T, nb = mel.shape
     n_mfcc = dct.shape[0]
     out = torch.empty(B, T, n_mfcc, dtype=torch.float32, device=mel.device)
-    cabi.call("ssar_mfcc", ptr(mel), ptr(max_key), ptr(dct), i32(B), i32(T), i32(nb), i32(n_mfcc), f32(top_db), ptr(out))
+    cabi.call("ssar_mfcc", ptr(mel), ptr(max_key), ptr(dct), i32(B), i32(T), i32(nb), i32(n_mfcc), f32(top_db), ptr(out),
+              nbytes=cabi.nbytes_of(mel, out))
     return out
 
 
@@ -173,7 +174,7 @@ def power_to_db(x: torch.Tensor, n_clips: int = 1, top_db: float | None = 80.0, 
     if top_db is not None and max_key is None:
         _, max_key = minmax_keys(x, n_clips, want_min=False)
     cabi.call("ssar_power_to_db", ptr(x), i32(n_clips), i64(x.numel() // max(n_clips, 1)), ptr(max_key),
-              f32(top_db if top_db is not None else 0.0), i32(top_db is not None), ptr(out))
+              f32(top_db if top_db is not None else 0.0), i32(top_db is not None), ptr(out), nbytes=cabi.nbytes_of(x, out))
     return out
 
 
@@ -237,7 +238,8 @@ def frames_rms(x: torch.Tensor, frame_length: int, hop: int, n_frames: int):
     x, _ = _as_batch(x)
     B, N = x.shape
     out = torch.empty(B, n_frames, dtype=torch.float32, device=x.device)
-    cabi.call("ssar_rms_frames", ptr(x), i64(N), i64(x.stride(0)), i32(B), i32(frame_length), i32(hop), i32(n_frames), ptr(out))
+    cabi.call("ssar_rms_frames", ptr(x), i64(N), i64(x.stride(0)), i32(B), i32(frame_length), i32(hop), i32(n_frames), ptr(out),
+              nbytes=cabi.nbytes_of(x, out))
     return out
 
 
@@ -259,7 +261,8 @@ def gauss1d(x: torch.Tensor, sigma: float, mode: str = "circular", batched: bool
         raise SsarError(f"gaussian_filter: unsupported padding mode {mode!r}")
     w = plan.gaussian_taps(float(sigma), radius, str(x.device))
     out = torch.empty_like(x)
-    cabi.call("ssar_gauss1d", ptr(x), i32(n_clips), i32(T), i64(inner), ptr(w), i32(radius), i32(PAD_MODES[mode]), ptr(out))
+    cabi.call("ssar_gauss1d", ptr(x), i32(n_clips), i32(T), i64(inner), ptr(w), i32(radius), i32(PAD_MODES[mode]), ptr(out),
+              nbytes=cabi.nbytes_of(x, out))
     return out
 
 
@@ -268,7 +271,7 @@ def col_minmax(x: torch.Tensor):
     B, T, Cc = x.shape
     mn = torch.empty(B, Cc, dtype=torch.float32, device=x.device)
     mx = torch.empty(B, Cc, dtype=torch.float32, device=x.device)
-    cabi.call("ssar_col_minmax", ptr(x), i32(B), i32(T), i32(Cc), ptr(mn), ptr(mx))
+    cabi.call("ssar_col_minmax", ptr(x), i32(B), i32(T), i32(Cc), ptr(mn), ptr(mx), nbytes=cabi.nbytes_of(x))
     return mn, mx
 
 
@@ -279,14 +282,14 @@ def col_quantile(x: torch.Tensor, q: float, subset: str = "all", interp: str = "
     cnt = torch.empty(B, Cc, dtype=torch.int32, device=x.device) if want_count else None
     ps, pd = (pre if pre is not None else (None, None))
     cabi.call("ssar_col_quantile", ptr(x), i32(B), i32(T), i32(Cc), i32({"all": 0, "peaks": 1}[subset]), f64(q),
-              i32({"linear": 0, "midpoint": 3}[interp]), ptr(ps), ptr(pd), ptr(out), ptr(cnt))
+              i32({"linear": 0, "midpoint": 3}[interp]), ptr(ps), ptr(pd), ptr(out), ptr(cnt), nbytes=cabi.nbytes_of(x))
     return (out, cnt) if want_count else out
 
 
 def clamp_cols(x: torch.Tensor, lo=None, hi=None):
     B, T, Cc = x.shape
     out = torch.empty_like(x)
-    cabi.call("ssar_clamp_cols", ptr(x), i32(B), i32(T), i32(Cc), ptr(lo), ptr(hi), ptr(out))
+    cabi.call("ssar_clamp_cols", ptr(x), i32(B), i32(T), i32(Cc), ptr(lo), ptr(hi), ptr(out), nbytes=cabi.nbytes_of(x, out))
     return out
 
 
@@ -295,7 +298,8 @@ def normalize(x: torch.Tensor, n_clips: int = 1, eps: float = 1e-8):
     x = x.contiguous()
     mn, mx = minmax_keys(x, n_clips)
     out = torch.empty_like(x)
-    cabi.call("ssar_normalize", ptr(x), i32(n_clips), i64(x.numel() // max(n_clips, 1)), ptr(mn), ptr(mx), f32(eps), ptr(out))
+    cabi.call("ssar_normalize", ptr(x), i32(n_clips), i64(x.numel() // max(n_clips, 1)), ptr(mn), ptr(mx), f32(eps), ptr(out),
+              nbytes=cabi.nbytes_of(x, out))
     return out
 
 
@@ -305,7 +309,7 @@ def emphasize(x: torch.Tensor, strength: float, percentile: float):
     scratch = torch.empty(2 * B * Cc, dtype=torch.float32, device=x.device)
     out = torch.empty_like(x)
     cabi.call("ssar_emphasize", ptr(x), i32(B), i32(T), i32(Cc), ptr(mn), ptr(mx), f32(strength), f64(percentile / 100),
-              ptr(scratch), ptr(out))
+              ptr(scratch), ptr(out), nbytes=cabi.nbytes_of(x, out))
     return out
 
 
@@ -313,7 +317,8 @@ def spectral_flux(x: torch.Tensor, n_clips: int = 1):
     x = x.contiguous()
     T = x.shape[1] if n_clips > 1 else x.shape[0]
     out = torch.empty_like(x)
-    cabi.call("ssar_spectral_flux", ptr(x), i32(n_clips), i32(T), i64(x.numel() // max(n_clips * T, 1)), ptr(out))
+    cabi.call("ssar_spectral_flux", ptr(x), i32(n_clips), i32(T), i64(x.numel() // max(n_clips * T, 1)), ptr(out),
+              nbytes=cabi.nbytes_of(x, out))
     return out
 
 
@@ -321,7 +326,7 @@ def hwr_rowsum(x: torch.Tensor):
     """x [rows, inner] -> [rows]: sum of the half-wave rectified entries."""
     rows, inner = x.shape
     out = torch.empty(rows, dtype=torch.float32, device=x.device)
-    cabi.call("ssar_hwr_rowsum", ptr(x), i64(rows), i32(inner), ptr(out))
+    cabi.call("ssar_hwr_rowsum", ptr(x), i64(rows), i32(inner), ptr(out), nbytes=cabi.nbytes_of(x, out))
     return out
 
 
@@ -331,7 +336,7 @@ def feature_stats(x: torch.Tensor, stats: torch.Tensor | None = None):
     x = x.contiguous()
     if stats is None:
         stats = torch.zeros(3, Cc, dtype=torch.float64, device=x.device)
-    cabi.call("ssar_feature_stats", ptr(x), i64(x.numel() // Cc), i32(Cc), ptr(stats))
+    cabi.call("ssar_feature_stats", ptr(x), i64(x.numel() // Cc), i32(Cc), ptr(stats), nbytes=cabi.nbytes_of(x))
     return stats
 
 
@@ -344,10 +349,11 @@ def spectral_contrast(mag: torch.Tensor, bands, linear: bool = False, top_db: fl
     keys = torch.empty(2, B, dtype=torch.int32, device=dev)
     fill_u32(keys, KEY_NEG_INF)
     cabi.call("ssar_contrast_bands", ptr(mag), i64(F), i32(B), i32(T), i32(bands.n), ptr(bands.start), ptr(bands.count),
-              ptr(bands.q), i32(bands.max_count), ptr(peak), ptr(valley), ptr(keys[0]), ptr(keys[1]))
+              ptr(bands.q), i32(bands.max_count), ptr(peak), ptr(valley), ptr(keys[0]), ptr(keys[1]),
+              nbytes=cabi.nbytes_of(mag, peak, valley))
     out = torch.empty_like(peak)
     cabi.call("ssar_contrast_finish", ptr(peak), ptr(valley), ptr(keys[0]), ptr(keys[1]), i32(B), i64(T * bands.n),
-              i32(1 if linear else 0), f32(top_db), ptr(out))
+              i32(1 if linear else 0), f32(top_db), ptr(out), nbytes=cabi.nbytes_of(peak, valley, out))
     return out
 
 
@@ -368,7 +374,7 @@ def estimate_tuning(y: torch.Tensor, sr, n_fft: int = 2048, bins_per_octave: int
     mag = torch.empty_like(pitch)
     count = torch.empty(B, dtype=torch.int32, device=y.device)
     cabi.call("ssar_piptrack", ptr(S), i64(S.shape[2]), i32(B), i32(T), i32(S.shape[2]), i32(k_lo), i32(k_hi),
-              f32(threshold), f32(float(sr)), i32(n_fft), i64(cap), ptr(pitch), ptr(mag), ptr(count))
+              f32(threshold), f32(float(sr)), i32(n_fft), i64(cap), ptr(pitch), ptr(mag), ptr(count), nbytes=cabi.nbytes_of(S))
     idx = torch.empty(B, dtype=torch.int32, device=y.device)
     val = torch.empty(B, dtype=torch.float32, device=y.device)
     edges = plan.tuning_edges(str(y.device))
@@ -387,7 +393,7 @@ def chroma_from_cqt(C_fm: torch.Tensor, bins_per_octave: int = 36, n_chroma: int
     out = torch.empty(B, T, n_chroma, dtype=torch.float32, device=C_fm.device)
     cabi.call("ssar_chroma_from_cqt", ptr(C_fm), i64(nb), i32(B), i32(T), i32(nb), ptr(cmap), i32(n_chroma),
               i32(1 if quantize else 0), ptr(knots), ptr(sa), ptr(sb), ptr(sc), ptr(sd), i32(knots.numel()),
-              f32(0.25), f32(20.0), ptr(out))
+              f32(0.25), f32(20.0), ptr(out), nbytes=cabi.nbytes_of(C_fm, out))
     return out
 
 
@@ -397,7 +403,7 @@ def cens_smooth(q: torch.Tensor, window: torch.Tensor | None, l2: bool = True):
         window = torch.ones(1, dtype=torch.float32, device=q.device)
     out = torch.empty_like(q)
     cabi.call("ssar_cens_smooth", ptr(q), i32(B), i32(T), i32(nc), ptr(window), i32(window.numel()), i32(1 if l2 else 0),
-              ptr(out))
+              ptr(out), nbytes=cabi.nbytes_of(q, out))
     return out
 
 
@@ -407,7 +413,7 @@ def tonnetz(chroma: torch.Tensor):
     nc = chroma.shape[-1]
     out = torch.empty(chroma.shape[:-1] + (6,), dtype=torch.float32, device=chroma.device)
     cabi.call("ssar_tonnetz", ptr(chroma), i64(chroma.numel() // nc), i32(nc), ptr(plan.tonnetz_phi(nc, str(chroma.device))),
-              i32(6), ptr(out))
+              i32(6), ptr(out), nbytes=cabi.nbytes_of(chroma, out))
     return out
 
 
@@ -464,7 +470,8 @@ def plp_from_onset(onset_env: torch.Tensor, sr, hop_length: int = 1024, win_leng
         keep &= ~(freqs > tempo_max)
     idx = keep.nonzero().flatten()
     k_lo, k_hi = (int(idx[0]), int(idx[-1]) + 1) if len(idx) else (0, 0)
-    cabi.call("ssar_plp_peaks", ptr(tg), i64(F), i32(B), i32(T + 1), i32(F), i32(k_lo), i32(k_hi))
+    cabi.call("ssar_plp_peaks", ptr(tg), i64(F), i32(B), i32(T + 1), i32(F), i32(k_lo), i32(k_hi),
+              nbytes=2 * cabi.nbytes_of(tg))
     pulse = istft(tg, win, 1, torch.hann_window, T)
     zero = torch.zeros(B, 1, dtype=torch.float32, device=pulse.device)
     pulse = clamp_cols(pulse.view(B, T, 1), zero, None).view(B, T)  # clamp(pulse, 0, pulse.max())
@@ -521,7 +528,8 @@ def weights_merge(weights: torch.Tensor, seq: torch.Tensor, g_begin: int, g_end:
     T, G, K = weights.shape
     a_t, b_t = (alpha if torch.is_tensor(alpha) else None), (beta if torch.is_tensor(beta) else None)
     cabi.call("ssar_weights_merge", ptr(weights), i32(T), i32(G), i32(K), i32(g_begin), i32(g_end), ptr(seq.contiguous()),
-              ptr(a_t), ptr(b_t), f32(0.0 if a_t is not None else alpha), f32(0.0 if b_t is not None else beta))
+              ptr(a_t), ptr(b_t), f32(0.0 if a_t is not None else alpha), f32(0.0 if b_t is not None else beta),
+              nbytes=T * (g_end - g_begin) * K * 8 + cabi.nbytes_of(seq))
     return weights
 
 
@@ -540,7 +548,8 @@ def subpatch_merge(weights: torch.Tensor, g_begin: int, g_end: int, selection: t
         radius, taps = 0, None
     cabi.call("ssar_subpatch_merge", ptr(weights), i32(T), i32(G), i32(P), i32(g_begin), i32(g_end), ptr(selection), i32(K),
               ptr(src), i64(src.stride(0)), f32(src_scale), i32(1 if lerp else 0), ptr(taps), i32(radius), ptr(mod),
-              i64(mod.stride(0) if mod is not None else 0), f32(mod_scale), f32(alpha), f32(beta))
+              i64(mod.stride(0) if mod is not None else 0), f32(mod_scale), f32(alpha), f32(beta),
+              nbytes=T * (g_end - g_begin) * P * (4 if (mod is None and alpha == 0.0) else 8) + T * K * 4)
     return weights
 
 
@@ -550,7 +559,8 @@ def onehot_gauss(labels: torch.Tensor, n_classes: int, sigma: float):
     radius = min(int(sigma * 4), 3 * T)
     taps = plan.gaussian_taps(float(sigma), radius, str(labels.device))
     out = torch.empty(T, n_classes, dtype=torch.float32, device=labels.device)
-    cabi.call("ssar_onehot_gauss", ptr(labels), i32(T), i32(n_classes), ptr(taps), i32(radius), ptr(out))
+    cabi.call("ssar_onehot_gauss", ptr(labels), i32(T), i32(n_classes), ptr(taps), i32(radius), ptr(out),
+              nbytes=cabi.nbytes_of(labels, out))
     return out
 
 
@@ -559,7 +569,8 @@ def rows_affine(x: torch.Tensor, mu=None, sig=None):
     x = x.contiguous()
     rows = x.shape[0]
     out = torch.empty_like(x)
-    cabi.call("ssar_rows_affine", ptr(x), i64(rows), i64(x.numel() // max(rows, 1)), ptr(mu), ptr(sig), ptr(out))
+    cabi.call("ssar_rows_affine", ptr(x), i64(rows), i64(x.numel() // max(rows, 1)), ptr(mu), ptr(sig), ptr(out),
+              nbytes=cabi.nbytes_of(x, out))
     return out
 
 
@@ -573,5 +584,5 @@ def noise_eval(ops_list, i: int, b: int, height: int, width: int, device):
     scratch = torch.empty(max(n_loops * b, 1), dtype=torch.float32, device=device)
     out = torch.empty(b, height, width, dtype=torch.float32, device=device)
     cabi.call("ssar_noise_eval", ptr(dev_ops), C.cast(arr, C.c_void_p), i32(n), i32(i), i32(b), i32(height), i32(width),
-              ptr(scratch), ptr(out))
+              ptr(scratch), ptr(out), nbytes=cabi.nbytes_of(out))
     return out

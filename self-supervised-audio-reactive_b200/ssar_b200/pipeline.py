@@ -199,7 +199,7 @@ def patch_features_batch(feats: torch.Tensor):
 
 
 def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, segmentations, tempo=120.0, seed=42,
-                         rng_device="cuda", workers=None, chunk=8):
+                         rng_device="cuda", workers=None, chunk=8, serial=False):
     """The north-star unit for a batch of clips: waveforms [B, N] -> (features [B, T, 59], latents [B, T, 18, 512]).
     Tempo and segmentations are inputs (random/mir.py:28-42 is CPU librosa / scipy work outside the path).
     rng_device: where the Patch generator lives ("cpu" reproduces a CPU-seeded reference run bit for bit in its draws;
@@ -213,7 +213,9 @@ def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, se
         values; its read-backs then never queue behind the feature kernels);
       * calling thread: as soon as a chunk's features are queued, binds them to that chunk's patches and renders
         (one fused launch per latent sub-patch, one mixing GEMM per clip, the noise-basis draws).
-    workers: sampler threads (CPU generators only: their large basis draws release the GIL; CUDA generators use one)."""
+    workers: sampler threads (CPU generators only: their large basis draws release the GIL; CUDA generators use one).
+    serial: queue everything from the calling thread on the current stream (no helper threads, no side streams) — the
+    mode bench.py uses for its per-kernel CUDA-event pass, where concurrent streams would stretch the event intervals."""
     import queue
     import threading
 
@@ -233,6 +235,23 @@ def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, se
     chunk = max(1, min(int(chunk), B))
     bounds = [(c0, min(c0 + chunk, B)) for c0 in range(0, B, chunk)]
     checks = []
+    if serial:
+        feats_chunks, latents, noises = [], None, [None] * B
+        with torch.cuda.device(dev), torch.cuda.stream(stream):
+            for c0, c1 in bounds:
+                f = audio2features_batch(audio[c0:c1].to(dev, non_blocking=True), sr, fps, deferred_checks=checks)
+                pf = patch_features_batch(f)
+                feats_chunks.append(f)
+                if latents is None:
+                    latents = torch.empty(B, f.shape[1], palette.shape[1], palette.shape[2], dtype=torch.float32, device=dev)
+                for b in range(c0, c1):
+                    patch = Patch(None, segmentations, tempo, fps=fps, seed=seed + b, device=rng_device)
+                    patch.bind({k: v[b - c0] for k, v in pf.items()})
+                    noises[b] = patch.forward(palette, downscale_factor=4, latents_out=latents[b])[1]
+            feats = feats_chunks[0] if len(feats_chunks) == 1 else torch.cat(feats_chunks, dim=0)
+        for check in checks:
+            check()
+        return feats, latents, noises
     pool = _pool(max(workers, 1) + 2)
     ready_feats = queue.Queue()
 
