@@ -355,6 +355,31 @@ typedef struct {
 int ssar_noise_eval(const ssar_noise_op* ops_device, const ssar_noise_op* ops_host, int n_ops, int first_frame,
                     int n_frames, int height, int width, float* loop_scratch, float* out, void* stream);
 
+/* ---- generator draws, batched (csrc/philox_draws.cu) -------------------------------------------------------------
+ * The reference draws with torch calls on a seeded torch.Generator; on a CUDA generator these entry points produce the
+ * values the per-call sequence produces (same Philox4x32-10 seed / subsequence / offset per element).              */
+
+/* Generator-offset increment of ONE torch.randn(numel) call on the current device (ATen nullary kernel geometry). */
+long long ssar_philox_normal_increment(long long numel);
+
+/* torch.randn(numel[s], generator) for s = 0..n_segments-1 issued back to back from generator offset `first_offset`
+ * (ssar/random/patch.py:123-131 base noise, ssar/random/noise.py:15,31,46 module bases).  dst / numel: HOST arrays (dst
+ * holds device pointers).  *end_offset (host, optional) = generator offset after the last call.                     */
+int ssar_philox_normal_segments(float* const* dst, const long long* numel, int n_segments, long long seed,
+                                long long first_offset, long long* end_offset, void* stream);
+
+/* Draw ops of a sampler program (one torch call each on <= 256 elements). */
+#define SSAR_DRAW_RANDN 0       /* torch.randn(())                        -> 1 float                                 */
+#define SSAR_DRAW_EXPONENTIAL 1 /* empty(n).exponential_(1) (multinomial) -> n floats                                */
+/* Patch.__init__'s config sampler (ssar/random/patch.py:41-66: randint / rand / random_choice / skewnorm draws) for
+ * n_seeds generators seeded seeds[i], one warp per seed.  program (device): int[2 * n_ops] = kinds then sizes of the
+ * head ops (after the randint + rand of :41-42), of one latent config (:77-91) and of one noise config (:93-106).
+ * out [n_seeds, capacity] floats: num_base_latents, rand() for sigma, head draws, latent configs, noise configs;
+ * counts [n_seeds, 3] = (n latent configs, n noise configs, floats produced); end_offset [n_seeds] generator offsets. */
+int ssar_patch_sample(const long long* seeds, int n_seeds, const int* program, int n_head_ops, int n_latent_ops,
+                      int n_noise_ops, int min_subpatches, int max_subpatches, int capacity, float* out, int* counts,
+                      long long* end_offset, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -6,6 +6,7 @@ torch's current stream.  Layout convention: spectra are frame-major `[clip, fram
 from __future__ import annotations
 
 import ctypes as C
+import math
 
 import torch
 
@@ -586,3 +587,83 @@ def noise_eval(ops_list, i: int, b: int, height: int, width: int, device):
     cabi.call("ssar_noise_eval", ptr(dev_ops), C.cast(arr, C.c_void_p), i32(n), i32(i), i32(b), i32(height), i32(width),
               ptr(scratch), ptr(out), nbytes=cabi.nbytes_of(out))
     return out
+
+
+# ------------------------------------------------------------------------------------------------
+# batched generator draws (csrc/philox_draws.cu)
+# ------------------------------------------------------------------------------------------------
+_PHILOX_OK = {}
+
+
+def philox_normal_increment(numel: int) -> int:
+    fn = cabi.lib().ssar_philox_normal_increment
+    fn.restype = C.c_longlong
+    return int(fn(C.c_longlong(int(numel))))
+
+
+def _philox_normal_raw(shapes, seed: int, first_offset: int, device):
+    numels = [int(math.prod(s)) for s in shapes]
+    total = sum(numels)
+    flat = torch.empty(max(total, 1), dtype=torch.float32, device=device)
+    n = len(shapes)
+    base = flat.data_ptr()
+    ptrs, o = (C.c_void_p * max(n, 1))(), 0
+    for i, ne in enumerate(numels):
+        ptrs[i] = base + 4 * o
+        o += ne
+    ne_arr = (C.c_longlong * max(n, 1))(*numels)
+    end = C.c_longlong(0)
+    cabi.call("ssar_philox_normal_segments", ptrs, ne_arr, i32(n), i64(seed), i64(first_offset), C.byref(end),
+              nbytes=4 * total)
+    views, o = [], 0
+    for s, ne in zip(shapes, numels):
+        views.append(flat[o : o + ne].view(s))
+        o += ne
+    return views, int(end.value)
+
+
+def philox_batched_ok(device) -> bool:
+    """One-time check per device that the batched draws equal torch's per-call CUDA draws bit for bit (values and
+    generator offsets, small / medium / grid-saturating sizes).  When it fails (another torch build with a different
+    kernel geometry) the callers keep issuing the per-call torch draws — still on the GPU, just one launch per draw."""
+    device = torch.device(device)
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    ok = _PHILOX_OK.get(key)
+    if ok is None:
+        with torch.cuda.device(key):
+            g = torch.Generator(device)
+            g.manual_seed(0x5EED1234)
+            g.set_offset(40)
+            shapes = [(3, 4, 4), (2, 7, 64, 64), (3, 256, 256), (2, 20, 256, 256)]
+            ref = [torch.randn(s, generator=g, device=device) for s in shapes]
+            got, end = _philox_normal_raw(shapes, 0x5EED1234, 40, device)
+            ok = end == g.get_offset() and all(torch.equal(a, b) for a, b in zip(ref, got))
+        _PHILOX_OK[key] = ok
+        if not ok:
+            import warnings
+
+            warnings.warn("ssar_b200: batched Philox draws differ from this torch build's per-call draws; "
+                          "using one torch call per draw")
+    return ok
+
+
+def philox_normal_segments(shapes, rng: torch.Generator):
+    """[torch.randn(s, generator=rng, device=rng.device) for s in shapes] in ONE launch (a few when there are more than
+    96 shapes); advances `rng` exactly as the per-call sequence would.  CUDA generators only."""
+    dev = rng.device
+    views, end = _philox_normal_raw(shapes, rng.initial_seed(), rng.get_offset(), dev)
+    rng.set_offset(end)
+    return views
+
+
+def patch_sample(seeds: torch.Tensor, program: torch.Tensor, n_head: int, n_lat: int, n_noise: int, min_sub: int,
+                 max_sub: int, capacity: int):
+    """seeds int64 [B] (device), program int32 [2 * n_ops] (device) -> (floats [B, capacity], counts int32 [B, 3],
+    end_offset int64 [B]) — see `ssar_patch_sample`."""
+    B = seeds.numel()
+    out = torch.empty(B, capacity, dtype=torch.float32, device=seeds.device)
+    counts = torch.empty(B, 3, dtype=torch.int32, device=seeds.device)
+    end = torch.empty(B, dtype=torch.int64, device=seeds.device)
+    cabi.call("ssar_patch_sample", ptr(seeds), i32(B), ptr(program), i32(n_head), i32(n_lat), i32(n_noise), i32(min_sub),
+              i32(max_sub), i32(capacity), ptr(out), ptr(counts), ptr(end))
+    return out, counts, end

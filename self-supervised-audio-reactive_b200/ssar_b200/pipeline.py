@@ -219,7 +219,7 @@ def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, se
     import queue
     import threading
 
-    from .random.patch import Patch, precapture_sampler_graphs
+    from .random.patch import Patch, precapture_sampler_graphs, sampler_kernel_ready
 
     # `audio` may live in (pinned) HOST memory: the feature thread then stages it chunk by chunk on a copy stream, one
     # chunk ahead of the kernels (input staging only — there is no CPU compute path)
@@ -229,7 +229,8 @@ def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, se
     stream = torch.cuda.current_stream(dev)
     if str(rng_device).startswith("cuda"):
         with torch.cuda.device(dev):
-            precapture_sampler_graphs(dev, segmentations)  # no-op once captured
+            if not sampler_kernel_ready(dev, segmentations):  # fallback sampler: one CUDA graph per sub-patch count
+                precapture_sampler_graphs(dev, segmentations)  # no-op once captured
     workers = default_patch_workers(rng_device) if workers is None else int(workers)
     B = audio.shape[0]
     chunk = max(1, min(int(chunk), B))
@@ -244,8 +245,10 @@ def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, se
                 feats_chunks.append(f)
                 if latents is None:
                     latents = torch.empty(B, f.shape[1], palette.shape[1], palette.shape[2], dtype=torch.float32, device=dev)
+                chunk_patches = Patch.sample_batch([seed + b for b in range(c0, c1)], segmentations, tempo, fps=fps,
+                                                   device=rng_device)
                 for b in range(c0, c1):
-                    patch = Patch(None, segmentations, tempo, fps=fps, seed=seed + b, device=rng_device)
+                    patch = chunk_patches[b - c0]
                     patch.bind({k: v[b - c0] for k, v in pf.items()})
                     noises[b] = patch.forward(palette, downscale_factor=4, latents_out=latents[b])[1]
             feats = feats_chunks[0] if len(feats_chunks) == 1 else torch.cat(feats_chunks, dim=0)
@@ -290,6 +293,15 @@ def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, se
     def sample_job(indices):
         try:
             with torch.cuda.device(dev), torch.cuda.stream(_side_stream(dev)):
+                if str(rng_device).startswith("cuda"):
+                    # one sampler kernel + one read-back per chunk of clips (Patch.sample_batch)
+                    for c0 in range(0, len(indices), chunk):
+                        part = indices[c0 : c0 + chunk]
+                        for b, pt in zip(part, Patch.sample_batch([seed + b for b in part], segmentations, tempo, fps=fps,
+                                                                  device=rng_device)):
+                            patches[b] = pt
+                            sampled[b].set()
+                    return
                 for b in indices:
                     patches[b] = Patch(None, segmentations, tempo, fps=fps, seed=seed + b, device=rng_device)
                     sampled[b].set()

@@ -283,12 +283,26 @@ class NoiseProgram(Noise):
     __call__ = forward
 
 
-def base_noise_programs(rng, length, sizes, n_loops, sigma, device):
-    """patch.py:123-131: one `Loop` per layer (same draw per layer: randn(3, H, W))."""
+def noise_draw_shapes(sizes, noise_patches, features):
+    """Shapes of every basis draw `base_noise_programs` + `noise_patch_programs` make, in draw order (patch.py:123-131,
+    noise.py:89-140) — lets `Patch.forward` issue all of them as ONE batched Philox launch."""
+    shapes = [(3, int(h), int(w)) for (h, w) in sizes]
+    for sp in noise_patches:
+        M = features[sp["seq_feat"]].shape[1]
+        for n in NOISE_LAYER_RANGES[sp["merge_depth"]]:
+            h, w = int(sizes[n][0]), int(sizes[n][1])
+            shapes.append((2, M, h, w) if sp["patch_type"] == "blend" else (M, h, w) if sp["patch_type"] == "multiply"
+                          else (3, h, w))
+    return shapes
+
+
+def base_noise_programs(rng, length, sizes, n_loops, sigma, device, draws=None):
+    """patch.py:123-131: one `Loop` per layer (same draw per layer: randn(3, H, W)).
+    draws: iterator over pre-drawn bases (batched Philox launch, same values) instead of one torch.randn per layer."""
     progs = []
     for size in sizes:
         p = NoiseProgram(length, size, device)
-        noise = torch.randn((3, size[0], size[1]), generator=rng, device=rng.device)
+        noise = next(draws) if draws is not None else torch.randn((3, size[0], size[1]), generator=rng, device=rng.device)
         if noise.device != p.device:
             noise = noise.to(p.device)
         p.leaf(LOOP, noise, plan.loop_phase(n_loops, int(length), str(device)), p0=sigma / 50, to_acc=1)
@@ -297,7 +311,7 @@ def base_noise_programs(rng, length, sizes, n_loops, sigma, device):
 
 
 def noise_patch_programs(rng, progs, features, tempo, fps, patch_type, loop_bars, seq_feat, seq_feat_weight, mod_feat,
-                         mod_feat_weight, merge_type, merge_depth, noise_mean, noise_std):
+                         mod_feat_weight, merge_type, merge_depth, noise_mean, noise_std, draws=None):
     """ssar/random/noise.py:89-140 on `NoiseProgram`s: same generator draws (one basis per wrapped layer, in layer order),
     same arithmetic (the kernel evaluates the same ops the module tree would emit)."""
     layers = NOISE_LAYER_RANGES[merge_depth]
@@ -318,7 +332,9 @@ def noise_patch_programs(rng, progs, features, tempo, fps, patch_type, loop_bars
     for n in layers:
         p = progs[n]
         h, w = p.size
-        if patch_type == "blend":
+        if draws is not None:
+            noise = next(draws)
+        elif patch_type == "blend":
             noise = torch.randn((2, M, h, w), generator=rng, device=rdev)
         elif patch_type == "multiply":
             noise = torch.randn((M, h, w), generator=rng, device=rdev)

@@ -12,8 +12,8 @@ import torch
 from . import DEVICE
 from .latent import LatentWeights, latent_patch, merge_coefficients, sequence_weights, spline_loop_latents  # noqa: F401
 from .mir import ALLFEATS, UNITFEATS
-from .noise import Loop, base_noise_programs, noise_patch, noise_patch_programs  # noqa: F401
-from .. import plan
+from .noise import Loop, base_noise_programs, noise_draw_shapes, noise_patch, noise_patch_programs  # noqa: F401
+from .. import ops, plan
 
 
 def random_choice(rng, options, weights=None, n=1, replacement=False):
@@ -99,10 +99,12 @@ class _Sampler:
             floats = self.flat().cpu().numpy() if self.floats else None
         f = np.float32
 
-        def host_probs(p, weights):
-            key = (p.shape[0], None if weights is None else tuple(weights))
+        def host_probs(p, weights, n_options):
+            key = (n_options, None if weights is None else tuple(weights))
             h = self._host_probs.get(key)
             if h is None:
+                if p is None:  # dry sampler: the same fp32 expressions as `_probs`, evaluated by torch on the host
+                    p = torch.ones(n_options) / n_options if weights is None else torch.tensor(weights) / np.sum(weights)
                 h = self._host_probs[key] = p.cpu().numpy()
             return h
 
@@ -110,7 +112,7 @@ class _Sampler:
             if d.kind == "choice":
                 options, p, weights = d.aux
                 q = floats[d.slot : d.slot + len(options)]
-                return options[int(np.argmax(host_probs(p, weights) / q))]  # fp32 IEEE division, first maximum
+                return options[int(np.argmax(host_probs(p, weights, len(options)) / q))]  # fp32 IEEE division, first maximum
             if d.kind == "randn":
                 return float(floats[d.slot]) * d.aux
             a, loc, scale = d.aux
@@ -130,6 +132,31 @@ class _Sampler:
             return o
 
         return walk(tree)
+
+
+class _DrySampler(_Sampler):
+    """Records the draw program of a config (which torch call, on how many elements) without drawing: the program
+    `ssar_patch_sample` executes on the device, and the deferred tree `resolve` turns the drawn floats into."""
+
+    def __init__(self):
+        super().__init__(None, ({}, {}, {}))
+        self.ops = []
+
+    def choice(self, options, weights=None):
+        n = len(options)
+        self.ops.append((1, n))  # SSAR_DRAW_EXPONENTIAL
+        self._n_floats += n
+        return _Deferred("choice", self._n_floats - n, (options, None, weights))
+
+    def randn(self, scale=1.0):
+        self.ops.append((0, 1))  # SSAR_DRAW_RANDN
+        self._n_floats += 1
+        return _Deferred("randn", self._n_floats - 1, scale)
+
+    def skewnorm(self, a, loc, scale):
+        self.ops += [(0, 1), (0, 1)]
+        self._n_floats += 2
+        return _Deferred("skewnorm", self._n_floats - 2, (a, loc, scale))
 
 
 DEPTHS = ["low", "mid", "high", "lowmid", "midhigh", "all"]
@@ -259,7 +286,127 @@ class _GraphSampler:
         return int(host[n_head]), 1 + 9 * float(host[n_head + 1]), loops_v, lat, noi, state
 
 
+class _KernelSampler:
+    """CUDA-generator path of the Patch sampler as ONE kernel for a whole batch of seeds (`ssar_patch_sample`): the
+    device walks the draw programs of patch.py:41-66 / 77-106 with the Philox streams the torch calls would use, the
+    host reads everything back with one copy and resolves the configs (`_Sampler.resolve`).  Checked once per device
+    against the eager torch sequence (`ok`); tests/test_gpu_philox.py checks it seed by seed."""
+
+    _instances = {}
+    _guard = __import__("threading").Lock()
+
+    @classmethod
+    def get(cls, device):
+        device = torch.device(device)
+        idx = device.index if device.index is not None else torch.cuda.current_device()
+        with cls._guard:
+            inst = cls._instances.get(idx)
+            if inst is None:
+                inst = cls._instances[idx] = cls(torch.device("cuda", idx))
+            return inst
+
+    def __init__(self, device):
+        self.device = device
+        self.programs = {}
+        self._ok = None
+
+    def program(self, ks):
+        key = tuple(ks)
+        prog = self.programs.get(key)
+        if prog is None:
+            head, lat, noi = _DrySampler(), _DrySampler(), _DrySampler()
+            head_tree = head.choice([1, 2, 4, 8, 16, 32, 64])
+            lat_tree = _latent_config(lat.choice, lat.skewnorm, list(ks))
+            noi_tree = _noise_config(noi.choice, noi.skewnorm, noi.randn)
+            ops_all = head.ops + lat.ops + noi.ops
+            dev_prog = torch.tensor([k for k, _ in ops_all] + [n for _, n in ops_all], dtype=torch.int32).to(self.device)
+            prog = self.programs[key] = (dev_prog, (head, head_tree), (lat, lat_tree), (noi, noi_tree))
+        return prog
+
+    def sample_many(self, seeds, ks, min_subpatches, max_subpatches):
+        """-> list of (num_base_latents, sigma_base_noise, loops_base_noise, latent configs, noise configs, end offset)."""
+        dev_prog, (head, head_tree), (lat, lat_tree), (noi, noi_tree) = self.program(ks)
+        cap = 2 + head._n_floats + (max_subpatches - 1) * (lat._n_floats + noi._n_floats)
+        with torch.cuda.device(self.device):
+            seeds_d = torch.tensor([int(s) for s in seeds], dtype=torch.int64).to(self.device)
+            out, counts, end = ops.patch_sample(seeds_d, dev_prog, len(head.ops), len(lat.ops), len(noi.ops),
+                                                min_subpatches, max_subpatches, cap)
+            # ONE read-back for the whole batch
+            packed = torch.cat([out.view(-1), counts.view(-1).float(), end.float()]).cpu().numpy()
+        B = len(seeds)
+        floats = packed[: B * cap].reshape(B, cap)
+        cnt = packed[B * cap : B * cap + 3 * B].reshape(B, 3).astype(np.int64)
+        ends = packed[B * cap + 3 * B :].astype(np.int64)
+        res = []
+        for b in range(B):
+            f = floats[b]
+            o = 2
+            loops = head.resolve(head_tree, f[o : o + head._n_floats])
+            o += head._n_floats
+            lats = []
+            for _ in range(cnt[b, 0]):
+                lats.append(lat.resolve(lat_tree, f[o : o + lat._n_floats]))
+                o += lat._n_floats
+            nois = []
+            for _ in range(cnt[b, 1]):
+                nois.append(noi.resolve(noi_tree, f[o : o + noi._n_floats]))
+                o += noi._n_floats
+            assert o == cnt[b, 2] <= cap
+            res.append((int(f[0]), 1 + 9 * float(f[1]), loops, lats, nois, int(ends[b])))
+        return res
+
+    def ok(self, segmentations_ks):
+        """One-time check per device: the kernel's draws for two seeds equal the eager deferred sampler's."""
+        if self._ok is None:
+            try:
+                ks = list(segmentations_ks)
+                got = self.sample_many([1234567, 42], ks, 5, 20)
+                good = True
+                for seed, g in zip([1234567, 42], got):
+                    rng = torch.Generator(self.device)
+                    rng.manual_seed(seed)
+                    ref = _eager_sample(rng, ks, 5, 20)
+                    good = good and ref == g[:5] and rng.get_offset() == g[5]
+                self._ok = bool(good)
+            except Exception:  # pragma: no cover - a torch build without get_offset etc.
+                self._ok = False
+            if not self._ok:
+                import warnings
+
+                warnings.warn("ssar_b200: ssar_patch_sample differs from this torch build's eager sampler draws; "
+                              "using the per-call sampler")
+        return self._ok
+
+
+def _eager_sample(rng, ks, min_subpatches, max_subpatches):
+    """patch.py:41-66 with one torch call per draw (deferred read-back) -> (num_base, sigma, loops, latent, noise)."""
+    sm = _Sampler(rng)
+    num_base_latents = torch.randint(3, 15, size=(), generator=rng, device=rng.device)
+    sigma_u = torch.rand((), generator=rng, device=rng.device)
+    loops_base_noise = sm.choice([1, 2, 4, 8, 16, 32, 64])
+    latent_patches = [
+        _latent_config(sm.choice, sm.skewnorm, ks)
+        for _ in range(torch.randint(min_subpatches, max_subpatches, size=(), generator=rng, device=rng.device))
+    ]
+    noise_patches = [
+        _noise_config(sm.choice, sm.skewnorm, sm.randn)
+        for _ in range(torch.randint(min_subpatches, max_subpatches, size=(), generator=rng, device=rng.device))
+    ]
+    loops, lats, nois = sm.resolve([loops_base_noise, latent_patches, noise_patches])
+    return int(num_base_latents.item()), 1 + 9 * sigma_u.item(), loops, lats, nois
+
+
 USE_SAMPLER_GRAPHS = True  # CUDA generators only; False = the eager deferred sampler
+USE_BATCHED_DRAWS = True   # CUDA generators only: noise bases of a Patch in one Philox launch (ssar_philox_normal_segments)
+USE_SAMPLER_KERNEL = True  # CUDA generators only: the config sampler as one kernel per batch of seeds (ssar_patch_sample)
+
+
+def sampler_kernel_ready(device, segmentations) -> bool:
+    """True when Patch sampling on `device` goes through `ssar_patch_sample` (checked against the eager draws once)."""
+    if not USE_SAMPLER_KERNEL:
+        return False
+    ks = np.unique([k for (_, k) in segmentations]).tolist()
+    return _KernelSampler.get(device).ok(ks)
 
 
 def precapture_sampler_graphs(device, segmentations, min_subpatches=5, max_subpatches=20):
@@ -278,7 +425,7 @@ class Patch:
     trajectory tensors live (defaults to the palette's device at forward time)."""
 
     def __init__(self, features, segmentations, tempo, fps=24, seed=42, min_subpatches=5, max_subpatches=20,
-                 device=DEVICE):
+                 device=DEVICE, presampled=None):
         rng = torch.Generator(device)
         rng.manual_seed(seed)
         self.seed = seed
@@ -289,6 +436,17 @@ class Patch:
         self.length = features[list(features.keys())[0]].shape[0] if features is not None else None
         self.segmentations = segmentations
         self.ks = np.unique([k for (_, k) in segmentations]).tolist()
+        if presampled is None and rng.device.type == "cuda" and USE_SAMPLER_KERNEL:
+            ksamp = _KernelSampler.get(rng.device)
+            if ksamp.ok(self.ks):
+                presampled = ksamp.sample_many([seed], self.ks, min_subpatches, max_subpatches)[0]
+        if presampled is not None:
+            (self.num_base_latents, self.sigma_base_noise, self.loops_base_noise, self.latent_patches, self.noise_patches,
+             end_offset) = presampled
+            if rng.device.type == "cuda":
+                rng.set_offset(end_offset)
+            self._sampler = None
+            return
         if rng.device.type == "cuda" and USE_SAMPLER_GRAPHS:
             (self.num_base_latents, self.sigma_base_noise, self.loops_base_noise, self.latent_patches, self.noise_patches,
              state) = _GraphSampler.get(rng.device).sample(seed, self.ks, min_subpatches, max_subpatches)
@@ -312,6 +470,20 @@ class Patch:
         self.num_base_latents = num_base_latents.item()
         self.sigma_base_noise = 1 + 9 * sigma_u.item()
         self._sampler = None
+
+    @classmethod
+    def sample_batch(cls, seeds, segmentations, tempo, fps=24, min_subpatches=5, max_subpatches=20, device=DEVICE):
+        """[Patch(None, segmentations, tempo, fps, seed=s, device=device) for s in seeds] with the config draws of all
+        seeds made by ONE kernel and read back with ONE copy (CUDA generators; per-seed construction otherwise)."""
+        device = torch.device(device)
+        pres = [None] * len(seeds)
+        if device.type == "cuda" and USE_SAMPLER_KERNEL and len(seeds):
+            ks = np.unique([k for (_, k) in segmentations]).tolist()
+            ksamp = _KernelSampler.get(device)
+            if ksamp.ok(ks):
+                pres = ksamp.sample_many(list(seeds), ks, min_subpatches, max_subpatches)
+        return [cls(None, segmentations, tempo, fps=fps, seed=int(s), min_subpatches=min_subpatches,
+                    max_subpatches=max_subpatches, device=device, presampled=p) for s, p in zip(seeds, pres)]
 
     def bind(self, features):
         """Attach the feature dict of a patch sampled with features=None (batched pipelines sample the configs — which
@@ -372,9 +544,14 @@ class Patch:
 
         sizes = [(round(aspect_ratio * size / downscale_factor), round(size / downscale_factor))
                  for size in [4, 8, 8, 16, 16, 32, 32, 64, 64, 128, 128, 256, 256, 512, 512, 1024, 1024]]
-        noise = base_noise_programs(self.rng, self.length, sizes, self.loops_base_noise, self.sigma_base_noise, dev)
+        draws = None
+        if self.rng.device.type == "cuda" and USE_BATCHED_DRAWS and ops.philox_batched_ok(self.rng.device):
+            # every basis draw of this patch in one launch: same Philox streams as the per-layer torch.randn calls
+            draws = iter(ops.philox_normal_segments(noise_draw_shapes(sizes, self.noise_patches, feats), self.rng))
+        noise = base_noise_programs(self.rng, self.length, sizes, self.loops_base_noise, self.sigma_base_noise, dev,
+                                    draws=draws)
         for sp in self.noise_patches:
-            noise = noise_patch_programs(self.rng, noise, feats, self.tempo, self.fps, **sp)
+            noise = noise_patch_programs(self.rng, noise, feats, self.tempo, self.fps, draws=draws, **sp)
         return latents, noise
 
     __call__ = forward
