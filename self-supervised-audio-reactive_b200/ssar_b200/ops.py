@@ -418,7 +418,7 @@ def tonnetz(chroma: torch.Tensor):
     return out
 
 
-def cqt(y: torch.Tensor, sr, hop_length: int = 1024, tuning_idx=None):
+def cqt(y: torch.Tensor, sr, hop_length: int = 1024, tuning_idx=None, sync_free: bool = False):
     """rosa/constantq.py:13-115 for the reference's only configuration (C1, 7 octaves x 36 bins, filter_scale 1,
     sparsity 0.01): returns the frame-major complex-as-real CQT [B, T, 252, 2] with 1/sqrt(length) applied.
     tuning_idx: int32 [B] from estimate_tuning (None -> estimate, like tuning=None in chroma_cqt)."""
@@ -433,7 +433,10 @@ def cqt(y: torch.Tensor, sr, hop_length: int = 1024, tuning_idx=None):
     if tuning_idx is None:
         tuning_idx, _ = estimate_tuning(y, sr, bins_per_octave=bpo)
     tables = plan.cqt_tables(float(sr), str(y.device))
-    slots = tables.slots_for(tuning_idx.cpu().tolist())  # one small D2H sync per batch: the basis is data-dependent
+    if sync_free:  # all tuned bases resident; the per-clip choice is a device gather (no read-back: graph-capturable)
+        slots = tables.slot_map()[tuning_idx.long()].contiguous()
+    else:
+        slots = tables.slots_for(tuning_idx.cpu().tolist())  # one small D2H sync per batch: the basis is data-dependent
     # octave signals: y_i = resample(y_{i-1}, /2, kaiser) * sqrt(2)
     sigs, hops = [y], [hop_length]
     rp = plan.resample_plan(2, 1, "kaiser_window", str(y.device))

@@ -374,6 +374,16 @@ class CqtTables:
             self.row_scale = torch.stack(self._rscale).contiguous().to(self.device)  # [n_slots, 252]
         return torch.tensor([self.slot_of[int(v)] for v in tuning_idx_host], dtype=torch.int32, device=self.device)
 
+    def slot_map(self):
+        """int32 device table tuning index -> slot with EVERY tuning's basis resident (101 x 36 rows, ~0.5 MB): lets a
+        batch pipeline pick each clip's basis on the device (`slot_map[tuning_idx]`) with no read-back — the form a
+        CUDA-graph capture of the feature path needs."""
+        n = len(cqt_tuning_values())
+        if getattr(self, "_slot_map", None) is None or len(self.slot_of) < n:
+            self.slots_for(range(n))
+            self._slot_map = torch.tensor([self.slot_of[i] for i in range(n)], dtype=torch.int32, device=self.device)
+        return self._slot_map
+
 
 @functools.lru_cache(maxsize=None)
 def cqt_tables(sr: float, device) -> CqtTables:

@@ -78,3 +78,39 @@ def test_audio2features_batch_matches_single():
     for b in range(2):
         fs = pipeline.audio2features_batch(xs[b : b + 1], 44100, 24)[0]
         assert rel_l2(fb[b], fs) < 1e-6
+
+
+def test_feature_graph_replay_equals_eager():
+    """The CUDA-graph replay of the feature path (pipeline.FeatureGraph: device-side choice of each clip's tuned CQT
+    basis, no read-back) gives the eager call's features bit for bit, replay after replay with new inputs."""
+    from ssar_b200 import pipeline
+
+    g = pipeline.FeatureGraph.get(2, 44100 * 45, 44100, 24, "cuda:0")
+    for ids in ((3, 9), (5, 1)):
+        xs = torch.stack([synth_clip(44100 * 45, 44100, i) for i in ids]).cuda()
+        checks = []
+        f, pf = g.run(xs, deferred_checks=checks)
+        for c in checks:
+            c()
+        fe = pipeline.audio2features_batch(xs, 44100, 24)
+        assert torch.equal(f, fe)
+        pe = pipeline.patch_features_batch(fe)
+        assert all(torch.equal(pf[k], pe[k]) for k in pe)
+
+
+def test_features_and_latents_graph_vs_serial():
+    """The threaded pipeline (feature graphs, batched sampler, side streams) == the serially queued one."""
+    from ssar_b200 import pipeline
+    from ssar_b200.synth import synth_patch_inputs
+
+    xs = torch.stack([synth_clip(44100 * 45, 44100, i) for i in (3, 9, 4)]).cuda()
+    _, segs, palette = synth_patch_inputs(1080, 0)
+    palette = palette.cuda()
+    fa, la, _ = pipeline.features_and_latents(xs, 44100, 24, palette, segs, chunk=2)
+    fb, lb, _ = pipeline.features_and_latents(xs, 44100, 24, palette, segs, chunk=2, serial=True)
+    torch.cuda.synchronize()
+    assert torch.equal(fa, fb) and torch.equal(la, lb)
+    # pinned host input: staged chunk by chunk
+    fc, lc, _ = pipeline.features_and_latents(xs.cpu().pin_memory(), 44100, 24, palette, segs, chunk=2)
+    torch.cuda.synchronize()
+    assert torch.equal(fa, fc) and torch.equal(la, lc)
