@@ -380,6 +380,12 @@ int ssar_patch_sample(const long long* seeds, int n_seeds, const int* program, i
                       int n_noise_ops, int min_subpatches, int max_subpatches, int capacity, float* out, int* counts,
                       long long* end_offset, void* stream);
 
+/* `count` consecutive torch.randperm(n, generator) calls (ssar/random/patch.py:113, ssar/random/latent.py:37: one per
+ * latent sub-patch) from generator offset first_offset, call k at first_offset + k * offset_stride.  bits = ATen's key
+ * width for n (ceil(log2(n - (6 n^2 + 1) / (12 ln 0.9)))); n <= 1024.  out: int64 [count, n] (device).            */
+int ssar_philox_randperm(long long seed, long long first_offset, long long offset_stride, int n, int bits, int count,
+                         long long* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -11,6 +11,7 @@
 // launch geometry of ATen's nullary distribution kernels: block 256, grid min(ceil(numel / 256), SMs * (max threads per
 // SM / 256)), unroll 4.  tests/test_gpu_philox.py checks both entry points bit for bit against the eager torch calls.
 #include <curand_kernel.h>
+#include <limits.h>
 
 #include "common.cuh"
 
@@ -151,6 +152,65 @@ __global__ void __launch_bounds__(128) patch_sample_kernel(const long long* __re
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// torch.randperm(n) on a CUDA generator, n <= 1024 (ATen randperm_out_cuda): int32 keys random_(INT_MIN, INT_MAX)
+// (element i = the 64-bit value of thread i's first two engine words, modulo 2^32 - 1), stable ascending sort of the indices by the low `bits`
+// key bits, then every run of equal keys is Fisher-Yates shuffled by its first thread from a second Philox state
+// (subsequence = position of the run, offset = key offset + 4).  One CTA per permutation; the stable sort is a
+// rank count (n^2 / CTA comparisons, n = 180 on the path).
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) randperm_kernel(unsigned long long seed, unsigned long long first_offset,
+                                                       unsigned long long stride, int n, int bits,
+                                                       long long* __restrict__ out) {
+    extern __shared__ int rp_sm[];
+    int* key = rp_sm;           // masked keys in element order
+    int* skey = rp_sm + n;      // masked keys in sorted order
+    int* data = rp_sm + 2 * n;  // permutation
+    const unsigned long long off = first_offset + stride * blockIdx.x;
+    const unsigned mask = bits >= 32 ? 0xffffffffu : ((1u << bits) - 1u);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        curandStatePhilox4_32_10_t st;
+        curand_init(seed, (unsigned long long)i, off, &st);
+        const uint4 r = curand4(&st);
+        // random_from_to with range = 2^32 - 1 takes ATen's 64-bit branch: two engine words form one 64-bit value
+        const unsigned long long r64 = (unsigned long long)r.x | ((unsigned long long)r.y << 32);
+        const long long v = (long long)(r64 % 4294967295ull) + (long long)INT_MIN;  // uniform_int_from_to(rand, range, base)
+        key[i] = (int)((unsigned)(int)v & mask);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const int k = key[i];
+        int pos = 0;
+        for (int j = 0; j < n; ++j) {
+            const int kj = key[j];
+            pos += (kj < k) || (kj == k && j < i);
+        }
+        skey[pos] = k;
+        data[pos] = i;
+    }
+    __syncthreads();
+    for (int tid = threadIdx.x; tid < n - 1; tid += blockDim.x) {
+        if (skey[tid] != skey[tid + 1]) continue;               // not in a run
+        if (tid != 0 && skey[tid] == skey[tid - 1]) continue;   // not the beginning of a run
+        int island = 0;
+        do { ++island; } while (tid + island < n && skey[tid + island] == skey[tid]);
+        curandStatePhilox4_32_10_t st;
+        curand_init(seed, (unsigned long long)tid, off + 4, &st);
+        int* d = data + tid;
+        for (int i = island - 1; i > 0; --i) {
+            const unsigned r = curand(&st) % (unsigned)(i + 1);
+            if ((unsigned)i != r) {
+                const int tmp = d[i];
+                d[i] = d[r];
+                d[r] = tmp;
+            }
+        }
+    }
+    __syncthreads();
+    long long* o = out + (long long)blockIdx.x * n;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) o[i] = (long long)data[i];
+}
+
 unsigned max_nullary_blocks() {
     static unsigned cached = 0;
     if (cached == 0) {
@@ -219,4 +279,17 @@ extern "C" int ssar_patch_sample(const long long* seeds, int n_seeds, const int*
         seeds, n_seeds, program, n_head_ops, n_latent_ops, n_noise_ops, min_subpatches, max_subpatches, capacity, out,
         counts, end_offset);
     return ssar_launch_status("patch_sample");
+}
+
+extern "C" int ssar_philox_randperm(long long seed, long long first_offset, long long offset_stride, int n, int bits,
+                                    int count, long long* out, void* stream) {
+    if (count == 0 || n == 0) return SSAR_OK;
+    SSAR_REQUIRE(out != nullptr, "philox_randperm: null pointer");
+    SSAR_REQUIRE(n > 0 && n <= 1024 && count > 0, "philox_randperm: n must be in [1, 1024]");
+    SSAR_REQUIRE(bits > 0 && bits <= 32, "philox_randperm: bits must be in [1, 32]");
+    SSAR_REQUIRE(first_offset >= 0 && first_offset % 4 == 0 && offset_stride % 4 == 0,
+                 "philox_randperm: offsets must be multiples of 4");
+    randperm_kernel<<<count, 256, 3 * n * sizeof(int), (cudaStream_t)stream>>>(
+        (unsigned long long)seed, (unsigned long long)first_offset, (unsigned long long)offset_stride, n, bits, out);
+    return ssar_launch_status("philox_randperm");
 }

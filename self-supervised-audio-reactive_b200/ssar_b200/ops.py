@@ -670,3 +670,58 @@ def patch_sample(seeds: torch.Tensor, program: torch.Tensor, n_head: int, n_lat:
     cabi.call("ssar_patch_sample", ptr(seeds), i32(B), ptr(program), i32(n_head), i32(n_lat), i32(n_noise), i32(min_sub),
               i32(max_sub), i32(capacity), ptr(out), ptr(counts), ptr(end))
     return out, counts, end
+
+
+_RANDPERM = {}
+
+
+def randperm_bits(n: int) -> int:
+    """Key width ATen's randperm_out_cuda uses for n elements (TensorFactories.cu, 'Algorithm of randperm')."""
+    nd = float(n)
+    return min(64, int(math.ceil(math.log2(nd - (6 * nd * nd + 1) / (math.log(0.9) * 12)))))
+
+
+def _philox_randperm_raw(seed: int, first_offset: int, stride: int, n: int, count: int, device):
+    out = torch.empty(count, n, dtype=torch.int64, device=device)
+    cabi.call("ssar_philox_randperm", i64(seed), i64(first_offset), i64(stride), i32(n), i32(randperm_bits(n)), i32(count),
+              ptr(out), nbytes=8 * count * n)
+    return out
+
+
+def philox_randperm_stride(device, n: int):
+    """Generator-offset increment of one torch.randperm(n) on `device` when `ssar_philox_randperm` reproduces torch's
+    permutations bit for bit (checked once per (device, n) on 256 consecutive calls: ~15 of them contain runs of equal
+    keys and exercise the duplicate shuffle), else None — callers then keep calling torch.randperm."""
+    device = torch.device(device)
+    key = (device.index if device.index is not None else torch.cuda.current_device(), int(n))
+    st = _RANDPERM.get(key, 0)
+    if st == 0:
+        st = None
+        try:
+            if 0 < n <= 1024 and randperm_bits(n) <= 32:
+                with torch.cuda.device(key[0]):
+                    g = torch.Generator(device)
+                    g.manual_seed(0xC0FFEE)
+                    first = torch.randperm(n, generator=g, device=device)
+                    inc = g.get_offset()
+                    ref = torch.stack([first] + [torch.randperm(n, generator=g, device=device) for _ in range(255)])
+                    got = _philox_randperm_raw(0xC0FFEE, 0, inc, n, 256, device)
+                    if inc > 0 and inc % 4 == 0 and g.get_offset() == 256 * inc and torch.equal(ref, got):
+                        st = int(inc)
+        except Exception:  # pragma: no cover
+            st = None
+        _RANDPERM[key] = st
+        if st is None:
+            import warnings
+
+            warnings.warn("ssar_b200: batched randperm differs from this torch build's torch.randperm; using torch.randperm")
+    return st
+
+
+def philox_randperm(rng: torch.Generator, n: int, count: int, stride: int):
+    """torch.stack([torch.randperm(n, generator=rng, device=rng.device) for _ in range(count)]) in one launch;
+    advances `rng` as the calls would.  stride: `philox_randperm_stride(rng.device, n)` (not None)."""
+    first = rng.get_offset()
+    out = _philox_randperm_raw(rng.initial_seed(), first, stride, n, count, rng.device)
+    rng.set_offset(first + count * stride)
+    return out

@@ -113,11 +113,13 @@ class LatentWeights:
         return t
 
     def apply_subpatch(self, rng, segmentations, features, tempo, fps, patch_type, segments, loop_bars, seq_feat,
-                       seq_feat_weight, mod_feat, mod_feat_weight, merge_type, merge_depth):
-        """latent.py:35-78 on the weights: same RNG draw (one randperm per sub-patch), same arithmetic per element."""
+                       seq_feat_weight, mod_feat, mod_feat_weight, merge_type, merge_depth, permutation=None):
+        """latent.py:35-78 on the weights: same RNG draw (one randperm per sub-patch), same arithmetic per element.
+        permutation: this sub-patch's torch.randperm(P) when the caller drew it already (batched Philox launch)."""
         T, P = self.T, self.P
         segmentation = segmentations[(seq_feat, segments)]  # looked up for every patch type, like latent.py:36
-        permutation = torch.randperm(P, generator=rng, device=rng.device)
+        if permutation is None:
+            permutation = torch.randperm(P, generator=rng, device=rng.device)
         lerp, scale = False, 1.0
         if patch_type == "segmentation":
             selection = permutation[:segments]

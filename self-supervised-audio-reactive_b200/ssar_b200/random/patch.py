@@ -535,11 +535,19 @@ class Patch:
                 v = v.float().reshape(T, -1).contiguous()
             feats[k] = v
 
-        base_selection = torch.randperm(P, generator=self.rng, device=self.rng.device)[: self.num_base_latents]
+        perms = None
+        if self.rng.device.type == "cuda" and USE_BATCHED_DRAWS:
+            stride = ops.philox_randperm_stride(self.rng.device, P)
+            if stride is not None:
+                # the base permutation and the one of every latent sub-patch (latent.py:37) in one launch
+                perms = ops.philox_randperm(self.rng, P, 1 + len(self.latent_patches), stride)
+        base_perm = perms[0] if perms is not None else torch.randperm(P, generator=self.rng, device=self.rng.device)
+        base_selection = base_perm[: self.num_base_latents]
         acc = LatentWeights(T, P, latent_palette.shape[1], 6, dev)
         acc.set_base(base_selection, plan.spline_loop_weights(len(base_selection), T, 1, str(dev)))
-        for sp in self.latent_patches:
-            acc.apply_subpatch(self.rng, self.segmentations, feats, self.tempo, self.fps, **sp)
+        for j, sp in enumerate(self.latent_patches):
+            acc.apply_subpatch(self.rng, self.segmentations, feats, self.tempo, self.fps,
+                               permutation=perms[j + 1] if perms is not None else None, **sp)
         latents = acc.render(latent_palette, out=latents_out)
 
         sizes = [(round(aspect_ratio * size / downscale_factor), round(size / downscale_factor))

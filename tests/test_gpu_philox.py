@@ -110,3 +110,22 @@ def test_patch_paths_agree(dev):
             P.USE_SAMPLER_KERNEL = True
         assert pb.latent_patches == one.latent_patches and pb.noise_patches == one.noise_patches
         assert pb.rng.get_offset() == one.rng.get_offset()
+
+
+def test_randperm_equals_torch(dev):
+    from ssar_b200 import ops
+
+    for n in (180, 7, 64, 1000):
+        stride = ops.philox_randperm_stride(dev, n)
+        assert stride is not None, n
+        for seed, off in [(42, 0), (2 ** 35 + 9, 184 * 7)]:
+            g = torch.Generator(dev)
+            g.manual_seed(seed)
+            g.set_offset(off)
+            ref = torch.stack([torch.randperm(n, generator=g, device=dev) for _ in range(300)])
+            g2 = torch.Generator(dev)
+            g2.manual_seed(seed)
+            g2.set_offset(off)
+            got = ops.philox_randperm(g2, n, 300, stride)
+            assert g2.get_offset() == g.get_offset()
+            assert torch.equal(ref, got), (n, seed)
