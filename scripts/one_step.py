@@ -15,7 +15,7 @@ _, segs, palette = synth_patch_inputs(5760, 0)
 palette = palette.cuda()
 stats = torch.zeros(3, 59, dtype=torch.float64, device="cuda")
 for _ in range(n_steps):
-    feats, latents, _ = pipeline.features_and_latents(x, 44100, 24, palette, segs, rng_device="cuda", workers=1)
+    feats, latents, _ = pipeline.features_and_latents(x, 44100, 24, palette, segs, rng_device="cuda", serial=True)
     stats.zero_()
     ops.feature_stats(feats, stats)
     torch.cuda.synchronize()

@@ -105,6 +105,7 @@ __global__ void overlap_add_kernel(const float* __restrict__ frames, const float
             if (t_hi > n_frames - 1) t_hi = n_frames - 1;
             long long t_lo = (p - n_fft + hop) / hop;  // ceil((p - n_fft + 1)/hop) for p - n_fft + 1 > 0
             if (p - n_fft + 1 <= 0) t_lo = 0;
+#pragma unroll 8  // hop 1 (PLP) sums n_fft frames per sample: keep 8 independent loads in flight, same summation order
             for (long long t = t_lo; t <= t_hi; ++t) {
                 const int i = (int)(p - t * hop);
                 acc += __ldg(fc + t * n_fft + i);

@@ -29,6 +29,46 @@ __global__ void resample_kernel(const float* __restrict__ x, long long n_in, lon
     }
 }
 
+// v1: the launch's thread count is a multiple of `newf`, so every output a thread walks to (stride = thread count) has
+// the SAME phase: its <= 32 taps are loaded once into registers, and an interior output costs max_taps coalesced loads +
+// FMAs with no index arithmetic in the tap loop (same ascending-tap fmaf chain as v0: bit-identical results).
+template <int MAXT>
+__global__ void __launch_bounds__(256) resample_phase_kernel(const float* __restrict__ x, long long n_in, long long stride_in,
+                                                             const float* __restrict__ taps, const int* __restrict__ first,
+                                                             int orig, int newf, int width, int max_taps, float post_scale,
+                                                             float* __restrict__ y, long long n_out, long long stride_out) {
+    const int clip = blockIdx.y;
+    const float* __restrict__ xc = x + (long long)clip * stride_in;
+    float* __restrict__ yc = y + (long long)clip * stride_out;
+    const long long S = (long long)gridDim.x * blockDim.x;  // multiple of newf
+    const long long j0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j0 >= n_out) return;
+    const int ph = (int)(j0 % newf);
+    float tp[MAXT];
+#pragma unroll
+    for (int k = 0; k < MAXT; ++k) tp[k] = k < max_taps ? __ldg(taps + (long long)k * newf + ph) : 0.f;
+    const long long dbase = (S / newf) * orig;
+    long long base = (j0 / newf) * orig - width + __ldg(first + ph);
+    for (long long j = j0; j < n_out; j += S, base += dbase) {
+        float acc = 0.f;
+        if (base >= 0 && base + max_taps <= n_in) {
+            const float* __restrict__ p = xc + base;
+#pragma unroll
+            for (int k = 0; k < MAXT; ++k)
+                if (k < max_taps) acc = fmaf(tp[k], __ldg(p + k), acc);
+        } else {
+#pragma unroll
+            for (int k = 0; k < MAXT; ++k) {
+                if (k < max_taps) {
+                    const long long i = base + k;
+                    acc = fmaf(tp[k], (i >= 0 && i < n_in) ? __ldg(xc + i) : 0.f, acc);
+                }
+            }
+        }
+        yc[j] = acc * post_scale;
+    }
+}
+
 }  // namespace
 
 extern "C" int ssar_resample(const float* x, long long n_in, long long stride_in, int n_clips, const float* taps,
@@ -37,6 +77,20 @@ extern "C" int ssar_resample(const float* x, long long n_in, long long stride_in
     if (n_clips == 0 || n_out == 0) return SSAR_OK;
     SSAR_REQUIRE(x && taps && first && y, "resample: null pointer");
     SSAR_REQUIRE(orig > 0 && newf > 0 && max_taps > 0, "resample: bad rates");
+    if (max_taps <= 32 && (newf <= 256 ? 256 % newf == 0 : newf % 256 == 0)) {
+        // thread count = multiple of newf and of 256: whole "phase periods" per grid row
+        const long long period = newf <= 256 ? 1 : newf / 256;  // blocks per phase period
+        long long gxp = ((n_out + 255) / 256 + period - 1) / period * period;
+        const long long cap = (long long)SSAR_NUM_SMS * 16 / period * period;
+        if (gxp > cap && cap > 0) gxp = cap;
+        if (max_taps <= 24)
+            resample_phase_kernel<24><<<dim3((unsigned)gxp, n_clips), 256, 0, (cudaStream_t)stream>>>(
+                x, n_in, stride_in, taps, first, orig, newf, width, max_taps, post_scale, y, n_out, stride_out);
+        else
+            resample_phase_kernel<32><<<dim3((unsigned)gxp, n_clips), 256, 0, (cudaStream_t)stream>>>(
+                x, n_in, stride_in, taps, first, orig, newf, width, max_taps, post_scale, y, n_out, stride_out);
+        return ssar_launch_status("resample");
+    }
     int gx = ssar_div_up(n_out, 256);
     if (gx > SSAR_NUM_SMS * 16) gx = SSAR_NUM_SMS * 16;
     resample_kernel<<<dim3(gx, n_clips), 256, 0, (cudaStream_t)stream>>>(x, n_in, stride_in, taps, first, orig, newf, width,

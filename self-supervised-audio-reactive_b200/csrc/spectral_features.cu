@@ -63,6 +63,101 @@ __global__ void mfcc_kernel(const float* __restrict__ mel, const uint32_t* __res
     }
 }
 
+// v1 of the mean-aggregated onset envelope for 128 bands: one warp walks OF_RUN consecutive frames, each lane keeps the
+// dB values of its 4 bands of the previous frame in registers, so every mel row is read (128-bit loads) and converted
+// to dB once; the band mean is a shuffle reduction.  (v0 spends one 128-thread CTA and two block barriers per frame.)
+constexpr int OF_RUN = 16;
+__global__ void __launch_bounds__(256) onset_flux_mean128_kernel(const float* __restrict__ mel,
+                                                                 const uint32_t* __restrict__ max_key, int T, int pad_width,
+                                                                 float top_db, float* __restrict__ out, int runs_per_clip) {
+    const int lane = threadIdx.x & 31;
+    const long long wid = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int clip = blockIdx.y;
+    if (wid >= runs_per_clip) return;
+    const int t0 = (int)wid * OF_RUN;
+    const float fl = db_floor_from_key(max_key[clip], top_db);
+    const float4* __restrict__ rows = reinterpret_cast<const float4*>(mel + (long long)clip * T * 128) + lane;
+    float* __restrict__ oc = out + (long long)clip * T;
+    float4 prev = make_float4(0.f, 0.f, 0.f, 0.f);
+    int jprev = -2;  // flux index whose dB row `prev` holds
+    for (int t = t0; t < t0 + OF_RUN && t < T; ++t) {
+        const int j = t - pad_width;
+        float result = 0.f;
+        if (j >= 0 && j + 1 < T) {
+            if (jprev != j) {
+                const float4 a = __ldg(rows + (long long)j * 32);
+                prev = make_float4(to_db(a.x, fl), to_db(a.y, fl), to_db(a.z, fl), to_db(a.w, fl));
+            }
+            const float4 b = __ldg(rows + (long long)(j + 1) * 32);
+            const float4 cur = make_float4(to_db(b.x, fl), to_db(b.y, fl), to_db(b.z, fl), to_db(b.w, fl));
+            float acc = fmaxf(0.f, cur.x - prev.x);
+            acc += fmaxf(0.f, cur.y - prev.y);
+            acc += fmaxf(0.f, cur.z - prev.z);
+            acc += fmaxf(0.f, cur.w - prev.w);
+            result = warp_sum(acc) / 128.f;
+            prev = cur;
+            jprev = j + 1;
+        }
+        if (lane == 0) oc[t] = result;
+    }
+}
+
+// v1 of the MFCC tail: one warp per 4 consecutive frames; the DCT matrix sits transposed in shared memory (lanes =
+// coefficients: conflict-free), the 4 dB rows are read as 128-bit broadcasts.  Same ascending-band fmaf chain per
+// coefficient as v0 (bit-identical), ~190 instead of ~2 700 shared/L1 wavefronts per frame.
+constexpr int MF_FR = 4;
+__global__ void __launch_bounds__(256) mfcc4_kernel(const float* __restrict__ mel, const uint32_t* __restrict__ max_key,
+                                                    const float* __restrict__ dct, int T, int nb, int n_mfcc, float top_db,
+                                                    float* __restrict__ out, int n_clips) {
+    extern __shared__ float4 sm4[];
+    float* dctT = reinterpret_cast<float*>(sm4);                      // [nb][n_mfcc]
+    const int warps = blockDim.x >> 5, w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    float* rows = dctT + ((nb * n_mfcc + 3) & ~3) + (size_t)w * MF_FR * nb;  // [MF_FR][nb], 16-byte aligned
+    for (int i = threadIdx.x; i < nb * n_mfcc; i += blockDim.x) {
+        const int k = i / nb, m = i - k * nb;
+        dctT[m * n_mfcc + k] = __ldg(dct + i);
+    }
+    __syncthreads();
+    const long long total = (long long)n_clips * T;
+    const long long groups = (total + MF_FR - 1) / MF_FR;
+    for (long long g = (long long)blockIdx.x * warps + w; g < groups; g += (long long)gridDim.x * warps) {
+#pragma unroll
+        for (int fr = 0; fr < MF_FR; ++fr) {
+            const long long f = g * MF_FR + fr;
+            if (f < total) {
+                const float fl = db_floor_from_key(max_key[(int)(f / T)], top_db);
+                for (int m = l; m < nb; m += 32) rows[fr * nb + m] = to_db(__ldg(mel + f * nb + m), fl);
+            } else {
+                for (int m = l; m < nb; m += 32) rows[fr * nb + m] = 0.f;
+            }
+        }
+        __syncwarp();
+        for (int k = l; k < n_mfcc; k += 32) {
+            float acc[MF_FR];
+#pragma unroll
+            for (int fr = 0; fr < MF_FR; ++fr) acc[fr] = 0.f;
+            for (int m = 0; m < nb; m += 4) {
+                const float d0 = dctT[m * n_mfcc + k], d1 = dctT[(m + 1) * n_mfcc + k];
+                const float d2 = dctT[(m + 2) * n_mfcc + k], d3 = dctT[(m + 3) * n_mfcc + k];
+#pragma unroll
+                for (int fr = 0; fr < MF_FR; ++fr) {
+                    const float4 r = *reinterpret_cast<const float4*>(rows + fr * nb + m);
+                    acc[fr] = fmaf(d0, r.x, acc[fr]);
+                    acc[fr] = fmaf(d1, r.y, acc[fr]);
+                    acc[fr] = fmaf(d2, r.z, acc[fr]);
+                    acc[fr] = fmaf(d3, r.w, acc[fr]);
+                }
+            }
+#pragma unroll
+            for (int fr = 0; fr < MF_FR; ++fr) {
+                const long long f = g * MF_FR + fr;
+                if (f < total) out[f * n_mfcc + k] = acc[fr];
+            }
+        }
+        __syncwarp();
+    }
+}
+
 __global__ void power_to_db_kernel(const float* __restrict__ x, long long n_per_clip, const uint32_t* __restrict__ max_key,
                                    float top_db, int has_top, float* __restrict__ out) {
     const int clip = blockIdx.y;
@@ -99,6 +194,12 @@ extern "C" int ssar_onset_flux(const float* mel, const uint32_t* max_key, int n_
     SSAR_REQUIRE(mel && max_key && out, "onset_flux: null pointer");
     SSAR_REQUIRE(n_bands > 0 && n_bands <= 4096, "onset_flux: n_bands out of range");
     SSAR_REQUIRE(aggregate == 0 || aggregate == 1, "onset_flux: aggregate must be 0 (mean) or 1 (median)");
+    if (aggregate == 0 && n_bands == 128 && (reinterpret_cast<uintptr_t>(mel) & 15) == 0) {
+        const int runs = ssar_div_up(n_frames, OF_RUN);
+        onset_flux_mean128_kernel<<<dim3(ssar_div_up(runs, 8), n_clips), 256, 0, (cudaStream_t)stream>>>(
+            mel, max_key, n_frames, pad_width, top_db, out, runs);
+        return ssar_launch_status("onset_flux");
+    }
     dim3 grid(n_frames, n_clips);
     const size_t smem = (32 + next_pow2(n_bands)) * sizeof(float);
     onset_flux_kernel<<<grid, 128, smem, (cudaStream_t)stream>>>(mel, max_key, n_frames, n_bands, pad_width, aggregate,
@@ -113,6 +214,19 @@ extern "C" int ssar_mfcc(const float* mel, const uint32_t* max_key, const float*
     SSAR_REQUIRE(n_bands > 0 && n_bands <= 1024, "mfcc: n_bands out of range");
     const int warps = 8;
     const long long total = (long long)n_clips * n_frames;
+    if (n_bands % 4 == 0) {
+        const size_t smem4 = (((size_t)n_bands * n_mfcc + 3) & ~(size_t)3) * sizeof(float) +
+                             (size_t)warps * MF_FR * n_bands * sizeof(float);
+        if (smem4 <= 200 * 1024) {
+            if (smem4 > 48 * 1024)
+                cudaFuncSetAttribute(mfcc4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4);
+            int g4 = ssar_div_up(ssar_div_up(total, MF_FR), warps);
+            if (g4 > SSAR_NUM_SMS * 4) g4 = SSAR_NUM_SMS * 4;
+            mfcc4_kernel<<<g4, warps * 32, smem4, (cudaStream_t)stream>>>(mel, max_key, dct, n_frames, n_bands, n_mfcc,
+                                                                        top_db, out, n_clips);
+            return ssar_launch_status("mfcc");
+        }
+    }
     int grid = ssar_div_up(total, warps);
     if (grid > SSAR_NUM_SMS * 8) grid = SSAR_NUM_SMS * 8;
     mfcc_kernel<<<grid, warps * 32, warps * n_bands * sizeof(float), (cudaStream_t)stream>>>(
