@@ -386,6 +386,25 @@ int ssar_patch_sample(const long long* seeds, int n_seeds, const int* program, i
 int ssar_philox_randperm(long long seed, long long first_offset, long long offset_stride, int n, int bits, int count,
                          long long* out, void* stream);
 
+/* One latent sub-patch of a stack (the arguments of ssar_subpatch_merge, plus src_mode 2: segmentation labels).     */
+typedef struct {
+    const long long* selection; /* device int64 [n_select]: palette columns (a torch.randperm prefix)               */
+    const void* src;            /* src_mode 0 / 1: float [T, src_ld];  src_mode 2: int64 labels [T]                  */
+    const float* mod;           /* modulation feature [T, mod_ld] (column 0) or NULL                                 */
+    const float* pre_taps;      /* src_mode 2: Gaussian taps [2 * pre_radius + 1] of the one-hot smoothing (sigma 5) */
+    long long src_ld, mod_ld;
+    float src_scale, mod_scale, alpha, beta;
+    int g_begin, g_end, n_select, src_mode, radius, pre_radius;
+} ssar_subpatch_desc;
+
+/* A whole stack of latent sub-patches (ssar/random/patch.py:113-121 -> latent.py:35-78 per sub-patch) applied to the
+ * weights [n_rows, n_groups, n_basis] in ONE launch: a CTA keeps its 8 frames of weights in shared memory and applies the
+ * sub-patches in order (each exactly as ssar_subpatch_merge would; src_mode 2 = ssar_onehot_gauss fused in).  descs: HOST
+ * array of n_descs <= 24 descriptors.  taps: Gaussian taps of the sigma = 1 smoothing for descriptors with radius > 0
+ * (all share `radius`).  load_initial = 0 when descs[0] overwrites every group (the base loop latents).             */
+int ssar_latent_stack(float* weights, int n_rows, int n_groups, int n_basis, const ssar_subpatch_desc* descs, int n_descs,
+                      const float* taps, int load_initial, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -117,6 +117,52 @@ __global__ void overlap_add_kernel(const float* __restrict__ frames, const float
     }
 }
 
+// Dense overlap (n_fft / hop >= 64: PLP's hop-1 inverse, rosa/beat.py:72, sums 1024 frames per sample): the frame range
+// of a sample is cut into OD_SEG consecutive segments summed by OD_SEG threads (8x the loads in flight of the serial
+// gather, which is latency-bound at 46 k threads), and the partial sums are added in ascending frame order.
+constexpr int OD_SEG = 8;
+__global__ void __launch_bounds__(32 * OD_SEG) overlap_add_dense_kernel(const float* __restrict__ frames,
+                                                                        const float* __restrict__ win, int n_fft, int hop,
+                                                                        int n_frames, long long length,
+                                                                        float* __restrict__ out) {
+    __shared__ float sacc[OD_SEG][32], senv[OD_SEG][32];
+    const int clip = blockIdx.y, seg = threadIdx.y;
+    const float* fc = frames + (long long)clip * n_frames * n_fft;
+    float* oc = out + (long long)clip * length;
+    const long long total = (long long)n_fft + (long long)hop * (n_frames - 1);
+    const long long n = (long long)blockIdx.x * 32 + threadIdx.x;
+    const long long p = n + n_fft / 2;
+    float acc = 0.f, env = 0.f;
+    if (n < length && p < total) {
+        long long t_hi = p / hop;
+        if (t_hi > n_frames - 1) t_hi = n_frames - 1;
+        long long t_lo = (p - n_fft + hop) / hop;
+        if (p - n_fft + 1 <= 0) t_lo = 0;
+        const long long cnt = t_hi - t_lo + 1, per = (cnt + OD_SEG - 1) / OD_SEG;
+        const long long a = t_lo + seg * per;
+        long long b = a + per - 1;
+        if (b > t_hi) b = t_hi;
+#pragma unroll 8
+        for (long long t = a; t <= b; ++t) {
+            const int i = (int)(p - t * hop);
+            acc += __ldg(fc + t * n_fft + i);
+            const float w = win ? __ldg(win + i) : 1.f;
+            env = fmaf(w, w, env);
+        }
+    }
+    sacc[seg][threadIdx.x] = acc;
+    senv[seg][threadIdx.x] = env;
+    __syncthreads();
+    if (seg == 0 && n < length) {
+#pragma unroll
+        for (int s = 1; s < OD_SEG; ++s) {
+            acc += sacc[s][threadIdx.x];
+            env += senv[s][threadIdx.x];
+        }
+        oc[n] = env > 1e-11f ? acc / env : 0.f;
+    }
+}
+
 // Same gather, four consecutive output samples per thread (128-bit loads / stores, 32-bit index arithmetic): used when
 // hop, n_fft / 2 and the clip length are multiples of 4 and every index fits 31 bits — the HPSS case (hop = n_fft / 2).
 // The four samples share their covering frames; per sample the frames are summed in the same order as above.
@@ -313,6 +359,11 @@ extern "C" int ssar_overlap_add(const float* frames, const float* window, int n_
         if (g4 > SSAR_NUM_SMS * 16) g4 = SSAR_NUM_SMS * 16;
         overlap_add_vec4_kernel<<<dim3(g4, n_clips), 256, 0, (cudaStream_t)stream>>>(frames, window, n_fft, hop, n_frames,
                                                                                  (int)length, out);
+        return ssar_launch_status("overlap_add");
+    }
+    if (n_fft / hop >= 64 && (length + 31) / 32 <= 0x7fffffffLL) {
+        overlap_add_dense_kernel<<<dim3((unsigned)((length + 31) / 32), n_clips), dim3(32, OD_SEG), 0, (cudaStream_t)stream>>>(
+            frames, window, n_fft, hop, n_frames, length, out);
         return ssar_launch_status("overlap_add");
     }
     int gx = ssar_div_up(length, 256);

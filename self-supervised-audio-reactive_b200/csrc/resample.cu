@@ -69,6 +69,52 @@ __global__ void __launch_bounds__(256) resample_phase_kernel(const float* __rest
     }
 }
 
+// Decimation by 2 (orig 2, new 1: the CQT octave chain, rosa/constantq.py:83): every output uses the same taps and the
+// windows of neighbouring outputs overlap by max_taps - 2 samples, so a thread makes 4 consecutive outputs from one
+// register window of max_taps + 6 samples (3.3x fewer loads than one window per output).  Per output the taps are
+// accumulated in the same ascending fmaf chain as the generic kernels.
+template <int MAXT>
+__global__ void __launch_bounds__(256) decimate2_kernel(const float* __restrict__ x, long long n_in, long long stride_in,
+                                                        const float* __restrict__ taps, const int* __restrict__ first, int width,
+                                                        int max_taps, float post_scale, float* __restrict__ y, long long n_out,
+                                                        long long stride_out) {
+    const int clip = blockIdx.y;
+    const float* __restrict__ xc = x + (long long)clip * stride_in;
+    float* __restrict__ yc = y + (long long)clip * stride_out;
+    float tp[MAXT];
+#pragma unroll
+    for (int k = 0; k < MAXT; ++k) tp[k] = k < max_taps ? __ldg(taps + k) : 0.f;
+    const int first0 = __ldg(first);
+    const long long groups = (n_out + 3) / 4;
+    for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < groups; q += (long long)gridDim.x * blockDim.x) {
+        const long long j = 4 * q;
+        const long long base = 2 * j - width + first0;  // window of output j; output j + r starts at base + 2 r
+        float w[MAXT + 6];
+        if (base >= 0 && base + max_taps + 6 <= n_in) {
+#pragma unroll
+            for (int i = 0; i < MAXT + 6; ++i)
+                if (i < max_taps + 6) w[i] = __ldg(xc + base + i);
+        } else {
+#pragma unroll
+            for (int i = 0; i < MAXT + 6; ++i) {
+                const long long g = base + i;
+                w[i] = (i < max_taps + 6 && g >= 0 && g < n_in) ? __ldg(xc + g) : 0.f;
+            }
+        }
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int k = 0; k < MAXT; ++k) {
+            if (k < max_taps) {
+#pragma unroll
+                for (int r = 0; r < 4; ++r) acc[r] = fmaf(tp[k], w[k + 2 * r], acc[r]);
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+            if (j + r < n_out) yc[j + r] = acc[r] * post_scale;
+    }
+}
+
 }  // namespace
 
 extern "C" int ssar_resample(const float* x, long long n_in, long long stride_in, int n_clips, const float* taps,
@@ -77,6 +123,13 @@ extern "C" int ssar_resample(const float* x, long long n_in, long long stride_in
     if (n_clips == 0 || n_out == 0) return SSAR_OK;
     SSAR_REQUIRE(x && taps && first && y, "resample: null pointer");
     SSAR_REQUIRE(orig > 0 && newf > 0 && max_taps > 0, "resample: bad rates");
+    if (orig == 2 && newf == 1 && max_taps <= 28) {
+        long long gq = ((n_out + 3) / 4 + 255) / 256;
+        if (gq > SSAR_NUM_SMS * 16) gq = SSAR_NUM_SMS * 16;
+        decimate2_kernel<28><<<dim3((unsigned)gq, n_clips), 256, 0, (cudaStream_t)stream>>>(
+            x, n_in, stride_in, taps, first, width, max_taps, post_scale, y, n_out, stride_out);
+        return ssar_launch_status("resample");
+    }
     if (max_taps <= 32 && (newf <= 256 ? 256 % newf == 0 : newf % 256 == 0)) {
         // thread count = multiple of newf and of 256: whole "phase periods" per grid row
         const long long period = newf <= 256 ? 1 : newf / 256;  // blocks per phase period

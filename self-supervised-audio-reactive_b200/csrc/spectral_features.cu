@@ -67,6 +67,7 @@ __global__ void mfcc_kernel(const float* __restrict__ mel, const uint32_t* __res
 // dB values of its 4 bands of the previous frame in registers, so every mel row is read (128-bit loads) and converted
 // to dB once; the band mean is a shuffle reduction.  (v0 spends one 128-thread CTA and two block barriers per frame.)
 constexpr int OF_RUN = 16;
+template <bool MEDIAN>
 __global__ void __launch_bounds__(256) onset_flux_mean128_kernel(const float* __restrict__ mel,
                                                                  const uint32_t* __restrict__ max_key, int T, int pad_width,
                                                                  float top_db, float* __restrict__ out, int runs_per_clip) {
@@ -90,11 +91,40 @@ __global__ void __launch_bounds__(256) onset_flux_mean128_kernel(const float* __
             }
             const float4 b = __ldg(rows + (long long)(j + 1) * 32);
             const float4 cur = make_float4(to_db(b.x, fl), to_db(b.y, fl), to_db(b.z, fl), to_db(b.w, fl));
-            float acc = fmaxf(0.f, cur.x - prev.x);
-            acc += fmaxf(0.f, cur.y - prev.y);
-            acc += fmaxf(0.f, cur.z - prev.z);
-            acc += fmaxf(0.f, cur.w - prev.w);
-            result = warp_sum(acc) / 128.f;
+            const float d[4] = {fmaxf(0.f, cur.x - prev.x), fmaxf(0.f, cur.y - prev.y), fmaxf(0.f, cur.z - prev.z),
+                                fmaxf(0.f, cur.w - prev.w)};
+            if (!MEDIAN) {
+                float acc = d[0];
+                acc += d[1];
+                acc += d[2];
+                acc += d[3];
+                result = warp_sum(acc) / 128.f;
+            } else {
+                // lower median (torch.median): the element of rank 63 under (value, band index) order, found by
+                // counting — every lane ranks its 4 bands against the 128 values parked in shared memory
+                __shared__ float4 med_rows[8][32];
+                float4* row = med_rows[threadIdx.x >> 5];
+                __syncwarp();
+                row[lane] = make_float4(d[0], d[1], d[2], d[3]);
+                __syncwarp();
+                int cnt[4] = {0, 0, 0, 0};
+                for (int q = 0; q < 32; ++q) {
+                    const float4 o = row[q];
+                    const float ov[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        const int e = 4 * q + c;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            cnt[i] += (ov[c] < d[i]) || (ov[c] == d[i] && e < 4 * lane + i);
+                    }
+                }
+                float mine = -1.f;  // flux values are >= 0
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    if (cnt[i] == 63) mine = d[i];
+                result = warp_max(mine);
+            }
             prev = cur;
             jprev = j + 1;
         }
@@ -194,10 +224,14 @@ extern "C" int ssar_onset_flux(const float* mel, const uint32_t* max_key, int n_
     SSAR_REQUIRE(mel && max_key && out, "onset_flux: null pointer");
     SSAR_REQUIRE(n_bands > 0 && n_bands <= 4096, "onset_flux: n_bands out of range");
     SSAR_REQUIRE(aggregate == 0 || aggregate == 1, "onset_flux: aggregate must be 0 (mean) or 1 (median)");
-    if (aggregate == 0 && n_bands == 128 && (reinterpret_cast<uintptr_t>(mel) & 15) == 0) {
+    if (n_bands == 128 && (reinterpret_cast<uintptr_t>(mel) & 15) == 0) {
         const int runs = ssar_div_up(n_frames, OF_RUN);
-        onset_flux_mean128_kernel<<<dim3(ssar_div_up(runs, 8), n_clips), 256, 0, (cudaStream_t)stream>>>(
-            mel, max_key, n_frames, pad_width, top_db, out, runs);
+        if (aggregate == 0)
+            onset_flux_mean128_kernel<false><<<dim3(ssar_div_up(runs, 8), n_clips), 256, 0, (cudaStream_t)stream>>>(
+                mel, max_key, n_frames, pad_width, top_db, out, runs);
+        else
+            onset_flux_mean128_kernel<true><<<dim3(ssar_div_up(runs, 8), n_clips), 256, 0, (cudaStream_t)stream>>>(
+                mel, max_key, n_frames, pad_width, top_db, out, runs);
         return ssar_launch_status("onset_flux");
     }
     dim3 grid(n_frames, n_clips);

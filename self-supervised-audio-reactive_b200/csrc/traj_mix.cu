@@ -196,6 +196,118 @@ __global__ void __launch_bounds__(256) subpatch_merge_kernel(float* __restrict__
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// The whole sub-patch stack of one clip in one launch.  W[t] after sub-patch j depends only on W[t] after j - 1 and on
+// the (time-smoothed) source of sub-patch j around t, so a CTA that owns SP_TT frames can walk the stack with its
+// weight rows resident in shared memory: [T, G, P] is written once instead of read + written per sub-patch, and the
+// ~13 dependent launches per clip become one.  Arithmetic per element is subpatch_merge_kernel's.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int STACK_MAX = 24;
+constexpr int STACK_KMAX = 32;
+struct StackArgs {
+    ssar_subpatch_desc d[STACK_MAX];
+    int n;
+};
+
+__global__ void __launch_bounds__(256) latent_stack_kernel(float* __restrict__ Wt, int T, int G, int P, const StackArgs sa,
+                                                           const float* __restrict__ taps, int load_initial) {
+    extern __shared__ float st_smem[];
+    const int GP = G * P;
+    float* W = st_smem;                                    // [SP_TT][G * P]
+    float* S = W + SP_TT * GP;                             // [SP_TT][STACK_KMAX]
+    float* OH = S + SP_TT * STACK_KMAX;                    // [SP_TT + 2 * 8][STACK_KMAX] (radius <= 8)
+    float* ab = OH + (SP_TT + 16) * STACK_KMAX;            // [SP_TT][2]
+    int* inv = reinterpret_cast<int*>(ab + SP_TT * 2);     // [P]
+    const int t0 = blockIdx.x * SP_TT;
+    const int rows = min(SP_TT, T - t0);
+    if (load_initial)
+        for (int i = threadIdx.x; i < rows * GP; i += blockDim.x) W[i] = Wt[(long long)t0 * GP + i];
+    for (int j = 0; j < sa.n; ++j) {
+        const ssar_subpatch_desc& d = sa.d[j];
+        const int K = d.n_select, radius = d.radius;
+        __syncthreads();  // previous sub-patch applied; S / inv / OH free
+        for (int p = threadIdx.x; p < P; p += blockDim.x) inv[p] = -1;
+        __syncthreads();
+        for (int k = threadIdx.x; k < K; k += blockDim.x) {
+            const long long p = d.selection[k];
+            if (p >= 0 && p < P) inv[(int)p] = k;
+        }
+        if (d.src_mode == 2) {
+            // smoothed one-hot rows for t0 - radius .. t0 + SP_TT + radius (onehot_gauss_kernel's tap order)
+            const long long* __restrict__ labels = reinterpret_cast<const long long*>(d.src);
+            const int nr = SP_TT + 2 * radius, pr = d.pre_radius;
+            for (int i = threadIdx.x; i < nr * K; i += blockDim.x) {
+                const int rr = i / K, k = i - rr * K;
+                int t = (t0 - radius + rr) % T;
+                if (t < 0) t += T;
+                int ti = (t - pr) % T;
+                if (ti < 0) ti += T;
+                float acc = 0.f;
+                for (int q = 0; q <= 2 * pr; ++q) {
+                    acc = fmaf(__ldg(d.pre_taps + q), (__ldg(labels + ti) == k) ? 1.f : 0.f, acc);
+                    if (++ti == T) ti = 0;
+                }
+                OH[rr * STACK_KMAX + k] = acc;
+            }
+            __syncthreads();
+        }
+        const float* __restrict__ srcf = reinterpret_cast<const float*>(d.src);
+        for (int i = threadIdx.x; i < SP_TT * K; i += blockDim.x) {
+            const int tt = i / K, k = i - tt * K;
+            const int t = t0 + tt;
+            float acc = 0.f;
+            if (t < T) {
+                if (d.src_mode == 2) {
+                    if (radius == 0) {
+                        acc = __fmul_rn(d.src_scale, OH[tt * STACK_KMAX + k]);
+                    } else {
+                        for (int q = 0; q <= 2 * radius; ++q)
+                            acc = fmaf(__ldg(taps + q), __fmul_rn(d.src_scale, OH[(tt + q) * STACK_KMAX + k]), acc);
+                    }
+                } else if (radius == 0) {
+                    acc = subpatch_raw(srcf, d.src_ld, d.src_scale, d.src_mode, t, k);
+                } else {
+                    int ti = (t - radius) % T;
+                    if (ti < 0) ti += T;
+                    for (int q = 0; q <= 2 * radius; ++q) {
+                        acc = fmaf(__ldg(taps + q), subpatch_raw(srcf, d.src_ld, d.src_scale, d.src_mode, ti, k), acc);
+                        if (++ti == T) ti = 0;
+                    }
+                }
+            }
+            S[tt * STACK_KMAX + k] = acc;
+        }
+        if (threadIdx.x < SP_TT) {
+            const int t = t0 + threadIdx.x;
+            float al = d.alpha, be = d.beta;
+            if (d.mod && t < T) {
+                be = __fmul_rn(d.mod_scale, __ldg(d.mod + (long long)t * d.mod_ld));
+                al = __fsub_rn(1.f, be);
+            }
+            ab[2 * threadIdx.x] = al;
+            ab[2 * threadIdx.x + 1] = be;
+        }
+        __syncthreads();
+        const int g0 = d.g_begin, Gr = d.g_end - d.g_begin;
+        const bool overwrite = (d.mod == nullptr) && d.alpha == 0.f;
+        const int span = Gr * P;  // contiguous inside a row: groups g0 .. g1 - 1
+        for (int tt = 0; tt < rows; ++tt) {
+            const float al = ab[2 * tt], be = ab[2 * tt + 1];
+            float* wrow = W + tt * GP + g0 * P;
+            const float* srow = S + tt * STACK_KMAX;
+            for (int i = threadIdx.x; i < span; i += blockDim.x) {
+                int p = i;
+                while (p >= P) p -= P;  // Gr <= 3
+                const int k = inv[p];
+                const float sv = k >= 0 ? srow[k] : 0.f;
+                wrow[i] = overwrite ? be * sv : fmaf(al, wrow[i], be * sv);
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < rows * GP; i += blockDim.x) Wt[(long long)t0 * GP + i] = W[i];
+}
+
 // out[t, k] = sum_i taps[i] * (labels[(t + i - radius) mod T] == k): the one-hot gather of latent.py:39-40 followed by
 // the circular Gaussian of :41, without materialising the one-hot matrix (same tap order as gauss1d_kernel).
 __global__ void onehot_gauss_kernel(const long long* __restrict__ labels, int T, int K, const float* __restrict__ taps,
@@ -276,6 +388,34 @@ extern "C" int ssar_subpatch_merge(float* weights, int n_rows, int n_groups, int
         weights, n_rows, n_groups, n_basis, g_begin, g_end, selection, n_select, src, src_ld, src_scale, src_mode, taps,
         radius, mod, mod_ld, mod_scale, alpha_scalar, beta_scalar);
     return ssar_launch_status("subpatch_merge");
+}
+
+extern "C" int ssar_latent_stack(float* weights, int n_rows, int n_groups, int n_basis, const ssar_subpatch_desc* descs,
+                                 int n_descs, const float* taps, int load_initial, void* stream) {
+    if (n_rows == 0 || n_basis == 0 || n_descs == 0) return SSAR_OK;
+    SSAR_REQUIRE(weights && descs, "latent_stack: null pointer");
+    SSAR_REQUIRE(n_descs > 0 && n_descs <= STACK_MAX, "latent_stack: at most 24 sub-patches per launch");
+    StackArgs sa;
+    sa.n = n_descs;
+    for (int j = 0; j < n_descs; ++j) {
+        const ssar_subpatch_desc& d = descs[j];
+        SSAR_REQUIRE(d.selection && d.src, "latent_stack: null selection / src in sub-patch %d", j);
+        SSAR_REQUIRE(0 <= d.g_begin && d.g_begin < d.g_end && d.g_end <= n_groups, "latent_stack: bad group range");
+        SSAR_REQUIRE(d.n_select > 0 && d.n_select <= STACK_KMAX, "latent_stack: 1..32 selected latents per sub-patch");
+        SSAR_REQUIRE(d.src_mode == 0 || d.src_mode == 2 || (d.src_mode == 1 && d.n_select == 2),
+                     "latent_stack: src_mode 1 (lerp) needs exactly 2 selected latents");
+        SSAR_REQUIRE(d.radius >= 0 && d.radius <= 8 && (d.radius == 0 || taps), "latent_stack: radius must be in [0, 8]");
+        SSAR_REQUIRE(d.src_mode != 2 || (d.pre_taps && d.pre_radius >= 0), "latent_stack: labels need pre_taps");
+        sa.d[j] = d;
+    }
+    const size_t smem = ((size_t)SP_TT * n_groups * n_basis + SP_TT * STACK_KMAX + (SP_TT + 16) * STACK_KMAX + SP_TT * 2 +
+                         n_basis) * sizeof(float);
+    SSAR_REQUIRE(smem <= 200 * 1024, "latent_stack: palette too large for one CTA's shared memory");
+    if (smem > 48 * 1024)
+        cudaFuncSetAttribute(latent_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    latent_stack_kernel<<<ssar_div_up(n_rows, SP_TT), 256, smem, (cudaStream_t)stream>>>(weights, n_rows, n_groups, n_basis,
+                                                                                       sa, taps, load_initial);
+    return ssar_launch_status("latent_stack");
 }
 
 extern "C" int ssar_onehot_gauss(const long long* labels, int n_rows, int n_classes, const float* taps, int radius,

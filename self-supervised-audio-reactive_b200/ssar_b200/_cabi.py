@@ -58,6 +58,17 @@ class NoiseOp(C.Structure):
     ]
 
 
+class SubpatchDesc(C.Structure):
+    """ssar_subpatch_desc (include/ssar_b200.h)."""
+    _fields_ = [
+        ("selection", C.c_void_p), ("src", C.c_void_p), ("mod", C.c_void_p), ("pre_taps", C.c_void_p),
+        ("src_ld", C.c_longlong), ("mod_ld", C.c_longlong),
+        ("src_scale", C.c_float), ("mod_scale", C.c_float), ("alpha", C.c_float), ("beta", C.c_float),
+        ("g_begin", C.c_int), ("g_end", C.c_int), ("n_select", C.c_int), ("src_mode", C.c_int), ("radius", C.c_int),
+        ("pre_radius", C.c_int),
+    ]
+
+
 def lib():
     """Loads the library once; raises (never falls back) when it has not been built."""
     global _lib

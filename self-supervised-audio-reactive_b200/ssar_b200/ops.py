@@ -725,3 +725,17 @@ def philox_randperm(rng: torch.Generator, n: int, count: int, stride: int):
     out = _philox_randperm_raw(rng.initial_seed(), first, stride, n, count, rng.device)
     rng.set_offset(first + count * stride)
     return out
+
+
+STACK_MAX = 24  # sub-patches per ssar_latent_stack launch
+
+
+def latent_stack(weights: torch.Tensor, descs, taps: torch.Tensor | None, load_initial: bool):
+    """Applies a list of `_cabi.SubpatchDesc` to weights [T, G, P] in place, in order, one launch per 24 descriptors."""
+    T, G, P = weights.shape
+    for c0 in range(0, len(descs), STACK_MAX):
+        part = descs[c0 : c0 + STACK_MAX]
+        arr = (cabi.SubpatchDesc * len(part))(*part)
+        cabi.call("ssar_latent_stack", ptr(weights), i32(T), i32(G), i32(P), arr, i32(len(part)), ptr(taps),
+                  i32(1 if (load_initial or c0 > 0) else 0), nbytes=T * G * P * (8 if (load_initial or c0 > 0) else 4))
+    return weights

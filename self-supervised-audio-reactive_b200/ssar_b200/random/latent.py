@@ -7,6 +7,7 @@ from __future__ import annotations
 
 import torch
 
+from .. import _cabi as cabi
 from .. import ops, plan
 
 LAYER_SLICES = {"low": (0, 6), "mid": (6, 12), "high": (12, 18), "lowmid": (0, 12), "midhigh": (6, 18), "all": (0, 18)}
@@ -86,17 +87,52 @@ class LatentWeights:
         self.device = torch.device(device)
         self.w = torch.empty(self.T, self.G, self.P, dtype=torch.float32, device=self.device)
         self._labels = {}
+        # deferred mode (Patch.forward): sub-patches are queued as descriptors and applied by ONE ssar_latent_stack launch
+        self.deferred = False
+        self._queue, self._keep, self._fresh = [], [], True
 
     def _sel(self, selection):
         return selection.to(self.device, non_blocking=True)
 
+    def _enqueue(self, selection, src, g_begin, g_end, src_mode=0, src_scale=1.0, sigma=0, mod=None, mod_scale=1.0,
+                 alpha=0.5, beta=0.5, pre_sigma=None):
+        d = cabi.SubpatchDesc()
+        selection = self._sel(selection)
+        d.selection, d.src, d.n_select = selection.data_ptr(), src.data_ptr(), int(selection.numel())
+        d.src_ld = src.stride(0) if src_mode != 2 else 0
+        d.src_scale, d.src_mode = float(src_scale), int(src_mode)
+        d.g_begin, d.g_end = int(g_begin), int(g_end)
+        d.radius = min(int(sigma * 4), 3 * self.T) if sigma else 0
+        if mod is not None:
+            d.mod, d.mod_ld, d.mod_scale = mod.data_ptr(), mod.stride(0), float(mod_scale)
+        d.alpha, d.beta = float(alpha), float(beta)
+        if src_mode == 2:
+            d.pre_radius = min(int(pre_sigma * 4), 3 * self.T)
+            pre = plan.gaussian_taps(float(pre_sigma), d.pre_radius, str(self.device))
+            d.pre_taps = pre.data_ptr()
+            self._keep.append(pre)
+        self._keep += [selection, src, mod]
+        self._queue.append(d)
+
+    def flush(self):
+        """Applies the queued sub-patches (deferred mode) with one launch per 24 of them."""
+        if self._queue:
+            taps = plan.gaussian_taps(1.0, min(4, 3 * self.T), str(self.device))
+            ops.latent_stack(self.w, self._queue, taps, load_initial=not self._fresh)
+            self._queue, self._keep, self._fresh = [], [], False
+
     def set_base(self, selection, S):
         """weights = S scattered to the selected palette columns in every layer group (overwrites)."""
+        if self.deferred and len(selection) <= 32:
+            self._enqueue(selection, S, 0, self.G, sigma=0, alpha=0.0, beta=1.0)
+            return
+        self._fresh = False
         ops.subpatch_merge(self.w, 0, self.G, self._sel(selection), S, sigma=0, alpha=0.0, beta=1.0)
 
     def merge(self, selection, S, alpha, beta, merge_depth):
         """Generic merge of an already smoothed sequence S [T, K] with float or [T] tensor coefficients."""
         lo, hi = LAYER_SLICES[merge_depth]
+        self.flush()
         if torch.is_tensor(alpha) or torch.is_tensor(beta):
             D = torch.zeros(self.T, self.P, dtype=torch.float32, device=self.device)
             D.index_add_(1, self._sel(selection).long(), S)
@@ -121,9 +157,14 @@ class LatentWeights:
         if permutation is None:
             permutation = torch.randperm(P, generator=rng, device=rng.device)
         lerp, scale = False, 1.0
+        use_stack = self.deferred and min(int(1 * 4), 3 * T) <= 8
+        src_mode = None
         if patch_type == "segmentation":
             selection = permutation[:segments]
-            src = ops.onehot_gauss(self.labels((seq_feat, segments), segmentation), int(segments), 5)
+            if use_stack and int(segments) <= 32:
+                src, src_mode = self.labels((seq_feat, segments), segmentation), 2
+            else:
+                src = ops.onehot_gauss(self.labels((seq_feat, segments), segmentation), int(segments), 5)
         elif patch_type == "feature":
             feature = features[seq_feat]
             scale = float(seq_feat_weight)
@@ -143,8 +184,15 @@ class LatentWeights:
         else:
             mod, mod_scale = None, 1.0
             alpha, beta = (0.5, 0.5) if merge_type == "average" else (0.0, 1.0)
+        if use_stack and len(selection) <= 32:
+            self._enqueue(selection, src, lo // self.gl, hi // self.gl, src_mode=src_mode if src_mode is not None else
+                          (1 if lerp else 0), src_scale=scale, sigma=1, mod=mod, mod_scale=mod_scale, alpha=alpha, beta=beta,
+                          pre_sigma=5)
+            return
+        self.flush()
         ops.subpatch_merge(self.w, lo // self.gl, hi // self.gl, self._sel(selection), src, src_scale=scale, lerp=lerp,
                            sigma=1, mod=mod, mod_scale=mod_scale, alpha=alpha, beta=beta)
 
     def render(self, palette, out=None):
+        self.flush()
         return ops.mix_gemm(self.w, palette.to(self.device), out=out)

@@ -398,6 +398,7 @@ def _eager_sample(rng, ks, min_subpatches, max_subpatches):
 
 USE_SAMPLER_GRAPHS = True  # CUDA generators only; False = the eager deferred sampler
 USE_BATCHED_DRAWS = True   # CUDA generators only: noise bases of a Patch in one Philox launch (ssar_philox_normal_segments)
+USE_LATENT_STACK = True    # Patch.forward: all latent sub-patches of a clip in one launch (ssar_latent_stack)
 USE_SAMPLER_KERNEL = True  # CUDA generators only: the config sampler as one kernel per batch of seeds (ssar_patch_sample)
 
 
@@ -544,6 +545,7 @@ class Patch:
         base_perm = perms[0] if perms is not None else torch.randperm(P, generator=self.rng, device=self.rng.device)
         base_selection = base_perm[: self.num_base_latents]
         acc = LatentWeights(T, P, latent_palette.shape[1], 6, dev)
+        acc.deferred = USE_LATENT_STACK  # the whole sub-patch stack as one ssar_latent_stack launch
         acc.set_base(base_selection, plan.spline_loop_weights(len(base_selection), T, 1, str(dev)))
         for j, sp in enumerate(self.latent_patches):
             acc.apply_subpatch(self.rng, self.segmentations, feats, self.tempo, self.fps,

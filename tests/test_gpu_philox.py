@@ -66,7 +66,8 @@ def test_patch_sampler_kernel_equals_eager_draws(dev):
 
 
 def test_patch_paths_agree(dev):
-    """Patch(...) / Patch.forward with the batched draws == the per-call CUDA draws (configs, bases, generator state)."""
+    """Patch(...) / Patch.forward with the batched draws and the one-launch sub-patch stack == the per-call CUDA draws and
+    one launch per sub-patch (configs, latents bit for bit, bases, generator state)."""
     from ssar_b200.random import patch as P
     from ssar_b200.synth import synth_patch_inputs
 
@@ -76,16 +77,16 @@ def test_patch_paths_agree(dev):
     palette = palette.to(dev)
 
     def run(kernel, batched, seed):
-        P.USE_SAMPLER_KERNEL, P.USE_BATCHED_DRAWS = kernel, batched
+        P.USE_SAMPLER_KERNEL, P.USE_BATCHED_DRAWS, P.USE_LATENT_STACK = kernel, batched, batched
         try:
             p = P.Patch(feats, segs, 120.0, fps=24, seed=seed, device=dev)
             off0 = p.rng.get_offset()
             lat, noise = p.forward(palette, downscale_factor=8)
             return p, off0, lat, noise, p.rng.get_offset()
         finally:
-            P.USE_SAMPLER_KERNEL = P.USE_BATCHED_DRAWS = True
+            P.USE_SAMPLER_KERNEL = P.USE_BATCHED_DRAWS = P.USE_LATENT_STACK = True
 
-    for seed in (42, 7, 1001):
+    for seed in (42, 7, 1001, 5, 6, 8, 9, 10):
         a = run(True, True, seed)
         b = run(False, False, seed)
         assert a[0].latent_patches == b[0].latent_patches and a[0].noise_patches == b[0].noise_patches
