@@ -180,6 +180,7 @@ def main():
     ap.add_argument("--clips", type=int, default=None)
     ap.add_argument("--rng", default="cuda", choices=["cpu", "cuda"], help="device of the per-clip Patch generator")
     ap.add_argument("--workers", type=int, default=None, help="host threads building the per-clip patches")
+    ap.add_argument("--chunk", type=int, default=8, help="clips per feature-graph replay / sampler batch (full workload)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
@@ -231,7 +232,7 @@ def main():
 
         def step(xd, serial=False):
             feats, latents, _ = pipeline.features_and_latents(xd, SR, FPS, palette, segs, rng_device=args.rng,
-                                                              workers=args.workers, serial=serial)
+                                                              workers=args.workers, serial=serial, chunk=args.chunk)
             # the one cross-clip reduction of the path: per-feature (count, sum, sum^2) for the dataset mean / std
             stats.zero_()
             ops.feature_stats(feats, stats)

@@ -100,30 +100,18 @@ __global__ void __launch_bounds__(256) onset_flux_mean128_kernel(const float* __
                 acc += d[3];
                 result = warp_sum(acc) / 128.f;
             } else {
-                // lower median (torch.median): the element of rank 63 under (value, band index) order, found by
-                // counting — every lane ranks its 4 bands against the 128 values parked in shared memory
-                __shared__ float4 med_rows[8][32];
-                float4* row = med_rows[threadIdx.x >> 5];
-                __syncwarp();
-                row[lane] = make_float4(d[0], d[1], d[2], d[3]);
-                __syncwarp();
-                int cnt[4] = {0, 0, 0, 0};
-                for (int q = 0; q < 32; ++q) {
-                    const float4 o = row[q];
-                    const float ov[4] = {o.x, o.y, o.z, o.w};
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        const int e = 4 * q + c;
-#pragma unroll
-                        for (int i = 0; i < 4; ++i)
-                            cnt[i] += (ov[c] < d[i]) || (ov[c] == d[i] && e < 4 * lane + i);
-                    }
+                // lower median (torch.median) = the value of rank 63 of the 128 non-negative flux values: bitwise radix
+                // select on the float bit patterns (monotone for values >= 0) — the largest v with #(values < v) <= 63
+                const unsigned u[4] = {__float_as_uint(d[0]) & 0x7fffffffu, __float_as_uint(d[1]) & 0x7fffffffu,
+                                       __float_as_uint(d[2]) & 0x7fffffffu, __float_as_uint(d[3]) & 0x7fffffffu};
+                unsigned prefix = 0;
+#pragma unroll 1
+                for (int bit = 30; bit >= 0; --bit) {
+                    const unsigned cand = prefix | (1u << bit);
+                    const unsigned c = (u[0] < cand) + (u[1] < cand) + (u[2] < cand) + (u[3] < cand);
+                    if (__reduce_add_sync(0xffffffffu, c) <= 63u) prefix = cand;
                 }
-                float mine = -1.f;  // flux values are >= 0
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    if (cnt[i] == 63) mine = d[i];
-                result = warp_max(mine);
+                result = __uint_as_float(prefix);
             }
             prev = cur;
             jprev = j + 1;
