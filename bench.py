@@ -200,6 +200,12 @@ def main():
     from ssar_b200 import ops, pipeline
     from ssar_b200.synth import synth_batch_device, synth_patch_inputs
 
+    # stdout carries exactly ONE JSON line: libraries that write to fd 1 (NCCL prints its version banner there) are
+    # pointed at stderr, and the result line goes out through a private duplicate of the original stdout
+    sys.stdout.flush()
+    result_fd = os.dup(1)
+    os.dup2(2, 1)
+    result_out = os.fdopen(result_fd, "w")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
@@ -369,7 +375,7 @@ def main():
             v, dt, s = time_cpu(kind, 1 if kind == "full" else 3, 1)
             cpu = {"value": v, "unit": "audio-s/s", "cores": torch.get_num_threads(), "kind": "port",
                    "sample": f"1 clip x {s} s of the same workload, oracle port (torch-CPU fp32), {dt:.2f} s per pass"}
-        print(json.dumps({
+        result_out.write(json.dumps({
             "metric": "audio-sec/sec", "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -381,7 +387,8 @@ def main():
                        "host_threads": (args.workers or pipeline.default_patch_workers(args.rng)) if kind == "full" else 1},
             "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
             "single_track": single,
-        }))
+        }) + "\n")
+        result_out.flush()
     if world > 1:
         dist.destroy_process_group()
 

@@ -618,11 +618,8 @@ def _philox_normal_raw(shapes, seed: int, first_offset: int, device):
     end = C.c_longlong(0)
     cabi.call("ssar_philox_normal_segments", ptrs, ne_arr, i32(n), i64(seed), i64(first_offset), C.byref(end),
               nbytes=4 * total)
-    views, o = [], 0
-    for s, ne in zip(shapes, numels):
-        views.append(flat[o : o + ne].view(s))
-        o += ne
-    return views, int(end.value)
+    parts = flat[:total].split(numels) if total else [flat[:0]] * n  # one call for all slices
+    return [p.view(s) for p, s in zip(parts, shapes)], int(end.value)
 
 
 def philox_batched_ok(device) -> bool:
