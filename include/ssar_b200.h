@@ -405,6 +405,15 @@ typedef struct {
 int ssar_latent_stack(float* weights, int n_rows, int n_groups, int n_basis, const ssar_subpatch_desc* descs, int n_descs,
                       const float* taps, int load_initial, void* stream);
 
+/* maua/maua/audiovisual/audioreactive/latent.py:55-81 (slerp, slerp_loops): spherical interpolation between the
+ * consecutive unit-normalised knots cat([y] * n_loops + [y[0]]) on linspace(0, 1, n_t), rows in the reference's
+ * (t, segment) order, linearly resampled along time to `size` (F.interpolate, align_corners=False), written straight
+ * into out [size, n_layers, latent_dim].  y: [n_latents, n_layers, latent_dim]; n_t = round(size / (n_latents * n_loops
+ * + 1)) (computed by the caller like the reference); scratch: ssar_slerp_loops_scratch_floats(...) floats.          */
+long long ssar_slerp_loops_scratch_floats(int n_latents, int n_loops, int n_layers, int latent_dim);
+int ssar_slerp_loops(const float* y, int n_latents, int n_layers, int latent_dim, int n_loops, int n_t, int size,
+                     float* scratch, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

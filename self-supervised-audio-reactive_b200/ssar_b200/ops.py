@@ -250,8 +250,9 @@ def frames_rms(x: torch.Tensor, frame_length: int, hop: int, n_frames: int):
 PAD_MODES = {"circular": 0, "reflect": 1, "replicate": 2}
 
 
-def gauss1d(x: torch.Tensor, sigma: float, mode: str = "circular", batched: bool = False):
-    """Gaussian smoothing along time.  x: [T, inner...] or, with batched=True, [B, T, inner...] -> same shape."""
+def gauss1d(x: torch.Tensor, sigma: float, mode: str = "circular", batched: bool = False, causal="plain"):
+    """Gaussian smoothing along time.  x: [T, inner...] or, with batched=True, [B, T, inner...] -> same shape.
+    causal: "plain" = features/processing.py's kernel; None / number = maua signal.py's `causal` argument."""
     if not x.is_cuda:
         raise SsarError("ssar_b200 needs CUDA tensors (no CPU fallback)")
     x = x.contiguous().float()
@@ -260,7 +261,8 @@ def gauss1d(x: torch.Tensor, sigma: float, mode: str = "circular", batched: bool
     radius = min(int(sigma * 4), 3 * T)
     if mode not in PAD_MODES:
         raise SsarError(f"gaussian_filter: unsupported padding mode {mode!r}")
-    w = plan.gaussian_taps(float(sigma), radius, str(x.device))
+    w = (plan.gaussian_taps(float(sigma), radius, str(x.device)) if isinstance(causal, str) else
+         plan.gaussian_taps_causal(float(sigma), radius, causal, str(x.device)))
     out = torch.empty_like(x)
     cabi.call("ssar_gauss1d", ptr(x), i32(n_clips), i32(T), i64(inner), ptr(w), i32(radius), i32(PAD_MODES[mode]), ptr(out),
               nbytes=cabi.nbytes_of(x, out))
@@ -557,11 +559,12 @@ def subpatch_merge(weights: torch.Tensor, g_begin: int, g_end: int, selection: t
     return weights
 
 
-def onehot_gauss(labels: torch.Tensor, n_classes: int, sigma: float):
+def onehot_gauss(labels: torch.Tensor, n_classes: int, sigma: float, causal="plain"):
     """labels int64 [T] on the GPU -> circularly smoothed one-hot weights [T, n_classes] (latent.py:39-41)."""
     T = labels.shape[0]
     radius = min(int(sigma * 4), 3 * T)
-    taps = plan.gaussian_taps(float(sigma), radius, str(labels.device))
+    taps = (plan.gaussian_taps(float(sigma), radius, str(labels.device)) if isinstance(causal, str) else
+            plan.gaussian_taps_causal(float(sigma), radius, causal, str(labels.device)))
     out = torch.empty(T, n_classes, dtype=torch.float32, device=labels.device)
     cabi.call("ssar_onehot_gauss", ptr(labels), i32(T), i32(n_classes), ptr(taps), i32(radius), ptr(out),
               nbytes=cabi.nbytes_of(labels, out))
@@ -736,3 +739,19 @@ def latent_stack(weights: torch.Tensor, descs, taps: torch.Tensor | None, load_i
         cabi.call("ssar_latent_stack", ptr(weights), i32(T), i32(G), i32(P), arr, i32(len(part)), ptr(taps),
                   i32(1 if (load_initial or c0 > 0) else 0), nbytes=T * G * P * (8 if (load_initial or c0 > 0) else 4))
     return weights
+
+
+def slerp_loops(y: torch.Tensor, size: int, n_loops: int):
+    """maua audioreactive/latent.py:69-81: y [K, W, L] -> [size, W, L] (see `ssar_slerp_loops`)."""
+    y = y.contiguous().float()
+    K, Wn, L = y.shape
+    n_t = round(size / (K * n_loops + 1))  # Python round, like the reference
+    if n_t < 1:
+        raise RuntimeError("slerp_loops: size is smaller than half the number of knots (linspace of 0 steps)")
+    fn = cabi.lib().ssar_slerp_loops_scratch_floats
+    fn.restype = C.c_longlong
+    scratch = torch.empty(int(fn(i32(K), i32(n_loops), i32(Wn), i32(L))), dtype=torch.float32, device=y.device)
+    out = torch.empty(size, Wn, L, dtype=torch.float32, device=y.device)
+    cabi.call("ssar_slerp_loops", ptr(y), i32(K), i32(Wn), i32(L), i32(n_loops), i32(n_t), i32(size), ptr(scratch), ptr(out),
+              nbytes=cabi.nbytes_of(y, out))
+    return out

@@ -234,6 +234,18 @@ def gaussian_taps(sigma: float, radius: int, device) -> torch.Tensor:
     return k.to(_dev(device))
 
 
+@functools.lru_cache(maxsize=64)
+def gaussian_taps_causal(sigma: float, radius: int, causal, device) -> torch.Tensor:
+    """maua audioreactive/signal.py:124-130: the same Gaussian with the taps right of the centre scaled by `causal`
+    (by 0 when `causal` is not a float) BEFORE the normalisation; `causal=None` = the plain kernel."""
+    k = torch.arange(-radius, radius + 1, dtype=torch.float32)
+    k = torch.exp(-0.5 / sigma ** 2 * k ** 2)
+    if causal is not None:
+        k[radius + 1:] *= 0 if not isinstance(causal, float) else causal
+    k = k / k.sum()
+    return k.to(_dev(device))
+
+
 @dataclass(frozen=True)
 class ContrastBands:
     start: torch.Tensor  # int32 [n_bands + 1]
@@ -520,6 +532,24 @@ def spline_loop_weights_cpu(n_knots: int, size: int, n_loops=1) -> torch.Tensor:
     W = W.copy()
     W[:, 0] += W[:, -1]
     return torch.from_numpy(W[:, :-1].astype(np.float32))
+
+
+def knot_loop_weights_cpu(n_latents: int, size: int, n_loops: int) -> torch.Tensor:
+    """Cardinal weights of maua audioreactive/latent.py:84-92 (spline_loops): natural cubic spline through
+    cat([y] * n_loops + [y[0]]) on linspace(0, 1, K n_loops + 1), evaluated at linspace(0, 1, size); the weight of knot j
+    is folded onto latent j % K.  Returns fp32 [size, n_latents]."""
+    K1 = n_latents * n_loops + 1
+    t_in = torch.linspace(0, 1, K1)
+    t_out = torch.linspace(0, 1, size)
+    idx = (torch.bucketize(t_out, t_in) - 1).clamp(0, K1 - 2)
+    frac = (t_out - t_in[idx]).double().numpy()[:, None]
+    idx = idx.numpy()
+    a, b, c2, d3 = _cardinal_spline_coeffs(K1)
+    Wf = a.T[idx] + (b.T[idx] + (0.5 * c2.T[idx] + d3.T[idx] * frac / 3.0) * frac) * frac  # [size, K1]
+    W = np.zeros((size, n_latents))
+    for j in range(K1):
+        W[:, j % n_latents] += Wf[:, j]
+    return torch.from_numpy(W.astype(np.float32))
 
 
 @functools.lru_cache(maxsize=256)

@@ -198,7 +198,39 @@ def g_traj(ref):
     save("traj", **out)
 
 
-GROUPS = {"traj": g_traj, "a2f": g_a2f, "chroma": g_chroma, "post": g_post, "spectral": g_spectral, "frame_features": g_frame_features, "hpss_filters": g_hpss_filters}
+def g_maua(ref):
+    """maua audioreactive/latent.py + signal.py run unmodified: slerp / spline loops, weighted sums, quantised selection,
+    causal Gaussian.  [T, 18, 512] outputs stored as the fixed 512 -> 8 projection plus a few whole frames."""
+    from ref_loader import load_maua_audioreactive
+
+    ma = load_maua_audioreactive()
+    T = 600
+    R = projection_matrix()
+    _, _, palette = synth_patch_inputs(T, 0)
+    out = {}
+    for name, (k0, k1, loops) in {"a": (0, 5, 1), "b": (5, 8, 3), "c": (8, 20, 2)}.items():
+        sl = ma.latent.slerp_loops(palette[k0:k1], T, loops)
+        out[f"slerp_{name}_proj"], out[f"slerp_{name}_frames"] = sl @ R, sl[::97]
+        sp = ma.latent.spline_loops(palette[k0:k1], T, loops)
+        out[f"spline_{name}_proj"] = sp @ R
+    out["tempo_slerp_proj"] = ma.latent.tempo_loops(palette[:4], T, 24, 96.0, type="slerp") @ R
+    env = synth_features(T, 1, 11).abs().reshape(T)
+    env = env / env.max()
+    out["single_proj"] = ma.latent.single_weighted(palette[0], palette[1], env) @ R
+    envs = synth_features(T, 7, 12).abs() + 0.05
+    out["multi_proj"] = ma.latent.multi_weighted(palette[:7], envs.clone()) @ R
+    out["multi_wrap_proj"] = ma.latent.multi_weighted(palette[:3], envs.clone()) @ R
+    sm = ma.latent.select_modulo(palette[:6], env.clone(), smooth=2)
+    out["select_proj"], out["select_frames"] = sm @ R, sm[::97]
+    x = synth_features(T, 5, 13)
+    out["gauss_causal_none"] = ma.signal.gaussian_filter(x, 3.0)
+    out["gauss_causal_0"] = ma.signal.gaussian_filter(x, 3.0, causal=0)
+    out["gauss_causal_half"] = ma.signal.gaussian_filter(x, 3.0, causal=0.5)
+    out["normalize"] = ma.signal.normalize(x)
+    save("maua", **out)
+
+
+GROUPS = {"maua": g_maua, "traj": g_traj, "a2f": g_a2f, "chroma": g_chroma, "post": g_post, "spectral": g_spectral, "frame_features": g_frame_features, "hpss_filters": g_hpss_filters}
 
 if __name__ == "__main__":
     torch.manual_seed(0)

@@ -279,3 +279,34 @@ if __name__ == "__main__":
     x = torch.randn(24576 * 3)
     print(ref.audio.rms(x, 24576).shape, ref.audio.spectral_flatness(x, 24576).shape)
     print("C1", ref.convert.note_to_hz("C1"))
+
+
+def load_maua_audioreactive():
+    """The two trajectory files of the vendored maua package (`audioreactive/latent.py`, `audioreactive/signal.py`),
+    imported unmodified through symlinks as the throw-away package `maua_ar` (the real package __init__ pulls librosa,
+    madmom, openunmix...).  Shims: torchtyping.TensorType (annotations only), torchcubicspline (as above)."""
+    if not reference_available():
+        raise RuntimeError(f"reference not found at {REFERENCE_ROOT}")
+    _install_shims()
+
+    class _TT:
+        def __class_getitem__(cls, item):
+            return cls
+
+    if "torchtyping" not in sys.modules:
+        m = types.ModuleType("torchtyping")
+        m.TensorType = _TT
+        sys.modules["torchtyping"] = m
+    d = TREE / "maua_ar"
+    d.mkdir(parents=True, exist_ok=True)
+    (d / "__init__.py").write_text("")
+    for f in ("latent.py", "signal.py"):
+        dst = d / f
+        if not dst.exists():
+            dst.symlink_to(REFERENCE_ROOT / "maua/maua/audiovisual/audioreactive" / f)
+    if str(TREE) not in sys.path:
+        sys.path.insert(0, str(TREE))
+    ns = types.SimpleNamespace()
+    ns.signal = importlib.import_module("maua_ar.signal")
+    ns.latent = importlib.import_module("maua_ar.latent")
+    return ns
