@@ -90,7 +90,7 @@ __global__ void col_minmax_kernel(const float* __restrict__ x, int T, int C, flo
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void col_quantile_kernel(const float* __restrict__ x, int T, int C, int subset, double q, int interp,
                                     const float* __restrict__ pre_sub, const float* __restrict__ pre_div,
-                                    float* __restrict__ out, int* __restrict__ count_out) {
+                                    float* __restrict__ out, int* __restrict__ count_out, int staged_keys) {
     __shared__ uint32_t hist[256];
     __shared__ uint32_t bcast[2];
     __shared__ int s_count;
@@ -106,10 +106,14 @@ __global__ void col_quantile_kernel(const float* __restrict__ x, int T, int C, i
     c.div = c.pre ? pre_div[clip * C + col] : 1.f;
     if (threadIdx.x == 0) s_count = 0;
     __syncthreads();
+    extern __shared__ uint32_t q_keys[];  // staged keys of the selected subset (when the launch provides room for T)
+    const bool staged = staged_keys != 0;
     int local = 0;
     for (int t = threadIdx.x; t < T; t += blockDim.x) {
         float v;
-        local += sel_value(c, t, v) ? 1 : 0;
+        if (!sel_value(c, t, v)) continue;
+        if (staged) q_keys[atomicAdd(&s_count, 1)] = f2key(v);
+        else ++local;
     }
     if (local) atomicAdd(&s_count, local);
     __syncthreads();
@@ -132,8 +136,9 @@ __global__ void col_quantile_kernel(const float* __restrict__ x, int T, int C, i
         lo = (long long)rank;
         hi = (long long)ceil(rank);
     }
-    const float vlo = key2f(radix_select(c, lo, hist, bcast));
-    const float vhi = hi == lo ? vlo : key2f(radix_select(c, hi, hist, bcast));
+    const uint32_t* kp = staged ? q_keys : nullptr;
+    const float vlo = key2f(radix_select(c, lo, hist, bcast, kp, n));
+    const float vhi = hi == lo ? vlo : key2f(radix_select(c, hi, hist, bcast, kp, n));
     if (threadIdx.x == 0) {
         float r;
         if (interp == 0) {  // ATen lerp: w < 0.5 ? a + w (b - a) : b - (b - a)(1 - w)
@@ -284,8 +289,11 @@ extern "C" int ssar_col_quantile(const float* x, int n_clips, int n_frames, int 
     SSAR_REQUIRE((pre_sub == nullptr) == (pre_div == nullptr), "col_quantile: pre_sub and pre_div go together");
     SSAR_REQUIRE(n_clips <= 65535, "col_quantile: too many clips per launch");
     const int threads = n_frames >= 4096 ? 512 : 256;
-    col_quantile_kernel<<<dim3(n_cols, n_clips), threads, 0, ST(stream)>>>(x, n_frames, n_cols, subset, q, interp, pre_sub,
-                                                                          pre_div, out, count_out);
+    // columns of up to 11 776 frames are staged (as order-preserving keys) in shared memory once; the ~9 radix passes
+    // then never touch the strided column again
+    const int staged = n_frames <= 11776 ? 1 : 0;  // 46 KB + the static arrays stay under the 48 KB default
+    col_quantile_kernel<<<dim3(n_cols, n_clips), threads, staged ? (size_t)n_frames * sizeof(uint32_t) : 0, ST(stream)>>>(
+        x, n_frames, n_cols, subset, q, interp, pre_sub, pre_div, out, count_out, staged);
     return ssar_launch_status("col_quantile");
 }
 
