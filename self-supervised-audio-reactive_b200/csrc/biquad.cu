@@ -87,6 +87,7 @@ __global__ void __launch_bounds__(CPB) biquad_chunks_kernel(const float* __restr
     const int clip = blockIdx.y;
     const float* xc = x + (long long)clip * stride_x;
     const long long tile0 = (long long)blockIdx.x * CPB * L;
+#pragma unroll 4
     for (int i = threadIdx.x; i < CPB * L; i += CPB) {
         const long long g = tile0 + i;
         tile[(i / L) * LDT + (i % L)] = g < n ? __ldg(xc + g) : 0.f;

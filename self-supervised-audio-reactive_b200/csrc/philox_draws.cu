@@ -25,6 +25,7 @@ struct SegBatch {
     float* dst[MAX_SEG];
     long long numel[MAX_SEG];
     unsigned long long offset[MAX_SEG];
+    unsigned blk_start[MAX_SEG + 1];  // first CTA of every segment in the flattened grid (exclusive prefix of its blocks)
     int n;
 };
 
@@ -35,12 +36,18 @@ __host__ __device__ inline unsigned seg_blocks(long long numel, unsigned max_blo
 
 // randn: out[li] = (k-th component of the c-th curand_normal4 call of thread li mod S), S = 256 * blocks
 __global__ void __launch_bounds__(PB) normal_segments_kernel(const SegBatch sb, unsigned long long seed, unsigned max_blocks) {
-    const int s = blockIdx.y;
+    // flattened grid: CTA -> (segment, block inside the segment's emulated ATen grid) by binary search over blk_start
+    int lo = 0, hi = sb.n;
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (sb.blk_start[mid] <= blockIdx.x) lo = mid; else hi = mid;
+    }
+    const int s = lo;
     const long long numel = sb.numel[s];
     const unsigned blocks = seg_blocks(numel, max_blocks);
-    if (blockIdx.x >= blocks) return;
+    const unsigned bx = blockIdx.x - sb.blk_start[s];
     const long long S = (long long)blocks * PB;
-    const long long idx = (long long)blockIdx.x * PB + threadIdx.x;
+    const long long idx = (long long)bx * PB + threadIdx.x;
     curandStatePhilox4_32_10_t state;
     curand_init(seed, (unsigned long long)idx, sb.offset[s], &state);
     float* __restrict__ out = sb.dst[s];
@@ -241,7 +248,7 @@ extern "C" int ssar_philox_normal_segments(float* const* dst, const long long* n
     while (done < n_segments) {
         SegBatch sb;
         sb.n = 0;
-        unsigned gx = 1;
+        unsigned gx = 0;
         while (done < n_segments && sb.n < MAX_SEG) {
             const long long ne = numel[done];
             SSAR_REQUIRE(ne >= 0, "philox_normal_segments: negative numel");
@@ -250,15 +257,16 @@ extern "C" int ssar_philox_normal_segments(float* const* dst, const long long* n
                 sb.dst[sb.n] = dst[done];
                 sb.numel[sb.n] = ne;
                 sb.offset[sb.n] = off;
-                const unsigned b = seg_blocks(ne, maxb);
-                if (b > gx) gx = b;
+                sb.blk_start[sb.n] = gx;
+                gx += seg_blocks(ne, maxb);
                 off += (unsigned long long)ssar_philox_normal_increment(ne);
                 ++sb.n;
             }
             ++done;
         }
         if (sb.n > 0) {
-            normal_segments_kernel<<<dim3(gx, sb.n), PB, 0, (cudaStream_t)stream>>>(sb, (unsigned long long)seed, maxb);
+            sb.blk_start[sb.n] = gx;
+            normal_segments_kernel<<<gx, PB, 0, (cudaStream_t)stream>>>(sb, (unsigned long long)seed, maxb);
             const int rc = ssar_launch_status("philox_normal_segments");
             if (rc != SSAR_OK) return rc;
         }
