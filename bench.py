@@ -61,10 +61,14 @@ class ClockSampler:
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index: int):
-        self.index, self.rows, self.proc = index, [], None
+    def __init__(self, indices, enabled=True):
+        """indices: GPU indices to watch (ONE nvidia-smi process for all of them: rank 0 samples the whole job, so N ranks
+        do not run N pollers against the driver during the timed region)."""
+        self.index, self.rows, self.proc, self.enabled = ",".join(str(i) for i in indices), [], None, enabled
 
     def __enter__(self):
+        if not self.enabled:
+            return self
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
@@ -257,7 +261,7 @@ def main():
     barrier()
     launches0 = cabi.launch_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local_rank) as clocks:
+    with ClockSampler(range(world) if world > 1 else [local_rank], enabled=(rank == 0)) as clocks:
         barrier()
         ev0.record()
         for _ in range(args.steps):

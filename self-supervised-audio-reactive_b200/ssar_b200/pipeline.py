@@ -162,16 +162,32 @@ class FeatureGraph:
     copied (or staged from pinned host memory) into the static buffer `x`; outputs are static too and must be consumed or
     cloned before the next replay (`run` returns clones of the small ones)."""
 
-    _cache = {}
+    _cache = {}     # key -> FeatureGraph, insertion-ordered: least recently used first
+    _seen = {}      # key -> how often the shape was asked for
+    MAX_GRAPHS = 3  # each graph pins its private pool (~0.4 GB per clip): keep only the most recently used shapes
 
     @classmethod
     def get(cls, n_clips, n_samples, sr, fps, device):
         device = torch.device(device)
         key = (int(n_clips), int(n_samples), float(sr), int(fps), device.index)
-        g = cls._cache.get(key)
+        g = cls._cache.pop(key, None)
         if g is None:
-            g = cls._cache[key] = cls(n_clips, n_samples, sr, fps, device)
+            g = cls(n_clips, n_samples, sr, fps, device)
+            while len(cls._cache) >= cls.MAX_GRAPHS:
+                cls._cache.pop(next(iter(cls._cache)))  # drops the graph and its pool
+        cls._cache[key] = g
         return g
+
+    @classmethod
+    def get_if_recurring(cls, n_clips, n_samples, sr, fps, device):
+        """The graph for this shape from its SECOND request on (None the first time): a dataset of clips of many different
+        lengths runs eagerly instead of capturing — and pinning memory for — a graph per length."""
+        device = torch.device(device)
+        key = (int(n_clips), int(n_samples), float(sr), int(fps), device.index)
+        n = cls._seen[key] = cls._seen.get(key, 0) + 1
+        if len(cls._seen) > 4096:
+            cls._seen.clear()
+        return cls.get(n_clips, n_samples, sr, fps, device) if (n >= 2 or key in cls._cache) else None
 
     def __init__(self, n_clips, n_samples, sr, fps, device):
         self.device, self.sr, self.fps = device, sr, fps
@@ -301,7 +317,11 @@ def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, se
     if USE_FEATURE_GRAPHS and not serial:
         # captured here, before the helper threads start launching (one graph per distinct chunk size)
         with torch.cuda.device(dev), torch.cuda.stream(stream):
-            fgraphs = {n: FeatureGraph.get(n, audio.shape[1], sr, fps, dev) for n in {c1 - c0 for c0, c1 in bounds}}
+            fgraphs = {}
+            for n in sorted({c1 - c0 for c0, c1 in bounds}):
+                g = FeatureGraph.get_if_recurring(n, audio.shape[1], sr, fps, dev)
+                if g is not None:
+                    fgraphs[n] = g
     if serial:
         feats_chunks, latents, noises = [], None, [None] * B
         with torch.cuda.device(dev), torch.cuda.stream(stream):

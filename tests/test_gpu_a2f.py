@@ -106,10 +106,12 @@ def test_features_and_latents_graph_vs_serial():
     xs = torch.stack([synth_clip(44100 * 45, 44100, i) for i in (3, 9, 4)]).cuda()
     _, segs, palette = synth_patch_inputs(1080, 0)
     palette = palette.cuda()
-    fa, la, _ = pipeline.features_and_latents(xs, 44100, 24, palette, segs, chunk=2)
+    f0, l0, _ = pipeline.features_and_latents(xs, 44100, 24, palette, segs, chunk=2)  # first sight of the shape: eager
+    fa, la, _ = pipeline.features_and_latents(xs, 44100, 24, palette, segs, chunk=2)  # recurring shape: graph replays
+    assert any(k[0] == 2 and k[1] == xs.shape[1] for k in pipeline.FeatureGraph._cache)
     fb, lb, _ = pipeline.features_and_latents(xs, 44100, 24, palette, segs, chunk=2, serial=True)
     torch.cuda.synchronize()
-    assert torch.equal(fa, fb) and torch.equal(la, lb)
+    assert torch.equal(fa, fb) and torch.equal(la, lb) and torch.equal(f0, fb) and torch.equal(l0, lb)
     # pinned host input: staged chunk by chunk
     fc, lc, _ = pipeline.features_and_latents(xs.cpu().pin_memory(), 44100, 24, palette, segs, chunk=2)
     torch.cuda.synchronize()
