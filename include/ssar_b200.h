@@ -414,6 +414,10 @@ long long ssar_slerp_loops_scratch_floats(int n_latents, int n_loops, int n_laye
 int ssar_slerp_loops(const float* y, int n_latents, int n_layers, int latent_dim, int n_loops, int n_t, int size,
                      float* scratch, float* out, void* stream);
 
+/* processing.py:52-55 normalize for per-clip arrays of <= 262 144 elements: min, max and the rescale in ONE launch (one
+ * CTA per clip) — same result as ssar_minmax_keys + ssar_normalize.                                                  */
+int ssar_normalize_fused(const float* x, int n_clips, long long n_per_clip, float eps, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

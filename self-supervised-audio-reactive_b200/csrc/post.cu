@@ -181,6 +181,33 @@ __global__ void normalize_kernel(const float* __restrict__ x, long long n_per_cl
         oc[i] = (xc[i] - mn) / den;
 }
 
+// normalize for small per-clip arrays (<= 256 k elements, L2 resident): ONE CTA per clip finds min / max and rescales —
+// one launch instead of two key fills + minmax + normalize.  Same min / max (exact) and the same expression per element.
+__global__ void __launch_bounds__(1024) normalize_fused_kernel(const float* __restrict__ x, long long n_per_clip, float eps,
+                                                                float* __restrict__ out) {
+    __shared__ float scratch[32];
+    __shared__ float s_mn, s_mx;
+    const int clip = blockIdx.x;
+    const float* xc = x + (long long)clip * n_per_clip;
+    float* oc = out + (long long)clip * n_per_clip;
+    float mn = INFINITY, mx = -INFINITY;
+    for (long long i = threadIdx.x; i < n_per_clip; i += blockDim.x) {
+        const float v = xc[i];
+        mn = fminf(mn, v);
+        mx = fmaxf(mx, v);
+    }
+    mn = block_min(mn, scratch);
+    __syncthreads();
+    mx = block_max(mx, scratch);
+    if (threadIdx.x == 0) {
+        s_mn = mn;
+        s_mx = mx;
+    }
+    __syncthreads();
+    const float lo = s_mn, den = (s_mx - s_mn) + eps;
+    for (long long i = threadIdx.x; i < n_per_clip; i += blockDim.x) oc[i] = (xc[i] - lo) / den;
+}
+
 // emphasize (processing.py:132-138): xn = (x - min)/max' ; xn * (1 + tanh(s (xn - qv))) * max' + min
 __global__ void emphasize_kernel(const float* __restrict__ x, long long n_per_clip, int C, const float* __restrict__ mn,
                                  const float* __restrict__ rng, const float* __restrict__ qv, float strength,
@@ -319,6 +346,14 @@ extern "C" int ssar_normalize(const float* x, int n_clips, long long n_per_clip,
     SSAR_REQUIRE(x && min_key && max_key && out, "normalize: null pointer");
     normalize_kernel<<<flat_grid(n_per_clip, n_clips), 256, 0, ST(stream)>>>(x, n_per_clip, min_key, max_key, eps, out);
     return ssar_launch_status("normalize");
+}
+
+extern "C" int ssar_normalize_fused(const float* x, int n_clips, long long n_per_clip, float eps, float* out, void* stream) {
+    if (n_clips == 0 || n_per_clip == 0) return SSAR_OK;
+    SSAR_REQUIRE(x && out, "normalize_fused: null pointer");
+    SSAR_REQUIRE(n_per_clip <= (1LL << 18), "normalize_fused: at most 262 144 elements per clip (use minmax_keys + normalize)");
+    normalize_fused_kernel<<<n_clips, 1024, 0, ST(stream)>>>(x, n_per_clip, eps, out);
+    return ssar_launch_status("normalize_fused");
 }
 
 extern "C" int ssar_emphasize(const float* x, int n_clips, int n_frames, int n_cols, const float* col_min,

@@ -299,8 +299,12 @@ def clamp_cols(x: torch.Tensor, lo=None, hi=None):
 def normalize(x: torch.Tensor, n_clips: int = 1, eps: float = 1e-8):
     """(x - min) / ((max - min) + eps) with min/max over each clip's whole array."""
     x = x.contiguous()
-    mn, mx = minmax_keys(x, n_clips)
     out = torch.empty_like(x)
+    n_per = x.numel() // max(n_clips, 1)
+    if 0 < n_per <= (1 << 18) and x.dtype == torch.float32:
+        cabi.call("ssar_normalize_fused", ptr(x), i32(n_clips), i64(n_per), f32(eps), ptr(out), nbytes=cabi.nbytes_of(x, out))
+        return out
+    mn, mx = minmax_keys(x, n_clips)
     cabi.call("ssar_normalize", ptr(x), i32(n_clips), i64(x.numel() // max(n_clips, 1)), ptr(mn), ptr(mx), f32(eps), ptr(out),
               nbytes=cabi.nbytes_of(x, out))
     return out
