@@ -374,6 +374,13 @@ def main():
             "timing": "CUDA events around each launch on the launching stream, one extra step queued serially",
         }
         roof["frac"] = roof["achieved"] / peak if roof["achieved"] else None
+        # DRAM traffic of the dominant kernel from the committed ncu --set full captures (dram__bytes_read + write summed
+        # over its launches of one step, scaled to this run's clip count): profiles/r01_ncu_frames_fft_full_v6.md (full:
+        # 3.242 GB per 8 clips) and profiles/r01_frames_fft_v1.md (cfg2: 2.316 GB per 16 clips)
+        ncu_bytes_per_clip = {"full": 3.2419e9 / 8, "cfg2": 2.3160e9 / 16}
+        if name == "ssar_frames_fft":
+            roof["traffic"] = ncu_bytes_per_clip[kind] * B
+            roof["traffic_source"] = "ncu capture (profiles/), per step"
         cpu = None
         if world == 1 and not args.no_cpu:
             v, dt, s = time_cpu(kind, 1 if kind == "full" else 3, 1)
