@@ -611,7 +611,7 @@ def philox_normal_increment(numel: int) -> int:
     return int(fn(C.c_longlong(int(numel))))
 
 
-def _philox_normal_raw(shapes, seed: int, first_offset: int, device):
+def _philox_normal_raw(shapes, seed: int, first_offset: int, device, lazy_views: bool = False):
     numels = [int(math.prod(s)) for s in shapes]
     total = sum(numels)
     flat = torch.empty(max(total, 1), dtype=torch.float32, device=device)
@@ -625,8 +625,14 @@ def _philox_normal_raw(shapes, seed: int, first_offset: int, device):
     end = C.c_longlong(0)
     cabi.call("ssar_philox_normal_segments", ptrs, ne_arr, i32(n), i64(seed), i64(first_offset), C.byref(end),
               nbytes=4 * total)
-    parts = flat[:total].split(numels) if total else [flat[:0]] * n  # one call for all slices
-    return [p.view(s) for p, s in zip(parts, shapes)], int(end.value)
+    if lazy_views:  # the caller slices `flat` when (if) the tensors are looked at
+        return (flat, numels, total), int(end.value)
+    return _segment_views(flat, numels, total, shapes), int(end.value)
+
+
+def _segment_views(flat, numels, total, shapes):
+    parts = flat[:total].split(numels) if total else [flat[:0]] * len(shapes)  # one call for all slices
+    return [p.view(s) for p, s in zip(parts, shapes)]
 
 
 def philox_batched_ok(device) -> bool:
@@ -661,6 +667,16 @@ def philox_normal_segments(shapes, rng: torch.Generator):
     views, end = _philox_normal_raw(shapes, rng.initial_seed(), rng.get_offset(), dev)
     rng.set_offset(end)
     return views
+
+
+def philox_normal_segments_deferred(shapes, rng: torch.Generator):
+    """Same launch and generator advance as `philox_normal_segments`; returns a zero-argument function that slices the
+    drawn buffer into the per-shape tensors when called (the ~100 view objects of a Patch cost more host time than the
+    launch itself, and lazy noise modules may never be evaluated)."""
+    (flat, numels, total), end = _philox_normal_raw(shapes, rng.initial_seed(), rng.get_offset(), rng.device, lazy_views=True)
+    rng.set_offset(end)
+    shapes = list(shapes)
+    return lambda: _segment_views(flat, numels, total, shapes)
 
 
 def patch_sample(seeds: torch.Tensor, program: torch.Tensor, n_head: int, n_lat: int, n_noise: int, min_sub: int,

@@ -296,6 +296,51 @@ def noise_draw_shapes(sizes, noise_patches, features):
     return shapes
 
 
+class LazyNoisePrograms:
+    """The 17 per-layer noise programs of one Patch, built on first use.  `Patch.forward` draws every basis eagerly (one
+    batched Philox launch: the generator ends in the reference's state) and hands the recipe — the sub-patch configs, the
+    bound features and the drawn buffer — to this object; the per-layer op lists and the per-sub-patch modulator
+    scalings (ssar/random/noise.py:89-140) materialise when a layer is first evaluated or inspected, like the lazy
+    `forward(i, b)` of the reference's modules.  Building them costs ~0.5 ms of Python per Patch, which a batch pipeline
+    that only consumes latents (or evaluates a few layers) should not pay up front."""
+
+    def __init__(self, views_fn, length, sizes, n_loops, sigma, device, noise_patches, features, tempo, fps):
+        self._args = (views_fn, length, sizes, n_loops, sigma, device, [dict(sp) for sp in noise_patches], features, tempo, fps)
+        self._progs = None
+        self._lock = __import__("threading").Lock()
+
+    def programs(self):
+        with self._lock:
+            if self._progs is None:
+                views_fn, length, sizes, n_loops, sigma, device, patches, feats, tempo, fps = self._args
+                with torch.cuda.device(device):
+                    draws = iter(views_fn())
+                    progs = base_noise_programs(None, length, sizes, n_loops, sigma, device, draws=draws)
+                    for sp in patches:
+                        progs = noise_patch_programs(None, progs, feats, tempo, fps, draws=draws, **sp)
+                self._progs, self._args = progs, None
+            return self._progs
+
+
+class LazyNoiseProgram(NoiseProgram):
+    """Layer `index` of a `LazyNoisePrograms` recipe: a `NoiseProgram` whose `steps` appear on first access."""
+
+    def __init__(self, owner, index, length, size, device):
+        Noise.__init__(self, length, size)
+        self._device = torch.device(device)
+        self._owner, self._index, self._steps = owner, index, None
+
+    @property
+    def steps(self):
+        if self._steps is None:
+            self._steps = self._owner.programs()[self._index].steps
+        return self._steps
+
+    @steps.setter
+    def steps(self, value):
+        self._steps = value
+
+
 def base_noise_programs(rng, length, sizes, n_loops, sigma, device, draws=None):
     """patch.py:123-131: one `Loop` per layer (same draw per layer: randn(3, H, W)).
     draws: iterator over pre-drawn bases (batched Philox launch, same values) instead of one torch.randn per layer."""
@@ -328,7 +373,7 @@ def noise_patch_programs(rng, progs, features, tempo, fps, patch_type, loop_bars
     if patch_type == "loop":
         phase = plan.loop_phase(length / fps / 60 / tempo / 4 / loop_bars, int(length), str(dev))
     merged = merge_type in ("average", "modulate")
-    rdev = rng.device
+    rdev = rng.device if rng is not None else None
     for n in layers:
         p = progs[n]
         h, w = p.size

@@ -12,7 +12,8 @@ import torch
 from . import DEVICE
 from .latent import LatentWeights, latent_patch, merge_coefficients, sequence_weights, spline_loop_latents  # noqa: F401
 from .mir import ALLFEATS, UNITFEATS
-from .noise import Loop, base_noise_programs, noise_draw_shapes, noise_patch, noise_patch_programs  # noqa: F401
+from .noise import (LazyNoiseProgram, LazyNoisePrograms, Loop, base_noise_programs, noise_draw_shapes,  # noqa: F401
+                    noise_patch, noise_patch_programs)
 from .. import ops, plan
 
 
@@ -398,6 +399,7 @@ def _eager_sample(rng, ks, min_subpatches, max_subpatches):
 
 USE_SAMPLER_GRAPHS = True  # CUDA generators only; False = the eager deferred sampler
 USE_BATCHED_DRAWS = True   # CUDA generators only: noise bases of a Patch in one Philox launch (ssar_philox_normal_segments)
+USE_LAZY_NOISE_PROGRAMS = True  # with batched draws: per-layer noise op lists are built on first use (bases drawn eagerly)
 USE_LATENT_STACK = True    # Patch.forward: all latent sub-patches of a clip in one launch (ssar_latent_stack)
 USE_SAMPLER_KERNEL = True  # CUDA generators only: the config sampler as one kernel per batch of seeds (ssar_patch_sample)
 
@@ -555,6 +557,13 @@ class Patch:
         sizes = [(round(aspect_ratio * size / downscale_factor), round(size / downscale_factor))
                  for size in [4, 8, 8, 16, 16, 32, 32, 64, 64, 128, 128, 256, 256, 512, 512, 1024, 1024]]
         draws = None
+        if (self.rng.device.type == "cuda" and USE_BATCHED_DRAWS and USE_LAZY_NOISE_PROGRAMS
+                and ops.philox_batched_ok(self.rng.device)):
+            # every basis drawn now (one launch, generator advanced as the reference's calls would); op lists on demand
+            views_fn = ops.philox_normal_segments_deferred(noise_draw_shapes(sizes, self.noise_patches, feats), self.rng)
+            owner = LazyNoisePrograms(views_fn, self.length, sizes, self.loops_base_noise, self.sigma_base_noise, dev,
+                                      self.noise_patches, feats, self.tempo, self.fps)
+            return latents, [LazyNoiseProgram(owner, j, self.length, sizes[j], dev) for j in range(len(sizes))]
         if self.rng.device.type == "cuda" and USE_BATCHED_DRAWS and ops.philox_batched_ok(self.rng.device):
             # every basis draw of this patch in one launch: same Philox streams as the per-layer torch.randn calls
             draws = iter(ops.philox_normal_segments(noise_draw_shapes(sizes, self.noise_patches, feats), self.rng))
