@@ -418,6 +418,16 @@ int ssar_slerp_loops(const float* y, int n_latents, int n_layers, int latent_dim
  * CTA per clip) — same result as ssar_minmax_keys + ssar_normalize.                                                  */
 int ssar_normalize_fused(const float* x, int n_clips, long long n_per_clip, float eps, float* out, void* stream);
 
+/* ssar_biquad that also leaves the sums of squares of its (clamped) output per 1024-sample block in
+ * block_ss [n_clips, ceil(n_samples / 1024) + 2] (the last two entries of a row are y[0] and y[1024]); y may be NULL when
+ * only the framed RMS of the filtered signal is wanted (supervised/data.py:75-86: rms(low_pass(..)), ...).
+ * ssar_rms_from_block_ss turns those sums into rms(y, 2048, 1024) [n_clips, n_frames] (features/audio.py:31-37):
+ * frame t >= 1 = blocks t - 1 and t, frame 0 = the reflected edge.                                               */
+int ssar_biquad_ss(const float* x, long long n_samples, long long stride_x, int n_clips, float b0, float b1, float b2,
+                   float a1, float a2, int clamp, float* y, long long stride_y, float* block_ss, void* scratch,
+                   void* stream);
+int ssar_rms_from_block_ss(const float* block_ss, long long n_blocks, int n_clips, int n_frames, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -80,7 +80,8 @@ __global__ void __launch_bounds__(CPB) biquad_chunks_kernel(const float* __restr
                                                             float2* __restrict__ state_out, float* __restrict__ y,
                                                             long long stride_y, long long n_chunks, int clamp,
                                                             V2* __restrict__ cta_z, const V2* __restrict__ cta_s,
-                                                            double a1d, double a2d) {
+                                                            double a1d, double a2d, float* __restrict__ block_ss,
+                                                            long long n_ss_blocks) {
     __shared__ float tile[CPB * LDT];
     __shared__ V2 sq[CPB];
     const ALPowers pw = al_powers(a1d, a2d);
@@ -94,7 +95,7 @@ __global__ void __launch_bounds__(CPB) biquad_chunks_kernel(const float* __restr
     }
     __syncthreads();
     const long long chunk = (long long)blockIdx.x * CPB + threadIdx.x;
-    float y1 = 0.f, y2 = 0.f;
+    float y1 = 0.f, y2 = 0.f, ssq = 0.f;
     if (WRITE) {
         // true state entering every chunk of this CTA: S_j = AL^(j+1) S_in + sum_{i<=j} AL^(j-i) z_i (fp64), chunk j starts
         // from S_{j-1}; S_in = the state entering the CTA from the carry kernel
@@ -129,7 +130,13 @@ __global__ void __launch_bounds__(CPB) biquad_chunks_kernel(const float* __restr
         for (int i = 0; i < L; ++i) {
             const float x0 = row[i];
             const float yy = step(c, x0, x1, x2, y1, y2);
-            if (WRITE) row[i] = clamp ? fminf(fmaxf(yy, -1.f), 1.f) : yy;
+            if (WRITE) {
+                const float yo = clamp ? fminf(fmaxf(yy, -1.f), 1.f) : yy;
+                row[i] = yo;
+                if (n0 + i < n) ssq = fmaf(yo, yo, ssq);
+                if (i == 0 && block_ss && (n0 == 0 || n0 == 1024))  // y[0], y[1024]: the reflected edge of rms frame 0
+                    block_ss[(long long)clip * (n_ss_blocks + 2) + n_ss_blocks + (n0 == 0 ? 0 : 1)] = yo;
+            }
             x2 = x1;
             x1 = x0;
             y2 = y1;
@@ -144,7 +151,15 @@ __global__ void __launch_bounds__(CPB) biquad_chunks_kernel(const float* __restr
         const V2 q = block_scan_states(z, pw, sq);
         if (threadIdx.x == CPB - 1) cta_z[(long long)clip * gridDim.x + blockIdx.x] = q;
     }
-    if (WRITE) {
+    if (WRITE && block_ss) {
+        // sum of squares of the (clamped) output per 1024-sample block = 16 consecutive chunks = 16 lanes
+        static_assert(L * 16 == 1024, "block_ss assumes 16 chunks per 1024 samples");
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) ssq += __shfl_xor_sync(0xffffffffu, ssq, o);
+        const long long blk = (long long)blockIdx.x * (CPB / 16) + (threadIdx.x >> 4);
+        if ((threadIdx.x & 15) == 0 && blk < n_ss_blocks) block_ss[(long long)clip * (n_ss_blocks + 2) + blk] = ssq;
+    }
+    if (WRITE && y) {
         __syncthreads();
         float* yc = y + (long long)clip * stride_y;
         for (int i = threadIdx.x; i < CPB * L; i += CPB) {
@@ -213,6 +228,25 @@ __global__ void __launch_bounds__(1024) biquad_carry_kernel(const V2* __restrict
     }
 }
 
+// rms(y, frame_length 2048, hop 1024, centre, reflect) (features/audio.py:31-37) from the per-1024-sample sums of squares
+// the biquad's output pass leaves behind: frame t >= 1 covers blocks t - 1 and t; frame 0 covers the reflection
+// y[1024..1] followed by y[0..1023].  y is only read for that one edge frame (two samples per clip).
+__global__ void rms_from_block_ss_kernel(const float* __restrict__ ss, long long n_blocks, int n_frames,
+                                         float* __restrict__ out) {
+    const int clip = blockIdx.y;
+    const float* s = ss + (long long)clip * (n_blocks + 2);  // [n_blocks sums | y[0] | y[1024]]
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n_frames; t += gridDim.x * blockDim.x) {
+        float acc;
+        if (t == 0) {
+            const float a = s[n_blocks], b = s[n_blocks + 1];
+            acc = s[0] + ((s[0] - a * a) + b * b);
+        } else {
+            acc = s[t - 1] + s[t];
+        }
+        out[(long long)clip * n_frames + t] = sqrtf(acc / 2048.f);
+    }
+}
+
 }  // namespace
 
 extern "C" long long ssar_biquad_scratch_bytes(int n_clips, long long n_samples) {
@@ -221,11 +255,11 @@ extern "C" long long ssar_biquad_scratch_bytes(int n_clips, long long n_samples)
     return (long long)n_clips * n_chunks * (long long)sizeof(float2) + 16 + 2LL * n_clips * n_ctas * 16;
 }
 
-extern "C" int ssar_biquad(const float* x, long long n_samples, long long stride_x, int n_clips, float b0, float b1,
-                           float b2, float a1, float a2, int clamp, float* y, long long stride_y, void* scratch,
-                           void* stream) {
+static int biquad_impl(const float* x, long long n_samples, long long stride_x, int n_clips, float b0, float b1, float b2,
+                       float a1, float a2, int clamp, float* y, long long stride_y, float* block_ss, void* scratch,
+                       void* stream) {
     if (n_clips == 0 || n_samples == 0) return SSAR_OK;
-    SSAR_REQUIRE(x && y && scratch, "biquad: null pointer");
+    SSAR_REQUIRE(x && (y || block_ss) && scratch, "biquad: null pointer");
     SSAR_REQUIRE(n_clips <= 65535, "biquad: too many clips per launch");
     cudaStream_t st = (cudaStream_t)stream;
     const long long n_chunks = (n_samples + L - 1) / L;
@@ -237,10 +271,35 @@ extern "C" int ssar_biquad(const float* x, long long n_samples, long long stride
     V2* cs = cz + (long long)n_clips * n_ctas;
     const Coef c = {b0, b1, b2, a1, a2};
     dim3 grid((unsigned)n_ctas, n_clips);
+    const long long n_ss = (n_samples + 1023) / 1024;
     biquad_chunks_kernel<false><<<grid, CPB, 0, st>>>(x, n_samples, stride_x, c, nullptr, z, nullptr, 0, n_chunks, 0, cz,
-                                                     nullptr, (double)a1, (double)a2);
+                                                     nullptr, (double)a1, (double)a2, nullptr, 0);
     biquad_carry_kernel<<<n_clips, 1024, 0, st>>>(cz, cs, n_ctas, (double)a1, (double)a2);
     biquad_chunks_kernel<true><<<grid, CPB, 0, st>>>(x, n_samples, stride_x, c, z, nullptr, y, stride_y, n_chunks, clamp,
-                                                    nullptr, cs, (double)a1, (double)a2);
+                                                    nullptr, cs, (double)a1, (double)a2, block_ss, n_ss);
     return ssar_launch_status("biquad");
+}
+
+extern "C" int ssar_biquad(const float* x, long long n_samples, long long stride_x, int n_clips, float b0, float b1,
+                           float b2, float a1, float a2, int clamp, float* y, long long stride_y, void* scratch,
+                           void* stream) {
+    SSAR_REQUIRE(y != nullptr, "biquad: null pointer");
+    return biquad_impl(x, n_samples, stride_x, n_clips, b0, b1, b2, a1, a2, clamp, y, stride_y, nullptr, scratch, stream);
+}
+
+extern "C" int ssar_biquad_ss(const float* x, long long n_samples, long long stride_x, int n_clips, float b0, float b1,
+                              float b2, float a1, float a2, int clamp, float* y, long long stride_y, float* block_ss,
+                              void* scratch, void* stream) {
+    SSAR_REQUIRE(block_ss != nullptr, "biquad_ss: null block_ss");
+    return biquad_impl(x, n_samples, stride_x, n_clips, b0, b1, b2, a1, a2, clamp, y, stride_y, block_ss, scratch, stream);
+}
+
+extern "C" int ssar_rms_from_block_ss(const float* block_ss, long long n_blocks, int n_clips, int n_frames, float* out,
+                                      void* stream) {
+    if (n_clips == 0 || n_frames == 0) return SSAR_OK;
+    SSAR_REQUIRE(block_ss && out, "rms_from_block_ss: null pointer");
+    SSAR_REQUIRE(n_frames <= n_blocks && n_blocks >= 2, "rms_from_block_ss: frame t needs blocks t - 1 and t");
+    rms_from_block_ss_kernel<<<dim3(ssar_div_up(n_frames, 256), n_clips), 256, 0, (cudaStream_t)stream>>>(
+        block_ss, n_blocks, n_frames, out);
+    return ssar_launch_status("rms_from_block_ss");
 }

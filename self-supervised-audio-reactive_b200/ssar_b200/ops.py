@@ -223,6 +223,28 @@ def biquad(x: torch.Tensor, coeffs, clamp: bool = True):
     return y
 
 
+def biquad_rms(x: torch.Tensor, coeffs, clamp: bool = True, want_signal: bool = False, n_frames: int | None = None):
+    """rms(biquad(x), 2048, 1024)[:, :n_frames] -> [B, n_frames] from the filter's own output pass (per-1024-sample sums
+    of squares), without a second pass over the filtered signal; the signal itself is only written with want_signal
+    (-> (rms, y)).  Same filter arithmetic as `biquad`."""
+    x, _ = _as_batch(x)
+    B, N = x.shape
+    n_blocks = (N + 1023) // 1024
+    T = N // 1024 if n_frames is None else int(n_frames)
+    if n_blocks < 2 or T > n_blocks:
+        raise SsarError("biquad_rms: clip too short for 2048-sample frames")
+    y = torch.empty(B, N, dtype=torch.float32, device=x.device) if want_signal else None
+    ss = torch.empty(B, n_blocks + 2, dtype=torch.float32, device=x.device)
+    nbytes = cabi.lib().ssar_biquad_scratch_bytes(C.c_int(B), C.c_longlong(N))
+    scratch = torch.empty(max(int(nbytes), 8), dtype=torch.uint8, device=x.device)
+    b0, b1, b2, a1, a2 = coeffs
+    cabi.call("ssar_biquad_ss", ptr(x), i64(N), i64(x.stride(0)), i32(B), f32(b0), f32(b1), f32(b2), f32(a1), f32(a2),
+              i32(1 if clamp else 0), ptr(y), i64(N), ptr(ss), ptr(scratch), nbytes=cabi.nbytes_of(x, y))
+    out = torch.empty(B, T, dtype=torch.float32, device=x.device)
+    cabi.call("ssar_rms_from_block_ss", ptr(ss), i64(n_blocks), i32(B), i32(T), ptr(out), nbytes=cabi.nbytes_of(ss, out))
+    return (out, y) if want_signal else out
+
+
 def resample(x: torch.Tensor, rp, post_scale: float = 1.0):
     """x [B, N] -> [B, ceil(new*N/orig)] with a `plan.ResamplePlan`."""
     x, _ = _as_batch(x)

@@ -57,6 +57,14 @@ def band_split(x: torch.Tensor, sr):
     return ops.biquad(x, lo_c, clamp=True), ops.biquad(high, lo_c, clamp=True), high
 
 
+def band_rms(x: torch.Tensor, sr, n_frames: int):
+    """rms(low_pass(x)), rms(mid_pass(x)), rms(high_pass(x)) (frame 2048 / hop 1024) -> three [B, n_frames] tensors, from
+    the filters' own output passes: only the 4 kHz high-pass signal (the mid filter's input) is ever written."""
+    lo_c, hi_c = plan.biquad_coeffs("low", sr, 200), plan.biquad_coeffs("high", sr, 4000)
+    r_hi, high = ops.biquad_rms(x, hi_c, want_signal=True, n_frames=n_frames)
+    return ops.biquad_rms(x, lo_c, n_frames=n_frames), ops.biquad_rms(high, lo_c, n_frames=n_frames), r_hi
+
+
 def onset_pair(x: torch.Tensor, sr, hop: int = 1024, n_fft: int = 2048, want_median: bool = False):
     """onset_strength(x) with mean aggregation (+ the median-aggregated envelope plp needs) from one mel pass."""
     bank = plan.mel_bank(float(sr), n_fft, 128, 0.0, 11025.0, str(x.device))
@@ -113,10 +121,15 @@ def audio2features_batch(audio: torch.Tensor, sr, fps, clamp=True, smooth=True, 
     pulse = ops.plp_from_onset(on_med, sr, hop)
 
     # --- rms of the harmonic part and its bands; drop strength of the full signal and its bands
-    h_lo, h_mid, h_hi = band_split(harm, sr)
-    rms_h = [ops.frames_rms(s, n_fft, hop, T) for s in (harm, h_lo, h_mid, h_hi)]
-    a_lo, a_mid, a_hi = band_split(x, sr)
-    rms_a = torch.stack([fa["rms"]] + [ops.frames_rms(s, n_fft, hop, T) for s in (a_lo, a_mid, a_hi)], dim=-1)  # [B,T,4]
+    if n_fft == 2048 and hop == 1024 and N >= 2048:
+        # band signals of harm / x are only ever looked at through their RMS: taken from the filters' output passes
+        rms_h = [ops.frames_rms(harm, n_fft, hop, T), *band_rms(harm, sr, T)]
+        rms_a = torch.stack([fa["rms"], *band_rms(x, sr, T)], dim=-1)  # [B,T,4]
+    else:
+        h_lo, h_mid, h_hi = band_split(harm, sr)
+        rms_h = [ops.frames_rms(s, n_fft, hop, T) for s in (harm, h_lo, h_mid, h_hi)]
+        a_lo, a_mid, a_hi = band_split(x, sr)
+        rms_a = torch.stack([fa["rms"]] + [ops.frames_rms(s, n_fft, hop, T) for s in (a_lo, a_mid, a_hi)], dim=-1)
     drop = ops.emphasize(ops.gauss1d(rms_a, 10, "circular", batched=True), 10, 50)
 
     Tm = min(T, cens.shape[1])

@@ -97,3 +97,25 @@ def test_resample_vs_golden():
     yb = resample(xs.cuda(), 48000, 24576)
     for b in range(2):
         assert rel_l2(yb[b], dsp.resample(xs[b], 48000, 24576)) < 1e-5
+
+
+def test_biquad_rms_equals_rms_of_biquad():
+    """ops.biquad_rms (framed RMS from the filter's own output pass) == frames_rms(biquad(x)) — features/audio.py:31-37 on
+    features/processing.py:141-150 — including the reflected first frame; the optional signal is biquad's, bit for bit."""
+    import torch
+
+    from ssar_b200 import ops, plan
+    from ssar_b200.synth import synth_clip
+
+    sr = 24576
+    x = torch.stack([synth_clip(sr * 20 + 777, sr, i) for i in (2, 5)]).cuda()
+    T = x.shape[1] // 1024
+    for kind, fc in (("low", 200), ("high", 4000)):
+        c = plan.biquad_coeffs(kind, sr, fc)
+        y = ops.biquad(x, c, clamp=True)
+        ref = ops.frames_rms(y, 2048, 1024, T)
+        got, y2 = ops.biquad_rms(x, c, want_signal=True, n_frames=T)
+        assert torch.equal(y, y2)
+        assert got.shape == ref.shape and rel_l2(got, ref) < 1e-6
+        assert float((got[:, 0] - ref[:, 0]).abs().max()) < 1e-6 * float(ref.abs().max())
+        assert rel_l2(ops.biquad_rms(x, c, n_frames=T), ref) < 1e-6
