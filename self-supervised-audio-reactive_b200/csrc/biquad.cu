@@ -91,10 +91,24 @@ __global__ void __launch_bounds__(CPB) biquad_chunks_kernel(const float* __restr
     const int clip = blockIdx.y;
     const float* xc = x + (long long)clip * stride_x;
     const long long tile0 = (long long)blockIdx.x * CPB * L;
+    const bool vec_ok = tile0 + (long long)CPB * L <= n && ((reinterpret_cast<uintptr_t>(xc + tile0) & 15) == 0);
+    if (vec_ok) {  // whole tile inside the clip and 16-byte aligned: 128-bit loads, 8 in flight per thread
+        const float4* __restrict__ x4 = reinterpret_cast<const float4*>(xc + tile0);
+#pragma unroll 8
+        for (int q = threadIdx.x; q < CPB * L / 4; q += CPB) {
+            const float4 v = __ldg(x4 + q);
+            float* d = tile + ((4 * q) / L) * LDT + ((4 * q) % L);
+            d[0] = v.x;
+            d[1] = v.y;
+            d[2] = v.z;
+            d[3] = v.w;
+        }
+    } else {
 #pragma unroll 4
-    for (int i = threadIdx.x; i < CPB * L; i += CPB) {
-        const long long g = tile0 + i;
-        tile[(i / L) * LDT + (i % L)] = g < n ? __ldg(xc + g) : 0.f;
+        for (int i = threadIdx.x; i < CPB * L; i += CPB) {
+            const long long g = tile0 + i;
+            tile[(i / L) * LDT + (i % L)] = g < n ? __ldg(xc + g) : 0.f;
+        }
     }
     __syncthreads();
     const long long chunk = (long long)blockIdx.x * CPB + threadIdx.x;
@@ -165,9 +179,18 @@ __global__ void __launch_bounds__(CPB) biquad_chunks_kernel(const float* __restr
     if (WRITE && y) {
         __syncthreads();
         float* yc = y + (long long)clip * stride_y;
-        for (int i = threadIdx.x; i < CPB * L; i += CPB) {
-            const long long g = tile0 + i;
-            if (g < n) yc[g] = tile[(i / L) * LDT + (i % L)];
+        if (tile0 + (long long)CPB * L <= n && ((reinterpret_cast<uintptr_t>(yc + tile0) & 15) == 0)) {
+            float4* __restrict__ y4 = reinterpret_cast<float4*>(yc + tile0);
+#pragma unroll 4
+            for (int q = threadIdx.x; q < CPB * L / 4; q += CPB) {
+                const float* d = tile + ((4 * q) / L) * LDT + ((4 * q) % L);
+                y4[q] = make_float4(d[0], d[1], d[2], d[3]);
+            }
+        } else {
+            for (int i = threadIdx.x; i < CPB * L; i += CPB) {
+                const long long g = tile0 + i;
+                if (g < n) yc[g] = tile[(i / L) * LDT + (i % L)];
+            }
         }
     }
 }
