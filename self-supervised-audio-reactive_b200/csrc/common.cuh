@@ -80,5 +80,14 @@ __host__ __device__ __forceinline__ float key2f(uint32_t k) {
 }
 
 // atomic max/min on floats via the order-preserving key (buffers hold keys; init with ssar_fill_u32)
-__device__ __forceinline__ void atomic_max_key(uint32_t* addr, float v) { atomicMax(addr, f2key(v)); }
-__device__ __forceinline__ void atomic_min_key(uint32_t* addr, float v) { atomicMin(addr, f2key(v)); }
+// The running extreme is read first (from L2: it only ever moves one way, so a stale value costs one redundant atomic,
+// never a wrong result): tens of thousands of warps fold into ONE word per clip, and same-address atomics serialise at
+// ~1-2 ns each in L2 — unfiltered they were most of spectral contrast's run time.
+__device__ __forceinline__ void atomic_max_key(uint32_t* addr, float v) {
+    const uint32_t k = f2key(v);
+    if (k > __ldcg(addr)) atomicMax(addr, k);
+}
+__device__ __forceinline__ void atomic_min_key(uint32_t* addr, float v) {
+    const uint32_t k = f2key(v);
+    if (k < __ldcg(addr)) atomicMin(addr, k);
+}

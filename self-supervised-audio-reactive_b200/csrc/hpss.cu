@@ -107,23 +107,27 @@ __global__ void __launch_bounds__(HP_THREADS, 2) hpss_kernel(const float2* __res
 
     {   // phase 1: median along time (window rows r .. r+30 at column c+15) -> harmonic-enhanced
         const int c = threadIdx.x % TF, r = (threadIdx.x / TF) * 4;
-        float m[4];
-        median31_x4(mag + r * LDS + c + HALF, LDS, m);
+        if (f0 + c < n_bins && t0 + r < n_frames) {  // 1025 bins = 16 tiles + 1 column: the last tile is nearly empty
+            float m[4];
+            median31_x4(mag + r * LDS + c + HALF, LDS, m);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) gh[(r + j) * LDG + c] = m[j];
+            for (int j = 0; j < 4; ++j) gh[(r + j) * LDG + c] = m[j];
+        }
     }
     __syncthreads();
     {   // phase 2: median along frequency (row r+15, columns c .. c+30) -> percussive-enhanced; soft masks -> gains
         const int r = threadIdx.x % TT, c = (threadIdx.x / TT) * 4;
-        float m[4];
-        median31_x4(mag + (r + HALF) * LDS + c, 1, m);
-        const float split = (margin_h == 1.f && margin_p == 1.f) ? 0.5f : 0.f;  // rosa/spectral.py:158
+        if (f0 + c < n_bins && t0 + r < n_frames) {
+            float m[4];
+            median31_x4(mag + (r + HALF) * LDS + c, 1, m);
+            const float split = (margin_h == 1.f && margin_p == 1.f) ? 0.5f : 0.f;  // rosa/spectral.py:158
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const float harm = gh[r * LDG + c + j], perc = m[j];
-            const float S = mag[(r + HALF) * LDS + c + j + HALF];
-            gh[r * LDG + c + j] = S * softmask2(harm, perc * margin_h, split);
-            gp[r * LDG + c + j] = S * softmask2(perc, harm * margin_p, split);
+            for (int j = 0; j < 4; ++j) {
+                const float harm = gh[r * LDG + c + j], perc = m[j];
+                const float S = mag[(r + HALF) * LDS + c + j + HALF];
+                gh[r * LDG + c + j] = S * softmask2(harm, perc * margin_h, split);
+                gp[r * LDG + c + j] = S * softmask2(perc, harm * margin_p, split);
+            }
         }
     }
     __syncthreads();

@@ -69,3 +69,21 @@ def test_contrast_full_length_properties():
     assert tuple(c.shape) == (5760, 7) and bool(torch.isfinite(c).all())
     ref = dsp.spectral_contrast(x, sr)
     assert rel_l2(c, ref) < TOL_CHROMA
+
+
+def test_contrast_sorted_columns_equal_general_kernel():
+    """Bands of <= 512 bins take the sorted-lane-column kernel; declaring a wider slab forces the general arg-min
+    kernel on the same bands.  Same values summed in the same order -> bit-equal, ragged band sizes included."""
+    import dataclasses
+
+    from ssar_b200 import ops, plan
+
+    g = torch.Generator().manual_seed(5)
+    mag = torch.rand(2, 301, 1025, generator=g).cuda()
+    mag[0, :, 40:60] = 0.25  # ties
+    for n_fft_bins, fmin, nb in ((2048, 200.0, 6), (2048, 300.0, 6)):
+        bands = plan.contrast_bands(22050.0, n_fft_bins, fmin, nb, 0.02, "cuda")
+        assert bands.max_count <= 512
+        fast = ops.spectral_contrast(mag, bands)
+        slow = ops.spectral_contrast(mag, dataclasses.replace(bands, max_count=600))
+        assert torch.equal(fast, slow)
