@@ -34,6 +34,7 @@ KEYS = [
     ("smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio", "st_notsel"),
     ("smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio", "st_noinst"),
 ]
+csv.field_size_limit(1 << 30)
 rows = list(csv.reader(open(sys.argv[1], errors="replace")))
 rows = [r for r in rows if len(r) > 10]
 hdr, units = rows[0], rows[1]
