@@ -58,6 +58,16 @@ typedef struct {
     long long ld;
     uint32_t* max_key;      /* optional [n_clips]: running max of `out` per clip as an order-preserving key
                                (ssar_fill_u32 it with 0 first); feeds power_to_db's global-max floor */
+    /* optional (all four or none; on_power banks only): the same weights lane-interleaved for the kernel's warps.
+       Bands go in passes of 32 (band 32 p + lane); band b's window starts at the 4-aligned bin lane_start4[b]
+       ([n_pass*32]) and every band of pass p spans 4 * lane_count4[p] bins, zero weights padding the rest;
+       lane_weights[((lane_offset4[p] + k4) * 32 + lane) * 4 + c] multiplies bin lane_start4[b] + 4 k4 + c.  Windows
+       may run up to 64 bins past the spectrum (the kernel keeps that tail zero).  Results are bit-identical to the
+       packed form: the extra terms are fmaf(0, finite, acc). */
+    const int* lane_start4;
+    const int* lane_count4;
+    const int* lane_offset4;
+    const float* lane_weights;
 } ssar_filterbank;
 
 /* a banded complex projection of the complex spectrum: out[row] = scale * sum_k w[offset+k] * X[start+k] */

@@ -12,13 +12,15 @@
 
 namespace {
 
+constexpr int LANE_PAD = 64;  // zeroed floats behind the M + 1 bins of a power tile (lane-interleaved banks read into them)
+
 template <int M>
 size_t frames_smem_bytes(bool window, bool separate_power) {
     using L = WarpFft<M>;
     size_t b = (size_t)32 * L::N1 * sizeof(float2);                  // twiddle table [k2][n1]
     if (window) b += (size_t)2 * M * sizeof(float);
     b += (size_t)L::WPB * L::FPW * L::ZF * sizeof(float2);
-    if (separate_power) b += (size_t)L::WPB * L::FPW * (M + 4) * sizeof(float);
+    if (separate_power) b += (size_t)L::WPB * L::FPW * (M + 4 + LANE_PAD) * sizeof(float);
     return b;
 }
 
@@ -134,7 +136,7 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
             __syncwarp();
 
             // epilogue 1: complex / power / magnitude outputs, flatness sums; the power tile goes to shared memory
-            float* pw = separate_power ? pall + (size_t)(warp * FPW + fs) * (M + 4) : reinterpret_cast<float*>(z);
+            float* pw = separate_power ? pall + (size_t)(warp * FPW + fs) * (M + 4 + LANE_PAD) : reinterpret_cast<float*>(z);
             if (a.out_complex || need_pw) {
                 float2* oc = a.out_complex ? reinterpret_cast<float2*>(a.out_complex) + orow * a.ldc : nullptr;
                 float* os = a.out_spec ? a.out_spec + orow * a.lds : nullptr;
@@ -169,6 +171,8 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
                         const int k = lane + 32 * j;
                         if (k < NBINS) pw[k] = pj[j];
                     }
+                    static_assert(2 * ZF >= NBINS + 3 + LANE_PAD, "the zeroed tail must fit the aliased frame buffer");
+                    for (int k = NBINS + lane; k < NBINS + 3 + LANE_PAD; k += 32) pw[k] = 0.f;
                     __syncwarp();
                 }
             }
@@ -179,6 +183,32 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
                 const ssar_filterbank& fb = a.fb[q];
                 if (fb.n_bands <= 0) continue;
                 float bmax = -INFINITY;
+                if (fb.lane_weights && fb.on_power) {
+                    // lane-interleaved weights: one coalesced 512-byte row of weights and one 128-bit tile read per
+                    // 4 bins, warp-uniform trip count per pass of 32 bands
+                    const int n_pass = (fb.n_bands + 31) >> 5;
+                    for (int p = 0; p < n_pass; ++p) {
+                        const int b = 32 * p + lane;
+                        const int n4 = __ldg(fb.lane_count4 + p);
+                        const float4* __restrict__ w =
+                            reinterpret_cast<const float4*>(fb.lane_weights) + (size_t)__ldg(fb.lane_offset4 + p) * 32 + lane;
+                        const float4* pp = reinterpret_cast<const float4*>(pw + __ldg(fb.lane_start4 + b));
+                        float acc = 0.f;
+#pragma unroll 4
+                        for (int k4 = 0; k4 < n4; ++k4) {
+                            const float4 wv = __ldg(w + (size_t)k4 * 32);
+                            const float4 pv = pp[k4];
+                            acc = fmaf(wv.x, pv.x, acc);
+                            acc = fmaf(wv.y, pv.y, acc);
+                            acc = fmaf(wv.z, pv.z, acc);
+                            acc = fmaf(wv.w, pv.w, acc);
+                        }
+                        if (b < fb.n_bands) {
+                            fb.out[orow * fb.ld + b] = acc;
+                            bmax = fmaxf(bmax, acc);
+                        }
+                    }
+                } else
                 for (int b = lane; b < fb.n_bands; b += 32) {
                     const int st = __ldg(fb.start + b), cn = __ldg(fb.count + b);
                     const float* __restrict__ w = fb.weights + __ldg(fb.offset + b);

@@ -27,6 +27,8 @@ class Filterbank(C.Structure):
         ("n_bands", C.c_int), ("on_power", C.c_int),
         ("start", C.c_void_p), ("count", C.c_void_p), ("offset", C.c_void_p), ("weights", C.c_void_p),
         ("out", C.c_void_p), ("ld", C.c_longlong), ("max_key", C.c_void_p),
+        ("lane_start4", C.c_void_p), ("lane_count4", C.c_void_p), ("lane_offset4", C.c_void_p),
+        ("lane_weights", C.c_void_p),
     ]
 
 

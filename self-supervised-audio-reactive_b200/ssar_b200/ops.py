@@ -104,6 +104,10 @@ def frames_fft(
         fb.on_power = 1 if on_power else 0
         fb.start, fb.count, fb.offset = bank.start.data_ptr(), bank.count.data_ptr(), bank.offset.data_ptr()
         fb.weights = bank.weights.data_ptr()
+        if getattr(bank, "lanes", None) is not None and on_power:
+            ln = bank.lanes
+            fb.lane_start4, fb.lane_count4 = ln.start4.data_ptr(), ln.count4.data_ptr()
+            fb.lane_offset4, fb.lane_weights = ln.offset4.data_ptr(), ln.weights.data_ptr()
         o = torch.empty(B, n_frames, bank.n_rows, dtype=torch.float32, device=dev)
         out[f"bank{i}"] = o
         fb.out = o.data_ptr()

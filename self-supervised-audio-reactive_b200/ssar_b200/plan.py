@@ -60,6 +60,51 @@ class Banded:
     offset: torch.Tensor  # int32 [n_rows]
     weights: torch.Tensor  # fp32 [nnz] (or [nnz, 2] for complex)
     dense: torch.Tensor   # the dense matrix on the device (row-major), for GEMM-style consumers / inspection
+    lanes: object = None  # LaneBanks (real banks only): the lane-interleaved form the frames_fft epilogue streams
+
+
+LANE_PAD = 64  # zeroed floats the frames_fft kernel keeps behind the n_cols spectrum bins of its power tile
+
+
+@dataclass
+class LaneBanks:
+    """Rows in passes of 32 (row 32 p + lane): lane reads 4 k4 + c of its row's 16-byte-aligned window
+    [start4, start4 + 4 count4[p]) at weights[((offset4[p] + k4) * 32 + lane) * 4 + c]; zero weights pad every row to
+    its pass's longest, so a warp streams coalesced 512-byte rows of weights whatever the row widths."""
+
+    start4: torch.Tensor   # int32 [n_pass * 32]
+    count4: torch.Tensor   # int32 [n_pass]
+    offset4: torch.Tensor  # int32 [n_pass]
+    weights: torch.Tensor  # fp32 [sum(count4) * 32 * 4]
+
+
+def lane_banks(starts, counts, rows_cpu, n_cols, device):
+    """rows_cpu[r]: the packed fp32 weights of row r.  None when a padded window would leave the zeroed tile tail."""
+    n_rows = len(starts)
+    n_pass = (n_rows + 31) // 32
+    start4 = [0] * (n_pass * 32)
+    count4, offset4, blocks = [], [], []
+    off = 0
+    for p_ in range(n_pass):
+        rows = range(32 * p_, min(32 * p_ + 32, n_rows))
+        n4 = max([((starts[r] & 3) + counts[r] + 3) // 4 for r in rows] + [0])
+        blk = torch.zeros(n4, 32, 4, dtype=torch.float32)
+        for r in rows:
+            s4 = starts[r] & ~3
+            if s4 + 4 * n4 > n_cols + LANE_PAD:
+                return None
+            start4[r] = s4
+            lead = starts[r] - s4
+            flat = torch.zeros(4 * n4, dtype=torch.float32)
+            flat[lead:lead + counts[r]] = rows_cpu[r]
+            blk[:, r - 32 * p_, :] = flat.view(n4, 4)
+        count4.append(n4)
+        offset4.append(off)
+        off += n4
+        blocks.append(blk.reshape(-1))
+    i32 = lambda v: torch.tensor(v, dtype=torch.int32, device=device)
+    w = torch.cat(blocks) if blocks else torch.zeros(0)
+    return LaneBanks(i32(start4), i32(count4), i32(offset4), w.contiguous().to(device))
 
 
 def banded_from_dense(dense_cpu: torch.Tensor, device) -> Banded:
@@ -83,9 +128,11 @@ def banded_from_dense(dense_cpu: torch.Tensor, device) -> Banded:
         off += c
     w = torch.cat(chunks) if off > 0 else torch.zeros((0, 2) if is_c else (0,), dtype=torch.float32)
     i32 = lambda v: torch.tensor(v, dtype=torch.int32, device=device)
+    lanes = None if is_c else lane_banks(starts, counts, chunks, n_cols, device)
     return Banded(
         n_rows, n_cols, i32(starts), i32(counts), i32(offsets), w.contiguous().to(device),
         (torch.view_as_real(dense_cpu.to(torch.complex64)) if is_c else dense_cpu.to(torch.float32)).contiguous().to(device),
+        lanes,
     )
 
 

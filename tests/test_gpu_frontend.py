@@ -137,3 +137,24 @@ def test_parseval_full_size():
         seg = x[:, t * 512 - 1024 : t * 512 + 1024] * w
         assert torch.allclose(lhs[:, t], (seg * seg).sum(-1), rtol=2e-4)
         assert torch.allclose(out["rms"][:, t], x[:, t * 512 - 1024 : t * 512 + 1024].pow(2).mean(-1).sqrt(), rtol=1e-4)
+
+
+def test_lane_interleaved_banks_equal_packed_banks():
+    """The filterbank epilogue streams lane-interleaved, zero-padded weights (plan.lane_banks); dropping that form sends
+    the same launch down the packed per-band loop.  Zero-weight terms are fmaf(0, finite, acc): bit-equal, for both
+    transform sizes, two banks per launch, band counts that are not a multiple of 32, and with the running max."""
+    import dataclasses
+
+    from ssar_b200 import ops, plan
+
+    x = torch.stack([synth_clip(22050 * 3, 22050, i) for i in (1, 5)]).cuda()
+    for n_fft, hop, n_mels in ((2048, 512, 128), (1024, 256, 40)):
+        a = plan.mel_bank(22050.0, n_fft, n_mels, 0.0, None, "cuda")
+        b = plan.mel_bank(22050.0, n_fft, 20, 300.0, 8000.0, "cuda")
+        assert a.lanes is not None and b.lanes is not None
+        n_frames = 1 + x.shape[1] // hop
+        fast = ops.frames_fft(x, n_fft, hop, n_frames, banks=((a, True, True), (b, True, False)))
+        packed = [dataclasses.replace(k, lanes=None) for k in (a, b)]
+        slow = ops.frames_fft(x, n_fft, hop, n_frames, banks=((packed[0], True, True), (packed[1], True, False)))
+        for key in ("bank0", "bank1", "bank0_max"):
+            assert torch.equal(fast[key], slow[key]), (n_fft, key)
