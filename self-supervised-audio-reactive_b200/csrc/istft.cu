@@ -130,36 +130,58 @@ __global__ void __launch_bounds__(32 * OD_SEG) overlap_add_dense_kernel(const fl
     const float* fc = frames + (long long)clip * n_frames * n_fft;
     float* oc = out + (long long)clip * length;
     const long long total = (long long)n_fft + (long long)hop * (n_frames - 1);
-    const long long n = (long long)blockIdx.x * 32 + threadIdx.x;
-    const long long p = n + n_fft / 2;
-    float acc = 0.f, env = 0.f;
-    if (n < length && p < total) {
-        long long t_hi = p / hop;
-        if (t_hi > n_frames - 1) t_hi = n_frames - 1;
-        long long t_lo = (p - n_fft + hop) / hop;
-        if (p - n_fft + 1 <= 0) t_lo = 0;
-        const long long cnt = t_hi - t_lo + 1, per = (cnt + OD_SEG - 1) / OD_SEG;
-        const long long a = t_lo + seg * per;
-        long long b = a + per - 1;
-        if (b > t_hi) b = t_hi;
+    // Persistent over 32-sample blocks (one full wave of CTAs instead of 1.1).  A sample covered by all n_fft / hop
+    // frames sees the window in the same order whatever its position, so this warp's share of the envelope is computed
+    // once (same fmaf order as the general loop below) and reused for every such block.
+    const int full = n_fft / hop;  // frames over an interior sample (hop divides n_fft in this path)
+    float env_full = 0.f;
+    bool have_env_full = false;
+    for (long long blk = blockIdx.x; blk * 32 < length; blk += gridDim.x) {
+        const long long n = blk * 32 + threadIdx.x;
+        const long long p = n + n_fft / 2;
+        float acc = 0.f, env = 0.f;
+        if (n < length && p < total) {
+            long long t_hi = p / hop;
+            if (t_hi > n_frames - 1) t_hi = n_frames - 1;
+            long long t_lo = (p - n_fft + hop) / hop;
+            if (p - n_fft + 1 <= 0) t_lo = 0;
+            const long long cnt = t_hi - t_lo + 1, per = (cnt + OD_SEG - 1) / OD_SEG;
+            const long long a = t_lo + seg * per;
+            long long b = a + per - 1;
+            if (b > t_hi) b = t_hi;
+            // hop == 1: i = p - t runs over the same values for every interior sample
+            const bool interior = hop == 1 && cnt == full;
+            const bool warp_interior = __all_sync(__activemask(), interior) && __activemask() == 0xffffffffu;
+            if (warp_interior && have_env_full) {
 #pragma unroll 8
-        for (long long t = a; t <= b; ++t) {
-            const int i = (int)(p - t * hop);
-            acc += __ldg(fc + t * n_fft + i);
-            const float w = win ? __ldg(win + i) : 1.f;
-            env = fmaf(w, w, env);
+                for (long long t = a; t <= b; ++t) acc += __ldg(fc + t * n_fft + (int)(p - t * hop));
+                env = env_full;
+            } else {
+#pragma unroll 8
+                for (long long t = a; t <= b; ++t) {
+                    const int i = (int)(p - t * hop);
+                    acc += __ldg(fc + t * n_fft + i);
+                    const float w = win ? __ldg(win + i) : 1.f;
+                    env = fmaf(w, w, env);
+                }
+                if (warp_interior) {
+                    env_full = env;
+                    have_env_full = true;
+                }
+            }
         }
-    }
-    sacc[seg][threadIdx.x] = acc;
-    senv[seg][threadIdx.x] = env;
-    __syncthreads();
-    if (seg == 0 && n < length) {
+        sacc[seg][threadIdx.x] = acc;
+        senv[seg][threadIdx.x] = env;
+        __syncthreads();
+        if (seg == 0 && n < length) {
 #pragma unroll
-        for (int s = 1; s < OD_SEG; ++s) {
-            acc += sacc[s][threadIdx.x];
-            env += senv[s][threadIdx.x];
+            for (int s2 = 1; s2 < OD_SEG; ++s2) {
+                acc += sacc[s2][threadIdx.x];
+                env += senv[s2][threadIdx.x];
+            }
+            oc[n] = env > 1e-11f ? acc / env : 0.f;
         }
-        oc[n] = env > 1e-11f ? acc / env : 0.f;
+        __syncthreads();
     }
 }
 
@@ -362,7 +384,10 @@ extern "C" int ssar_overlap_add(const float* frames, const float* window, int n_
         return ssar_launch_status("overlap_add");
     }
     if (n_fft / hop >= 64 && (length + 31) / 32 <= 0x7fffffffLL) {
-        overlap_add_dense_kernel<<<dim3((unsigned)((length + 31) / 32), n_clips), dim3(32, OD_SEG), 0, (cudaStream_t)stream>>>(
+        long long gd = (length + 31) / 32;
+        const long long capd = ((long long)SSAR_NUM_SMS * 8 + n_clips - 1) / n_clips;  // 8 CTAs of 256 threads per SM
+        if (gd > capd) gd = capd;
+        overlap_add_dense_kernel<<<dim3((unsigned)gd, n_clips), dim3(32, OD_SEG), 0, (cudaStream_t)stream>>>(
             frames, window, n_fft, hop, n_frames, length, out);
         return ssar_launch_status("overlap_add");
     }

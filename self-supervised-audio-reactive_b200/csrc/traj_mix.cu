@@ -209,103 +209,142 @@ struct StackArgs {
     int n;
 };
 
+// v2: the sources of ALL sub-patches are independent of W, so they are evaluated side by side first (phase A: every
+// thread has its global loads of ~n sub-patches in flight at once, one barrier), and a weight element then walks the
+// stack in a register (phase B: element (t, g, p) after sub-patch j depends only on itself and S_j[t][inv_j[p]]), so
+// the per-sub-patch barriers and their serialised load latencies (v1: 5 barriers x n, barrier stall 5-6 per issue) are
+// gone and W no longer needs shared memory.  Per-element arithmetic is unchanged.
 __global__ void __launch_bounds__(256) latent_stack_kernel(float* __restrict__ Wt, int T, int G, int P, const StackArgs sa,
-                                                           const float* __restrict__ taps, int load_initial) {
+                                                           const float* __restrict__ taps, int load_initial, int n_label) {
     extern __shared__ float st_smem[];
+    const int n = sa.n;
     const int GP = G * P;
-    float* W = st_smem;                                    // [SP_TT][G * P]
-    float* S = W + SP_TT * GP;                             // [SP_TT][STACK_KMAX]
-    float* OH = S + SP_TT * STACK_KMAX;                    // [SP_TT + 2 * 8][STACK_KMAX] (radius <= 8)
-    float* ab = OH + (SP_TT + 16) * STACK_KMAX;            // [SP_TT][2]
-    int* inv = reinterpret_cast<int*>(ab + SP_TT * 2);     // [P]
+    float* S = st_smem;                                          // [n][SP_TT][STACK_KMAX]
+    float* ab = S + n * SP_TT * STACK_KMAX;                      // [n][SP_TT][2]
+    float* OH = ab + n * SP_TT * 2;                              // [n_label][SP_TT + 16][STACK_KMAX] (radius <= 8)
+    signed char* inv = reinterpret_cast<signed char*>(OH + n_label * (SP_TT + 16) * STACK_KMAX);  // [n][P]
+    __shared__ int label_slot[STACK_MAX], item_off[STACK_MAX + 1];
     const int t0 = blockIdx.x * SP_TT;
     const int rows = min(SP_TT, T - t0);
-    if (load_initial)
-        for (int i = threadIdx.x; i < rows * GP; i += blockDim.x) W[i] = Wt[(long long)t0 * GP + i];
-    for (int j = 0; j < sa.n; ++j) {
-        const ssar_subpatch_desc& d = sa.d[j];
-        const int K = d.n_select, radius = d.radius;
-        __syncthreads();  // previous sub-patch applied; S / inv / OH free
-        for (int p = threadIdx.x; p < P; p += blockDim.x) inv[p] = -1;
-        __syncthreads();
-        for (int k = threadIdx.x; k < K; k += blockDim.x) {
-            const long long p = d.selection[k];
-            if (p >= 0 && p < P) inv[(int)p] = k;
+
+    for (int i = threadIdx.x; i < n * P; i += blockDim.x) inv[i] = -1;
+    if (threadIdx.x == 0) {
+        int c = 0, o = 0;
+        for (int j = 0; j < n; ++j) {
+            label_slot[j] = sa.d[j].src_mode == 2 ? c++ : -1;
+            item_off[j] = o;
+            o += SP_TT * sa.d[j].n_select;
         }
-        if (d.src_mode == 2) {
-            // smoothed one-hot rows for t0 - radius .. t0 + SP_TT + radius (onehot_gauss_kernel's tap order)
-            const long long* __restrict__ labels = reinterpret_cast<const long long*>(d.src);
-            const int nr = SP_TT + 2 * radius, pr = d.pre_radius;
-            for (int i = threadIdx.x; i < nr * K; i += blockDim.x) {
-                const int rr = i / K, k = i - rr * K;
-                int t = (t0 - radius + rr) % T;
-                if (t < 0) t += T;
-                int ti = (t - pr) % T;
-                if (ti < 0) ti += T;
-                float acc = 0.f;
-                for (int q = 0; q <= 2 * pr; ++q) {
-                    acc = fmaf(__ldg(d.pre_taps + q), (__ldg(labels + ti) == k) ? 1.f : 0.f, acc);
-                    if (++ti == T) ti = 0;
-                }
-                OH[rr * STACK_KMAX + k] = acc;
-            }
-            __syncthreads();
-        }
-        const float* __restrict__ srcf = reinterpret_cast<const float*>(d.src);
-        for (int i = threadIdx.x; i < SP_TT * K; i += blockDim.x) {
-            const int tt = i / K, k = i - tt * K;
-            const int t = t0 + tt;
-            float acc = 0.f;
-            if (t < T) {
-                if (d.src_mode == 2) {
-                    if (radius == 0) {
-                        acc = __fmul_rn(d.src_scale, OH[tt * STACK_KMAX + k]);
-                    } else {
-                        for (int q = 0; q <= 2 * radius; ++q)
-                            acc = fmaf(__ldg(taps + q), __fmul_rn(d.src_scale, OH[(tt + q) * STACK_KMAX + k]), acc);
-                    }
-                } else if (radius == 0) {
-                    acc = subpatch_raw(srcf, d.src_ld, d.src_scale, d.src_mode, t, k);
-                } else {
-                    int ti = (t - radius) % T;
-                    if (ti < 0) ti += T;
-                    for (int q = 0; q <= 2 * radius; ++q) {
-                        acc = fmaf(__ldg(taps + q), subpatch_raw(srcf, d.src_ld, d.src_scale, d.src_mode, ti, k), acc);
-                        if (++ti == T) ti = 0;
-                    }
-                }
-            }
-            S[tt * STACK_KMAX + k] = acc;
-        }
-        if (threadIdx.x < SP_TT) {
-            const int t = t0 + threadIdx.x;
-            float al = d.alpha, be = d.beta;
-            if (d.mod && t < T) {
-                be = __fmul_rn(d.mod_scale, __ldg(d.mod + (long long)t * d.mod_ld));
-                al = __fsub_rn(1.f, be);
-            }
-            ab[2 * threadIdx.x] = al;
-            ab[2 * threadIdx.x + 1] = be;
-        }
-        __syncthreads();
-        const int g0 = d.g_begin, Gr = d.g_end - d.g_begin;
-        const bool overwrite = (d.mod == nullptr) && d.alpha == 0.f;
-        const int span = Gr * P;  // contiguous inside a row: groups g0 .. g1 - 1
-        for (int tt = 0; tt < rows; ++tt) {
-            const float al = ab[2 * tt], be = ab[2 * tt + 1];
-            float* wrow = W + tt * GP + g0 * P;
-            const float* srow = S + tt * STACK_KMAX;
-            for (int i = threadIdx.x; i < span; i += blockDim.x) {
-                int p = i;
-                while (p >= P) p -= P;  // Gr <= 3
-                const int k = inv[p];
-                const float sv = k >= 0 ? srow[k] : 0.f;
-                wrow[i] = overwrite ? be * sv : fmaf(al, wrow[i], be * sv);
-            }
-        }
+        item_off[n] = o;
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < rows * GP; i += blockDim.x) Wt[(long long)t0 * GP + i] = W[i];
+    for (int i = threadIdx.x; i < n * STACK_KMAX; i += blockDim.x) {
+        const int j = i / STACK_KMAX, k = i - j * STACK_KMAX;
+        if (k < sa.d[j].n_select) {
+            const long long p = sa.d[j].selection[k];
+            if (p >= 0 && p < P) inv[j * P + (int)p] = (signed char)k;
+        }
+    }
+    // smoothed one-hot rows of the label sub-patches for t0 - radius .. t0 + SP_TT + radius (onehot_gauss_kernel's order)
+    for (int j = 0; j < n; ++j) {
+        const ssar_subpatch_desc& d = sa.d[j];
+        if (d.src_mode != 2) continue;
+        const long long* __restrict__ labels = reinterpret_cast<const long long*>(d.src);
+        const int K = d.n_select, nr = SP_TT + 2 * d.radius, pr = d.pre_radius;
+        float* oh = OH + label_slot[j] * (SP_TT + 16) * STACK_KMAX;
+        for (int i = threadIdx.x; i < nr * K; i += blockDim.x) {
+            const int rr = i / K, k = i - rr * K;
+            int t = (t0 - d.radius + rr) % T;
+            if (t < 0) t += T;
+            int ti = (t - pr) % T;
+            if (ti < 0) ti += T;
+            float acc = 0.f;
+            for (int q = 0; q <= 2 * pr; ++q) {
+                acc = fmaf(__ldg(d.pre_taps + q), (__ldg(labels + ti) == k) ? 1.f : 0.f, acc);
+                if (++ti == T) ti = 0;
+            }
+            oh[rr * STACK_KMAX + k] = acc;
+        }
+    }
+    if (n_label > 0) __syncthreads();
+    // phase A: time-smoothed sources S_j[tt][k] of every sub-patch; the (j, tt, k < K_j) items are packed so that all
+    // 256 threads hold loads of different sub-patches at once, and an item's taps are fetched before its fmaf chain
+    const int n_items = item_off[n];
+    for (int i = threadIdx.x; i < n_items; i += blockDim.x) {
+        int j = 0;
+        while (i >= item_off[j + 1]) ++j;
+        const ssar_subpatch_desc& d = sa.d[j];
+        const int K = d.n_select, radius = d.radius;
+        const int li = i - item_off[j];
+        const int tt = li / K, k = li - tt * K;
+        const int t = t0 + tt;
+        float acc = 0.f;
+        if (t < T) {
+            const float* __restrict__ srcf = reinterpret_cast<const float*>(d.src);
+            if (d.src_mode == 2) {
+                const float* oh = OH + label_slot[j] * (SP_TT + 16) * STACK_KMAX;
+                if (radius == 0) {
+                    acc = __fmul_rn(d.src_scale, oh[tt * STACK_KMAX + k]);
+                } else {
+                    for (int q = 0; q <= 2 * radius; ++q)
+                        acc = fmaf(__ldg(taps + q), __fmul_rn(d.src_scale, oh[(tt + q) * STACK_KMAX + k]), acc);
+                }
+            } else if (radius == 0) {
+                acc = subpatch_raw(srcf, d.src_ld, d.src_scale, d.src_mode, t, k);
+            } else {
+                int ti = (t - radius) % T;
+                if (ti < 0) ti += T;
+                float v[17];
+#pragma unroll
+                for (int q = 0; q < 17; ++q) {
+                    v[q] = q <= 2 * radius ? subpatch_raw(srcf, d.src_ld, d.src_scale, d.src_mode, ti, k) : 0.f;
+                    if (++ti == T) ti = 0;
+                }
+#pragma unroll
+                for (int q = 0; q < 17; ++q)
+                    if (q <= 2 * radius) acc = fmaf(__ldg(taps + q), v[q], acc);
+            }
+        }
+        S[(j * SP_TT + tt) * STACK_KMAX + k] = acc;
+    }
+    for (int i = threadIdx.x; i < n * SP_TT; i += blockDim.x) {
+        const int j = i / SP_TT, t = t0 + (i - j * SP_TT);
+        const ssar_subpatch_desc& d = sa.d[j];
+        float al = d.alpha, be = d.beta;
+        if (d.mod && t < T) {
+            be = __fmul_rn(d.mod_scale, __ldg(d.mod + (long long)t * d.mod_ld));
+            al = __fsub_rn(1.f, be);
+        }
+        ab[2 * i] = al;
+        ab[2 * i + 1] = be;
+    }
+    __syncthreads();
+    // phase B: a thread owns weight columns (g, p) for the CTA's SP_TT frames and walks them through the stack in
+    // registers; per (sub-patch, column) one inv lookup, per frame one S and one (alpha, beta) read
+    const float2* ab2 = reinterpret_cast<const float2*>(ab);
+    for (int r = threadIdx.x; r < GP; r += blockDim.x) {
+        const int g = r / P, p = r - g * P;
+        float* wp = Wt + (long long)t0 * GP + r;
+        float w[SP_TT];
+#pragma unroll
+        for (int tt = 0; tt < SP_TT; ++tt) w[tt] = (load_initial && tt < rows) ? wp[(long long)tt * GP] : 0.f;
+        for (int j = 0; j < n; ++j) {
+            const ssar_subpatch_desc& d = sa.d[j];
+            if (g < d.g_begin || g >= d.g_end) continue;
+            const int k = inv[j * P + p];
+            const bool overwrite = (d.mod == nullptr) && d.alpha == 0.f;
+            const float* Sj = S + j * SP_TT * STACK_KMAX + max(k, 0);
+#pragma unroll
+            for (int tt = 0; tt < SP_TT; ++tt) {
+                const float sv = k >= 0 ? Sj[tt * STACK_KMAX] : 0.f;
+                const float2 q = ab2[j * SP_TT + tt];
+                w[tt] = overwrite ? q.y * sv : fmaf(q.x, w[tt], q.y * sv);
+            }
+        }
+#pragma unroll
+        for (int tt = 0; tt < SP_TT; ++tt)
+            if (tt < rows) wp[(long long)tt * GP] = w[tt];
+    }
 }
 
 // out[t, k] = sum_i taps[i] * (labels[(t + i - radius) mod T] == k): the one-hot gather of latent.py:39-40 followed by
@@ -408,13 +447,15 @@ extern "C" int ssar_latent_stack(float* weights, int n_rows, int n_groups, int n
         SSAR_REQUIRE(d.src_mode != 2 || (d.pre_taps && d.pre_radius >= 0), "latent_stack: labels need pre_taps");
         sa.d[j] = d;
     }
-    const size_t smem = ((size_t)SP_TT * n_groups * n_basis + SP_TT * STACK_KMAX + (SP_TT + 16) * STACK_KMAX + SP_TT * 2 +
-                         n_basis) * sizeof(float);
-    SSAR_REQUIRE(smem <= 200 * 1024, "latent_stack: palette too large for one CTA's shared memory");
+    int n_label = 0;
+    for (int j = 0; j < n_descs; ++j) n_label += descs[j].src_mode == 2 ? 1 : 0;
+    const size_t smem = ((size_t)n_descs * SP_TT * STACK_KMAX + (size_t)n_descs * SP_TT * 2 +
+                         (size_t)n_label * (SP_TT + 16) * STACK_KMAX) * sizeof(float) + (size_t)n_descs * n_basis;
+    SSAR_REQUIRE(smem <= 200 * 1024 && n_basis <= 32767, "latent_stack: too many basis latents for one CTA's shared memory");
     if (smem > 48 * 1024)
         cudaFuncSetAttribute(latent_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     latent_stack_kernel<<<ssar_div_up(n_rows, SP_TT), 256, smem, (cudaStream_t)stream>>>(weights, n_rows, n_groups, n_basis,
-                                                                                       sa, taps, load_initial);
+                                                                                       sa, taps, load_initial, n_label);
     return ssar_launch_status("latent_stack");
 }
 
