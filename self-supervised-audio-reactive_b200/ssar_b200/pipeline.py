@@ -253,6 +253,22 @@ def _side_stream(device, purpose="sampler"):
     return st
 
 
+_STAGING = {}
+
+
+def _staging(device, shape, dtype):
+    """Two device buffers of `shape` for the H2D ping-pong of host-resident audio, kept per (device, thread, shape);
+    `free[i]` is the event after which buffer i may be overwritten."""
+    key = (torch.device(device).index, __import__("threading").get_ident(), tuple(shape), dtype)
+    st = _STAGING.get(key)
+    if st is None:
+        if len(_STAGING) >= 4:
+            _STAGING.clear()
+        st = _STAGING[key] = {"buf": [torch.empty(shape, dtype=dtype, device=device) for _ in range(2)],
+                              "free": [None, None]}
+    return st
+
+
 def _pool(workers: int):
     from concurrent.futures import ThreadPoolExecutor
 
@@ -368,20 +384,27 @@ def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, se
                 staged = None
                 if not audio.is_cuda:
                     copy_stream = _side_stream(dev, "h2d")
+                    # two persistent device buffers (ping-pong): a fresh allocation per chunk on the copy stream makes
+                    # the caching allocator cudaMalloc (a device-wide sync) whenever its blocks are still held by the
+                    # feature stream, which stalled the copy / compute overlap
+                    ring = _staging(dev, (max(c1 - c0 for c0, c1 in bounds),) + tuple(audio.shape[1:]), audio.dtype)
 
-                    def stage(c0, c1):
+                    def stage(ci, c0, c1):
+                        slot = ci % 2
                         with torch.cuda.stream(copy_stream):
-                            xd = audio[c0:c1].to(dev, non_blocking=True)
+                            if ring["free"][slot] is not None:
+                                copy_stream.wait_event(ring["free"][slot])  # its previous chunk has been consumed
+                            xd = ring["buf"][slot][: c1 - c0]
+                            xd.copy_(audio[c0:c1], non_blocking=True)
                             ev = torch.cuda.Event()
                             ev.record(copy_stream)
-                        xd.record_stream(fstream)
                         return xd, ev
 
-                    staged = stage(*bounds[0])
+                    staged = stage(0, *bounds[0])
                 for ci, (c0, c1) in enumerate(bounds):
                     if staged is not None:
                         xd, ev = staged
-                        staged = stage(*bounds[ci + 1]) if ci + 1 < len(bounds) else None  # one chunk ahead
+                        staged = stage(ci + 1, *bounds[ci + 1]) if ci + 1 < len(bounds) else None  # one chunk ahead
                         fstream.wait_event(ev)
                     else:
                         xd = audio[c0:c1]
@@ -392,6 +415,8 @@ def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, se
                         pf = patch_features_batch(f)
                     done = torch.cuda.Event()
                     done.record(fstream)
+                    if not audio.is_cuda:
+                        ring["free"][ci % 2] = done
                     for t in (f, *pf.values()):
                         t.record_stream(stream)  # allocated on the feature stream, consumed on the caller's
                     ready_feats.put((c0, c1, f, pf, done))

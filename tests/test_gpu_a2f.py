@@ -116,3 +116,9 @@ def test_features_and_latents_graph_vs_serial():
     fc, lc, _ = pipeline.features_and_latents(xs.cpu().pin_memory(), 44100, 24, palette, segs, chunk=2)
     torch.cuda.synchronize()
     assert torch.equal(fa, fc) and torch.equal(la, lc)
+    # again, with other audio: the two staging buffers are reused across chunks and across calls
+    ys = torch.stack([synth_clip(44100 * 45, 44100, i) for i in (5, 1, 8)])
+    fd, ld, _ = pipeline.features_and_latents(ys.pin_memory(), 44100, 24, palette, segs, chunk=2)
+    fe, le, _ = pipeline.features_and_latents(ys.cuda(), 44100, 24, palette, segs, chunk=2, serial=True)
+    torch.cuda.synchronize()
+    assert torch.equal(fd, fe) and torch.equal(ld, le)
