@@ -39,9 +39,13 @@ __global__ void gauss1d_kernel(const float* __restrict__ x, int T, long long inn
     const int clip = blockIdx.z;
     const float* xc = x + (long long)clip * T * inner;
     float* oc = out + (long long)clip * T * inner;
-    const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= inner) return;
-    const int t0 = blockIdx.y * G_TPT;
+    // (time block, column) pairs are packed into the CTA, columns fastest: narrow matrices ([T, 4] envelopes) still
+    // fill their warps
+    const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long tb = gid / inner;
+    const long long j = gid - tb * inner;
+    if (tb * G_TPT >= T) return;
+    const int t0 = (int)tb * G_TPT;
     float acc[G_TPT];
 #pragma unroll
     for (int o = 0; o < G_TPT; ++o) acc[o] = 0.f;
@@ -289,9 +293,10 @@ extern "C" int ssar_gauss1d(const float* x, int n_clips, int n_frames, long long
     SSAR_REQUIRE(mode != 1 || radius < n_frames, "gauss1d: reflect padding needs radius < n_frames");
     SSAR_REQUIRE((2 * radius + 1) * sizeof(float) <= 200 * 1024, "gauss1d: kernel too long");
     SSAR_REQUIRE(n_clips <= 65535, "gauss1d: too many clips per launch");
-    const int threads = inner >= 128 ? 128 : (inner >= 64 ? 64 : 32);
-    dim3 grid((unsigned)((inner + threads - 1) / threads), (unsigned)((n_frames + G_TPT - 1) / G_TPT), n_clips);
-    SSAR_REQUIRE(grid.y <= 65535, "gauss1d: too many frames per launch");
+    const int threads = 128;
+    const long long items = inner * ((n_frames + G_TPT - 1) / G_TPT);
+    SSAR_REQUIRE((items + threads - 1) / threads <= 0x7fffffffLL, "gauss1d: too many elements per launch");
+    dim3 grid((unsigned)((items + threads - 1) / threads), 1, n_clips);
     const size_t smem = (2 * radius + 1) * sizeof(float);
     if (smem > 48 * 1024) cudaFuncSetAttribute(gauss1d_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     gauss1d_kernel<<<grid, threads, smem, ST(stream)>>>(x, n_frames, inner, weights, radius, mode, out);
