@@ -1,5 +1,5 @@
-"""GPU box: ONE warm-up + ONE full step (B clips) with a single launching thread — the command ncu wraps for the
-launch list of the full path (every launch serialised, so per-kernel SHARES are comparable with bench.py's)."""
+"""GPU box: warm-up step(s) + ONE profiled full step (B clips) with a single launching thread — the command
+`ncu --profile-from-start off` wraps for the launch list of the full path (every launch serialised, so per-kernel SHARES are comparable with bench.py's)."""
 import sys
 from pathlib import Path
 ROOT = Path(__file__).resolve().parent.parent
@@ -14,9 +14,15 @@ x = synth_batch_device(B, 44100 * 240, 44100, "cuda")
 _, segs, palette = synth_patch_inputs(5760, 0)
 palette = palette.cuda()
 stats = torch.zeros(3, 59, dtype=torch.float64, device="cuda")
-for _ in range(n_steps):
+for i in range(n_steps):
+    if i == n_steps - 1:
+        # ncu --profile-from-start off: only the LAST step is listed (the first one also runs the one-time checks of
+        # the batched Philox draws against torch's per-call draws: ~600 torch launches that never recur)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
     feats, latents, _ = pipeline.features_and_latents(x, 44100, 24, palette, segs, rng_device="cuda", serial=True)
     stats.zero_()
     ops.feature_stats(feats, stats)
     torch.cuda.synchronize()
+torch.cuda.profiler.stop()
 print("ok", feats.shape, latents.shape, float(stats[1].sum()))
