@@ -66,10 +66,45 @@ class ClockSampler:
         do not run N pollers against the driver during the timed region)."""
         self.index, self.rows, self.proc, self.enabled = ",".join(str(i) for i in indices), [], None, enabled
 
+    def _nvml_loop(self, handles):
+        import pynvml as nv
+        bits = {"hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8),
+                "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+                "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+                "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4)}
+        mx = [nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM) for h in handles]
+        while not self.stop.is_set():
+            for h, m in zip(handles, mx):
+                try:
+                    sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                    try:
+                        rs = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                    except Exception:
+                        rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                    self.rows.append([str(sm), str(m)] + ["Active" if rs & bits[n] else "Not Active" for n in
+                                                         ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")])
+                except Exception:
+                    pass
+            self.stop.wait(0.1)
+
     def __enter__(self):
         if not self.enabled:
             return self
+        # NVML in this process (the library nvidia-smi itself reads): two calls per GPU every 100 ms.  A looping
+        # nvidia-smi process polling 8 GPUs cost 2.4 ms of a 48 ms step at N = 8 (driver locks); it stays as the fallback.
         try:
+            import pynvml as nv
+            nv.nvmlInit()
+            handles = [nv.nvmlDeviceGetHandleByIndex(int(i)) for i in self.index.split(",")]
+            self.stop = threading.Event()
+            self.source = "nvml"
+            self.thread = threading.Thread(target=self._nvml_loop, args=(handles,), daemon=True)
+            self.thread.start()
+            return self
+        except Exception:
+            self.stop = None
+        try:
+            self.source = "nvidia-smi"
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -84,6 +119,10 @@ class ClockSampler:
             self.rows.append([c.strip() for c in line.split(",")])
 
     def __exit__(self, *a):
+        if getattr(self, "stop", None) is not None:
+            time.sleep(0.12)
+            self.stop.set()
+            self.thread.join(timeout=2)
         if self.proc:
             time.sleep(0.15)
             self.proc.terminate()
@@ -106,7 +145,7 @@ class ClockSampler:
                 pass
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "source": getattr(self, "source", None)}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -261,7 +300,7 @@ def main():
     barrier()
     launches0 = cabi.launch_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(range(world) if world > 1 else [local_rank], enabled=(rank == 0)) as clocks:
+    with ClockSampler(range(world) if world > 1 else [local_rank], enabled=(rank == 0 and not os.environ.get("SSAR_BENCH_NO_CLOCKS"))) as clocks:
         barrier()
         ev0.record()
         for _ in range(args.steps):
