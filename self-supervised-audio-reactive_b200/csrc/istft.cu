@@ -246,12 +246,11 @@ int launch_irfft(const float* spec, long long ld, const float* win, const float*
 // transforms frames b0-1 .. b0+RUN-1 one after the other, parks each frame's second half in shared memory and emits a
 // block per frame (one extra transform per run: 1/RUN overhead).
 // ---------------------------------------------------------------------------------------------------------------
-constexpr int OLA_RUN = 24;
 
 __global__ void __launch_bounds__(256, 2) istft_half_overlap_kernel(const float2* __restrict__ X, long long ldx,
                                                                     const float* __restrict__ win,
                                                                     const float2* __restrict__ tw, int n_clips, int n_frames,
-                                                                    long long length, float* __restrict__ out) {
+                                                                    long long length, float* __restrict__ out, int OLA_RUN) {
     constexpr int M = 1024;
     using L = WarpFft<M>;
     constexpr int ZF = L::ZF;
@@ -359,12 +358,26 @@ extern "C" int ssar_istft_half_overlap(const float* spec, long long ld, int n_cl
         return SSAR_ERR_CUDA;
     }
     const long long n_blocks = (length + 1023) / 1024;
+    // run length: a run of R blocks costs R + 1 transforms and the launch takes ceil(runs / resident warps) rounds, so
+    // pick the R in [8, 32] with the cheapest rounds * (R + 1) (8 clips x 5760 blocks: R = 20 fills 288 of the 296 CTA
+    // slots in one round; the fixed R = 24 of v1 left 19 % of them empty)
+    const long long slots = (long long)SSAR_NUM_SMS * 2 * L::WPB;
+    int OLA_RUN = 24;
+    long long best = -1;
+    for (int R = 8; R <= 32; ++R) {
+        const long long r_ = ((n_blocks + R - 1) / R) * n_clips;
+        const long long cost = ((r_ + slots - 1) / slots) * (R + 1);
+        if (best < 0 || cost <= best) {
+            best = cost;
+            OLA_RUN = R;
+        }
+    }
     const long long runs = ((n_blocks + OLA_RUN - 1) / OLA_RUN) * n_clips;
     long long grid = (runs + L::WPB - 1) / L::WPB;
     if (grid > (long long)SSAR_NUM_SMS * 2) grid = (long long)SSAR_NUM_SMS * 2;
     istft_half_overlap_kernel<<<(unsigned)grid, 256, smem, (cudaStream_t)stream>>>(
         reinterpret_cast<const float2*>(spec), ld, window, reinterpret_cast<const float2*>(twiddle), n_clips, n_frames, length,
-        out);
+        out, OLA_RUN);
     return ssar_launch_status("istft_half_overlap");
 }
 
