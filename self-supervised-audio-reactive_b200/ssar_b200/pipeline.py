@@ -341,6 +341,14 @@ def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, se
     B = audio.shape[0]
     chunk = max(1, min(int(chunk), B))
     bounds = [(c0, min(c0 + chunk, B)) for c0 in range(0, B, chunk)]
+    if not serial and chunk >= 4 and chunk % 2 == 0 and B % chunk == 0 and B >= 3 * chunk:
+        # tapered schedule (half chunks first and last, two graph shapes): patch rendering starts after half a chunk of
+        # features instead of a whole one, and only half a chunk of patches is left to render — host-paced, ~0.75 ms per
+        # clip — after the last feature kernels have finished
+        h = chunk // 2
+        cuts = [0, h] + list(range(h + chunk, B - h, chunk)) + [B - h, B]
+        cuts = sorted(set(cuts))
+        bounds = list(zip(cuts[:-1], cuts[1:]))
     checks = []
     fgraphs = None
     if USE_FEATURE_GRAPHS and not serial:

@@ -122,3 +122,19 @@ def test_features_and_latents_graph_vs_serial():
     fe, le, _ = pipeline.features_and_latents(ys.cuda(), 44100, 24, palette, segs, chunk=2, serial=True)
     torch.cuda.synchronize()
     assert torch.equal(fd, fe) and torch.equal(ld, le)
+
+
+def test_features_and_latents_tapered_chunks():
+    """B >= 3 chunks: the threaded pipeline runs half chunks first and last (two feature-graph shapes); same results as the
+    serially queued pipeline on whole chunks, from device and from pinned host audio."""
+    from ssar_b200 import pipeline
+    from ssar_b200.synth import synth_patch_inputs
+
+    xs = torch.stack([synth_clip(44100 * 45, 44100, i) for i in range(12)])
+    _, segs, palette = synth_patch_inputs(1080, 0)
+    palette = palette.cuda()
+    fs, ls, _ = pipeline.features_and_latents(xs.cuda(), 44100, 24, palette, segs, chunk=4, serial=True)
+    for audio in (xs.cuda(), xs.cuda(), xs.pin_memory()):  # eager shapes, then graph replays, then staged host input
+        f, l, _ = pipeline.features_and_latents(audio, 44100, 24, palette, segs, chunk=4)
+        torch.cuda.synchronize()
+        assert torch.equal(f, fs) and torch.equal(l, ls)
