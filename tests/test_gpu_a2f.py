@@ -125,8 +125,8 @@ def test_features_and_latents_graph_vs_serial():
 
 
 def test_features_and_latents_tapered_chunks():
-    """B >= 3 chunks: the threaded pipeline runs half chunks first and last (two feature-graph shapes); same results as the
-    serially queued pipeline on whole chunks, from device and from pinned host audio."""
+    """B >= 3 chunks of pinned host audio: the threaded pipeline runs half chunks first and last (two feature-graph
+    shapes); same results as the serially queued pipeline on whole chunks."""
     from ssar_b200 import pipeline
     from ssar_b200.synth import synth_patch_inputs
 
@@ -134,7 +134,7 @@ def test_features_and_latents_tapered_chunks():
     _, segs, palette = synth_patch_inputs(1080, 0)
     palette = palette.cuda()
     fs, ls, _ = pipeline.features_and_latents(xs.cuda(), 44100, 24, palette, segs, chunk=4, serial=True)
-    for audio in (xs.cuda(), xs.cuda(), xs.pin_memory()):  # eager shapes, then graph replays, then staged host input
+    for audio in (xs.cuda(), xs.pin_memory(), xs.pin_memory(), xs.pin_memory()):  # whole chunks; tapered: eager, capture, replay
         f, l, _ = pipeline.features_and_latents(audio, 44100, 24, palette, segs, chunk=4)
         torch.cuda.synchronize()
         assert torch.equal(f, fs) and torch.equal(l, ls)
