@@ -208,18 +208,19 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
                             bmax = fmaxf(bmax, acc);
                         }
                     }
-                } else
-                for (int b = lane; b < fb.n_bands; b += 32) {
-                    const int st = __ldg(fb.start + b), cn = __ldg(fb.count + b);
-                    const float* __restrict__ w = fb.weights + __ldg(fb.offset + b);
-                    float acc = 0.f;
-                    if (fb.on_power) {
-                        for (int k = 0; k < cn; ++k) acc = fmaf(__ldg(w + k), pw[st + k], acc);
-                    } else {
-                        for (int k = 0; k < cn; ++k) acc = fmaf(__ldg(w + k), sqrtf(pw[st + k]), acc);
+                } else {  // packed weights: one lane per band, a trip per bin
+                    for (int b = lane; b < fb.n_bands; b += 32) {
+                        const int st = __ldg(fb.start + b), cn = __ldg(fb.count + b);
+                        const float* __restrict__ w = fb.weights + __ldg(fb.offset + b);
+                        float acc = 0.f;
+                        if (fb.on_power) {
+                            for (int k = 0; k < cn; ++k) acc = fmaf(__ldg(w + k), pw[st + k], acc);
+                        } else {
+                            for (int k = 0; k < cn; ++k) acc = fmaf(__ldg(w + k), sqrtf(pw[st + k]), acc);
+                        }
+                        fb.out[orow * fb.ld + b] = acc;
+                        bmax = fmaxf(bmax, acc);
                     }
-                    fb.out[orow * fb.ld + b] = acc;
-                    bmax = fmaxf(bmax, acc);
                 }
                 if (fb.max_key) {
                     bmax = warp_max(bmax);
