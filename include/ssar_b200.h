@@ -106,9 +106,26 @@ typedef struct {
                                features/audio.py:126-133 */
     ssar_filterbank fb[2];
     ssar_projection proj;
+    int aux_frames;         /* 0 = n_frames.  Otherwise every output EXCEPT out_complex (spec, rms, flatness, filterbanks and
+                               their max keys, projection) covers only frames [0, aux_frames) of each clip and is laid out
+                               [n_clips, aux_frames, ...]: one launch then serves stft (1 + N/hop frames, complex) and the
+                               spectrogram-style features that drop the last frame (rosa/spectral.py:60) of the same signal */
 } ssar_frames_args;
 
 int ssar_frames_fft(const ssar_frames_args* args, void* stream);
+
+/* The same transform for ARBITRARY n_fft in [2, 4096] (direct DFT, no radix restriction), restricted to the bins
+ * [k_lo, k_hi) of the one-sided spectrum: torch.stft(center=True, pad_mode="reflect") behind rosa/spectral.py:10-21 as
+ * rosa/beat.py:46-49 reaches it for a clip shorter than win_length frames (n_fft = min(len(onset_envelope), 1024), hop 1;
+ * only the 60-180 BPM bins survive rosa/beat.py:54-57).  n_frames <= 1 + (n_samples + 2*(n_fft/2) - n_fft) / hop.
+ * out_complex: [n_clips, n_frames, k_hi - k_lo] (re, im). */
+int ssar_frames_dft(const float* x, long long n_samples, long long clip_stride, int n_clips, int n_fft, int hop,
+                    int n_frames, const float* window, int k_lo, int k_hi, float* out_complex, void* stream);
+
+/* torch.istft(center=True, length) (rosa/spectral.py:24-32, as rosa/beat.py:69 calls it) for arbitrary n_fft from a
+ * spectrum whose only non-zero bins are [k_lo, k_hi): spec complex [n_clips, n_frames, k_hi - k_lo]; out [n_clips, length]. */
+int ssar_istft_band(const float* spec, int n_clips, int n_frames, int n_fft, int hop, const float* window, int k_lo,
+                    int k_hi, long long length, float* out, void* stream);
 
 /* fills n 32-bit words with `value` (used to reset max/min key accumulators) */
 int ssar_fill_u32(uint32_t* dst, long long n, uint32_t value, void* stream);
@@ -288,6 +305,22 @@ int ssar_hwr_rowsum(const float* x, long long n_rows, int inner, float* out, voi
 /* ssar/supervised/data.py:317-319 dataset statistics: accumulates (count, sum, sum of squares) per column in fp64
  * into stats[3, n_cols] (caller zeroes it; all-reduce it over ranks, then mean = s/n, std = sqrt(ss/n - mean^2)) */
 int ssar_feature_stats(const float* x, long long n_rows, int n_cols, double* stats, void* stream);
+
+/* ssar/random/mir.py:14-22 (salience_weighted) after the three Gaussians (ssar_gauss1d: sigma 2 circular -> env, then
+ * sigma 5 and sigma 80 in reflect mode of env): out = (smooth_short / smooth_long)^2 * env for a batch of feature matrices
+ * [n_clips, n_frames, n_cols] whose columns are grouped into features (col_group[n_cols] in [0, n_groups)), plus the
+ * running min / max of every (clip, group) as order-preserving keys [n_clips, n_groups] (ssar_fill_u32 them with
+ * 0xFF800000 / 0x007FFFFF first). */
+int ssar_salience_weight(const float* env, const float* smooth_short, const float* smooth_long, int n_clips, int n_frames,
+                         int n_cols, const int* col_group, int n_groups, float* out, uint32_t* min_key, uint32_t* max_key,
+                         void* stream);
+
+/* ssar/random/mir.py:44's closing normalize (features/processing.py:52-55) per (clip, feature): (w - min) / ((max - min) +
+ * eps) with the keys of ssar_salience_weight.  group_start[n_groups]: first column of each group (groups are contiguous
+ * column ranges).  out is FEATURE-BLOCKED: clip b, group g = contiguous [n_frames, C_g] at
+ * out + b * n_frames * n_cols + n_frames * group_start[g]. */
+int ssar_group_normalize(const float* w, int n_clips, int n_frames, int n_cols, const int* col_group, const int* group_start,
+                         int n_groups, const uint32_t* min_key, const uint32_t* max_key, float eps, float* out, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Trajectory construction: latent sequences [T, num_ws, 512] and per-layer noise maps

@@ -49,3 +49,36 @@ def audio2features(audio, sr, fps, clamp=True, smooth=True, emphasis=False):
     if emphasis:
         feats = post.emphasize(feats, 2, 75)
     return feats
+
+
+# ------------------------------------------------------------------------------------------------
+# ssar/random/mir.py: the `Patch` inputs (feature part of retrieve_music_information)
+# ------------------------------------------------------------------------------------------------
+def salience_weighted(envelope, short_sigma=5, long_sigma=80):
+    """random/mir.py:14-22."""
+    if envelope.dim() > 1:
+        envelope = envelope.squeeze(1)
+    short = post.gaussian_filter(envelope, short_sigma, mode="reflect")
+    long = post.gaussian_filter(envelope, long_sigma, mode="reflect")
+    weighted = (short / long) ** 2 * envelope
+    if weighted.dim() < 2:
+        weighted = weighted.unsqueeze(1)
+    return weighted
+
+
+AFEATFNS = {  # random/mir.py:8, in its order; every function is called on the audio itself (nothing shared)
+    "chromagram": lambda a, sr: ocqt.chromagram(a, sr),
+    "tonnetz": lambda a, sr: ocqt.tonnetz(a, sr),
+    "mfcc": lambda a, sr: dsp.mfcc(a, sr),
+    "spectral_contrast": lambda a, sr: dsp.spectral_contrast(a, sr),
+    "spectral_flatness": lambda a, sr: dsp.spectral_flatness(a, sr).reshape(-1, 1),
+    "rms": lambda a, sr: dsp.rms(a, sr).reshape(-1, 1),
+    "drop_strength": lambda a, sr: drop_strength(a, sr),
+    "onsets": lambda a, sr: onsets(a, sr),
+}
+
+
+def retrieve_music_features(audio, sr):
+    """random/mir.py:26 and :44 (tempo, beats and segmentations, :28-42, are inputs of `Patch` here)."""
+    raw = {name: fn(audio, sr) for name, fn in AFEATFNS.items()}
+    return {k: post.normalize(salience_weighted(post.gaussian_filter(af, 2))) for k, af in raw.items()}

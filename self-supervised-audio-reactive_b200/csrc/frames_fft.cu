@@ -37,6 +37,7 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int h = lane / N1, n1 = lane % N1;  // frame slot inside the warp, point index inside the frame
+    const int aux_frames = a.aux_frames > 0 ? a.aux_frames : a.n_frames;
     const float2* __restrict__ tw = reinterpret_cast<const float2*>(a.twiddle);  // exp(-2 pi i k / 2M), k in [0, 2M)
 
     warp_fft_fill_twiddles<M>(twT, tw);
@@ -108,7 +109,7 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
         if (a.out_rms) {
 #pragma unroll
             for (int o = N1 / 2; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-            if (active && n1 == 0) a.out_rms[(long long)clip * a.n_frames + t] = sqrtf(ss / (float)N);
+            if (active && n1 == 0 && t < aux_frames) a.out_rms[(long long)clip * aux_frames + t] = sqrtf(ss / (float)N);
         }
 
         // ------------------------------------------------------------------ per frame: untangle + epilogues, 32 lanes wide
@@ -118,7 +119,9 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
             if (ff >= total_frames) break;  // warp-uniform
             const int fclip = (int)(ff / a.n_frames);
             const int ft = (int)(ff - (long long)fclip * a.n_frames);
-            const long long orow = (long long)fclip * a.n_frames + ft;
+            const long long crow = (long long)fclip * a.n_frames + ft;  // row of the complex output
+            const long long orow = (long long)fclip * aux_frames + ft;  // row of every other output
+            const bool aux = ft < aux_frames;                            // warp-uniform
             float2* z = zw + fs * ZF;
 
             // untangle the packed real transform in place: X[k] = E + w^k O, X[M-k] = conj(E - w^k O)
@@ -137,9 +140,9 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
 
             // epilogue 1: complex / power / magnitude outputs, flatness sums; the power tile goes to shared memory
             float* pw = separate_power ? pall + (size_t)(warp * FPW + fs) * (M + 4 + LANE_PAD) : reinterpret_cast<float*>(z);
-            if (a.out_complex || need_pw) {
-                float2* oc = a.out_complex ? reinterpret_cast<float2*>(a.out_complex) + orow * a.ldc : nullptr;
-                float* os = a.out_spec ? a.out_spec + orow * a.lds : nullptr;
+            if (a.out_complex || (need_pw && aux)) {
+                float2* oc = a.out_complex ? reinterpret_cast<float2*>(a.out_complex) + crow * a.ldc : nullptr;
+                float* os = (a.out_spec && aux) ? a.out_spec + orow * a.lds : nullptr;
                 float pj[NJ];
                 float slog = 0.f, slin = 0.f;
 #pragma unroll
@@ -159,12 +162,12 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
                         }
                     }
                 }
-                if (a.out_flatness) {
+                if (a.out_flatness && aux) {
                     slog = warp_sum(slog);
                     slin = warp_sum(slin);
                     if (lane == 0) a.out_flatness[orow] = expf(slog / (float)NBINS) / (slin / (float)NBINS);
                 }
-                if (a.fb[0].n_bands > 0 || a.fb[1].n_bands > 0) {
+                if (aux && (a.fb[0].n_bands > 0 || a.fb[1].n_bands > 0)) {
                     if (!separate_power) __syncwarp();  // every lane has read its bins: the tile may be overwritten
 #pragma unroll
                     for (int j = 0; j < NJ; ++j) {
@@ -181,7 +184,7 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
 #pragma unroll
             for (int q = 0; q < 2; ++q) {
                 const ssar_filterbank& fb = a.fb[q];
-                if (fb.n_bands <= 0) continue;
+                if (fb.n_bands <= 0 || !aux) continue;
                 float bmax = -INFINITY;
                 if (fb.lane_weights && fb.on_power) {
                     // lane-interleaved weights: one coalesced 512-byte row of weights and one 128-bit tile read per
@@ -229,7 +232,7 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
             }
 
             // epilogue 3: banded complex projection of the complex spectrum (CQT basis); needs z intact
-            if (a.proj.n_rows > 0) {
+            if (a.proj.n_rows > 0 && aux) {
                 const ssar_projection& pjn = a.proj;
                 const int slot = pjn.clip_slot ? __ldg(pjn.clip_slot + fclip) : 0;
                 const int rb = slot * pjn.n_rows;
@@ -289,6 +292,7 @@ extern "C" int ssar_frames_fft(const ssar_frames_args* args, void* stream) {
     SSAR_REQUIRE(a.n_clips >= 0 && a.n_frames >= 0 && a.hop > 0, "frames_fft: bad sizes");
     SSAR_REQUIRE(a.n_samples > a.n_fft / 2, "frames_fft: clip shorter than n_fft/2+1 samples cannot be reflect-padded");
     SSAR_REQUIRE(a.spec_power == 1 || a.spec_power == 2 || !a.out_spec, "frames_fft: spec_power must be 1 or 2");
+    SSAR_REQUIRE(a.aux_frames >= 0 && a.aux_frames <= a.n_frames, "frames_fft: aux_frames=%d outside [0, n_frames]", a.aux_frames);
     SSAR_REQUIRE(a.n_frames == 0 || (long long)(a.n_frames - 1) * a.hop <= a.n_samples,
                  "frames_fft: n_frames=%d exceeds 1 + n_samples/hop", a.n_frames);
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);

@@ -49,7 +49,7 @@ class FramesArgs(C.Structure):
         ("out_complex", C.c_void_p), ("ldc", C.c_longlong),
         ("out_spec", C.c_void_p), ("lds", C.c_longlong), ("spec_power", C.c_int),
         ("out_rms", C.c_void_p), ("out_flatness", C.c_void_p),
-        ("fb", Filterbank * 2), ("proj", Projection),
+        ("fb", Filterbank * 2), ("proj", Projection), ("aux_frames", C.c_int),
     ]
 
 

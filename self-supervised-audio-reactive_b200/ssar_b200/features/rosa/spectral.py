@@ -28,7 +28,11 @@ def stft(y, n_fft=2048, hop_length=1024, center=True, window=torch.hann_window, 
     _check_stft_args(center, pad_mode)
     squeeze = y.dim() == 1
     n = y.shape[-1]
-    out = ops.frames_fft(y, n_fft, hop_length, 1 + n // hop_length, window, want_complex=True)["complex"]
+    n_frames = 1 + (n + 2 * (n_fft // 2) - n_fft) // hop_length
+    if n_fft in (1024, 2048):
+        out = ops.frames_fft(y, n_fft, hop_length, n_frames, window, want_complex=True)["complex"]
+    else:  # any other length (e.g. the tempogram window of a clip shorter than 1024 frames): direct DFT
+        out = ops.frames_dft(y, n_fft, hop_length, n_frames, window)
     c = torch.view_as_complex(out)
     c = _ft(c, squeeze)
     return c if return_complex else torch.view_as_real(c)

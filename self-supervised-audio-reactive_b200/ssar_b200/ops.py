@@ -50,6 +50,7 @@ def frames_fft(
     want_flatness: bool = False,
     banks=(),
     proj: dict | None = None,
+    aux_frames: int | None = None,
 ):
     """Framed real FFT + fused epilogues over a batch of clips.
 
@@ -60,6 +61,8 @@ def frames_fft(
       n_rows, start, count, offset, weights (device tables), out (complex-as-real tensor or view whose element
       [b, t, r] sits at out.data_ptr + ((b*T + t)*ld + r) complex elements), ld, scale, and optionally
       slots (int32 [B]: per-clip table slot), row_scale (fp32 [n_slots, row_scale_ld] view), row_scale_ld.
+    aux_frames: when given (<= n_frames), every output except `complex` covers only the first aux_frames frames of each
+      clip ([B, aux_frames, ...]): stft (T + 1 frames) and the last-frame-dropping features of one signal in one launch.
     """
     x, _ = _as_batch(x)
     B, N = x.shape
@@ -79,8 +82,12 @@ def frames_fft(
     a.twiddle = tw.data_ptr()
     out = {}
     keep = [x, win, tw]
+    n_cplx = n_frames
+    if aux_frames is not None and int(aux_frames) != n_frames:
+        a.aux_frames = int(aux_frames)
+        n_frames = int(aux_frames)  # every allocation below except the complex spectrum
     if want_complex:
-        out["complex"] = torch.empty(B, n_frames, F, 2, dtype=torch.float32, device=dev)
+        out["complex"] = torch.empty(B, n_cplx, F, 2, dtype=torch.float32, device=dev)
         a.out_complex = out["complex"].data_ptr()
         a.ldc = F
     if spec_power is not None:
@@ -199,6 +206,8 @@ def istft(spec_fm: torch.Tensor, n_fft: int, hop: int, window=torch.hann_window,
     dev = spec_fm.device
     if length is None:
         length = hop * (T1 - 1)
+    if n_fft not in (1024, 2048):  # arbitrary length: direct inverse DFT over all bins
+        return istft_band(spec_fm.contiguous(), n_fft, hop, window, 0, length)
     win = plan.window_tensor(window, n_fft, dev)
     if n_fft == 2048 and hop == 1024 and length % 2 == 0:  # the HPSS case: fused transform + overlap-add
         out = torch.empty(B, length, dtype=torch.float32, device=dev)
@@ -287,6 +296,10 @@ def gauss1d(x: torch.Tensor, sigma: float, mode: str = "circular", batched: bool
     radius = min(int(sigma * 4), 3 * T)
     if mode not in PAD_MODES:
         raise SsarError(f"gaussian_filter: unsupported padding mode {mode!r}")
+    if mode == "reflect" and min(radius, T) >= T:
+        # torch's reflect pad (features/processing.py:30,37) refuses a pad as long as the sequence; so does the mirror
+        raise RuntimeError(f"Argument #4: Padding size should be less than the corresponding input dimension, but got: "
+                           f"padding ({min(radius, T)}, {min(radius, T)}) at dimension 2 of input of {T} frames")
     w = (plan.gaussian_taps(float(sigma), radius, str(x.device)) if isinstance(causal, str) else
          plan.gaussian_taps_causal(float(sigma), radius, causal, str(x.device)))
     out = torch.empty_like(x)
@@ -361,6 +374,48 @@ def hwr_rowsum(x: torch.Tensor):
     out = torch.empty(rows, dtype=torch.float32, device=x.device)
     cabi.call("ssar_hwr_rowsum", ptr(x), i64(rows), i32(inner), ptr(out), nbytes=cabi.nbytes_of(x, out))
     return out
+
+
+_GROUP_TABLES = {}
+
+
+def _group_tables(group_sizes, device):
+    key = (tuple(int(g) for g in group_sizes), str(device))
+    t = _GROUP_TABLES.get(key)
+    if t is None:
+        starts, cols = [], []
+        for g, n in enumerate(key[0]):
+            starts.append(len(cols))
+            cols += [g] * n
+        t = _GROUP_TABLES[key] = (torch.tensor(cols, dtype=torch.int32, device=device),
+                                  torch.tensor(starts, dtype=torch.int32, device=device), starts)
+    return t
+
+
+def salience_features(raw: torch.Tensor, group_sizes, sigma: float = 2.0, short_sigma: float = 5.0, long_sigma: float = 80.0,
+                      eps: float = 1e-8):
+    """random/mir.py:44 for a batch: raw [B, T, C] holds the features of every clip side by side (column groups of
+    `group_sizes`); every group g becomes normalize(salience_weighted(gaussian_filter(raw_g, sigma))) (mir.py:14-22).
+    Returns a list of contiguous [B, T, C_g] tensors... as views of ONE feature-blocked buffer [B, T * C]: entry g is
+    buf[:, T * start_g : T * (start_g + C_g)].view(B, T, C_g) (contiguous per clip)."""
+    B, T, Cc = raw.shape
+    if sum(group_sizes) != Cc:
+        raise SsarError("salience_features: group sizes do not add up to the column count")
+    col_group, group_start, starts = _group_tables(group_sizes, raw.device)
+    G = len(group_sizes)
+    env = gauss1d(raw, sigma, "circular", batched=True)
+    short = gauss1d(env, short_sigma, "reflect", batched=True)
+    long = gauss1d(env, long_sigma, "reflect", batched=True)
+    keys = torch.empty(2, B, G, dtype=torch.int32, device=raw.device)
+    fill_u32(keys[0], KEY_POS_INF)
+    fill_u32(keys[1], KEY_NEG_INF)
+    w = torch.empty_like(env)
+    cabi.call("ssar_salience_weight", ptr(env), ptr(short), ptr(long), i32(B), i32(T), i32(Cc), ptr(col_group), i32(G), ptr(w),
+              ptr(keys[0]), ptr(keys[1]), nbytes=cabi.nbytes_of(env, short, long, w))
+    buf = torch.empty(B, T * Cc, dtype=torch.float32, device=raw.device)
+    cabi.call("ssar_group_normalize", ptr(w), i32(B), i32(T), i32(Cc), ptr(col_group), ptr(group_start), i32(G), ptr(keys[0]),
+              ptr(keys[1]), f32(eps), ptr(buf), nbytes=cabi.nbytes_of(w, buf))
+    return [buf[:, T * st : T * (st + n)].view(B, T, n) for st, n in zip(starts, group_sizes)]
 
 
 def feature_stats(x: torch.Tensor, stats: torch.Tensor | None = None):
@@ -488,15 +543,33 @@ def cqt(y: torch.Tensor, sr, hop_length: int = 1024, tuning_idx=None, sync_free:
     return out
 
 
-def plp_from_onset(onset_env: torch.Tensor, sr, hop_length: int = 1024, win_length: int = 1024, tempo_min=60, tempo_max=180):
-    """rosa/beat.py:46-75 after the onset envelope: onset_env [B, T] -> pulse [B, T] (normalised per clip)."""
-    onset_env, _ = _as_batch(onset_env)
-    B, T = onset_env.shape
-    win = min(T, win_length)
-    if win not in (1024, 2048):
-        raise NotImplementedError(f"plp: tempogram window {win} (clip shorter than {win_length} frames) is not built; "
-                                  "only the full 1024-frame window is")
-    tg = frames_fft(onset_env, win, 1, T + 1, torch.hann_window, want_complex=True)["complex"]  # [B, T+1, F, 2]
+def frames_dft(x: torch.Tensor, n_fft: int, hop: int, n_frames: int, window=torch.hann_window, k_lo: int = 0,
+               k_hi: int | None = None):
+    """torch.stft(center=True, reflect) for ANY n_fft in [2, 4096], bins [k_lo, k_hi) only (direct DFT, `ssar_frames_dft`)
+    -> complex-as-real [B, n_frames, k_hi - k_lo, 2]."""
+    x, _ = _as_batch(x)
+    B, N = x.shape
+    k_hi = n_fft // 2 + 1 if k_hi is None else int(k_hi)
+    win = plan.window_tensor(window, n_fft, x.device)
+    out = torch.empty(B, n_frames, max(k_hi - k_lo, 0), 2, dtype=torch.float32, device=x.device)
+    cabi.call("ssar_frames_dft", ptr(x), i64(N), i64(x.stride(0)), i32(B), i32(n_fft), i32(hop), i32(n_frames), ptr(win),
+              i32(k_lo), i32(k_hi), ptr(out), nbytes=cabi.nbytes_of(x, out))
+    return out
+
+
+def istft_band(spec_band: torch.Tensor, n_fft: int, hop: int, window, k_lo: int, length: int):
+    """torch.istft(center=True, length) for ANY n_fft from a spectrum that is zero outside bins [k_lo, k_lo + nb):
+    spec_band complex-as-real [B, n_frames, nb, 2] -> [B, length] (`ssar_istft_band`)."""
+    B, T1, nb, _ = spec_band.shape
+    win = plan.window_tensor(window, n_fft, spec_band.device)
+    out = torch.empty(B, length, dtype=torch.float32, device=spec_band.device)
+    cabi.call("ssar_istft_band", ptr(spec_band), i32(B), i32(T1), i32(n_fft), i32(hop), ptr(win), i32(k_lo), i32(k_lo + nb),
+              i64(length), ptr(out), nbytes=cabi.nbytes_of(spec_band, out))
+    return out
+
+
+def tempo_bin_range(sr, hop_length: int, win: int, tempo_min, tempo_max):
+    """Bins of the Fourier tempogram that rosa/beat.py:52-57 keeps: [k_lo, k_hi) of linspace(0, rate / 2, 1 + win // 2)."""
     F = win // 2 + 1
     freqs = torch.linspace(0, float(sr * 60 / float(hop_length)) / 2, F)
     keep = torch.ones(F, dtype=torch.bool)
@@ -505,10 +578,34 @@ def plp_from_onset(onset_env: torch.Tensor, sr, hop_length: int = 1024, win_leng
     if tempo_max is not None:
         keep &= ~(freqs > tempo_max)
     idx = keep.nonzero().flatten()
-    k_lo, k_hi = (int(idx[0]), int(idx[-1]) + 1) if len(idx) else (0, 0)
-    cabi.call("ssar_plp_peaks", ptr(tg), i64(F), i32(B), i32(T + 1), i32(F), i32(k_lo), i32(k_hi),
-              nbytes=2 * cabi.nbytes_of(tg))
-    pulse = istft(tg, win, 1, torch.hann_window, T)
+    return (int(idx[0]), int(idx[-1]) + 1) if len(idx) else (0, 0)
+
+
+def plp_from_onset(onset_env: torch.Tensor, sr, hop_length: int = 1024, win_length: int = 1024, tempo_min=60, tempo_max=180):
+    """rosa/beat.py:46-75 after the onset envelope: onset_env [B, T] -> pulse [B, T] (normalised per clip).
+    The tempogram window is min(T, win_length) (beat.py:47): 1024 / 2048 run on the radix FFT kernels; any other length
+    (a clip shorter than win_length frames) on the band-limited direct DFT, which only ever forms the 60-180 BPM bins."""
+    onset_env, _ = _as_batch(onset_env)
+    B, T = onset_env.shape
+    win = min(T, win_length)
+    k_lo, k_hi = tempo_bin_range(sr, hop_length, win, tempo_min, tempo_max)
+    n_frames = 1 + (T + 2 * (win // 2) - win)  # torch.stft, hop 1, centre-padded by win // 2 on both sides
+    if win in (1024, 2048):
+        F = win // 2 + 1
+        tg = frames_fft(onset_env, win, 1, n_frames, torch.hann_window, want_complex=True)["complex"]  # [B, T+1, F, 2]
+        cabi.call("ssar_plp_peaks", ptr(tg), i64(F), i32(B), i32(n_frames), i32(F), i32(k_lo), i32(k_hi),
+                  nbytes=2 * cabi.nbytes_of(tg))
+        pulse = istft(tg, win, 1, torch.hann_window, T)
+    else:
+        if win < 2:
+            raise SsarError("plp: the onset envelope needs at least 2 frames")
+        nb = k_hi - k_lo
+        tg = frames_dft(onset_env, win, 1, n_frames, torch.hann_window, k_lo, k_hi)  # [B, n_frames, nb, 2]
+        if nb > 0:
+            cabi.call("ssar_plp_peaks", ptr(tg), i64(nb), i32(B), i32(n_frames), i32(nb), i32(0), i32(nb),
+                      nbytes=2 * cabi.nbytes_of(tg))
+        pulse = (istft_band(tg, win, 1, torch.hann_window, k_lo, T) if nb > 0 else
+                 torch.zeros(B, T, dtype=torch.float32, device=onset_env.device))
     zero = torch.zeros(B, 1, dtype=torch.float32, device=pulse.device)
     pulse = clamp_cols(pulse.view(B, T, 1), zero, None).view(B, T)  # clamp(pulse, 0, pulse.max())
     return normalize(pulse, B)

@@ -159,6 +159,38 @@ def g_a2f(ref):
     )
 
 
+def g_a2f_short(ref):
+    """audio2features on clips SHORTER than the 1024-frame tempogram window (rosa/beat.py:46-47: win_length = T): 10 s,
+    16 s (the reference generators' own clip length, features/generate.py:51-54) and 42 s at 44.1 kHz -> T = 240, 384,
+    1008; plus plp / pulse on a 24 576 Hz clip of T = 300 and an odd T = 333."""
+    import contextlib, io
+
+    out = {}
+    for secs, ci in ((10, 11), (16, 12), (42, 13)):
+        x44 = synth_clip(44100 * secs, 44100, ci)
+        with contextlib.redirect_stdout(io.StringIO()):  # T = 240 prints the short-sequence Gaussian warning (sigma 10)
+            out[f"features_{secs}s"] = ref.data.audio2features(x44, 44100, 24)
+            out[f"features_raw_{secs}s"] = ref.data.audio2features(x44, 44100, 24, clamp=False, smooth=False)
+    for T, ci in ((300, 14), (333, 15)):
+        x = synth_clip(1024 * T + 17, SR, ci)
+        out[f"plp_T{T}"] = ref.beat.plp(x, SR)
+        med = lambda *a, **k: torch.median(*a, **k).values
+        out[f"onset_median_T{T}"] = ref.beat.onset_strength(x, SR, aggregate=med)
+    save("a2f_short", **out)
+
+
+def g_mir(ref):
+    """The UNMODIFIED retrieve_music_information (random/mir.py:25-46) on a 20 s clip: its feature dict (the part on the
+    path: 8 feature functions -> gaussian sigma 2 -> salience_weighted -> normalize).  Tempo / beats / segmentations come
+    from stand-ins (ref_loader) and are not stored."""
+    n = SR * 20 + 100
+    x = synth_clip(n, SR, 16)
+    feats, _, _ = ref.mir.retrieve_music_information(x, SR, device="cpu")
+    env = synth_features(500, 3, 21).abs()
+    save("mir", n=n, sr=SR, clip_index=16, salience_2d=ref.mir.salience_weighted(env), salience_1d=ref.mir.salience_weighted(env[:, 0]),
+         **{f"feat_{k}": v for k, v in feats.items()})
+
+
 def g_traj(ref):
     """Patch(seed).forward latents / noise batches, spline loops, latent_patch, FixedLatentNoiseDecoder.
     Full [T, 18, 512] tensors are stored as a fixed random projection (512 -> 8) plus a few whole frames."""
@@ -230,7 +262,7 @@ def g_maua(ref):
     save("maua", **out)
 
 
-GROUPS = {"maua": g_maua, "traj": g_traj, "a2f": g_a2f, "chroma": g_chroma, "post": g_post, "spectral": g_spectral, "frame_features": g_frame_features, "hpss_filters": g_hpss_filters}
+GROUPS = {"mir": g_mir, "a2f_short": g_a2f_short, "maua": g_maua, "traj": g_traj, "a2f": g_a2f, "chroma": g_chroma, "post": g_post, "spectral": g_spectral, "frame_features": g_frame_features, "hpss_filters": g_hpss_filters}
 
 if __name__ == "__main__":
     torch.manual_seed(0)

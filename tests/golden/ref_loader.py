@@ -126,7 +126,11 @@ def _install_shims():
 
     conv = mod("librosa.core.convert", note_to_hz=note_to_hz)
     core = mod("librosa.core", convert=conv, note_to_hz=note_to_hz)
-    mod("librosa", core=core, note_to_hz=note_to_hz, beat=mod("librosa.beat"))
+    # librosa.beat: tempo / beat tracking are OFF the path (random/mir.py:28-33; inputs of Patch) — fixed answers so that
+    # the unmodified retrieve_music_information can run end to end for its feature part
+    beat = mod("librosa.beat", tempo=lambda **k: 120.0,
+               beat_track=lambda **k: (120.0, list(range(0, len(k["onset_envelope"]), 12))))
+    mod("librosa", core=core, note_to_hz=note_to_hz, beat=beat)
 
     mod(
         "torchcubicspline",
@@ -199,6 +203,20 @@ def _build_tree():
         'UNITFEATS = ["rms", "drop_strength", "onsets", "spectral_flatness"]\n'
         'ALLFEATS = ["chromagram", "tonnetz", "mfcc", "spectral_contrast"] + UNITFEATS\n'
     )
+    # the REAL random/mir.py under another name (`mir_real`): its feature part (:14-22, :26, :44) is on the path.  Its
+    # off-path imports are satisfied by stand-ins: rosa/segment.py (torch_geometric / sklearn / librosa) by a stub module
+    # whose two functions return fixed label tensors, librosa.beat.tempo / beat_track by the shims below.
+    dst = TREE / "ssar/random/mir_real.py"
+    if not dst.exists():
+        dst.symlink_to(REFERENCE_ROOT / "ssar/random/mir.py")
+    (TREE / "ssar/features/rosa/segment.py").write_text(
+        "import torch\n"
+        "def laplacian_segmentation(feature, beats, ks=[2, 4, 6, 8, 12, 16]):\n"
+        "    T = feature.shape[0]\n"
+        "    return [torch.nn.functional.one_hot(torch.arange(T) % k, k).float() for k in ks]\n"
+        "def laplacian_segmentation_rosa(audio, sr, n_frames, ks=[2, 4, 6, 8, 12, 16]):\n"
+        "    return torch.stack([torch.arange(n_frames) % k for k in ks], dim=1)\n"
+    )
     # sibling model modules imported by latent_n_noise2.py but never executed on the path
     for stub in ["ssar/models/convnext.py", "ssar/models/mlp.py", "ssar/models/audio2latent.py",
                  "ssar/models/sashimi/sashimi.py"]:
@@ -268,6 +286,8 @@ def load_reference(build_quantile: bool = True):
     ns.noise = importlib.import_module("ssar.random.noise")
     ns.patch = importlib.import_module("ssar.random.patch")
     ns.lnn2 = importlib.import_module("ssar.models.latent_n_noise2")
+    import scipy.stats  # noqa: F401  (mir.py:29 uses scipy.stats through a bare `import scipy`)
+    ns.mir = importlib.import_module("ssar.random.mir_real")
     ns.spline_coeffs = _natural_cubic_spline_coeffs
     ns.NaturalCubicSpline = _NaturalCubicSpline
     _LOADED = ns
