@@ -157,19 +157,31 @@ def cpu_pass(kind, x, sr):
     if kind == "cfg2":
         S = dsp.spectrogram(x, N_FFT, HOP2, power=2)
         return S, dsp.mel_basis(sr, N_FFT) @ S, dsp.onset_strength(x, sr, HOP2, N_FFT), dsp.rms(x, sr, N_FFT, HOP2)
-    from ssar_b200.pipeline import PATCH_FEATURE_COLUMNS
     from ssar_b200.synth import synth_patch_inputs
-    from ssar_oracle import features, post, traj
+    from ssar_oracle import features, traj
 
+    # the reference's two call sites for one track: audio2features (supervised/data.py:60-107) for the dataset features
+    # and retrieve_music_information's feature part (random/sample.py:34,61; mir.py:26,44) -> Patch -> latents
     f = features.audio2features(x, sr, FPS)
     _, segs, palette = synth_patch_inputs(f.shape[0], 0)
-    pf = {n: post.normalize(f[:, a:b]) for n, (a, b) in PATCH_FEATURE_COLUMNS.items()}
+    pf = features.retrieve_music_features(dsp.resample(x, sr, FPS * 1024), FPS * 1024)
     lat, _ = traj.Patch(pf, segs, 120.0, fps=FPS, seed=42).forward(palette, downscale_factor=4)
     return f, lat
 
 
 def cpu_sample_seconds(kind):
-    return 60 if kind == "cfg2" else 45  # full: 45 s is the shortest clip whose PLP uses the full 1024-frame window
+    return 60 if kind == "cfg2" else DUR_S  # full: one whole clip of the GPU arm's workload (240 s)
+
+
+def use_all_host_threads():
+    """torch.distributed.run exports OMP_NUM_THREADS=1 to its workers; the CPU arm is the reference's torch-CPU code with
+    every host core it can use, so the thread count is set explicitly (and reported)."""
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    torch.set_num_threads(max(1, n))
+    return torch.get_num_threads()
 
 
 def time_cpu(kind, steps, warmup):
@@ -189,8 +201,8 @@ def time_cpu(kind, steps, warmup):
 def run_reference(args, rank):
     if rank != 0:
         return
-    v, dt, s = time_cpu(args.workload, args.steps, max(1, min(args.warmup, 2)))
-    cores = torch.get_num_threads()
+    cores = use_all_host_threads()
+    v, dt, s = time_cpu(args.workload, args.steps, 1 if args.warmup > 0 else 0)
     sample = (f"1 clip x {s} s of the workload per step (oracle port of the reference's torch-CPU code, fp32, "
               f"{cores} threads)")
     print(json.dumps({
@@ -431,8 +443,9 @@ def main():
             roof["traffic_source"] = "ncu capture (profiles/), per step"
         cpu = None
         if world == 1 and not args.no_cpu:
-            v, dt, s = time_cpu(kind, 1 if kind == "full" else 3, 1)
-            cpu = {"value": v, "unit": "audio-s/s", "cores": torch.get_num_threads(), "kind": "port",
+            n_threads = use_all_host_threads()
+            v, dt, s = time_cpu(kind, 1 if kind == "full" else 3, 0 if kind == "full" else 1)
+            cpu = {"value": v, "unit": "audio-s/s", "cores": n_threads, "kind": "port",
                    "sample": f"1 clip x {s} s of the same workload, oracle port (torch-CPU fp32), {dt:.2f} s per pass"}
         result_out.write(json.dumps({
             "metric": "audio-sec/sec", "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps,

@@ -23,13 +23,13 @@ def tm(fn, n=3):
 
 ms, feats = tm(lambda: pipeline.audio2features_batch(x, 44100, 24))
 print(f"a2f batch B={B}: {ms:.1f} ms  ({ms/B:.2f} ms/clip)")
-pf = pipeline.patch_features_from_matrix(feats[0])
+pf = pipeline.features_and_patch_inputs(x, 44100, 24)[1]
 for dev in ("cpu", "cuda"):
     ms, patch = tm(lambda: Patch(pf, segs, 120.0, seed=42, device=dev))
     print(f"Patch.__init__ rng={dev}: {ms:.2f} ms")
     ms, _ = tm(lambda: patch.forward(palette, downscale_factor=4))
     print(f"Patch.forward rng={dev}: {ms:.2f} ms")
-ms, _ = tm(lambda: pipeline.patch_features_from_matrix(feats[0]))
+ms, _ = tm(lambda: pipeline.features_and_patch_inputs(x, 44100, 24)[1])
 print(f"patch_features_from_matrix: {ms:.2f} ms")
 import cProfile, pstats
 patch = Patch(pf, segs, 120.0, seed=42, device="cuda")

@@ -29,7 +29,7 @@ for C in (8, 32):
     h, g, _ = timed(lambda: [pipeline.audio2features_batch(x[c:c + C], 44100, 24, deferred_checks=[]) for c in range(0, B, C)])
     print(f"a2f 32 clips in chunks of {C}: host {h:.1f} ms, gpu {g:.1f} ms")
 feats = pipeline.audio2features_batch(x, 44100, 24)
-h, g, pf = timed(lambda: pipeline.patch_features_batch(feats))
+h, g, pf = timed(lambda: pipeline.features_and_patch_inputs(x, 44100, 24)[1])
 print(f"patch_features_batch: host {h:.2f} ms gpu {g:.2f} ms")
 h, g, patches = timed(lambda: [Patch(None, segs, 120.0, seed=42 + b, device="cuda") for b in range(B)])
 print(f"sampling 32 patches: host {h:.1f} ms, gpu {g:.1f} ms")

@@ -6,6 +6,7 @@ and with everything that can share an FFT fused into that FFT's epilogue.
 from __future__ import annotations
 
 import functools
+import threading
 
 import torch
 
@@ -80,64 +81,86 @@ def _check_peak_counts(cnt):
         raise RuntimeError("quantile() input tensor must be non-empty")
 
 
-def audio2features_batch(audio: torch.Tensor, sr, fps, clamp=True, smooth=True, emphasis=False, deferred_checks=None,
-                         sync_free=False):
-    """supervised/data.py:60-107 for a batch of mono clips [B, N] at `sr` -> [B, T, 59].
+# random/mir.py:8 (AFEATFNS, in its order) with each feature's column count: the inputs of `Patch`
+MIR_GROUPS = (("chromagram", 12), ("tonnetz", 6), ("mfcc", 20), ("spectral_contrast", 7), ("spectral_flatness", 1),
+              ("rms", 1), ("drop_strength", 1), ("onsets", 1))
 
-    Same arithmetic per clip as the reference call sequence; work the reference repeats on identical inputs is done
-    once (harmonic/percussive share an STFT + medians; chromagram(audio_harm) is computed once for both the chroma and
-    the tonnetz columns; the three band filters share the 4 kHz high-pass; the audio STFT feeds mfcc, contrast,
-    flatness and the HPSS)."""
-    from .resampling import resample
 
-    if audio.dim() != 2:
-        raise ValueError("audio2features_batch expects [clips, samples]")
-    x = resample(audio, sr, fps * 1024)
-    sr = fps * 1024
+def _cens_and_tonnetz(y: torch.Tensor, sr, hop: int, sync_free: bool):
+    """chroma_cens(y, sr).T and the tonnetz of it (rosa/spectral.py:239-280, features/audio.py:48-57) -> [B, T, 12], [B, T, 6].
+    The tuning is estimated from `y` itself (chroma_cqt's tuning=None)."""
+    C = ops.cqt(y, sr, hop, sync_free=sync_free)
+    cens = ops.cens_smooth(ops.chroma_from_cqt(C, quantize=True), plan.cens_window(41, str(y.device)), l2=True)
+    return cens, ops.tonnetz(cens)
+
+
+def feature_chain(x: torch.Tensor, sr, want_a2f: bool = True, want_mir: bool = False, sync_free: bool = False):
+    """Every per-frame feature of a batch of clips x [B, N] that is ALREADY at sr = 1024 * fps (n_fft 2048, hop 1024):
+
+      a2f: the 59 un-clamped, un-smoothed columns of supervised/data.py:64-99 -> [B, T, 59]
+      mir: the 8 raw feature functions random/mir.py:26 calls on the audio itself, side by side -> [B, T, 49] in
+           MIR_GROUPS order (before mir.py:44's smoothing / salience weighting / normalisation)
+
+    Same arithmetic per clip as the reference's call sequences; work the reference repeats on identical inputs is done
+    once: every signal is transformed ONCE per (n_fft, hop) — the launch over `x` emits the complex STFT the HPSS needs
+    (T + 1 frames) together with magnitude (contrast), mel (mfcc), flatness and RMS of the first T frames; harmonic /
+    percussive share the STFT and the medians; the three band filters share the 4 kHz high-pass.  The two paths differ in
+    which signal the chroma features see: mir.py's chromagram(audio) = chroma_cens(harmonic(audio)), while data.py:68-69
+    passes audio_harm in, i.e. chroma_cens(harmonic(harmonic(audio))) — both are built when both are wanted."""
     B, N = x.shape
     n_fft, hop = 2048, 1024
     T = N // hop
     dev = str(x.device)
 
-    # --- full-band per-frame features: one pass over the audio for mel(mfcc) / magnitude(contrast) / flatness / rms
+    # --- one pass over the audio: complex STFT (T + 1 frames) + mel(mfcc) / magnitude(contrast) / flatness / rms (T frames)
     mel_bank = plan.mel_bank(float(sr), n_fft, 128, 0.0, None, dev)
-    fa = ops.frames_fft(x, n_fft, hop, T, torch.hann_window, spec_power=1, want_flatness=True, want_rms=True,
-                        banks=[(mel_bank, True, True)])
+    fa = ops.frames_fft(x, n_fft, hop, T + 1, torch.hann_window, want_complex=True, spec_power=1, want_flatness=True,
+                        want_rms=True, banks=[(mel_bank, True, True)], aux_frames=T)
     mfcc = ops.mfcc_from_mel(fa["bank0"], fa["bank0_max"], plan.dct_matrix(20, 128, dev))
     contrast = ops.spectral_contrast(fa["spec"], plan.contrast_bands(float(sr), n_fft, 200.0, 6, 0.02, dev))
     flatness = fa["flatness"]
 
-    # --- harmonic / percussive separation (and the second separation chromagram() applies to audio_harm)
-    harm, perc = hpss_pair(x)
-    harm2 = hpss_pair(harm, want_perc=False)[0]  # harmonic(audio_harm): features/audio.py:44-45 applied to data.py:68-69's argument
-    C = ops.cqt(harm2, sr, hop, sync_free=sync_free)
-    cens = ops.cens_smooth(ops.chroma_from_cqt(C, quantize=True), plan.cens_window(41, dev), l2=True)  # [B, T, 12]
-    ton = ops.tonnetz(cens)
+    # --- harmonic / percussive separation
+    harm, perc = hpss_pair(x, D=fa["complex"])
+    del fa["complex"], fa["spec"]
+    on, on_med = onset_pair(perc, sr, hop, n_fft, want_median=want_a2f)
 
-    # --- onset envelopes of the percussive part and its three bands; pulse
-    p_lo, p_mid, p_hi = band_split(perc, sr)
-    on, on_med = onset_pair(perc, sr, hop, n_fft, want_median=True)
-    on_lo, on_mid, on_hi = (onset_pair(b, sr, hop, n_fft)[0] for b in (p_lo, p_mid, p_hi))
-    pulse = ops.plp_from_onset(on_med, sr, hop)
-
-    # --- rms of the harmonic part and its bands; drop strength of the full signal and its bands
-    if n_fft == 2048 and hop == 1024 and N >= 2048:
+    out = {}
+    cens1 = ton1 = None
+    if want_mir:
+        cens1, ton1 = _cens_and_tonnetz(harm, sr, hop, sync_free)  # chromagram(audio), tonnetz(audio)
+    if want_a2f or want_mir:
+        rms_x_bands = band_rms(x, sr, T) if want_a2f else ()
+        rms_a = torch.stack([fa["rms"], *rms_x_bands], dim=-1)  # [B, T, 4] (or [B, T, 1])
+        drop = ops.emphasize(ops.gauss1d(rms_a, 10, "circular", batched=True), 10, 50)
+    if want_a2f:
+        # harmonic(audio_harm): features/audio.py:44-45 applied to data.py:68-69's argument; the same launch gives rms(harm)
+        fh = ops.frames_fft(harm, n_fft, hop, T + 1, torch.hann_window, want_complex=True, want_rms=True, aux_frames=T)
+        harm2 = hpss_pair(harm, D=fh["complex"], want_perc=False)[0]
+        del fh["complex"]
+        cens, ton = _cens_and_tonnetz(harm2, sr, hop, sync_free)
+        # onset envelopes of the percussive part's three bands; pulse
+        p_lo, p_mid, p_hi = band_split(perc, sr)
+        on_lo, on_mid, on_hi = (onset_pair(b, sr, hop, n_fft)[0] for b in (p_lo, p_mid, p_hi))
+        pulse = ops.plp_from_onset(on_med, sr, hop)
         # band signals of harm / x are only ever looked at through their RMS: taken from the filters' output passes
-        rms_h = [ops.frames_rms(harm, n_fft, hop, T), *band_rms(harm, sr, T)]
-        rms_a = torch.stack([fa["rms"], *band_rms(x, sr, T)], dim=-1)  # [B,T,4]
-    else:
-        h_lo, h_mid, h_hi = band_split(harm, sr)
-        rms_h = [ops.frames_rms(s, n_fft, hop, T) for s in (harm, h_lo, h_mid, h_hi)]
-        a_lo, a_mid, a_hi = band_split(x, sr)
-        rms_a = torch.stack([fa["rms"]] + [ops.frames_rms(s, n_fft, hop, T) for s in (a_lo, a_mid, a_hi)], dim=-1)
-    drop = ops.emphasize(ops.gauss1d(rms_a, 10, "circular", batched=True), 10, 50)
+        rms_h = [fh["rms"], *band_rms(harm, sr, T)]
+        Tm = min(T, cens.shape[1])
+        cols = [mfcc[:, :Tm], cens[:, :Tm], ton[:, :Tm], contrast[:, :Tm]]
+        cols += [s[:, :Tm, None] for s in (flatness, on, on_lo, on_mid, on_hi, pulse, *rms_h)]
+        cols.append(drop[:, :Tm])
+        out["a2f"] = torch.cat(cols, dim=2).contiguous()
+    if want_mir:
+        Tm = min(T, cens1.shape[1])
+        onsets = ops.normalize(on, B)  # features/audio.py:27-28
+        cols = [cens1[:, :Tm], ton1[:, :Tm], mfcc[:, :Tm], contrast[:, :Tm]]
+        cols += [s[:, :Tm, None] for s in (flatness, fa["rms"], drop[:, :, 0], onsets)]
+        out["mir"] = torch.cat(cols, dim=2).contiguous()
+    return out
 
-    Tm = min(T, cens.shape[1])
-    cols = [mfcc[:, :Tm], cens[:, :Tm], ton[:, :Tm], contrast[:, :Tm]]
-    cols += [s[:, :Tm, None] for s in (flatness, on, on_lo, on_mid, on_hi, pulse, *rms_h)]
-    cols.append(drop[:, :Tm])
-    feats = torch.cat(cols, dim=2).contiguous()
 
+def finish_features(feats: torch.Tensor, fps, clamp=True, smooth=True, emphasis=False, deferred_checks=None):
+    """supervised/data.py:100-106 on [B, T, 59]: peak-percentile clamp, lower-percentile clamp, smoothing, emphasis."""
     if clamp:
         thr, cnt = ops.col_quantile(feats, (100 - 2.5) / 100, "peaks", "linear", want_count=True)
         feats = ops.clamp_cols(feats, None, thr)
@@ -155,19 +178,45 @@ def audio2features_batch(audio: torch.Tensor, sr, fps, clamp=True, smooth=True, 
     return feats
 
 
-# column ranges of the [T, 59] feature matrix (supervised/data.py:32-51) used as `Patch` inputs (SURVEY.md 8d cfg 4)
-PATCH_FEATURE_COLUMNS = {"mfcc": (0, 20), "chromagram": (20, 32), "tonnetz": (32, 38), "spectral_contrast": (38, 45),
-                         "spectral_flatness": (45, 46), "onsets": (46, 47), "rms": (51, 52), "drop_strength": (55, 56)}
+def patch_inputs_from_raw(mir_raw: torch.Tensor):
+    """random/mir.py:44 for a batch: [B, T, 49] raw features (MIR_GROUPS order) -> dict name -> [B, T, C] of
+    normalize(salience_weighted(gaussian_filter(f, sigma=2))), each (clip, feature) block normalised on its own."""
+    parts = ops.salience_features(mir_raw, [n for _, n in MIR_GROUPS], sigma=2.0, short_sigma=5.0, long_sigma=80.0)
+    return {name: p for (name, _), p in zip(MIR_GROUPS, parts)}
 
 
-def patch_features_from_matrix(feats: torch.Tensor):
-    """[T, 59] feature matrix of one clip -> dict of normalised [T, C] features in the shape `Patch` expects
-    (random/mir.py:44 ends in `normalize`: every entry lies in [0, 1])."""
-    return {name: ops.normalize(feats[:, a:b].contiguous(), 1) for name, (a, b) in PATCH_FEATURE_COLUMNS.items()}
+def audio2features_batch(audio: torch.Tensor, sr, fps, clamp=True, smooth=True, emphasis=False, deferred_checks=None,
+                         sync_free=False):
+    """supervised/data.py:60-107 for a batch of mono clips [B, N] at `sr` -> [B, T, 59]."""
+    from .resampling import resample
+
+    if audio.dim() != 2:
+        raise ValueError("audio2features_batch expects [clips, samples]")
+    x = resample(audio, sr, fps * 1024)
+    raw = feature_chain(x, fps * 1024, want_a2f=True, want_mir=False, sync_free=sync_free)["a2f"]
+    return finish_features(raw, fps, clamp, smooth, emphasis, deferred_checks)
+
+
+def music_features_batch(x: torch.Tensor, sr, sync_free=False):
+    """The feature part of random/mir.py:25-46 (`retrieve_music_information`) for a batch of clips x [B, N] at sr:
+    dict name -> [B, T, C], the `features` argument of `Patch`.  Tempo, beats and the Laplacian segmentations
+    (mir.py:28-42: librosa / scipy on the CPU) are inputs of `Patch` here, not computed."""
+    return patch_inputs_from_raw(feature_chain(x, sr, want_a2f=False, want_mir=True, sync_free=sync_free)["mir"])
+
+
+def features_and_patch_inputs(audio: torch.Tensor, sr, fps, deferred_checks=None, sync_free=False):
+    """One pass over a batch of clips [B, N] at `sr` for both consumers of the north-star unit: the dataset features
+    `audio2features(audio, sr, fps)` [B, T, 59] (supervised/data.py:60-107) and the `Patch` inputs
+    `retrieve_music_information(resample(audio, sr, 1024 * fps), 1024 * fps)[0]` (random/sample.py:34,61; mir.py:26,44)."""
+    from .resampling import resample
+
+    x = resample(audio, sr, fps * 1024)
+    ch = feature_chain(x, fps * 1024, want_a2f=True, want_mir=True, sync_free=sync_free)
+    return finish_features(ch["a2f"], fps, deferred_checks=deferred_checks), patch_inputs_from_raw(ch["mir"])
 
 
 class FeatureGraph:
-    """`audio2features_batch` + `patch_features_batch` for a fixed (clips, samples, sr, fps) as ONE replayed CUDA graph.
+    """`features_and_patch_inputs` for a fixed (clips, samples, sr, fps) as ONE replayed CUDA graph.
 
     The feature path of a chunk of clips is ~300 launches whose arguments depend only on the shapes (the one
     data-dependent choice, each clip's tuned CQT basis, is a device gather with `sync_free=True`), so it is captured once
@@ -178,17 +227,26 @@ class FeatureGraph:
     _cache = {}     # key -> FeatureGraph, insertion-ordered: least recently used first
     _seen = {}      # key -> how often the shape was asked for
     MAX_GRAPHS = 3  # each graph pins its private pool (~0.4 GB per clip): keep only the most recently used shapes
+    _lock = threading.RLock()
+
+    @staticmethod
+    def _key(n_clips, n_samples, sr, fps, device):
+        # a graph owns static input / output buffers: it belongs to the host thread that asked for it (two threads that
+        # process the same shape concurrently get two graphs, never each other's buffers)
+        return (int(n_clips), int(n_samples), float(sr), int(fps), device.index, threading.get_ident())
 
     @classmethod
     def get(cls, n_clips, n_samples, sr, fps, device):
         device = torch.device(device)
-        key = (int(n_clips), int(n_samples), float(sr), int(fps), device.index)
-        g = cls._cache.pop(key, None)
-        if g is None:
-            g = cls(n_clips, n_samples, sr, fps, device)
-            while len(cls._cache) >= cls.MAX_GRAPHS:
-                cls._cache.pop(next(iter(cls._cache)))  # drops the graph and its pool
-        cls._cache[key] = g
+        key = cls._key(n_clips, n_samples, sr, fps, device)
+        with cls._lock:
+            g = cls._cache.pop(key, None)
+            if g is None:
+                g = cls(n_clips, n_samples, sr, fps, device)
+                mine = [k for k in cls._cache if k[-1] == key[-1]]  # only this thread's graphs are ever evicted here:
+                while len(mine) >= cls.MAX_GRAPHS:                  # another thread may be replaying its own
+                    cls._cache.pop(mine.pop(0))  # drops the graph and its pool
+            cls._cache[key] = g
         return g
 
     @classmethod
@@ -196,11 +254,13 @@ class FeatureGraph:
         """The graph for this shape from its SECOND request on (None the first time): a dataset of clips of many different
         lengths runs eagerly instead of capturing — and pinning memory for — a graph per length."""
         device = torch.device(device)
-        key = (int(n_clips), int(n_samples), float(sr), int(fps), device.index)
-        n = cls._seen[key] = cls._seen.get(key, 0) + 1
-        if len(cls._seen) > 4096:
-            cls._seen.clear()
-        return cls.get(n_clips, n_samples, sr, fps, device) if (n >= 2 or key in cls._cache) else None
+        key = cls._key(n_clips, n_samples, sr, fps, device)
+        with cls._lock:
+            n = cls._seen[key] = cls._seen.get(key, 0) + 1
+            if len(cls._seen) > 4096:
+                cls._seen.clear()
+            cached = key in cls._cache
+        return cls.get(n_clips, n_samples, sr, fps, device) if (n >= 2 or cached) else None
 
     def __init__(self, n_clips, n_samples, sr, fps, device):
         self.device, self.sr, self.fps = device, sr, fps
@@ -211,13 +271,13 @@ class FeatureGraph:
             cs = torch.cuda.Stream(device)
             cs.wait_stream(torch.cuda.current_stream(device))
             with torch.cuda.stream(cs):  # eager warm-up: plan tables, function attributes, allocator pools
-                patch_features_batch(audio2features_batch(self.x, sr, fps, deferred_checks=[], sync_free=True))
+                features_and_patch_inputs(self.x, sr, fps, deferred_checks=[], sync_free=True)
             cs.synchronize()
             self.graph = torch.cuda.CUDAGraph()
             checks = []
             with torch.cuda.graph(self.graph, stream=cs, capture_error_mode="thread_local"):
-                self.feats = audio2features_batch(self.x, sr, fps, deferred_checks=checks, sync_free=True)
-                self.patch_feats = patch_features_batch(self.feats)
+                self.feats, self.patch_feats = features_and_patch_inputs(self.x, sr, fps, deferred_checks=checks,
+                                                                         sync_free=True)
             self._checks = checks
             self.peak_count = checks[0].args[0] if checks else None  # static [B, 59] interior-peak counts
 
@@ -245,7 +305,7 @@ _SIDE_STREAMS = {}
 
 
 def _side_stream(device, purpose="sampler"):
-    key = (torch.device(device).index, __import__("threading").get_ident(), purpose)
+    key = (torch.device(device).index, threading.get_ident(), purpose)
     st = _SIDE_STREAMS.get(key)
     if st is None:
         # sampler: high priority, so its tiny generator kernels jump the queue of feature kernels
@@ -259,13 +319,14 @@ _STAGING = {}
 def _staging(device, shape, dtype):
     """Two device buffers of `shape` for the H2D ping-pong of host-resident audio, kept per (device, thread, shape);
     `free[i]` is the event after which buffer i may be overwritten."""
-    key = (torch.device(device).index, __import__("threading").get_ident(), tuple(shape), dtype)
+    key = (torch.device(device).index, threading.get_ident(), tuple(shape), dtype)
     st = _STAGING.get(key)
     if st is None:
-        if len(_STAGING) >= 4:
-            _STAGING.clear()
-        st = _STAGING[key] = {"buf": [torch.empty(shape, dtype=dtype, device=device) for _ in range(2)],
-                              "free": [None, None]}
+        with FeatureGraph._lock:
+            for k in [k for k in _STAGING if k[1] == key[1]][:-1]:  # this thread's older shapes only; their copies were
+                _STAGING.pop(k)                                     # consumed by the calls that issued them
+            st = _STAGING[key] = {"buf": [torch.empty(shape, dtype=dtype, device=device) for _ in range(2)],
+                                  "free": [None, None]}
     return st
 
 
@@ -293,15 +354,6 @@ def default_patch_workers(rng_device="cpu") -> int:
         cores = os.cpu_count() or 1
     share = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", "1"))))
     return max(1, min(8, cores // share))
-
-
-def patch_features_batch(feats: torch.Tensor):
-    """[B, T, 59] -> dict of [B, T, C] features, each (clip, feature) block min-max normalised on its own — the batched
-    form of `patch_features_from_matrix` (one launch set per feature instead of one per clip and feature)."""
-    out = {}
-    for name, (a, b) in PATCH_FEATURE_COLUMNS.items():
-        out[name] = ops.normalize(feats[:, :, a:b].contiguous(), feats.shape[0])
-    return out
 
 
 def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, segmentations, tempo=120.0, seed=42,
@@ -364,8 +416,7 @@ def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, se
         feats_chunks, latents, noises = [], None, [None] * B
         with torch.cuda.device(dev), torch.cuda.stream(stream):
             for c0, c1 in bounds:
-                f = audio2features_batch(audio[c0:c1].to(dev, non_blocking=True), sr, fps, deferred_checks=checks)
-                pf = patch_features_batch(f)
+                f, pf = features_and_patch_inputs(audio[c0:c1].to(dev, non_blocking=True), sr, fps, deferred_checks=checks)
                 feats_chunks.append(f)
                 if latents is None:
                     latents = torch.empty(B, f.shape[1], palette.shape[1], palette.shape[2], dtype=torch.float32, device=dev)
@@ -420,8 +471,7 @@ def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, se
                     if fgraphs is not None and (c1 - c0) in fgraphs:
                         f, pf = fgraphs[c1 - c0].run(xd, deferred_checks=checks)
                     else:
-                        f = audio2features_batch(xd, sr, fps, deferred_checks=checks)
-                        pf = patch_features_batch(f)
+                        f, pf = features_and_patch_inputs(xd, sr, fps, deferred_checks=checks)
                     done = torch.cuda.Event()
                     done.record(fstream)
                     if not audio.is_cuda:
