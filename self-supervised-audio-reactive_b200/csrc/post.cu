@@ -28,8 +28,11 @@ __device__ __forceinline__ int pad_index(int v, int T, int radius, int mode) {
     return v;
 }
 
-constexpr int G_TPT = 4;  // consecutive time steps per thread (register sliding window)
-
+// TPT consecutive time steps per thread.  The taps travel through a circular register window (slot u holds tap i for
+// i = u mod TPT), so an input row costs one global load, one shared-memory tap read and TPT FMAs; every output still
+// accumulates its taps in ascending order, so the result does not depend on TPT.  TPT = 4 for the short kernels of the
+// [T, 59] smoothing, 16 for the long ones (sigma 80 of random/mir.py:14-22: 641 taps).
+template <int TPT>
 __global__ void gauss1d_kernel(const float* __restrict__ x, int T, long long inner, const float* __restrict__ w,
                                int radius, int mode, float* __restrict__ out) {
     extern __shared__ float ws[];
@@ -44,22 +47,27 @@ __global__ void gauss1d_kernel(const float* __restrict__ x, int T, long long inn
     const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const long long tb = gid / inner;
     const long long j = gid - tb * inner;
-    if (tb * G_TPT >= T) return;
-    const int t0 = (int)tb * G_TPT;
-    float acc[G_TPT];
+    if (tb * TPT >= T) return;
+    const int t0 = (int)tb * TPT;
+    float acc[TPT], wr[TPT];
 #pragma unroll
-    for (int o = 0; o < G_TPT; ++o) acc[o] = 0.f;
-    // input rows t0 - r .. t0 + G_TPT - 1 + r; row i contributes to output o with tap k = i - o (relative indices)
-    for (int i = 0; i < taps + G_TPT - 1; ++i) {
-        const float v = __ldg(xc + (long long)pad_index(t0 + i - radius, T, radius, mode) * inner + j);
+    for (int o = 0; o < TPT; ++o) acc[o] = 0.f, wr[o] = 0.f;
+    // input rows t0 - r .. t0 + TPT - 1 + r; row i contributes to output o with tap k = i - o (relative indices)
+    const int n_in = taps + TPT - 1;
+    for (int i0 = 0; i0 < n_in; i0 += TPT) {
 #pragma unroll
-        for (int o = 0; o < G_TPT; ++o) {
-            const int k = i - o;
-            if (k >= 0 && k < taps) acc[o] = fmaf(ws[k], v, acc[o]);
+        for (int u = 0; u < TPT; ++u) {
+            const int i = i0 + u;
+            if (i < n_in) {  // (uniform across the CTA)
+                const float v = __ldg(xc + (long long)pad_index(t0 + i - radius, T, radius, mode) * inner + j);
+                wr[u] = i < taps ? ws[i] : 0.f;  // tap i enters the window; taps below 0 / beyond the kernel are zeros
+#pragma unroll
+                for (int o = 0; o < TPT; ++o) acc[o] = fmaf(wr[(u - o + TPT) % TPT], v, acc[o]);
+            }
         }
     }
 #pragma unroll
-    for (int o = 0; o < G_TPT; ++o)
+    for (int o = 0; o < TPT; ++o)
         if (t0 + o < T) oc[(long long)(t0 + o) * inner + j] = acc[o];
 }
 
@@ -294,12 +302,15 @@ extern "C" int ssar_gauss1d(const float* x, int n_clips, int n_frames, long long
     SSAR_REQUIRE((2 * radius + 1) * sizeof(float) <= 200 * 1024, "gauss1d: kernel too long");
     SSAR_REQUIRE(n_clips <= 65535, "gauss1d: too many clips per launch");
     const int threads = 128;
-    const long long items = inner * ((n_frames + G_TPT - 1) / G_TPT);
+    // long kernels on enough rows: 16 outputs per thread (16 FMAs per loaded row instead of 4)
+    const int tpt = (radius >= 32 && inner * ((n_frames + 15) / 16) >= (long long)SSAR_NUM_SMS * threads) ? 16 : 4;
+    const long long items = inner * ((n_frames + tpt - 1) / tpt);
     SSAR_REQUIRE((items + threads - 1) / threads <= 0x7fffffffLL, "gauss1d: too many elements per launch");
     dim3 grid((unsigned)((items + threads - 1) / threads), 1, n_clips);
     const size_t smem = (2 * radius + 1) * sizeof(float);
-    if (smem > 48 * 1024) cudaFuncSetAttribute(gauss1d_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    gauss1d_kernel<<<grid, threads, smem, ST(stream)>>>(x, n_frames, inner, weights, radius, mode, out);
+    auto kern = tpt == 16 ? gauss1d_kernel<16> : gauss1d_kernel<4>;
+    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    kern<<<grid, threads, smem, ST(stream)>>>(x, n_frames, inner, weights, radius, mode, out);
     return ssar_launch_status("gauss1d");
 }
 

@@ -57,7 +57,7 @@ def test_audio2features_vs_golden():
     # envelope (reference noise floor), which moves the pulse by O(1e-3).  The kernel itself is exact given the same
     # envelope (test_plp_exact_given_envelope, 1e-5); through the chain the column is held to 1e-2.
     tol = {name: 2e-3 for name in FEATURE_NAMES}
-    tol["pulse"] = 1e-2
+    tol["pulse"] = 2e-3
     bad = {k: v for k, v in worst.items() if v > tol[k]}
     assert not bad, bad
     f = audio2features(x, 44100, 24)
@@ -152,7 +152,7 @@ def test_audio2features_short_clips_vs_golden():
         ref = g[f"features_raw_{secs}s"]
         assert tuple(raw.shape) == tuple(ref.shape) == (24 * secs, 59)
         worst = {n: rel_l2(raw[:, j], ref[:, j]) for j, n in enumerate(FEATURE_NAMES)}
-        bad = {k: v for k, v in worst.items() if v > (1e-2 if k == "pulse" else 2e-3)}
+        bad = {k: v for k, v in worst.items() if v > 2e-3}
         assert not bad, (secs, bad)
         f = audio2features(x, 44100, 24)
         keep = [j for j, n in enumerate(FEATURE_NAMES) if n != "pulse"]
@@ -183,10 +183,11 @@ def test_frames_dft_and_band_inverse_vs_torch():
     for n_fft, n in ((240, 240), (333, 333), (1008, 1008), (384, 500)):
         x = torch.randn(2, n, generator=gen)
         win = torch.hann_window(n_fft)
-        ref = torch.stft(x, n_fft, 1, window=win, center=True, pad_mode="reflect", return_complex=True)  # [B, F, n + 1]
-        F = n_fft // 2 + 1
-        got = ops.frames_dft(x.cuda(), n_fft, 1, n + 1, torch.hann_window)
-        assert tuple(got.shape) == (2, n + 1, F, 2)
+        ref = torch.stft(x, n_fft, 1, window=win, center=True, pad_mode="reflect", return_complex=True)  # [B, F, frames]
+        F, n_frames = n_fft // 2 + 1, 1 + n + 2 * (n_fft // 2) - n_fft  # an odd window gives n frames, an even one n + 1
+        assert ref.shape[2] == n_frames
+        got = ops.frames_dft(x.cuda(), n_fft, 1, n_frames, torch.hann_window)
+        assert tuple(got.shape) == (2, n_frames, F, 2)
         assert rel_l2(torch.view_as_complex(got.cpu()).transpose(1, 2).abs(), ref.abs()) < 1e-5
         assert rel_l2(torch.view_as_real(torch.view_as_complex(got.cpu()).transpose(1, 2)), torch.view_as_real(ref)) < 1e-5
         k_lo, k_hi = F // 5, F // 2
@@ -223,7 +224,7 @@ def test_pulse_argmax_flips_counted():
     assert rel_l2(env_gpu, env_ref) < 1e-3
     flips = int((kept_bins(env_gpu) != kept_bins(env_ref)).sum())
     print("plp arg-max flips on the golden clip:", flips, "of", len(env_ref) + 1)
-    assert flips <= 16
+    assert flips <= 2
     # and given the GPU envelope, the CUDA plp equals the oracle's arithmetic on that same envelope
     p_gpu = ops.plp_from_onset(env_gpu[None], sr)[0]
     G = dsp.stft(env_gpu.cpu(), 1024, 1)

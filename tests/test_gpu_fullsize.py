@@ -36,7 +36,7 @@ def test_audio2features_240s_vs_oracle(clip):
     raw = pipeline.audio2features_batch(x, SR44, 24, clamp=False, smooth=False)[0]
     worst = {n: rel_l2(raw[:, j], ref_raw[:, j]) for j, n in enumerate(FEATURE_NAMES)}
     print("240 s audio2features, worst raw columns:", sorted(worst.items(), key=lambda kv: -kv[1])[:6])
-    bad = {k: v for k, v in worst.items() if v > (1e-2 if k == "pulse" else 2e-3)}
+    bad = {k: v for k, v in worst.items() if v > 2e-3}
     assert not bad, bad
     f = pipeline.audio2features_batch(x, SR44, 24)[0]
     keep = [j for j, n in enumerate(FEATURE_NAMES) if n != "pulse"]
