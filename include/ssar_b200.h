@@ -471,6 +471,14 @@ int ssar_biquad_ss(const float* x, long long n_samples, long long stride_x, int 
                    void* stream);
 int ssar_rms_from_block_ss(const float* block_ss, long long n_blocks, int n_clips, int n_frames, float* out, void* stream);
 
+/* maua/maua/GAN/wrappers/stylegan2.py:193-210 make_noise_pyramid (normalize = 1) and the synthesizer's own resize of a
+ * mismatched noise input, :86-96 (normalize = 0): noise [n_frames, in_h, in_w] -> outs[l] [n_frames, heights[l], widths[l]]
+ * for l < n_layers <= 16, bicubic (torch.nn.functional.interpolate, mode="bicubic", align_corners=False); with
+ * normalize each frame of each layer is divided by its own unbiased standard deviation (noises.std((1, 2, 3))).
+ * heights / widths / outs: HOST arrays.  One launch for all layers.                                                 */
+int ssar_noise_pyramid(const float* noise, int n_frames, int in_h, int in_w, int n_layers, const int* heights,
+                       const int* widths, float* const* outs, int normalize, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,9 +1,10 @@
 """Oracle: the latent / noise builders of ssar/features/generate.py:155-230 and the per-song fixed decoder of
 ssar/optimize.py:103-142 (torch CPU, fp32).  TEST INFRASTRUCTURE ONLY.
 
-PARITY UNPINNED for this file: neither module can be imported here (generate.py loads a StyleGAN2 pickle and decord at
-import, optimize.py imports maua + matplotlib), so these are restatements of the cited lines; every primitive they call
-(gaussian_filter, clamp_*_percentile, normalize) is pinned to the reference in post.py.  Random draws and the mapped
+Neither module can be imported here (generate.py loads a StyleGAN2 pickle and decord at
+import, optimize.py imports maua + matplotlib), so these are restatements of the cited lines — PINNED since round 2 by
+tests/test_oracle_widened.py against fixtures made by compiling and running the reference's unmodified function text
+(tests/golden/ref_loader.py::exec_reference_defs).  Random draws and the mapped
 latents `ws` are arguments (the reference draws them with torch.randn / G.mapper)."""
 from __future__ import annotations
 

@@ -82,3 +82,35 @@ def retrieve_music_features(audio, sr):
     """random/mir.py:26 and :44 (tempo, beats and segmentations, :28-42, are inputs of `Patch` here)."""
     raw = {name: fn(audio, sr) for name, fn in AFEATFNS.items()}
     return {k: post.normalize(salience_weighted(post.gaussian_filter(af, 2))) for k, af in raw.items()}
+
+
+def audio2features_generate(audio, sr, clamp=True, smooth=True):
+    """ssar/features/generate.py:106-136: the generators' variant of audio2features — audio already at sr = 1024 * fps,
+    the multi-column features and the flatness pre-smoothed with sigma 10, pulse from the audio itself, clamp to the
+    per-column [q10, q97.5] (torch.quantile, linear), then sigma 2."""
+    harm, perc = dsp.harmonic(audio), dsp.percussive(audio)
+    g10 = lambda f: post.gaussian_filter(f, 10)
+    multi = [g10(dsp.mfcc(audio, sr)), g10(ocqt.chromagram(harm, sr)), g10(ocqt.tonnetz(harm, sr)),
+             g10(dsp.spectral_contrast(audio, sr))]
+    single = [
+        g10(dsp.spectral_flatness(audio, sr)),
+        dsp.onset_strength(perc, sr),
+        dsp.onset_strength(dsp.low_pass(perc, sr), sr),
+        dsp.onset_strength(dsp.mid_pass(perc, sr), sr),
+        dsp.onset_strength(dsp.high_pass(perc, sr), sr),
+        dsp.plp(audio, sr),
+        dsp.rms(harm, sr),
+        dsp.rms(dsp.low_pass(harm, sr), sr),
+        dsp.rms(dsp.mid_pass(harm, sr), sr),
+        dsp.rms(dsp.high_pass(harm, sr), sr),
+        drop_strength(audio, sr),
+        drop_strength(dsp.low_pass(audio, sr), sr),
+        drop_strength(dsp.mid_pass(audio, sr), sr),
+        drop_strength(dsp.high_pass(audio, sr), sr),
+    ]
+    feats = torch.cat(multi + [s.reshape(-1, 1) for s in single], dim=1)
+    if clamp:
+        feats = feats.clamp(torch.quantile(feats, q=0.1, dim=0), torch.quantile(feats, q=0.975, dim=0))
+    if smooth:
+        feats = post.gaussian_filter(feats, 2)
+    return feats

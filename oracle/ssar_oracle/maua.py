@@ -109,3 +109,14 @@ def tempo_loops(latents, n_frames, fps, tempo, type="spline"):
     """latent.py:96-103."""
     n_loops = round(n_frames / fps * (tempo / 4 / 60))
     return spline_loops(latents, n_frames, n_loops) if type == "spline" else slerp_loops(latents, n_frames, n_loops)
+
+
+def make_noise_pyramid(noise, sizes):
+    """maua/GAN/wrappers/stylegan2.py:193-210: noise [T, 1, H, W] -> one [T, 1, h, w] tensor per (h, w) in `sizes`
+    (the noise_const shapes of synthesis layers 1..9), bicubic (align_corners=False), each FRAME divided by its own
+    unbiased standard deviation."""
+    out = []
+    for h, w in sizes:
+        n = F.interpolate(noise, (h, w), mode="bicubic", align_corners=False)
+        out.append(n / n.std((1, 2, 3), keepdim=True))
+    return out

@@ -272,3 +272,56 @@ def fixed_decoder(latents, x, hidden_size, n_latent_split, noise_draws, sigma=5)
         z = gaussian_filter(noise_draws[i].transpose(1, 0), sigma).transpose(1, 0)
         noise.append(mu[..., None, None] + sig[..., None, None] * z)
     return lat, noise
+
+
+class LatentAugmenter:
+    """ssar/supervised/latent_augmenter.py:23-105 with the mapped-latent bank `ws` [num, W, L] as an argument (the
+    reference maps 16 384 random z through a StyleGAN2 checkpoint, :25-29).  Draws come from numpy's and Python's GLOBAL
+    generators in the reference's order (np.random.seed / random.seed reproduce a run).  `normalize` is
+    features/processing.py's (the module asks supervised/data.py for it, which does not define one)."""
+
+    FEAT_IDXS = {"chroma": (20, 32), "tonnetz": (32, 38), "onsets": (46, 47), "onsets_low": (47, 48), "onsets_mid": (48, 49),
+                 "onsets_high": (49, 50), "volume": (51, 52), "volume_low": (52, 53), "volume_mid": (53, 54),
+                 "volume_high": (54, 55), "volume_long": (55, 56), "volume_low_long": (56, 57),
+                 "volume_mid_long": (57, 58), "volume_high_long": (58, 59)}
+
+    def __init__(self, ws, n_patches):
+        self.ws, self.n_patches = ws, n_patches
+        self.num, self.nw = ws.shape[0], ws.shape[1]
+        self.feat_idxs = dict(self.FEAT_IDXS)  # the literal's repeated keys collapse (latent_augmenter.py:31-56)
+        self.feat_keys = list(self.feat_idxs)
+        self.single_dim = -12
+
+    def random_patch(self, feature):
+        import random
+
+        from .post import normalize
+
+        n_knots = np.random.randint(3, 12)  # evaluated before the call it is an argument of (:70-71)
+        latent = spline_loop_latents(self.ws[np.random.randint(0, self.num, n_knots)].to(feature), len(feature))
+        for _ in range(self.n_patches):
+            start, stop = self.feat_idxs[random.choice(self.feat_keys)]
+            if np.random.rand() > 0.5:
+                lay_start = np.random.randint(0, self.nw - 6)
+                lay_stop = np.random.randint(lay_start, self.nw)
+            else:
+                lay_start, lay_stop = 0, self.nw
+            if stop - start == 1:
+                lat = self.ws[np.random.randint(0, self.num, 1)].to(feature)
+                m = normalize(feature[:, start:stop, None])
+                latent[:, lay_start:lay_stop] *= 1 - m
+                latent[:, lay_start:lay_stop] += m * lat[:, lay_start:lay_stop]
+            else:
+                lats = self.ws[np.random.randint(0, self.num, stop - start)].to(feature)
+                m = normalize(feature[:, start:stop])
+                m = m / (m.sum(1, keepdim=True) + 1e-8)
+                patch_latent = torch.einsum("Atwl,Atwl->twl", m.permute(1, 0)[..., None, None], lats[:, None])
+                if np.random.rand() > 0.666:
+                    a, b = self.feat_idxs[random.choice(self.feat_keys[self.single_dim:])]
+                    im = normalize(feature[:, a:b, None])
+                    latent[:, lay_start:lay_stop] *= 1 - im
+                    latent[:, lay_start:lay_stop] += im * patch_latent[:, lay_start:lay_stop]
+                else:
+                    latent[:, lay_start:lay_stop] = patch_latent[:, lay_start:lay_stop]
+        offset = latent.mean(dim=(0, 1), keepdim=True)
+        return latent - offset, offset

@@ -14,6 +14,25 @@ from .processing import clamp_lower_percentile, clamp_peaks_percentile, gaussian
 FPS = 24  # generate.py:51
 
 
+def audio2features(audio, sr, clamp=True, smooth=True):
+    """generate.py:106-136: the generators' variant of audio2features.  audio [N] (or [B, N]) ALREADY at sr = 1024 * fps
+    -> [T, 59] (or [B, T, 59]): the multi-column features and the flatness pre-smoothed with sigma 10, pulse = plp(audio)
+    (not of the percussive part), clamp to each column's [q10, q97.5] (torch.quantile, linear), then sigma 2.  Same
+    kernels and the same shared passes as supervised/data.py's audio2features (pipeline.feature_chain)."""
+    from .. import pipeline
+
+    squeeze = audio.dim() == 1
+    x = audio[None] if squeeze else audio
+    raw = pipeline.feature_chain(x.float(), sr, want_a2f=True, want_mir=False, pulse_of="audio")["a2f"]
+    feats = torch.cat([ops.gauss1d(raw[:, :, :46].contiguous(), 10, "circular", batched=True), raw[:, :, 46:]], dim=2)
+    feats = feats.contiguous()
+    if clamp:
+        feats = ops.clamp_cols(feats, ops.col_quantile(feats, 0.1), ops.col_quantile(feats, 0.975))
+    if smooth:
+        feats = ops.gauss1d(feats, 2, "circular", batched=True)
+    return feats[0] if squeeze else feats
+
+
 def _chroma_weights(chroma, fps):
     """generate.py:159-164: smooth, clamp peaks (97) / lower (5), L1-normalise per frame."""
     c = gaussian_filter(chroma, fps / 24)

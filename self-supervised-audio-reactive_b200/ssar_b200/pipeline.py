@@ -94,7 +94,8 @@ def _cens_and_tonnetz(y: torch.Tensor, sr, hop: int, sync_free: bool):
     return cens, ops.tonnetz(cens)
 
 
-def feature_chain(x: torch.Tensor, sr, want_a2f: bool = True, want_mir: bool = False, sync_free: bool = False):
+def feature_chain(x: torch.Tensor, sr, want_a2f: bool = True, want_mir: bool = False, sync_free: bool = False,
+                  pulse_of: str = "perc"):
     """Every per-frame feature of a batch of clips x [B, N] that is ALREADY at sr = 1024 * fps (n_fft 2048, hop 1024):
 
       a2f: the 59 un-clamped, un-smoothed columns of supervised/data.py:64-99 -> [B, T, 59]
@@ -106,7 +107,8 @@ def feature_chain(x: torch.Tensor, sr, want_a2f: bool = True, want_mir: bool = F
     (T + 1 frames) together with magnitude (contrast), mel (mfcc), flatness and RMS of the first T frames; harmonic /
     percussive share the STFT and the medians; the three band filters share the 4 kHz high-pass.  The two paths differ in
     which signal the chroma features see: mir.py's chromagram(audio) = chroma_cens(harmonic(audio)), while data.py:68-69
-    passes audio_harm in, i.e. chroma_cens(harmonic(harmonic(audio))) — both are built when both are wanted."""
+    passes audio_harm in, i.e. chroma_cens(harmonic(harmonic(audio))) — both are built when both are wanted.
+    pulse_of: "perc" = plp(audio_perc) (data.py:89), "audio" = plp(audio) (features/generate.py:123)."""
     B, N = x.shape
     n_fft, hop = 2048, 1024
     T = N // hop
@@ -123,7 +125,9 @@ def feature_chain(x: torch.Tensor, sr, want_a2f: bool = True, want_mir: bool = F
     # --- harmonic / percussive separation
     harm, perc = hpss_pair(x, D=fa["complex"])
     del fa["complex"], fa["spec"]
-    on, on_med = onset_pair(perc, sr, hop, n_fft, want_median=want_a2f)
+    on, on_med = onset_pair(perc, sr, hop, n_fft, want_median=want_a2f and pulse_of == "perc")
+    if want_a2f and pulse_of != "perc":
+        on_med = onset_pair(x, sr, hop, n_fft, want_median=True)[1]
 
     out = {}
     cens1 = ton1 = None

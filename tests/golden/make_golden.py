@@ -262,7 +262,118 @@ def g_maua(ref):
     save("maua", **out)
 
 
-GROUPS = {"mir": g_mir, "a2f_short": g_a2f_short, "maua": g_maua, "traj": g_traj, "a2f": g_a2f, "chroma": g_chroma, "post": g_post, "spectral": g_spectral, "frame_features": g_frame_features, "hpss_filters": g_hpss_filters}
+def augmenter_ws():
+    """The mapped-latent bank a LatentAugmenter holds (16 384 rows): a seeded [256, 18, 512] base repeated 64 times."""
+    return torch.randn(256, 18, 512, generator=torch.Generator("cpu").manual_seed(4242)).repeat(64, 1, 1)
+
+
+def g_widened(ref):
+    """Functions whose MODULES cannot be imported (a GAN pickle / decord / maua / matplotlib at import time): their
+    unmodified source text is compiled straight from the reference files (ref_loader.exec_reference_defs) and run with
+    the reference's own feature functions plus stand-ins for what is off the path (random audio picker, GAN mapper,
+    get_video).  generate.py:106-136 audio2features variant, :155-230 builders; optimize.py:103-142 decoder;
+    supervised/latent_augmenter.py:14-105; maua StyleGAN2 wrapper make_noise_pyramid :193-210."""
+    import random
+    import types
+
+    from ref_loader import TorchOnCpu, exec_reference_defs, exec_reference_methods
+
+    R = projection_matrix()
+    out = {}
+    # ---- generate.py: audio2features variant + builders on a 16 s clip (DUR = 16, generate.py:52)
+    n = SR * 16
+    audio = synth_clip(n, SR, 18)
+    _, _, palette = synth_patch_inputs(8, 1)
+    tcpu = TorchOnCpu()
+    ns = dict(torch=tcpu, np=np, FPS=24, DUR=16, N=16 * 24, SR=SR,
+              harmonic=ref.audio.harmonic, percussive=ref.audio.percussive, mfcc=ref.audio.mfcc,
+              chromagram=ref.audio.chromagram, tonnetz=ref.audio.tonnetz, spectral_contrast=ref.audio.spectral_contrast,
+              spectral_flatness=ref.audio.spectral_flatness, rms=ref.audio.rms, drop_strength=ref.audio.drop_strength,
+              onsets=ref.audio.onsets, onset_strength=ref.beat.onset_strength, plp=ref.beat.plp,
+              low_pass=ref.processing.low_pass, mid_pass=ref.processing.mid_pass, high_pass=ref.processing.high_pass,
+              gaussian_filter=ref.data.gaussian_filter, normalize=ref.processing.normalize,
+              clamp_peaks_percentile=ref.processing.clamp_peaks_percentile,
+              clamp_lower_percentile=ref.processing.clamp_lower_percentile,
+              get_random_audio=lambda: (audio, SR), get_video=lambda latents, noise: (latents, noise),
+              G=types.SimpleNamespace(mapper=lambda z: palette[: len(z)]))
+    exec_reference_defs("ssar/features/generate.py", ["audio2features", "high_chroma_correlation", "high_onset_correlation",
+                                                      "high_both_correlation"], ns)
+    out["gen_n"], out["gen_clip_index"] = n, 18
+    out["gen_a2f_raw"] = ns["audio2features"](audio, SR, clamp=False, smooth=False)
+    out["gen_a2f"] = ns["audio2features"](audio, SR)
+    out["gen_chroma"], out["gen_onsets"] = ref.audio.chromagram(audio, SR), ref.audio.onsets(audio, SR)
+    for name, k, size in (("high_chroma_correlation", 12, 32), ("high_onset_correlation", 2, 64), ("high_both_correlation", 14, 64)):
+        torch.manual_seed(100 + k)  # the test repeats: manual_seed, randn(k, 512) (the mapper's z), randn(T, 1, s, s)
+        _, _, (lat, noise), _ = ns[name]()
+        out[f"{name}_proj"], out[f"{name}_noise"] = lat @ R, noise[::16, :, ::4, ::4]
+        out[f"{name}_noise_std"] = noise.std(dim=(1, 2, 3))
+    # ---- optimize.py FixedLatentNoiseDecoder
+    T = 720
+    ns = dict(torch=torch, gaussian_filter=ref.processing.gaussian_filter)
+    exec_reference_defs("ssar/optimize.py", ["FixedLatentNoiseDecoder"], ns)
+    x = synth_features(T, 27 + 8, 31)
+    dec = ns["FixedLatentNoiseDecoder"](palette_27(), 3, 3, 3)
+    torch.manual_seed(0)  # the test repeats: manual_seed(0), randn(T, s, s) for s = 4, 8, 16, 32
+    lat, noise = dec.forward(x)
+    out["opt_proj"] = lat @ R
+    for i, nz in enumerate(noise):
+        out[f"opt_noise_{i}"] = nz[:, ::2, ::2] if nz.shape[-1] > 8 else nz
+    # ---- maua StyleGAN2Synthesizer.make_noise_pyramid (+ the synthesizer's own resize of mismatched noise, :86-96)
+    sizes = [4, 8, 8, 16, 16, 32, 32, 64, 64, 128, 128]  # noise_const sizes of the first 11 synthesis layers
+    bs = []
+    names = []
+    for li, sz in enumerate(sizes):
+        b, c = (li + 1) // 2, "conv1" if li % 2 == 0 else "conv0"
+        while len(bs) <= b:
+            bs.append(types.SimpleNamespace())
+        setattr(bs[b], c, types.SimpleNamespace(noise_const=torch.empty(sz, sz)))
+        names.append(f"bs.{b}.{c}")
+    fake = types.SimpleNamespace(layer_names=names, G_synth=types.SimpleNamespace(bs=bs))
+    ns = exec_reference_methods("maua/maua/GAN/wrappers/stylegan2.py", "StyleGAN2Synthesizer", ["make_noise_pyramid"],
+                                dict(torch=torch))
+    for tag, hw in (("16", (16, 16)), ("32", (32, 32)), ("64", (64, 64)), ("12x20", (12, 20))):
+        nz = torch.randn(40, 1, *hw, generator=torch.Generator("cpu").manual_seed(77))
+        pyr = ns["make_noise_pyramid"](fake, nz)
+        assert list(pyr) == [f"noise{l}" for l in range(9)]
+        for l in range(9):
+            out[f"pyr{tag}_{l}"] = pyr[f"noise{l}"][::8] if pyr[f"noise{l}"].shape[-1] <= 32 else pyr[f"noise{l}"][::8, :, ::2, ::2]
+    nz = torch.randn(6, 1, 16, 16, generator=torch.Generator("cpu").manual_seed(78))
+    out["resize_16_to_64"] = torch.nn.functional.interpolate(nz, (64, 64), mode="bicubic", align_corners=False)  # stylegan2.py:95
+    # ---- supervised/latent_augmenter.py: spline_loop_latents twin + LatentAugmenter.random_patch
+    from ref_loader import _NaturalCubicSpline, _natural_cubic_spline_coeffs
+
+    ws = augmenter_ws()
+
+    class Mapper:  # StyleGAN2Mapper stand-in: the bank is an input here
+        def __init__(self, *a, **k):
+            pass
+
+        def eval(self):
+            return self
+
+        def forward(self, latent_z):
+            return ws
+
+    ns = dict(torch=torch, np=np, random=random, NaturalCubicSpline=_NaturalCubicSpline,
+              natural_cubic_spline_coeffs=_natural_cubic_spline_coeffs, normalize=ref.processing.normalize,
+              StyleGAN2Mapper=Mapper)
+    exec_reference_defs("ssar/supervised/latent_augmenter.py", ["spline_loop_latents", "LatentAugmenter"], ns)
+    feats = synth_features(384, 59, 33)
+    for seed in (0, 1, 2, 3):
+        la = ns["LatentAugmenter"]("ckpt", n_patches=5 if seed < 3 else 9)
+        np.random.seed(seed)
+        random.seed(seed)
+        res, off = la.random_patch(feats.clone())
+        out[f"aug_res_proj_{seed}"], out[f"aug_off_{seed}"] = res @ R, off
+        out[f"aug_res_frames_{seed}"] = res[::128]
+    save("widened", **out)
+
+
+def palette_27():
+    return synth_patch_inputs(8, 1)[2][:27]
+
+
+GROUPS = {"widened": g_widened, "mir": g_mir, "a2f_short": g_a2f_short, "maua": g_maua, "traj": g_traj, "a2f": g_a2f, "chroma": g_chroma, "post": g_post, "spectral": g_spectral, "frame_features": g_frame_features, "hpss_filters": g_hpss_filters}
 
 if __name__ == "__main__":
     torch.manual_seed(0)

@@ -330,3 +330,54 @@ def load_maua_audioreactive():
     ns.signal = importlib.import_module("maua_ar.signal")
     ns.latent = importlib.import_module("maua_ar.latent")
     return ns
+
+
+def exec_reference_defs(relpath: str, names, namespace: dict) -> dict:
+    """Runs the UNMODIFIED source text of the named top-level functions / classes of a reference file whose module
+    cannot be imported (`ssar/features/generate.py` loads a GAN pickle and decord at import, `ssar/optimize.py` imports
+    maua + matplotlib, `supervised/latent_augmenter.py` imports a name its sibling lacks, the maua StyleGAN2 wrapper
+    imports the NVIDIA ops): the file is parsed with `ast`, only the requested definitions are compiled (with the
+    reference's own file name and line numbers) and executed in `namespace`, which the caller fills with the reference's
+    own imported functions (`load_reference()`) and stand-ins for the globals that are outside the path (the GAN
+    mapper, the random audio picker, ...).  Nothing is copied: the source is read from `/root/reference` at run time."""
+    import ast
+
+    path = REFERENCE_ROOT / relpath
+    tree = ast.parse(path.read_text(), filename=str(path))
+    wanted = [n for n in tree.body if isinstance(n, (ast.FunctionDef, ast.ClassDef)) and n.name in set(names)]
+    missing = set(names) - {n.name for n in wanted}
+    if missing:
+        raise KeyError(f"{relpath}: no top-level definition named {sorted(missing)}")
+    mod = ast.Module(body=wanted, type_ignores=[])
+    exec(compile(mod, str(path), "exec"), namespace)
+    return namespace
+
+
+def exec_reference_methods(relpath: str, class_name: str, methods, namespace: dict) -> dict:
+    """Like `exec_reference_defs` for methods of a class: the named methods are compiled as plain functions (taking
+    `self`) — for classes whose constructor needs what is not here (a StyleGAN2 checkpoint)."""
+    import ast
+
+    path = REFERENCE_ROOT / relpath
+    tree = ast.parse(path.read_text(), filename=str(path))
+    cls = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == class_name)
+    wanted = [n for n in cls.body if isinstance(n, ast.FunctionDef) and n.name in set(methods)]
+    missing = set(methods) - {n.name for n in wanted}
+    if missing:
+        raise KeyError(f"{relpath}:{class_name}: no method named {sorted(missing)}")
+    exec(compile(ast.Module(body=wanted, type_ignores=[]), str(path), "exec"), namespace)
+    return namespace
+
+
+class TorchOnCpu:
+    """`torch` as seen by reference code that asks for device="cuda" in its draws (generate.py:166,171,...): the same
+    module, with the device keyword of the factory functions dropped so the unmodified text runs on the CPU."""
+
+    def __getattr__(self, k):
+        v = getattr(torch, k)
+        if k in ("randn", "rand", "zeros", "ones", "empty", "tensor", "arange", "linspace", "randint"):
+            def f(*a, **kw):
+                kw.pop("device", None)
+                return v(*a, **kw)
+            return f
+        return v
