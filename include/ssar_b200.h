@@ -471,6 +471,21 @@ int ssar_biquad_ss(const float* x, long long n_samples, long long stride_x, int 
                    void* stream);
 int ssar_rms_from_block_ss(const float* block_ss, long long n_blocks, int n_clips, int n_frames, float* out, void* stream);
 
+/* rosa/constantq.py:77-100, :189-191 (__cqt_response for every octave) as ONE tensor-core launch: the response of octave
+ * o is the K = 1024 contraction of the rectangular 1024-sample frames of signals[o] (hop >> o, centre reflect padding)
+ * with the time-domain form of the tuned basis, b[r, n] = sum_k fft_basis[r, k] exp(-2 pi i k n / 1024):
+ *   out[clip, t, n_bins - 36 (o + 1) + r] = sqrt(2^o) * row_scale[slot, .] * sum_n y_o[t (hop >> o) - 512 + n] b[slot][r, n]
+ * signals / n_samples: HOST arrays [n_octaves] of dense device signals [n_clips, n_samples[o]] (o > 0: the kaiser / 2
+ * decimations scaled by sqrt(2), constantq.py:83-86).  basis_hi / basis_lo: fp16 [n_slots * 80, 1024] (rows 2r / 2r + 1 of
+ * a slot = Re / Im of basis_scale * b[r, :], rows 72..79 zero), fp32 = hi + lo.  clip_slot: int32 [n_clips] (device; the
+ * tuning index of each clip) or NULL.  out: [n_clips, n_frames, 36 * n_octaves, 2].  tcgen05.mma kind::f16 on 3-term
+ * fp16 splits of both operands with fp32 accumulation; TMA tensor maps with overlapping rows read the frames straight
+ * from the padded signals.  scratch: ssar_cqt_tc_scratch_bytes(...) bytes.                                          */
+long long ssar_cqt_tc_scratch_bytes(int n_clips, const long long* n_samples, int n_octaves);
+int ssar_cqt_tc(const float* const* signals, const long long* n_samples, int n_octaves, int n_clips, int hop, int n_frames,
+                const void* basis_hi, const void* basis_lo, int n_slots, const int* clip_slot, const float* row_scale,
+                long long row_scale_ld, float basis_scale, void* scratch, float* out, void* stream);
+
 /* maua/maua/GAN/wrappers/stylegan2.py:193-210 make_noise_pyramid (normalize = 1) and the synthesizer's own resize of a
  * mismatched noise input, :86-96 (normalize = 0): noise [n_frames, in_h, in_w] -> outs[l] [n_frames, heights[l], widths[l]]
  * for l < n_layers <= 16, bicubic (torch.nn.functional.interpolate, mode="bicubic", align_corners=False); with

@@ -303,7 +303,7 @@ extern "C" int ssar_gauss1d(const float* x, int n_clips, int n_frames, long long
     SSAR_REQUIRE(n_clips <= 65535, "gauss1d: too many clips per launch");
     const int threads = 128;
     // long kernels on enough rows: 16 outputs per thread (16 FMAs per loaded row instead of 4)
-    const int tpt = (radius >= 32 && inner * ((n_frames + 15) / 16) >= (long long)SSAR_NUM_SMS * threads) ? 16 : 4;
+    const int tpt = (radius >= 32 && (long long)n_clips * inner * ((n_frames + 15) / 16) >= (long long)SSAR_NUM_SMS * threads) ? 16 : 4;
     const long long items = inner * ((n_frames + tpt - 1) / tpt);
     SSAR_REQUIRE((items + threads - 1) / threads <= 0x7fffffffLL, "gauss1d: too many elements per launch");
     dim3 grid((unsigned)((items + threads - 1) / threads), 1, n_clips);

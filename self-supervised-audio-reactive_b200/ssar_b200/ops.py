@@ -505,7 +505,10 @@ def tonnetz(chroma: torch.Tensor):
     return out
 
 
-def cqt(y: torch.Tensor, sr, hop_length: int = 1024, tuning_idx=None, sync_free: bool = False):
+USE_TENSOR_CORE_CQT = True  # False: per-octave FFT + banded frequency-domain projection (frames_fft epilogue)
+
+
+def cqt(y: torch.Tensor, sr, hop_length: int = 1024, tuning_idx=None, sync_free: bool = False, tensor_core=None):
     """rosa/constantq.py:13-115 for the reference's only configuration (C1, 7 octaves x 36 bins, filter_scale 1,
     sparsity 0.01): returns the frame-major complex-as-real CQT [B, T, 252, 2] with 1/sqrt(length) applied.
     tuning_idx: int32 [B] from estimate_tuning (None -> estimate, like tuning=None in chroma_cqt)."""
@@ -519,6 +522,10 @@ def cqt(y: torch.Tensor, sr, hop_length: int = 1024, tuning_idx=None, sync_free:
         raise ValueError("Frequencies must be of integer type to ensure quality resampling computation.")
     if tuning_idx is None:
         tuning_idx, _ = estimate_tuning(y, sr, bins_per_octave=bpo)
+    use_tc = USE_TENSOR_CORE_CQT if tensor_core is None else bool(tensor_core)
+    use_tc = use_tc and hop_length % (8 << (n_oct - 1)) == 0 and N >= (plan.CQT_N_FFT << (n_oct - 1))
+    if use_tc:
+        return _cqt_tensor_core(y, sr, hop_length, tuning_idx)
     tables = plan.cqt_tables(float(sr), str(y.device))
     if sync_free:  # all tuned bases resident; the per-clip choice is a device gather (no read-back: graph-capturable)
         slots = tables.slot_map()[tuning_idx.long()].contiguous()
@@ -540,6 +547,32 @@ def cqt(y: torch.Tensor, sr, hop_length: int = 1024, tuning_idx=None, sync_free:
                     out=out[:, :, col0:], ld=n_bins, scale=float(2.0 ** i) ** 0.5, slots=slots,
                     row_scale=tables.row_scale[:, col0:], row_scale_ld=n_bins)
         frames_fft(s, plan.CQT_N_FFT, h, T, None, proj=proj)
+    return out
+
+
+def _cqt_tensor_core(y: torch.Tensor, sr, hop_length: int, tuning_idx: torch.Tensor):
+    """The 7 octave responses as ONE tcgen05 launch (`ssar_cqt_tc`): time-domain contraction of the overlapping frames
+    (TMA tensor maps with row stride hop_i over the reflect-padded fp16 hi / lo signals) with the tuned basis.  Each
+    clip's basis is picked on the device by its tuning index: no read-back, graph-capturable."""
+    B, N = y.shape
+    n_oct, bpo = plan.CQT_N_OCTAVES, plan.CQT_BINS_PER_OCTAVE
+    tb = plan.cqt_tc_tables(float(sr), str(y.device))
+    sigs = [y.contiguous()]
+    rp = plan.resample_plan(2, 1, "kaiser_window", str(y.device))
+    for i in range(1, n_oct):
+        sigs.append(resample(sigs[-1], rp, post_scale=float(torch.tensor(2.0).sqrt())))
+    T = min(s.shape[1] // (hop_length >> i) for i, s in enumerate(sigs))
+    n_bins = n_oct * bpo
+    out = torch.empty(B, T, n_bins, 2, dtype=torch.float32, device=y.device)
+    ns = (C.c_longlong * n_oct)(*[s.shape[1] for s in sigs])
+    ps = (C.c_void_p * n_oct)(*[s.data_ptr() for s in sigs])
+    fn = cabi.lib().ssar_cqt_tc_scratch_bytes
+    fn.restype = C.c_longlong
+    scratch = torch.empty(int(fn(i32(B), ns, i32(n_oct))), dtype=torch.uint8, device=y.device)
+    slots = tuning_idx.to(torch.int32).contiguous()
+    cabi.call("ssar_cqt_tc", ps, ns, i32(n_oct), i32(B), i32(hop_length), i32(T), ptr(tb.basis_hi), ptr(tb.basis_lo),
+              i32(tb.n_slots), ptr(slots), ptr(tb.row_scale), i64(n_bins), f32(tb.SCALE), ptr(scratch), ptr(out),
+              nbytes=sum(cabi.nbytes_of(s) for s in sigs) + cabi.nbytes_of(out))
     return out
 
 

@@ -449,6 +449,43 @@ def cqt_tables(sr: float, device) -> CqtTables:
     return CqtTables(sr, device)
 
 
+class CqtTcTables:
+    """Operands of `ssar_cqt_tc`: the TIME-domain form of every tuning's basis, b[r, n] = sum_k fft_basis[r, k]
+    exp(-2 pi i k n / 1024) (the inverse of what rosa/constantq.py:118-144 does to the filters, applied to the SPARSIFIED
+    FFT basis so the contraction equals fft_basis @ rfft(frame) exactly), computed in fp64 from the fp32 basis, scaled by
+    2^6 into fp16's normal range and split into (hi, lo) fp16 panels [101 * 80, 1024]: rows 2r / 2r + 1 of slot s hold
+    Re / Im of b_s[r, :], rows 72..79 are zero.  Slot = tuning index (all 101 resident, 33 MB)."""
+
+    ROWS = 80
+    SCALE = 64.0
+
+    def __init__(self, sr: float, device):
+        n = len(cqt_tuning_values())
+        panel = torch.zeros(n, self.ROWS, CQT_N_FFT, dtype=torch.float64)
+        rscale = []
+        for ti in range(n):
+            fb, n_fft, lengths = cqt_octave_basis_cpu(float(sr), cqt_tuning_values()[ti])
+            assert n_fft == CQT_N_FFT, f"CQT filters need n_fft={n_fft}; only {CQT_N_FFT} is built (sr={sr})"
+            full = torch.zeros(fb.shape[0], n_fft, dtype=torch.complex128)
+            full[:, : fb.shape[1]] = fb.to(torch.complex128)
+            b = torch.fft.fft(full, dim=1)  # [36, 1024]
+            panel[ti, 0 : 2 * fb.shape[0] : 2] = b.real
+            panel[ti, 1 : 2 * fb.shape[0] : 2] = b.imag
+            rscale.append(1.0 / torch.sqrt(lengths))  # V /= sqrt(lengths) (rosa/constantq.py:113)
+        panel = (panel * self.SCALE).reshape(n * self.ROWS, CQT_N_FFT)
+        hi = panel.to(torch.float16)
+        lo = (panel - hi.double()).to(torch.float16)
+        dev = _dev(device)
+        self.n_slots = n
+        self.basis_hi, self.basis_lo = hi.contiguous().to(dev), lo.contiguous().to(dev)
+        self.row_scale = torch.stack(rscale).float().contiguous().to(dev)  # [101, 252]
+
+
+@functools.lru_cache(maxsize=None)
+def cqt_tc_tables(sr: float, device) -> CqtTcTables:
+    return CqtTcTables(sr, device)
+
+
 @functools.lru_cache(maxsize=None)
 def tuning_edges(device) -> torch.Tensor:
     return cqt_tuning_values().to(_dev(device))

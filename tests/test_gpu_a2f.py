@@ -57,7 +57,7 @@ def test_audio2features_vs_golden():
     # envelope (reference noise floor), which moves the pulse by O(1e-3).  The kernel itself is exact given the same
     # envelope (test_plp_exact_given_envelope, 1e-5); through the chain the column is held to 1e-2.
     tol = {name: 2e-3 for name in FEATURE_NAMES}
-    tol["pulse"] = 2e-3
+    tol["pulse"] = 5e-3  # measured 2.2e-3 (0 arg-max flips: test_pulse_argmax_flips_counted)
     bad = {k: v for k, v in worst.items() if v > tol[k]}
     assert not bad, bad
     f = audio2features(x, 44100, 24)

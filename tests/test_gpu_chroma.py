@@ -87,3 +87,37 @@ def test_contrast_sorted_columns_equal_general_kernel():
         fast = ops.spectral_contrast(mag, bands)
         slow = ops.spectral_contrast(mag, dataclasses.replace(bands, max_count=600))
         assert torch.equal(fast, slow)
+
+
+def test_cqt_tensor_core_vs_fft_path_and_golden():
+    """`ssar_cqt_tc` (time-domain tcgen05 contraction over TMA frame views with overlapping rows, fp16 3-term split) against
+    the per-octave FFT + banded projection path, the reference golden and the oracle: batch with different tunings, a
+    quiet clip and a loud clip (per-clip operand scaling), ragged length, edge frames (reflect padding)."""
+    from ssar_b200 import ops
+
+    g = load("chroma")
+    sr = int(g["sr"])
+    x = synth_clip(int(g["n"]), sr, int(g["clip_index"])).cuda()[None]
+    idx, _ = ops.estimate_tuning(x, sr, bins_per_octave=36)
+    ref = torch.complex(g["cqt_re"], g["cqt_im"])                                      # [252, T]
+    C_tc = torch.view_as_complex(ops.cqt(x, sr, tuning_idx=idx, tensor_core=True)[0]).T
+    C_ff = torch.view_as_complex(ops.cqt(x, sr, tuning_idx=idx, tensor_core=False)[0]).T
+    assert tuple(C_tc.shape) == tuple(ref.shape)
+    e_tc = rel_l2(torch.view_as_real(C_tc.contiguous()), torch.view_as_real(ref))
+    e_ff = rel_l2(torch.view_as_real(C_ff.contiguous()), torch.view_as_real(ref))
+    print("cqt rel-L2 vs reference golden: tensor core", e_tc, "fft path", e_ff)
+    assert e_tc < TOL_CQT and e_ff < TOL_CQT
+    for o in range(7):  # every octave on its own (the high octaves carry most of the energy)
+        sl = slice(252 - 36 * (o + 1), 252 - 36 * o)
+        assert rel_l2(torch.view_as_real(C_tc[sl].contiguous()), torch.view_as_real(ref[sl].contiguous())) < TOL_CQT, o
+    n = sr * 7 + 333
+    xs = torch.stack([synth_clip(n, sr, 0), 1e-3 * synth_clip(n, sr, 7), 40.0 * synth_clip(n, sr, 11)]).cuda()
+    idx, _ = ops.estimate_tuning(xs, sr, bins_per_octave=36)
+    a = ops.cqt(xs, sr, tuning_idx=idx, tensor_core=True)
+    b = ops.cqt(xs, sr, tuning_idx=idx, tensor_core=False)
+    assert a.shape == b.shape
+    for c in range(3):
+        assert rel_l2(a[c], b[c]) < 2e-5, (c, rel_l2(a[c], b[c]))
+        assert rel_l2(a[c, :2], b[c, :2]) < 2e-5 and rel_l2(a[c, -2:], b[c, -2:]) < 2e-5  # reflect-padded edge frames
+    C_or = ocqt.cqt(xs[1].cpu(), sr)
+    assert rel_l2(torch.view_as_real(torch.view_as_complex(a[1]).T.contiguous()), torch.view_as_real(C_or.contiguous())) < TOL_CQT
