@@ -59,14 +59,24 @@ __global__ void cqt_amax_kernel(const float* __restrict__ x, long long n, uint32
     const int clip = blockIdx.y;
     const float* xc = x + (long long)clip * n;
     float m = 0.f;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-        m = fmaxf(m, fabsf(__ldg(xc + i)));
+    const long long head = min(n, (long long)((4 - ((reinterpret_cast<uintptr_t>(xc) >> 2) & 3)) & 3));  // to 16-byte alignment
+    const long long n4 = (n - head) >> 2;
+    const float4* __restrict__ x4 = reinterpret_cast<const float4*>(xc + head);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+        const float4 v = __ldg(x4 + i);
+        m = fmaxf(fmaxf(m, fmaxf(fabsf(v.x), fabsf(v.y))), fmaxf(fabsf(v.z), fabsf(v.w)));
+    }
+    if (blockIdx.x == 0 && threadIdx.x < 8) {  // the unaligned head and the tail
+        const long long i = threadIdx.x < 4 ? threadIdx.x : head + 4 * n4 + (threadIdx.x - 4);
+        if ((threadIdx.x < 4 && i < head) || (threadIdx.x >= 4 && i < n)) m = fmaxf(m, fabsf(__ldg(xc + i)));
+    }
     m = warp_max(m);
     if ((threadIdx.x & 31) == 0 && __float_as_uint(m) > __ldcg(amax + clip)) atomicMax(amax + clip, __float_as_uint(m));
 }
 
 // y_i [clip, n] fp32 -> hi / lo fp16 [clip, padded]: sample j of a row is y_i[reflect(j - 512)] * scale (zeros beyond
-// n + 1024), i.e. torch.stft's centre padding baked in, so frame t starts at row offset t * hop_i
+// n + 1024), i.e. torch.stft's centre padding baked in, so frame t starts at row offset t * hop_i.
+// Four samples per thread (64-bit stores); the interior takes a path without the reflection arithmetic.
 __global__ void cqt_split_kernel(const CqtOctaves oc, int n_clips, const uint32_t* __restrict__ amax,
                                  __half* __restrict__ hi, __half* __restrict__ lo) {
     const int o = blockIdx.z, clip = blockIdx.y;
@@ -75,18 +85,26 @@ __global__ void cqt_split_kernel(const CqtOctaves oc, int n_clips, const uint32_
     const float s = clip_scale(__ldg(amax + clip));
     __half* h = hi + oc.offset[o] + (long long)clip * lp;
     __half* l = lo + oc.offset[o] + (long long)clip * lp;
-    // two samples per thread: 32-bit stores
-    for (long long j2 = (long long)blockIdx.x * blockDim.x + threadIdx.x; 2 * j2 < lp; j2 += (long long)gridDim.x * blockDim.x) {
-        __half hh[2], ll[2];
+    constexpr int HALF = CQ_NFFT / 2;
+    const long long lp4 = lp >> 2;  // padded rows are multiples of 1024 samples
+    for (long long j4 = (long long)blockIdx.x * blockDim.x + threadIdx.x; j4 < lp4; j4 += (long long)gridDim.x * blockDim.x) {
+        const long long j = 4 * j4;
+        float v[4];
+        if (j >= HALF && j + 3 < n + HALF) {
+            const float* p = src + (j - HALF);
 #pragma unroll
-        for (int u = 0; u < 2; ++u) {
-            const long long j = 2 * j2 + u;
-            float v = 0.f;
-            if (j < n + CQ_NFFT) v = __ldg(src + ssar_reflect(j - CQ_NFFT / 2, n)) * s;
-            split_half(v, hh[u], ll[u]);
+            for (int u = 0; u < 4; ++u) v[u] = __ldg(p + u) * s;
+        } else {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) v[u] = (j + u < n + CQ_NFFT) ? __ldg(src + ssar_reflect(j + u - HALF, n)) * s : 0.f;
         }
-        *reinterpret_cast<__half2*>(h + 2 * j2) = __halves2half2(hh[0], hh[1]);
-        *reinterpret_cast<__half2*>(l + 2 * j2) = __halves2half2(ll[0], ll[1]);
+        __half hh[4], ll[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) split_half(v[u], hh[u], ll[u]);
+        __half2 h01 = __halves2half2(hh[0], hh[1]), h23 = __halves2half2(hh[2], hh[3]);
+        __half2 l01 = __halves2half2(ll[0], ll[1]), l23 = __halves2half2(ll[2], ll[3]);
+        *reinterpret_cast<uint2*>(h + j) = make_uint2(*reinterpret_cast<uint32_t*>(&h01), *reinterpret_cast<uint32_t*>(&h23));
+        *reinterpret_cast<uint2*>(l + j) = make_uint2(*reinterpret_cast<uint32_t*>(&l01), *reinterpret_cast<uint32_t*>(&l23));
     }
 }
 
@@ -288,10 +306,10 @@ extern "C" int ssar_cqt_tc(const float* const* signals, const long long* n_sampl
     }
     {
         int gx = ssar_div_up(n_samples[0], 256 * 16);
-        if (gx > SSAR_NUM_SMS * 4) gx = SSAR_NUM_SMS * 4;
+        if (gx > SSAR_NUM_SMS * 2) gx = SSAR_NUM_SMS * 2;
         cqt_amax_kernel<<<dim3(gx, n_clips), 256, 0, st>>>(signals[0], n_samples[0], amax);
-        int sx = ssar_div_up(oc.padded[0] / 2, 256 * 4);
-        if (sx > SSAR_NUM_SMS * 4) sx = SSAR_NUM_SMS * 4;
+        int sx = ssar_div_up(oc.padded[0] / 4, 256);
+        if (sx > SSAR_NUM_SMS * 8) sx = SSAR_NUM_SMS * 8;
         cqt_split_kernel<<<dim3(sx, n_clips, n_octaves), 256, 0, st>>>(oc, n_clips, amax, hi, lo);
     }
     EncodeTiledFn enc = get_encode_fn();
