@@ -218,6 +218,61 @@ def run_reference(args, rank):
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
+def time_cfg4(dev, palette, segs, T, rng_device):
+    """configs[3]: (a) noise delivery of one Patch(seed 42): every `forward(i, 32)` batch of all 17 layers over the 5760
+    frames at downscale 4 and 1, CUDA events around the whole sweep (after one warm-up sweep of the first 4 batches),
+    GB/s against 4 * sum(H * W) bytes per frame written; (b) FixedLatentNoiseDecoder(latents [9, 18, 512], H 3, S 3,
+    n 4) on [1, 5760, 17] envelopes -> latents [1, 5760, 18, 512] + noise 4..32."""
+    from ssar_b200.models.latent_n_noise2 import FixedLatentNoiseDecoder
+    from ssar_b200.random.patch import Patch
+    from ssar_b200.synth import synth_features, synth_patch_inputs
+
+    peak, _ = measured_peaks()
+    feats, _, _ = synth_patch_inputs(T, 0)
+    feats = {k: v.to(dev) for k, v in feats.items()}
+    out = {}
+    for ds in (4, 1):
+        patch = Patch(feats, segs, 120.0, fps=FPS, seed=42, device=rng_device)
+        _, noise = patch.forward(palette, downscale_factor=ds)
+        for i in range(0, 4 * 32, 32):
+            for m in noise:
+                m.forward(i, 32)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        nbytes, n_calls = 0, 0
+        e0.record()
+        for i in range(0, T, 32):
+            for m in noise:
+                o = m.forward(i, min(32, T - i))
+                nbytes += o.numel() * 4
+                n_calls += 1
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        out[f"noise_downscale_{ds}"] = {"ms": round(ms, 2), "launch_calls": n_calls, "bytes_written": nbytes,
+                                         "GBps": round(nbytes / (ms * 1e-3) / 1e9, 1),
+                                         "frac_of_hbm_peak": round(nbytes / (ms * 1e-3) / 1e9 / peak, 4),
+                                         "audio_s_per_s": round(T / FPS / (ms * 1e-3), 1)}
+        del noise, patch
+    x = synth_features(T, 3 * 3 + 2 * 4, 31).abs().add_(0.01)[None].to(dev)
+    dec = FixedLatentNoiseDecoder(palette[:9], hidden_size=3, n_latent_split=3, n_noise=4)
+    for _ in range(2):
+        dec(x)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(5):
+        lat, nz = dec(x)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 5
+    nb = lat.numel() * 4 + sum(n.numel() * 4 for n in nz)
+    out["fixed_decoder"] = {"ms": round(ms, 3), "bytes_written": nb, "GBps": round(nb / (ms * 1e-3) / 1e9, 1),
+                            "frac_of_hbm_peak": round(nb / (ms * 1e-3) / 1e9 / peak, 4),
+                            "audio_s_per_s": round(T / FPS / (ms * 1e-3), 1)}
+    return out
+
+
 class EventLog(dict):
     """cabi.event_log that records every entry point."""
 
@@ -238,6 +293,7 @@ def main():
     ap.add_argument("--chunk", type=int, default=8, help="clips per feature-graph replay / sampler batch (full workload)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-cfg4", action="store_true", help="skip the configs[3] noise / decoder legs")
     args = ap.parse_args()
     if args.clips is None:
         args.clips = DEFAULT_CLIPS[args.workload]
@@ -413,6 +469,12 @@ def main():
         single = {"ms_median": ts[len(ts) // 2], "ms_min": ts[0], "clips": 1,
                   "note": "one 240 s clip resident in HBM -> features [5760,59] + latents [5760,18,512], wall clock"}
 
+    # configs[3] (SURVEY 8d cfg 4) legs, N = 1 only: (a) every noise batch of one 4-minute Patch — all 180
+    # `forward(i, 32)` calls of the 17 layers at downscale 4 and 1 — and (b) the fixed decoder on [1, 5760, 17] envelopes
+    cfg4 = None
+    if kind == "full" and world == 1 and not args.no_cfg4:
+        cfg4 = time_cfg4(dev, palette, segs, T, args.rng)
+
     if rank == 0:
         peak, peak_src = measured_peaks()
         top = sorted(per_kernel.items(), key=lambda kv: -kv[1][0])
@@ -452,13 +514,13 @@ def main():
             "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload_name(kind, B), "clips_per_gpu": B, "frames_per_clip": T,
+                       "single_track": single, "cfg4": cfg4,
                        "l2": f"inputs_exceed_l2 ({B * n * 4 / 1e9:.2f} GB of waveforms per step)",
                        "parallelism": f"clip-sharded x{world}; one NCCL all-reduce of 59x3 fp64 feature stats per step"
                        if kind == "full" else f"clip-sharded x{world}, no data-path collective",
                        "patch_rng": args.rng if kind == "full" else None,
                        "host_threads": (args.workers or pipeline.default_patch_workers(args.rng)) if kind == "full" else 1},
             "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
-            "single_track": single,
         }) + "\n")
         result_out.flush()
     if world > 1:

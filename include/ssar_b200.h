@@ -339,11 +339,16 @@ int ssar_mix_gemm(const float* weights, long long ldw, long long group_stride, i
 /* The same product as ssar_mix_gemm for whole rows (no row_alpha / row_beta, all n_cols columns, n_basis <= 192) on the
  * tensor cores: tcgen05.mma kind::f16 with a 3-term fp16 split of both operands (fp32-accurate, fp32 accumulation in
  * TMEM), TMA-fed, A-stationary (csrc/traj_mix_tc.cu).  n_cols / group_cols weight groups; group_cols a multiple of 128.
- * scratch: ssar_mix_gemm_tc_scratch_bytes(...) bytes of device memory (the split fp16 operand panels). */
+ * Both operands are scaled by a power of two taken from their amax before the split (any fp32 range is safe) and the
+ * scale is undone in the epilogue.  basis_split: NULL, or a block written by ssar_mix_gemm_tc_split_basis for this
+ * (basis, n_basis, n_cols) — one palette split for all clips of a batch; `basis` may then be NULL.
+ * scratch: ssar_mix_gemm_tc_scratch_bytes(...) bytes; basis_split: ssar_mix_gemm_tc_basis_bytes(...) bytes. */
 long long ssar_mix_gemm_tc_scratch_bytes(int n_rows, int n_groups, int n_basis, int n_cols);
+long long ssar_mix_gemm_tc_basis_bytes(int n_basis, int n_cols);
+int ssar_mix_gemm_tc_split_basis(const float* basis, long long ldb, int n_basis, int n_cols, void* basis_split, void* stream);
 int ssar_mix_gemm_tc(const float* weights, long long ldw, long long group_stride, int group_cols, const float* basis,
-                     long long ldb, float* out, long long ldo, int n_rows, int n_basis, int n_cols, void* scratch,
-                     void* stream);
+                     long long ldb, float* out, long long ldo, int n_rows, int n_basis, int n_cols, const void* basis_split,
+                     void* scratch, void* stream);
 
 /* weights[t, g, k] = alpha[t] * weights[t, g, k] + beta[t] * seq[t, k] for g in [g_begin, g_end): the average /
  * modulate / overwrite merges of latent.py:68-78 applied to weight matrices [n_rows, n_groups, n_basis].

@@ -14,6 +14,7 @@
 //   * warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (+ TMEM allocator), warps 2..5 = epilogue
 //     (tcgen05.ld 32x32b -> registers -> swizzled shared tile -> TMA store), all synchronised with mbarriers only.
 // The kernel is write bound: 36.9 kB of output per frame against 2 * 3 * K * 9216 tensor FLOP.
+#include "block_utils.cuh"
 #include "tc_common.cuh"
 
 namespace {
@@ -28,31 +29,69 @@ constexpr int TC_CSTAGE_BYTES = 32 * 32 * 4;              // per epilogue warp: 
 // ---------------------------------------------------------------------------------------------------------------
 // operand split: fp32 -> (hi, lo) fp16, K-major, K zero-padded to KP
 // ---------------------------------------------------------------------------------------------------------------
-// W [T, G, P] (row stride ldw, group stride gs) -> Ah / Al [G][Tpad][KP]
-__global__ void split_weights_kernel(const float* __restrict__ W, long long ldw, long long gs, int T, int Tpad, int G, int P,
-                                     int KP, __half* __restrict__ Ah, __half* __restrict__ Al) {
-    const long long n = (long long)G * Tpad * KP;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-        const int k = (int)(i % KP);
-        const long long r = i / KP;
-        const int t = (int)(r % Tpad), g = (int)(r / Tpad);
-        float a = 0.f;
-        if (t < T && k < P) a = __ldg(W + (long long)t * ldw + (long long)g * gs + k);
-        __half h, l;
-        split_half(a, h, l);
-        Ah[i] = h;
-        Al[i] = l;
+// Power-of-two operand scale from the operand's amax: brings it into [2^9, 2^10), so hi AND lo stay normal fp16 numbers
+// for every element down to 2^-12 of the peak (no overflow for operands >= 65504, no subnormal lo terms for tiny ones).
+__device__ __forceinline__ float operand_scale(uint32_t amax_bits) {
+    const float amax = __uint_as_float(amax_bits);
+    if (!(amax > 0.f) || !isfinite(amax)) return 1.f;
+    return exp2f((float)(9 - ilogbf(amax)));
+}
+
+__global__ void basis_amax_kernel(const float* __restrict__ B, long long ldb, int P, int NC, uint32_t* __restrict__ amax) {
+    const long long n = (long long)P * NC;
+    float m = 0.f;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        m = fmaxf(m, fabsf(__ldg(B + (i / NC) * ldb + (i % NC))));
+    m = warp_max(m);
+    if ((threadIdx.x & 31) == 0 && __float_as_uint(m) > __ldcg(amax)) atomicMax(amax, __float_as_uint(m));
+}
+
+// W [T, G, P] (row stride ldw, group stride gs) -> Ah / Al [G][Tpad][KP].  One WARP per (group, row): the row's own amax
+// gives its power-of-two scale (amax bits written to scales[g * Tpad + t]; the epilogue, where a lane owns an output
+// row, undoes it), so there is no separate reduction pass, no atomic, and every row keeps full fp16 x 2 precision
+// whatever the other rows hold.  Rows beyond T are written as zeros.
+__global__ void __launch_bounds__(256) split_weights_kernel(const float* __restrict__ W, long long ldw, long long gs, int T,
+                                                            int Tpad, int G, int P, int KP, uint32_t* __restrict__ scales,
+                                                            __half* __restrict__ Ah, __half* __restrict__ Al) {
+    const int lane = threadIdx.x & 31;
+    const long long n_rows = (long long)G * Tpad;
+    for (long long r = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < n_rows;
+         r += (long long)gridDim.x * (blockDim.x >> 5)) {
+        const int g = (int)(r / Tpad), t = (int)(r - (long long)g * Tpad);
+        const float* __restrict__ row = W + (long long)t * ldw + (long long)g * gs;
+        float v[6];  // KP <= 192: six values per lane
+        float m = 0.f;
+#pragma unroll
+        for (int j = 0; j < 6; ++j) {
+            const int k = lane + 32 * j;
+            v[j] = (t < T && k < P) ? __ldg(row + k) : 0.f;
+            m = fmaxf(m, fabsf(v[j]));
+        }
+        m = warp_max(m);
+        if (lane == 0) scales[r] = __float_as_uint(m);
+        const float sc = operand_scale(__float_as_uint(m));
+#pragma unroll
+        for (int j = 0; j < 6; ++j) {
+            const int k = lane + 32 * j;
+            if (k < KP) {
+                __half h, l;
+                split_half(v[j] * sc, h, l);
+                Ah[r * KP + k] = h;
+                Al[r * KP + k] = l;
+            }
+        }
     }
 }
 
-// palette [P, NC] (row stride ldb) -> Bh / Bl [NC][KP] (transposed through a 32 x 32 shared tile)
+// palette [P, NC] (row stride ldb) -> Bh / Bl [NC][KP] (transposed through a 32 x 32 shared tile), scaled likewise
 __global__ void split_palette_kernel(const float* __restrict__ B, long long ldb, int P, int NC, int KP,
-                                     __half* __restrict__ Bh, __half* __restrict__ Bl) {
+                                     const uint32_t* __restrict__ amax, __half* __restrict__ Bh, __half* __restrict__ Bl) {
     __shared__ float tile[32][33];
+    const float sc = operand_scale(__ldg(amax));
     const int n0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
     for (int r = threadIdx.y; r < 32; r += blockDim.y) {
         const int k = k0 + r, n = n0 + threadIdx.x;
-        tile[r][threadIdx.x] = (k < P && n < NC) ? __ldg(B + (long long)k * ldb + n) : 0.f;
+        tile[r][threadIdx.x] = (k < P && n < NC) ? __ldg(B + (long long)k * ldb + n) * sc : 0.f;
     }
     __syncthreads();
     for (int r = threadIdx.y; r < 32; r += blockDim.y) {
@@ -79,7 +118,8 @@ struct TcShared {
 __global__ void __launch_bounds__(TC_THREADS, 1)
 mix_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_constant__ CUtensorMap map_al,
                    const __grid_constant__ CUtensorMap map_bh, const __grid_constant__ CUtensorMap map_bl,
-                   const __grid_constant__ CUtensorMap map_out, int Tpad, int n_groups, int group_cols, int KB, int n_splits) {
+                   const __grid_constant__ CUtensorMap map_out, int Tpad, int n_groups, int group_cols, int KB, int n_splits,
+                   const uint32_t* __restrict__ amax_w, const uint32_t* __restrict__ amax_b) {
     extern __shared__ __align__(1024) uint8_t tc_smem_raw[];
     // carve: [A panel: KB x (hi 16 KB | lo 16 KB)] [B ring: STAGES x (hi 16 KB | lo 16 KB)] [barriers]
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(tc_smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -200,12 +240,15 @@ mix_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_cons
         // ===================================================================== epilogue warps 2..5
         const int quad = warp & 3;  // TMEM lane quadrant this warp may read
         uint8_t* stage_buf = c_stage + (size_t)quad * TC_CSTAGE_BYTES;
+        const float unscale_b = 1.f / operand_scale(__ldg(amax_b));  // powers of two: exact
         uint32_t acc = 0, acc_phase = 0;
         for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
             const int sp = item % n_splits, gm = item / n_splits;
             const int g = gm / m_tiles, mt = gm - g * m_tiles;
             const int nt0 = sp * n_tiles, nt1 = min(nt0 + n_tiles, tiles_per_group);
             const int row0 = mt * TC_BM + quad * 32;  // first output row of this warp's 32-lane slice
+            // this lane's output row carries its own operand scale (rows past the tensor's end read a zero-row scale of 1)
+            const float unscale = unscale_b / operand_scale(__ldg(amax_w + (long long)g * Tpad + row0 + lane));
             for (int nt = nt0; nt < nt1; ++nt) {
                 mbar_wait(&sh->acc_full[acc], acc_phase);
                 tc_fence_after();
@@ -233,8 +276,9 @@ mix_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_cons
                     uint8_t* rowp = stage_buf + lane * 128;
 #pragma unroll
                     for (int q = 0; q < 8; ++q)
-                        *reinterpret_cast<uint4*>(rowp + ((q ^ (lane & 7)) << 4)) =
-                            make_uint4(r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]);
+                        *reinterpret_cast<float4*>(rowp + ((q ^ (lane & 7)) << 4)) =
+                            make_float4(__uint_as_float(r[4 * q]) * unscale, __uint_as_float(r[4 * q + 1]) * unscale,
+                                        __uint_as_float(r[4 * q + 2]) * unscale, __uint_as_float(r[4 * q + 3]) * unscale);
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                     __syncwarp();
                     if (lane == 0) {  // rows beyond the tensor's extent are clipped by the TMA unit
@@ -295,17 +339,52 @@ bool make_out_map(CUtensorMap* map, const void* ptr, long long rows, long long c
 
 static inline long long tc_kp(int n_basis) { return ((long long)n_basis + TC_BK - 1) / TC_BK * TC_BK; }
 static inline long long tc_tpad(int n_rows) { return ((long long)n_rows + TC_BM - 1) / TC_BM * TC_BM; }
+static inline long long tc_scale_bytes(int n_groups, long long Tpad) {
+    return ((long long)n_groups * Tpad * 4 + 1023) / 1024 * 1024;  // one amax word per (group, row)
+}
+
+// split basis block: [amax word, padded to 1024 B][Bh [n_cols][KP]][Bl [n_cols][KP]]
+extern "C" long long ssar_mix_gemm_tc_basis_bytes(int n_basis, int n_cols) {
+    return 1024 + 2 * (long long)n_cols * tc_kp(n_basis) * 2 + 1024;
+}
+
+static int tc_split_basis(const float* basis, long long ldb, int n_basis, int n_cols, uint8_t* blk, cudaStream_t st) {
+    const int KP = (int)tc_kp(n_basis);
+    uint32_t* amax = reinterpret_cast<uint32_t*>(blk);
+    __half* Bh = reinterpret_cast<__half*>(blk + 1024);
+    __half* Bl = Bh + (long long)n_cols * KP;
+    cudaError_t e = cudaMemsetAsync(amax, 0, sizeof(uint32_t), st);
+    if (e != cudaSuccess) {
+        ssar_set_error("mix_gemm_tc: memset: %s", cudaGetErrorString(e));
+        return SSAR_ERR_CUDA;
+    }
+    int grid = ssar_div_up((long long)n_basis * n_cols, 256 * 8);
+    if (grid > SSAR_NUM_SMS * 4) grid = SSAR_NUM_SMS * 4;
+    basis_amax_kernel<<<grid, 256, 0, st>>>(basis, ldb, n_basis, n_cols, amax);
+    split_palette_kernel<<<dim3(ssar_div_up(n_cols, 32), ssar_div_up(KP, 32)), dim3(32, 8), 0, st>>>(basis, ldb, n_basis, n_cols,
+                                                                                                  KP, amax, Bh, Bl);
+    return ssar_launch_status("mix_gemm_tc_split_basis");
+}
+
+extern "C" int ssar_mix_gemm_tc_split_basis(const float* basis, long long ldb, int n_basis, int n_cols, void* basis_split,
+                                            void* stream) {
+    SSAR_REQUIRE(basis && basis_split, "mix_gemm_tc_split_basis: null pointer");
+    SSAR_REQUIRE(n_basis > 0 && n_basis <= TC_MAX_KB * TC_BK && n_cols > 0, "mix_gemm_tc_split_basis: n_basis must be in [1, 192]");
+    uint8_t* blk = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(basis_split) + 1023) & ~(uintptr_t)1023);
+    return tc_split_basis(basis, ldb, n_basis, n_cols, blk, (cudaStream_t)stream);
+}
 
 extern "C" long long ssar_mix_gemm_tc_scratch_bytes(int n_rows, int n_groups, int n_basis, int n_cols) {
     const long long KP = tc_kp(n_basis), Tpad = tc_tpad(n_rows);
-    return 2 * ((long long)n_groups * Tpad * KP + (long long)n_cols * KP) * 2 + 1024;
+    return 1024 + tc_scale_bytes(n_groups, Tpad) + 2 * (long long)n_groups * Tpad * KP * 2 +
+           ssar_mix_gemm_tc_basis_bytes(n_basis, n_cols) + 1024;
 }
 
 extern "C" int ssar_mix_gemm_tc(const float* weights, long long ldw, long long group_stride, int group_cols,
                                 const float* basis, long long ldb, float* out, long long ldo, int n_rows, int n_basis,
-                                int n_cols, void* scratch, void* stream) {
+                                int n_cols, const void* basis_split, void* scratch, void* stream) {
     if (n_rows == 0 || n_cols == 0) return SSAR_OK;
-    SSAR_REQUIRE(weights && basis && out && scratch, "mix_gemm_tc: null pointer");
+    SSAR_REQUIRE(weights && (basis || basis_split) && out && scratch, "mix_gemm_tc: null pointer");
     SSAR_REQUIRE(group_cols > 0 && group_cols % TC_BN == 0 && n_cols % group_cols == 0,
                  "mix_gemm_tc: group_cols must be a multiple of 128 that divides n_cols");
     SSAR_REQUIRE(n_basis > 0 && n_basis <= TC_MAX_KB * TC_BK, "mix_gemm_tc: n_basis must be in [1, 192] (use ssar_mix_gemm)");
@@ -315,18 +394,27 @@ extern "C" int ssar_mix_gemm_tc(const float* weights, long long ldw, long long g
     const int G = n_cols / group_cols;
     const int KP = (int)tc_kp(n_basis), Tpad = (int)tc_tpad(n_rows), KB = KP / TC_BK;
     uint8_t* sb = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(scratch) + 1023) & ~(uintptr_t)1023);
-    __half* Ah = reinterpret_cast<__half*>(sb);
+    uint32_t* amax_w = reinterpret_cast<uint32_t*>(sb);  // one amax word per (group, row)
+    __half* Ah = reinterpret_cast<__half*>(sb + tc_scale_bytes(G, Tpad));
     __half* Al = Ah + (long long)G * Tpad * KP;
-    __half* Bh = Al + (long long)G * Tpad * KP;
-    __half* Bl = Bh + (long long)n_cols * KP;
+    const uint8_t* bblk;
+    if (basis_split) {  // the basis was split once for many calls (ssar_mix_gemm_tc_split_basis)
+        bblk = reinterpret_cast<const uint8_t*>((reinterpret_cast<uintptr_t>(basis_split) + 1023) & ~(uintptr_t)1023);
+    } else {
+        uint8_t* mine = reinterpret_cast<uint8_t*>(Al + (long long)G * Tpad * KP);
+        mine = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(mine) + 1023) & ~(uintptr_t)1023);
+        const int rc = tc_split_basis(basis, ldb, n_basis, n_cols, mine, st);
+        if (rc != SSAR_OK) return rc;
+        bblk = mine;
+    }
+    const uint32_t* amax_b = reinterpret_cast<const uint32_t*>(bblk);
+    const __half* Bh = reinterpret_cast<const __half*>(bblk + 1024);
+    const __half* Bl = Bh + (long long)n_cols * KP;
 
     {
-        const long long n = (long long)G * Tpad * KP;
-        int grid = ssar_div_up(n, 256);
-        if (grid > SSAR_NUM_SMS * 16) grid = SSAR_NUM_SMS * 16;
-        split_weights_kernel<<<grid, 256, 0, st>>>(weights, ldw, group_stride, n_rows, Tpad, G, n_basis, KP, Ah, Al);
-        split_palette_kernel<<<dim3(ssar_div_up(n_cols, 32), ssar_div_up(KP, 32)), dim3(32, 8), 0, st>>>(basis, ldb, n_basis,
-                                                                                                      n_cols, KP, Bh, Bl);
+        int grid = ssar_div_up((long long)G * Tpad, 8);
+        if (grid > SSAR_NUM_SMS * 8) grid = SSAR_NUM_SMS * 8;
+        split_weights_kernel<<<grid, 256, 0, st>>>(weights, ldw, group_stride, n_rows, Tpad, G, n_basis, KP, amax_w, Ah, Al);
     }
     CUtensorMap mah, mal, mbh, mbl, mout;
     if (!make_panel_map(&mah, Ah, (long long)G * Tpad, KP) || !make_panel_map(&mal, Al, (long long)G * Tpad, KP) ||
@@ -347,6 +435,7 @@ extern "C" int ssar_mix_gemm_tc(const float* weights, long long ldw, long long g
     if (n_splits > tiles_per_group) n_splits = tiles_per_group;
     int grid = base_items * n_splits;
     if (grid > SSAR_NUM_SMS) grid = SSAR_NUM_SMS;
-    mix_gemm_tc_kernel<<<grid, TC_THREADS, smem, st>>>(mah, mal, mbh, mbl, mout, Tpad, G, group_cols, KB, n_splits);
+    mix_gemm_tc_kernel<<<grid, TC_THREADS, smem, st>>>(mah, mal, mbh, mbl, mout, Tpad, G, group_cols, KB, n_splits, amax_w,
+                                                       amax_b);
     return ssar_launch_status("mix_gemm_tc");
 }

@@ -650,8 +650,28 @@ def plp_from_onset(onset_env: torch.Tensor, sr, hop_length: int = 1024, win_leng
 USE_TENSOR_CORE_MIX = True  # False: always the CUDA-core fp32 GEMM (ssar_mix_gemm)
 
 
+class SplitBasis:
+    """A basis [K, ...] (a latent palette) split ONCE into the tensor-core mix's fp16 (hi, lo) panels
+    (`ssar_mix_gemm_tc_split_basis`): pass it as `mix_gemm(..., basis_split=...)` for every product with that basis —
+    a batch of clips renders against one palette.  Valid while `basis` is not modified."""
+
+    def __init__(self, basis: torch.Tensor):
+        if not basis.is_cuda:
+            raise SsarError("ssar_b200 needs CUDA tensors (no CPU fallback)")
+        self.basis = basis.contiguous().float()
+        self.K = self.basis.shape[0]
+        self.N = self.basis.numel() // max(self.K, 1)
+        self.block = None
+        if 0 < self.K <= 192 and self.N % 128 == 0:
+            fn = cabi.lib().ssar_mix_gemm_tc_basis_bytes
+            fn.restype = C.c_longlong
+            self.block = torch.empty(int(fn(i32(self.K), i32(self.N))), dtype=torch.uint8, device=basis.device)
+            cabi.call("ssar_mix_gemm_tc_split_basis", ptr(self.basis), i64(self.N), i32(self.K), i32(self.N), ptr(self.block),
+                      nbytes=cabi.nbytes_of(self.basis) + self.K * self.N * 4)
+
+
 def mix_gemm(weights: torch.Tensor, basis: torch.Tensor, out: torch.Tensor | None = None, group_cols: int | None = None,
-             col_begin: int = 0, col_end: int | None = None, row_alpha=None, row_beta=None):
+             col_begin: int = 0, col_end: int | None = None, row_alpha=None, row_beta=None, basis_split: SplitBasis | None = None):
     """out[t, n] = row_alpha[t] * out[t, n] + row_beta[t] * sum_k weights[t, g(n), k] * basis[k, n].
 
     weights: [T, K] (one group) or [T, G, K]; basis: [K, ...] flattened to [K, N]; out: [T, ...] with N elements per row
@@ -679,8 +699,13 @@ def mix_gemm(weights: torch.Tensor, basis: torch.Tensor, out: torch.Tensor | Non
             and T >= 128 and group_cols % 128 == 0 and N % group_cols == 0 and N // group_cols == G):
         nb = int(cabi.lib().ssar_mix_gemm_tc_scratch_bytes(C.c_int(T), C.c_int(G), C.c_int(K), C.c_int(N)))
         scratch = torch.empty(nb, dtype=torch.uint8, device=out.device)
+        pre = None
+        if basis_split is not None and basis_split.block is not None:
+            if basis_split.K != K or basis_split.N != N:
+                raise SsarError("mix_gemm: basis_split was made for another basis shape")
+            pre = basis_split.block
         cabi.call("ssar_mix_gemm_tc", ptr(weights), i64(G * K), i64(K), i32(group_cols), ptr(basis), i64(N), ptr(out), i64(N),
-                  i32(T), i32(K), i32(N), ptr(scratch), nbytes=cabi.nbytes_of(weights, basis) + T * N * 4)
+                  i32(T), i32(K), i32(N), ptr(pre), ptr(scratch), nbytes=cabi.nbytes_of(weights, basis) + T * N * 4)
         return out
     cabi.call("ssar_mix_gemm", ptr(weights), i64(G * K), i64(K), i32(group_cols), ptr(basis), i64(N), ptr(out), i64(N),
               i32(T), i32(K), i32(col_begin), i32(col_end), ptr(row_alpha), ptr(row_beta),
@@ -741,13 +766,19 @@ def rows_affine(x: torch.Tensor, mu=None, sig=None):
     return out
 
 
-def noise_eval(ops_list, i: int, b: int, height: int, width: int, device):
-    """Runs a compiled noise program (list of `_cabi.NoiseOp`) for frames [i, i + b) -> [b, height, width]."""
+def noise_program(ops_list, device):
+    """A list of `_cabi.NoiseOp` as (host array, device copy, n_ops, n_loops): made once per program, passed to
+    `noise_eval` for every frame batch."""
     n = len(ops_list)
     arr = (cabi.NoiseOp * n)(*ops_list)
-    host_bytes = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
-    dev_ops = host_bytes.to(device)
-    n_loops = sum(1 for o in ops_list if o.kind == 0)
+    dev_ops = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).to(device)
+    return arr, dev_ops, n, sum(1 for o in ops_list if o.kind == 0)
+
+
+def noise_eval(ops_list, i: int, b: int, height: int, width: int, device):
+    """Runs a compiled noise program (list of `_cabi.NoiseOp`, or the tuple `noise_program` made of one) for frames
+    [i, i + b) -> [b, height, width]."""
+    arr, dev_ops, n, n_loops = ops_list if isinstance(ops_list, tuple) else noise_program(ops_list, device)
     scratch = torch.empty(max(n_loops * b, 1), dtype=torch.float32, device=device)
     out = torch.empty(b, height, width, dtype=torch.float32, device=device)
     cabi.call("ssar_noise_eval", ptr(dev_ops), C.cast(arr, C.c_void_p), i32(n), i32(i), i32(b), i32(height), i32(width),

@@ -394,6 +394,8 @@ def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, se
             if not sampler_kernel_ready(dev, segmentations):  # fallback sampler: one CUDA graph per sub-patch count
                 precapture_sampler_graphs(dev, segmentations)  # no-op once captured
     workers = default_patch_workers(rng_device) if workers is None else int(workers)
+    with torch.cuda.device(dev), torch.cuda.stream(stream):
+        palette_split = ops.SplitBasis(palette)  # one fp16 (hi, lo) split of the palette for every clip's render
     B = audio.shape[0]
     chunk = max(1, min(int(chunk), B))
     bounds = [(c0, min(c0 + chunk, B)) for c0 in range(0, B, chunk)]
@@ -429,7 +431,7 @@ def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, se
                 for b in range(c0, c1):
                     patch = chunk_patches[b - c0]
                     patch.bind({k: v[b - c0] for k, v in pf.items()})
-                    noises[b] = patch.forward(palette, downscale_factor=4, latents_out=latents[b])[1]
+                    noises[b] = patch.forward(palette, downscale_factor=4, latents_out=latents[b], palette_split=palette_split)[1]
             feats = feats_chunks[0] if len(feats_chunks) == 1 else torch.cat(feats_chunks, dim=0)
         for check in checks:
             check()
@@ -531,7 +533,8 @@ def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, se
                 if sample_error:
                     raise sample_error[0]
                 patches[b].bind({k: v[b - c0] for k, v in pf.items()})
-                noises[b] = patches[b].forward(palette, downscale_factor=4, latents_out=latents[b])[1]
+                noises[b] = patches[b].forward(palette, downscale_factor=4, latents_out=latents[b],
+                                               palette_split=palette_split)[1]
         feats = feats_chunks[0] if len(feats_chunks) == 1 else torch.cat(feats_chunks, dim=0)
     for fu in futs:
         fu.result()

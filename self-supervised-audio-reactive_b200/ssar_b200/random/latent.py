@@ -193,6 +193,6 @@ class LatentWeights:
         ops.subpatch_merge(self.w, lo // self.gl, hi // self.gl, self._sel(selection), src, src_scale=scale, lerp=lerp,
                            sigma=1, mod=mod, mod_scale=mod_scale, alpha=alpha, beta=beta)
 
-    def render(self, palette, out=None):
+    def render(self, palette, out=None, palette_split=None):
         self.flush()
-        return ops.mix_gemm(self.w, palette.to(self.device), out=out)
+        return ops.mix_gemm(self.w, palette.to(self.device), out=out, basis_split=palette_split)

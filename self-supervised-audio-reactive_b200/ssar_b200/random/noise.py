@@ -265,20 +265,28 @@ class NoiseProgram(Noise):
             self.steps = [(k, n.to(device) if n is not None else None, m.to(device) if m is not None else None, M, p0, p1, ta)
                           for (k, n, m, M, p0, p1, ta) in self.steps]
             self._device = device
+            self._compiled = None
         return self
 
     def leaf(self, kind, noise, mod, M=0, p0=0.0, to_acc=0):
         if to_acc:
             self.steps.clear()  # a leaf into `acc` replaces the layer's history (merge_type other than average / modulate)
         self.steps.append((kind, noise, mod, M, p0, 0.0, to_acc))
+        self._compiled = None
 
     def merge(self, kind, mod=None, p0=0.0, p1=0.0):
         self.steps.append((kind, None, mod, 0, p0, p1, 0))
+        self._compiled = None
 
     def forward(self, i, b):
         b = max(0, min(int(b), self.length - int(i)))
-        prog = [_op(k, noise=n, mod=m, M=M, p0=p0, p1=p1, to_acc=ta) for (k, n, m, M, p0, p1, ta) in self.steps]
-        return ops.noise_eval(prog, int(i), b, int(self.size[0]), int(self.size[1]), self._device)
+        # the op list does not depend on (i, b): its host array and device copy are made once per program, so a sweep of
+        # forward(i, 32) over a track costs two launches per call and no host-to-device copy
+        comp = getattr(self, "_compiled", None)
+        if comp is None or comp[0] != len(self.steps) or comp[1] != self._device:
+            prog = [_op(k, noise=n, mod=m, M=M, p0=p0, p1=p1, to_acc=ta) for (k, n, m, M, p0, p1, ta) in self.steps]
+            comp = self._compiled = (len(self.steps), self._device, ops.noise_program(prog, self._device))
+        return ops.noise_eval(comp[2], int(i), b, int(self.size[0]), int(self.size[1]), self._device)
 
     __call__ = forward
 

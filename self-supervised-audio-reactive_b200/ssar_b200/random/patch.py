@@ -525,9 +525,10 @@ class Patch:
         choice, skew, randn = self._draws()
         return _noise_config(choice, skew, randn)
 
-    def forward(self, latent_palette, downscale_factor=1, aspect_ratio=1, latents_out=None):
+    def forward(self, latent_palette, downscale_factor=1, aspect_ratio=1, latents_out=None, palette_split=None):
         """patch.py:108-133 -> (latents [T, 18, 512], list of 17 lazy noise modules).
-        latents_out: optional preallocated contiguous [T, 18, 512] tensor to render into (batch pipelines)."""
+        latents_out: optional preallocated contiguous [T, 18, 512] tensor to render into (batch pipelines).
+        palette_split: optional `ops.SplitBasis(latent_palette)` shared by every Patch rendered against this palette."""
         self.rng.manual_seed(self.seed)
         dev = latent_palette.device
         T, P = self.length, len(latent_palette)
@@ -552,7 +553,7 @@ class Patch:
         for j, sp in enumerate(self.latent_patches):
             acc.apply_subpatch(self.rng, self.segmentations, feats, self.tempo, self.fps,
                                permutation=perms[j + 1] if perms is not None else None, **sp)
-        latents = acc.render(latent_palette, out=latents_out)
+        latents = acc.render(latent_palette, out=latents_out, palette_split=palette_split)
 
         sizes = [(round(aspect_ratio * size / downscale_factor), round(size / downscale_factor))
                  for size in [4, 8, 8, 16, 16, 32, 32, 64, 64, 128, 128, 256, 256, 512, 512, 1024, 1024]]

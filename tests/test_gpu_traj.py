@@ -212,3 +212,24 @@ def test_tensor_core_mix_vs_fp32_kernel_and_fp64():
             assert rel_l2(got, ref32) < 5e-6, (Tn, G, K)
     finally:
         ops.USE_TENSOR_CORE_MIX = True
+
+
+def test_tensor_core_mix_operand_ranges_and_presplit_basis():
+    """Operands far outside fp16's range (palette x 1e5: fp16(value) would be inf; palette x 1e-6: the lo halves would be
+    subnormal) keep fp32 accuracy through the per-operand power-of-two scaling; a basis split once
+    (`ops.SplitBasis`) gives the same bits as the per-call split."""
+    from ssar_b200 import ops
+
+    g = torch.Generator("cpu").manual_seed(12)
+    Tn, G, K = 1024, 3, 180
+    W = torch.rand(Tn, G, K, generator=g).cuda()
+    P = torch.randn(K, 18, 512, generator=g).cuda()
+    for ws, ps in ((1.0, 1e5), (1.0, 1e-6), (3e4, 1e3), (1e-5, 1e-5)):
+        got = ops.mix_gemm(W * ws, P * ps)
+        ref64 = torch.einsum("tgk,kgn->tgn", (W * ws).double(), (P * ps).reshape(K, G, -1).double()).reshape(Tn, 18, 512)
+        assert bool(torch.isfinite(got).all()) and rel_l2(got.double(), ref64) < 2e-6, (ws, ps, rel_l2(got.double(), ref64))
+    sp = ops.SplitBasis(P)
+    assert sp.block is not None
+    assert torch.equal(ops.mix_gemm(W, P, basis_split=sp), ops.mix_gemm(W, P))
+    W2 = torch.rand(300, G, K, generator=g).cuda()
+    assert torch.equal(ops.mix_gemm(W2, P, basis_split=sp), ops.mix_gemm(W2, P))
