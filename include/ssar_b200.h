@@ -86,6 +86,18 @@ typedef struct {
     long long row_scale_ld;
 } ssar_projection;
 
+/* rosa/pitch.py:27-83 piptrack as an epilogue of the frame transform (the magnitude spectrogram it looks at never leaves
+ * shared memory): same arithmetic and outputs as ssar_piptrack on sqrt(|X|^2) */
+typedef struct {
+    int* count;             /* NULL = unused; [n_clips], zeroed by ssar_frames_fft */
+    float* pitch;           /* [n_clips, capacity] */
+    float* mag;             /* [n_clips, capacity] */
+    long long capacity;     /* >= ssar_piptrack_capacity(n_frames, k_lo, k_hi) */
+    int k_lo, k_hi;         /* bins fmin <= f < fmax */
+    float threshold;
+    float sr;
+} ssar_piptrack_epilogue;
+
 typedef struct {
     const float* x;         /* [n_clips, clip_stride] waveform */
     long long n_samples;    /* valid samples per clip */
@@ -110,6 +122,7 @@ typedef struct {
                                their max keys, projection) covers only frames [0, aux_frames) of each clip and is laid out
                                [n_clips, aux_frames, ...]: one launch then serves stft (1 + N/hop frames, complex) and the
                                spectrogram-style features that drop the last frame (rosa/spectral.py:60) of the same signal */
+    ssar_piptrack_epilogue pip;
 } ssar_frames_args;
 
 int ssar_frames_fft(const ssar_frames_args* args, void* stream);

@@ -46,7 +46,7 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
     __syncthreads();
 
     float2* zw = zall + (size_t)warp * FPW * ZF;  // this warp's frame buffers
-    const bool need_pw = a.out_spec || a.out_flatness || a.fb[0].n_bands > 0 || a.fb[1].n_bands > 0;
+    const bool need_pw = a.out_spec || a.out_flatness || a.fb[0].n_bands > 0 || a.fb[1].n_bands > 0 || a.pip.count;
 
     for (long long fbase = ((long long)blockIdx.x * L::WPB + warp) * FPW; fbase < total_frames;
          fbase += (long long)gridDim.x * L::WPB * FPW) {
@@ -167,7 +167,7 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
                     slin = warp_sum(slin);
                     if (lane == 0) a.out_flatness[orow] = expf(slog / (float)NBINS) / (slin / (float)NBINS);
                 }
-                if (aux && (a.fb[0].n_bands > 0 || a.fb[1].n_bands > 0)) {
+                if (aux && (a.fb[0].n_bands > 0 || a.fb[1].n_bands > 0 || a.pip.count)) {
                     if (!separate_power) __syncwarp();  // every lane has read its bins: the tile may be overwritten
 #pragma unroll
                     for (int j = 0; j < NJ; ++j) {
@@ -231,6 +231,52 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
                 }
             }
 
+            // epilogue 2b: piptrack on the magnitudes sqrt(power tile) (rosa/pitch.py:27-83; tuning.cu's piptrack_kernel
+            // reads the same values back from a [frames, 1025] spectrogram in HBM)
+            if (a.pip.count && aux) {
+                const ssar_piptrack_epilogue& pp = a.pip;
+                float mxp = 0.f;
+                for (int k = lane; k < NBINS; k += 32) mxp = fmaxf(mxp, pw[k]);
+                const float ref = pp.threshold * sqrtf(warp_max(mxp));  // sqrt is monotone: max of the magnitudes
+                for (int kb = pp.k_lo; kb < pp.k_hi; kb += 32) {
+                    const int k = kb + lane;
+                    float p = 0.f, m = 0.f;
+                    bool is_peak = false;
+                    if (k < pp.k_hi) {
+                        const float c = sqrtf(pw[k]);
+                        const float prev = k > 0 ? sqrtf(pw[k - 1]) : 0.f;
+                        const float next = k + 1 < NBINS ? sqrtf(pw[k + 1]) : 0.f;
+                        const float cm = c > ref ? c : 0.f;
+                        const float pm = (k > 0 && prev > ref) ? prev : 0.f;
+                        const float nm = (k + 1 < NBINS && next > ref) ? next : 0.f;
+                        if (cm > pm && cm >= nm) {
+                            float avg = 0.f, shift = 0.f;
+                            if (k > 0 && k + 1 < NBINS) {
+                                avg = 0.5f * (next - prev);
+                                const float den = 2.f * c - next - prev;
+                                shift = avg / (den + (fabsf(den) < 1.17549435e-38f ? 1.f : 0.f));
+                            }
+                            p = ((float)k + shift) * pp.sr / (float)N;
+                            m = c + 0.5f * avg * shift;
+                            is_peak = p > 0.f;
+                        }
+                    }
+                    const unsigned ballot = __ballot_sync(0xffffffffu, is_peak);
+                    if (ballot) {
+                        int base = 0;
+                        if (lane == 0) base = atomicAdd(pp.count + fclip, __popc(ballot));
+                        base = __shfl_sync(0xffffffffu, base, 0);
+                        if (is_peak) {
+                            const long long slot = base + __popc(ballot & ((1u << lane) - 1u));
+                            if (slot < pp.capacity) {
+                                pp.pitch[fclip * pp.capacity + slot] = p;
+                                pp.mag[fclip * pp.capacity + slot] = m;
+                            }
+                        }
+                    }
+                }
+            }
+
             // epilogue 3: banded complex projection of the complex spectrum (CQT basis); needs z intact
             if (a.proj.n_rows > 0 && aux) {
                 const ssar_projection& pjn = a.proj;
@@ -262,8 +308,15 @@ int launch_frames(const ssar_frames_args& a, cudaStream_t st) {
     using L = WarpFft<M>;
     const long long total = (long long)a.n_clips * a.n_frames;
     if (total == 0) return SSAR_OK;
-    const bool banks = a.fb[0].n_bands > 0 || a.fb[1].n_bands > 0;
+    const bool banks = a.fb[0].n_bands > 0 || a.fb[1].n_bands > 0 || a.pip.count;
     const int separate_power = (banks && a.proj.n_rows > 0) ? 1 : 0;  // the projection needs the complex tile intact
+    if (a.pip.count) {
+        cudaError_t em = cudaMemsetAsync(a.pip.count, 0, sizeof(int) * a.n_clips, st);
+        if (em != cudaSuccess) {
+            ssar_set_error("frames_fft: memset: %s", cudaGetErrorString(em));
+            return SSAR_ERR_CUDA;
+        }
+    }
     const size_t smem = frames_smem_bytes<M>(a.window != nullptr, separate_power != 0);
     cudaError_t e = cudaFuncSetAttribute(frames_fft_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) {
@@ -293,6 +346,10 @@ extern "C" int ssar_frames_fft(const ssar_frames_args* args, void* stream) {
     SSAR_REQUIRE(a.n_samples > a.n_fft / 2, "frames_fft: clip shorter than n_fft/2+1 samples cannot be reflect-padded");
     SSAR_REQUIRE(a.spec_power == 1 || a.spec_power == 2 || !a.out_spec, "frames_fft: spec_power must be 1 or 2");
     SSAR_REQUIRE(a.aux_frames >= 0 && a.aux_frames <= a.n_frames, "frames_fft: aux_frames=%d outside [0, n_frames]", a.aux_frames);
+    SSAR_REQUIRE(!a.pip.count || (a.pip.pitch && a.pip.mag && 0 <= a.pip.k_lo && a.pip.k_lo < a.pip.k_hi &&
+                                  a.pip.k_hi <= a.n_fft / 2 + 1 &&
+                                  a.pip.capacity >= ssar_piptrack_capacity(a.aux_frames > 0 ? a.aux_frames : a.n_frames, a.pip.k_lo, a.pip.k_hi)),
+                 "frames_fft: bad piptrack epilogue (null lists, bin range or capacity)");
     SSAR_REQUIRE(a.n_frames == 0 || (long long)(a.n_frames - 1) * a.hop <= a.n_samples,
                  "frames_fft: n_frames=%d exceeds 1 + n_samples/hop", a.n_frames);
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);

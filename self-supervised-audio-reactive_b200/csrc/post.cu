@@ -54,15 +54,32 @@ __global__ void gauss1d_kernel(const float* __restrict__ x, int T, long long inn
     for (int o = 0; o < TPT; ++o) acc[o] = 0.f, wr[o] = 0.f;
     // input rows t0 - r .. t0 + TPT - 1 + r; row i contributes to output o with tap k = i - o (relative indices)
     const int n_in = taps + TPT - 1;
-    for (int i0 = 0; i0 < n_in; i0 += TPT) {
+    if (t0 - radius >= 0 && t0 + TPT - 1 + radius < T) {
+        // interior: no padding arithmetic, the row pointer just advances
+        const float* __restrict__ px = xc + (long long)(t0 - radius) * inner + j;
+        for (int i0 = 0; i0 < n_in; i0 += TPT) {
 #pragma unroll
-        for (int u = 0; u < TPT; ++u) {
-            const int i = i0 + u;
-            if (i < n_in) {  // (uniform across the CTA)
-                const float v = __ldg(xc + (long long)pad_index(t0 + i - radius, T, radius, mode) * inner + j);
-                wr[u] = i < taps ? ws[i] : 0.f;  // tap i enters the window; taps below 0 / beyond the kernel are zeros
+            for (int u = 0; u < TPT; ++u) {
+                const int i = i0 + u;
+                if (i < n_in) {  // (uniform across the CTA)
+                    const float v = __ldg(px + (long long)i * inner);
+                    wr[u] = i < taps ? ws[i] : 0.f;  // tap i enters the window; taps beyond the kernel are zeros
 #pragma unroll
-                for (int o = 0; o < TPT; ++o) acc[o] = fmaf(wr[(u - o + TPT) % TPT], v, acc[o]);
+                    for (int o = 0; o < TPT; ++o) acc[o] = fmaf(wr[(u - o + TPT) % TPT], v, acc[o]);
+                }
+            }
+        }
+    } else {
+        for (int i0 = 0; i0 < n_in; i0 += TPT) {
+#pragma unroll
+            for (int u = 0; u < TPT; ++u) {
+                const int i = i0 + u;
+                if (i < n_in) {
+                    const float v = __ldg(xc + (long long)pad_index(t0 + i - radius, T, radius, mode) * inner + j);
+                    wr[u] = i < taps ? ws[i] : 0.f;
+#pragma unroll
+                    for (int o = 0; o < TPT; ++o) acc[o] = fmaf(wr[(u - o + TPT) % TPT], v, acc[o]);
+                }
             }
         }
     }

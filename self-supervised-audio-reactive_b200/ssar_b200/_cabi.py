@@ -41,6 +41,13 @@ class Projection(C.Structure):
     ]
 
 
+class PiptrackEpilogue(C.Structure):
+    _fields_ = [
+        ("count", C.c_void_p), ("pitch", C.c_void_p), ("mag", C.c_void_p), ("capacity", C.c_longlong),
+        ("k_lo", C.c_int), ("k_hi", C.c_int), ("threshold", C.c_float), ("sr", C.c_float),
+    ]
+
+
 class FramesArgs(C.Structure):
     _fields_ = [
         ("x", C.c_void_p), ("n_samples", C.c_longlong), ("clip_stride", C.c_longlong),
@@ -49,7 +56,7 @@ class FramesArgs(C.Structure):
         ("out_complex", C.c_void_p), ("ldc", C.c_longlong),
         ("out_spec", C.c_void_p), ("lds", C.c_longlong), ("spec_power", C.c_int),
         ("out_rms", C.c_void_p), ("out_flatness", C.c_void_p),
-        ("fb", Filterbank * 2), ("proj", Projection), ("aux_frames", C.c_int),
+        ("fb", Filterbank * 2), ("proj", Projection), ("aux_frames", C.c_int), ("pip", PiptrackEpilogue),
     ]
 
 

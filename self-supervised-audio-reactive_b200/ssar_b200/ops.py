@@ -51,6 +51,7 @@ def frames_fft(
     banks=(),
     proj: dict | None = None,
     aux_frames: int | None = None,
+    piptrack: dict | None = None,
 ):
     """Framed real FFT + fused epilogues over a batch of clips.
 
@@ -139,7 +140,16 @@ def frames_fft(
             pj.row_scale = proj["row_scale"].data_ptr()
             pj.row_scale_ld = int(proj["row_scale_ld"])
         keep.append(proj)
-    outs = [v for v in out.values()] + ([proj["out"]] if proj is not None else [])
+    if piptrack is not None:  # dict(k_lo, k_hi, threshold, sr) -> out["pip_pitch"], out["pip_mag"], out["pip_count"]
+        cap = int(cabi.lib().ssar_piptrack_capacity(C.c_int(n_frames), C.c_int(piptrack["k_lo"]), C.c_int(piptrack["k_hi"])))
+        out["pip_pitch"] = torch.empty(B, cap, dtype=torch.float32, device=dev)
+        out["pip_mag"] = torch.empty(B, cap, dtype=torch.float32, device=dev)
+        out["pip_count"] = torch.empty(B, dtype=torch.int32, device=dev)
+        a.pip.count, a.pip.pitch, a.pip.mag = out["pip_count"].data_ptr(), out["pip_pitch"].data_ptr(), out["pip_mag"].data_ptr()
+        a.pip.capacity, a.pip.k_lo, a.pip.k_hi = cap, int(piptrack["k_lo"]), int(piptrack["k_hi"])
+        a.pip.threshold, a.pip.sr = float(piptrack["threshold"]), float(piptrack["sr"])
+    # (the piptrack lists are capacity-sized; what is written is a few peaks per frame: not counted as algorithmic bytes)
+    outs = [v for k, v in out.items() if not k.startswith("pip_")] + ([proj["out"]] if proj is not None else [])
     nb = cabi.nbytes_of(x) + sum(o.numel() * o.element_size() for o in outs if proj is None or o is not proj["out"])
     if proj is not None:
         nb += B * n_frames * int(proj["n_rows"]) * 8
@@ -448,6 +458,9 @@ def spectral_contrast(mag: torch.Tensor, bands, linear: bool = False, top_db: fl
 # ------------------------------------------------------------------------------------------------
 # tuning / chroma / tonnetz (csrc/tuning.cu, csrc/chroma.cu)
 # ------------------------------------------------------------------------------------------------
+FUSED_PIPTRACK = True  # piptrack as an epilogue of the hop n_fft/4 transform (False: spectrogram to HBM + ssar_piptrack)
+
+
 def estimate_tuning(y: torch.Tensor, sr, n_fft: int = 2048, bins_per_octave: int = 12, threshold: float = 0.1,
                     fmin: float = 150.0, fmax: float = 4000.0):
     """rosa/pitch.py:9-24 for a batch [B, N] -> (tuning_idx int32 [B] in [0, 100], tuning_val fp32 [B])."""
@@ -455,14 +468,20 @@ def estimate_tuning(y: torch.Tensor, sr, n_fft: int = 2048, bins_per_octave: int
     B, N = y.shape
     hop = n_fft // 4  # hop_length=None reaches torch.stft's default through rosa/spectral.py:59-62
     T = N // hop
-    S = frames_fft(y, n_fft, hop, T, torch.hann_window, spec_power=1)["spec"]
     k_lo, k_hi = plan.piptrack_bin_range(float(sr), n_fft, fmin, fmax)
-    cap = int(cabi.lib().ssar_piptrack_capacity(C.c_int(T), C.c_int(k_lo), C.c_int(k_hi)))
-    pitch = torch.empty(B, cap, dtype=torch.float32, device=y.device)
-    mag = torch.empty_like(pitch)
-    count = torch.empty(B, dtype=torch.int32, device=y.device)
-    cabi.call("ssar_piptrack", ptr(S), i64(S.shape[2]), i32(B), i32(T), i32(S.shape[2]), i32(k_lo), i32(k_hi),
-              f32(threshold), f32(float(sr)), i32(n_fft), i64(cap), ptr(pitch), ptr(mag), ptr(count), nbytes=cabi.nbytes_of(S))
+    if FUSED_PIPTRACK and n_fft in (1024, 2048):
+        # the peak picking runs in the transform's epilogue: the [frames, 1025] magnitudes never reach HBM
+        o = frames_fft(y, n_fft, hop, T, torch.hann_window, piptrack=dict(k_lo=k_lo, k_hi=k_hi, threshold=threshold, sr=sr))
+        pitch, mag, count = o["pip_pitch"], o["pip_mag"], o["pip_count"]
+        cap = pitch.shape[1]
+    else:
+        S = frames_fft(y, n_fft, hop, T, torch.hann_window, spec_power=1)["spec"]
+        cap = int(cabi.lib().ssar_piptrack_capacity(C.c_int(T), C.c_int(k_lo), C.c_int(k_hi)))
+        pitch = torch.empty(B, cap, dtype=torch.float32, device=y.device)
+        mag = torch.empty_like(pitch)
+        count = torch.empty(B, dtype=torch.int32, device=y.device)
+        cabi.call("ssar_piptrack", ptr(S), i64(S.shape[2]), i32(B), i32(T), i32(S.shape[2]), i32(k_lo), i32(k_hi),
+                  f32(threshold), f32(float(sr)), i32(n_fft), i64(cap), ptr(pitch), ptr(mag), ptr(count), nbytes=cabi.nbytes_of(S))
     idx = torch.empty(B, dtype=torch.int32, device=y.device)
     val = torch.empty(B, dtype=torch.float32, device=y.device)
     edges = plan.tuning_edges(str(y.device))

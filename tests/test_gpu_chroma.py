@@ -121,3 +121,41 @@ def test_cqt_tensor_core_vs_fft_path_and_golden():
         assert rel_l2(a[c, :2], b[c, :2]) < 2e-5 and rel_l2(a[c, -2:], b[c, -2:]) < 2e-5  # reflect-padded edge frames
     C_or = ocqt.cqt(xs[1].cpu(), sr)
     assert rel_l2(torch.view_as_real(torch.view_as_complex(a[1]).T.contiguous()), torch.view_as_real(C_or.contiguous())) < TOL_CQT
+
+
+def test_fused_piptrack_equals_spectrogram_path():
+    """estimate_tuning with the peak picking in the STFT epilogue == spectrogram to HBM + ssar_piptrack: same tuning, and
+    the same multiset of (pitch, magnitude) pairs per clip bit for bit (the lists are unordered)."""
+    from ssar_b200 import ops, plan
+
+    sr, n = 24576, 24576 * 9 + 77
+    xs = torch.stack([synth_clip(n, sr, i) for i in (0, 7, 11, 4)]).cuda()
+    try:
+        ops.FUSED_PIPTRACK = False
+        i0, v0 = ops.estimate_tuning(xs, sr, bins_per_octave=36)
+        ops.FUSED_PIPTRACK = True
+        i1, v1 = ops.estimate_tuning(xs, sr, bins_per_octave=36)
+    finally:
+        ops.FUSED_PIPTRACK = True
+    assert torch.equal(i0, i1) and torch.equal(v0, v1)
+    k_lo, k_hi = plan.piptrack_bin_range(float(sr), 2048)
+    T = n // 512
+    o = ops.frames_fft(xs, 2048, 512, T, torch.hann_window, spec_power=1, piptrack=dict(k_lo=k_lo, k_hi=k_hi, threshold=0.1, sr=sr))
+    S = o["spec"]
+    import ctypes as C
+
+    from ssar_b200 import _cabi as cabi
+    cap = o["pip_pitch"].shape[1]
+    pitch, mag = torch.empty_like(o["pip_pitch"]), torch.empty_like(o["pip_mag"])
+    count = torch.empty_like(o["pip_count"])
+    cabi.call("ssar_piptrack", cabi.ptr(S), cabi.i64(S.shape[2]), cabi.i32(4), cabi.i32(T), cabi.i32(S.shape[2]), cabi.i32(k_lo),
+              cabi.i32(k_hi), cabi.f32(0.1), cabi.f32(float(sr)), cabi.i32(2048), cabi.i64(cap), cabi.ptr(pitch), cabi.ptr(mag),
+              cabi.ptr(count))
+    assert torch.equal(count, o["pip_count"]) and int(count.min()) > 0
+    for c in range(4):
+        m = int(count[c])
+        a = torch.stack([pitch[c, :m], mag[c, :m]], 1).cpu()
+        b = torch.stack([o["pip_pitch"][c, :m], o["pip_mag"][c, :m]], 1).cpu()
+        key = lambda t: t[torch.argsort(t[:, 0] * 1e3 + t[:, 1], stable=True)]
+        assert torch.equal(torch.sort(a[:, 0]).values, torch.sort(b[:, 0]).values)
+        assert torch.equal(torch.sort(a[:, 1]).values, torch.sort(b[:, 1]).values)
