@@ -123,6 +123,13 @@ typedef struct {
                                [n_clips, aux_frames, ...]: one launch then serves stft (1 + N/hop frames, complex) and the
                                spectrogram-style features that drop the last frame (rosa/spectral.py:60) of the same signal */
     ssar_piptrack_epilogue pip;
+    /* RAGGED batches (clips of different lengths in one launch; both NULL = every clip has n_samples / n_frames):
+       clip c holds clip_samples[c] <= n_samples valid samples (reflect padding happens at ITS end) and produces
+       clip_frames[c] <= n_frames frames (its aux outputs cover clip_frames[c] - (n_frames - aux_frames) frames).  Rows of
+       frames beyond a clip's count are written as ZEROS in every output, so whole-tensor maxima of the non-negative
+       spectra and every later kernel that honours the same lengths see exactly what a per-clip call would.  Device arrays. */
+    const long long* clip_samples;
+    const int* clip_frames;
 } ssar_frames_args;
 
 int ssar_frames_fft(const ssar_frames_args* args, void* stream);
@@ -181,8 +188,10 @@ int ssar_rms_frames(const float* x, long long n_samples, long long clip_stride, 
 /* rosa/spectral.py:145-161 hpss on a complex STFT [n_clips, n_frames, ld] (complex, frame-major): 31-tap medians
  * along time / frequency (features/processing.py:74-84, reflect padding) + soft masks (rosa/spectral.py:120-142,
  * power 2, margin).  Either output may be NULL.  Outputs have the input's layout. */
+/* clip_frames: NULL, or int [n_clips] (device) for a RAGGED batch: clip c has clip_frames[c] <= n_frames frames (the time
+ * medians reflect at ITS last frame); the rows beyond are written as zeros. */
 int ssar_hpss(const float* stft, int n_clips, int n_frames, int n_bins, long long ld, float margin_harm,
-              float margin_perc, float* out_harm, float* out_perc, void* stream);
+              float margin_perc, float* out_harm, float* out_perc, const int* clip_frames, void* stream);
 
 /* torch.istft (rosa/spectral.py:24-32), step 1: per-frame inverse real FFT times the synthesis window.
  * spec: complex [n_clips, n_frames, ld]; frames: [n_clips, n_frames, n_fft]. n_fft 1024 or 2048. */
@@ -193,13 +202,16 @@ int ssar_irfft_frames(const float* spec, long long ld, int n_clips, int n_frames
  * synthesis window, overlap-add, division by the summed squared window, centre trim — the [frames, n_fft] intermediate
  * of ssar_irfft_frames + ssar_overlap_add is never written.  spec: frame-major complex [n_clips, n_frames, ld];
  * out [n_clips, length] (length even, 8-byte aligned). */
+/* clip_frames / clip_len: NULL, or device arrays [n_clips] for a RAGGED batch (clip c: clip_frames[c] <= n_frames frames,
+ * clip_len[c] <= length samples; the tail of its output row is zeros). */
 int ssar_istft_half_overlap(const float* spec, long long ld, int n_clips, int n_frames, int n_fft, const float* window,
-                            const float* twiddle, long long length, float* out, void* stream);
+                            const float* twiddle, long long length, float* out, const int* clip_frames,
+                            const long long* clip_len, void* stream);
 
 /* torch.istft step 2: overlap-add of `frames`, division by the summed squared window, drop n_fft/2 leading
  * samples, produce `length` samples per clip (zeros past the covered range). out: [n_clips, length]. */
 int ssar_overlap_add(const float* frames, const float* window, int n_clips, int n_frames, int n_fft, int hop,
-                     long long length, float* out, void* stream);
+                     long long length, float* out, const int* clip_frames, const long long* clip_len, void* stream);
 
 /* torchaudio lfilter for one biquad (features/processing.py:141-150): coefficients already divided by a0.
  * scratch: ssar_biquad_scratch_bytes(n_clips, n_samples) bytes of device memory.  y must not alias x. */
@@ -211,9 +223,11 @@ int ssar_biquad(const float* x, long long n_samples, long long stride_x, int n_c
 /* torchaudio.functional.resample (supervised/data.py:63; rosa/constantq.py:83) with banded polyphase taps:
  * taps [max_taps, newf] tap-major, first [newf] = index of the first kept tap of each phase in torchaudio's
  * dense kernel; y[j] = post_scale * sum_k taps[k][j % newf] * xpad[(j / newf) * orig + first + k]. */
+/* clip_n_in: NULL, or long long [n_clips] (device) for a RAGGED batch: clip c holds clip_n_in[c] <= n_in samples followed by
+ * zeros; its outputs past ceil(newf * clip_n_in[c] / orig) are written as zeros. */
 int ssar_resample(const float* x, long long n_in, long long stride_in, int n_clips, const float* taps,
                   const int* first, int orig, int newf, int width, int max_taps, float post_scale, float* y,
-                  long long n_out, long long stride_out, void* stream);
+                  long long n_out, long long stride_out, const long long* clip_n_in, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Tuning estimate, chroma, CENS, tonnetz
@@ -246,8 +260,10 @@ int ssar_chroma_from_cqt(const float* cqt, long long ldc, int n_clips, int n_fra
 
 /* rosa/spectral.py:273-280: correlation along time with window[win_len] (already normalised), zero "same" padding,
  * then (l2_normalize) division by the per-frame L2 norm.  q, out: [n_clips, n_frames, n_chroma]. */
+/* clip_frames: NULL, or int [n_clips] (device) for a RAGGED batch (the zero padding starts at each clip's own last frame;
+ * rows past it are written as zeros). */
 int ssar_cens_smooth(const float* q, int n_clips, int n_frames, int n_chroma, const float* window, int win_len,
-                     int l2_normalize, float* out, void* stream);
+                     int l2_normalize, float* out, const int* clip_frames, void* stream);
 
 /* features/audio.py:48-57 tonnetz: out[row] = phi[n_out, n_chroma] @ (chroma[row] / ||chroma[row]||_1) */
 int ssar_tonnetz(const float* chroma, long long n_rows, int n_chroma, const float* phi, int n_out, float* out,
@@ -280,12 +296,15 @@ int ssar_contrast_finish(const float* peak, const float* valley, const uint32_t*
 /* features/processing.py:10-48 gaussian_filter along time of [n_clips, n_frames, inner]: weights [2*radius+1] are
  * the normalised taps (built by the host exactly like :21-24); mode 0 circular (default), 1 reflect, 2 replicate;
  * radius > n_frames reproduces the short-sequence branch (:30-35: mode-pad by n_frames, then replicate). */
+/* clip_frames: NULL, or int [n_clips] (device) for a RAGGED batch: clip c has clip_frames[c] <= n_frames rows (the wrap /
+ * reflection happens at ITS length); the rows beyond are written as zeros. */
 int ssar_gauss1d(const float* x, int n_clips, int n_frames, long long inner, const float* weights, int radius,
-                 int mode, float* out, void* stream);
+                 int mode, float* out, const int* clip_frames, void* stream);
 
 /* per-(clip, column) minimum / maximum -> [n_clips, n_cols] (either output may be NULL) */
+/* clip_frames: NULL, or int [n_clips] (device) for a RAGGED batch: only the first clip_frames[c] rows of clip c are real. */
 int ssar_col_minmax(const float* x, int n_clips, int n_frames, int n_cols, float* min_out, float* max_out,
-                    void* stream);
+                    const int* clip_frames, void* stream);
 
 /* per-(clip, column) quantile by radix select (exact order statistics).
  *   subset 0: all non-NaN values; 1: strict interior local maxima (features/processing.py:107-115)
@@ -293,8 +312,10 @@ int ssar_col_minmax(const float* x, int n_clips, int n_frames, int n_cols, float
  *             (ssar/analysis/efficient_quantile/efficient_quantile.cpp:72-75, wrapper __init__.py:5-6)
  *   pre_sub/pre_div [n_clips, n_cols] or NULL: select on (x - pre_sub) / pre_div (emphasize, :133-137)
  *   count_out [n_clips, n_cols] or NULL: size of the subset (0 -> out = NaN; the host raises like torch) */
+/* clip_frames: NULL, or int [n_clips] (device) for a RAGGED batch: only the first clip_frames[c] rows of clip c are real. */
 int ssar_col_quantile(const float* x, int n_clips, int n_frames, int n_cols, int subset, double q, int interp,
-                      const float* pre_sub, const float* pre_div, float* out, int* count_out, void* stream);
+                      const float* pre_sub, const float* pre_div, float* out, int* count_out,
+                      const int* clip_frames, void* stream);
 
 /* torch.clamp by per-(clip, column) bounds [n_clips, n_cols] (features/processing.py:117,124-129) */
 int ssar_clamp_cols(const float* x, int n_clips, int n_frames, int n_cols, const float* lo, const float* hi,
@@ -306,8 +327,10 @@ int ssar_normalize(const float* x, int n_clips, long long n_per_clip, const uint
                    const uint32_t* max_key, float eps, float* out, void* stream);
 
 /* features/processing.py:132-138 emphasize; col_min/col_max from ssar_col_minmax; scratch: 2*n_clips*n_cols floats */
+/* clip_frames: NULL, or int [n_clips] (device) for a RAGGED batch: only the first clip_frames[c] rows of clip c are real. */
 int ssar_emphasize(const float* x, int n_clips, int n_frames, int n_cols, const float* col_min,
-                   const float* col_max, float strength, double q, float* scratch, float* out, void* stream);
+                   const float* col_max, float strength, double q, float* scratch, float* out,
+                   const int* clip_frames, void* stream);
 
 /* features/processing.py:88-89 spectral_flux: out[t] = x[t+1] - x[t] with a zero row appended */
 int ssar_spectral_flux(const float* x, int n_clips, int n_frames, long long inner, float* out, void* stream);
@@ -317,16 +340,20 @@ int ssar_hwr_rowsum(const float* x, long long n_rows, int inner, float* out, voi
 
 /* ssar/supervised/data.py:317-319 dataset statistics: accumulates (count, sum, sum of squares) per column in fp64
  * into stats[3, n_cols] (caller zeroes it; all-reduce it over ranks, then mean = s/n, std = sqrt(ss/n - mean^2)) */
-int ssar_feature_stats(const float* x, long long n_rows, int n_cols, double* stats, void* stream);
+/* clip_frames: NULL, or int [n_rows / frames_per_clip] (device) for a RAGGED batch: rows t >= clip_frames[c] of clip c are
+ * skipped (x is [n_clips, frames_per_clip, n_cols]). */
+int ssar_feature_stats(const float* x, long long n_rows, int n_cols, double* stats, int frames_per_clip,
+                       const int* clip_frames, void* stream);
 
 /* ssar/random/mir.py:14-22 (salience_weighted) after the three Gaussians (ssar_gauss1d: sigma 2 circular -> env, then
  * sigma 5 and sigma 80 in reflect mode of env): out = (smooth_short / smooth_long)^2 * env for a batch of feature matrices
  * [n_clips, n_frames, n_cols] whose columns are grouped into features (col_group[n_cols] in [0, n_groups)), plus the
  * running min / max of every (clip, group) as order-preserving keys [n_clips, n_groups] (ssar_fill_u32 them with
  * 0xFF800000 / 0x007FFFFF first). */
+/* clip_frames: NULL, or int [n_clips] (device) for a RAGGED batch: only the first clip_frames[c] rows of clip c are real. */
 int ssar_salience_weight(const float* env, const float* smooth_short, const float* smooth_long, int n_clips, int n_frames,
                          int n_cols, const int* col_group, int n_groups, float* out, uint32_t* min_key, uint32_t* max_key,
-                         void* stream);
+                         const int* clip_frames, void* stream);
 
 /* ssar/random/mir.py:44's closing normalize (features/processing.py:52-55) per (clip, feature): (w - min) / ((max - min) +
  * eps) with the keys of ssar_salience_weight.  group_start[n_groups]: first column of each group (groups are contiguous
@@ -477,7 +504,10 @@ int ssar_slerp_loops(const float* y, int n_latents, int n_layers, int latent_dim
 
 /* processing.py:52-55 normalize for per-clip arrays of <= 262 144 elements: min, max and the rescale in ONE launch (one
  * CTA per clip) — same result as ssar_minmax_keys + ssar_normalize.                                                  */
-int ssar_normalize_fused(const float* x, int n_clips, long long n_per_clip, float eps, float* out, void* stream);
+/* clip_rows: NULL, or int [n_clips] (device) for a RAGGED batch: the first clip_rows[c] * row_elems elements of clip c are
+ * real (min / max over them only); the rest of the row is written as zeros. */
+int ssar_normalize_fused(const float* x, int n_clips, long long n_per_clip, float eps, float* out,
+                         const int* clip_rows, long long row_elems, void* stream);
 
 /* ssar_biquad that also leaves the sums of squares of its (clamped) output per 1024-sample block in
  * block_ss [n_clips, ceil(n_samples / 1024) + 2] (the last two entries of a row are y[0] and y[1024]); y may be NULL when
@@ -498,11 +528,14 @@ int ssar_rms_from_block_ss(const float* block_ss, long long n_blocks, int n_clip
  * a slot = Re / Im of basis_scale * b[r, :], rows 72..79 zero), fp32 = hi + lo.  clip_slot: int32 [n_clips] (device; the
  * tuning index of each clip) or NULL.  out: [n_clips, n_frames, 36 * n_octaves, 2].  tcgen05.mma kind::f16 on 3-term
  * fp16 splits of both operands with fp32 accumulation; TMA tensor maps with overlapping rows read the frames straight
- * from the padded signals.  scratch: ssar_cqt_tc_scratch_bytes(...) bytes.                                          */
+ * from the padded signals.  scratch: ssar_cqt_tc_scratch_bytes(...) bytes.  clip_samples / clip_frames: NULL, or device
+ * arrays [n_clips] for a RAGGED batch (octave-0 samples of each clip — octave o holds ceil(.. / 2^o) — and its frame count;
+ * reflection at the clip's own end, rows past its frame count written as zeros).                                     */
 long long ssar_cqt_tc_scratch_bytes(int n_clips, const long long* n_samples, int n_octaves);
 int ssar_cqt_tc(const float* const* signals, const long long* n_samples, int n_octaves, int n_clips, int hop, int n_frames,
                 const void* basis_hi, const void* basis_lo, int n_slots, const int* clip_slot, const float* row_scale,
-                long long row_scale_ld, float basis_scale, void* scratch, float* out, void* stream);
+                long long row_scale_ld, float basis_scale, void* scratch, float* out, const long long* clip_samples,
+                const int* clip_frames, void* stream);
 
 /* maua/maua/GAN/wrappers/stylegan2.py:193-210 make_noise_pyramid (normalize = 1) and the synthesizer's own resize of a
  * mismatched noise input, :86-96 (normalize = 0): noise [n_frames, in_h, in_w] -> outs[l] [n_frames, heights[l], widths[l]]

@@ -77,12 +77,18 @@ __global__ void __launch_bounds__(CQ_WARPS * 32) chroma_quant_kernel(
 }
 
 // block = (32 lanes over chroma, 8 frames)
-__global__ void cens_smooth_kernel(const float* __restrict__ q, int n_frames, int n_chroma, const float* __restrict__ win,
-                                   int win_len, int do_l2, float* __restrict__ out) {
+__global__ void cens_smooth_kernel(const float* __restrict__ q, int cap_frames, int n_chroma, const float* __restrict__ win,
+                                   int win_len, int do_l2, float* __restrict__ out, const int* __restrict__ clip_frames) {
     const int clip = blockIdx.y;
     const int t = blockIdx.x * blockDim.y + threadIdx.y;
     const int l = threadIdx.x;
-    const float* qc = q + (long long)clip * n_frames * n_chroma;
+    const float* qc = q + (long long)clip * cap_frames * n_chroma;
+    // ragged batches: the zero "same" padding starts at the clip's own last frame; rows past it are written as zeros
+    const int n_frames = clip_frames ? __ldg(clip_frames + clip) : cap_frames;
+    if (t >= n_frames) {
+        if (t < cap_frames && l < n_chroma) out[((long long)clip * cap_frames + t) * n_chroma + l] = 0.f;
+        return;
+    }
     float v = 0.f;
     if (t < n_frames && l < n_chroma) {
         const int left = (win_len - 1) / 2;  // conv1d padding="same": total pad = win_len - 1, left = total / 2
@@ -93,7 +99,7 @@ __global__ void cens_smooth_kernel(const float* __restrict__ q, int n_frames, in
     }
     const float ss = warp_sum((t < n_frames && l < n_chroma) ? v * v : 0.f);
     if (t < n_frames && l < n_chroma)
-        out[((long long)clip * n_frames + t) * n_chroma + l] = do_l2 ? v / sqrtf(ss) : v;
+        out[((long long)clip * cap_frames + t) * n_chroma + l] = do_l2 ? v / sqrtf(ss) : v;
 }
 
 __global__ void tonnetz_kernel(const float* __restrict__ chroma, long long n_rows, int n_chroma, const float* __restrict__ phi,
@@ -140,13 +146,14 @@ extern "C" int ssar_chroma_from_cqt(const float* cqt, long long ldc, int n_clips
 }
 
 extern "C" int ssar_cens_smooth(const float* q, int n_clips, int n_frames, int n_chroma, const float* window, int win_len,
-                                int l2_normalize, float* out, void* stream) {
+                                int l2_normalize, float* out, const int* clip_frames, void* stream) {
     if (n_clips == 0 || n_frames == 0) return SSAR_OK;
     SSAR_REQUIRE(q && window && out && q != out, "cens_smooth: null pointer or aliasing");
     SSAR_REQUIRE(n_chroma > 0 && n_chroma <= 32 && win_len > 0, "cens_smooth: bad sizes");
     dim3 block(32, 8);
     dim3 grid(ssar_div_up(n_frames, 8), n_clips);
-    cens_smooth_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(q, n_frames, n_chroma, window, win_len, l2_normalize, out);
+    cens_smooth_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(q, n_frames, n_chroma, window, win_len, l2_normalize, out,
+                                                                 clip_frames);
     return ssar_launch_status("cens_smooth");
 }
 

@@ -78,10 +78,17 @@ __global__ void cqt_amax_kernel(const float* __restrict__ x, long long n, uint32
 // n + 1024), i.e. torch.stft's centre padding baked in, so frame t starts at row offset t * hop_i.
 // Four samples per thread (64-bit stores); the interior takes a path without the reflection arithmetic.
 __global__ void cqt_split_kernel(const CqtOctaves oc, int n_clips, const uint32_t* __restrict__ amax,
-                                 __half* __restrict__ hi, __half* __restrict__ lo) {
+                                 __half* __restrict__ hi, __half* __restrict__ lo, const long long* __restrict__ clip_samples) {
     const int o = blockIdx.z, clip = blockIdx.y;
-    const long long n = oc.n_samples[o], lp = oc.padded[o];
-    const float* __restrict__ src = oc.signal[o] + (long long)clip * n;
+    const long long lp = oc.padded[o];
+    const float* __restrict__ src = oc.signal[o] + (long long)clip * oc.n_samples[o];
+    // ragged batches: the clip's own length at this octave (each decimation halves, rounding up) — the reflection
+    // happens at ITS end
+    long long n = oc.n_samples[o];
+    if (clip_samples) {
+        n = __ldg(clip_samples + clip);
+        for (int q = 0; q < o; ++q) n = (n + 1) >> 1;
+    }
     const float s = clip_scale(__ldg(amax + clip));
     __half* h = hi + oc.offset[o] + (long long)clip * lp;
     __half* l = lo + oc.offset[o] + (long long)clip * lp;
@@ -117,7 +124,7 @@ struct CqShared {
 __global__ void __launch_bounds__(CQ_THREADS, 1)
 cqt_tc_kernel(const __grid_constant__ CqtMaps maps, int n_oct, int n_clips, int n_frames, const int* __restrict__ clip_slot,
               const uint32_t* __restrict__ amax, const float* __restrict__ row_scale, long long row_scale_ld,
-              float basis_scale_inv, float* __restrict__ out) {
+              float basis_scale_inv, float* __restrict__ out, const int* __restrict__ clip_frames) {
     extern __shared__ __align__(1024) uint8_t cq_smem_raw[];
     uint8_t* ring = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(cq_smem_raw) + 1023) & ~(uintptr_t)1023);
     CqShared* sh = reinterpret_cast<CqShared*>(ring + (size_t)CQ_STAGES * CQ_STAGE_BYTES);
@@ -218,7 +225,10 @@ cqt_tc_kernel(const __grid_constant__ CqtMaps maps, int n_oct, int n_clips, int 
             const int col0 = n_bins - CQ_ROWS * (o + 1);  // octave o fills bins [col0, col0 + 36) (constantq.py:100-104)
             const int t = mt * CQ_BM + quad * 32 + lane;
             // sqrt(2^o) (basis gain, :97) / sqrt(filter length) (:113), and the operand scales undone
-            const float gain = sqrtf((float)(1 << o)) * basis_scale_inv / clip_scale(__ldg(amax + clip));
+            // (ragged batches: frames past the clip's own count are written as zeros)
+            const float gain = (clip_frames && t >= __ldg(clip_frames + clip))
+                                   ? 0.f
+                                   : sqrtf((float)(1 << o)) * basis_scale_inv / clip_scale(__ldg(amax + clip));
             const float* __restrict__ rs = row_scale + (long long)slot * row_scale_ld + col0;
             mbar_wait(&sh->acc_full[acc], acc_phase);
             tc_fence_after();
@@ -272,7 +282,7 @@ extern "C" long long ssar_cqt_tc_scratch_bytes(int n_clips, const long long* n_s
 extern "C" int ssar_cqt_tc(const float* const* signals, const long long* n_samples, int n_octaves, int n_clips, int hop,
                            int n_frames, const void* basis_hi, const void* basis_lo, int n_slots, const int* clip_slot,
                            const float* row_scale, long long row_scale_ld, float basis_scale, void* scratch, float* out,
-                           void* stream) {
+                           const long long* clip_samples, const int* clip_frames, void* stream) {
     if (n_clips == 0 || n_frames == 0) return SSAR_OK;
     SSAR_REQUIRE(signals && n_samples && basis_hi && basis_lo && row_scale && scratch && out, "cqt_tc: null pointer");
     SSAR_REQUIRE(n_octaves >= 1 && n_octaves <= CQ_MAX_OCT, "cqt_tc: 1..%d octaves", CQ_MAX_OCT);
@@ -310,7 +320,7 @@ extern "C" int ssar_cqt_tc(const float* const* signals, const long long* n_sampl
         cqt_amax_kernel<<<dim3(gx, n_clips), 256, 0, st>>>(signals[0], n_samples[0], amax);
         int sx = ssar_div_up(oc.padded[0] / 4, 256);
         if (sx > SSAR_NUM_SMS * 8) sx = SSAR_NUM_SMS * 8;
-        cqt_split_kernel<<<dim3(sx, n_clips, n_octaves), 256, 0, st>>>(oc, n_clips, amax, hi, lo);
+        cqt_split_kernel<<<dim3(sx, n_clips, n_octaves), 256, 0, st>>>(oc, n_clips, amax, hi, lo, clip_samples);
     }
     EncodeTiledFn enc = get_encode_fn();
     if (!enc) {
@@ -357,6 +367,6 @@ extern "C" int ssar_cqt_tc(const float* const* signals, const long long* n_sampl
     const long long items = (long long)n_octaves * n_clips * ((n_frames + CQ_BM - 1) / CQ_BM);
     const int grid = (int)(items < SSAR_NUM_SMS ? items : SSAR_NUM_SMS);
     cqt_tc_kernel<<<grid, CQ_THREADS, smem, st>>>(maps, n_octaves, n_clips, n_frames, clip_slot, amax, row_scale, row_scale_ld,
-                                                 1.f / basis_scale, out);
+                                                 1.f / basis_scale, out, clip_frames);
     return ssar_launch_status("cqt_tc");
 }

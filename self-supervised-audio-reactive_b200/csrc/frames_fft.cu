@@ -52,15 +52,18 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
          fbase += (long long)gridDim.x * L::WPB * FPW) {
         // ------------------------------------------------------------------ load + window (lane: n = n1 + N1 r)
         const long long f = fbase + h;
-        const bool active = f < total_frames;
-        const int clip = active ? (int)(f / a.n_frames) : 0;
-        const int t = active ? (int)(f - (long long)clip * a.n_frames) : 0;
+        const bool in_grid = f < total_frames;
+        const int clip = in_grid ? (int)(f / a.n_frames) : 0;
+        const int t = in_grid ? (int)(f - (long long)clip * a.n_frames) : 0;
+        // ragged batches: frames past the clip's own count transform zeros (and write zero rows below)
+        const bool active = in_grid && (!a.clip_frames || t < __ldg(a.clip_frames + clip));
+        const long long n_samples = a.clip_samples ? __ldg(a.clip_samples + clip) : a.n_samples;
         float2 v[32];
         float ss = 0.f;
         if (active) {
             const float* __restrict__ xc = a.x + (long long)clip * a.clip_stride;
             const long long start = (long long)t * a.hop - M;
-            const bool interior = start >= 0 && start + N <= a.n_samples;
+            const bool interior = start >= 0 && start + N <= n_samples;
             const bool vec = interior && ((((long long)clip * a.clip_stride + start) & 1LL) == 0) &&
                              ((reinterpret_cast<uintptr_t>(a.x) & 7) == 0);
             if (vec) {
@@ -77,8 +80,8 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
 #pragma unroll
                 for (int r = 0; r < 32; ++r) {
                     const int n = n1 + N1 * r;
-                    v[r] = make_float2(__ldg(xc + ssar_reflect(start + 2 * n, a.n_samples)),
-                                       __ldg(xc + ssar_reflect(start + 2 * n + 1, a.n_samples)));
+                    v[r] = make_float2(__ldg(xc + ssar_reflect(start + 2 * n, n_samples)),
+                                       __ldg(xc + ssar_reflect(start + 2 * n + 1, n_samples)));
                 }
             }
             if (a.out_rms) {
@@ -109,7 +112,7 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
         if (a.out_rms) {
 #pragma unroll
             for (int o = N1 / 2; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-            if (active && n1 == 0 && t < aux_frames) a.out_rms[(long long)clip * aux_frames + t] = sqrtf(ss / (float)N);
+            if (in_grid && n1 == 0 && t < aux_frames) a.out_rms[(long long)clip * aux_frames + t] = sqrtf(ss / (float)N);
         }
 
         // ------------------------------------------------------------------ per frame: untangle + epilogues, 32 lanes wide
@@ -121,6 +124,10 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
             const int ft = (int)(ff - (long long)fclip * a.n_frames);
             const long long crow = (long long)fclip * a.n_frames + ft;  // row of the complex output
             const long long orow = (long long)fclip * aux_frames + ft;  // row of every other output
+            // ragged: this clip's own frame count; its aux outputs stop (n_frames - aux_frames) frames earlier.  A frame past
+            // the count carries an all-zero spectrum: it is written (zero rows) but feeds no maximum and no peak list
+            const int cf = a.clip_frames ? __ldg(a.clip_frames + fclip) : a.n_frames;
+            const bool valid = ft < cf - (a.n_frames - aux_frames);
             const bool aux = ft < aux_frames;                            // warp-uniform
             float2* z = zw + fs * ZF;
 
@@ -225,7 +232,7 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
                         bmax = fmaxf(bmax, acc);
                     }
                 }
-                if (fb.max_key) {
+                if (fb.max_key && valid) {
                     bmax = warp_max(bmax);
                     if (lane == 0) atomic_max_key(fb.max_key + fclip, bmax);
                 }
@@ -233,7 +240,7 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
 
             // epilogue 2b: piptrack on the magnitudes sqrt(power tile) (rosa/pitch.py:27-83; tuning.cu's piptrack_kernel
             // reads the same values back from a [frames, 1025] spectrogram in HBM)
-            if (a.pip.count && aux) {
+            if (a.pip.count && aux && valid) {
                 const ssar_piptrack_epilogue& pp = a.pip;
                 float mxp = 0.f;
                 for (int k = lane; k < NBINS; k += 32) mxp = fmaxf(mxp, pw[k]);

@@ -73,15 +73,30 @@ __device__ __forceinline__ float softmask2(float X, float Xref, float split) {
     return __fdividef(m, m + r);
 }
 
-__global__ void __launch_bounds__(HP_THREADS, 2) hpss_kernel(const float2* __restrict__ D, int n_frames, int n_bins,
+__global__ void __launch_bounds__(HP_THREADS, 2) hpss_kernel(const float2* __restrict__ D, int cap_frames, int n_bins,
                                                              long long ld, float margin_h, float margin_p,
-                                                             float2* __restrict__ out_h, float2* __restrict__ out_p) {
+                                                             float2* __restrict__ out_h, float2* __restrict__ out_p,
+                                                             const int* __restrict__ clip_frames) {
     __shared__ float mag[ROWS * LDS];
     __shared__ float gh[TT * LDG];  // harmonic medians, then harmonic gains
     __shared__ float gp[TT * LDG];  // percussive gains
     const int clip = blockIdx.z;
     const int t0 = blockIdx.y * TT, f0 = blockIdx.x * TF;
-    const float2* Dc = D + (long long)clip * n_frames * ld;
+    const float2* Dc = D + (long long)clip * cap_frames * ld;
+    // ragged batches: the clip's own frame count bounds the time axis (reflection at ITS last frame); rows of the
+    // capacity beyond it are written as zeros
+    const int n_frames = clip_frames ? __ldg(clip_frames + clip) : cap_frames;
+    if (t0 >= n_frames) {
+        for (int o = threadIdx.x; o < TT * TF; o += HP_THREADS) {
+            const int r = o / TF, c = o - r * TF;
+            const int t = t0 + r, f = f0 + c;
+            if (t >= cap_frames || f >= n_bins) continue;
+            const long long idx = ((long long)clip * cap_frames + t) * ld + f;
+            if (out_h) out_h[idx] = make_float2(0.f, 0.f);
+            if (out_p) out_p[idx] = make_float2(0.f, 0.f);
+        }
+        return;
+    }
 
     const bool interior = t0 >= HALF && t0 + TT + HALF <= n_frames && f0 >= HALF && f0 + TF + HALF <= n_bins;
     if (interior) {  // no reflection / clamping anywhere in the tile: plain strided rows
@@ -135,8 +150,13 @@ __global__ void __launch_bounds__(HP_THREADS, 2) hpss_kernel(const float2* __res
     for (int o = threadIdx.x; o < TT * TF; o += HP_THREADS) {
         const int r = o / TF, c = o - r * TF;
         const int t = t0 + r, f = f0 + c;
-        if (t >= n_frames || f >= n_bins) continue;
-        const long long idx = ((long long)clip * n_frames + t) * ld + f;
+        if (t >= cap_frames || f >= n_bins) continue;
+        const long long idx = ((long long)clip * cap_frames + t) * ld + f;
+        if (t >= n_frames) {  // (ragged) past this clip's end
+            if (out_h) out_h[idx] = make_float2(0.f, 0.f);
+            if (out_p) out_p[idx] = make_float2(0.f, 0.f);
+            continue;
+        }
         const float2 z = __ldg(&D[idx]);
         const float S = mag[(r + HALF) * LDS + c + HALF];
         float2 ph = make_float2(1.f, 0.f);
@@ -158,7 +178,7 @@ __global__ void __launch_bounds__(HP_THREADS, 2) hpss_kernel(const float2* __res
 }  // namespace
 
 extern "C" int ssar_hpss(const float* stft, int n_clips, int n_frames, int n_bins, long long ld, float margin_harm,
-                         float margin_perc, float* out_harm, float* out_perc, void* stream) {
+                         float margin_perc, float* out_harm, float* out_perc, const int* clip_frames, void* stream) {
     if (n_clips == 0 || n_frames == 0) return SSAR_OK;
     SSAR_REQUIRE(stft && (out_harm || out_perc), "hpss: null pointer");
     SSAR_REQUIRE(n_frames > HALF && n_bins > HALF, "hpss: reflect padding of 15 needs more than 15 frames and bins");
@@ -166,6 +186,6 @@ extern "C" int ssar_hpss(const float* stft, int n_clips, int n_frames, int n_bin
     dim3 grid(ssar_div_up(n_bins, TF), ssar_div_up(n_frames, TT), n_clips);
     hpss_kernel<<<grid, HP_THREADS, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float2*>(stft), n_frames, n_bins, ld,
                                                        margin_harm, margin_perc, reinterpret_cast<float2*>(out_harm),
-                                                       reinterpret_cast<float2*>(out_perc));
+                                                       reinterpret_cast<float2*>(out_perc), clip_frames);
     return ssar_launch_status("hpss");
 }

@@ -91,16 +91,22 @@ __global__ void __launch_bounds__(256, 2) irfft_frames_kernel(const float2* __re
     }
 }
 
+// Ragged batches (all three overlap-add kernels and the fused inverse): clip c has clip_frames[c] <= n_frames frames and
+// clip_len[c] <= length output samples; frames / samples beyond them do not exist (no contribution to the sums or the
+// window envelope) and the tail of the output row is written as zeros.  Both NULL = uniform batch.
 __global__ void overlap_add_kernel(const float* __restrict__ frames, const float* __restrict__ win, int n_fft, int hop,
-                                   int n_frames, long long length, float* __restrict__ out) {
+                                   int cap_frames, long long length, float* __restrict__ out,
+                                   const int* __restrict__ clip_frames, const long long* __restrict__ clip_len) {
     const int clip = blockIdx.y;
-    const float* fc = frames + (long long)clip * n_frames * n_fft;
+    const float* fc = frames + (long long)clip * cap_frames * n_fft;
     float* oc = out + (long long)clip * length;
+    const int n_frames = clip_frames ? __ldg(clip_frames + clip) : cap_frames;
+    const long long len_c = clip_len ? __ldg(clip_len + clip) : length;
     const long long total = (long long)n_fft + (long long)hop * (n_frames - 1);
     for (long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x; n < length; n += (long long)gridDim.x * blockDim.x) {
         const long long p = n + n_fft / 2;
         float acc = 0.f, env = 0.f;
-        if (p < total) {
+        if (p < total && n < len_c) {
             long long t_hi = p / hop;
             if (t_hi > n_frames - 1) t_hi = n_frames - 1;
             long long t_lo = (p - n_fft + hop) / hop;  // ceil((p - n_fft + 1)/hop) for p - n_fft + 1 > 0
@@ -123,12 +129,16 @@ __global__ void overlap_add_kernel(const float* __restrict__ frames, const float
 constexpr int OD_SEG = 8;
 __global__ void __launch_bounds__(32 * OD_SEG) overlap_add_dense_kernel(const float* __restrict__ frames,
                                                                         const float* __restrict__ win, int n_fft, int hop,
-                                                                        int n_frames, long long length,
-                                                                        float* __restrict__ out) {
+                                                                        int cap_frames, long long length,
+                                                                        float* __restrict__ out,
+                                                                        const int* __restrict__ clip_frames,
+                                                                        const long long* __restrict__ clip_len) {
     __shared__ float sacc[OD_SEG][32], senv[OD_SEG][32];
     const int clip = blockIdx.y, seg = threadIdx.y;
-    const float* fc = frames + (long long)clip * n_frames * n_fft;
+    const float* fc = frames + (long long)clip * cap_frames * n_fft;
     float* oc = out + (long long)clip * length;
+    const int n_frames = clip_frames ? __ldg(clip_frames + clip) : cap_frames;
+    const long long len_c = clip_len ? __ldg(clip_len + clip) : length;
     const long long total = (long long)n_fft + (long long)hop * (n_frames - 1);
     // Persistent over 32-sample blocks (one full wave of CTAs instead of 1.1).  A sample covered by all n_fft / hop
     // frames sees the window in the same order whatever its position, so this warp's share of the envelope is computed
@@ -140,7 +150,7 @@ __global__ void __launch_bounds__(32 * OD_SEG) overlap_add_dense_kernel(const fl
         const long long n = blk * 32 + threadIdx.x;
         const long long p = n + n_fft / 2;
         float acc = 0.f, env = 0.f;
-        if (n < length && p < total) {
+        if (n < len_c && p < total) {
             long long t_hi = p / hop;
             if (t_hi > n_frames - 1) t_hi = n_frames - 1;
             long long t_lo = (p - n_fft + hop) / hop;
@@ -249,8 +259,10 @@ int launch_irfft(const float* spec, long long ld, const float* win, const float*
 
 __global__ void __launch_bounds__(256, 2) istft_half_overlap_kernel(const float2* __restrict__ X, long long ldx,
                                                                     const float* __restrict__ win,
-                                                                    const float2* __restrict__ tw, int n_clips, int n_frames,
-                                                                    long long length, float* __restrict__ out, int OLA_RUN) {
+                                                                    const float2* __restrict__ tw, int n_clips, int cap_frames,
+                                                                    long long length, float* __restrict__ out, int OLA_RUN,
+                                                                    const int* __restrict__ clip_frames,
+                                                                    const long long* __restrict__ clip_len) {
     constexpr int M = 1024;
     using L = WarpFft<M>;
     constexpr int ZF = L::ZF;
@@ -273,8 +285,10 @@ __global__ void __launch_bounds__(256, 2) istft_half_overlap_kernel(const float2
         const long long b0 = 1 + (run - (long long)clip * runs_per_clip) * OLA_RUN;
         long long b1 = b0 + OLA_RUN;  // exclusive
         if (b1 > n_blocks + 1) b1 = n_blocks + 1;
-        const float2* Xc = X + (long long)clip * n_frames * ldx;
+        const float2* Xc = X + (long long)clip * cap_frames * ldx;
         float* oc = out + (long long)clip * length;
+        const int n_frames = clip_frames ? __ldg(clip_frames + clip) : cap_frames;
+        const long long len_c = clip_len ? __ldg(clip_len + clip) : length;
         for (long long t = b0 - 1; t < b1; ++t) {
             const bool have = t < n_frames;          // frame t exists (warp-uniform)
             const bool have_prev = t - 1 < n_frames;  // frame t - 1 exists
@@ -305,8 +319,8 @@ __global__ void __launch_bounds__(256, 2) istft_half_overlap_kernel(const float2
                         env.y = fmaf(wc.y, wc.y, env.y);
                     }
                     const long long g = n0 + 2 * n;
-                    const float r0 = env.x > 1e-11f ? acc.x / env.x : 0.f;
-                    const float r1 = env.y > 1e-11f ? acc.y / env.y : 0.f;
+                    const float r0 = (env.x > 1e-11f && g < len_c) ? acc.x / env.x : 0.f;
+                    const float r1 = (env.y > 1e-11f && g + 1 < len_c) ? acc.y / env.y : 0.f;
                     if (g + 1 < length) {
                         *reinterpret_cast<float2*>(oc + g) = make_float2(r0, r1);
                     } else if (g < length) {
@@ -344,12 +358,13 @@ extern "C" int ssar_irfft_frames(const float* spec, long long ld, int n_clips, i
 
 extern "C" int ssar_istft_half_overlap(const float* spec, long long ld, int n_clips, int n_frames, int n_fft,
                                        const float* window, const float* twiddle, long long length, float* out,
-                                       void* stream) {
+                                       const int* clip_frames, const long long* clip_len, void* stream) {
     if (n_clips == 0 || length == 0) return SSAR_OK;
     SSAR_REQUIRE(spec && twiddle && out, "istft_half_overlap: null pointer");
     SSAR_REQUIRE(n_fft == 2048, "istft_half_overlap: n_fft must be 2048 (hop = 1024); use irfft_frames + overlap_add");
-    SSAR_REQUIRE(n_frames > 0 && length % 2 == 0 && ((uintptr_t)out % 8 == 0) && (!window || (uintptr_t)window % 8 == 0),
-                 "istft_half_overlap: needs an even length and 8-byte aligned buffers");
+    SSAR_REQUIRE(n_frames > 0 && (length % 2 == 0 || n_clips == 1) && ((uintptr_t)out % 8 == 0) &&
+                     (!window || (uintptr_t)window % 8 == 0),
+                 "istft_half_overlap: needs an even length (or a single clip) and 8-byte aligned buffers");
     using L = WarpFft<1024>;
     const size_t smem = ((size_t)32 * 32 + (size_t)L::WPB * (L::ZF + 512)) * sizeof(float2);
     cudaError_t e = cudaFuncSetAttribute(istft_half_overlap_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -377,17 +392,19 @@ extern "C" int ssar_istft_half_overlap(const float* spec, long long ld, int n_cl
     if (grid > (long long)SSAR_NUM_SMS * 2) grid = (long long)SSAR_NUM_SMS * 2;
     istft_half_overlap_kernel<<<(unsigned)grid, 256, smem, (cudaStream_t)stream>>>(
         reinterpret_cast<const float2*>(spec), ld, window, reinterpret_cast<const float2*>(twiddle), n_clips, n_frames, length,
-        out, OLA_RUN);
+        out, OLA_RUN, clip_frames, clip_len);
     return ssar_launch_status("istft_half_overlap");
 }
 
 extern "C" int ssar_overlap_add(const float* frames, const float* window, int n_clips, int n_frames, int n_fft, int hop,
-                                long long length, float* out, void* stream) {
+                                long long length, float* out, const int* clip_frames, const long long* clip_len,
+                                void* stream) {
     if (n_clips == 0 || length == 0) return SSAR_OK;
     SSAR_REQUIRE(frames && out, "overlap_add: null pointer");
     SSAR_REQUIRE(hop > 0 && n_fft > 0 && n_frames > 0, "overlap_add: bad sizes");
     const long long span = (long long)n_fft + (long long)hop * (n_frames - 1);
-    const bool vec4 = hop % 4 == 0 && n_fft % 8 == 0 && length % 4 == 0 && span < (1LL << 30) && length < (1LL << 30) &&
+    const bool vec4 = !clip_frames && !clip_len && hop % 4 == 0 && n_fft % 8 == 0 && length % 4 == 0 && span < (1LL << 30) &&
+                      length < (1LL << 30) &&
                       ((uintptr_t)frames % 16 == 0) && ((uintptr_t)out % 16 == 0) && (!window || (uintptr_t)window % 16 == 0);
     if (vec4) {
         int g4 = ssar_div_up(length / 4, 256);
@@ -401,11 +418,12 @@ extern "C" int ssar_overlap_add(const float* frames, const float* window, int n_
         const long long capd = ((long long)SSAR_NUM_SMS * 8 + n_clips - 1) / n_clips;  // 8 CTAs of 256 threads per SM
         if (gd > capd) gd = capd;
         overlap_add_dense_kernel<<<dim3((unsigned)gd, n_clips), dim3(32, OD_SEG), 0, (cudaStream_t)stream>>>(
-            frames, window, n_fft, hop, n_frames, length, out);
+            frames, window, n_fft, hop, n_frames, length, out, clip_frames, clip_len);
         return ssar_launch_status("overlap_add");
     }
     int gx = ssar_div_up(length, 256);
     if (gx > SSAR_NUM_SMS * 16) gx = SSAR_NUM_SMS * 16;
-    overlap_add_kernel<<<dim3(gx, n_clips), 256, 0, (cudaStream_t)stream>>>(frames, window, n_fft, hop, n_frames, length, out);
+    overlap_add_kernel<<<dim3(gx, n_clips), 256, 0, (cudaStream_t)stream>>>(frames, window, n_fft, hop, n_frames, length, out,
+                                                                            clip_frames, clip_len);
     return ssar_launch_status("overlap_add");
 }

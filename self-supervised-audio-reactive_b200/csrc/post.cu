@@ -32,23 +32,32 @@ __device__ __forceinline__ int pad_index(int v, int T, int radius, int mode) {
 // i = u mod TPT), so an input row costs one global load, one shared-memory tap read and TPT FMAs; every output still
 // accumulates its taps in ascending order, so the result does not depend on TPT.  TPT = 4 for the short kernels of the
 // [T, 59] smoothing, 16 for the long ones (sigma 80 of random/mir.py:14-22: 641 taps).
+// Ragged batches: clip_frames[c] <= T rows of clip c are real; the padding (wrap / reflection) happens at ITS length and the
+// rows beyond are written as zeros.
 template <int TPT>
-__global__ void gauss1d_kernel(const float* __restrict__ x, int T, long long inner, const float* __restrict__ w,
-                               int radius, int mode, float* __restrict__ out) {
+__global__ void gauss1d_kernel(const float* __restrict__ x, int cap_T, long long inner, const float* __restrict__ w,
+                               int radius, int mode, float* __restrict__ out, const int* __restrict__ clip_frames) {
     extern __shared__ float ws[];
     const int taps = 2 * radius + 1;
     for (int i = threadIdx.x; i < taps; i += blockDim.x) ws[i] = w[i];
     __syncthreads();
     const int clip = blockIdx.z;
-    const float* xc = x + (long long)clip * T * inner;
-    float* oc = out + (long long)clip * T * inner;
+    const float* xc = x + (long long)clip * cap_T * inner;
+    float* oc = out + (long long)clip * cap_T * inner;
+    const int T = clip_frames ? __ldg(clip_frames + clip) : cap_T;
     // (time block, column) pairs are packed into the CTA, columns fastest: narrow matrices ([T, 4] envelopes) still
     // fill their warps
     const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const long long tb = gid / inner;
     const long long j = gid - tb * inner;
-    if (tb * TPT >= T) return;
+    if (tb * TPT >= cap_T) return;
     const int t0 = (int)tb * TPT;
+    if (t0 >= T) {  // (ragged) a block of rows past the clip's end
+#pragma unroll
+        for (int o = 0; o < TPT; ++o)
+            if (t0 + o < cap_T) oc[(long long)(t0 + o) * inner + j] = 0.f;
+        return;
+    }
     float acc[TPT], wr[TPT];
 #pragma unroll
     for (int o = 0; o < TPT; ++o) acc[o] = 0.f, wr[o] = 0.f;
@@ -85,17 +94,18 @@ __global__ void gauss1d_kernel(const float* __restrict__ x, int T, long long inn
     }
 #pragma unroll
     for (int o = 0; o < TPT; ++o)
-        if (t0 + o < T) oc[(long long)(t0 + o) * inner + j] = acc[o];
+        if (t0 + o < cap_T) oc[(long long)(t0 + o) * inner + j] = t0 + o < T ? acc[o] : 0.f;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
 // per-(clip, column) min / max of [clip, T, C]
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void col_minmax_kernel(const float* __restrict__ x, int T, int C, float* __restrict__ mn_out,
-                                  float* __restrict__ mx_out) {
+__global__ void col_minmax_kernel(const float* __restrict__ x, int cap_T, int C, float* __restrict__ mn_out,
+                                  float* __restrict__ mx_out, const int* __restrict__ clip_frames) {
     __shared__ float scratch[32];
     const int col = blockIdx.x, clip = blockIdx.y;
-    const float* xc = x + (long long)clip * T * C + col;
+    const float* xc = x + (long long)clip * cap_T * C + col;
+    const int T = clip_frames ? __ldg(clip_frames + clip) : cap_T;  // ragged batches: the clip's own rows only
     float mn = INFINITY, mx = -INFINITY;
     for (int t = threadIdx.x; t < T; t += blockDim.x) {
         const float v = xc[(long long)t * C];
@@ -117,15 +127,17 @@ __global__ void col_minmax_kernel(const float* __restrict__ x, int T, int C, flo
 //   interp 3: efficient_quantile midpoint (rank = double(float(q)) * (n - 1), trunc / ceil neighbours, mean in fp64)
 //   pre-transform: v -> (v - sub[col]) / div[col] when sub != NULL (emphasize's rescale, processing.py:133-136)
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void col_quantile_kernel(const float* __restrict__ x, int T, int C, int subset, double q, int interp,
+__global__ void col_quantile_kernel(const float* __restrict__ x, int cap_T, int C, int subset, double q, int interp,
                                     const float* __restrict__ pre_sub, const float* __restrict__ pre_div,
-                                    float* __restrict__ out, int* __restrict__ count_out, int staged_keys) {
+                                    float* __restrict__ out, int* __restrict__ count_out, int staged_keys,
+                                    const int* __restrict__ clip_frames) {
     __shared__ uint32_t hist[256];
     __shared__ uint32_t bcast[2];
     __shared__ int s_count;
     const int col = blockIdx.x, clip = blockIdx.y;
+    const int T = clip_frames ? __ldg(clip_frames + clip) : cap_T;  // ragged batches: the clip's own rows only
     SelectCtx c;
-    c.xc = x + (long long)clip * T * C + col;
+    c.xc = x + (long long)clip * cap_T * C + col;
     c.T = T;
     c.C = C;
     c.aux = nullptr;
@@ -212,13 +224,17 @@ __global__ void normalize_kernel(const float* __restrict__ x, long long n_per_cl
 
 // normalize for small per-clip arrays (<= 256 k elements, L2 resident): ONE CTA per clip finds min / max and rescales —
 // one launch instead of two key fills + minmax + normalize.  Same min / max (exact) and the same expression per element.
-__global__ void __launch_bounds__(1024) normalize_fused_kernel(const float* __restrict__ x, long long n_per_clip, float eps,
-                                                                float* __restrict__ out) {
+__global__ void __launch_bounds__(1024) normalize_fused_kernel(const float* __restrict__ x, long long cap_per_clip, float eps,
+                                                                float* __restrict__ out, const int* __restrict__ clip_rows,
+                                                                long long row_elems) {
     __shared__ float scratch[32];
     __shared__ float s_mn, s_mx;
     const int clip = blockIdx.x;
-    const float* xc = x + (long long)clip * n_per_clip;
-    float* oc = out + (long long)clip * n_per_clip;
+    const float* xc = x + (long long)clip * cap_per_clip;
+    float* oc = out + (long long)clip * cap_per_clip;
+    // ragged batches: the first clip_rows[c] * row_elems elements of the clip are real; the rest is written as zeros
+    const long long n_per_clip = clip_rows ? min(cap_per_clip, (long long)__ldg(clip_rows + clip) * row_elems) : cap_per_clip;
+    for (long long i = n_per_clip + threadIdx.x; i < cap_per_clip; i += blockDim.x) oc[i] = 0.f;
     float mn = INFINITY, mx = -INFINITY;
     for (long long i = threadIdx.x; i < n_per_clip; i += blockDim.x) {
         const float v = xc[i];
@@ -287,12 +303,14 @@ __global__ void hwr_rowsum_kernel(const float* __restrict__ x, long long rows, i
 
 // (count, sum, sum of squares) per column in fp64, atomically accumulated into stats[3, C] (zeroed by the caller).
 // rows = n_clips * T flattened (the statistic is over all windows and frames, supervised/data.py:317-319).
-__global__ void feature_stats_kernel(const float* __restrict__ x, long long rows, int C, double* __restrict__ stats) {
+__global__ void feature_stats_kernel(const float* __restrict__ x, long long rows, int C, double* __restrict__ stats,
+                                     int cap_T, const int* __restrict__ clip_frames) {
     // blockDim = (32, 8): x = column lane, y = row lane
     for (int col = blockIdx.x * 32 + threadIdx.x; col < C; col += gridDim.x * 32) {
         double s = 0.0, ss = 0.0;
         long long cnt = 0;
         for (long long r = (long long)blockIdx.y * blockDim.y + threadIdx.y; r < rows; r += (long long)gridDim.y * blockDim.y) {
+            if (clip_frames && (int)(r % cap_T) >= __ldg(clip_frames + r / cap_T)) continue;  // (ragged) past the clip's end
             const double v = (double)x[r * C + col];
             s += v;
             ss += v * v;
@@ -309,7 +327,7 @@ __global__ void feature_stats_kernel(const float* __restrict__ x, long long rows
 #define ST(s) reinterpret_cast<cudaStream_t>(s)
 
 extern "C" int ssar_gauss1d(const float* x, int n_clips, int n_frames, long long inner, const float* weights, int radius,
-                            int mode, float* out, void* stream) {
+                            int mode, float* out, const int* clip_frames, void* stream) {
     if (n_clips == 0 || n_frames == 0 || inner == 0) return SSAR_OK;
     SSAR_REQUIRE(x && weights && out, "gauss1d: null pointer");
     SSAR_REQUIRE(x != out, "gauss1d: in-place filtering is not supported");
@@ -327,20 +345,21 @@ extern "C" int ssar_gauss1d(const float* x, int n_clips, int n_frames, long long
     const size_t smem = (2 * radius + 1) * sizeof(float);
     auto kern = tpt == 16 ? gauss1d_kernel<16> : gauss1d_kernel<4>;
     if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    kern<<<grid, threads, smem, ST(stream)>>>(x, n_frames, inner, weights, radius, mode, out);
+    kern<<<grid, threads, smem, ST(stream)>>>(x, n_frames, inner, weights, radius, mode, out, clip_frames);
     return ssar_launch_status("gauss1d");
 }
 
 extern "C" int ssar_col_minmax(const float* x, int n_clips, int n_frames, int n_cols, float* min_out, float* max_out,
-                               void* stream) {
+                               const int* clip_frames, void* stream) {
     if (n_clips == 0 || n_cols == 0) return SSAR_OK;
     SSAR_REQUIRE(x && n_frames > 0, "col_minmax: null pointer or empty columns");
-    col_minmax_kernel<<<dim3(n_cols, n_clips), 256, 0, ST(stream)>>>(x, n_frames, n_cols, min_out, max_out);
+    col_minmax_kernel<<<dim3(n_cols, n_clips), 256, 0, ST(stream)>>>(x, n_frames, n_cols, min_out, max_out, clip_frames);
     return ssar_launch_status("col_minmax");
 }
 
 extern "C" int ssar_col_quantile(const float* x, int n_clips, int n_frames, int n_cols, int subset, double q, int interp,
-                                 const float* pre_sub, const float* pre_div, float* out, int* count_out, void* stream) {
+                                 const float* pre_sub, const float* pre_div, float* out, int* count_out,
+                                 const int* clip_frames, void* stream) {
     if (n_clips == 0 || n_cols == 0) return SSAR_OK;
     SSAR_REQUIRE(x && out, "col_quantile: null pointer");
     SSAR_REQUIRE(q >= 0.0 && q <= 1.0, "col_quantile: q must be in [0, 1]");
@@ -353,7 +372,7 @@ extern "C" int ssar_col_quantile(const float* x, int n_clips, int n_frames, int 
     // then never touch the strided column again
     const int staged = n_frames <= 11776 ? 1 : 0;  // 46 KB + the static arrays stay under the 48 KB default
     col_quantile_kernel<<<dim3(n_cols, n_clips), threads, staged ? (size_t)n_frames * sizeof(uint32_t) : 0, ST(stream)>>>(
-        x, n_frames, n_cols, subset, q, interp, pre_sub, pre_div, out, count_out, staged);
+        x, n_frames, n_cols, subset, q, interp, pre_sub, pre_div, out, count_out, staged, clip_frames);
     return ssar_launch_status("col_quantile");
 }
 
@@ -381,23 +400,26 @@ extern "C" int ssar_normalize(const float* x, int n_clips, long long n_per_clip,
     return ssar_launch_status("normalize");
 }
 
-extern "C" int ssar_normalize_fused(const float* x, int n_clips, long long n_per_clip, float eps, float* out, void* stream) {
+extern "C" int ssar_normalize_fused(const float* x, int n_clips, long long n_per_clip, float eps, float* out,
+                                    const int* clip_rows, long long row_elems, void* stream) {
     if (n_clips == 0 || n_per_clip == 0) return SSAR_OK;
     SSAR_REQUIRE(x && out, "normalize_fused: null pointer");
     SSAR_REQUIRE(n_per_clip <= (1LL << 18), "normalize_fused: at most 262 144 elements per clip (use minmax_keys + normalize)");
-    normalize_fused_kernel<<<n_clips, 1024, 0, ST(stream)>>>(x, n_per_clip, eps, out);
+    SSAR_REQUIRE(!clip_rows || row_elems > 0, "normalize_fused: row_elems must be positive with clip_rows");
+    normalize_fused_kernel<<<n_clips, 1024, 0, ST(stream)>>>(x, n_per_clip, eps, out, clip_rows, row_elems);
     return ssar_launch_status("normalize_fused");
 }
 
 extern "C" int ssar_emphasize(const float* x, int n_clips, int n_frames, int n_cols, const float* col_min,
-                              const float* col_max, float strength, double q, float* scratch, float* out, void* stream) {
+                              const float* col_max, float strength, double q, float* scratch, float* out,
+                              const int* clip_frames, void* stream) {
     if (n_clips == 0 || n_frames == 0 || n_cols == 0) return SSAR_OK;
     SSAR_REQUIRE(x && col_min && col_max && scratch && out, "emphasize: null pointer");
     const int nc = n_clips * n_cols;
     float* rng = scratch;        // [n_clips * n_cols]
     float* qv = scratch + nc;    // [n_clips * n_cols]
     range_kernel<<<ssar_div_up(nc, 256), 256, 0, ST(stream)>>>(col_min, col_max, nc, rng);
-    int rc = ssar_col_quantile(x, n_clips, n_frames, n_cols, 0, q, 0, col_min, rng, qv, nullptr, stream);
+    int rc = ssar_col_quantile(x, n_clips, n_frames, n_cols, 0, q, 0, col_min, rng, qv, nullptr, clip_frames, stream);
     if (rc != SSAR_OK) return rc;
     const long long n = (long long)n_frames * n_cols;
     emphasize_kernel<<<flat_grid(n, n_clips), 256, 0, ST(stream)>>>(x, n, n_cols, col_min, rng, qv, strength, out);
@@ -420,12 +442,16 @@ extern "C" int ssar_hwr_rowsum(const float* x, long long n_rows, int inner, floa
     return ssar_launch_status("hwr_rowsum");
 }
 
-extern "C" int ssar_feature_stats(const float* x, long long n_rows, int n_cols, double* stats, void* stream) {
+extern "C" int ssar_feature_stats(const float* x, long long n_rows, int n_cols, double* stats, int frames_per_clip,
+                                  const int* clip_frames, void* stream) {
     if (n_rows == 0 || n_cols == 0) return SSAR_OK;
     SSAR_REQUIRE(x && stats, "feature_stats: null pointer");
     int gy = ssar_div_up(n_rows, 8 * 64);
     if (gy > SSAR_NUM_SMS * 2) gy = SSAR_NUM_SMS * 2;
     if (gy < 1) gy = 1;
-    feature_stats_kernel<<<dim3(ssar_div_up(n_cols, 32), gy), dim3(32, 8), 0, ST(stream)>>>(x, n_rows, n_cols, stats);
+    SSAR_REQUIRE(!clip_frames || (frames_per_clip > 0 && n_rows % frames_per_clip == 0),
+                 "feature_stats: ragged batches need rows = n_clips * frames_per_clip");
+    feature_stats_kernel<<<dim3(ssar_div_up(n_cols, 32), gy), dim3(32, 8), 0, ST(stream)>>>(x, n_rows, n_cols, stats,
+                                                                                       frames_per_clip, clip_frames);
     return ssar_launch_status("feature_stats");
 }

@@ -7,13 +7,24 @@
 
 namespace {
 
+// Ragged batches: clip c holds clip_n_in[c] <= n_in samples and ZEROS behind them (the convention of every ragged
+// producer), so the filter sees exactly torchaudio's zero padding; only the outputs past ceil(newf * clip_n_in[c] / orig)
+// — the filter's ringing into the padding, which a per-clip call never produces — have to be forced to zero.
+__device__ __forceinline__ long long ragged_n_out(const long long* __restrict__ clip_n_in, int clip, int orig, int newf,
+                                                  long long n_out) {
+    if (!clip_n_in) return n_out;
+    const long long n = __ldg(clip_n_in + clip);
+    return min(n_out, (n * newf + orig - 1) / orig);
+}
+
 __global__ void resample_kernel(const float* __restrict__ x, long long n_in, long long stride_in,
                                 const float* __restrict__ taps, const int* __restrict__ first, int orig, int newf,
                                 int width, int max_taps, float post_scale, float* __restrict__ y, long long n_out,
-                                long long stride_out) {
+                                long long stride_out, const long long* __restrict__ clip_n_in) {
     const int clip = blockIdx.y;
     const float* xc = x + (long long)clip * stride_in;
     float* yc = y + (long long)clip * stride_out;
+    const long long n_out_c = ragged_n_out(clip_n_in, clip, orig, newf, n_out);
     for (long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x; j < n_out; j += (long long)gridDim.x * blockDim.x) {
         const long long blk = j / newf;
         const int ph = (int)(j - blk * newf);
@@ -25,7 +36,7 @@ __global__ void resample_kernel(const float* __restrict__ x, long long n_in, lon
             const float v = (i >= 0 && i < n_in) ? __ldg(xc + i) : 0.f;
             acc = fmaf(__ldg(taps + (long long)k * newf + ph), v, acc);
         }
-        yc[j] = acc * post_scale;
+        yc[j] = j < n_out_c ? acc * post_scale : 0.f;
     }
 }
 
@@ -36,10 +47,12 @@ template <int MAXT>
 __global__ void __launch_bounds__(256) resample_phase_kernel(const float* __restrict__ x, long long n_in, long long stride_in,
                                                              const float* __restrict__ taps, const int* __restrict__ first,
                                                              int orig, int newf, int width, int max_taps, float post_scale,
-                                                             float* __restrict__ y, long long n_out, long long stride_out) {
+                                                             float* __restrict__ y, long long n_out, long long stride_out,
+                                                             const long long* __restrict__ clip_n_in) {
     const int clip = blockIdx.y;
     const float* __restrict__ xc = x + (long long)clip * stride_in;
     float* __restrict__ yc = y + (long long)clip * stride_out;
+    const long long n_out_c = ragged_n_out(clip_n_in, clip, orig, newf, n_out);
     const long long S = (long long)gridDim.x * blockDim.x;  // multiple of newf
     const long long j0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (j0 >= n_out) return;
@@ -65,7 +78,7 @@ __global__ void __launch_bounds__(256) resample_phase_kernel(const float* __rest
                 }
             }
         }
-        yc[j] = acc * post_scale;
+        yc[j] = j < n_out_c ? acc * post_scale : 0.f;
     }
 }
 
@@ -85,7 +98,7 @@ __global__ void __launch_bounds__(256) decimate2_staged_kernel(const float* __re
                                                                const float* __restrict__ taps, const int* __restrict__ first,
                                                                int width, int max_taps, float post_scale,
                                                                float* __restrict__ y, long long n_out, long long stride_out,
-                                                               long long n_tiles) {
+                                                               long long n_tiles, const long long* __restrict__ clip_n_in) {
     constexpr int SPAN = 2 * D2_OUT + MAXT + 6;          // samples staged per tile (upper bound)
     constexpr int NW = (MAXT + 6) / 2;                   // 64-bit words per thread window
     __shared__ float2 S2[(SPAN + 2 * (SPAN / 32) + 2 + 1) / 2];
@@ -93,6 +106,7 @@ __global__ void __launch_bounds__(256) decimate2_staged_kernel(const float* __re
     const int clip = blockIdx.y;
     const float* __restrict__ xc = x + (long long)clip * stride_in;
     float* __restrict__ yc = y + (long long)clip * stride_out;
+    const long long n_out_c = ragged_n_out(clip_n_in, clip, 2, 1, n_out);
     float tp[MAXT];
 #pragma unroll
     for (int k = 0; k < MAXT; ++k) tp[k] = k < max_taps ? __ldg(taps + k) : 0.f;
@@ -130,6 +144,11 @@ __global__ void __launch_bounds__(256) decimate2_staged_kernel(const float* __re
             }
         }
         const long long j = j0 + 4 * t;
+        if (clip_n_in) {
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+                if (j + r >= n_out_c) acc[r] = 0.f;
+        }
         if (j + 3 < n_out && ((reinterpret_cast<uintptr_t>(yc + j) & 15) == 0)) {
             *reinterpret_cast<float4*>(yc + j) =
                 make_float4(acc[0] * post_scale, acc[1] * post_scale, acc[2] * post_scale, acc[3] * post_scale);
@@ -146,7 +165,7 @@ __global__ void __launch_bounds__(256) decimate2_staged_kernel(const float* __re
 
 extern "C" int ssar_resample(const float* x, long long n_in, long long stride_in, int n_clips, const float* taps,
                              const int* first, int orig, int newf, int width, int max_taps, float post_scale, float* y,
-                             long long n_out, long long stride_out, void* stream) {
+                             long long n_out, long long stride_out, const long long* clip_n_in, void* stream) {
     if (n_clips == 0 || n_out == 0) return SSAR_OK;
     SSAR_REQUIRE(x && taps && first && y, "resample: null pointer");
     SSAR_REQUIRE(orig > 0 && newf > 0 && max_taps > 0, "resample: bad rates");
@@ -156,7 +175,7 @@ extern "C" int ssar_resample(const float* x, long long n_in, long long stride_in
         const long long cap = ((long long)SSAR_NUM_SMS * 8 + n_clips - 1) / n_clips;
         if (gq > cap) gq = cap;
         decimate2_staged_kernel<28><<<dim3((unsigned)gq, n_clips), 256, 0, (cudaStream_t)stream>>>(
-            x, n_in, stride_in, taps, first, width, max_taps, post_scale, y, n_out, stride_out, n_tiles);
+            x, n_in, stride_in, taps, first, width, max_taps, post_scale, y, n_out, stride_out, n_tiles, clip_n_in);
         return ssar_launch_status("resample");
     }
     if (max_taps <= 32 && (newf <= 256 ? 256 % newf == 0 : newf % 256 == 0)) {
@@ -167,15 +186,15 @@ extern "C" int ssar_resample(const float* x, long long n_in, long long stride_in
         if (gxp > cap && cap > 0) gxp = cap;
         if (max_taps <= 24)
             resample_phase_kernel<24><<<dim3((unsigned)gxp, n_clips), 256, 0, (cudaStream_t)stream>>>(
-                x, n_in, stride_in, taps, first, orig, newf, width, max_taps, post_scale, y, n_out, stride_out);
+                x, n_in, stride_in, taps, first, orig, newf, width, max_taps, post_scale, y, n_out, stride_out, clip_n_in);
         else
             resample_phase_kernel<32><<<dim3((unsigned)gxp, n_clips), 256, 0, (cudaStream_t)stream>>>(
-                x, n_in, stride_in, taps, first, orig, newf, width, max_taps, post_scale, y, n_out, stride_out);
+                x, n_in, stride_in, taps, first, orig, newf, width, max_taps, post_scale, y, n_out, stride_out, clip_n_in);
         return ssar_launch_status("resample");
     }
     int gx = ssar_div_up(n_out, 256);
     if (gx > SSAR_NUM_SMS * 16) gx = SSAR_NUM_SMS * 16;
     resample_kernel<<<dim3(gx, n_clips), 256, 0, (cudaStream_t)stream>>>(x, n_in, stride_in, taps, first, orig, newf, width,
-                                                                        max_taps, post_scale, y, n_out, stride_out);
+                                                                        max_taps, post_scale, y, n_out, stride_out, clip_n_in);
     return ssar_launch_status("resample");
 }

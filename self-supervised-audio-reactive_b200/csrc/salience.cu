@@ -18,9 +18,12 @@ __global__ void __launch_bounds__(SAL_THREADS) salience_weight_kernel(const floa
                                                                        const float* __restrict__ slong, long long n_per_clip,
                                                                        int C, const int* __restrict__ col_group, int G,
                                                                        float* __restrict__ out, uint32_t* __restrict__ min_key,
-                                                                       uint32_t* __restrict__ max_key) {
+                                                                       uint32_t* __restrict__ max_key,
+                                                                       const int* __restrict__ clip_frames) {
     __shared__ uint32_t smin[SAL_MAX_GROUPS], smax[SAL_MAX_GROUPS];
     const int clip = blockIdx.y;
+    // ragged batches: only the clip's own rows feed the minima / maxima (the rest is written, as zeros)
+    const long long n_valid = clip_frames ? min(n_per_clip, (long long)__ldg(clip_frames + clip) * C) : n_per_clip;
     if (threadIdx.x < G) {
         smin[threadIdx.x] = 0xFFFFFFFFu;
         smax[threadIdx.x] = 0u;
@@ -28,6 +31,10 @@ __global__ void __launch_bounds__(SAL_THREADS) salience_weight_kernel(const floa
     __syncthreads();
     const long long base = (long long)clip * n_per_clip;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_per_clip; i += (long long)gridDim.x * blockDim.x) {
+        if (i >= n_valid) {
+            out[base + i] = 0.f;
+            continue;
+        }
         const float e = env[base + i];
         const float r = sshort[base + i] / slong[base + i];  // mir.py:19: (short / long) ** 2 * envelope
         const float w = (r * r) * e;
@@ -77,7 +84,7 @@ __global__ void __launch_bounds__(SAL_THREADS) group_normalize_kernel(const floa
 
 extern "C" int ssar_salience_weight(const float* env, const float* smooth_short, const float* smooth_long, int n_clips,
                                     int n_frames, int n_cols, const int* col_group, int n_groups, float* out,
-                                    uint32_t* min_key, uint32_t* max_key, void* stream) {
+                                    uint32_t* min_key, uint32_t* max_key, const int* clip_frames, void* stream) {
     if (n_clips <= 0 || n_frames <= 0 || n_cols <= 0) return SSAR_OK;
     SSAR_REQUIRE(env && smooth_short && smooth_long && col_group && out && min_key && max_key, "salience_weight: null pointer");
     SSAR_REQUIRE(n_groups >= 1 && n_groups <= SAL_MAX_GROUPS, "salience_weight: 1..%d column groups", SAL_MAX_GROUPS);
@@ -85,7 +92,8 @@ extern "C" int ssar_salience_weight(const float* env, const float* smooth_short,
     int gx = ssar_div_up(n, SAL_THREADS * 4);
     if (gx > SSAR_NUM_SMS * 4) gx = SSAR_NUM_SMS * 4;
     salience_weight_kernel<<<dim3(gx, n_clips), SAL_THREADS, 0, (cudaStream_t)stream>>>(env, smooth_short, smooth_long, n, n_cols,
-                                                                                     col_group, n_groups, out, min_key, max_key);
+                                                                                     col_group, n_groups, out, min_key, max_key,
+                                                                                     clip_frames);
     return ssar_launch_status("salience_weight");
 }
 

@@ -57,6 +57,7 @@ class FramesArgs(C.Structure):
         ("out_spec", C.c_void_p), ("lds", C.c_longlong), ("spec_power", C.c_int),
         ("out_rms", C.c_void_p), ("out_flatness", C.c_void_p),
         ("fb", Filterbank * 2), ("proj", Projection), ("aux_frames", C.c_int), ("pip", PiptrackEpilogue),
+        ("clip_samples", C.c_void_p), ("clip_frames", C.c_void_p),
     ]
 
 

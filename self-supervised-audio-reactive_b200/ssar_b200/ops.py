@@ -52,6 +52,8 @@ def frames_fft(
     proj: dict | None = None,
     aux_frames: int | None = None,
     piptrack: dict | None = None,
+    clip_samples: torch.Tensor | None = None,
+    clip_frames: torch.Tensor | None = None,
 ):
     """Framed real FFT + fused epilogues over a batch of clips.
 
@@ -64,6 +66,8 @@ def frames_fft(
       slots (int32 [B]: per-clip table slot), row_scale (fp32 [n_slots, row_scale_ld] view), row_scale_ld.
     aux_frames: when given (<= n_frames), every output except `complex` covers only the first aux_frames frames of each
       clip ([B, aux_frames, ...]): stft (T + 1 frames) and the last-frame-dropping features of one signal in one launch.
+    clip_samples (int64 [B]) / clip_frames (int32 [B]): RAGGED batch — clip b holds clip_samples[b] <= N samples and
+      produces clip_frames[b] <= n_frames frames; rows past a clip's count are zeros in every output.
     """
     x, _ = _as_batch(x)
     B, N = x.shape
@@ -81,6 +85,10 @@ def frames_fft(
     a.window = win.data_ptr() if win is not None else None
     tw = plan.twiddle(n_fft, str(dev))
     a.twiddle = tw.data_ptr()
+    if clip_samples is not None or clip_frames is not None:
+        if clip_samples is None or clip_frames is None or clip_samples.dtype != torch.int64 or clip_frames.dtype != torch.int32:
+            raise SsarError("frames_fft: ragged batches need clip_samples (int64) and clip_frames (int32) together")
+        a.clip_samples, a.clip_frames = clip_samples.data_ptr(), clip_frames.data_ptr()
     out = {}
     keep = [x, win, tw]
     n_cplx = n_frames
@@ -200,18 +208,20 @@ def power_to_db(x: torch.Tensor, n_clips: int = 1, top_db: float | None = 80.0, 
     return out
 
 
-def hpss(stft_fm: torch.Tensor, margin: float = 1.0, want_harm: bool = True, want_perc: bool = True):
+def hpss(stft_fm: torch.Tensor, margin: float = 1.0, want_harm: bool = True, want_perc: bool = True, clip_frames=None):
     """stft_fm: frame-major complex STFT as real view [B, T1, F, 2].  Returns (harm, perc) in the same layout."""
     B, T1, F, _ = stft_fm.shape
     h = torch.empty_like(stft_fm) if want_harm else None
     p = torch.empty_like(stft_fm) if want_perc else None
     cabi.call("ssar_hpss", ptr(stft_fm), i32(B), i32(T1), i32(F), i64(F), f32(margin), f32(margin), ptr(h), ptr(p),
-              nbytes=cabi.nbytes_of(stft_fm, h, p))
+              ptr(clip_frames), nbytes=cabi.nbytes_of(stft_fm, h, p))
     return h, p
 
 
-def istft(spec_fm: torch.Tensor, n_fft: int, hop: int, window=torch.hann_window, length: int | None = None):
-    """spec_fm: frame-major complex [B, T1, F, 2] -> waveform [B, length] (torch.istft semantics, center=True)."""
+def istft(spec_fm: torch.Tensor, n_fft: int, hop: int, window=torch.hann_window, length: int | None = None,
+          clip_frames=None, clip_len=None):
+    """spec_fm: frame-major complex [B, T1, F, 2] -> waveform [B, length] (torch.istft semantics, center=True).
+    clip_frames (int32 [B]) / clip_len (int64 [B]): ragged batch (per-clip frame counts and output lengths)."""
     B, T1, F, _ = spec_fm.shape
     dev = spec_fm.device
     if length is None:
@@ -219,17 +229,19 @@ def istft(spec_fm: torch.Tensor, n_fft: int, hop: int, window=torch.hann_window,
     if n_fft not in (1024, 2048):  # arbitrary length: direct inverse DFT over all bins
         return istft_band(spec_fm.contiguous(), n_fft, hop, window, 0, length)
     win = plan.window_tensor(window, n_fft, dev)
-    if n_fft == 2048 and hop == 1024 and length % 2 == 0:  # the HPSS case: fused transform + overlap-add
+    if n_fft == 2048 and hop == 1024 and (length % 2 == 0 or B == 1):  # the HPSS case: fused transform + overlap-add
+        # (rows must start 8-byte aligned: an even length, or a single clip)
         out = torch.empty(B, length, dtype=torch.float32, device=dev)
         cabi.call("ssar_istft_half_overlap", ptr(spec_fm), i64(F), i32(B), i32(T1), i32(n_fft), ptr(win),
-                  ptr(plan.twiddle(n_fft, str(dev))), i64(length), ptr(out), nbytes=cabi.nbytes_of(spec_fm, out))
+                  ptr(plan.twiddle(n_fft, str(dev))), i64(length), ptr(out), ptr(clip_frames), ptr(clip_len),
+                  nbytes=cabi.nbytes_of(spec_fm, out))
         return out
     frames = torch.empty(B, T1, n_fft, dtype=torch.float32, device=dev)
     cabi.call("ssar_irfft_frames", ptr(spec_fm), i64(F), i32(B), i32(T1), i32(n_fft), ptr(win),
               ptr(plan.twiddle(n_fft, str(dev))), ptr(frames), nbytes=cabi.nbytes_of(spec_fm, frames))
     out = torch.empty(B, length, dtype=torch.float32, device=dev)
     cabi.call("ssar_overlap_add", ptr(frames), ptr(win), i32(B), i32(T1), i32(n_fft), i32(hop), i64(length), ptr(out),
-              nbytes=cabi.nbytes_of(frames, out))
+              ptr(clip_frames), ptr(clip_len), nbytes=cabi.nbytes_of(frames, out))
     return out
 
 
@@ -268,14 +280,16 @@ def biquad_rms(x: torch.Tensor, coeffs, clamp: bool = True, want_signal: bool = 
     return (out, y) if want_signal else out
 
 
-def resample(x: torch.Tensor, rp, post_scale: float = 1.0):
-    """x [B, N] -> [B, ceil(new*N/orig)] with a `plan.ResamplePlan`."""
+def resample(x: torch.Tensor, rp, post_scale: float = 1.0, clip_n_in=None):
+    """x [B, N] -> [B, ceil(new*N/orig)] with a `plan.ResamplePlan`.  clip_n_in (int64 [B]): ragged batch — clip b holds
+    clip_n_in[b] samples followed by zeros; its outputs past ceil(new * clip_n_in[b] / orig) are zeros."""
     x, _ = _as_batch(x)
     B, N = x.shape
     n_out = -((-rp.new * N) // rp.orig)
     y = torch.empty(B, n_out, dtype=torch.float32, device=x.device)
     cabi.call("ssar_resample", ptr(x), i64(N), i64(x.stride(0)), i32(B), ptr(rp.taps), ptr(rp.first), i32(rp.orig),
-              i32(rp.new), i32(rp.width), i32(rp.max_taps), f32(post_scale), ptr(y), i64(n_out), i64(n_out), nbytes=cabi.nbytes_of(x, y))
+              i32(rp.new), i32(rp.width), i32(rp.max_taps), f32(post_scale), ptr(y), i64(n_out), i64(n_out), ptr(clip_n_in),
+              nbytes=cabi.nbytes_of(x, y))
     return y
 
 
@@ -295,7 +309,7 @@ def frames_rms(x: torch.Tensor, frame_length: int, hop: int, n_frames: int):
 PAD_MODES = {"circular": 0, "reflect": 1, "replicate": 2}
 
 
-def gauss1d(x: torch.Tensor, sigma: float, mode: str = "circular", batched: bool = False, causal="plain"):
+def gauss1d(x: torch.Tensor, sigma: float, mode: str = "circular", batched: bool = False, causal="plain", clip_frames=None):
     """Gaussian smoothing along time.  x: [T, inner...] or, with batched=True, [B, T, inner...] -> same shape.
     causal: "plain" = features/processing.py's kernel; None / number = maua signal.py's `causal` argument."""
     if not x.is_cuda:
@@ -314,27 +328,29 @@ def gauss1d(x: torch.Tensor, sigma: float, mode: str = "circular", batched: bool
          plan.gaussian_taps_causal(float(sigma), radius, causal, str(x.device)))
     out = torch.empty_like(x)
     cabi.call("ssar_gauss1d", ptr(x), i32(n_clips), i32(T), i64(inner), ptr(w), i32(radius), i32(PAD_MODES[mode]), ptr(out),
-              nbytes=cabi.nbytes_of(x, out))
+              ptr(clip_frames), nbytes=cabi.nbytes_of(x, out))
     return out
 
 
-def col_minmax(x: torch.Tensor):
+def col_minmax(x: torch.Tensor, clip_frames=None):
     """x [B, T, C] -> (min [B, C], max [B, C])."""
     B, T, Cc = x.shape
     mn = torch.empty(B, Cc, dtype=torch.float32, device=x.device)
     mx = torch.empty(B, Cc, dtype=torch.float32, device=x.device)
-    cabi.call("ssar_col_minmax", ptr(x), i32(B), i32(T), i32(Cc), ptr(mn), ptr(mx), nbytes=cabi.nbytes_of(x))
+    cabi.call("ssar_col_minmax", ptr(x), i32(B), i32(T), i32(Cc), ptr(mn), ptr(mx), ptr(clip_frames), nbytes=cabi.nbytes_of(x))
     return mn, mx
 
 
-def col_quantile(x: torch.Tensor, q: float, subset: str = "all", interp: str = "linear", pre=None, want_count=False):
+def col_quantile(x: torch.Tensor, q: float, subset: str = "all", interp: str = "linear", pre=None, want_count=False,
+                 clip_frames=None):
     """x [B, T, C] contiguous -> per-(clip, column) quantile [B, C] (exact order statistics, radix select)."""
     B, T, Cc = x.shape
     out = torch.empty(B, Cc, dtype=torch.float32, device=x.device)
     cnt = torch.empty(B, Cc, dtype=torch.int32, device=x.device) if want_count else None
     ps, pd = (pre if pre is not None else (None, None))
     cabi.call("ssar_col_quantile", ptr(x), i32(B), i32(T), i32(Cc), i32({"all": 0, "peaks": 1}[subset]), f64(q),
-              i32({"linear": 0, "midpoint": 3}[interp]), ptr(ps), ptr(pd), ptr(out), ptr(cnt), nbytes=cabi.nbytes_of(x))
+              i32({"linear": 0, "midpoint": 3}[interp]), ptr(ps), ptr(pd), ptr(out), ptr(cnt), ptr(clip_frames),
+              nbytes=cabi.nbytes_of(x))
     return (out, cnt) if want_count else out
 
 
@@ -345,27 +361,32 @@ def clamp_cols(x: torch.Tensor, lo=None, hi=None):
     return out
 
 
-def normalize(x: torch.Tensor, n_clips: int = 1, eps: float = 1e-8):
-    """(x - min) / ((max - min) + eps) with min/max over each clip's whole array."""
+def normalize(x: torch.Tensor, n_clips: int = 1, eps: float = 1e-8, clip_rows=None):
+    """(x - min) / ((max - min) + eps) with min/max over each clip's whole array.  clip_rows (int32 [n_clips]): ragged
+    batch [n_clips, T, ...] — only the first clip_rows[c] rows of clip c are real (the rest comes back as zeros)."""
     x = x.contiguous()
     out = torch.empty_like(x)
     n_per = x.numel() // max(n_clips, 1)
     if 0 < n_per <= (1 << 18) and x.dtype == torch.float32:
-        cabi.call("ssar_normalize_fused", ptr(x), i32(n_clips), i64(n_per), f32(eps), ptr(out), nbytes=cabi.nbytes_of(x, out))
+        row_elems = n_per // max(x.shape[1], 1) if (clip_rows is not None and x.dim() >= 2) else 0
+        cabi.call("ssar_normalize_fused", ptr(x), i32(n_clips), i64(n_per), f32(eps), ptr(out), ptr(clip_rows), i64(row_elems),
+                  nbytes=cabi.nbytes_of(x, out))
         return out
+    if clip_rows is not None:
+        raise SsarError("normalize: ragged batches are limited to 262 144 elements per clip")
     mn, mx = minmax_keys(x, n_clips)
     cabi.call("ssar_normalize", ptr(x), i32(n_clips), i64(x.numel() // max(n_clips, 1)), ptr(mn), ptr(mx), f32(eps), ptr(out),
               nbytes=cabi.nbytes_of(x, out))
     return out
 
 
-def emphasize(x: torch.Tensor, strength: float, percentile: float):
+def emphasize(x: torch.Tensor, strength: float, percentile: float, clip_frames=None):
     B, T, Cc = x.shape
-    mn, mx = col_minmax(x)
+    mn, mx = col_minmax(x, clip_frames)
     scratch = torch.empty(2 * B * Cc, dtype=torch.float32, device=x.device)
     out = torch.empty_like(x)
     cabi.call("ssar_emphasize", ptr(x), i32(B), i32(T), i32(Cc), ptr(mn), ptr(mx), f32(strength), f64(percentile / 100),
-              ptr(scratch), ptr(out), nbytes=cabi.nbytes_of(x, out))
+              ptr(scratch), ptr(out), ptr(clip_frames), nbytes=cabi.nbytes_of(x, out))
     return out
 
 
@@ -403,7 +424,7 @@ def _group_tables(group_sizes, device):
 
 
 def salience_features(raw: torch.Tensor, group_sizes, sigma: float = 2.0, short_sigma: float = 5.0, long_sigma: float = 80.0,
-                      eps: float = 1e-8):
+                      eps: float = 1e-8, clip_frames=None):
     """random/mir.py:44 for a batch: raw [B, T, C] holds the features of every clip side by side (column groups of
     `group_sizes`); every group g becomes normalize(salience_weighted(gaussian_filter(raw_g, sigma))) (mir.py:14-22).
     Returns a list of contiguous [B, T, C_g] tensors... as views of ONE feature-blocked buffer [B, T * C]: entry g is
@@ -413,28 +434,30 @@ def salience_features(raw: torch.Tensor, group_sizes, sigma: float = 2.0, short_
         raise SsarError("salience_features: group sizes do not add up to the column count")
     col_group, group_start, starts = _group_tables(group_sizes, raw.device)
     G = len(group_sizes)
-    env = gauss1d(raw, sigma, "circular", batched=True)
-    short = gauss1d(env, short_sigma, "reflect", batched=True)
-    long = gauss1d(env, long_sigma, "reflect", batched=True)
+    env = gauss1d(raw, sigma, "circular", batched=True, clip_frames=clip_frames)
+    short = gauss1d(env, short_sigma, "reflect", batched=True, clip_frames=clip_frames)
+    long = gauss1d(env, long_sigma, "reflect", batched=True, clip_frames=clip_frames)
     keys = torch.empty(2, B, G, dtype=torch.int32, device=raw.device)
     fill_u32(keys[0], KEY_POS_INF)
     fill_u32(keys[1], KEY_NEG_INF)
     w = torch.empty_like(env)
     cabi.call("ssar_salience_weight", ptr(env), ptr(short), ptr(long), i32(B), i32(T), i32(Cc), ptr(col_group), i32(G), ptr(w),
-              ptr(keys[0]), ptr(keys[1]), nbytes=cabi.nbytes_of(env, short, long, w))
+              ptr(keys[0]), ptr(keys[1]), ptr(clip_frames), nbytes=cabi.nbytes_of(env, short, long, w))
     buf = torch.empty(B, T * Cc, dtype=torch.float32, device=raw.device)
     cabi.call("ssar_group_normalize", ptr(w), i32(B), i32(T), i32(Cc), ptr(col_group), ptr(group_start), i32(G), ptr(keys[0]),
               ptr(keys[1]), f32(eps), ptr(buf), nbytes=cabi.nbytes_of(w, buf))
     return [buf[:, T * st : T * (st + n)].view(B, T, n) for st, n in zip(starts, group_sizes)]
 
 
-def feature_stats(x: torch.Tensor, stats: torch.Tensor | None = None):
-    """x [..., C] -> fp64 [3, C] = (count, sum, sum of squares) accumulated into `stats` (allocated if None)."""
+def feature_stats(x: torch.Tensor, stats: torch.Tensor | None = None, clip_frames=None):
+    """x [..., C] -> fp64 [3, C] = (count, sum, sum of squares) accumulated into `stats` (allocated if None).
+    clip_frames (int32 [B]): ragged batch x [B, T, C] — rows past each clip's own count are skipped."""
     Cc = x.shape[-1]
     x = x.contiguous()
     if stats is None:
         stats = torch.zeros(3, Cc, dtype=torch.float64, device=x.device)
-    cabi.call("ssar_feature_stats", ptr(x), i64(x.numel() // Cc), i32(Cc), ptr(stats), nbytes=cabi.nbytes_of(x))
+    cabi.call("ssar_feature_stats", ptr(x), i64(x.numel() // Cc), i32(Cc), ptr(stats),
+              i32(x.shape[1] if clip_frames is not None else 0), ptr(clip_frames), nbytes=cabi.nbytes_of(x))
     return stats
 
 
@@ -462,8 +485,9 @@ FUSED_PIPTRACK = True  # piptrack as an epilogue of the hop n_fft/4 transform (F
 
 
 def estimate_tuning(y: torch.Tensor, sr, n_fft: int = 2048, bins_per_octave: int = 12, threshold: float = 0.1,
-                    fmin: float = 150.0, fmax: float = 4000.0):
-    """rosa/pitch.py:9-24 for a batch [B, N] -> (tuning_idx int32 [B] in [0, 100], tuning_val fp32 [B])."""
+                    fmin: float = 150.0, fmax: float = 4000.0, lens=None):
+    """rosa/pitch.py:9-24 for a batch [B, N] -> (tuning_idx int32 [B] in [0, 100], tuning_val fp32 [B]).
+    lens: `ragged.ClipLengths` of a ragged batch (n_fft 2048 only)."""
     y, _ = _as_batch(y)
     B, N = y.shape
     hop = n_fft // 4  # hop_length=None reaches torch.stft's default through rosa/spectral.py:59-62
@@ -471,10 +495,13 @@ def estimate_tuning(y: torch.Tensor, sr, n_fft: int = 2048, bins_per_octave: int
     k_lo, k_hi = plan.piptrack_bin_range(float(sr), n_fft, fmin, fmax)
     if FUSED_PIPTRACK and n_fft in (1024, 2048):
         # the peak picking runs in the transform's epilogue: the [frames, 1025] magnitudes never reach HBM
-        o = frames_fft(y, n_fft, hop, T, torch.hann_window, piptrack=dict(k_lo=k_lo, k_hi=k_hi, threshold=threshold, sr=sr))
+        rag = dict(clip_samples=lens.n, clip_frames=lens.P) if lens is not None else {}
+        o = frames_fft(y, n_fft, hop, T, torch.hann_window, piptrack=dict(k_lo=k_lo, k_hi=k_hi, threshold=threshold, sr=sr), **rag)
         pitch, mag, count = o["pip_pitch"], o["pip_mag"], o["pip_count"]
         cap = pitch.shape[1]
     else:
+        if lens is not None:
+            raise SsarError("estimate_tuning: ragged batches need the fused piptrack epilogue (n_fft 1024 / 2048)")
         S = frames_fft(y, n_fft, hop, T, torch.hann_window, spec_power=1)["spec"]
         cap = int(cabi.lib().ssar_piptrack_capacity(C.c_int(T), C.c_int(k_lo), C.c_int(k_hi)))
         pitch = torch.empty(B, cap, dtype=torch.float32, device=y.device)
@@ -504,13 +531,13 @@ def chroma_from_cqt(C_fm: torch.Tensor, bins_per_octave: int = 36, n_chroma: int
     return out
 
 
-def cens_smooth(q: torch.Tensor, window: torch.Tensor | None, l2: bool = True):
+def cens_smooth(q: torch.Tensor, window: torch.Tensor | None, l2: bool = True, clip_frames=None):
     B, T, nc = q.shape
     if window is None:
         window = torch.ones(1, dtype=torch.float32, device=q.device)
     out = torch.empty_like(q)
     cabi.call("ssar_cens_smooth", ptr(q), i32(B), i32(T), i32(nc), ptr(window), i32(window.numel()), i32(1 if l2 else 0),
-              ptr(out), nbytes=cabi.nbytes_of(q, out))
+              ptr(out), ptr(clip_frames), nbytes=cabi.nbytes_of(q, out))
     return out
 
 
@@ -527,7 +554,7 @@ def tonnetz(chroma: torch.Tensor):
 USE_TENSOR_CORE_CQT = True  # False: per-octave FFT + banded frequency-domain projection (frames_fft epilogue)
 
 
-def cqt(y: torch.Tensor, sr, hop_length: int = 1024, tuning_idx=None, sync_free: bool = False, tensor_core=None):
+def cqt(y: torch.Tensor, sr, hop_length: int = 1024, tuning_idx=None, sync_free: bool = False, tensor_core=None, lens=None):
     """rosa/constantq.py:13-115 for the reference's only configuration (C1, 7 octaves x 36 bins, filter_scale 1,
     sparsity 0.01): returns the frame-major complex-as-real CQT [B, T, 252, 2] with 1/sqrt(length) applied.
     tuning_idx: int32 [B] from estimate_tuning (None -> estimate, like tuning=None in chroma_cqt)."""
@@ -540,11 +567,13 @@ def cqt(y: torch.Tensor, sr, hop_length: int = 1024, tuning_idx=None, sync_free:
     if float(sr) / (1 << (n_oct - 1)) != int(float(sr) / (1 << (n_oct - 1))):
         raise ValueError("Frequencies must be of integer type to ensure quality resampling computation.")
     if tuning_idx is None:
-        tuning_idx, _ = estimate_tuning(y, sr, bins_per_octave=bpo)
+        tuning_idx, _ = estimate_tuning(y, sr, bins_per_octave=bpo, lens=lens)
     use_tc = USE_TENSOR_CORE_CQT if tensor_core is None else bool(tensor_core)
     use_tc = use_tc and hop_length % (8 << (n_oct - 1)) == 0 and N >= (plan.CQT_N_FFT << (n_oct - 1))
     if use_tc:
-        return _cqt_tensor_core(y, sr, hop_length, tuning_idx)
+        return _cqt_tensor_core(y, sr, hop_length, tuning_idx, lens)
+    if lens is not None:
+        raise SsarError("cqt: ragged batches run on the tensor-core path only (hop a multiple of 512, clips >= 65 536 samples)")
     tables = plan.cqt_tables(float(sr), str(y.device))
     if sync_free:  # all tuned bases resident; the per-clip choice is a device gather (no read-back: graph-capturable)
         slots = tables.slot_map()[tuning_idx.long()].contiguous()
@@ -569,7 +598,7 @@ def cqt(y: torch.Tensor, sr, hop_length: int = 1024, tuning_idx=None, sync_free:
     return out
 
 
-def _cqt_tensor_core(y: torch.Tensor, sr, hop_length: int, tuning_idx: torch.Tensor):
+def _cqt_tensor_core(y: torch.Tensor, sr, hop_length: int, tuning_idx: torch.Tensor, lens=None):
     """The 7 octave responses as ONE tcgen05 launch (`ssar_cqt_tc`): time-domain contraction of the overlapping frames
     (TMA tensor maps with row stride hop_i over the reflect-padded fp16 hi / lo signals) with the tuned basis.  Each
     clip's basis is picked on the device by its tuning index: no read-back, graph-capturable."""
@@ -579,7 +608,8 @@ def _cqt_tensor_core(y: torch.Tensor, sr, hop_length: int, tuning_idx: torch.Ten
     sigs = [y.contiguous()]
     rp = plan.resample_plan(2, 1, "kaiser_window", str(y.device))
     for i in range(1, n_oct):
-        sigs.append(resample(sigs[-1], rp, post_scale=float(torch.tensor(2.0).sqrt())))
+        sigs.append(resample(sigs[-1], rp, post_scale=float(torch.tensor(2.0).sqrt()),
+                             clip_n_in=lens.octave_n(i - 1) if lens is not None else None))
     T = min(s.shape[1] // (hop_length >> i) for i, s in enumerate(sigs))
     n_bins = n_oct * bpo
     out = torch.empty(B, T, n_bins, 2, dtype=torch.float32, device=y.device)
@@ -591,6 +621,7 @@ def _cqt_tensor_core(y: torch.Tensor, sr, hop_length: int, tuning_idx: torch.Ten
     slots = tuning_idx.to(torch.int32).contiguous()
     cabi.call("ssar_cqt_tc", ps, ns, i32(n_oct), i32(B), i32(hop_length), i32(T), ptr(tb.basis_hi), ptr(tb.basis_lo),
               i32(tb.n_slots), ptr(slots), ptr(tb.row_scale), i64(n_bins), f32(tb.SCALE), ptr(scratch), ptr(out),
+              ptr(lens.n if lens is not None else None), ptr(lens.T if lens is not None else None),
               nbytes=sum(cabi.nbytes_of(s) for s in sigs) + cabi.nbytes_of(out))
     return out
 
@@ -633,21 +664,26 @@ def tempo_bin_range(sr, hop_length: int, win: int, tempo_min, tempo_max):
     return (int(idx[0]), int(idx[-1]) + 1) if len(idx) else (0, 0)
 
 
-def plp_from_onset(onset_env: torch.Tensor, sr, hop_length: int = 1024, win_length: int = 1024, tempo_min=60, tempo_max=180):
+def plp_from_onset(onset_env: torch.Tensor, sr, hop_length: int = 1024, win_length: int = 1024, tempo_min=60, tempo_max=180,
+                   lens=None):
     """rosa/beat.py:46-75 after the onset envelope: onset_env [B, T] -> pulse [B, T] (normalised per clip).
     The tempogram window is min(T, win_length) (beat.py:47): 1024 / 2048 run on the radix FFT kernels; any other length
     (a clip shorter than win_length frames) on the band-limited direct DFT, which only ever forms the 60-180 BPM bins."""
     onset_env, _ = _as_batch(onset_env)
     B, T = onset_env.shape
     win = min(T, win_length)
+    if lens is not None and (win_length not in (1024, 2048) or min(lens.host_T) < win_length):
+        raise SsarError("plp: every clip of a ragged batch needs at least win_length frames (the window would differ per clip)")
     k_lo, k_hi = tempo_bin_range(sr, hop_length, win, tempo_min, tempo_max)
     n_frames = 1 + (T + 2 * (win // 2) - win)  # torch.stft, hop 1, centre-padded by win // 2 on both sides
     if win in (1024, 2048):
         F = win // 2 + 1
-        tg = frames_fft(onset_env, win, 1, n_frames, torch.hann_window, want_complex=True)["complex"]  # [B, T+1, F, 2]
+        rag = dict(clip_samples=lens.T64, clip_frames=lens.T1) if lens is not None else {}
+        tg = frames_fft(onset_env, win, 1, n_frames, torch.hann_window, want_complex=True, **rag)["complex"]  # [B, T+1, F, 2]
         cabi.call("ssar_plp_peaks", ptr(tg), i64(F), i32(B), i32(n_frames), i32(F), i32(k_lo), i32(k_hi),
                   nbytes=2 * cabi.nbytes_of(tg))
-        pulse = istft(tg, win, 1, torch.hann_window, T)
+        pulse = istft(tg, win, 1, torch.hann_window, T, clip_frames=lens.T1 if lens is not None else None,
+                      clip_len=lens.T64 if lens is not None else None)
     else:
         if win < 2:
             raise SsarError("plp: the onset envelope needs at least 2 frames")
@@ -660,7 +696,7 @@ def plp_from_onset(onset_env: torch.Tensor, sr, hop_length: int = 1024, win_leng
                  torch.zeros(B, T, dtype=torch.float32, device=onset_env.device))
     zero = torch.zeros(B, 1, dtype=torch.float32, device=pulse.device)
     pulse = clamp_cols(pulse.view(B, T, 1), zero, None).view(B, T)  # clamp(pulse, 0, pulse.max())
-    return normalize(pulse, B)
+    return normalize(pulse, B, clip_rows=lens.T if lens is not None else None)
 
 
 # ------------------------------------------------------------------------------------------------

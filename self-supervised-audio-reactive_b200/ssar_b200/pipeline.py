@@ -38,16 +38,18 @@ def spectral_frontend(x: torch.Tensor, sr, n_fft: int = 2048, hop: int = 512, wa
 
 
 def hpss_pair(x: torch.Tensor, margin: float = 8.0, n_fft: int = 2048, hop: int = 1024, D=None, want_harm=True,
-              want_perc=True):
+              want_perc=True, lens=None):
     """harmonic(x), percussive(x) (features/audio.py:13-24) from ONE forward STFT and ONE pair of median passes.
     x [B, N] -> (harm [B, N], perc [B, N]) (None for a part that is not wanted).  Exact: the two reference calls differ
     only in the mask applied."""
     n = x.shape[-1]
+    rag = dict(clip_samples=lens.n, clip_frames=lens.T1) if lens is not None else {}
     if D is None:
-        D = ops.frames_fft(x, n_fft, hop, 1 + n // hop, torch.hann_window, want_complex=True)["complex"]
-    h, p = ops.hpss(D, margin, want_harm, want_perc)
-    return (ops.istft(h, n_fft, hop, torch.hann_window, n) if want_harm else None,
-            ops.istft(p, n_fft, hop, torch.hann_window, n) if want_perc else None)
+        D = ops.frames_fft(x, n_fft, hop, 1 + n // hop, torch.hann_window, want_complex=True, **rag)["complex"]
+    h, p = ops.hpss(D, margin, want_harm, want_perc, clip_frames=lens.T1 if lens is not None else None)
+    irag = dict(clip_frames=lens.T1, clip_len=lens.n) if lens is not None else {}
+    return (ops.istft(h, n_fft, hop, torch.hann_window, n, **irag) if want_harm else None,
+            ops.istft(p, n_fft, hop, torch.hann_window, n, **irag) if want_perc else None)
 
 
 def band_split(x: torch.Tensor, sr):
@@ -66,10 +68,11 @@ def band_rms(x: torch.Tensor, sr, n_frames: int):
     return ops.biquad_rms(x, lo_c, n_frames=n_frames), ops.biquad_rms(high, lo_c, n_frames=n_frames), r_hi
 
 
-def onset_pair(x: torch.Tensor, sr, hop: int = 1024, n_fft: int = 2048, want_median: bool = False):
+def onset_pair(x: torch.Tensor, sr, hop: int = 1024, n_fft: int = 2048, want_median: bool = False, lens=None):
     """onset_strength(x) with mean aggregation (+ the median-aggregated envelope plp needs) from one mel pass."""
     bank = plan.mel_bank(float(sr), n_fft, 128, 0.0, 11025.0, str(x.device))
-    out = ops.frames_fft(x, n_fft, hop, x.shape[-1] // hop, torch.hann_window, banks=[(bank, True, True)])
+    rag = dict(clip_samples=lens.n, clip_frames=lens.T) if lens is not None else {}
+    out = ops.frames_fft(x, n_fft, hop, x.shape[-1] // hop, torch.hann_window, banks=[(bank, True, True)], **rag)
     pad = 1 + n_fft // (2 * hop)
     mean = ops.onset_flux(out["bank0"], out["bank0_max"], pad, "mean")
     med = ops.onset_flux(out["bank0"], out["bank0_max"], pad, "median") if want_median else None
@@ -86,16 +89,17 @@ MIR_GROUPS = (("chromagram", 12), ("tonnetz", 6), ("mfcc", 20), ("spectral_contr
               ("rms", 1), ("drop_strength", 1), ("onsets", 1))
 
 
-def _cens_and_tonnetz(y: torch.Tensor, sr, hop: int, sync_free: bool):
+def _cens_and_tonnetz(y: torch.Tensor, sr, hop: int, sync_free: bool, lens=None):
     """chroma_cens(y, sr).T and the tonnetz of it (rosa/spectral.py:239-280, features/audio.py:48-57) -> [B, T, 12], [B, T, 6].
     The tuning is estimated from `y` itself (chroma_cqt's tuning=None)."""
-    C = ops.cqt(y, sr, hop, sync_free=sync_free)
-    cens = ops.cens_smooth(ops.chroma_from_cqt(C, quantize=True), plan.cens_window(41, str(y.device)), l2=True)
+    C = ops.cqt(y, sr, hop, sync_free=sync_free, lens=lens)
+    cens = ops.cens_smooth(ops.chroma_from_cqt(C, quantize=True), plan.cens_window(41, str(y.device)), l2=True,
+                           clip_frames=lens.T if lens is not None else None)
     return cens, ops.tonnetz(cens)
 
 
 def feature_chain(x: torch.Tensor, sr, want_a2f: bool = True, want_mir: bool = False, sync_free: bool = False,
-                  pulse_of: str = "perc"):
+                  pulse_of: str = "perc", lens=None):
     """Every per-frame feature of a batch of clips x [B, N] that is ALREADY at sr = 1024 * fps (n_fft 2048, hop 1024):
 
       a2f: the 59 un-clamped, un-smoothed columns of supervised/data.py:64-99 -> [B, T, 59]
@@ -108,7 +112,9 @@ def feature_chain(x: torch.Tensor, sr, want_a2f: bool = True, want_mir: bool = F
     percussive share the STFT and the medians; the three band filters share the 4 kHz high-pass.  The two paths differ in
     which signal the chroma features see: mir.py's chromagram(audio) = chroma_cens(harmonic(audio)), while data.py:68-69
     passes audio_harm in, i.e. chroma_cens(harmonic(harmonic(audio))) — both are built when both are wanted.
-    pulse_of: "perc" = plp(audio_perc) (data.py:89), "audio" = plp(audio) (features/generate.py:123)."""
+    pulse_of: "perc" = plp(audio_perc) (data.py:89), "audio" = plp(audio) (features/generate.py:123).
+    lens: `ragged.ClipLengths` when the rows of x are clips of DIFFERENT lengths (valid samples followed by zeros): every
+    kernel then works on each clip's own length and the rows past a clip's frame count come back as zeros / don't-care."""
     B, N = x.shape
     n_fft, hop = 2048, 1024
     T = N // hop
@@ -116,37 +122,39 @@ def feature_chain(x: torch.Tensor, sr, want_a2f: bool = True, want_mir: bool = F
 
     # --- one pass over the audio: complex STFT (T + 1 frames) + mel(mfcc) / magnitude(contrast) / flatness / rms (T frames)
     mel_bank = plan.mel_bank(float(sr), n_fft, 128, 0.0, None, dev)
+    rag1 = dict(clip_samples=lens.n, clip_frames=lens.T1) if lens is not None else {}
+    cf = lens.T if lens is not None else None
     fa = ops.frames_fft(x, n_fft, hop, T + 1, torch.hann_window, want_complex=True, spec_power=1, want_flatness=True,
-                        want_rms=True, banks=[(mel_bank, True, True)], aux_frames=T)
+                        want_rms=True, banks=[(mel_bank, True, True)], aux_frames=T, **rag1)
     mfcc = ops.mfcc_from_mel(fa["bank0"], fa["bank0_max"], plan.dct_matrix(20, 128, dev))
     contrast = ops.spectral_contrast(fa["spec"], plan.contrast_bands(float(sr), n_fft, 200.0, 6, 0.02, dev))
     flatness = fa["flatness"]
 
     # --- harmonic / percussive separation
-    harm, perc = hpss_pair(x, D=fa["complex"])
+    harm, perc = hpss_pair(x, D=fa["complex"], lens=lens)
     del fa["complex"], fa["spec"]
-    on, on_med = onset_pair(perc, sr, hop, n_fft, want_median=want_a2f and pulse_of == "perc")
+    on, on_med = onset_pair(perc, sr, hop, n_fft, want_median=want_a2f and pulse_of == "perc", lens=lens)
     if want_a2f and pulse_of != "perc":
-        on_med = onset_pair(x, sr, hop, n_fft, want_median=True)[1]
+        on_med = onset_pair(x, sr, hop, n_fft, want_median=True, lens=lens)[1]
 
     out = {}
     cens1 = ton1 = None
     if want_mir:
-        cens1, ton1 = _cens_and_tonnetz(harm, sr, hop, sync_free)  # chromagram(audio), tonnetz(audio)
+        cens1, ton1 = _cens_and_tonnetz(harm, sr, hop, sync_free, lens)  # chromagram(audio), tonnetz(audio)
     if want_a2f or want_mir:
         rms_x_bands = band_rms(x, sr, T) if want_a2f else ()
         rms_a = torch.stack([fa["rms"], *rms_x_bands], dim=-1)  # [B, T, 4] (or [B, T, 1])
-        drop = ops.emphasize(ops.gauss1d(rms_a, 10, "circular", batched=True), 10, 50)
+        drop = ops.emphasize(ops.gauss1d(rms_a, 10, "circular", batched=True, clip_frames=cf), 10, 50, clip_frames=cf)
     if want_a2f:
         # harmonic(audio_harm): features/audio.py:44-45 applied to data.py:68-69's argument; the same launch gives rms(harm)
-        fh = ops.frames_fft(harm, n_fft, hop, T + 1, torch.hann_window, want_complex=True, want_rms=True, aux_frames=T)
-        harm2 = hpss_pair(harm, D=fh["complex"], want_perc=False)[0]
+        fh = ops.frames_fft(harm, n_fft, hop, T + 1, torch.hann_window, want_complex=True, want_rms=True, aux_frames=T, **rag1)
+        harm2 = hpss_pair(harm, D=fh["complex"], want_perc=False, lens=lens)[0]
         del fh["complex"]
-        cens, ton = _cens_and_tonnetz(harm2, sr, hop, sync_free)
+        cens, ton = _cens_and_tonnetz(harm2, sr, hop, sync_free, lens)
         # onset envelopes of the percussive part's three bands; pulse
         p_lo, p_mid, p_hi = band_split(perc, sr)
-        on_lo, on_mid, on_hi = (onset_pair(b, sr, hop, n_fft)[0] for b in (p_lo, p_mid, p_hi))
-        pulse = ops.plp_from_onset(on_med, sr, hop)
+        on_lo, on_mid, on_hi = (onset_pair(b, sr, hop, n_fft, lens=lens)[0] for b in (p_lo, p_mid, p_hi))
+        pulse = ops.plp_from_onset(on_med, sr, hop, lens=lens)
         # band signals of harm / x are only ever looked at through their RMS: taken from the filters' output passes
         rms_h = [fh["rms"], *band_rms(harm, sr, T)]
         Tm = min(T, cens.shape[1])
@@ -156,19 +164,20 @@ def feature_chain(x: torch.Tensor, sr, want_a2f: bool = True, want_mir: bool = F
         out["a2f"] = torch.cat(cols, dim=2).contiguous()
     if want_mir:
         Tm = min(T, cens1.shape[1])
-        onsets = ops.normalize(on, B)  # features/audio.py:27-28
+        onsets = ops.normalize(on, B, clip_rows=cf)  # features/audio.py:27-28
         cols = [cens1[:, :Tm], ton1[:, :Tm], mfcc[:, :Tm], contrast[:, :Tm]]
         cols += [s[:, :Tm, None] for s in (flatness, fa["rms"], drop[:, :, 0], onsets)]
         out["mir"] = torch.cat(cols, dim=2).contiguous()
     return out
 
 
-def finish_features(feats: torch.Tensor, fps, clamp=True, smooth=True, emphasis=False, deferred_checks=None):
+def finish_features(feats: torch.Tensor, fps, clamp=True, smooth=True, emphasis=False, deferred_checks=None, lens=None):
     """supervised/data.py:100-106 on [B, T, 59]: peak-percentile clamp, lower-percentile clamp, smoothing, emphasis."""
+    cf = lens.T if lens is not None else None
     if clamp:
-        thr, cnt = ops.col_quantile(feats, (100 - 2.5) / 100, "peaks", "linear", want_count=True)
+        thr, cnt = ops.col_quantile(feats, (100 - 2.5) / 100, "peaks", "linear", want_count=True, clip_frames=cf)
         feats = ops.clamp_cols(feats, None, thr)
-        feats = ops.clamp_cols(feats, ops.col_quantile(feats, 4 * 2.5 / 100), None)
+        feats = ops.clamp_cols(feats, ops.col_quantile(feats, 4 * 2.5 / 100, clip_frames=cf), None)
         # the reference raises when a column has no interior peak; reading the count back synchronises the stream, so a
         # batched caller may collect the check and run it after it has queued the rest of its work
         if deferred_checks is None:
@@ -176,16 +185,17 @@ def finish_features(feats: torch.Tensor, fps, clamp=True, smooth=True, emphasis=
         else:
             deferred_checks.append(functools.partial(_check_peak_counts, cnt))
     if smooth:
-        feats = ops.gauss1d(feats, 0.1 * fps, "circular", batched=True)
+        feats = ops.gauss1d(feats, 0.1 * fps, "circular", batched=True, clip_frames=cf)
     if emphasis:
-        feats = ops.emphasize(feats, 2, 75)
+        feats = ops.emphasize(feats, 2, 75, clip_frames=cf)
     return feats
 
 
-def patch_inputs_from_raw(mir_raw: torch.Tensor):
+def patch_inputs_from_raw(mir_raw: torch.Tensor, lens=None):
     """random/mir.py:44 for a batch: [B, T, 49] raw features (MIR_GROUPS order) -> dict name -> [B, T, C] of
     normalize(salience_weighted(gaussian_filter(f, sigma=2))), each (clip, feature) block normalised on its own."""
-    parts = ops.salience_features(mir_raw, [n for _, n in MIR_GROUPS], sigma=2.0, short_sigma=5.0, long_sigma=80.0)
+    parts = ops.salience_features(mir_raw, [n for _, n in MIR_GROUPS], sigma=2.0, short_sigma=5.0, long_sigma=80.0,
+                                  clip_frames=lens.T if lens is not None else None)
     return {name: p for (name, _), p in zip(MIR_GROUPS, parts)}
 
 
@@ -208,15 +218,16 @@ def music_features_batch(x: torch.Tensor, sr, sync_free=False):
     return patch_inputs_from_raw(feature_chain(x, sr, want_a2f=False, want_mir=True, sync_free=sync_free)["mir"])
 
 
-def features_and_patch_inputs(audio: torch.Tensor, sr, fps, deferred_checks=None, sync_free=False):
+def features_and_patch_inputs(audio: torch.Tensor, sr, fps, deferred_checks=None, sync_free=False, lens=None):
     """One pass over a batch of clips [B, N] at `sr` for both consumers of the north-star unit: the dataset features
     `audio2features(audio, sr, fps)` [B, T, 59] (supervised/data.py:60-107) and the `Patch` inputs
     `retrieve_music_information(resample(audio, sr, 1024 * fps), 1024 * fps)[0]` (random/sample.py:34,61; mir.py:26,44)."""
     from .resampling import resample
 
-    x = resample(audio, sr, fps * 1024)
-    ch = feature_chain(x, fps * 1024, want_a2f=True, want_mir=True, sync_free=sync_free)
-    return finish_features(ch["a2f"], fps, deferred_checks=deferred_checks), patch_inputs_from_raw(ch["mir"])
+    x = resample(audio, sr, fps * 1024, clip_n_in=lens.n_in if lens is not None else None)
+    ch = feature_chain(x, fps * 1024, want_a2f=True, want_mir=True, sync_free=sync_free, lens=lens)
+    return (finish_features(ch["a2f"], fps, deferred_checks=deferred_checks, lens=lens),
+            patch_inputs_from_raw(ch["mir"], lens=lens))
 
 
 class FeatureGraph:
