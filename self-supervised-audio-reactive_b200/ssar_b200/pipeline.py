@@ -313,6 +313,163 @@ class FeatureGraph:
         return feats, pf
 
 
+class RaggedFeatureGraph:
+    """`features_and_patch_inputs` for up to `n_clips` clips of DIFFERENT lengths (each <= `cap_samples`) as one replayed
+    CUDA graph: the clips sit zero-padded in the static input, their lengths are device data (`ragged.ClipLengths`, fixed
+    addresses), so one capture serves every combination of lengths — the per-track eager pass (~400 launches) a dataset
+    of 1000 distinct durations would otherwise need is replaced by one graph launch per chunk."""
+
+    _cache = {}
+    MAX_GRAPHS = 10  # one per capacity bucket (~0.05 GB per clip-minute each)
+
+    @classmethod
+    def get(cls, n_clips, cap_samples, sr, fps, device):
+        device = torch.device(device)
+        key = (int(n_clips), int(cap_samples), float(sr), int(fps), device.index, threading.get_ident())
+        with FeatureGraph._lock:
+            g = cls._cache.pop(key, None)
+            if g is None:
+                mine = [k for k in cls._cache if k[-1] == key[-1]]
+                while len(mine) >= cls.MAX_GRAPHS:
+                    cls._cache.pop(mine.pop(0))
+                g = cls(n_clips, cap_samples, sr, fps, device)
+            cls._cache[key] = g
+        return g
+
+    def __init__(self, n_clips, cap_samples, sr, fps, device):
+        from .ragged import ClipLengths
+
+        self.device, self.sr, self.fps, self.B, self.cap = device, sr, fps, int(n_clips), int(cap_samples)
+        with torch.cuda.device(device):
+            self.x = torch.zeros(n_clips, cap_samples, dtype=torch.float32, device=device)
+            self.x[:, ::997] = 0.25  # not silent: the warm-up pass must not hit the reference's empty-peak-set error
+            self.x[:, 1::1499] = -0.5
+            self.lens = ClipLengths(n_clips, device).update([cap_samples] * n_clips, sr, fps * 1024)
+            cs = torch.cuda.Stream(device)
+            cs.wait_stream(torch.cuda.current_stream(device))
+            with torch.cuda.stream(cs):
+                features_and_patch_inputs(self.x, sr, fps, deferred_checks=[], sync_free=True, lens=self.lens)
+            cs.synchronize()
+            self.graph = torch.cuda.CUDAGraph()
+            checks = []
+            with torch.cuda.graph(self.graph, stream=cs, capture_error_mode="thread_local"):
+                self.feats, self.patch_feats = features_and_patch_inputs(self.x, sr, fps, deferred_checks=checks,
+                                                                         sync_free=True, lens=self.lens)
+            self.peak_count = checks[0].args[0] if checks else None
+
+    def run(self, clips, deferred_checks=None):
+        """clips: up to n_clips 1-D waveforms (CUDA or pinned host), each <= cap_samples long.  Replays on the current
+        stream -> (features [B, T_cap, 59], patch feature dict, frames per clip); rows past a clip's own frame count and
+        clips beyond len(clips) are don't-care."""
+        n = len(clips)
+        lengths = [int(c.shape[-1]) for c in clips]
+        pad = lengths + [lengths[-1]] * (self.B - n)  # unused slots repeat the last clip's length (and hold its audio)
+        self.lens.update(pad, self.sr, self.fps * 1024)
+        for b in range(self.B):
+            c, L = clips[min(b, n - 1)], pad[b]
+            self.x[b, :L].copy_(c, non_blocking=True)
+            if L < self.cap:
+                self.x[b, L:].zero_()
+        self.graph.replay()
+        feats = self.feats[:n].clone()
+        pf = {k: v[:n].clone() for k, v in self.patch_feats.items()}
+        if self.peak_count is not None:
+            cnt = self.peak_count[:n].clone()
+            if deferred_checks is not None:
+                deferred_checks.append(functools.partial(_check_peak_counts, cnt))
+            else:
+                _check_peak_counts(cnt)
+        return feats, pf, list(self.lens.host_T[:n])
+
+
+def features_and_latents_ragged(clips, sr, fps, palette: torch.Tensor, segmentations, tempo=120.0, seed=42,
+                                rng_device="cuda", chunk=8, bucket_seconds=30.0, on_clip=None, use_graphs=True,
+                                stats=None):
+    """The north-star unit for tracks of DIFFERENT durations (SURVEY 8d cfg 5): clips = list of 1-D waveforms at `sr`
+    (CUDA, or pinned host: staged per chunk).  Tracks are processed longest first in chunks of `chunk`, each chunk
+    zero-padded to its longest member rounded up to `bucket_seconds` — ONE ragged launch set (a replayed CUDA graph per
+    capacity bucket) serves the chunk, results identical to per-track calls (tests/test_gpu_ragged.py).
+
+    segmentations: dict (name, k) -> label tensor of at least the longest track's frame count (sliced per track), or a
+    callable (track index, n_frames) -> dict.  on_clip(i, features [T_i, 59], latents [T_i, 18, 512]) is called per
+    track while its latents are alive (1000 four-minute tracks of latents are 212 GB: they cannot all stay resident);
+    without it the features and latents of every track are collected and returned as two lists (small sets only).
+    stats: optional fp64 [3, 59] accumulator of the dataset statistic (count, sum, sum of squares over valid frames)."""
+    from .random.patch import Patch, precapture_sampler_graphs, sampler_kernel_ready
+
+    dev = palette.device
+    if dev.type != "cuda":
+        raise ops.SsarError("features_and_latents_ragged needs the palette (and the compute) on a CUDA device")
+    n_tracks = len(clips)
+    if n_tracks == 0:
+        return [], []
+    order = sorted(range(n_tracks), key=lambda i: (-int(clips[i].shape[-1]), i))
+    chunk = max(1, int(chunk))
+    bucket = max(1, int(round(bucket_seconds * sr)))
+    stream = torch.cuda.current_stream(dev)
+    fstream = _side_stream(dev, "features")
+    seg0 = segmentations if isinstance(segmentations, dict) else segmentations(order[0], int(clips[order[0]].shape[-1]) * fps // sr)
+    if str(rng_device).startswith("cuda"):
+        with torch.cuda.device(dev):
+            if not sampler_kernel_ready(dev, seg0):
+                precapture_sampler_graphs(dev, seg0)
+    with torch.cuda.device(dev), torch.cuda.stream(stream):
+        palette_split = ops.SplitBasis(palette)
+    feats_out, lat_out = [None] * n_tracks, [None] * n_tracks
+    checks = []
+    W, L = palette.shape[1], palette.shape[2]
+
+    def render(item):
+        idxs, f, pf, Ts, done = item
+        with torch.cuda.device(dev), torch.cuda.stream(stream):
+            stream.wait_event(done)
+            patches = Patch.sample_batch([seed + i for i in idxs], seg0, tempo, fps=fps, device=rng_device)
+            lat = torch.empty(len(idxs), max(Ts), W, L, dtype=torch.float32, device=dev)
+            for j, i in enumerate(idxs):
+                T = Ts[j]
+                segs = ({k: v[:T] for k, v in segmentations.items()} if isinstance(segmentations, dict)
+                        else segmentations(i, T))
+                patches[j].segmentations = segs
+                patches[j].bind({k: v[j, :T] for k, v in pf.items()})
+                patches[j].forward(palette, downscale_factor=4, latents_out=lat[j, :T], palette_split=palette_split)
+                if stats is not None:
+                    ops.feature_stats(f[j, :T], stats)
+                if on_clip is not None:
+                    on_clip(i, f[j, :T], lat[j, :T])
+                else:
+                    feats_out[i], lat_out[i] = f[j, :T], lat[j, :T]
+
+    pending = None
+    fstream.wait_stream(stream)
+    for c0 in range(0, n_tracks, chunk):
+        idxs = order[c0 : c0 + chunk]
+        cap = -(-int(clips[idxs[0]].shape[-1]) // bucket) * bucket  # longest first: the chunk's first track
+        with torch.cuda.device(dev), torch.cuda.stream(fstream):
+            if use_graphs:
+                f, pf, Ts = RaggedFeatureGraph.get(chunk, cap, sr, fps, dev).run([clips[i] for i in idxs], deferred_checks=checks)
+            else:
+                from .ragged import ClipLengths
+
+                lens = ClipLengths(len(idxs), dev).update([int(clips[i].shape[-1]) for i in idxs], sr, fps * 1024)
+                x = torch.zeros(len(idxs), cap, dtype=torch.float32, device=dev)
+                for b, i in enumerate(idxs):
+                    x[b, : clips[i].shape[-1]].copy_(clips[i], non_blocking=True)
+                f, pf = features_and_patch_inputs(x, sr, fps, deferred_checks=checks, lens=lens)
+                Ts = list(lens.host_T)
+            done = torch.cuda.Event()
+            done.record(fstream)
+            for t in (f, *pf.values()):
+                t.record_stream(stream)
+        if pending is not None:
+            render(pending)  # chunk k's patches are queued while chunk k + 1's feature kernels run
+        pending = (idxs, f, pf, Ts, done)
+    render(pending)
+    fstream.wait_stream(stream)
+    for check in checks:
+        check()
+    return feats_out, lat_out
+
+
 USE_FEATURE_GRAPHS = True  # batched pipeline: replay the feature path of each chunk as a CUDA graph
 
 _POOLS = {}

@@ -77,3 +77,34 @@ def test_ragged_stages_equal_per_clip_calls():
         assert torch.equal(fin[b, :T], pipeline.finish_features(feats[b : b + 1, :T].contiguous(), FPS)[0]), b
         ops.feature_stats(feats[b, :T].contiguous(), ref_stats)
     assert torch.equal(stats[0], ref_stats[0]) and rel_l2(stats, ref_stats) < 1e-12
+
+
+def test_ragged_pipeline_graph_equals_per_track_calls():
+    """features_and_latents_ragged (longest-first chunks, capacity buckets, replayed ragged graph) == one
+    features_and_latents call per track, features and latents bit for bit; the dataset statistic over valid frames only."""
+    from ssar_b200 import ops, pipeline
+    from ssar_b200.synth import synth_patch_inputs
+
+    secs = (50.0, 61.37, 47.713, 55.5, 44.2)
+    clips = [synth_clip(int(SR44 * s), SR44, 30 + i).cuda() for i, s in enumerate(secs)]
+    Tmax = max(len(c) for c in clips) * FPS // SR44 + 2
+    _, segs, palette = synth_patch_inputs(Tmax, 0)
+    palette = palette.cuda()
+    segs = {k: v.cuda() for k, v in segs.items()}
+    ref = []
+    for i, c in enumerate(clips):
+        T = (-(-len(c) * 2048 // 3675)) // 1024
+        f, lat, _ = pipeline.features_and_latents(c[None], SR44, FPS, palette, {k: v[:T] for k, v in segs.items()}, seed=42 + i,
+                                                  serial=True)
+        ref.append((f[0], lat[0]))
+    for use_graphs in (False, True, True):  # eager ragged, graph capture, graph replay
+        stats = torch.zeros(3, 59, dtype=torch.float64, device="cuda")
+        feats, lats = pipeline.features_and_latents_ragged(clips, SR44, FPS, palette, segs, chunk=2, bucket_seconds=10.0,
+                                                           use_graphs=use_graphs, stats=stats)
+        torch.cuda.synchronize()
+        ref_stats = torch.zeros_like(stats)
+        for i, (f, lat) in enumerate(ref):
+            assert torch.equal(feats[i], f), (use_graphs, i, rel_l2(feats[i], f))
+            assert torch.equal(lats[i], lat), (use_graphs, i, rel_l2(lats[i], lat))
+            ops.feature_stats(f, ref_stats)
+        assert torch.equal(stats[0], ref_stats[0]) and rel_l2(stats, ref_stats) < 1e-12
