@@ -37,12 +37,17 @@ import torch  # noqa: E402
 
 SR, DUR_S, N_FFT, HOP2 = 44100, 240, 2048, 512
 FPS = 24
-DEFAULT_CLIPS = {"full": 32, "cfg2": 64}
+DEFAULT_CLIPS = {"full": 32, "cfg2": 64, "cfg5": 1000}
+CFG5_SECONDS = (120.0, 360.0)  # SURVEY 8d cfg 5: track durations ~ U[120, 360] s, seeded
 
 
 def workload_name(kind, clips):
     if kind == "cfg2":
         return f"cfg2: STFT+mel+onset+RMS, {clips} clips x {DUR_S} s @44.1kHz per GPU, n_fft {N_FFT} hop {HOP2}"
+    if kind == "cfg5":
+        return (f"cfg5: audio2features + Patch latents for {clips} tracks of U[{CFG5_SECONDS[0]:.0f}, {CFG5_SECONDS[1]:.0f}] s "
+                f"@44.1kHz IN TOTAL (strong scaling), sharded by track (longest-first bin packing), ragged chunks of 8, "
+                f"per-feature (count, sum, sum^2) all-reduced over NCCL")
     return (f"full: audio2features [5760,59] + Patch latents [5760,18,512], {clips} clips x {DUR_S} s @44.1kHz per GPU "
             f"(resampled to {FPS * 1024} Hz, n_fft {N_FFT} hop 1024, {FPS} fps)")
 
@@ -280,13 +285,172 @@ class EventLog(dict):
         return self.setdefault(k, [])
 
 
+def cfg5_durations(n_tracks):
+    g = torch.Generator("cpu").manual_seed(2025)
+    return (CFG5_SECONDS[0] + (CFG5_SECONDS[1] - CFG5_SECONDS[0]) * torch.rand(n_tracks, generator=g)).tolist()
+
+
+def run_cfg5(args, rank, world, local_rank):
+    """configs[4]: 1000 tracks of different durations over the node's GPUs.  One step = one pass over ALL tracks (strong
+    scaling): every rank processes its shard (longest-first greedy bin packing by duration) through the ragged pipeline,
+    accumulates the per-feature (count, sum, sum^2) of its frames in fp64 and the ranks all-reduce them (NCCL) into the
+    dataset mean / std."""
+    import torch.distributed as dist
+
+    from ssar_b200 import _cabi as cabi
+    from ssar_b200 import distributed, ops, pipeline
+    from ssar_b200.synth import synth_batch_device, synth_clip, synth_patch_inputs
+
+    sys.stdout.flush()
+    result_fd = os.dup(1)
+    os.dup2(2, 1)
+    result_out = os.fdopen(result_fd, "w")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    durations = cfg5_durations(args.clips)
+    mine = distributed.shard_clips(durations, world)[rank]
+    lengths = {i: int(round(durations[i] * SR)) for i in mine}
+    clips = [synth_batch_device(1, lengths[i], SR, dev, first_index=i)[0] for i in mine]  # resident in HBM
+    Tmax = int(CFG5_SECONDS[1] * FPS) + 2
+    _, segs, palette = synth_patch_inputs(Tmax, 0)
+    palette, segs = palette.to(dev), {k: v.to(dev) for k, v in segs.items()}
+    stats = torch.zeros(3, 59, dtype=torch.float64, device=dev)
+    total_audio_s = sum(durations)
+    steps, warmup = max(1, args.steps), max(1, min(args.warmup, 2))
+
+    def step(src, on_clip=None):
+        stats.zero_()
+        pipeline.features_and_latents_ragged(src, SR, FPS, palette, segs, rng_device=args.rng, chunk=args.chunk,
+                                             on_clip=on_clip or (lambda i, f, lat: None), stats=stats)
+        if world > 1:
+            dist.all_reduce(stats)
+        return stats
+
+    for _ in range(warmup):
+        step(clips)
+    barrier()
+    launches0 = cabi.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(range(world) if world > 1 else [local_rank], enabled=(rank == 0)) as clocks:
+        barrier()
+        ev0.record()
+        for _ in range(steps):
+            step(clips)
+        ev1.record()
+        barrier()
+    ms = ev0.elapsed_time(ev1)
+    launches = cabi.launch_count - launches0
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    value = total_audio_s * steps / (ms_max * 1e-3)
+    mean, std = distributed.mean_std_from_stats(stats.clone())
+
+    # e2e: the rank's first tracks from PINNED HOST memory (staged per chunk inside the call), features + a latent checksum
+    # back to pinned host per track
+    e2e = None
+    if not args.no_e2e:
+        sub = list(range(min(len(clips), 96)))
+        host = [clips[j].cpu().pin_memory() for j in sub]
+        host_f = [torch.empty(int(lengths[mine[j]] * 2048 // 3675 + 1) // 1024, 59, pin_memory=True) for j in sub]
+        host_c = torch.zeros(len(sub), pin_memory=True)
+
+        def sink(i, f, lat):
+            host_f[i][: f.shape[0]].copy_(f, non_blocking=True)
+            host_c[i : i + 1].copy_(lat.sum().reshape(1), non_blocking=True)
+
+        step(host, sink)
+        barrier()
+        t0 = time.perf_counter()
+        step(host, sink)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        td = torch.tensor([dt, sum(durations[mine[j]] for j in sub)], device=dev, dtype=torch.float64)
+        if world > 1:
+            tmax = td[:1].clone()
+            dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+            dist.all_reduce(td[1:], op=dist.ReduceOp.SUM)
+            td[0] = tmax[0]
+        e2e = {"value": float(td[1] / td[0]), "unit": "audio-s/s",
+               "h2d_bytes_per_step": int(sum(h.numel() * 4 for h in host)), "d2h_bytes_per_step": int(sum(h.numel() * 4 for h in host_f) + 4 * len(sub)),
+               "steps": 1, "note": f"per rank: its first {len(sub)} tracks from pinned host memory, features + latent checksum back per track"}
+
+    # per-kernel table of one eager ragged chunk (8 tracks), CUDA events around each launch
+    barrier()
+    per_kernel = {}
+    if rank == 0:
+        cabi.event_log = EventLog()
+        pipeline.features_and_latents_ragged(clips[:8], SR, FPS, palette, segs, rng_device=args.rng, chunk=8, use_graphs=False,
+                                             on_clip=lambda i, f, lat: None)
+        torch.cuda.synchronize()
+        for name, evs in cabi.event_log.items():
+            per_kernel[name] = (sum(a.elapsed_time(b) for a, b, _ in evs), sum(c for _, _, c in evs if c is not None), len(evs))
+        cabi.event_log = None
+    verify = None
+    if rank == 0 and world == 1 and args.verify_tracks > 0:
+        from ssar_oracle import features as ofeat
+        import numpy as np
+        idx = list(range(min(args.verify_tracks, len(clips))))
+        sub_stats = torch.zeros(3, 59, dtype=torch.float64, device=dev)
+        pipeline.features_and_latents_ragged([clips[j] for j in idx], SR, FPS, palette, segs, rng_device=args.rng,
+                                             on_clip=lambda i, f, lat: None, stats=sub_stats)
+        m_gpu, s_gpu = distributed.mean_std_from_stats(sub_stats)
+        ref = np.concatenate([ofeat.audio2features(clips[j].cpu(), SR, FPS).numpy() for j in idx])
+        keep = [j for j in range(59) if j != 50]
+        verify = {"tracks": len(idx), "mean_rel_l2": float(np.linalg.norm(m_gpu.cpu().numpy()[keep] - ref.mean(0)[keep]) / np.linalg.norm(ref.mean(0)[keep])),
+                  "std_rel_l2": float(np.linalg.norm(s_gpu.cpu().numpy()[keep] - ref.std(0)[keep]) / np.linalg.norm(ref.std(0)[keep]))}
+    if rank == 0:
+        peak, peak_src = measured_peaks()
+        top = sorted(per_kernel.items(), key=lambda kv: -kv[1][0])
+        name, (k_ms, k_bytes, k_n) = top[0]
+        roof = {"bound": "hbm", "kernel": name, "achieved": k_bytes / (k_ms * 1e-3) / 1e9 if k_bytes else None, "peak": peak,
+                "peak_source": peak_src, "unit": "GB/s", "traffic": None,
+                "timing": "CUDA events around each launch of ONE eager ragged chunk (the 8 longest tracks of rank 0)",
+                "top5_ms_per_chunk": {k: round(v[0], 3) for k, v in top[:5]}}
+        roof["frac"] = roof["achieved"] / peak if roof["achieved"] else None
+        cpu = None
+        if world == 1 and not args.no_cpu:
+            n_threads = use_all_host_threads()
+            x = synth_clip(int(SR * CFG5_SECONDS[0]), SR, 0)
+            t0 = time.perf_counter()
+            cpu_pass("full", x, SR)
+            dt = time.perf_counter() - t0
+            cpu = {"value": CFG5_SECONDS[0] / dt, "unit": "audio-s/s", "cores": n_threads, "kind": "port",
+                   "sample": f"1 track x {CFG5_SECONDS[0]:.0f} s (the shortest duration of the workload), oracle port, {dt:.2f} s"}
+        result_out.write(json.dumps({
+            "metric": "audio-sec/sec", "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": steps, "warmup": warmup,
+            "ms_per_step": ms_max / steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": workload_name("cfg5", args.clips), "tracks_total": args.clips, "tracks_rank0": len(mine),
+                       "audio_seconds_total": total_audio_s, "chunk": args.chunk,
+                       "l2": f"inputs_exceed_l2 ({sum(lengths.values()) * 4 / 1e9:.1f} GB of waveforms on rank 0)",
+                       "parallelism": f"track-sharded x{world} (longest-first greedy bin packing); one NCCL all-reduce of 59x3 fp64 per step",
+                       "dataset_mean_head": [round(float(v), 5) for v in mean[:4]], "dataset_std_head": [round(float(v), 5) for v in std[:4]],
+                       "verify_vs_oracle": verify},
+            "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
+        }) + "\n")
+        result_out.flush()
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="full", choices=["full", "cfg2"])
+    ap.add_argument("--workload", default="full", choices=["full", "cfg2", "cfg5"])
+    ap.add_argument("--verify-tracks", type=int, default=0, help="cfg5: compare mean / std of this many tracks with the CPU oracle")
     ap.add_argument("--clips", type=int, default=None)
     ap.add_argument("--rng", default="cuda", choices=["cpu", "cuda"], help="device of the per-clip Patch generator")
     ap.add_argument("--workers", type=int, default=None, help="host threads building the per-clip patches")
@@ -303,6 +467,8 @@ def main():
     if args.impl == "reference":
         run_reference(args, rank)
         return
+    if args.workload == "cfg5":
+        return run_cfg5(args, rank, world, local_rank)
     args.warmup = max(args.warmup, 3)
 
     import torch.distributed as dist

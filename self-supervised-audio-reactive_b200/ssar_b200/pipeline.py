@@ -419,21 +419,66 @@ def features_and_latents_ragged(clips, sr, fps, palette: torch.Tensor, segmentat
     checks = []
     W, L = palette.shape[1], palette.shape[2]
 
+    class _Prefix(dict):
+        """segmentations[(name, k)][:T], sliced when (if) a sub-patch asks for that key."""
+
+        def __init__(self, full, T):
+            super().__init__()
+            self._full, self._T = full, T
+
+        def __missing__(self, key):
+            v = self[key] = self._full[key][: self._T]
+            return v
+
+        def keys(self):
+            return self._full.keys()
+
+        def __iter__(self):
+            return iter(self._full)
+
+        def __len__(self):
+            return len(self._full)
+
+    # the config draws of every track (patch.py:41-66 needs no feature values) on a helper thread and a high-priority
+    # side stream, 64 seeds per sampler launch + read-back, in processing order: the chunk loop below waits only for
+    # the batch of 64 its tracks are in, and otherwise never on the GPU, so the host queues ahead of the kernels
+    patch_of, sampled, sample_error = {}, {}, []
+    batches = [order[c0 : c0 + 64] for c0 in range(0, n_tracks, 64)]
+    for part in batches:
+        ev = threading.Event()
+        for i in part:
+            sampled[i] = ev
+
+    def sample_job():
+        try:
+            with torch.cuda.device(dev), torch.cuda.stream(_side_stream(dev)):
+                for part in batches:
+                    for i, pt in zip(part, Patch.sample_batch([seed + i for i in part], seg0, tempo, fps=fps, device=rng_device)):
+                        patch_of[i] = pt
+                    sampled[part[0]].set()
+        except BaseException as e:  # surfaced by the calling thread
+            sample_error.append(e)
+            for ev in sampled.values():
+                ev.set()
+
+    sampler = _pool(3).submit(sample_job)
+
     def render(item):
-        idxs, f, pf, Ts, done = item
+        idxs, f, pf, Ts, done, frames_dev = item
         with torch.cuda.device(dev), torch.cuda.stream(stream):
             stream.wait_event(done)
-            patches = Patch.sample_batch([seed + i for i in idxs], seg0, tempo, fps=fps, device=rng_device)
+            if stats is not None:
+                ops.feature_stats(f, stats, clip_frames=frames_dev)  # valid frames of the whole chunk in one launch
             lat = torch.empty(len(idxs), max(Ts), W, L, dtype=torch.float32, device=dev)
             for j, i in enumerate(idxs):
                 T = Ts[j]
-                segs = ({k: v[:T] for k, v in segmentations.items()} if isinstance(segmentations, dict)
-                        else segmentations(i, T))
-                patches[j].segmentations = segs
-                patches[j].bind({k: v[j, :T] for k, v in pf.items()})
-                patches[j].forward(palette, downscale_factor=4, latents_out=lat[j, :T], palette_split=palette_split)
-                if stats is not None:
-                    ops.feature_stats(f[j, :T], stats)
+                sampled[i].wait()
+                if sample_error:
+                    raise sample_error[0]
+                patch = patch_of.pop(i)
+                patch.segmentations = _Prefix(segmentations, T) if isinstance(segmentations, dict) else segmentations(i, T)
+                patch.bind({k: v[j, :T] for k, v in pf.items()})
+                patch.forward(palette, downscale_factor=4, latents_out=lat[j, :T], palette_split=palette_split)
                 if on_clip is not None:
                     on_clip(i, f[j, :T], lat[j, :T])
                 else:
@@ -446,7 +491,9 @@ def features_and_latents_ragged(clips, sr, fps, palette: torch.Tensor, segmentat
         cap = -(-int(clips[idxs[0]].shape[-1]) // bucket) * bucket  # longest first: the chunk's first track
         with torch.cuda.device(dev), torch.cuda.stream(fstream):
             if use_graphs:
-                f, pf, Ts = RaggedFeatureGraph.get(chunk, cap, sr, fps, dev).run([clips[i] for i in idxs], deferred_checks=checks)
+                g = RaggedFeatureGraph.get(chunk, cap, sr, fps, dev)
+                f, pf, Ts = g.run([clips[i] for i in idxs], deferred_checks=checks)
+                frames_dev = g.lens.T[: len(idxs)].clone()
             else:
                 from .ragged import ClipLengths
 
@@ -455,15 +502,16 @@ def features_and_latents_ragged(clips, sr, fps, palette: torch.Tensor, segmentat
                 for b, i in enumerate(idxs):
                     x[b, : clips[i].shape[-1]].copy_(clips[i], non_blocking=True)
                 f, pf = features_and_patch_inputs(x, sr, fps, deferred_checks=checks, lens=lens)
-                Ts = list(lens.host_T)
+                Ts, frames_dev = list(lens.host_T), lens.T
             done = torch.cuda.Event()
             done.record(fstream)
-            for t in (f, *pf.values()):
+            for t in (f, frames_dev, *pf.values()):
                 t.record_stream(stream)
         if pending is not None:
             render(pending)  # chunk k's patches are queued while chunk k + 1's feature kernels run
-        pending = (idxs, f, pf, Ts, done)
+        pending = (idxs, f, pf, Ts, done, frames_dev)
     render(pending)
+    sampler.result()
     fstream.wait_stream(stream)
     for check in checks:
         check()

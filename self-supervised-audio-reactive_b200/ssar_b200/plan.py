@@ -636,11 +636,32 @@ def knot_loop_weights_cpu(n_latents: int, size: int, n_loops: int) -> torch.Tens
     return torch.from_numpy(W.astype(np.float32))
 
 
+@functools.lru_cache(maxsize=64)
+def _cardinal_tables_device(K1: int, device):
+    """(t_in fp32 [K1], coefficient tables fp64 [K1 - 1, 4, K1]) of `_cardinal_spline_coeffs` on the device."""
+    a, b, c2, d3 = _cardinal_spline_coeffs(K1)
+    tab = torch.from_numpy(np.stack([a.T, b.T, c2.T, d3.T], axis=1))
+    return torch.linspace(0, 1, K1).to(_dev(device)), tab.to(_dev(device))
+
+
 @functools.lru_cache(maxsize=256)
 def spline_loop_weights(n_knots: int, size: int, n_loops, device) -> torch.Tensor:
-    """`spline_loop_weights_cpu` cached on the device (the weights depend only on the knot count, length and loop count,
-    so every sub-patch / clip of a batch shares them).  Read-only: callers must not write into the result."""
-    return spline_loop_weights_cpu(n_knots, size, n_loops).to(_dev(device))
+    """`spline_loop_weights_cpu` on the device, cached (the weights depend only on the knot count, length and loop count,
+    so every sub-patch / clip of a batch of equal-length clips shares them).  The evaluation points are made on the host
+    like the reference makes them (`torch.linspace(0, n_loops, size) % 1`, latent.py:10); the table lookup and the cubic
+    run on the device in fp64 with the host function's expression — a dataset of tracks of distinct lengths misses the
+    cache for every track, and the numpy version cost 0.6 ms of host time per call.  Read-only result."""
+    K1 = n_knots + 1
+    if K1 == 2:
+        return spline_loop_weights_cpu(n_knots, size, n_loops).to(_dev(device))
+    t_in, tab = _cardinal_tables_device(K1, device)
+    t_out = (torch.linspace(0, n_loops, size) % 1).to(t_in.device, non_blocking=True)
+    idx = (torch.bucketize(t_out, t_in) - 1).clamp(0, K1 - 2)
+    frac = (t_out - t_in[idx]).double()[:, None]
+    c = tab[idx]  # [size, 4, K1]
+    W = c[:, 0] + (c[:, 1] + (0.5 * c[:, 2] + c[:, 3] * frac / 3.0) * frac) * frac
+    W[:, 0] += W[:, -1]
+    return W[:, :-1].float().contiguous()
 
 
 @functools.lru_cache(maxsize=256)

@@ -22,8 +22,11 @@ class ClipLengths:
         self.B, self.device = int(n_clips), torch.device(device)
         self._i64 = torch.zeros(self.I64_ROWS, self.B, dtype=torch.int64, device=self.device)
         self._i32 = torch.zeros(self.I32_ROWS, self.B, dtype=torch.int32, device=self.device)
-        self._h64 = torch.zeros(self.I64_ROWS, self.B, dtype=torch.int64).pin_memory()
-        self._h32 = torch.zeros(self.I32_ROWS, self.B, dtype=torch.int32).pin_memory()
+        # pinned staging for update(): a ring, because the host may queue several chunks ahead of the GPU and an
+        # asynchronous copy reads its pinned source when it EXECUTES (slot reuse waits on the slot's last copy)
+        self._ring = [(torch.zeros(self.I64_ROWS, self.B, dtype=torch.int64).pin_memory(),
+                       torch.zeros(self.I32_ROWS, self.B, dtype=torch.int32).pin_memory(), [None]) for _ in range(4)]
+        self._slot = 0
         self.host_n_in = self.host_n = self.host_T = None
 
     def update(self, n_in, orig: int, new: int, hop: int = 1024):
@@ -35,7 +38,10 @@ class ClipLengths:
         n = [-((-nw * v) // o) for v in n_in]          # ceil(new * n_in / orig): torchaudio's output length
         T = [v // hop for v in n]
         self.host_n_in, self.host_n, self.host_T = n_in, n, T
-        h64, h32 = self._h64, self._h32
+        h64, h32, ev = self._ring[self._slot]
+        self._slot = (self._slot + 1) % len(self._ring)
+        if ev[0] is not None:
+            ev[0].synchronize()
         h64[0] = torch.tensor(n_in)
         h64[1] = torch.tensor(n)
         h64[2] = torch.tensor(T)
@@ -51,6 +57,8 @@ class ClipLengths:
         h32[3] = h32[1]
         self._i64.copy_(h64, non_blocking=True)
         self._i32.copy_(h32, non_blocking=True)
+        ev[0] = torch.cuda.Event()
+        ev[0].record(torch.cuda.current_stream(self.device))
         return self
 
     # int64 views
