@@ -8,32 +8,36 @@
 // persistently with neighbouring warps on neighbouring frames, so the 2x-4x overlapped waveform reads are served by
 // L1/L2 and HBM sees each sample once.  The spectrum of a frame lives only in shared memory: |X|^2 -> filterbanks happen
 // before anything is written, so the [frames, 1025] spectrogram never round-trips HBM unless it is a requested output.
+#include <stdlib.h>
+
 #include "fft_warp.cuh"
 
 namespace {
 
 constexpr int LANE_PAD = 64;  // zeroed floats behind the M + 1 bins of a power tile (lane-interleaved banks read into them)
 
-template <int M>
+template <int M, int WPB>
 size_t frames_smem_bytes(bool window, bool separate_power) {
     using L = WarpFft<M>;
     size_t b = (size_t)32 * L::N1 * sizeof(float2);                  // twiddle table [k2][n1]
     if (window) b += (size_t)2 * M * sizeof(float);
-    b += (size_t)L::WPB * L::FPW * L::ZF * sizeof(float2);
-    if (separate_power) b += (size_t)L::WPB * L::FPW * (M + 4 + LANE_PAD) * sizeof(float);
+    b += (size_t)WPB * L::FPW * L::ZF * sizeof(float2);
+    if (separate_power) b += (size_t)WPB * L::FPW * (M + 4 + LANE_PAD) * sizeof(float);
     return b;
 }
 
-template <int M>
-__global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_args a, const long long total_frames,
-                                                            const int separate_power) {
+// WPB warps per CTA, CPS CTAs per SM: (8, 2) = 16 resident warps at <= 128 registers; (24, 1) = 24 resident warps at
+// <= 85 registers (one CTA owns the SM's shared memory: 24 frame buffers of 8.4 KB + the tables)
+template <int M, int WPB, int CPS>
+__global__ void __launch_bounds__(32 * WPB, CPS) frames_fft_kernel(const ssar_frames_args a, const long long total_frames,
+                                                                   const int separate_power) {
     using L = WarpFft<M>;
     constexpr int N1 = L::N1, FPW = L::FPW, TLD = L::TLD, ZF = L::ZF, N = 2 * M, NBINS = M + 1, NJ = L::NJ;
     extern __shared__ float4 smem_raw[];
     float2* twT = reinterpret_cast<float2*>(smem_raw);                 // [32][N1]: W_M^{n1 k2}
     float* wins = reinterpret_cast<float*>(twT + 32 * N1);             // [2M] or absent
     float2* zall = reinterpret_cast<float2*>(wins + (a.window ? N : 0));
-    float* pall = reinterpret_cast<float*>(zall + L::WPB * FPW * ZF);  // only with separate_power
+    float* pall = reinterpret_cast<float*>(zall + WPB * FPW * ZF);  // only with separate_power
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int h = lane / N1, n1 = lane % N1;  // frame slot inside the warp, point index inside the frame
@@ -48,8 +52,8 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
     float2* zw = zall + (size_t)warp * FPW * ZF;  // this warp's frame buffers
     const bool need_pw = a.out_spec || a.out_flatness || a.fb[0].n_bands > 0 || a.fb[1].n_bands > 0 || a.pip.count;
 
-    for (long long fbase = ((long long)blockIdx.x * L::WPB + warp) * FPW; fbase < total_frames;
-         fbase += (long long)gridDim.x * L::WPB * FPW) {
+    for (long long fbase = ((long long)blockIdx.x * WPB + warp) * FPW; fbase < total_frames;
+         fbase += (long long)gridDim.x * WPB * FPW) {
         // ------------------------------------------------------------------ load + window (lane: n = n1 + N1 r)
         const long long f = fbase + h;
         const bool in_grid = f < total_frames;
@@ -310,9 +314,28 @@ __global__ void __launch_bounds__(256, 2) frames_fft_kernel(const ssar_frames_ar
     }
 }
 
+template <int M, int WPB, int CPS>
+int launch_frames_cfg(const ssar_frames_args& a, cudaStream_t st, long long total, int separate_power) {
+    using L = WarpFft<M>;
+    const size_t smem = frames_smem_bytes<M, WPB>(a.window != nullptr, separate_power != 0);
+    cudaError_t e = cudaFuncSetAttribute(frames_fft_kernel<M, WPB, CPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) {
+        ssar_set_error("frames_fft: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        return SSAR_ERR_CUDA;
+    }
+    const long long groups = (total + WPB * L::FPW - 1) / (WPB * L::FPW);
+    long long grid = (long long)SSAR_NUM_SMS * CPS;  // persistent grid: a multiple of the SM count
+    if (groups < grid) grid = groups;
+    frames_fft_kernel<M, WPB, CPS><<<(unsigned)grid, 32 * WPB, smem, st>>>(a, total, separate_power);
+    return ssar_launch_status("frames_fft");
+}
+
+// 24 warps per SM at 80 registers (236 B of spills per thread) beat 16 warps at 128: cfg2 10.34 -> 8.99 ms per step, full
+// workload 12.0 -> 11.0 ms of frames_fft per step.  SSAR_FRAMES_WIDE=0 selects the 2 x 8-warp configuration.
+int g_frames_wide = -1;
+
 template <int M>
 int launch_frames(const ssar_frames_args& a, cudaStream_t st) {
-    using L = WarpFft<M>;
     const long long total = (long long)a.n_clips * a.n_frames;
     if (total == 0) return SSAR_OK;
     const bool banks = a.fb[0].n_bands > 0 || a.fb[1].n_bands > 0 || a.pip.count;
@@ -324,18 +347,12 @@ int launch_frames(const ssar_frames_args& a, cudaStream_t st) {
             return SSAR_ERR_CUDA;
         }
     }
-    const size_t smem = frames_smem_bytes<M>(a.window != nullptr, separate_power != 0);
-    cudaError_t e = cudaFuncSetAttribute(frames_fft_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) {
-        ssar_set_error("frames_fft: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-        return SSAR_ERR_CUDA;
+    if (g_frames_wide < 0) {
+        const char* env = getenv("SSAR_FRAMES_WIDE");
+        g_frames_wide = (env && env[0] == '0') ? 0 : 1;
     }
-    const long long groups = (total + L::WPB * L::FPW - 1) / (L::WPB * L::FPW);
-    // persistent grid: a multiple of the SM count, 2 CTAs of 8 warps per SM (registers: 128 per thread)
-    long long grid = (long long)SSAR_NUM_SMS * 2;
-    if (groups < grid) grid = groups;
-    frames_fft_kernel<M><<<(unsigned)grid, 256, smem, st>>>(a, total, separate_power);
-    return ssar_launch_status("frames_fft");
+    if (g_frames_wide && !separate_power) return launch_frames_cfg<M, 24, 1>(a, st, total, separate_power);
+    return launch_frames_cfg<M, 8, 2>(a, st, total, separate_power);
 }
 
 __global__ void fill_u32_kernel(uint32_t* dst, long long n, uint32_t v) {
