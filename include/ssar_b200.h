@@ -519,6 +519,14 @@ int ssar_biquad_ss(const float* x, long long n_samples, long long stride_x, int 
                    void* stream);
 int ssar_rms_from_block_ss(const float* block_ss, long long n_blocks, int n_clips, int n_frames, float* out, void* stream);
 
+/* TWO biquads over the SAME input in one set of passes (features/processing.py:141-150: low_pass(x) and high_pass(x), which
+ * also feeds mid_pass): the input is read once per phase instead of once per filter and phase.  coeffs: HOST array of 10
+ * floats (b0, b1, b2, a1, a2 of filter 0, then of filter 1).  y0 / y1: output signals or NULL; block_ss0 / block_ss1: as in
+ * ssar_biquad_ss or NULL; every filter needs at least one of the two.  Same arithmetic per filter as ssar_biquad. */
+int ssar_biquad_pair(const float* x, long long n_samples, long long stride_x, int n_clips, const float* coeffs, int clamp,
+                     float* y0, float* y1, long long stride_y, float* block_ss0, float* block_ss1, void* scratch,
+                     void* stream);
+
 /* rosa/constantq.py:77-100, :189-191 (__cqt_response for every octave) as ONE tensor-core launch: the response of octave
  * o is the K = 1024 contraction of the rectangular 1024-sample frames of signals[o] (hop >> o, centre reflect padding)
  * with the time-domain form of the tuned basis, b[r, n] = sum_k fft_basis[r, k] exp(-2 pi i k n / 1024):

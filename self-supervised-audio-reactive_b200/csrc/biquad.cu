@@ -25,8 +25,10 @@ struct Coef {
 };
 
 __device__ __forceinline__ float step(const Coef& c, float x0, float x1, float x2, float y1, float y2) {
-    const float v = c.b2 * x2 + c.b1 * x1 + c.b0 * x0;
-    return v - (c.a2 * y2 + c.a1 * y1);
+    // explicit roundings: the contraction of these sums must not depend on what else the compiler sees in the loop (the
+    // single- and the dual-filter instantiation have to give the same bits)
+    const float v = __fmaf_rn(c.b0, x0, __fmaf_rn(c.b1, x1, __fmul_rn(c.b2, x2)));
+    return __fsub_rn(v, __fmaf_rn(c.a1, y1, __fmul_rn(c.a2, y2)));
 }
 
 struct M2 {
@@ -74,20 +76,33 @@ __device__ __forceinline__ V2 block_scan_states(V2 q, const ALPowers& pw, V2* sq
     return q;
 }
 
-template <bool WRITE>
+// Per-filter arguments of the chunk kernel: NF = 1, or 2 filters applied to the SAME input in one pass (the low-pass and the
+// high-pass of features/processing.py:141-150 read their common input once; two independent recurrences per thread also
+// double the instruction-level parallelism of the 64-step chain).
+struct FilterArgs {
+    Coef c;
+    const float2* state_in;   // [clip, chunk] zero-state end states (phase C)
+    float2* state_out;        // [clip, chunk] (phase A)
+    float* y;                 // output signal or NULL
+    V2* cta_z;                // per-CTA aggregates (phase A)
+    const V2* cta_s;          // true state at the end of every CTA span (phase C)
+    double a1d, a2d;
+    float* block_ss;          // per-1024-sample sums of squares of the output, or NULL
+};
+
+template <bool WRITE, int NF>
 __global__ void __launch_bounds__(CPB) biquad_chunks_kernel(const float* __restrict__ x, long long n, long long stride_x,
-                                                            Coef c, const float2* __restrict__ state_in,
-                                                            float2* __restrict__ state_out, float* __restrict__ y,
-                                                            long long stride_y, long long n_chunks, int clamp,
-                                                            V2* __restrict__ cta_z, const V2* __restrict__ cta_s,
-                                                            double a1d, double a2d, float* __restrict__ block_ss,
-                                                            long long n_ss_blocks) {
+                                                            const FilterArgs fa0, const FilterArgs fa1, long long stride_y,
+                                                            long long n_chunks, int clamp, long long n_ss_blocks) {
+    const FilterArgs* fas[2] = {&fa0, &fa1};
     __shared__ float tile[CPB * LDT];
+    extern __shared__ float otile[];  // (WRITE && NF > 1): the second filter's output tile, CPB * LDT floats
     __shared__ V2 sq[CPB];
-    // powers of the chunk transition matrix: computed once per CTA (while the other threads load the tile) instead of by
+    // powers of the chunk transition matrices: computed once per CTA (while the other threads load the tile) instead of by
     // every thread — 64 registers of fp64 state and ~100 fp64 instructions per thread less, same values
-    __shared__ ALPowers pw;
-    if (threadIdx.x == 0) pw = al_powers(a1d, a2d);
+    __shared__ ALPowers pw[NF];
+    if (threadIdx.x == 0) pw[0] = al_powers(fa0.a1d, fa0.a2d);
+    if (NF > 1 && threadIdx.x == 32) pw[NF - 1] = al_powers(fa1.a1d, fa1.a2d);
     const int clip = blockIdx.y;
     const float* xc = x + (long long)clip * stride_x;
     const long long tile0 = (long long)blockIdx.x * CPB * L;
@@ -112,84 +127,112 @@ __global__ void __launch_bounds__(CPB) biquad_chunks_kernel(const float* __restr
     }
     __syncthreads();
     const long long chunk = (long long)blockIdx.x * CPB + threadIdx.x;
-    float y1 = 0.f, y2 = 0.f, ssq = 0.f;
+    float y1[NF], y2[NF], ssq[NF];
+#pragma unroll
+    for (int f = 0; f < NF; ++f) y1[f] = y2[f] = ssq[f] = 0.f;
     if (WRITE) {
         // true state entering every chunk of this CTA: S_j = AL^(j+1) S_in + sum_{i<=j} AL^(j-i) z_i (fp64), chunk j starts
         // from S_{j-1}; S_in = the state entering the CTA from the carry kernel
-        V2 z = {0.0, 0.0};
-        if (chunk < n_chunks) {
-            const float2 zz = state_in[(long long)clip * n_chunks + chunk];
-            z = {(double)zz.x, (double)zz.y};
-        }
-        V2 S = block_scan_states(z, pw, sq);
-        V2 sin = {0.0, 0.0};
-        if (blockIdx.x > 0) sin = cta_s[(long long)clip * gridDim.x + blockIdx.x - 1];
-        V2 prop = sin;
-        const int e = threadIdx.x + 1;
 #pragma unroll
-        for (int b = 0; b < 8; ++b)
-            if (e & (1 << b)) prop = mv(pw.p[b], prop);
-        S.x += prop.x;
-        S.y += prop.y;
-        __syncthreads();
-        sq[threadIdx.x] = S;
-        __syncthreads();
-        const V2 init = threadIdx.x > 0 ? sq[threadIdx.x - 1] : sin;
-        y1 = (float)init.x;
-        y2 = (float)init.y;
+        for (int f = 0; f < NF; ++f) {
+            V2 z = {0.0, 0.0};
+            if (chunk < n_chunks) {
+                const float2 zz = fas[f]->state_in[(long long)clip * n_chunks + chunk];
+                z = {(double)zz.x, (double)zz.y};
+            }
+            V2 S = block_scan_states(z, pw[f], sq);
+            V2 sin = {0.0, 0.0};
+            if (blockIdx.x > 0) sin = fas[f]->cta_s[(long long)clip * gridDim.x + blockIdx.x - 1];
+            V2 prop = sin;
+            const int e = threadIdx.x + 1;
+#pragma unroll
+            for (int b = 0; b < 8; ++b)
+                if (e & (1 << b)) prop = mv(pw[f].p[b], prop);
+            S.x += prop.x;
+            S.y += prop.y;
+            __syncthreads();
+            sq[threadIdx.x] = S;
+            __syncthreads();
+            const V2 init = threadIdx.x > 0 ? sq[threadIdx.x - 1] : sin;
+            y1[f] = (float)init.x;
+            y2[f] = (float)init.y;
+            __syncthreads();  // sq is reused by the next filter's scan
+        }
     }
     if (chunk < n_chunks) {
         const long long n0 = chunk * L;
         float x1 = n0 >= 1 ? __ldg(xc + n0 - 1) : 0.f;
         float x2 = n0 >= 2 ? __ldg(xc + n0 - 2) : 0.f;
         float* row = tile + threadIdx.x * LDT;
+        float* orow = otile + ((WRITE && NF > 1) ? threadIdx.x * LDT : 0);
 #pragma unroll 8
         for (int i = 0; i < L; ++i) {
             const float x0 = row[i];
-            const float yy = step(c, x0, x1, x2, y1, y2);
-            if (WRITE) {
-                const float yo = clamp ? fminf(fmaxf(yy, -1.f), 1.f) : yy;
-                row[i] = yo;
-                if (n0 + i < n) ssq = fmaf(yo, yo, ssq);
-                if (i == 0 && block_ss && (n0 == 0 || n0 == 1024))  // y[0], y[1024]: the reflected edge of rms frame 0
-                    block_ss[(long long)clip * (n_ss_blocks + 2) + n_ss_blocks + (n0 == 0 ? 0 : 1)] = yo;
+#pragma unroll
+            for (int f = 0; f < NF; ++f) {
+                const float yy = step(fas[f]->c, x0, x1, x2, y1[f], y2[f]);
+                if (WRITE) {
+                    const float yo = clamp ? fminf(fmaxf(yy, -1.f), 1.f) : yy;
+                    if (f == 0) row[i] = yo;
+                    else orow[i] = yo;
+                    if (n0 + i < n) ssq[f] = fmaf(yo, yo, ssq[f]);
+                    if (i == 0 && fas[f]->block_ss && (n0 == 0 || n0 == 1024))  // y[0], y[1024]: reflected edge of rms frame 0
+                        fas[f]->block_ss[(long long)clip * (n_ss_blocks + 2) + n_ss_blocks + (n0 == 0 ? 0 : 1)] = yo;
+                }
+                y2[f] = y1[f];
+                y1[f] = yy;
             }
             x2 = x1;
             x1 = x0;
-            y2 = y1;
-            y1 = yy;
         }
-        if (!WRITE) state_out[(long long)clip * n_chunks + chunk] = make_float2(y1, y2);
+        if (!WRITE) {
+#pragma unroll
+            for (int f = 0; f < NF; ++f) fas[f]->state_out[(long long)clip * n_chunks + chunk] = make_float2(y1[f], y2[f]);
+        }
     }
     if (!WRITE) {
         // CTA aggregate: zero-state end state of the CTA's whole span (chunks past the end contribute zero)
-        V2 z = {0.0, 0.0};
-        if (chunk < n_chunks) z = {(double)y1, (double)y2};
-        const V2 q = block_scan_states(z, pw, sq);
-        if (threadIdx.x == CPB - 1) cta_z[(long long)clip * gridDim.x + blockIdx.x] = q;
+#pragma unroll
+        for (int f = 0; f < NF; ++f) {
+            V2 z = {0.0, 0.0};
+            if (chunk < n_chunks) z = {(double)y1[f], (double)y2[f]};
+            const V2 q = block_scan_states(z, pw[f], sq);
+            if (threadIdx.x == CPB - 1) fas[f]->cta_z[(long long)clip * gridDim.x + blockIdx.x] = q;
+            __syncthreads();
+        }
     }
-    if (WRITE && block_ss) {
+    if (WRITE) {
         // sum of squares of the (clamped) output per 1024-sample block = 16 consecutive chunks = 16 lanes
         static_assert(L * 16 == 1024, "block_ss assumes 16 chunks per 1024 samples");
 #pragma unroll
-        for (int o = 8; o > 0; o >>= 1) ssq += __shfl_xor_sync(0xffffffffu, ssq, o);
-        const long long blk = (long long)blockIdx.x * (CPB / 16) + (threadIdx.x >> 4);
-        if ((threadIdx.x & 15) == 0 && blk < n_ss_blocks) block_ss[(long long)clip * (n_ss_blocks + 2) + blk] = ssq;
+        for (int f = 0; f < NF; ++f) {
+            if (!fas[f]->block_ss) continue;
+            float v = ssq[f];
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            const long long blk = (long long)blockIdx.x * (CPB / 16) + (threadIdx.x >> 4);
+            if ((threadIdx.x & 15) == 0 && blk < n_ss_blocks) fas[f]->block_ss[(long long)clip * (n_ss_blocks + 2) + blk] = v;
+        }
     }
-    if (WRITE && y) {
+    if (WRITE) {
         __syncthreads();
-        float* yc = y + (long long)clip * stride_y;
-        if (tile0 + (long long)CPB * L <= n && ((reinterpret_cast<uintptr_t>(yc + tile0) & 15) == 0)) {
-            float4* __restrict__ y4 = reinterpret_cast<float4*>(yc + tile0);
+#pragma unroll
+        for (int f = 0; f < NF; ++f) {
+            if (!fas[f]->y) continue;
+            const float* src = f == 0 ? tile : otile;
+            float* yc = fas[f]->y + (long long)clip * stride_y;
+            if (tile0 + (long long)CPB * L <= n && ((reinterpret_cast<uintptr_t>(yc + tile0) & 15) == 0)) {
+                float4* __restrict__ y4 = reinterpret_cast<float4*>(yc + tile0);
 #pragma unroll 4
-            for (int q = threadIdx.x; q < CPB * L / 4; q += CPB) {
-                const float* d = tile + ((4 * q) / L) * LDT + ((4 * q) % L);
-                y4[q] = make_float4(d[0], d[1], d[2], d[3]);
-            }
-        } else {
-            for (int i = threadIdx.x; i < CPB * L; i += CPB) {
-                const long long g = tile0 + i;
-                if (g < n) yc[g] = tile[(i / L) * LDT + (i % L)];
+                for (int q = threadIdx.x; q < CPB * L / 4; q += CPB) {
+                    const float* d = src + ((4 * q) / L) * LDT + ((4 * q) % L);
+                    y4[q] = make_float4(d[0], d[1], d[2], d[3]);
+                }
+            } else {
+                for (int i = threadIdx.x; i < CPB * L; i += CPB) {
+                    const long long g = tile0 + i;
+                    if (g < n) yc[g] = src[(i / L) * LDT + (i % L)];
+                }
             }
         }
     }
@@ -275,34 +318,66 @@ __global__ void rms_from_block_ss_kernel(const float* __restrict__ ss, long long
 
 }  // namespace
 
-extern "C" long long ssar_biquad_scratch_bytes(int n_clips, long long n_samples) {
+static long long biquad_scratch_one(int n_clips, long long n_samples) {
     const long long n_chunks = (n_samples + L - 1) / L;
     const long long n_ctas = (n_chunks + CPB - 1) / CPB;
-    return (long long)n_clips * n_chunks * (long long)sizeof(float2) + 16 + 2LL * n_clips * n_ctas * 16;
+    return (((long long)n_clips * n_chunks * (long long)sizeof(float2) + 15) / 16) * 16 + 2LL * n_clips * n_ctas * 16;
 }
 
-static int biquad_impl(const float* x, long long n_samples, long long stride_x, int n_clips, float b0, float b1, float b2,
-                       float a1, float a2, int clamp, float* y, long long stride_y, float* block_ss, void* scratch,
-                       void* stream) {
+extern "C" long long ssar_biquad_scratch_bytes(int n_clips, long long n_samples) {
+    return 2 * biquad_scratch_one(n_clips, n_samples) + 16;  // room for a filter pair
+}
+
+struct FilterSpec {
+    float b0, b1, b2, a1, a2;
+    float* y;
+    float* block_ss;
+};
+
+// n_filters = 1 or 2 filters over the same input: phase A (zero-state chunks), the per-clip carry scan(s), phase C
+static int biquad_impl(const float* x, long long n_samples, long long stride_x, int n_clips, const FilterSpec* specs,
+                       int n_filters, int clamp, long long stride_y, void* scratch, void* stream) {
     if (n_clips == 0 || n_samples == 0) return SSAR_OK;
-    SSAR_REQUIRE(x && (y || block_ss) && scratch, "biquad: null pointer");
+    SSAR_REQUIRE(x && scratch, "biquad: null pointer");
     SSAR_REQUIRE(n_clips <= 65535, "biquad: too many clips per launch");
     cudaStream_t st = (cudaStream_t)stream;
     const long long n_chunks = (n_samples + L - 1) / L;
-    // scratch: z [n_clips, n_chunks] float2 | per-CTA aggregates [n_clips, n_ctas] double2 | per-CTA states, same shape
-    float2* z = reinterpret_cast<float2*>(scratch);
     const long long n_ctas = (n_chunks + CPB - 1) / CPB;
-    V2* cz = reinterpret_cast<V2*>(reinterpret_cast<char*>(scratch) +
-                                   (((long long)n_clips * n_chunks * (long long)sizeof(float2) + 15) / 16) * 16);
-    V2* cs = cz + (long long)n_clips * n_ctas;
-    const Coef c = {b0, b1, b2, a1, a2};
-    dim3 grid((unsigned)n_ctas, n_clips);
     const long long n_ss = (n_samples + 1023) / 1024;
-    biquad_chunks_kernel<false><<<grid, CPB, 0, st>>>(x, n_samples, stride_x, c, nullptr, z, nullptr, 0, n_chunks, 0, cz,
-                                                     nullptr, (double)a1, (double)a2, nullptr, 0);
-    biquad_carry_kernel<<<n_clips, 1024, 0, st>>>(cz, cs, n_ctas, (double)a1, (double)a2);
-    biquad_chunks_kernel<true><<<grid, CPB, 0, st>>>(x, n_samples, stride_x, c, z, nullptr, y, stride_y, n_chunks, clamp,
-                                                    nullptr, cs, (double)a1, (double)a2, block_ss, n_ss);
+    // scratch per filter: z [n_clips, n_chunks] float2 | per-CTA aggregates [n_clips, n_ctas] double2 | per-CTA states
+    FilterArgs fa[2];
+    for (int f = 0; f < 2; ++f) {
+        const FilterSpec& sp = specs[f < n_filters ? f : 0];
+        SSAR_REQUIRE(f >= n_filters || sp.y || sp.block_ss, "biquad: a filter needs an output (signal or block sums)");
+        char* base = reinterpret_cast<char*>(scratch) + (long long)f * biquad_scratch_one(n_clips, n_samples);
+        float2* z = reinterpret_cast<float2*>(base);
+        V2* cz = reinterpret_cast<V2*>(base + (((long long)n_clips * n_chunks * (long long)sizeof(float2) + 15) / 16) * 16);
+        V2* cs = cz + (long long)n_clips * n_ctas;
+        fa[f].c = {sp.b0, sp.b1, sp.b2, sp.a1, sp.a2};
+        fa[f].state_in = z;
+        fa[f].state_out = z;
+        fa[f].y = sp.y;
+        fa[f].cta_z = cz;
+        fa[f].cta_s = cs;
+        fa[f].a1d = (double)sp.a1;
+        fa[f].a2d = (double)sp.a2;
+        fa[f].block_ss = sp.block_ss;
+    }
+    dim3 grid((unsigned)n_ctas, n_clips);
+    if (n_filters == 2) biquad_chunks_kernel<false, 2><<<grid, CPB, 0, st>>>(x, n_samples, stride_x, fa[0], fa[1], stride_y, n_chunks, 0, n_ss);
+    else biquad_chunks_kernel<false, 1><<<grid, CPB, 0, st>>>(x, n_samples, stride_x, fa[0], fa[0], stride_y, n_chunks, 0, n_ss);
+    for (int f = 0; f < n_filters; ++f)
+        biquad_carry_kernel<<<n_clips, 1024, 0, st>>>(fa[f].cta_z, const_cast<V2*>(fa[f].cta_s), n_ctas, fa[f].a1d, fa[f].a2d);
+    if (n_filters == 2) {
+        const size_t osm = (size_t)CPB * LDT * sizeof(float);  // + 35.6 KB static: above the 48 KB default
+        cudaError_t e = cudaFuncSetAttribute(biquad_chunks_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)osm);
+        if (e != cudaSuccess) {
+            ssar_set_error("biquad: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+            return SSAR_ERR_CUDA;
+        }
+        biquad_chunks_kernel<true, 2><<<grid, CPB, osm, st>>>(x, n_samples, stride_x, fa[0], fa[1], stride_y, n_chunks, clamp, n_ss);
+    }
+    else biquad_chunks_kernel<true, 1><<<grid, CPB, 0, st>>>(x, n_samples, stride_x, fa[0], fa[0], stride_y, n_chunks, clamp, n_ss);
     return ssar_launch_status("biquad");
 }
 
@@ -310,14 +385,25 @@ extern "C" int ssar_biquad(const float* x, long long n_samples, long long stride
                            float b2, float a1, float a2, int clamp, float* y, long long stride_y, void* scratch,
                            void* stream) {
     SSAR_REQUIRE(y != nullptr, "biquad: null pointer");
-    return biquad_impl(x, n_samples, stride_x, n_clips, b0, b1, b2, a1, a2, clamp, y, stride_y, nullptr, scratch, stream);
+    const FilterSpec sp = {b0, b1, b2, a1, a2, y, nullptr};
+    return biquad_impl(x, n_samples, stride_x, n_clips, &sp, 1, clamp, stride_y, scratch, stream);
 }
 
 extern "C" int ssar_biquad_ss(const float* x, long long n_samples, long long stride_x, int n_clips, float b0, float b1,
                               float b2, float a1, float a2, int clamp, float* y, long long stride_y, float* block_ss,
                               void* scratch, void* stream) {
     SSAR_REQUIRE(block_ss != nullptr, "biquad_ss: null block_ss");
-    return biquad_impl(x, n_samples, stride_x, n_clips, b0, b1, b2, a1, a2, clamp, y, stride_y, block_ss, scratch, stream);
+    const FilterSpec sp = {b0, b1, b2, a1, a2, y, block_ss};
+    return biquad_impl(x, n_samples, stride_x, n_clips, &sp, 1, clamp, stride_y, scratch, stream);
+}
+
+extern "C" int ssar_biquad_pair(const float* x, long long n_samples, long long stride_x, int n_clips, const float* coeffs,
+                                int clamp, float* y0, float* y1, long long stride_y, float* block_ss0, float* block_ss1,
+                                void* scratch, void* stream) {
+    SSAR_REQUIRE(coeffs != nullptr, "biquad_pair: null coefficients");
+    const FilterSpec sp[2] = {{coeffs[0], coeffs[1], coeffs[2], coeffs[3], coeffs[4], y0, block_ss0},
+                              {coeffs[5], coeffs[6], coeffs[7], coeffs[8], coeffs[9], y1, block_ss1}};
+    return biquad_impl(x, n_samples, stride_x, n_clips, sp, 2, clamp, stride_y, scratch, stream);
 }
 
 extern "C" int ssar_rms_from_block_ss(const float* block_ss, long long n_blocks, int n_clips, int n_frames, float* out,

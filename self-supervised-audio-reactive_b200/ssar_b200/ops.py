@@ -280,6 +280,34 @@ def biquad_rms(x: torch.Tensor, coeffs, clamp: bool = True, want_signal: bool = 
     return (out, y) if want_signal else out
 
 
+def biquad_pair(x: torch.Tensor, coeffs0, coeffs1, clamp: bool = True, want_signal=(True, True), want_rms=(False, False),
+                n_frames: int | None = None):
+    """Two biquads over the SAME input in one set of passes (`ssar_biquad_pair`: the input is read once per phase, not
+    once per filter).  -> [(y or None, rms [B, n_frames] or None) for the two filters]; same arithmetic per filter as
+    `biquad` / `biquad_rms`."""
+    x, _ = _as_batch(x)
+    B, N = x.shape
+    n_blocks = (N + 1023) // 1024
+    T = N // 1024 if n_frames is None else int(n_frames)
+    if any(want_rms) and (n_blocks < 2 or T > n_blocks):
+        raise SsarError("biquad_pair: clip too short for 2048-sample frames")
+    ys = [torch.empty(B, N, dtype=torch.float32, device=x.device) if w else None for w in want_signal]
+    sss = [torch.empty(B, n_blocks + 2, dtype=torch.float32, device=x.device) if w else None for w in want_rms]
+    nbytes = cabi.lib().ssar_biquad_scratch_bytes(C.c_int(B), C.c_longlong(N))
+    scratch = torch.empty(max(int(nbytes), 8), dtype=torch.uint8, device=x.device)
+    cf = (C.c_float * 10)(*[float(v) for v in (*coeffs0, *coeffs1)])
+    cabi.call("ssar_biquad_pair", ptr(x), i64(N), i64(x.stride(0)), i32(B), cf, i32(1 if clamp else 0), ptr(ys[0]), ptr(ys[1]),
+              i64(N), ptr(sss[0]), ptr(sss[1]), ptr(scratch), nbytes=cabi.nbytes_of(x, *ys))
+    out = []
+    for y, ss in zip(ys, sss):
+        r = None
+        if ss is not None:
+            r = torch.empty(B, T, dtype=torch.float32, device=x.device)
+            cabi.call("ssar_rms_from_block_ss", ptr(ss), i64(n_blocks), i32(B), i32(T), ptr(r), nbytes=cabi.nbytes_of(ss, r))
+        out.append((y, r))
+    return out
+
+
 def resample(x: torch.Tensor, rp, post_scale: float = 1.0, clip_n_in=None):
     """x [B, N] -> [B, ceil(new*N/orig)] with a `plan.ResamplePlan`.  clip_n_in (int64 [B]): ragged batch — clip b holds
     clip_n_in[b] samples followed by zeros; its outputs past ceil(new * clip_n_in[b] / orig) are zeros."""

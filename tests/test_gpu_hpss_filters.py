@@ -119,3 +119,19 @@ def test_biquad_rms_equals_rms_of_biquad():
         assert got.shape == ref.shape and rel_l2(got, ref) < 1e-6
         assert float((got[:, 0] - ref[:, 0]).abs().max()) < 1e-6 * float(ref.abs().max())
         assert rel_l2(ops.biquad_rms(x, c, n_frames=T), ref) < 1e-6
+
+
+def test_biquad_pair_equals_two_single_filters():
+    """ssar_biquad_pair (two filters over one input per pass) == ssar_biquad / ssar_biquad_ss per filter, bit for bit:
+    signals, framed RMS, ragged length (tile tail), batch of clips."""
+    from ssar_b200 import ops, plan
+
+    sr = 24576
+    xs = torch.stack([synth_clip(sr * 7 + 333, sr, i) for i in (2, 6, 9)]).cuda()
+    lo_c, hi_c = plan.biquad_coeffs("low", sr, 200), plan.biquad_coeffs("high", sr, 4000)
+    T = xs.shape[1] // 1024
+    (y_lo, r_lo), (y_hi, r_hi) = ops.biquad_pair(xs, lo_c, hi_c, want_signal=(True, True), want_rms=(True, True), n_frames=T)
+    assert torch.equal(y_lo, ops.biquad(xs, lo_c)) and torch.equal(y_hi, ops.biquad(xs, hi_c))
+    assert torch.equal(r_lo, ops.biquad_rms(xs, lo_c, n_frames=T)) and torch.equal(r_hi, ops.biquad_rms(xs, hi_c, n_frames=T))
+    (n0, r0), (y1, n1) = ops.biquad_pair(xs, lo_c, hi_c, want_signal=(False, True), want_rms=(True, False), n_frames=T)
+    assert n0 is None and n1 is None and torch.equal(r0, r_lo) and torch.equal(y1, y_hi)
