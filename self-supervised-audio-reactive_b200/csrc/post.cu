@@ -97,6 +97,70 @@ __global__ void gauss1d_kernel(const float* __restrict__ x, int cap_T, long long
         if (t0 + o < cap_T) oc[(long long)(t0 + o) * inner + j] = t0 + o < T ? acc[o] : 0.f;
 }
 
+// Long kernels (sigma 80 of random/mir.py:14-22: 641 taps): a CTA stages the (tile_rows + 2 radius) x inner input rows of
+// its output tile in shared memory ONCE (padding resolved per row while loading), then every thread makes 16 consecutive
+// outputs of one column from the tile with the same register tap window and the same ascending-tap fmaf chain as
+// gauss1d_kernel — identical results; two conflict-free shared-memory reads per 16 FMAs instead of a global load and the
+// padding arithmetic per tap.
+constexpr int GT_TPT = 16;
+__host__ __device__ inline int gt_round16(int v) { return (v + GT_TPT - 1) / GT_TPT * GT_TPT; }
+// shared memory: taps zero-padded to a multiple of 16 entries | tile of (16 * groups + padded taps) rows, zero rows past
+// the staged ones: the inner loop then runs in whole blocks of 16 input rows with no bound checks at all
+__global__ void __launch_bounds__(512) gauss1d_tiled_kernel(const float* __restrict__ x, int cap_T, int inner,
+                                                            const float* __restrict__ w, int radius, int mode,
+                                                            float* __restrict__ out, const int* __restrict__ clip_frames,
+                                                            int tile_rows) {
+    extern __shared__ float gsm[];
+    const int taps = 2 * radius + 1;
+    const int n_pad = gt_round16(taps + GT_TPT - 1);  // input rows walked per group of 16 outputs
+    float* ws = gsm;
+    float* tile = gsm + n_pad;
+    const int clip = blockIdx.y;
+    const float* xc = x + (long long)clip * cap_T * inner;
+    float* oc = out + (long long)clip * cap_T * inner;
+    const int T = clip_frames ? __ldg(clip_frames + clip) : cap_T;
+    const int t0 = blockIdx.x * tile_rows;
+    const int rows_out = min(tile_rows, cap_T - t0);
+    if (t0 >= T) {  // (ragged) a tile past the clip's end
+        for (int i = threadIdx.x; i < rows_out * inner; i += blockDim.x) oc[(long long)t0 * inner + i] = 0.f;
+        return;
+    }
+    for (int i = threadIdx.x; i < n_pad; i += blockDim.x) ws[i] = i < taps ? w[i] : 0.f;
+    const int groups = (rows_out + GT_TPT - 1) / GT_TPT;
+    const int rows_in = rows_out + 2 * radius;
+    const int rows_all = (groups - 1) * GT_TPT + n_pad;  // >= rows_in
+    for (int i = threadIdx.x; i < rows_all * inner; i += blockDim.x) {
+        const int r = i / inner, j = i - r * inner;
+        tile[i] = r < rows_in ? __ldg(xc + (long long)pad_index(t0 - radius + r, T, radius, mode) * inner + j) : 0.f;
+    }
+    __syncthreads();
+    for (int item = threadIdx.x; item < groups * inner; item += blockDim.x) {
+        const int g = item / inner, j = item - g * inner;
+        const int r0 = g * GT_TPT;
+        float acc[GT_TPT], wr[GT_TPT];
+#pragma unroll
+        for (int o = 0; o < GT_TPT; ++o) acc[o] = 0.f, wr[o] = 0.f;
+        const float* col = tile + r0 * inner + j;
+        const float* wp = ws;
+        for (int i0 = 0; i0 < n_pad; i0 += GT_TPT) {
+#pragma unroll
+            for (int u = 0; u < GT_TPT; ++u) {
+                const float v = *col;
+                col += inner;
+                wr[u] = wp[u];  // tap i0 + u enters the window (zeros beyond the kernel)
+#pragma unroll
+                for (int o = 0; o < GT_TPT; ++o) acc[o] = fmaf(wr[(u - o + GT_TPT) % GT_TPT], v, acc[o]);
+            }
+            wp += GT_TPT;
+        }
+#pragma unroll
+        for (int o = 0; o < GT_TPT; ++o) {
+            const int t = t0 + r0 + o;
+            if (r0 + o < rows_out) oc[(long long)t * inner + j] = t < T ? acc[o] : 0.f;
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // per-(clip, column) min / max of [clip, T, C]
 // ---------------------------------------------------------------------------------------------------------------
@@ -336,6 +400,34 @@ extern "C" int ssar_gauss1d(const float* x, int n_clips, int n_frames, long long
     SSAR_REQUIRE(mode != 1 || radius < n_frames, "gauss1d: reflect padding needs radius < n_frames");
     SSAR_REQUIRE((2 * radius + 1) * sizeof(float) <= 200 * 1024, "gauss1d: kernel too long");
     SSAR_REQUIRE(n_clips <= 65535, "gauss1d: too many clips per launch");
+    if (radius >= 32 && inner <= 4096) {  // (shorter kernels: the tile staging costs more than it saves, measured)
+        // tiled variant: tile rows chosen so that the launch is a whole number of waves of one CTA per SM (when it fits)
+        const int n_pad = gt_round16(2 * radius + 1 + GT_TPT - 1);
+        const long long smem_cap = 200 * 1024 - (long long)n_pad * 4;
+        const long long max_rows = smem_cap / (4 * inner) - n_pad;  // rows_all = 16 (groups - 1) + n_pad <= tile_rows + n_pad
+        if (max_rows >= 4 * GT_TPT) {
+            int tile_rows = (int)(max_rows / GT_TPT * GT_TPT);
+            // fewest tiles per clip that fit, then the smallest tile height giving that many tiles
+            const int tiles = (n_frames + tile_rows - 1) / tile_rows;
+            int waves_tiles = tiles;
+            // n_clips * tiles CTAs: round the tile count up until the grid fills its last wave to >= 85 %
+            for (int tt = tiles; tt <= tiles + 8; ++tt) {
+                const long long ctas = (long long)n_clips * tt;
+                const long long waves = (ctas + SSAR_NUM_SMS - 1) / SSAR_NUM_SMS;
+                if ((double)ctas / (double)(waves * SSAR_NUM_SMS) >= 0.85) {
+                    waves_tiles = tt;
+                    break;
+                }
+            }
+            tile_rows = ((n_frames + waves_tiles - 1) / waves_tiles + GT_TPT - 1) / GT_TPT * GT_TPT;
+            const int n_tiles = (n_frames + tile_rows - 1) / tile_rows;
+            const size_t smem = ((size_t)n_pad + (size_t)(tile_rows + n_pad) * inner) * sizeof(float);
+            cudaFuncSetAttribute(gauss1d_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            gauss1d_tiled_kernel<<<dim3(n_tiles, n_clips), 512, smem, ST(stream)>>>(x, n_frames, (int)inner, weights, radius, mode, out,
+                                                                                  clip_frames, tile_rows);
+            return ssar_launch_status("gauss1d");
+        }
+    }
     const int threads = 128;
     // long kernels on enough rows: 16 outputs per thread (16 FMAs per loaded row instead of 4)
     const int tpt = (radius >= 32 && (long long)n_clips * inner * ((n_frames + 15) / 16) >= (long long)SSAR_NUM_SMS * threads) ? 16 : 4;
