@@ -130,6 +130,14 @@ typedef struct {
        spectra and every later kernel that honours the same lengths see exactly what a per-clip call would.  Device arrays. */
     const long long* clip_samples;
     const int* clip_frames;
+    /* TIME SEGMENTS of long tracks (clip_total = 0: unused).  x[clip] then holds the samples [sample_offset, sample_offset +
+       n_samples) of a clip that is clip_total samples long, and local frame t is the clip's frame frame_offset + t: the
+       frame is cut at (frame_offset + t) * hop - n_fft / 2 in CLIP coordinates, reflected at the clip's true ends only,
+       and read from the segment — the caller ships each segment with an n_fft / 2 halo on both sides (clamped to the
+       clip).  Segments of one track then reproduce the whole-track transform frame for frame.  Not with clip_samples. */
+    long long sample_offset;
+    long long clip_total;
+    int frame_offset;
 } ssar_frames_args;
 
 int ssar_frames_fft(const ssar_frames_args* args, void* stream);

@@ -66,8 +66,13 @@ __global__ void __launch_bounds__(32 * WPB, CPS) frames_fft_kernel(const ssar_fr
         float ss = 0.f;
         if (active) {
             const float* __restrict__ xc = a.x + (long long)clip * a.clip_stride;
-            const long long start = (long long)t * a.hop - M;
-            const bool interior = start >= 0 && start + N <= n_samples;
+            long long start = (long long)t * a.hop - M;
+            bool interior = start >= 0 && start + N <= n_samples;
+            if (a.clip_total > 0) {  // time segment of a longer clip: frame position and reflection in clip coordinates
+                const long long gstart = (long long)(a.frame_offset + t) * a.hop - M;
+                interior = gstart >= 0 && gstart + N <= a.clip_total;
+                start = gstart - a.sample_offset;  // interior frames: plain segment-relative reads (the halo covers them)
+            }
             const bool vec = interior && ((((long long)clip * a.clip_stride + start) & 1LL) == 0) &&
                              ((reinterpret_cast<uintptr_t>(a.x) & 7) == 0);
             if (vec) {
@@ -84,8 +89,14 @@ __global__ void __launch_bounds__(32 * WPB, CPS) frames_fft_kernel(const ssar_fr
 #pragma unroll
                 for (int r = 0; r < 32; ++r) {
                     const int n = n1 + N1 * r;
-                    v[r] = make_float2(__ldg(xc + ssar_reflect(start + 2 * n, n_samples)),
-                                       __ldg(xc + ssar_reflect(start + 2 * n + 1, n_samples)));
+                    if (a.clip_total > 0) {
+                        const long long g = start + a.sample_offset + 2 * n;
+                        v[r] = make_float2(__ldg(xc + (ssar_reflect(g, a.clip_total) - a.sample_offset)),
+                                           __ldg(xc + (ssar_reflect(g + 1, a.clip_total) - a.sample_offset)));
+                    } else {
+                        v[r] = make_float2(__ldg(xc + ssar_reflect(start + 2 * n, n_samples)),
+                                           __ldg(xc + ssar_reflect(start + 2 * n + 1, n_samples)));
+                    }
                 }
             }
             if (a.out_rms) {
@@ -367,13 +378,30 @@ extern "C" int ssar_frames_fft(const ssar_frames_args* args, void* stream) {
     const ssar_frames_args& a = *args;
     SSAR_REQUIRE(a.x && a.twiddle, "frames_fft: x and twiddle are required");
     SSAR_REQUIRE(a.n_clips >= 0 && a.n_frames >= 0 && a.hop > 0, "frames_fft: bad sizes");
-    SSAR_REQUIRE(a.n_samples > a.n_fft / 2, "frames_fft: clip shorter than n_fft/2+1 samples cannot be reflect-padded");
+    SSAR_REQUIRE(a.n_samples > a.n_fft / 2 || a.clip_total > 0, "frames_fft: clip shorter than n_fft/2+1 samples cannot be reflect-padded");
     SSAR_REQUIRE(a.spec_power == 1 || a.spec_power == 2 || !a.out_spec, "frames_fft: spec_power must be 1 or 2");
     SSAR_REQUIRE(a.aux_frames >= 0 && a.aux_frames <= a.n_frames, "frames_fft: aux_frames=%d outside [0, n_frames]", a.aux_frames);
     SSAR_REQUIRE(!a.pip.count || (a.pip.pitch && a.pip.mag && 0 <= a.pip.k_lo && a.pip.k_lo < a.pip.k_hi &&
                                   a.pip.k_hi <= a.n_fft / 2 + 1 &&
                                   a.pip.capacity >= ssar_piptrack_capacity(a.aux_frames > 0 ? a.aux_frames : a.n_frames, a.pip.k_lo, a.pip.k_hi)),
                  "frames_fft: bad piptrack epilogue (null lists, bin range or capacity)");
+    if (a.clip_total > 0) {
+        SSAR_REQUIRE(!a.clip_samples && a.sample_offset >= 0 && a.sample_offset + a.n_samples <= a.clip_total && a.frame_offset >= 0,
+                     "frames_fft: bad time segment (offset / length outside the clip, or combined with ragged lengths)");
+        SSAR_REQUIRE(a.clip_total > a.n_fft / 2 && a.n_frames >= 0 &&
+                         (long long)(a.frame_offset + a.n_frames - 1) * a.hop <= a.clip_total,
+                     "frames_fft: the segment's frames exceed 1 + clip_total / hop");
+        // every sample a frame of the segment touches (after reflection at the clip's ends) must be resident
+        if (a.n_frames > 0) {
+            const long long first = (long long)a.frame_offset * a.hop - a.n_fft / 2;
+            const long long last = (long long)(a.frame_offset + a.n_frames - 1) * a.hop + a.n_fft / 2 - 1;
+            long long lo = first < 0 ? 0 : first, hi = last >= a.clip_total ? a.clip_total - 1 : last;
+            if (first < 0 && -first > hi) hi = -first;                                       // mirror of the leading pad
+            if (last >= a.clip_total && 2 * (a.clip_total - 1) - last < lo) lo = 2 * (a.clip_total - 1) - last;  // trailing
+            SSAR_REQUIRE(a.sample_offset <= lo && hi < a.sample_offset + a.n_samples,
+                         "frames_fft: the segment does not hold the n_fft / 2 halo its frames need");
+        }
+    } else
     SSAR_REQUIRE(a.n_frames == 0 || (long long)(a.n_frames - 1) * a.hop <= a.n_samples,
                  "frames_fft: n_frames=%d exceeds 1 + n_samples/hop", a.n_frames);
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);

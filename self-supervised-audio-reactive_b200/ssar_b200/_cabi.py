@@ -58,6 +58,7 @@ class FramesArgs(C.Structure):
         ("out_rms", C.c_void_p), ("out_flatness", C.c_void_p),
         ("fb", Filterbank * 2), ("proj", Projection), ("aux_frames", C.c_int), ("pip", PiptrackEpilogue),
         ("clip_samples", C.c_void_p), ("clip_frames", C.c_void_p),
+        ("sample_offset", C.c_longlong), ("clip_total", C.c_longlong), ("frame_offset", C.c_int),
     ]
 
 

@@ -54,6 +54,7 @@ def frames_fft(
     piptrack: dict | None = None,
     clip_samples: torch.Tensor | None = None,
     clip_frames: torch.Tensor | None = None,
+    segment: tuple | None = None,
 ):
     """Framed real FFT + fused epilogues over a batch of clips.
 
@@ -66,6 +67,8 @@ def frames_fft(
       slots (int32 [B]: per-clip table slot), row_scale (fp32 [n_slots, row_scale_ld] view), row_scale_ld.
     aux_frames: when given (<= n_frames), every output except `complex` covers only the first aux_frames frames of each
       clip ([B, aux_frames, ...]): stft (T + 1 frames) and the last-frame-dropping features of one signal in one launch.
+    segment: (sample_offset, clip_total, frame_offset) — x holds samples [sample_offset, sample_offset + N) of clips that are
+      clip_total long, local frame t = the clips' frame frame_offset + t (time segments of long tracks with n_fft / 2 halos).
     clip_samples (int64 [B]) / clip_frames (int32 [B]): RAGGED batch — clip b holds clip_samples[b] <= N samples and
       produces clip_frames[b] <= n_frames frames; rows past a clip's count are zeros in every output.
     """
@@ -85,6 +88,8 @@ def frames_fft(
     a.window = win.data_ptr() if win is not None else None
     tw = plan.twiddle(n_fft, str(dev))
     a.twiddle = tw.data_ptr()
+    if segment is not None:  # (sample_offset, clip_total, frame_offset): x is a time segment (with halos) of longer clips
+        a.sample_offset, a.clip_total, a.frame_offset = int(segment[0]), int(segment[1]), int(segment[2])
     if clip_samples is not None or clip_frames is not None:
         if clip_samples is None or clip_frames is None or clip_samples.dtype != torch.int64 or clip_frames.dtype != torch.int32:
             raise SsarError("frames_fft: ragged batches need clip_samples (int64) and clip_frames (int32) together")

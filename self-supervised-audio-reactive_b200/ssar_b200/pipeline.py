@@ -37,6 +37,66 @@ def spectral_frontend(x: torch.Tensor, sr, n_fft: int = 2048, hop: int = 512, wa
     return {"spec": out.get("spec"), "mel": out["bank0"], "onset": onset, "rms": out["rms"]}
 
 
+def spectral_frontend_segmented(x: torch.Tensor, sr, n_fft: int = 2048, hop: int = 512, seg_frames: int = 4096,
+                                want_spec: bool = True, device=None):
+    """`spectral_frontend` for LONG tracks cut into time segments with FFT-window halos (north star: "long tracks are split
+    by time segment with FFT-window halos"): each segment of seg_frames frames is transformed from the samples
+    [f0 * hop - n_fft / 2, (f1 - 1) * hop + n_fft / 2] (clamped to the track; reflection only at the track's true ends).
+    x [B, N] may live in (pinned) HOST memory: segment s + 1 crosses PCIe on a copy stream while segment s is
+    transformed, and only one segment (+ halo) of the waveform is resident at a time.  The one track-global quantity of
+    this front end — power_to_db's maximum over the whole mel spectrogram (rosa/beat.py:14-15) — is the maximum of the
+    segments' maxima, so the onset envelope is computed after the last segment.  Same outputs as `spectral_frontend`,
+    bit for bit (tests/test_gpu_frontend.py)."""
+    B, N = x.shape
+    dev = torch.device(device) if device is not None else (x.device if x.is_cuda else torch.device("cuda"))
+    T = N // hop
+    M = n_fft // 2
+    bank = plan.mel_bank(float(sr), n_fft, 128, 0.0, None, str(dev))
+    bank_onset = plan.mel_bank(float(sr), n_fft, 128, 0.0, 11025.0, str(dev))
+    spec = torch.empty(B, T, n_fft // 2 + 1, dtype=torch.float32, device=dev) if want_spec else None
+    mel = torch.empty(B, T, 128, dtype=torch.float32, device=dev)
+    mel_on = torch.empty(B, T, 128, dtype=torch.float32, device=dev)
+    rms = torch.empty(B, T, dtype=torch.float32, device=dev)
+    max_key = None
+    main = torch.cuda.current_stream(dev)
+    copy_stream = _side_stream(dev, "h2d") if not x.is_cuda else None
+    bounds = [(f0, min(f0 + seg_frames, T)) for f0 in range(0, T, seg_frames)]
+
+    def fetch(f0, f1):
+        lo, hi = max(0, f0 * hop - M), min(N, (f1 - 1) * hop + M)
+        if f0 == 0:
+            hi = max(hi, min(N, M + 1))          # reflection of the leading pad reads samples 1 .. n_fft / 2
+        if (f1 - 1) * hop + M > N:
+            lo = min(lo, max(0, N - 1 - M))      # ... and of the trailing pad the last n_fft / 2
+        if x.is_cuda:
+            return x[:, lo:hi], lo, None
+        with torch.cuda.stream(copy_stream):
+            seg = torch.empty(B, hi - lo, dtype=torch.float32, device=dev)
+            seg.copy_(x[:, lo:hi], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(copy_stream)
+        return seg, lo, ev
+
+    nxt = fetch(*bounds[0])
+    for si, (f0, f1) in enumerate(bounds):
+        seg, lo, ev = nxt
+        nxt = fetch(*bounds[si + 1]) if si + 1 < len(bounds) else None
+        if ev is not None:
+            main.wait_event(ev)
+            seg.record_stream(main)
+        o = ops.frames_fft(seg, n_fft, hop, f1 - f0, torch.hann_window, spec_power=2 if want_spec else None, want_rms=True,
+                           banks=[(bank, True, False), (bank_onset, True, True)], segment=(lo, N, f0))
+        if want_spec:
+            spec[:, f0:f1] = o["spec"]
+        mel[:, f0:f1], mel_on[:, f0:f1], rms[:, f0:f1] = o["bank0"], o["bank1"], o["rms"]
+        # order-preserving keys: the running maximum is an integer maximum (keys are stored as int32 bit patterns)
+        k = o["bank1_max"].view(torch.int32).to(torch.int64) & 0xFFFFFFFF
+        max_key = k if max_key is None else torch.maximum(max_key, k)
+    key32 = torch.where(max_key >= 2 ** 31, max_key - 2 ** 32, max_key).to(torch.int32)
+    onset = ops.onset_flux(mel_on, key32, 1 + n_fft // (2 * hop), "mean")
+    return {"spec": spec, "mel": mel, "onset": onset, "rms": rms}
+
+
 def hpss_pair(x: torch.Tensor, margin: float = 8.0, n_fft: int = 2048, hop: int = 1024, D=None, want_harm=True,
               want_perc=True, lens=None):
     """harmonic(x), percussive(x) (features/audio.py:13-24) from ONE forward STFT and ONE pair of median passes.

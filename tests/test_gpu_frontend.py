@@ -158,3 +158,19 @@ def test_lane_interleaved_banks_equal_packed_banks():
         slow = ops.frames_fft(x, n_fft, hop, n_frames, banks=((packed[0], True, True), (packed[1], True, False)))
         for key in ("bank0", "bank1", "bank0_max"):
             assert torch.equal(fast[key], slow[key]), (n_fft, key)
+
+
+def test_time_segments_with_halos_equal_whole_track():
+    """Long tracks cut into time segments with n_fft / 2 halos (frames_fft `segment`, pipeline.spectral_frontend_segmented):
+    every output equals the whole-track call bit for bit — device-resident and pinned-host waveforms, segment lengths that
+    do and do not divide the frame count, a ragged track length."""
+    from ssar_b200 import pipeline
+
+    sr = 44100
+    xs = torch.stack([synth_clip(sr * 21 + 311, sr, i) for i in (1, 4)])
+    whole = pipeline.spectral_frontend(xs.cuda(), sr, 2048, 512)
+    for seg_frames, src in ((256, xs.cuda()), (401, xs.pin_memory()), (5000, xs.cuda())):
+        seg = pipeline.spectral_frontend_segmented(src, sr, 2048, 512, seg_frames=seg_frames)
+        torch.cuda.synchronize()
+        for k in ("spec", "mel", "onset", "rms"):
+            assert torch.equal(seg[k], whole[k]), (seg_frames, k, rel_l2(seg[k], whole[k]))
