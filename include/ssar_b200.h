@@ -553,6 +553,27 @@ int ssar_cqt_tc(const float* const* signals, const long long* n_samples, int n_o
                 long long row_scale_ld, float basis_scale, void* scratch, float* out, const long long* clip_samples,
                 const int* clip_frames, void* stream);
 
+/* ssar/supervised/data.py:255-258 overlapping_slices (the dataset's training windows, also :119-132): window k = rows
+ * [offsets[k], offsets[k] + window) of x [n_rows, inner] -> out [n_windows, window, inner].  offsets: device int64, every
+ * offsets[k] + window <= n_rows (the caller lists the reference's windows: starts 0, L/4, L/2, 3L/4, splits of L, the last
+ * split of every start dropped). */
+int ssar_window_slices(const float* x, long long n_rows, long long inner, const long long* offsets, int n_windows, int window,
+                       float* out, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Video-side feature twins (ssar/features/video.py), video: [n_frames, n_channels, height, width] fp32
+ * ---------------------------------------------------------------------------------------------- */
+
+/* video.py:11-31 redogram / greenogram / blueogram: per frame torch.histc(video[t, channel], bins) over the frame's own
+ * [min, max] (a constant frame: [v - 1, v + 1]), divided by the largest count.  Written to
+ * out[t * out_ld + out_col0 + b] so rgb_hist's three histograms land side by side. */
+int ssar_video_hist(const float* video, int n_frames, int n_channels, int height, int width, int channel, int bins,
+                    float* out, long long out_ld, int out_col0, void* stream);
+/* video.py:58-59 visual_variance: (std over (C, H, W), unbiased) ** 2 per frame -> out [n_frames] */
+int ssar_video_variance(const float* video, int n_frames, long long n_per_frame, float* out, void* stream);
+/* video.py:62-73 absdiff: out[t] = sum |video[t + 1] - video[t]| for t < n_frames - 1, out[n_frames - 1] = out[n_frames - 2] */
+int ssar_video_absdiff(const float* video, int n_frames, long long n_per_frame, float* out, void* stream);
+
 /* maua/maua/GAN/wrappers/stylegan2.py:193-210 make_noise_pyramid (normalize = 1) and the synthesizer's own resize of a
  * mismatched noise input, :86-96 (normalize = 0): noise [n_frames, in_h, in_w] -> outs[l] [n_frames, heights[l], widths[l]]
  * for l < n_layers <= 16, bicubic (torch.nn.functional.interpolate, mode="bicubic", align_corners=False); with

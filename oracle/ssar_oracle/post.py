@@ -138,3 +138,12 @@ def feature_stats(feats):
     """supervised/data.py:317-319: mean and population std per feature over every window and frame (fp64 here)."""
     f = feats.reshape(-1, feats.shape[-1]).double().numpy()
     return np.mean(f, 0), np.std(f, 0)
+
+
+def overlapping_slices(tensor, length):
+    """supervised/data.py:255-258: for start in range(0, L, L // 4): the chunks of L rows of tensor[start:], the last chunk
+    of every start dropped; stacked in that order."""
+    out = []
+    for start in range(0, length, length // 4):
+        out += list(torch.split(tensor[start:], length)[:-1])
+    return torch.stack(out)

@@ -386,9 +386,41 @@ __global__ void feature_stats_kernel(const float* __restrict__ x, long long rows
     }
 }
 
+// overlapping_slices (supervised/data.py:255-258): window k = rows [offsets[k], offsets[k] + L) of x [T, inner] ->
+// out [n, L, inner].  A window is L * inner contiguous floats on both sides: 128-bit copies when aligned.
+__global__ void window_slices_kernel(const float* __restrict__ x, long long inner, const long long* __restrict__ offsets,
+                                     int L, float* __restrict__ out) {
+    const long long per = (long long)L * inner;
+    const float* src = x + __ldg(offsets + blockIdx.y) * inner;
+    float* dst = out + (long long)blockIdx.y * per;
+    if ((per & 3) == 0 && ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0) {
+        const float4* s4 = reinterpret_cast<const float4*>(src);
+        float4* d4 = reinterpret_cast<float4*>(dst);
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < (per >> 2); i += (long long)gridDim.x * blockDim.x)
+            d4[i] = __ldg(s4 + i);
+    } else {
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < per; i += (long long)gridDim.x * blockDim.x)
+            dst[i] = __ldg(src + i);
+    }
+}
+
 }  // namespace
 
 #define ST(s) reinterpret_cast<cudaStream_t>(s)
+
+extern "C" int ssar_window_slices(const float* x, long long n_rows, long long inner, const long long* offsets, int n_windows,
+                                  int window, float* out, void* stream) {
+    if (n_windows == 0 || window == 0 || inner == 0) return SSAR_OK;
+    SSAR_REQUIRE(x && offsets && out && n_rows >= window && n_windows <= 65535 * 64, "window_slices: null pointer or bad sizes");
+    const long long per = (long long)window * inner;
+    int gx = ssar_div_up(per, 256 * 8);
+    if (gx > 64) gx = 64;
+    for (int w0 = 0; w0 < n_windows; w0 += 65535) {
+        const int nw = n_windows - w0 < 65535 ? n_windows - w0 : 65535;
+        window_slices_kernel<<<dim3(gx, nw), 256, 0, ST(stream)>>>(x, inner, offsets + w0, window, out + (long long)w0 * per);
+    }
+    return ssar_launch_status("window_slices");
+}
 
 extern "C" int ssar_gauss1d(const float* x, int n_clips, int n_frames, long long inner, const float* weights, int radius,
                             int mode, float* out, const int* clip_frames, void* stream) {

@@ -482,6 +482,33 @@ def salience_features(raw: torch.Tensor, group_sizes, sigma: float = 2.0, short_
     return [buf[:, T * st : T * (st + n)].view(B, T, n) for st, n in zip(starts, group_sizes)]
 
 
+def window_offsets(n_rows: int, length: int):
+    """Start rows of supervised/data.py:255-258's windows, in its order: for start in range(0, L, L // 4), the splits of
+    tensor[start:] into chunks of L with the LAST chunk dropped (full or not)."""
+    offs = []
+    for start in range(0, length, length // 4):
+        n_chunks = -(-(n_rows - start) // length) if n_rows > start else 0
+        offs += [start + c * length for c in range(max(n_chunks - 1, 0))]
+    return offs
+
+
+def overlapping_slices(x: torch.Tensor, length: int):
+    """supervised/data.py:255-258: x [T, ...] -> [n_windows, length, ...] (one gather launch, `ssar_window_slices`)."""
+    if not x.is_cuda:
+        raise SsarError("ssar_b200 needs CUDA tensors (no CPU fallback)")
+    x = x.contiguous().float()
+    T = x.shape[0]
+    inner = x.numel() // max(T, 1)
+    offs = window_offsets(T, int(length))
+    if not offs:
+        raise RuntimeError("stack expects a non-empty TensorList")  # torch.stack([]) in the reference
+    o = torch.tensor(offs, dtype=torch.int64, device=x.device)
+    out = torch.empty((len(offs), int(length)) + tuple(x.shape[1:]), dtype=torch.float32, device=x.device)
+    cabi.call("ssar_window_slices", ptr(x), i64(T), i64(inner), ptr(o), i32(len(offs)), i32(length), ptr(out),
+              nbytes=2 * cabi.nbytes_of(out))
+    return out
+
+
 def feature_stats(x: torch.Tensor, stats: torch.Tensor | None = None, clip_frames=None):
     """x [..., C] -> fp64 [3, C] = (count, sum, sum of squares) accumulated into `stats` (allocated if None).
     clip_frames (int32 [B]): ragged batch x [B, T, C] — rows past each clip's own count are skipped."""

@@ -35,3 +35,23 @@ def audio2features(audio, sr, fps, clamp=True, smooth=True, emphasis=False):
     if audio.dim() == 2:
         audio = audio.mean(0)
     return pipeline.audio2features_batch(audio[None], sr, fps, clamp, smooth, emphasis)[0]
+
+
+def overlapping_slices(tensor, length):
+    """supervised/data.py:255-258 (and AudioFeatures.__getitem__, :128-131): the overlapping training windows of one
+    track's feature / latent / noise sequence, [T, ...] -> [n_windows, length, ...]."""
+    from .. import ops
+
+    return ops.overlapping_slices(tensor, int(length))
+
+
+def window_mean_std(feature_sequences, length, group=None):
+    """supervised/data.py:317-319: np.mean / np.std over ALL windows and frames of the sliced training set — a frame
+    counts once per window that holds it.  feature_sequences: iterable of [T_i, 59] CUDA tensors (this rank's tracks);
+    the (count, sum, sum of squares) accumulators are all-reduced across ranks (NCCL) when torch.distributed is up."""
+    from .. import distributed, ops
+
+    stats = None
+    for f in feature_sequences:
+        stats = ops.feature_stats(ops.overlapping_slices(f, int(length)), stats)
+    return distributed.mean_std_from_stats(distributed.merge_stats(stats, group))

@@ -369,11 +369,44 @@ def g_widened(ref):
     save("widened", **out)
 
 
+def g_slices(ref):
+    """supervised/data.py:255-258 overlapping_slices and the :317-319 window statistics (np.mean / np.std over all windows
+    and frames) on synthetic feature matrices."""
+    out = {}
+    for T, L in ((1000, 192), (768, 192), (777, 96), (5760, 192)):
+        x = synth_features(T, 59, 50 + T % 7)
+        w = ref.data.overlapping_slices(x, L)
+        out[f"first_row_{T}_{L}"] = torch.tensor([int((x[:, 0] == v).nonzero()[0]) for v in w[:, 0, 0]])
+        out[f"n_{T}_{L}"] = w.shape[0]
+    tracks = [synth_features(T, 59, 60 + i) for i, T in enumerate((1000, 2111, 777))]
+    allw = np.concatenate([ref.data.overlapping_slices(f, 192).numpy() for f in tracks])
+    out["win_mean"], out["win_std"] = np.mean(allw, axis=(0, 1)), np.std(allw, axis=(0, 1))
+    save("slices", **out)
+
+
+from video_synth import synth_video  # noqa: E402
+
+
+def g_video(ref):
+    """ssar/features/video.py:11-31, 58-73 (module imports cv2 + kornia: the functions' own text is compiled and run)."""
+    from ref_loader import exec_reference_defs
+
+    ns = exec_reference_defs("ssar/features/video.py", ["redogram", "greenogram", "blueogram", "rgb_hist", "visual_variance",
+                                                      "absdiff"], dict(torch=torch))
+    out = {}
+    for tag, kw in (("a", dict()), ("b", dict(T=129, H=33, W=65, seed=6)), ("c", dict(T=2, H=16, W=16, seed=7))):
+        v = synth_video(**kw)
+        out[f"red_{tag}"], out[f"green_{tag}"], out[f"blue_{tag}"] = ns["redogram"](v), ns["greenogram"](v, 20), ns["blueogram"](v)
+        out[f"rgb_{tag}"] = ns["rgb_hist"](v)
+        out[f"var_{tag}"], out[f"absdiff_{tag}"] = ns["visual_variance"](v), ns["absdiff"](v)
+    save("video", **out)
+
+
 def palette_27():
     return synth_patch_inputs(8, 1)[2][:27]
 
 
-GROUPS = {"widened": g_widened, "mir": g_mir, "a2f_short": g_a2f_short, "maua": g_maua, "traj": g_traj, "a2f": g_a2f, "chroma": g_chroma, "post": g_post, "spectral": g_spectral, "frame_features": g_frame_features, "hpss_filters": g_hpss_filters}
+GROUPS = {"video": g_video, "slices": g_slices, "widened": g_widened, "mir": g_mir, "a2f_short": g_a2f_short, "maua": g_maua, "traj": g_traj, "a2f": g_a2f, "chroma": g_chroma, "post": g_post, "spectral": g_spectral, "frame_features": g_frame_features, "hpss_filters": g_hpss_filters}
 
 if __name__ == "__main__":
     torch.manual_seed(0)

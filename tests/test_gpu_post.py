@@ -82,3 +82,43 @@ def test_clamp_peaks_raises_without_peaks():
 
     with pytest.raises(RuntimeError):
         P.clamp_peaks_percentile(torch.arange(100, dtype=torch.float32).cuda(), 97.5)
+
+
+def test_overlapping_slices_and_window_stats_vs_golden():
+    """supervised/data.py:255-258 (one gather launch) and :317-319 (mean / std over all windows: frames count once per
+    window that holds them) against the reference's own outputs."""
+    import numpy as np
+    from ssar_b200.supervised import data
+    from ssar_b200.synth import synth_features
+
+    g = {k: np.asarray(v) for k, v in np.load(GOLDEN / "slices.npz").items()}
+    for T, L in ((1000, 192), (768, 192), (777, 96), (5760, 192)):
+        x = synth_features(T, 59, 50 + T % 7)
+        w = data.overlapping_slices(x.cuda(), L).cpu()
+        assert tuple(w.shape) == (int(g[f"n_{T}_{L}"]), L, 59)
+        for k, r in enumerate(g[f"first_row_{T}_{L}"]):
+            assert torch.equal(w[k], x[int(r) : int(r) + L])
+    lat = torch.randn(700, 18, 512, generator=torch.Generator().manual_seed(2)).cuda()
+    wl = data.overlapping_slices(lat, 192)
+    assert tuple(wl.shape) == (11, 192, 18, 512)  # starts 0 / 48 / 96 / 144 -> 3 + 3 + 3 + 2 windows
+    assert torch.equal(wl[5], lat[48 + 384 : 48 + 576]) and torch.equal(wl[10], lat[144 + 192 : 144 + 384])
+    tracks = [synth_features(T, 59, 60 + i).cuda() for i, T in enumerate((1000, 2111, 777))]
+    mean, std = data.window_mean_std(tracks, 192)
+    assert np.allclose(mean.cpu().numpy(), g["win_mean"], rtol=1e-6, atol=1e-7) and np.allclose(std.cpu().numpy(), g["win_std"], rtol=1e-5)
+    with pytest.raises(RuntimeError):
+        data.overlapping_slices(torch.zeros(191, 59).cuda(), 192)
+
+
+def test_video_twins_vs_golden():
+    """features/video.py:11-31 (histogram COUNTS are integers: exact), :58-59, :62-73 against the reference's outputs."""
+    from video_synth import synth_video
+    from ssar_b200.features import video as vid
+
+    g = load("video")
+    for tag, kw in (("a", dict()), ("b", dict(T=129, H=33, W=65, seed=6)), ("c", dict(T=2, H=16, W=16, seed=7))):
+        v = synth_video(**kw).cuda()
+        assert torch.equal(vid.redogram(v).cpu(), g[f"red_{tag}"]), tag
+        assert torch.equal(vid.greenogram(v, 20).cpu(), g[f"green_{tag}"]) and torch.equal(vid.blueogram(v).cpu(), g[f"blue_{tag}"])
+        assert torch.equal(vid.rgb_hist(v).cpu(), g[f"rgb_{tag}"])
+        assert rel_l2(vid.visual_variance(v), g[f"var_{tag}"]) < 1e-5 and rel_l2(vid.absdiff(v), g[f"absdiff_{tag}"]) < 1e-5
+        assert tuple(vid.absdiff(v).shape) == (v.shape[0], 1)

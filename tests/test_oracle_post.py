@@ -51,3 +51,33 @@ def test_normalise_quantiles_clamps():
         assert v.shape == g[k].shape and torch.equal(v, g[k]), k  # order statistics: bit-exact
     assert rel_l2(post.emphasize(x, 2, 75), g["emphasize"]) < TOL
     assert rel_l2(post.emphasize(x[:, :1], 10, 50), g["emphasize_10_50"]) < TOL
+
+
+def test_overlapping_slices_and_window_stats():
+    """supervised/data.py:255-258, 317-319 against the reference's own function (tests/golden/slices.npz)."""
+    import numpy as np
+    from ssar_b200.synth import synth_features
+
+    g = {k: np.asarray(v) for k, v in np.load(GOLDEN / "slices.npz").items()}
+    for T, L in ((1000, 192), (768, 192), (777, 96), (5760, 192)):
+        x = synth_features(T, 59, 50 + T % 7)
+        w = post.overlapping_slices(x, L)
+        assert w.shape == (int(g[f"n_{T}_{L}"]), L, 59)
+        for k, r in enumerate(g[f"first_row_{T}_{L}"]):
+            assert torch.equal(w[k], x[int(r) : int(r) + L])
+    tracks = [synth_features(T, 59, 60 + i) for i, T in enumerate((1000, 2111, 777))]
+    allw = torch.cat([post.overlapping_slices(f, 192) for f in tracks]).numpy()
+    assert np.allclose(np.mean(allw, axis=(0, 1)), g["win_mean"], rtol=1e-6) and np.allclose(np.std(allw, axis=(0, 1)), g["win_std"], rtol=1e-6)
+
+
+def test_video_twins():
+    """video.py:11-31, 58-73 restated in oracle/video.py against the reference's own function text."""
+    from video_synth import synth_video
+    from ssar_oracle import video as ovid
+
+    g = load("video")
+    for tag, kw in (("a", dict()), ("b", dict(T=129, H=33, W=65, seed=6)), ("c", dict(T=2, H=16, W=16, seed=7))):
+        v = synth_video(**kw)
+        assert torch.equal(ovid.channel_hist(v, 0), g[f"red_{tag}"]) and torch.equal(ovid.channel_hist(v, 1, 20), g[f"green_{tag}"])
+        assert torch.equal(ovid.rgb_hist(v), g[f"rgb_{tag}"])
+        assert rel_l2(ovid.visual_variance(v), g[f"var_{tag}"]) < 1e-6 and rel_l2(ovid.absdiff(v), g[f"absdiff_{tag}"]) < 1e-6
