@@ -553,6 +553,10 @@ int ssar_cqt_tc(const float* const* signals, const long long* n_samples, int n_o
                 long long row_scale_ld, float basis_scale, void* scratch, float* out, const long long* clip_samples,
                 const int* clip_frames, void* stream);
 
+/* 16-bit PCM -> fp32: out[i] = pcm[i] / 32768 (exact; torchaudio.load's normalisation of the PCM files the reference reads,
+ * supervised/data.py:127, :180).  A host can ship audio in its on-disk width: half the host-to-device bytes. */
+int ssar_pcm16_to_float(const short* pcm, long long n, float* out, void* stream);
+
 /* ssar/supervised/data.py:255-258 overlapping_slices (the dataset's training windows, also :119-132): window k = rows
  * [offsets[k], offsets[k] + window) of x [n_rows, inner] -> out [n_windows, window, inner].  offsets: device int64, every
  * offsets[k] + window <= n_rows (the caller lists the reference's windows: starts 0, L/4, L/2, 3L/4, splits of L, the last

@@ -31,7 +31,40 @@ __global__ void rms_frames_kernel(const float* __restrict__ x, long long n_sampl
     }
 }
 
+// 16-bit PCM -> fp32 in [-1, 1): x / 32768, exact in fp32 (what torchaudio.load's normalisation does to the PCM files the
+// reference reads, supervised/data.py:127, :180): lets a host ship the audio in its on-disk width, half the H2D bytes.
+__global__ void pcm16_to_float_kernel(const short* __restrict__ in, long long n, float* __restrict__ out) {
+    const long long n8 = n >> 3;
+    if (((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0) {
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+            const int4 v = __ldg(reinterpret_cast<const int4*>(in) + i);
+            const short* s = reinterpret_cast<const short*>(&v);
+            float4 a, b;
+            a.x = (float)s[0] * (1.f / 32768.f); a.y = (float)s[1] * (1.f / 32768.f);
+            a.z = (float)s[2] * (1.f / 32768.f); a.w = (float)s[3] * (1.f / 32768.f);
+            b.x = (float)s[4] * (1.f / 32768.f); b.y = (float)s[5] * (1.f / 32768.f);
+            b.z = (float)s[6] * (1.f / 32768.f); b.w = (float)s[7] * (1.f / 32768.f);
+            reinterpret_cast<float4*>(out)[2 * i] = a;
+            reinterpret_cast<float4*>(out)[2 * i + 1] = b;
+        }
+        for (long long i = 8 * n8 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+            out[i] = (float)__ldg(in + i) * (1.f / 32768.f);
+    } else {
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+            out[i] = (float)__ldg(in + i) * (1.f / 32768.f);
+    }
+}
+
 }  // namespace
+
+extern "C" int ssar_pcm16_to_float(const short* pcm, long long n, float* out, void* stream) {
+    if (n == 0) return SSAR_OK;
+    SSAR_REQUIRE(pcm && out, "pcm16_to_float: null pointer");
+    int grid = ssar_div_up(n, 256 * 8);
+    if (grid > SSAR_NUM_SMS * 16) grid = SSAR_NUM_SMS * 16;
+    pcm16_to_float_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(pcm, n, out);
+    return ssar_launch_status("pcm16_to_float");
+}
 
 extern "C" int ssar_rms_frames(const float* x, long long n_samples, long long clip_stride, int n_clips,
                                int frame_length, int hop, int n_frames, float* out, void* stream) {

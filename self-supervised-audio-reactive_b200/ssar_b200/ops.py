@@ -33,6 +33,19 @@ def _as_batch(x: torch.Tensor):
     return x, squeeze
 
 
+def pcm16_to_float(pcm: torch.Tensor, out: torch.Tensor | None = None):
+    """int16 PCM (CUDA) -> fp32 / 32768 (`ssar_pcm16_to_float`); `out`: optional preallocated fp32 tensor of the same shape."""
+    if not pcm.is_cuda or pcm.dtype != torch.int16:
+        raise SsarError("pcm16_to_float needs a CUDA int16 tensor")
+    pcm = pcm.contiguous()
+    if out is None:
+        out = torch.empty(pcm.shape, dtype=torch.float32, device=pcm.device)
+    elif not out.is_contiguous() or out.shape != pcm.shape or out.dtype != torch.float32:
+        raise SsarError("pcm16_to_float: out must be a contiguous fp32 tensor of the input's shape")
+    cabi.call("ssar_pcm16_to_float", ptr(pcm), i64(pcm.numel()), ptr(out), nbytes=cabi.nbytes_of(pcm, out))
+    return out
+
+
 def fill_u32(t: torch.Tensor, value: int):
     cabi.call("ssar_fill_u32", ptr(t), i64(t.numel()), C.c_uint32(value))
 

@@ -284,6 +284,8 @@ def features_and_patch_inputs(audio: torch.Tensor, sr, fps, deferred_checks=None
     `retrieve_music_information(resample(audio, sr, 1024 * fps), 1024 * fps)[0]` (random/sample.py:34,61; mir.py:26,44)."""
     from .resampling import resample
 
+    if audio.dtype == torch.int16:  # 16-bit PCM: x / 32768 like torchaudio.load's normalisation (exact)
+        audio = ops.pcm16_to_float(audio)
     x = resample(audio, sr, fps * 1024, clip_n_in=lens.n_in if lens is not None else None)
     ch = feature_chain(x, fps * 1024, want_a2f=True, want_mir=True, sync_free=sync_free, lens=lens)
     return (finish_features(ch["a2f"], fps, deferred_checks=deferred_checks, lens=lens),
@@ -360,7 +362,10 @@ class FeatureGraph:
         """Replays on the current stream.  x: [clips, samples] CUDA tensor copied into the static input (None: the caller
         already filled `self.x`).  -> (features [B, T, 59], patch feature dict) as fresh tensors."""
         if x is not None:
-            self.x.copy_(x, non_blocking=True)
+            if x.dtype == torch.int16:
+                ops.pcm16_to_float(x, out=self.x)  # 16-bit PCM staging: converted straight into the static input
+            else:
+                self.x.copy_(x, non_blocking=True)
         self.graph.replay()
         feats = self.feats.clone()
         pf = {k: v.clone() for k, v in self.patch_feats.items()}
@@ -639,6 +644,8 @@ def default_patch_workers(rng_device="cpu") -> int:
 def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, segmentations, tempo=120.0, seed=42,
                          rng_device="cuda", workers=None, chunk=8, serial=False):
     """The north-star unit for a batch of clips: waveforms [B, N] -> (features [B, T, 59], latents [B, T, 18, 512]).
+    audio: fp32 waveforms, or int16 PCM (converted on the device as x / 32768, exactly torchaudio.load's normalisation of
+    the 16-bit files the reference reads — a host-resident batch then crosses PCIe at half the bytes).
     Tempo and segmentations are inputs (random/mir.py:28-42 is CPU librosa / scipy work outside the path).
     rng_device: where the Patch generator lives ("cpu" reproduces a CPU-seeded reference run bit for bit in its draws;
     the reference's own default is the compute device, random/__init__.py:1-3).

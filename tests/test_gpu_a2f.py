@@ -278,3 +278,25 @@ def test_features_and_patch_inputs_match_their_single_purpose_calls():
     assert torch.equal(f, pipeline.audio2features_batch(xs, 44100, 24))
     mf = pipeline.music_features_batch(resample(xs, 44100, 24 * 1024), 24 * 1024)
     assert all(torch.equal(pf[k], mf[k]) for k in mf)
+
+
+def test_pcm16_input_equals_normalised_float_input():
+    """int16 PCM in (device or pinned host, eager / graph / serial) == the same audio as x / 32768 fp32 (torchaudio.load's
+    normalisation), bit for bit."""
+    from ssar_b200 import ops, pipeline
+    from ssar_b200.synth import synth_patch_inputs
+
+    xs = torch.stack([synth_clip(44100 * 45, 44100, i) for i in (3, 9, 4, 7)])
+    pcm = (xs * 32767).round().clamp(-32768, 32767).to(torch.int16)
+    xf = pcm.float() / 32768
+    assert torch.equal(ops.pcm16_to_float(pcm.cuda()).cpu(), xf)
+    assert torch.equal(ops.pcm16_to_float(pcm.cuda()[:, 1:777]).cpu(), xf[:, 1:777])  # unaligned / ragged tail path
+    _, segs, palette = synth_patch_inputs(1080, 0)
+    palette = palette.cuda()
+    f0, l0, _ = pipeline.features_and_latents(xf.cuda(), 44100, 24, palette, segs, chunk=2, serial=True)
+    for audio in (pcm.cuda(), pcm.pin_memory(), pcm.pin_memory()):  # eager, capture, replay
+        f, l, _ = pipeline.features_and_latents(audio, 44100, 24, palette, segs, chunk=2)
+        torch.cuda.synchronize()
+        assert torch.equal(f, f0) and torch.equal(l, l0)
+    f, l, _ = pipeline.features_and_latents(pcm.cuda(), 44100, 24, palette, segs, chunk=2, serial=True)
+    assert torch.equal(f, f0) and torch.equal(l, l0)
