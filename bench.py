@@ -71,26 +71,30 @@ class ClockSampler:
         do not run N pollers against the driver during the timed region)."""
         self.index, self.rows, self.proc, self.enabled = ",".join(str(i) for i in indices), [], None, enabled
 
-    def _nvml_loop(self, handles):
+    def _nvml_loop(self, handles, mx):
         import pynvml as nv
         bits = {"hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8),
                 "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
                 "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
                 "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4)}
-        mx = [nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM) for h in handles]
+        # ONE GPU per tick, round robin (two NVML calls per 50 ms): polling all 8 GPUs of a busy node in one burst
+        # contends with the 8 launching processes for the driver's locks (it cost milliseconds per step and, on one box,
+        # returned nothing inside a 280 ms timed region)
+        i = 0
         while not self.stop.is_set():
-            for h, m in zip(handles, mx):
+            h, m = handles[i % len(handles)], mx[i % len(handles)]
+            i += 1
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
                 try:
-                    sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
-                    try:
-                        rs = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
-                    except Exception:
-                        rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
-                    self.rows.append([str(sm), str(m)] + ["Active" if rs & bits[n] else "Not Active" for n in
-                                                         ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")])
+                    rs = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
                 except Exception:
-                    pass
-            self.stop.wait(0.1)
+                    rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.rows.append([str(sm), str(m)] + ["Active" if rs & bits[n] else "Not Active" for n in
+                                                     ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")])
+            except Exception:
+                pass
+            self.stop.wait(0.05)
 
     def __enter__(self):
         if not self.enabled:
@@ -101,9 +105,10 @@ class ClockSampler:
             import pynvml as nv
             nv.nvmlInit()
             handles = [nv.nvmlDeviceGetHandleByIndex(int(i)) for i in self.index.split(",")]
+            mx = [nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM) for h in handles]  # (before the timed region)
             self.stop = threading.Event()
             self.source = "nvml"
-            self.thread = threading.Thread(target=self._nvml_loop, args=(handles,), daemon=True)
+            self.thread = threading.Thread(target=self._nvml_loop, args=(handles, mx), daemon=True)
             self.thread.start()
             return self
         except Exception:
