@@ -518,14 +518,26 @@ def main():
         _, segs, palette = synth_patch_inputs(T, 0)
         palette = palette.to(dev)
 
+        stats_ring = [stats, torch.zeros_like(stats)]
+        pending = [None, None]
+        step_no = [0]
+
         def step(xd, serial=False):
             feats, latents, _ = pipeline.features_and_latents(xd, SR, FPS, palette, segs, rng_device=args.rng,
                                                               workers=args.workers, serial=serial, chunk=args.chunk)
-            # the one cross-clip reduction of the path: per-feature (count, sum, sum^2) for the dataset mean / std
-            stats.zero_()
-            ops.feature_stats(feats, stats)
+            # the one cross-clip reduction of the path: per-feature (count, sum, sum^2) for the dataset mean / std.
+            # The all-reduce is asynchronous and double buffered: step k's reduction is only waited for when step k + 2
+            # reuses its buffer, so the ranks are not put in lock-step by a 1.4 kB collective (the sum of per-step maxima
+            # over 8 ranks is what a blocking all-reduce per step measures)
+            slot = step_no[0] % 2
+            step_no[0] += 1
+            buf = stats_ring[slot]
+            if pending[slot] is not None:
+                pending[slot].wait()
+            buf.zero_()
+            ops.feature_stats(feats, buf)
             if world > 1:
-                dist.all_reduce(stats)  # NCCL: 59 x 3 fp64
+                pending[slot] = dist.all_reduce(buf, async_op=True)  # NCCL: 59 x 3 fp64
             return {"feats": feats, "latents": latents}
 
         def results(o):
@@ -718,7 +730,7 @@ def main():
             "config": {"workload": workload_name(kind, B), "clips_per_gpu": B, "frames_per_clip": T,
                        "single_track": single, "cfg4": cfg4,
                        "l2": f"inputs_exceed_l2 ({B * n * 4 / 1e9:.2f} GB of waveforms per step)",
-                       "parallelism": f"clip-sharded x{world}; one NCCL all-reduce of 59x3 fp64 feature stats per step"
+                       "parallelism": f"clip-sharded x{world}; one asynchronous NCCL all-reduce of 59x3 fp64 feature stats per step"
                        if kind == "full" else f"clip-sharded x{world}, no data-path collective",
                        "patch_rng": args.rng if kind == "full" else None,
                        "host_threads": (args.workers or pipeline.default_patch_workers(args.rng)) if kind == "full" else 1},
