@@ -553,6 +553,13 @@ int ssar_cqt_tc(const float* const* signals, const long long* n_samples, int n_o
                 long long row_scale_ld, float basis_scale, void* scratch, float* out, const long long* clip_samples,
                 const int* clip_frames, void* stream);
 
+/* ssar/random/latent.py:7-13 spline_loop_latents as weights: out[t, k] with loop(y)[t] = sum_k out[t, k] y[k] for the closed
+ * natural cubic spline through (y_0 .. y_{K-1}, y_0) on linspace(0, 1, K + 1), evaluated at linspace(0, end, size) % 1.
+ * coef: fp64 [K, 4, K + 1] cardinal-spline coefficients (a, b, two_c, three_d) per segment; knots: fp32 [K + 1];
+ * n_knots_closed = K + 1 >= 3; out: fp32 [size, K] (the closing knot's weight folded onto knot 0). */
+int ssar_spline_loop_weights(const double* coef, const float* knots, int n_knots_closed, int size, float end, float* out,
+                             void* stream);
+
 /* 16-bit PCM -> fp32: out[i] = pcm[i] / 32768 (exact; torchaudio.load's normalisation of the PCM files the reference reads,
  * supervised/data.py:127, :180).  A host can ship audio in its on-disk width: half the host-to-device bytes. */
 int ssar_pcm16_to_float(const short* pcm, long long n, float* out, void* stream);

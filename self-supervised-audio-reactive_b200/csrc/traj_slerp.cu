@@ -125,3 +125,57 @@ extern "C" int ssar_slerp_loops(const float* y, int n_latents, int n_layers, int
     }
     return ssar_launch_status("slerp_loops");
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Cardinal weights of a closed natural-cubic-spline loop (ssar/random/latent.py:7-13): out[t, k] such that
+// spline_loop_latents(y, size, n_loops)[t] = sum_k out[t, k] y[k].  The evaluation points linspace(0, n_loops, size) % 1
+// (latent.py:10), the segment lookup (torch.bucketize, right = False) and the cubic in fp64 with explicit roundings
+// follow ssar_b200/plan.py::spline_loop_weights_cpu; one launch instead of a dozen small torch kernels — a dataset of
+// tracks of distinct lengths asks for new weights for every track.
+//   coef: fp64 [K1 - 1, 4, K1] = (a, b, two_c, three_d) of the K1 cardinal splines per segment; knots: fp32 [K1]
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+__global__ void spline_loop_weights_kernel(const double* __restrict__ coef, const float* __restrict__ knots, int K1, int size,
+                                           float end, float* __restrict__ out) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= size) return;
+    // torch.linspace(0, end, size): step = end / (size - 1); the first half counts up from the start, the second down
+    // from the end (ATen RangeFactories)
+    float v = 0.f;
+    if (size > 1) {
+        const float step = __fdiv_rn(end, (float)(size - 1));
+        v = t < size / 2 ? __fmul_rn(step, (float)t) : __fsub_rn(end, __fmul_rn(step, (float)(size - 1 - t)));
+    }
+    v = fmodf(v, 1.f);  // torch.remainder for non-negative operands
+    int lo = 0, hi = K1;  // bucketize(right=False): first i with knots[i] >= v
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(knots + mid) < v) lo = mid + 1;
+        else hi = mid;
+    }
+    const int idx = min(max(lo - 1, 0), K1 - 2);
+    const double f = (double)__fsub_rn(v, __ldg(knots + idx));
+    const double* c = coef + (long long)idx * 4 * K1;
+    const int K = K1 - 1;
+    float* o = out + (long long)t * K;
+    double w0 = 0.0;
+    for (int k = 0; k < K1; ++k) {
+        const double a = __ldg(c + k), b = __ldg(c + K1 + k), c2 = __ldg(c + 2 * K1 + k), d3 = __ldg(c + 3 * K1 + k);
+        // a + (b + (0.5 c2 + d3 f / 3) f) f, one rounding per operation like the host expression
+        const double inner = __dadd_rn(__dmul_rn(0.5, c2), __ddiv_rn(__dmul_rn(d3, f), 3.0));
+        const double w = __dadd_rn(a, __dmul_rn(__dadd_rn(b, __dmul_rn(inner, f)), f));
+        if (k == 0) w0 = w;
+        else if (k < K) o[k] = (float)w;
+        else w0 = __dadd_rn(w0, w);  // the closing knot is knot 0 again
+    }
+    o[0] = (float)w0;
+}
+}  // namespace
+
+extern "C" int ssar_spline_loop_weights(const double* coef, const float* knots, int n_knots_closed, int size, float end,
+                                        float* out, void* stream) {
+    if (size == 0) return SSAR_OK;
+    SSAR_REQUIRE(coef && knots && out && n_knots_closed >= 3 && size > 0, "spline_loop_weights: null pointer or fewer than 3 knots");
+    spline_loop_weights_kernel<<<ssar_div_up(size, 128), 128, 0, (cudaStream_t)stream>>>(coef, knots, n_knots_closed, size, end, out);
+    return ssar_launch_status("spline_loop_weights");
+}

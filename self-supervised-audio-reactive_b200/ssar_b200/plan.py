@@ -636,36 +636,47 @@ def knot_loop_weights_cpu(n_latents: int, size: int, n_loops: int) -> torch.Tens
     return torch.from_numpy(W.astype(np.float32))
 
 
+def _upload_async(t: torch.Tensor, device) -> torch.Tensor:
+    """Host tensor -> device through PINNED staging (torch's caching host allocator keeps the block alive until the copy
+    has run).  A copy from pageable memory synchronises the stream before it starts: per-track tables (a dataset of
+    distinct track lengths misses every length-keyed cache) then stall the host behind all queued kernels."""
+    pinned = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+    pinned.copy_(t)
+    return pinned.to(_dev(device), non_blocking=True)
+
+
 @functools.lru_cache(maxsize=64)
 def _cardinal_tables_device(K1: int, device):
     """(t_in fp32 [K1], coefficient tables fp64 [K1 - 1, 4, K1]) of `_cardinal_spline_coeffs` on the device."""
     a, b, c2, d3 = _cardinal_spline_coeffs(K1)
-    tab = torch.from_numpy(np.stack([a.T, b.T, c2.T, d3.T], axis=1))
-    return torch.linspace(0, 1, K1).to(_dev(device)), tab.to(_dev(device))
+    # (np.stack of transposed views comes back F-ordered: make the [segment, 4, knot] layout the kernel reads explicit)
+    tab = torch.from_numpy(np.ascontiguousarray(np.stack([a.T, b.T, c2.T, d3.T], axis=1)))
+    return torch.linspace(0, 1, K1).to(_dev(device)), tab.to(_dev(device)).contiguous()
 
 
 @functools.lru_cache(maxsize=256)
 def spline_loop_weights(n_knots: int, size: int, n_loops, device) -> torch.Tensor:
     """`spline_loop_weights_cpu` on the device, cached (the weights depend only on the knot count, length and loop count,
     so every sub-patch / clip of a batch of equal-length clips shares them).  The evaluation points are made on the host
-    like the reference makes them (`torch.linspace(0, n_loops, size) % 1`, latent.py:10); the table lookup and the cubic
-    run on the device in fp64 with the host function's expression — a dataset of tracks of distinct lengths misses the
-    cache for every track, and the numpy version cost 0.6 ms of host time per call.  Read-only result."""
+    ONE kernel (`ssar_spline_loop_weights`): the evaluation points `linspace(0, n_loops, size) % 1` (latent.py:10), the
+    table lookup and the cubic in fp64 with the host function's expression — a dataset of tracks of distinct lengths
+    misses the cache for every track, and the numpy version cost 0.6 ms (a torch-op version 0.24 ms) of host time per
+    call.  The device linspace can differ from torch's CPU linspace by an ulp of t (ATen's vectorised CPU kernel rounds
+    twice per element); the spline is continuous, so the weights move by ~1e-7.  Read-only result."""
     K1 = n_knots + 1
     if K1 == 2:
-        return spline_loop_weights_cpu(n_knots, size, n_loops).to(_dev(device))
+        return _upload_async(spline_loop_weights_cpu(n_knots, size, n_loops), device)
     t_in, tab = _cardinal_tables_device(K1, device)
-    t_out = (torch.linspace(0, n_loops, size) % 1).to(t_in.device, non_blocking=True)
-    idx = (torch.bucketize(t_out, t_in) - 1).clamp(0, K1 - 2)
-    frac = (t_out - t_in[idx]).double()[:, None]
-    c = tab[idx]  # [size, 4, K1]
-    W = c[:, 0] + (c[:, 1] + (0.5 * c[:, 2] + c[:, 3] * frac / 3.0) * frac) * frac
-    W[:, 0] += W[:, -1]
-    return W[:, :-1].float().contiguous()
+    from . import _cabi as cabi
+
+    out = torch.empty(size, n_knots, dtype=torch.float32, device=t_in.device)
+    cabi.call("ssar_spline_loop_weights", cabi.ptr(tab), cabi.ptr(t_in), cabi.i32(K1), cabi.i32(size), cabi.f32(float(n_loops)),
+              cabi.ptr(out), nbytes=cabi.nbytes_of(out))
+    return out
 
 
 @functools.lru_cache(maxsize=256)
 def loop_phase(n_loops, length: int, device) -> torch.Tensor:
     """ssar/random/noise.py:49: linspace(0, n_loops * 2 pi, length), evaluated on the CPU like the reference (the
     module is built on the default device and moved afterwards), cached on the device.  Read-only."""
-    return torch.linspace(0, n_loops * 2 * torch.pi, length).to(_dev(device))
+    return _upload_async(torch.linspace(0, n_loops * 2 * torch.pi, length), device)

@@ -233,3 +233,17 @@ def test_tensor_core_mix_operand_ranges_and_presplit_basis():
     assert torch.equal(ops.mix_gemm(W, P, basis_split=sp), ops.mix_gemm(W, P))
     W2 = torch.rand(300, G, K, generator=g).cuda()
     assert torch.equal(ops.mix_gemm(W2, P, basis_split=sp), ops.mix_gemm(W2, P))
+
+
+def test_spline_loop_weights_kernel_vs_host_tables():
+    """ssar_spline_loop_weights (device linspace + bucketize + fp64 cubic) against plan.spline_loop_weights_cpu (the host
+    tables the goldens of spline_loop_latents were checked with): the device linspace may sit an ulp of t away from
+    torch's CPU linspace (t reaches n_loops = 7 in one case), the spline is continuous -> 1e-5."""
+    from ssar_b200 import plan
+
+    for K, T, nl in ((8, 600, 1), (5, 777, 2.37), (12, 5760, 0.013), (3, 1000, 7), (20, 8641, 1)):
+        plan.spline_loop_weights.cache_clear()
+        w = plan.spline_loop_weights(K, T, nl, "cuda:0")
+        ref = plan.spline_loop_weights_cpu(K, T, nl)
+        assert tuple(w.shape) == (T, K) and float((w.cpu() - ref).abs().max()) < 1e-5, (K, T, nl, float((w.cpu() - ref).abs().max()))
+        assert float((w.sum(1) - 1).abs().max()) < 1e-5  # cardinal splines sum to one
