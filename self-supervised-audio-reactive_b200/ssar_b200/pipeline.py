@@ -292,6 +292,15 @@ def features_and_patch_inputs(audio: torch.Tensor, sr, fps, deferred_checks=None
             patch_inputs_from_raw(ch["mir"], lens=lens))
 
 
+def _count_replayed(n: int):
+    """A graph replay launches the kernels of the n C-ABI calls it captured: they count as launches (`_cabi.launch_count`
+    is what bench.py reports as `gpu_launches`)."""
+    from . import _cabi
+
+    with _cabi._count_lock:
+        _cabi.launch_count += n
+
+
 class FeatureGraph:
     """`features_and_patch_inputs` for a fixed (clips, samples, sr, fps) as ONE replayed CUDA graph.
 
@@ -352,9 +361,13 @@ class FeatureGraph:
             cs.synchronize()
             self.graph = torch.cuda.CUDAGraph()
             checks = []
+            from . import _cabi
+
+            n0 = _cabi.launch_count
             with torch.cuda.graph(self.graph, stream=cs, capture_error_mode="thread_local"):
                 self.feats, self.patch_feats = features_and_patch_inputs(self.x, sr, fps, deferred_checks=checks,
                                                                          sync_free=True)
+            self.n_launches = _cabi.launch_count - n0  # C-ABI entry points captured: every replay launches them again
             self._checks = checks
             self.peak_count = checks[0].args[0] if checks else None  # static [B, 59] interior-peak counts
 
@@ -367,6 +380,7 @@ class FeatureGraph:
             else:
                 self.x.copy_(x, non_blocking=True)
         self.graph.replay()
+        _count_replayed(self.n_launches)
         feats = self.feats.clone()
         pf = {k: v.clone() for k, v in self.patch_feats.items()}
         if self.peak_count is not None:
@@ -417,9 +431,13 @@ class RaggedFeatureGraph:
             cs.synchronize()
             self.graph = torch.cuda.CUDAGraph()
             checks = []
+            from . import _cabi
+
+            n0 = _cabi.launch_count
             with torch.cuda.graph(self.graph, stream=cs, capture_error_mode="thread_local"):
                 self.feats, self.patch_feats = features_and_patch_inputs(self.x, sr, fps, deferred_checks=checks,
                                                                          sync_free=True, lens=self.lens)
+            self.n_launches = _cabi.launch_count - n0
             self.peak_count = checks[0].args[0] if checks else None
 
     def run(self, clips, deferred_checks=None):
@@ -436,6 +454,7 @@ class RaggedFeatureGraph:
             if L < self.cap:
                 self.x[b, L:].zero_()
         self.graph.replay()
+        _count_replayed(self.n_launches)
         feats = self.feats[:n].clone()
         pf = {k: v[:n].clone() for k, v in self.patch_feats.items()}
         if self.peak_count is not None:
