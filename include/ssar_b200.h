@@ -527,6 +527,16 @@ int ssar_biquad_ss(const float* x, long long n_samples, long long stride_x, int 
                    void* stream);
 int ssar_rms_from_block_ss(const float* block_ss, long long n_blocks, int n_clips, int n_frames, float* out, void* stream);
 
+/* ssar_biquad WITHOUT caller scratch and without any allocation, for callers that cannot call cudaMalloc (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid it).  No counterpart in the reference.
+ * The scan scratch is a file-scope device array of SSAR_BIQUAD_STATIC_SCRATCH_BYTES inside the library
+ * (every GPU that loads the library holds it until exit); sizes whose ssar_biquad_scratch_bytes(n_clips, n_samples) exceeds
+ * it are rejected with SSAR_ERR_ARG (8 clips x 240 s at 24576 Hz fit).  Same kernels and results as ssar_biquad.  Every call
+ * on a GPU shares the array: calls that overlap on the GPU (different streams or threads) race; serialise them. */
+#define SSAR_BIQUAD_STATIC_SCRATCH_BYTES (16LL << 20)
+int ssar_biquad_static(const float* x, long long n_samples, long long stride_x, int n_clips, float b0, float b1, float b2,
+                       float a1, float a2, int clamp, float* y, long long stride_y, void* stream);
+
 /* TWO biquads over the SAME input in one set of passes (features/processing.py:141-150: low_pass(x) and high_pass(x), which
  * also feeds mid_pass): the input is read once per phase instead of once per filter and phase.  coeffs: HOST array of 10
  * floats (b0, b1, b2, a1, a2 of filter 0, then of filter 1).  y0 / y1: output signals or NULL; block_ss0 / block_ss1: as in

@@ -415,3 +415,60 @@ extern "C" int ssar_rms_from_block_ss(const float* block_ss, long long n_blocks,
         block_ss, n_blocks, n_frames, out);
     return ssar_launch_status("rms_from_block_ss");
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// ssar_biquad_static: ssar_biquad for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that
+// forbid cudaMalloc).  No counterpart in the reference.  The scan scratch
+// lives in a file-scope device array of SSAR_BIQUAD_STATIC_SCRATCH_BYTES (16 MiB; every GPU that loads the library holds
+// it until exit).  Every call shares the array and it keeps the last call's contents: the scan writes every word it
+// later reads, and anything that has to start from zero is cleared on the stream before the kernels; calls that overlap
+// on one GPU (two streams, two threads) race on it.
+// ---------------------------------------------------------------------------------------------------------------
+#include <mutex>
+
+namespace {
+constexpr long long STATIC_SCRATCH_BYTES = SSAR_BIQUAD_STATIC_SCRATCH_BYTES;
+static __device__ __align__(256) unsigned char g_biquad_static_scratch[STATIC_SCRATCH_BYTES];
+
+constexpr int MAX_DEVICES = 64;
+std::mutex g_static_mu;
+void* g_static_ptr[MAX_DEVICES] = {};  // device address of the array on every device, resolved once per device
+
+// In host code the array's name is a host-side stand-in, not a device address: resolve it with the device current.
+int static_scratch_ptr(void** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= MAX_DEVICES) {
+        ssar_set_error("biquad_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+        return SSAR_ERR_CUDA;
+    }
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_ptr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_biquad_static_scratch);
+        if (e != cudaSuccess || !p) {
+            ssar_set_error("biquad_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            return SSAR_ERR_CUDA;
+        }
+        g_static_ptr[dev] = p;
+    }
+    *out = g_static_ptr[dev];
+    return SSAR_OK;
+}
+}  // namespace
+
+extern "C" int ssar_biquad_static(const float* x, long long n_samples, long long stride_x, int n_clips, float b0, float b1,
+                                  float b2, float a1, float a2, int clamp, float* y, long long stride_y, void* stream) {
+    if (n_clips == 0 || n_samples == 0) return SSAR_OK;
+    SSAR_REQUIRE(x != nullptr && y != nullptr, "biquad_static: null pointer");
+    SSAR_REQUIRE(n_clips > 0 && n_samples > 0, "biquad_static: negative size");
+    const long long need = ssar_biquad_scratch_bytes(n_clips, n_samples);
+    SSAR_REQUIRE(need <= STATIC_SCRATCH_BYTES,
+                 "biquad_static: %d clips x %lld samples need %lld bytes of scratch, the static array holds %lld "
+                 "(use ssar_biquad with caller-provided scratch)", n_clips, n_samples, need, STATIC_SCRATCH_BYTES);
+    void* scratch = nullptr;
+    const int rc = static_scratch_ptr(&scratch);
+    if (rc != SSAR_OK) return rc;
+    const FilterSpec sp = {b0, b1, b2, a1, a2, y, nullptr};
+    return biquad_impl(x, n_samples, stride_x, n_clips, &sp, 1, clamp, stride_y, scratch, stream);
+}
