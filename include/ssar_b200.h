@@ -531,19 +531,29 @@ int ssar_rms_from_block_ss(const float* block_ss, long long n_blocks, int n_clip
  * graph capture, tight serving loops, harnesses that forbid it).  No counterpart in the reference.
  * The scan scratch is a file-scope device array of SSAR_BIQUAD_STATIC_SCRATCH_BYTES inside the library
  * (every GPU that loads the library holds it until exit); sizes whose ssar_biquad_scratch_bytes(n_clips, n_samples) exceeds
- * it are rejected with SSAR_ERR_ARG (8 clips x 240 s at 24576 Hz fit).  Same kernels and results as ssar_biquad.  Every call
+ * it are rejected with SSAR_ERR_ARG (the scan keeps 96 bytes per 8192-sample span: 2 MiB = 21 845 spans = 30 clips x 240 s at
+ * 24576 Hz).  Same kernel and results as ssar_biquad.  Every call
  * on a GPU shares the array: calls that overlap on the GPU (different streams or threads) race; serialise them. */
-#define SSAR_BIQUAD_STATIC_SCRATCH_BYTES (16LL << 20)
+#define SSAR_BIQUAD_STATIC_SCRATCH_BYTES (2LL << 20)
 int ssar_biquad_static(const float* x, long long n_samples, long long stride_x, int n_clips, float b0, float b1, float b2,
                        float a1, float a2, int clamp, float* y, long long stride_y, void* stream);
 
-/* TWO biquads over the SAME input in one set of passes (features/processing.py:141-150: low_pass(x) and high_pass(x), which
- * also feeds mid_pass): the input is read once per phase instead of once per filter and phase.  coeffs: HOST array of 10
+/* TWO biquads over the SAME input in one pass (features/processing.py:141-150: low_pass(x) and high_pass(x), which
+ * also feeds mid_pass): the input is read once instead of once per filter.  coeffs: HOST array of 10
  * floats (b0, b1, b2, a1, a2 of filter 0, then of filter 1).  y0 / y1: output signals or NULL; block_ss0 / block_ss1: as in
  * ssar_biquad_ss or NULL; every filter needs at least one of the two.  Same arithmetic per filter as ssar_biquad. */
 int ssar_biquad_pair(const float* x, long long n_samples, long long stride_x, int n_clips, const float* coeffs, int clamp,
                      float* y0, float* y1, long long stride_y, float* block_ss0, float* block_ss1, void* scratch,
                      void* stream);
+
+/* low_pass(x), high_pass(x) AND mid_pass(x) = low_pass(high_pass(x, 4000), 200) (features/processing.py:141-150) from ONE
+ * read of x: filters 0 and 1 run over x, filter 2 over filter 1's output (clamped when clamp != 0, as lfilter(clamp=True)
+ * returns it) without that signal leaving shared memory.  coeffs: HOST array of 15 floats (b0, b1, b2, a1, a2 per filter).
+ * y0..y2 / block_ss0..2: as in ssar_biquad_pair; filter 1 may have no output of its own.  Per filter the arithmetic inside a
+ * 32-sample chunk is ssar_biquad's; filter 2 sees filter 1's true entering state as its input history at chunk starts. */
+int ssar_biquad_chain(const float* x, long long n_samples, long long stride_x, int n_clips, const float* coeffs, int clamp,
+                      float* y0, float* y1, float* y2, long long stride_y, float* block_ss0, float* block_ss1,
+                      float* block_ss2, void* scratch, void* stream);
 
 /* rosa/constantq.py:77-100, :189-191 (__cqt_response for every octave) as ONE tensor-core launch: the response of octave
  * o is the K = 1024 contraction of the rectangular 1024-sample frames of signals[o] (hop >> o, centre reflect padding)

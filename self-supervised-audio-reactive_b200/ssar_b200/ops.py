@@ -269,7 +269,7 @@ def biquad(x: torch.Tensor, coeffs, clamp: bool = True):
     B, N = x.shape
     y = torch.empty(B, N, dtype=torch.float32, device=x.device)
     nbytes = cabi.lib().ssar_biquad_scratch_bytes(C.c_int(B), C.c_longlong(N))
-    scratch = torch.empty(max(int(nbytes), 8), dtype=torch.uint8, device=x.device)
+    scratch = torch.empty(max(int(nbytes), 16), dtype=torch.uint8, device=x.device)
     b0, b1, b2, a1, a2 = coeffs
     cabi.call("ssar_biquad", ptr(x), i64(N), i64(x.stride(0)), i32(B), f32(b0), f32(b1), f32(b2), f32(a1), f32(a2),
               i32(1 if clamp else 0), ptr(y), i64(N), ptr(scratch), nbytes=cabi.nbytes_of(x, y))
@@ -289,7 +289,7 @@ def biquad_rms(x: torch.Tensor, coeffs, clamp: bool = True, want_signal: bool = 
     y = torch.empty(B, N, dtype=torch.float32, device=x.device) if want_signal else None
     ss = torch.empty(B, n_blocks + 2, dtype=torch.float32, device=x.device)
     nbytes = cabi.lib().ssar_biquad_scratch_bytes(C.c_int(B), C.c_longlong(N))
-    scratch = torch.empty(max(int(nbytes), 8), dtype=torch.uint8, device=x.device)
+    scratch = torch.empty(max(int(nbytes), 16), dtype=torch.uint8, device=x.device)
     b0, b1, b2, a1, a2 = coeffs
     cabi.call("ssar_biquad_ss", ptr(x), i64(N), i64(x.stride(0)), i32(B), f32(b0), f32(b1), f32(b2), f32(a1), f32(a2),
               i32(1 if clamp else 0), ptr(y), i64(N), ptr(ss), ptr(scratch), nbytes=cabi.nbytes_of(x, y))
@@ -323,6 +323,41 @@ def biquad_pair(x: torch.Tensor, coeffs0, coeffs1, clamp: bool = True, want_sign
             r = torch.empty(B, T, dtype=torch.float32, device=x.device)
             cabi.call("ssar_rms_from_block_ss", ptr(ss), i64(n_blocks), i32(B), i32(T), ptr(r), nbytes=cabi.nbytes_of(ss, r))
         out.append((y, r))
+    return out
+
+
+def biquad_chain(x: torch.Tensor, coeffs0, coeffs1, coeffs2, clamp: bool = True, want_signal=(True, True, True),
+                 want_rms=(False, False, False), n_frames: int | None = None):
+    """biquad(x, coeffs0), biquad(x, coeffs1) and biquad(biquad(x, coeffs1), coeffs2) from one read of x
+    (`ssar_biquad_chain`: low / high / mid pass of features/processing.py:141-150).  -> [(y or None, rms [B, n_frames] or
+    None)] per filter; the framed RMS of all requested filters comes out of one `ssar_rms_from_block_ss` launch."""
+    x, _ = _as_batch(x)
+    B, N = x.shape
+    n_blocks = (N + 1023) // 1024
+    T = N // 1024 if n_frames is None else int(n_frames)
+    if any(want_rms) and (n_blocks < 2 or T > n_blocks):
+        raise SsarError("biquad_chain: clip too short for 2048-sample frames")
+    ys = [torch.empty(B, N, dtype=torch.float32, device=x.device) if w else None for w in want_signal]
+    n_rms = sum(bool(w) for w in want_rms)
+    ss_all = torch.empty(n_rms, B, n_blocks + 2, dtype=torch.float32, device=x.device) if n_rms else None
+    sss, k = [], 0
+    for w in want_rms:
+        sss.append(ss_all[k] if w else None)
+        k += bool(w)
+    nbytes = cabi.lib().ssar_biquad_scratch_bytes(C.c_int(B), C.c_longlong(N))
+    scratch = torch.empty(max(int(nbytes), 16), dtype=torch.uint8, device=x.device)
+    cf = (C.c_float * 15)(*[float(v) for v in (*coeffs0, *coeffs1, *coeffs2)])
+    cabi.call("ssar_biquad_chain", ptr(x), i64(N), i64(x.stride(0)), i32(B), cf, i32(1 if clamp else 0), ptr(ys[0]), ptr(ys[1]),
+              ptr(ys[2]), i64(N), ptr(sss[0]), ptr(sss[1]), ptr(sss[2]), ptr(scratch), nbytes=cabi.nbytes_of(x, *ys))
+    rms = None
+    if n_rms:
+        rms = torch.empty(n_rms, B, T, dtype=torch.float32, device=x.device)
+        cabi.call("ssar_rms_from_block_ss", ptr(ss_all), i64(n_blocks), i32(n_rms * B), i32(T), ptr(rms),
+                  nbytes=cabi.nbytes_of(ss_all, rms))
+    out, k = [], 0
+    for y, w in zip(ys, want_rms):
+        out.append((y, rms[k] if w else None))
+        k += bool(w)
     return out
 
 

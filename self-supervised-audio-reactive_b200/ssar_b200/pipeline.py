@@ -113,19 +113,20 @@ def hpss_pair(x: torch.Tensor, margin: float = 8.0, n_fft: int = 2048, hop: int 
 
 
 def band_split(x: torch.Tensor, sr):
-    """low_pass(x), mid_pass(x), high_pass(x) (features/processing.py:141-150) with three biquad passes: mid_pass is
-    literally low_pass(high_pass(x, 4000), 200), and high_pass(x, 4000) is also high_pass's default."""
+    """low_pass(x), mid_pass(x), high_pass(x) (features/processing.py:141-150) from ONE read of x: mid_pass is literally
+    low_pass(high_pass(x, 4000), 200), and high_pass(x, 4000) is also high_pass's default."""
     lo_c, hi_c = plan.biquad_coeffs("low", sr, 200), plan.biquad_coeffs("high", sr, 4000)
-    (low, _), (high, _) = ops.biquad_pair(x, lo_c, hi_c)  # the two filters of x share its passes
-    return low, ops.biquad(high, lo_c, clamp=True), high
+    (low, _), (high, _), (mid, _) = ops.biquad_chain(x, lo_c, hi_c, lo_c)
+    return low, mid, high
 
 
 def band_rms(x: torch.Tensor, sr, n_frames: int):
     """rms(low_pass(x)), rms(mid_pass(x)), rms(high_pass(x)) (frame 2048 / hop 1024) -> three [B, n_frames] tensors, from
-    the filters' own output passes: only the 4 kHz high-pass signal (the mid filter's input) is ever written."""
+    the filters' own output sweeps: no filtered signal is ever written."""
     lo_c, hi_c = plan.biquad_coeffs("low", sr, 200), plan.biquad_coeffs("high", sr, 4000)
-    (_, r_lo), (high, r_hi) = ops.biquad_pair(x, lo_c, hi_c, want_signal=(False, True), want_rms=(True, True), n_frames=n_frames)
-    return r_lo, ops.biquad_rms(high, lo_c, n_frames=n_frames), r_hi
+    (_, r_lo), (_, r_hi), (_, r_mid) = ops.biquad_chain(x, lo_c, hi_c, lo_c, want_signal=(False, False, False),
+                                                        want_rms=(True, True, True), n_frames=n_frames)
+    return r_lo, r_mid, r_hi
 
 
 def onset_pair(x: torch.Tensor, sr, hop: int = 1024, n_fft: int = 2048, want_median: bool = False, lens=None):

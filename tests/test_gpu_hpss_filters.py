@@ -135,3 +135,32 @@ def test_biquad_pair_equals_two_single_filters():
     assert torch.equal(r_lo, ops.biquad_rms(xs, lo_c, n_frames=T)) and torch.equal(r_hi, ops.biquad_rms(xs, hi_c, n_frames=T))
     (n0, r0), (y1, n1) = ops.biquad_pair(xs, lo_c, hi_c, want_signal=(False, True), want_rms=(True, False), n_frames=T)
     assert n0 is None and n1 is None and torch.equal(r0, r_lo) and torch.equal(y1, y_hi)
+
+
+def test_biquad_chain_low_high_mid_from_one_read():
+    """ssar_biquad_chain: low / high bit-equal to the single-filter launches; mid = low_pass(high_pass(x)) within 1e-6 of
+    the composed launches (its input history at chunk starts is the high-pass state, not the stored samples) and of the
+    oracle; framed RMS of all three; 70 s clips (> 32 spans: the look-back crosses group boundaries), odd length, loud
+    input (clamping between the chained filters); and the same bits on every run."""
+    from ssar_b200 import ops, plan
+
+    sr = 24576
+    xs = (torch.stack([synth_clip(sr * 70 + 4321, sr, i) for i in (3, 8)]) * 6.0).cuda()
+    lo_c, hi_c = plan.biquad_coeffs("low", sr, 200), plan.biquad_coeffs("high", sr, 4000)
+    T = xs.shape[1] // 1024
+    out = ops.biquad_chain(xs, lo_c, hi_c, lo_c, want_signal=(True, True, True), want_rms=(True, True, True), n_frames=T)
+    (y_lo, r_lo), (y_hi, r_hi), (y_mid, r_mid) = out
+    assert torch.equal(y_lo, ops.biquad(xs, lo_c)) and torch.equal(y_hi, ops.biquad(xs, hi_c))
+    assert torch.equal(r_lo, ops.biquad_rms(xs, lo_c, n_frames=T)) and torch.equal(r_hi, ops.biquad_rms(xs, hi_c, n_frames=T))
+    mid_ref = ops.biquad(y_hi, lo_c)
+    assert rel_l2(y_mid, mid_ref) < 1e-6
+    assert rel_l2(r_mid, ops.frames_rms(y_mid, 2048, 1024, T)) < 1e-6
+    assert float(y_hi.abs().max()) == 1.0  # the chained filter saw a clamped signal
+    for b in range(2):
+        assert rel_l2(y_mid[b], dsp.mid_pass(xs[b].cpu(), sr)) < TOL
+    again = ops.biquad_chain(xs, lo_c, hi_c, lo_c, want_signal=(True, True, True), want_rms=(True, True, True), n_frames=T)
+    for (a, ra), (b, rb) in zip(out, again):
+        assert torch.equal(a, b) and torch.equal(ra, rb)
+    only_rms = ops.biquad_chain(xs, lo_c, hi_c, lo_c, want_signal=(False, False, False), want_rms=(True, True, True), n_frames=T)
+    for (_, ra), (y, rb) in zip(out, only_rms):
+        assert y is None and torch.equal(ra, rb)

@@ -48,8 +48,8 @@ def test_biquad_static_rejects_sizes_beyond_the_array():
     from ssar_b200 import _cabi as cabi
 
     lib = cabi.lib()
-    n_clips, n = 16, 24576 * 240  # needs ~23 MB of scratch: over the 16 MiB array
-    assert lib.ssar_biquad_scratch_bytes(C.c_int(n_clips), C.c_longlong(n)) > (16 << 20)
+    n_clips, n = 64, 24576 * 240  # 46 080 spans x 96 bytes = 4.4 MB of scratch: over the 2 MiB array
+    assert lib.ssar_biquad_scratch_bytes(C.c_int(n_clips), C.c_longlong(n)) > (2 << 20)
     x = torch.zeros(1, 16, device="cuda")  # never touched: the size check comes first
     with pytest.raises(cabi.SsarError, match="static array holds"):
         cabi.call("ssar_biquad_static", cabi.ptr(x), cabi.i64(n), cabi.i64(n), cabi.i32(n_clips), cabi.f32(1), cabi.f32(0),
