@@ -543,8 +543,9 @@ def main():
         def results(o):
             # latents feed the generator on the device (maua StyleGAN2 wrapper); the host gets the features and a
             # per-clip fingerprint of the latents
-            return [o["feats"], o["latents"].sum(dim=(1, 2, 3))]
-        d2h_note = "features [B,5760,59] + a per-clip latent checksum out to pinned host; latents stay in HBM for the generator"
+            return [o["feats"], o["latents"][:, ::64].sum(dim=(1, 2, 3))]
+        d2h_note = ("features [B,5760,59] + a per-clip latent fingerprint (sum over every 64th frame) out to pinned host; "
+                    "latents stay in HBM for the generator")
 
     for _ in range(args.warmup):
         out = step(x)
@@ -592,14 +593,20 @@ def main():
         del probe
         streams = [torch.cuda.Stream(dev), torch.cuda.Stream(dev)]
 
+        staged = [pipeline.stage_batch(host_x, dev)] if kind == "full" else None
+
         def e2e_step(drain=True):
             if kind == "full":
-                # the public call takes the pinned host batch: it stages chunk k + 1 on a copy stream while chunk k's
-                # feature kernels run, and renders chunk k's patches meanwhile (pipeline.features_and_latents)
-                for h, r in zip(host_out, results(step(host_x))):
+                # a dataset job is software-pipelined over its batches (pipeline.stage_batch): every step starts the H2D
+                # copy of the NEXT batch from pinned host memory, then runs the public call on the batch staged one step
+                # earlier, so a step's interval holds one whole batch copy and one whole batch of compute
+                cur = staged[0]
+                staged[0] = pipeline.stage_batch(host_x, dev)
+                for h, r in zip(host_out, results(step(cur))):
                     h.copy_(r, non_blocking=True)
                 if drain:
                     torch.cuda.current_stream().synchronize()
+                    staged[0].ready.synchronize()  # the copy this step started has landed before the clock stops
                 return
             for ci, c0 in enumerate(range(0, B, chunk)):
                 s = streams[ci % 2]
@@ -620,9 +627,9 @@ def main():
         e_steps = max(2, min(args.steps, 5))
         per_step = []
         for i in range(e_steps):
-            # a dataset job does not drain the device between batches: batch k + 1's first H2D chunk is queued while batch
-            # k's last patches render and its results copy out; every batch's copies are inside the timed region and the
-            # device is drained before the clock stops
+            # a dataset job does not drain the device between batches; K batch copies (H2D) and K result copies (D2H) are
+            # issued and completed inside the timed region (the batch the first timed step computes on was staged by the
+            # last warm-up step, the copy the last timed step starts is waited for before the clock stops)
             ts = time.perf_counter()
             e2e_step(drain=(i == e_steps - 1))
             per_step.append(round((time.perf_counter() - ts) * 1e3, 2))
@@ -636,7 +643,7 @@ def main():
         e2e = {
             "value": audio_s_per_step * world * e_steps / float(td.item()), "unit": "audio-s/s",
             "h2d_bytes_per_step": B * n * 4, "d2h_bytes_per_step": sum(h.numel() * h.element_size() for h in host_out),
-            "steps": e_steps, "note": "per rank: pinned host waveforms in, " + d2h_note,
+            "steps": e_steps, "note": "per rank, software-pipelined (stage_batch: the H2D of batch k + 1 overlaps the kernels of batch k; one batch copy per step inside the timed region): pinned host waveforms in, " + d2h_note,
         }
 
     # the same end-to-end step from 16-bit PCM host buffers (the on-disk width of the audio the reference loads with
@@ -647,11 +654,16 @@ def main():
         host_pcm = torch.empty(B, n, dtype=torch.int16, pin_memory=True)
         host_pcm.copy_((x * 32767).round_().clamp_(-32768, 32767).to(torch.int16))
 
+        staged_pcm = [pipeline.stage_batch(host_pcm, dev)]
+
         def pcm_step(drain=True):
-            for h, r in zip(host_out, results(step(host_pcm))):
+            cur = staged_pcm[0]
+            staged_pcm[0] = pipeline.stage_batch(host_pcm, dev)
+            for h, r in zip(host_out, results(step(cur))):
                 h.copy_(r, non_blocking=True)
             if drain:
                 torch.cuda.current_stream().synchronize()
+                staged_pcm[0].ready.synchronize()
 
         for _ in range(3):
             pcm_step()

@@ -628,11 +628,58 @@ def _staging(device, shape, dtype):
     st = _STAGING.get(key)
     if st is None:
         with FeatureGraph._lock:
-            for k in [k for k in _STAGING if k[1] == key[1]][:-1]:  # this thread's older shapes only; their copies were
+            for k in [k for k in _STAGING if k[1] == key[1] and len(k) == 4][:-1]:  # this thread's older shapes only; their copies were
                 _STAGING.pop(k)                                     # consumed by the calls that issued them
             st = _STAGING[key] = {"buf": [torch.empty(shape, dtype=dtype, device=device) for _ in range(2)],
                                   "free": [None, None]}
     return st
+
+
+class StagedBatch:
+    """A host batch on its way to (or already in) one of two persistent device buffers: what `stage_batch` returns and
+    `features_and_latents` accepts in place of the batch."""
+
+    def __init__(self, tensor, ready, state, slot):
+        self.tensor, self.ready, self._state, self._slot = tensor, ready, state, slot
+
+    @property
+    def shape(self):
+        return self.tensor.shape
+
+    def consumed(self, stream):
+        """Called by the consumer once every kernel that reads the batch is queued on `stream`."""
+        ev = torch.cuda.Event()
+        ev.record(stream)
+        self._state["free"][self._slot] = ev
+
+
+def stage_batch(audio: torch.Tensor, device) -> StagedBatch:
+    """Start the H2D copy of a (pinned) host batch [B, N] (fp32 waveforms or int16 PCM) on the copy stream and return at
+    once.  A dataset job calls it for batch k + 1 before `features_and_latents(batch k)`: the PCIe transfer of a batch then
+    overlaps the kernels of the previous one instead of standing in front of its own (two persistent device buffers per
+    (device, thread, shape); a buffer is only overwritten after the call that consumed it has finished reading it).
+    Input staging only — there is no CPU compute path."""
+    device = torch.device(device)
+    if audio.is_cuda:
+        raise ValueError("stage_batch expects a host tensor")
+    key = (device.index, threading.get_ident(), tuple(audio.shape), audio.dtype, "batch")
+    st = _STAGING.get(key)
+    if st is None:
+        with FeatureGraph._lock:
+            for k in [k for k in _STAGING if k[1] == key[1] and k[-1] == "batch"]:
+                _STAGING.pop(k)
+            st = _STAGING[key] = {"buf": [torch.empty(audio.shape, dtype=audio.dtype, device=device) for _ in range(2)],
+                                  "free": [None, None], "next": 0}
+    slot = st["next"]
+    st["next"] = 1 - slot
+    copy_stream = _side_stream(device, "h2d")
+    with torch.cuda.device(device), torch.cuda.stream(copy_stream):
+        if st["free"][slot] is not None:
+            copy_stream.wait_event(st["free"][slot])
+        st["buf"][slot].copy_(audio, non_blocking=True)
+        ready = torch.cuda.Event()
+        ready.record(copy_stream)
+    return StagedBatch(st["buf"][slot], ready, st, slot)
 
 
 def _pool(workers: int):
@@ -661,10 +708,11 @@ def default_patch_workers(rng_device="cpu") -> int:
     return max(1, min(8, cores // share))
 
 
-def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, segmentations, tempo=120.0, seed=42,
+def features_and_latents(audio, sr, fps, palette: torch.Tensor, segmentations, tempo=120.0, seed=42,
                          rng_device="cuda", workers=None, chunk=8, serial=False):
     """The north-star unit for a batch of clips: waveforms [B, N] -> (features [B, T, 59], latents [B, T, 18, 512]).
-    audio: fp32 waveforms, or int16 PCM (converted on the device as x / 32768, exactly torchaudio.load's normalisation of
+    audio: a device or (pinned) host tensor, or the `StagedBatch` handle of `stage_batch` (a host batch whose copy was started
+    ahead of time); fp32 waveforms, or int16 PCM (converted on the device as x / 32768, exactly torchaudio.load's normalisation of
     the 16-bit files the reference reads — a host-resident batch then crosses PCIe at half the bytes).
     Tempo and segmentations are inputs (random/mir.py:28-42 is CPU librosa / scipy work outside the path).
     rng_device: where the Patch generator lives ("cpu" reproduces a CPU-seeded reference run bit for bit in its draws;
@@ -688,10 +736,15 @@ def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, se
 
     # `audio` may live in (pinned) HOST memory: the feature thread then stages it chunk by chunk on a copy stream, one
     # chunk ahead of the kernels (input staging only — there is no CPU compute path)
+    staged = audio if isinstance(audio, StagedBatch) else None
+    if staged is not None:  # `stage_batch`: the copy was started earlier; this call only waits for it in stream order
+        audio = staged.tensor
     dev = palette.device if not audio.is_cuda else audio.device
     if dev.type != "cuda":
         raise ops.SsarError("features_and_latents needs the palette (and the compute) on a CUDA device")
     stream = torch.cuda.current_stream(dev)
+    if staged is not None:
+        stream.wait_event(staged.ready)
     if str(rng_device).startswith("cuda"):
         with torch.cuda.device(dev):
             if not sampler_kernel_ready(dev, segmentations):  # fallback sampler: one CUDA graph per sub-patch count
@@ -736,6 +789,8 @@ def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, se
                     patch.bind({k: v[b - c0] for k, v in pf.items()})
                     noises[b] = patch.forward(palette, downscale_factor=4, latents_out=latents[b], palette_split=palette_split)[1]
             feats = feats_chunks[0] if len(feats_chunks) == 1 else torch.cat(feats_chunks, dim=0)
+        if staged is not None:
+            staged.consumed(stream)
         for check in checks:
             check()
         return feats, latents, noises
@@ -841,6 +896,8 @@ def features_and_latents(audio: torch.Tensor, sr, fps, palette: torch.Tensor, se
         feats = feats_chunks[0] if len(feats_chunks) == 1 else torch.cat(feats_chunks, dim=0)
     for fu in futs:
         fu.result()
+    if staged is not None:
+        staged.consumed(stream)  # (the caller's stream has waited for every chunk's feature kernels)
     for check in checks:  # error behaviour of the reference (empty peak set), read back once everything is queued
         check()
     return feats, latents, noises

@@ -122,6 +122,19 @@ def test_features_and_latents_graph_vs_serial():
     fe, le, _ = pipeline.features_and_latents(ys.cuda(), 44100, 24, palette, segs, chunk=2, serial=True)
     torch.cuda.synchronize()
     assert torch.equal(fd, fe) and torch.equal(ld, le)
+    # software-pipelined host batches (stage_batch): batch k + 1 is in flight while batch k is computed on; three batches
+    # through the two device buffers, each result compared after the buffer it read from has been re-staged
+    xp, yp = xs.cpu().pin_memory(), ys.pin_memory()
+    h0 = pipeline.stage_batch(xp, "cuda:0")
+    h1 = pipeline.stage_batch(yp, "cuda:0")
+    g0 = pipeline.features_and_latents(h0, 44100, 24, palette, segs, chunk=2)
+    h2 = pipeline.stage_batch(xp, "cuda:0")  # reuses h0's buffer: must wait for g0's kernels
+    g1 = pipeline.features_and_latents(h1, 44100, 24, palette, segs, chunk=2)
+    g2 = pipeline.features_and_latents(h2, 44100, 24, palette, segs, chunk=2)
+    torch.cuda.synchronize()
+    assert h0.tensor.data_ptr() == h2.tensor.data_ptr() != h1.tensor.data_ptr()
+    assert torch.equal(g0[0], fa) and torch.equal(g0[1], la) and torch.equal(g1[0], fe) and torch.equal(g1[1], le)
+    assert torch.equal(g2[0], fa) and torch.equal(g2[1], la)
 
 
 def test_features_and_latents_tapered_chunks():
