@@ -146,17 +146,41 @@ __global__ void __launch_bounds__(32 * WPB, CPS) frames_fft_kernel(const ssar_fr
             const bool aux = ft < aux_frames;                            // warp-uniform
             float2* z = zw + fs * ZF;
 
-            // untangle the packed real transform in place: X[k] = E + w^k O, X[M-k] = conj(E - w^k O)
-            for (int k = lane; k <= M / 2; k += 32) {
-                const float2 zk = z[k];
-                const float2 zm = z[k == 0 ? 0 : M - k];
-                const float2 w = __ldg(&tw[k]);
+            // untangle the packed real transform in place: X[k] = E + w^k O, X[M-k] = conj(E - w^k O).  A lane's bins (k and
+            // M - k, k = lane + 32 j) are touched by no other lane and no other j, so the loads of a batch of UB iterations
+            // are issued together (the compiler cannot prove that and would serialise load -> store -> load)
+            constexpr int UJ = M / 64;  // full iterations: k = lane + 32 j <= M / 2 - 1 for every lane; then k = M / 2 (lane 0)
+            constexpr int UB = 4;
+#pragma unroll
+            for (int j0 = 0; j0 < UJ; j0 += UB) {
+                float2 zk[UB], zm[UB], w[UB];
+#pragma unroll
+                for (int u = 0; u < UB; ++u) {
+                    const int k = lane + 32 * (j0 + u);
+                    zk[u] = z[k];
+                    zm[u] = z[k == 0 ? 0 : M - k];
+                    w[u] = __ldg(&tw[k]);
+                }
+#pragma unroll
+                for (int u = 0; u < UB; ++u) {
+                    const int k = lane + 32 * (j0 + u);
+                    const float2 e = make_float2(0.5f * (zk[u].x + zm[u].x), 0.5f * (zk[u].y - zm[u].y));
+                    const float2 d = make_float2(zk[u].x - zm[u].x, zk[u].y + zm[u].y);
+                    const float2 o = make_float2(0.5f * d.y, -0.5f * d.x);
+                    const float2 wo = cmul(w[u], o);
+                    z[k] = cadd(e, wo);
+                    z[M - k] = cconj(csub(e, wo));
+                }
+            }
+            static_assert(UJ % UB == 0, "untangle batches");
+            if (lane == 0) {  // k = M / 2: its own mirror
+                const float2 zk = z[M / 2], zm = zk;
+                const float2 w = __ldg(&tw[M / 2]);
                 const float2 e = make_float2(0.5f * (zk.x + zm.x), 0.5f * (zk.y - zm.y));
                 const float2 d = make_float2(zk.x - zm.x, zk.y + zm.y);
                 const float2 o = make_float2(0.5f * d.y, -0.5f * d.x);
                 const float2 wo = cmul(w, o);
-                z[k] = cadd(e, wo);
-                z[M - k] = cconj(csub(e, wo));
+                z[M / 2] = cconj(csub(e, wo));
             }
             __syncwarp();
 
@@ -219,14 +243,30 @@ __global__ void __launch_bounds__(32 * WPB, CPS) frames_fft_kernel(const ssar_fr
                             reinterpret_cast<const float4*>(fb.lane_weights) + (size_t)__ldg(fb.lane_offset4 + p) * 32 + lane;
                         const float4* pp = reinterpret_cast<const float4*>(pw + __ldg(fb.lane_start4 + b));
                         float acc = 0.f;
-#pragma unroll 4
-                        for (int k4 = 0; k4 < n4; ++k4) {
-                            const float4 wv = __ldg(w + (size_t)k4 * 32);
-                            const float4 pv = pp[k4];
-                            acc = fmaf(wv.x, pv.x, acc);
-                            acc = fmaf(wv.y, pv.y, acc);
-                            acc = fmaf(wv.z, pv.z, acc);
-                            acc = fmaf(wv.w, pv.w, acc);
+                        // weights two groups of 4 rows ahead of the sums (with ~200 KB of shared memory per CTA the L1 is
+                        // small and a weight row is an L2 hit more often than not); same order of additions
+                        constexpr int WG = 4;
+                        float4 wv[WG];
+#pragma unroll
+                        for (int u = 0; u < WG; ++u)
+                            wv[u] = u < n4 ? __ldg(w + (size_t)u * 32) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        for (int k4 = 0; k4 < n4; k4 += WG) {
+                            float4 nx[WG];
+#pragma unroll
+                            for (int u = 0; u < WG; ++u)
+                                nx[u] = k4 + WG + u < n4 ? __ldg(w + (size_t)(k4 + WG + u) * 32) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                            for (int u = 0; u < WG; ++u) {
+                                if (k4 + u < n4) {  // warp-uniform
+                                    const float4 pv = pp[k4 + u];
+                                    acc = fmaf(wv[u].x, pv.x, acc);
+                                    acc = fmaf(wv[u].y, pv.y, acc);
+                                    acc = fmaf(wv[u].z, pv.z, acc);
+                                    acc = fmaf(wv[u].w, pv.w, acc);
+                                }
+                            }
+#pragma unroll
+                            for (int u = 0; u < WG; ++u) wv[u] = nx[u];
                         }
                         if (b < fb.n_bands) {
                             fb.out[orow * fb.ld + b] = acc;

@@ -24,7 +24,9 @@ constexpr int TC_STAGES = 3;                              // palette ring
 constexpr int TC_MAX_KB = 3;                              // K <= 192 (A panel 96 KB)
 constexpr int TC_TILE_BYTES = TC_BM * TC_BK * 2;          // 16 KB: one 128 x 64 fp16 tile (A or B, hi or lo)
 constexpr int TC_THREADS = 192;
-constexpr int TC_CSTAGE_BYTES = 32 * 32 * 4;              // per epilogue warp: one [32 x 32] fp32 store tile
+constexpr int TC_CSTAGE_BYTES = 32 * 32 * 4;              // one [32 x 32] fp32 store tile
+constexpr int TC_CBUFS = 2;                               // store tiles per epilogue warp (the next chunk is staged while the
+                                                          // TMA unit still reads the previous one)
 
 // ---------------------------------------------------------------------------------------------------------------
 // operand split: fp32 -> (hi, lo) fp16, K-major, K zero-padded to KP
@@ -126,7 +128,7 @@ mix_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_cons
     uint8_t* a_panel = base;
     uint8_t* b_ring = a_panel + (size_t)TC_MAX_KB * 2 * TC_TILE_BYTES;
     uint8_t* c_stage = b_ring + (size_t)TC_STAGES * 2 * TC_TILE_BYTES;  // 4 epilogue warps x [32 rows x 128 B], swizzled
-    TcShared* sh = reinterpret_cast<TcShared*>(c_stage + 4 * TC_CSTAGE_BYTES);
+    TcShared* sh = reinterpret_cast<TcShared*>(c_stage + 4 * TC_CBUFS * TC_CSTAGE_BYTES);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m_tiles = Tpad / TC_BM;
@@ -239,7 +241,8 @@ mix_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_cons
     } else {
         // ===================================================================== epilogue warps 2..5
         const int quad = warp & 3;  // TMEM lane quadrant this warp may read
-        uint8_t* stage_buf = c_stage + (size_t)quad * TC_CSTAGE_BYTES;
+        uint8_t* stage_base = c_stage + (size_t)quad * TC_CBUFS * TC_CSTAGE_BYTES;
+        uint32_t cbuf = 0;
         const float unscale_b = 1.f / operand_scale(__ldg(amax_b));  // powers of two: exact
         uint32_t acc = 0, acc_phase = 0;
         for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
@@ -268,8 +271,11 @@ mix_gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ah, const __grid_cons
                         : "r"(taddr)
                         : "memory");
                     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                    // the previous TMA store must have finished READING the staging tile before it is rewritten
-                    if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                    // the TMA store issued TC_CBUFS chunks ago must have finished READING this staging tile before it is
+                    // rewritten (the last one may still be in flight)
+                    uint8_t* stage_buf = stage_base + (size_t)cbuf * TC_CSTAGE_BYTES;
+                    cbuf = (cbuf + 1) % TC_CBUFS;
+                    if (lane == 0) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(TC_CBUFS - 1) : "memory");
                     __syncwarp();
                     // lane = row: 32 floats = one 128-byte row of the [32 x 32] tile, 16-byte chunks XOR-swizzled by (row % 8)
                     // (the layout a SWIZZLE_128B tensor map expects; 4-way instead of 32-way bank conflicts)
@@ -423,7 +429,7 @@ extern "C" int ssar_mix_gemm_tc(const float* weights, long long ldw, long long g
         ssar_set_error("mix_gemm_tc: cuTensorMapEncodeTiled unavailable or failed");
         return SSAR_ERR_CUDA;
     }
-    const size_t smem = (size_t)(TC_MAX_KB + TC_STAGES) * 2 * TC_TILE_BYTES + 4 * TC_CSTAGE_BYTES + sizeof(TcShared) + 1024;
+    const size_t smem = (size_t)(TC_MAX_KB + TC_STAGES) * 2 * TC_TILE_BYTES + 4 * TC_CBUFS * TC_CSTAGE_BYTES + sizeof(TcShared) + 1024;
     cudaError_t e = cudaFuncSetAttribute(mix_gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) {
         ssar_set_error("mix_gemm_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
