@@ -138,6 +138,11 @@ typedef struct {
     long long sample_offset;
     long long clip_total;
     int frame_offset;
+    /* sub_every = s > 1: out_complex and out_rms are written for every s-th frame only (frame t = s u -> row u; complex has
+       ceil(n_frames / s) rows per clip, rms aux_frames / s): a transform at hop h also serves the consumer of the SAME signal's
+       transform at hop s h (rosa/pitch.py:27-83 runs its STFT at hop 512, features/audio.py:13-24 at hop 1024: frame 2 u of the
+       first is frame u of the second, bit for bit).  0 / 1 = every frame.  Not with clip_frames / time segments. */
+    int sub_every;
 } ssar_frames_args;
 
 int ssar_frames_fft(const ssar_frames_args* args, void* stream);

@@ -42,6 +42,8 @@ __global__ void __launch_bounds__(32 * WPB, CPS) frames_fft_kernel(const ssar_fr
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int h = lane / N1, n1 = lane % N1;  // frame slot inside the warp, point index inside the frame
     const int aux_frames = a.aux_frames > 0 ? a.aux_frames : a.n_frames;
+    const int sub = a.sub_every > 1 ? a.sub_every : 1;  // complex / rms rows: every sub-th frame
+    const int c_rows = (a.n_frames + sub - 1) / sub, r_rows = aux_frames / sub;
     const float2* __restrict__ tw = reinterpret_cast<const float2*>(a.twiddle);  // exp(-2 pi i k / 2M), k in [0, 2M)
 
     warp_fft_fill_twiddles<M>(twT, tw);
@@ -127,7 +129,8 @@ __global__ void __launch_bounds__(32 * WPB, CPS) frames_fft_kernel(const ssar_fr
         if (a.out_rms) {
 #pragma unroll
             for (int o = N1 / 2; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-            if (in_grid && n1 == 0 && t < aux_frames) a.out_rms[(long long)clip * aux_frames + t] = sqrtf(ss / (float)N);
+            if (in_grid && n1 == 0 && t < aux_frames && t % sub == 0)
+                a.out_rms[(long long)clip * r_rows + t / sub] = sqrtf(ss / (float)N);
         }
 
         // ------------------------------------------------------------------ per frame: untangle + epilogues, 32 lanes wide
@@ -137,7 +140,7 @@ __global__ void __launch_bounds__(32 * WPB, CPS) frames_fft_kernel(const ssar_fr
             if (ff >= total_frames) break;  // warp-uniform
             const int fclip = (int)(ff / a.n_frames);
             const int ft = (int)(ff - (long long)fclip * a.n_frames);
-            const long long crow = (long long)fclip * a.n_frames + ft;  // row of the complex output
+            const long long crow = (long long)fclip * c_rows + ft / sub;  // row of the complex output (if ft % sub == 0)
             const long long orow = (long long)fclip * aux_frames + ft;  // row of every other output
             // ragged: this clip's own frame count; its aux outputs stop (n_frames - aux_frames) frames earlier.  A frame past
             // the count carries an all-zero spectrum: it is written (zero rows) but feeds no maximum and no peak list
@@ -186,8 +189,9 @@ __global__ void __launch_bounds__(32 * WPB, CPS) frames_fft_kernel(const ssar_fr
 
             // epilogue 1: complex / power / magnitude outputs, flatness sums; the power tile goes to shared memory
             float* pw = separate_power ? pall + (size_t)(warp * FPW + fs) * (M + 4 + LANE_PAD) : reinterpret_cast<float*>(z);
-            if (a.out_complex || (need_pw && aux)) {
-                float2* oc = a.out_complex ? reinterpret_cast<float2*>(a.out_complex) + crow * a.ldc : nullptr;
+            const bool cplx = a.out_complex && ft % sub == 0;
+            if (cplx || (need_pw && aux)) {
+                float2* oc = cplx ? reinterpret_cast<float2*>(a.out_complex) + crow * a.ldc : nullptr;
                 float* os = (a.out_spec && aux) ? a.out_spec + orow * a.lds : nullptr;
                 float pj[NJ];
                 float slog = 0.f, slin = 0.f;
@@ -421,6 +425,9 @@ extern "C" int ssar_frames_fft(const ssar_frames_args* args, void* stream) {
     SSAR_REQUIRE(a.n_samples > a.n_fft / 2 || a.clip_total > 0, "frames_fft: clip shorter than n_fft/2+1 samples cannot be reflect-padded");
     SSAR_REQUIRE(a.spec_power == 1 || a.spec_power == 2 || !a.out_spec, "frames_fft: spec_power must be 1 or 2");
     SSAR_REQUIRE(a.aux_frames >= 0 && a.aux_frames <= a.n_frames, "frames_fft: aux_frames=%d outside [0, n_frames]", a.aux_frames);
+    SSAR_REQUIRE(a.sub_every >= 0 && (a.sub_every <= 1 || (!a.clip_frames && a.clip_total == 0 &&
+                                                           (a.aux_frames > 0 ? a.aux_frames : a.n_frames) % a.sub_every == 0)),
+                 "frames_fft: sub_every needs dense clips and (aux_)frames divisible by it");
     SSAR_REQUIRE(!a.pip.count || (a.pip.pitch && a.pip.mag && 0 <= a.pip.k_lo && a.pip.k_lo < a.pip.k_hi &&
                                   a.pip.k_hi <= a.n_fft / 2 + 1 &&
                                   a.pip.capacity >= ssar_piptrack_capacity(a.aux_frames > 0 ? a.aux_frames : a.n_frames, a.pip.k_lo, a.pip.k_hi)),

@@ -59,6 +59,7 @@ class FramesArgs(C.Structure):
         ("fb", Filterbank * 2), ("proj", Projection), ("aux_frames", C.c_int), ("pip", PiptrackEpilogue),
         ("clip_samples", C.c_void_p), ("clip_frames", C.c_void_p),
         ("sample_offset", C.c_longlong), ("clip_total", C.c_longlong), ("frame_offset", C.c_int),
+        ("sub_every", C.c_int),
     ]
 
 

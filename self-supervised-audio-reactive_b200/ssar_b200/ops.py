@@ -68,6 +68,7 @@ def frames_fft(
     clip_samples: torch.Tensor | None = None,
     clip_frames: torch.Tensor | None = None,
     segment: tuple | None = None,
+    sub_every: int = 1,
 ):
     """Framed real FFT + fused epilogues over a batch of clips.
 
@@ -82,6 +83,8 @@ def frames_fft(
       clip ([B, aux_frames, ...]): stft (T + 1 frames) and the last-frame-dropping features of one signal in one launch.
     segment: (sample_offset, clip_total, frame_offset) — x holds samples [sample_offset, sample_offset + N) of clips that are
       clip_total long, local frame t = the clips' frame frame_offset + t (time segments of long tracks with n_fft / 2 halos).
+    sub_every = s > 1: `complex` and `rms` hold every s-th frame only ([B, ceil(n_frames / s), F, 2] and [B, aux_frames / s]):
+      the launch then also serves the consumer of the same signal's transform at hop s * hop.
     clip_samples (int64 [B]) / clip_frames (int32 [B]): RAGGED batch — clip b holds clip_samples[b] <= N samples and
       produces clip_frames[b] <= n_frames frames; rows past a clip's count are zeros in every output.
     """
@@ -113,8 +116,11 @@ def frames_fft(
     if aux_frames is not None and int(aux_frames) != n_frames:
         a.aux_frames = int(aux_frames)
         n_frames = int(aux_frames)  # every allocation below except the complex spectrum
+    sub = max(1, int(sub_every))
+    if sub > 1:
+        a.sub_every = sub
     if want_complex:
-        out["complex"] = torch.empty(B, n_cplx, F, 2, dtype=torch.float32, device=dev)
+        out["complex"] = torch.empty(B, -(-n_cplx // sub), F, 2, dtype=torch.float32, device=dev)
         a.out_complex = out["complex"].data_ptr()
         a.ldc = F
     if spec_power is not None:
@@ -123,7 +129,7 @@ def frames_fft(
         a.lds = F
         a.spec_power = int(spec_power)
     if want_rms:
-        out["rms"] = torch.empty(B, n_frames, dtype=torch.float32, device=dev)
+        out["rms"] = torch.empty(B, n_frames // sub, dtype=torch.float32, device=dev)
         a.out_rms = out["rms"].data_ptr()
     if want_flatness:
         out["flatness"] = torch.empty(B, n_frames, dtype=torch.float32, device=dev)
@@ -593,9 +599,13 @@ FUSED_PIPTRACK = True  # piptrack as an epilogue of the hop n_fft/4 transform (F
 
 
 def estimate_tuning(y: torch.Tensor, sr, n_fft: int = 2048, bins_per_octave: int = 12, threshold: float = 0.1,
-                    fmin: float = 150.0, fmax: float = 4000.0, lens=None):
+                    fmin: float = 150.0, fmax: float = 4000.0, lens=None, stft_out: dict | None = None):
     """rosa/pitch.py:9-24 for a batch [B, N] -> (tuning_idx int32 [B] in [0, 100], tuning_val fp32 [B]).
-    lens: `ragged.ClipLengths` of a ragged batch (n_fft 2048 only)."""
+    lens: `ragged.ClipLengths` of a ragged batch (n_fft 2048 only).
+    stft_out: a dict that receives by-products of the SAME launch (dense batches, fused epilogue only): the pitch tracker's
+    transform runs at hop n_fft / 4, so every 2nd frame is a frame of stft(y, n_fft, hop n_fft / 2) (rosa/spectral.py:10-21) —
+    "complex" [B, N // (n_fft / 2) + 1, F, 2] and "rms" [B, N // (n_fft / 2)] (features/audio.py:31-37), bit-equal to a
+    frames_fft launch at hop n_fft / 2 with want_complex / want_rms."""
     y, _ = _as_batch(y)
     B, N = y.shape
     hop = n_fft // 4  # hop_length=None reaches torch.stft's default through rosa/spectral.py:59-62
@@ -604,7 +614,13 @@ def estimate_tuning(y: torch.Tensor, sr, n_fft: int = 2048, bins_per_octave: int
     if FUSED_PIPTRACK and n_fft in (1024, 2048):
         # the peak picking runs in the transform's epilogue: the [frames, 1025] magnitudes never reach HBM
         rag = dict(clip_samples=lens.n, clip_frames=lens.P) if lens is not None else {}
-        o = frames_fft(y, n_fft, hop, T, torch.hann_window, piptrack=dict(k_lo=k_lo, k_hi=k_hi, threshold=threshold, sr=sr), **rag)
+        if stft_out is not None and lens is None and T % 2 == 0:
+            # frames 0 .. T of the hop n_fft / 4 grid (one more than the tracker looks at): complex / rms rows = even frames
+            o = frames_fft(y, n_fft, hop, T + 1, torch.hann_window, want_complex=True, want_rms=True, aux_frames=T, sub_every=2,
+                           piptrack=dict(k_lo=k_lo, k_hi=k_hi, threshold=threshold, sr=sr))
+            stft_out["complex"], stft_out["rms"] = o["complex"], o["rms"]
+        else:
+            o = frames_fft(y, n_fft, hop, T, torch.hann_window, piptrack=dict(k_lo=k_lo, k_hi=k_hi, threshold=threshold, sr=sr), **rag)
         pitch, mag, count = o["pip_pitch"], o["pip_mag"], o["pip_count"]
         cap = pitch.shape[1]
     else:

@@ -150,10 +150,14 @@ MIR_GROUPS = (("chromagram", 12), ("tonnetz", 6), ("mfcc", 20), ("spectral_contr
               ("rms", 1), ("drop_strength", 1), ("onsets", 1))
 
 
-def _cens_and_tonnetz(y: torch.Tensor, sr, hop: int, sync_free: bool, lens=None):
+def _cens_and_tonnetz(y: torch.Tensor, sr, hop: int, sync_free: bool, lens=None, stft_out=None):
     """chroma_cens(y, sr).T and the tonnetz of it (rosa/spectral.py:239-280, features/audio.py:48-57) -> [B, T, 12], [B, T, 6].
-    The tuning is estimated from `y` itself (chroma_cqt's tuning=None)."""
-    C = ops.cqt(y, sr, hop, sync_free=sync_free, lens=lens)
+    The tuning is estimated from `y` itself (chroma_cqt's tuning=None).  stft_out: see ops.estimate_tuning (the pitch tracker's
+    launch can hand out stft(y, 2048, 1024) and rms(y) as by-products)."""
+    idx = None
+    if stft_out is not None:
+        idx, _ = ops.estimate_tuning(y, sr, bins_per_octave=plan.CQT_BINS_PER_OCTAVE, lens=lens, stft_out=stft_out)
+    C = ops.cqt(y, sr, hop, tuning_idx=idx, sync_free=sync_free, lens=lens)
     cens = ops.cens_smooth(ops.chroma_from_cqt(C, quantize=True), plan.cens_window(41, str(y.device)), l2=True,
                            clip_frames=lens.T if lens is not None else None)
     return cens, ops.tonnetz(cens)
@@ -200,15 +204,19 @@ def feature_chain(x: torch.Tensor, sr, want_a2f: bool = True, want_mir: bool = F
 
     out = {}
     cens1 = ton1 = None
+    harm_stft = {} if (want_mir and want_a2f and lens is None and n_fft == 2 * hop) else None
     if want_mir:
-        cens1, ton1 = _cens_and_tonnetz(harm, sr, hop, sync_free, lens)  # chromagram(audio), tonnetz(audio)
+        cens1, ton1 = _cens_and_tonnetz(harm, sr, hop, sync_free, lens, stft_out=harm_stft)  # chromagram(audio), tonnetz(audio)
     if want_a2f or want_mir:
         rms_x_bands = band_rms(x, sr, T) if want_a2f else ()
         rms_a = torch.stack([fa["rms"], *rms_x_bands], dim=-1)  # [B, T, 4] (or [B, T, 1])
         drop = ops.emphasize(ops.gauss1d(rms_a, 10, "circular", batched=True, clip_frames=cf), 10, 50, clip_frames=cf)
     if want_a2f:
         # harmonic(audio_harm): features/audio.py:44-45 applied to data.py:68-69's argument; the same launch gives rms(harm)
-        fh = ops.frames_fft(harm, n_fft, hop, T + 1, torch.hann_window, want_complex=True, want_rms=True, aux_frames=T, **rag1)
+        if harm_stft:  # the tuning estimate of `harm` above ran its STFT at hop 512: its even frames are this transform
+            fh = harm_stft
+        else:
+            fh = ops.frames_fft(harm, n_fft, hop, T + 1, torch.hann_window, want_complex=True, want_rms=True, aux_frames=T, **rag1)
         harm2 = hpss_pair(harm, D=fh["complex"], want_perc=False, lens=lens)[0]
         del fh["complex"]
         cens, ton = _cens_and_tonnetz(harm2, sr, hop, sync_free, lens)

@@ -174,3 +174,24 @@ def test_time_segments_with_halos_equal_whole_track():
         torch.cuda.synchronize()
         for k in ("spec", "mel", "onset", "rms"):
             assert torch.equal(seg[k], whole[k]), (seg_frames, k, rel_l2(seg[k], whole[k]))
+
+
+def test_sub_every_hop512_launch_serves_hop1024_consumers():
+    """A transform at hop 512 with sub_every = 2 hands out the even frames' complex spectrum and RMS: bit-equal to the hop 1024
+    launch (rosa/spectral.py:10-21, features/audio.py:31-37), and ops.estimate_tuning's by-products are those tensors while
+    its tuning is unchanged."""
+    from ssar_b200 import ops
+
+    sr, n = 24576, 24576 * 11
+    xs = torch.stack([synth_clip(n, sr, i) for i in (2, 5, 7)]).cuda()
+    T = n // 1024
+    ref = ops.frames_fft(xs, 2048, 1024, T + 1, torch.hann_window, want_complex=True, want_rms=True, aux_frames=T)
+    got = ops.frames_fft(xs, 2048, 512, 2 * T + 1, torch.hann_window, want_complex=True, want_rms=True, aux_frames=2 * T,
+                         sub_every=2)
+    assert got["complex"].shape == ref["complex"].shape and torch.equal(got["complex"], ref["complex"])
+    assert got["rms"].shape == ref["rms"].shape and torch.equal(got["rms"], ref["rms"])
+    by = {}
+    i1, v1 = ops.estimate_tuning(xs, sr, bins_per_octave=36, stft_out=by)
+    i0, v0 = ops.estimate_tuning(xs, sr, bins_per_octave=36)
+    assert torch.equal(i0, i1) and torch.equal(v0, v1)
+    assert torch.equal(by["complex"], ref["complex"]) and torch.equal(by["rms"], ref["rms"])
