@@ -725,14 +725,14 @@ def main():
         }
         roof["frac"] = roof["achieved"] / peak if roof["achieved"] else None
         # DRAM traffic of the dominant kernel from the committed ncu --set full captures (dram__bytes_read + write summed
-        # over its launches of one 8-clip chunk, scaled to this run's clip count): profiles/r02_ncu_sel_v1.md (full: the 9
-        # frames_fft launches of a chunk move 2.616 GB) and profiles/r01_frames_fft_v1.md (cfg2: 2.316 GB per 16 clips)
-        ncu_bytes_per_clip = {"full": 2.616e9 / 8, "cfg2": 2.3160e9 / 16}
+        # over its launches of one 8-clip chunk, scaled to this run's clip count): profiles/r02_ncu_sel_v2.md (full: the 8
+        # frames_fft launches of a chunk move 2.396 GB) and profiles/r01_frames_fft_v1.md (cfg2: 2.316 GB per 16 clips)
+        ncu_bytes_per_clip = {"full": 2.396e9 / 8, "cfg2": 2.3160e9 / 16}
         if name == "ssar_frames_fft":
             roof["traffic_per_step"] = ncu_bytes_per_clip[kind] * B
             roof["traffic"] = roof["traffic_per_step"] / max(k_n / args.steps, 1)  # per launch, like `achieved`
             roof["algorithmic_bytes_per_launch"] = k_bytes / max(k_n, 1)
-            roof["traffic_source"] = ("ncu --set full capture of the same kernels (profiles/r02_ncu_sel_v1.md), average per launch"
+            roof["traffic_source"] = ("ncu --set full capture of the same kernels (profiles/r02_ncu_sel_v2.md), average per launch"
                                       if kind == "full" else "ncu capture profiles/r01_frames_fft_v1.md, average per launch")
         cpu = None
         if world == 1 and not args.no_cpu:
