@@ -599,13 +599,17 @@ FUSED_PIPTRACK = True  # piptrack as an epilogue of the hop n_fft/4 transform (F
 
 
 def estimate_tuning(y: torch.Tensor, sr, n_fft: int = 2048, bins_per_octave: int = 12, threshold: float = 0.1,
-                    fmin: float = 150.0, fmax: float = 4000.0, lens=None, stft_out: dict | None = None):
+                    fmin: float = 150.0, fmax: float = 4000.0, lens=None, stft_out: dict | None = None,
+                    defer: list | None = None):
     """rosa/pitch.py:9-24 for a batch [B, N] -> (tuning_idx int32 [B] in [0, 100], tuning_val fp32 [B]).
     lens: `ragged.ClipLengths` of a ragged batch (n_fft 2048 only).
     stft_out: a dict that receives by-products of the SAME launch (dense batches, fused epilogue only): the pitch tracker's
     transform runs at hop n_fft / 4, so every 2nd frame is a frame of stft(y, n_fft, hop n_fft / 2) (rosa/spectral.py:10-21) —
     "complex" [B, N // (n_fft / 2) + 1, F, 2] and "rms" [B, N // (n_fft / 2)] (features/audio.py:31-37), bit-equal to a
-    frames_fft launch at hop n_fft / 2 with want_complex / want_rms."""
+    frames_fft launch at hop n_fft / 2 with want_complex / want_rms.
+    defer: a list -> the statistics kernel (`ssar_tuning_from_peaks`: one CTA per clip, latency-bound) is queued on a side
+    stream and a zero-argument `join` is appended to the list; the caller runs work that does not need the tuning (the
+    CQT's octave decimations) and calls join() before the first consumer of tuning_idx."""
     y, _ = _as_batch(y)
     B, N = y.shape
     hop = n_fft // 4  # hop_length=None reaches torch.stft's default through rosa/spectral.py:59-62
@@ -636,9 +640,38 @@ def estimate_tuning(y: torch.Tensor, sr, n_fft: int = 2048, bins_per_octave: int
     idx = torch.empty(B, dtype=torch.int32, device=y.device)
     val = torch.empty(B, dtype=torch.float32, device=y.device)
     edges = plan.tuning_edges(str(y.device))
-    cabi.call("ssar_tuning_from_peaks", ptr(pitch), ptr(mag), i32(B), i64(cap), ptr(count), ptr(edges),
-              i32(edges.numel() - 1), f32(float(bins_per_octave)), ptr(idx), ptr(val))
+    def launch():
+        cabi.call("ssar_tuning_from_peaks", ptr(pitch), ptr(mag), i32(B), i64(cap), ptr(count), ptr(edges),
+                  i32(edges.numel() - 1), f32(float(bins_per_octave)), ptr(idx), ptr(val))
+
+    if defer is None:
+        launch()
+    else:
+        main = torch.cuda.current_stream(y.device)
+        side = _tuning_stream(y.device)
+        side.wait_stream(main)
+        with torch.cuda.stream(side):
+            launch()
+        keep = (pitch, mag, count, edges, idx, val)  # the peak lists stay allocated until the side kernel has been joined
+
+        def join(_keep=keep):
+            main.wait_stream(side)
+
+        defer.append(join)
     return idx, val
+
+
+_TUNING_STREAMS = {}
+
+
+def _tuning_stream(device):
+    import threading
+
+    key = (torch.device(device).index, threading.get_ident())
+    st = _TUNING_STREAMS.get(key)
+    if st is None:
+        st = _TUNING_STREAMS[key] = torch.cuda.Stream(device)
+    return st
 
 
 def chroma_from_cqt(C_fm: torch.Tensor, bins_per_octave: int = 36, n_chroma: int = 12, quantize: bool = False):
@@ -678,7 +711,8 @@ def tonnetz(chroma: torch.Tensor):
 USE_TENSOR_CORE_CQT = True  # False: per-octave FFT + banded frequency-domain projection (frames_fft epilogue)
 
 
-def cqt(y: torch.Tensor, sr, hop_length: int = 1024, tuning_idx=None, sync_free: bool = False, tensor_core=None, lens=None):
+def cqt(y: torch.Tensor, sr, hop_length: int = 1024, tuning_idx=None, sync_free: bool = False, tensor_core=None, lens=None,
+        join=None):
     """rosa/constantq.py:13-115 for the reference's only configuration (C1, 7 octaves x 36 bins, filter_scale 1,
     sparsity 0.01): returns the frame-major complex-as-real CQT [B, T, 252, 2] with 1/sqrt(length) applied.
     tuning_idx: int32 [B] from estimate_tuning (None -> estimate, like tuning=None in chroma_cqt)."""
@@ -690,12 +724,15 @@ def cqt(y: torch.Tensor, sr, hop_length: int = 1024, tuning_idx=None, sync_free:
             n_oct - 1, n_oct))
     if float(sr) / (1 << (n_oct - 1)) != int(float(sr) / (1 << (n_oct - 1))):
         raise ValueError("Frequencies must be of integer type to ensure quality resampling computation.")
-    if tuning_idx is None:
-        tuning_idx, _ = estimate_tuning(y, sr, bins_per_octave=bpo, lens=lens)
     use_tc = USE_TENSOR_CORE_CQT if tensor_core is None else bool(tensor_core)
     use_tc = use_tc and hop_length % (8 << (n_oct - 1)) == 0 and N >= (plan.CQT_N_FFT << (n_oct - 1))
+    join = list(join) if join else []  # pending `estimate_tuning(defer=...)` joins of a tuning_idx the caller passed in
+    if tuning_idx is None:
+        tuning_idx, _ = estimate_tuning(y, sr, bins_per_octave=bpo, lens=lens, defer=join if use_tc else None)
     if use_tc:
-        return _cqt_tensor_core(y, sr, hop_length, tuning_idx, lens)
+        return _cqt_tensor_core(y, sr, hop_length, tuning_idx, lens, join)
+    for j in join:
+        j()
     if lens is not None:
         raise SsarError("cqt: ragged batches run on the tensor-core path only (hop a multiple of 512, clips >= 65 536 samples)")
     tables = plan.cqt_tables(float(sr), str(y.device))
@@ -722,7 +759,7 @@ def cqt(y: torch.Tensor, sr, hop_length: int = 1024, tuning_idx=None, sync_free:
     return out
 
 
-def _cqt_tensor_core(y: torch.Tensor, sr, hop_length: int, tuning_idx: torch.Tensor, lens=None):
+def _cqt_tensor_core(y: torch.Tensor, sr, hop_length: int, tuning_idx: torch.Tensor, lens=None, join=()):
     """The 7 octave responses as ONE tcgen05 launch (`ssar_cqt_tc`): time-domain contraction of the overlapping frames
     (TMA tensor maps with row stride hop_i over the reflect-padded fp16 hi / lo signals) with the tuned basis.  Each
     clip's basis is picked on the device by its tuning index: no read-back, graph-capturable."""
@@ -742,6 +779,8 @@ def _cqt_tensor_core(y: torch.Tensor, sr, hop_length: int, tuning_idx: torch.Ten
     fn = cabi.lib().ssar_cqt_tc_scratch_bytes
     fn.restype = C.c_longlong
     scratch = torch.empty(int(fn(i32(B), ns, i32(n_oct))), dtype=torch.uint8, device=y.device)
+    for j in join:  # the tuning statistics ran on a side stream next to the decimations above
+        j()
     slots = tuning_idx.to(torch.int32).contiguous()
     cabi.call("ssar_cqt_tc", ps, ns, i32(n_oct), i32(B), i32(hop_length), i32(T), ptr(tb.basis_hi), ptr(tb.basis_lo),
               i32(tb.n_slots), ptr(slots), ptr(tb.row_scale), i64(n_bins), f32(tb.SCALE), ptr(scratch), ptr(out),

@@ -154,10 +154,10 @@ def _cens_and_tonnetz(y: torch.Tensor, sr, hop: int, sync_free: bool, lens=None,
     """chroma_cens(y, sr).T and the tonnetz of it (rosa/spectral.py:239-280, features/audio.py:48-57) -> [B, T, 12], [B, T, 6].
     The tuning is estimated from `y` itself (chroma_cqt's tuning=None).  stft_out: see ops.estimate_tuning (the pitch tracker's
     launch can hand out stft(y, 2048, 1024) and rms(y) as by-products)."""
-    idx = None
+    idx, join = None, []
     if stft_out is not None:
-        idx, _ = ops.estimate_tuning(y, sr, bins_per_octave=plan.CQT_BINS_PER_OCTAVE, lens=lens, stft_out=stft_out)
-    C = ops.cqt(y, sr, hop, tuning_idx=idx, sync_free=sync_free, lens=lens)
+        idx, _ = ops.estimate_tuning(y, sr, bins_per_octave=plan.CQT_BINS_PER_OCTAVE, lens=lens, stft_out=stft_out, defer=join)
+    C = ops.cqt(y, sr, hop, tuning_idx=idx, sync_free=sync_free, lens=lens, join=join)
     cens = ops.cens_smooth(ops.chroma_from_cqt(C, quantize=True), plan.cens_window(41, str(y.device)), l2=True,
                            clip_frames=lens.T if lens is not None else None)
     return cens, ops.tonnetz(cens)
