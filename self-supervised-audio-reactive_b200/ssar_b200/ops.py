@@ -243,7 +243,7 @@ def hpss(stft_fm: torch.Tensor, margin: float = 1.0, want_harm: bool = True, wan
 
 
 def istft(spec_fm: torch.Tensor, n_fft: int, hop: int, window=torch.hann_window, length: int | None = None,
-          clip_frames=None, clip_len=None):
+          clip_frames=None, clip_len=None, out: torch.Tensor | None = None):
     """spec_fm: frame-major complex [B, T1, F, 2] -> waveform [B, length] (torch.istft semantics, center=True).
     clip_frames (int32 [B]) / clip_len (int64 [B]): ragged batch (per-clip frame counts and output lengths)."""
     B, T1, F, _ = spec_fm.shape
@@ -255,11 +255,16 @@ def istft(spec_fm: torch.Tensor, n_fft: int, hop: int, window=torch.hann_window,
     win = plan.window_tensor(window, n_fft, dev)
     if n_fft == 2048 and hop == 1024 and (length % 2 == 0 or B == 1):  # the HPSS case: fused transform + overlap-add
         # (rows must start 8-byte aligned: an even length, or a single clip)
-        out = torch.empty(B, length, dtype=torch.float32, device=dev)
+        if out is None:
+            out = torch.empty(B, length, dtype=torch.float32, device=dev)
+        elif tuple(out.shape) != (B, length) or not out.is_contiguous() or out.dtype != torch.float32:
+            raise SsarError("istft: out must be a contiguous fp32 [B, length] tensor")
         cabi.call("ssar_istft_half_overlap", ptr(spec_fm), i64(F), i32(B), i32(T1), i32(n_fft), ptr(win),
                   ptr(plan.twiddle(n_fft, str(dev))), i64(length), ptr(out), ptr(clip_frames), ptr(clip_len),
                   nbytes=cabi.nbytes_of(spec_fm, out))
         return out
+    if out is not None:
+        raise SsarError("istft: out= is only supported on the fused n_fft 2048 / hop 1024 path")
     frames = torch.empty(B, T1, n_fft, dtype=torch.float32, device=dev)
     cabi.call("ssar_irfft_frames", ptr(spec_fm), i64(F), i32(B), i32(T1), i32(n_fft), ptr(win),
               ptr(plan.twiddle(n_fft, str(dev))), ptr(frames), nbytes=cabi.nbytes_of(spec_fm, frames))
@@ -333,7 +338,7 @@ def biquad_pair(x: torch.Tensor, coeffs0, coeffs1, clamp: bool = True, want_sign
 
 
 def biquad_chain(x: torch.Tensor, coeffs0, coeffs1, coeffs2, clamp: bool = True, want_signal=(True, True, True),
-                 want_rms=(False, False, False), n_frames: int | None = None):
+                 want_rms=(False, False, False), n_frames: int | None = None, outs=None):
     """biquad(x, coeffs0), biquad(x, coeffs1) and biquad(biquad(x, coeffs1), coeffs2) from one read of x
     (`ssar_biquad_chain`: low / high / mid pass of features/processing.py:141-150).  -> [(y or None, rms [B, n_frames] or
     None)] per filter; the framed RMS of all requested filters comes out of one `ssar_rms_from_block_ss` launch."""
@@ -343,7 +348,13 @@ def biquad_chain(x: torch.Tensor, coeffs0, coeffs1, coeffs2, clamp: bool = True,
     T = N // 1024 if n_frames is None else int(n_frames)
     if any(want_rms) and (n_blocks < 2 or T > n_blocks):
         raise SsarError("biquad_chain: clip too short for 2048-sample frames")
-    ys = [torch.empty(B, N, dtype=torch.float32, device=x.device) if w else None for w in want_signal]
+    if outs is not None:  # caller-provided contiguous [B, N] signals (e.g. rows of one stacked buffer)
+        for o in outs:
+            if o is not None and (tuple(o.shape) != (B, N) or not o.is_contiguous() or o.dtype != torch.float32):
+                raise SsarError("biquad_chain: outs must be contiguous fp32 [B, N] tensors")
+        ys = list(outs)
+    else:
+        ys = [torch.empty(B, N, dtype=torch.float32, device=x.device) if w else None for w in want_signal]
     n_rms = sum(bool(w) for w in want_rms)
     ss_all = torch.empty(n_rms, B, n_blocks + 2, dtype=torch.float32, device=x.device) if n_rms else None
     sss, k = [], 0

@@ -98,7 +98,7 @@ def spectral_frontend_segmented(x: torch.Tensor, sr, n_fft: int = 2048, hop: int
 
 
 def hpss_pair(x: torch.Tensor, margin: float = 8.0, n_fft: int = 2048, hop: int = 1024, D=None, want_harm=True,
-              want_perc=True, lens=None):
+              want_perc=True, lens=None, perc_out=None):
     """harmonic(x), percussive(x) (features/audio.py:13-24) from ONE forward STFT and ONE pair of median passes.
     x [B, N] -> (harm [B, N], perc [B, N]) (None for a part that is not wanted).  Exact: the two reference calls differ
     only in the mask applied."""
@@ -109,7 +109,7 @@ def hpss_pair(x: torch.Tensor, margin: float = 8.0, n_fft: int = 2048, hop: int 
     h, p = ops.hpss(D, margin, want_harm, want_perc, clip_frames=lens.T1 if lens is not None else None)
     irag = dict(clip_frames=lens.T1, clip_len=lens.n) if lens is not None else {}
     return (ops.istft(h, n_fft, hop, torch.hann_window, n, **irag) if want_harm else None,
-            ops.istft(p, n_fft, hop, torch.hann_window, n, **irag) if want_perc else None)
+            ops.istft(p, n_fft, hop, torch.hann_window, n, out=perc_out, **irag) if want_perc else None)
 
 
 def band_split(x: torch.Tensor, sr):
@@ -196,9 +196,23 @@ def feature_chain(x: torch.Tensor, sr, want_a2f: bool = True, want_mir: bool = F
     flatness = fa["flatness"]
 
     # --- harmonic / percussive separation
-    harm, perc = hpss_pair(x, D=fa["complex"], lens=lens)
+    # a2f, dense batch: the percussive part and its three band signals sit in ONE [4, B, N] buffer, so their onset
+    # envelopes (supervised/data.py:70-88) come out of one transform launch and one flux launch over 4 B rows
+    pstack = torch.empty(4, B, N, dtype=torch.float32, device=x.device) if (want_a2f and lens is None and N % 2 == 0) else None
+    harm, perc = hpss_pair(x, D=fa["complex"], lens=lens, perc_out=pstack[0] if pstack is not None else None)
     del fa["complex"], fa["spec"]
-    on, on_med = onset_pair(perc, sr, hop, n_fft, want_median=want_a2f and pulse_of == "perc", lens=lens)
+    if pstack is not None:
+        lo_c, hi_c = plan.biquad_coeffs("low", sr, 200), plan.biquad_coeffs("high", sr, 4000)
+        ops.biquad_chain(perc, lo_c, hi_c, lo_c, outs=(pstack[1], pstack[3], pstack[2]))  # rows: perc, low, mid, high
+        bank = plan.mel_bank(float(sr), n_fft, 128, 0.0, 11025.0, dev)
+        pm = ops.frames_fft(pstack.view(4 * B, N), n_fft, hop, T, torch.hann_window, banks=[(bank, True, True)])
+        pad = 1 + n_fft // (2 * hop)
+        on4 = ops.onset_flux(pm["bank0"], pm["bank0_max"], pad, "mean").view(4, B, T)
+        on, on_lo, on_mid, on_hi = on4[0], on4[1], on4[2], on4[3]
+        on_med = ops.onset_flux(pm["bank0"][:B], pm["bank0_max"][:B], pad, "median") if pulse_of == "perc" else None
+        del pm
+    else:
+        on, on_med = onset_pair(perc, sr, hop, n_fft, want_median=want_a2f and pulse_of == "perc", lens=lens)
     if want_a2f and pulse_of != "perc":
         on_med = onset_pair(x, sr, hop, n_fft, want_median=True, lens=lens)[1]
 
@@ -221,8 +235,9 @@ def feature_chain(x: torch.Tensor, sr, want_a2f: bool = True, want_mir: bool = F
         del fh["complex"]
         cens, ton = _cens_and_tonnetz(harm2, sr, hop, sync_free, lens)
         # onset envelopes of the percussive part's three bands; pulse
-        p_lo, p_mid, p_hi = band_split(perc, sr)
-        on_lo, on_mid, on_hi = (onset_pair(b, sr, hop, n_fft, lens=lens)[0] for b in (p_lo, p_mid, p_hi))
+        if pstack is None:
+            p_lo, p_mid, p_hi = band_split(perc, sr)
+            on_lo, on_mid, on_hi = (onset_pair(b, sr, hop, n_fft, lens=lens)[0] for b in (p_lo, p_mid, p_hi))
         pulse = ops.plp_from_onset(on_med, sr, hop, lens=lens)
         # band signals of harm / x are only ever looked at through their RMS: taken from the filters' output passes
         rms_h = [fh["rms"], *band_rms(harm, sr, T)]
