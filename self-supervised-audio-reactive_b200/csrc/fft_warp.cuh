@@ -67,9 +67,11 @@ __device__ __forceinline__ void fft_dif_regs(float2 (&v)[N]) {
         for (int blk = 0; blk < N; blk += len) {
 #pragma unroll
             for (int j = 0; j < half; ++j) {
+                // (re, im) pairs add as ONE packed FADD2 (sm_100; IEEE round-to-nearest per component: the same bits as two
+                // FADDs, half the issue slots)
                 const float2 a = v[blk + j], b = v[blk + j + half];
-                v[blk + j] = cadd(a, b);
-                v[blk + j + half] = mul_w32<INV>(csub(a, b), j * (32 / len));
+                v[blk + j] = __fadd2_rn(a, b);
+                v[blk + j + half] = mul_w32<INV>(__fadd2_rn(a, make_float2(-b.x, -b.y)), j * (32 / len));
             }
         }
     }

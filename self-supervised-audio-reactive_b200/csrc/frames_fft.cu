@@ -112,9 +112,7 @@ __global__ void __launch_bounds__(32 * WPB, CPS) frames_fft_kernel(const ssar_fr
                 const float2* wp = reinterpret_cast<const float2*>(wins);
 #pragma unroll
                 for (int r = 0; r < 32; ++r) {
-                    const float2 w = wp[n1 + N1 * r];
-                    v[r].x *= w.x;
-                    v[r].y *= w.y;
+                    v[r] = __fmul2_rn(v[r], wp[n1 + N1 * r]);  // packed: same bits as two FMULs
                 }
             }
         } else {
@@ -167,12 +165,14 @@ __global__ void __launch_bounds__(32 * WPB, CPS) frames_fft_kernel(const ssar_fr
 #pragma unroll
                 for (int u = 0; u < UB; ++u) {
                     const int k = lane + 32 * (j0 + u);
-                    const float2 e = make_float2(0.5f * (zk[u].x + zm[u].x), 0.5f * (zk[u].y - zm[u].y));
-                    const float2 d = make_float2(zk[u].x - zm[u].x, zk[u].y + zm[u].y);
+                    // packed (re, im) arithmetic where both components take the same operation; same bits as the scalar form
+                    const float2 zc = make_float2(zm[u].x, -zm[u].y);  // conj(Z[M - k])
+                    const float2 e = __fmul2_rn(make_float2(0.5f, 0.5f), __fadd2_rn(zk[u], zc));
+                    const float2 d = __fadd2_rn(zk[u], make_float2(-zc.x, -zc.y));
                     const float2 o = make_float2(0.5f * d.y, -0.5f * d.x);
                     const float2 wo = cmul(w[u], o);
-                    z[k] = cadd(e, wo);
-                    z[M - k] = cconj(csub(e, wo));
+                    z[k] = __fadd2_rn(e, wo);
+                    z[M - k] = cconj(__fadd2_rn(e, make_float2(-wo.x, -wo.y)));
                 }
             }
             static_assert(UJ % UB == 0, "untangle batches");
