@@ -17,21 +17,42 @@ namespace {
 // inverse untangle of one frame into the warp's natural-order buffer: z[k] = conj(Z[k]) with Z = E + iO,
 // E = (X[k] + conj(X[M-k]))/2, O = conj(w^k) (X[k] - conj(X[M-k]))/2; imaginary parts of DC / Nyquist ignored (C2R)
 template <int M>
+__device__ __forceinline__ void inverse_untangle_one(float2 xk, float2 xm, float2 w, int k, float2* z) {
+    if (k == 0) {
+        xk.y = 0.f;
+        xm.y = 0.f;
+    }
+    const float2 e = make_float2(0.5f * (xk.x + xm.x), 0.5f * (xk.y - xm.y));
+    const float2 d = make_float2(0.5f * (xk.x - xm.x), 0.5f * (xk.y + xm.y));
+    const float2 o = cmul(cconj(w), d);
+    z[k] = make_float2(e.x - o.y, -(e.y + o.x));            // conj(Z[k])
+    if (k > 0) z[M - k] = make_float2(e.x + o.y, e.y - o.x);  // conj(Z[M-k])
+}
+
+template <int M>
 __device__ __forceinline__ void inverse_untangle(const float2* __restrict__ Xf, bool active, const float2* __restrict__ tw,
                                                  float2* z, int lane) {
-    for (int k = lane; k <= M / 2; k += 32) {
-        float2 xk = active ? __ldg(&Xf[k]) : make_float2(0.f, 0.f);
-        float2 xm = active ? __ldg(&Xf[M - k]) : make_float2(0.f, 0.f);
-        if (k == 0) {
-            xk.y = 0.f;
-            xm.y = 0.f;
+    // the spectrum rows come from HBM: the loads of a batch of UB iterations are issued together (one exposed memory
+    // latency per batch instead of one per iteration)
+    constexpr int UJ = M / 64, UB = 8;  // k = lane + 32 j <= M / 2 - 1 for j < UJ and every lane; then k = M / 2 (lane 0)
+    static_assert(UJ % UB == 0, "untangle batches");
+    const float2 zero = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int j0 = 0; j0 < UJ; j0 += UB) {
+        float2 xk[UB], xm[UB], w[UB];
+#pragma unroll
+        for (int u = 0; u < UB; ++u) {
+            const int k = lane + 32 * (j0 + u);
+            xk[u] = active ? __ldg(&Xf[k]) : zero;
+            xm[u] = active ? __ldg(&Xf[M - k]) : zero;
+            w[u] = __ldg(&tw[k]);
         }
-        const float2 w = __ldg(&tw[k]);
-        const float2 e = make_float2(0.5f * (xk.x + xm.x), 0.5f * (xk.y - xm.y));
-        const float2 d = make_float2(0.5f * (xk.x - xm.x), 0.5f * (xk.y + xm.y));
-        const float2 o = cmul(cconj(w), d);
-        z[k] = make_float2(e.x - o.y, -(e.y + o.x));            // conj(Z[k])
-        if (k > 0) z[M - k] = make_float2(e.x + o.y, e.y - o.x);  // conj(Z[M-k])
+#pragma unroll
+        for (int u = 0; u < UB; ++u) inverse_untangle_one<M>(xk[u], xm[u], w[u], lane + 32 * (j0 + u), z);
+    }
+    if (lane == 0) {
+        const float2 x = active ? __ldg(&Xf[M / 2]) : zero;
+        inverse_untangle_one<M>(x, x, __ldg(&tw[M / 2]), M / 2, z);
     }
 }
 
