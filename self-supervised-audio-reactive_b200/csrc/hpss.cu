@@ -100,11 +100,22 @@ __global__ void __launch_bounds__(HP_THREADS, 2) hpss_kernel(const float2* __res
 
     const bool interior = t0 >= HALF && t0 + TT + HALF <= n_frames && f0 >= HALF && f0 + TF + HALF <= n_bins;
     if (interior) {  // no reflection / clamping anywhere in the tile: plain strided rows
+        // every load of the thread's ~12 tile elements is issued before the first magnitude is formed (ncu: the kernel's
+        // largest stall was the long scoreboard — the compiler kept load -> sqrt -> store per element)
         const float2* base = Dc + (long long)(t0 - HALF) * ld + (f0 - HALF);
-        for (int i = threadIdx.x; i < ROWS * COLS; i += HP_THREADS) {
+        constexpr int NLD = (ROWS * COLS + HP_THREADS - 1) / HP_THREADS;
+        float2 zz[NLD];
+#pragma unroll
+        for (int u = 0; u < NLD; ++u) {
+            const int i = threadIdx.x + u * HP_THREADS;
             const int r = i / COLS, c = i - r * COLS;
-            const float2 z = __ldg(base + (long long)r * ld + c);
-            mag[r * LDS + c] = sqrtf(fmaf(z.x, z.x, z.y * z.y));
+            zz[u] = i < ROWS * COLS ? __ldg(base + (long long)r * ld + c) : make_float2(0.f, 0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < NLD; ++u) {
+            const int i = threadIdx.x + u * HP_THREADS;
+            const int r = i / COLS, c = i - r * COLS;
+            if (i < ROWS * COLS) mag[r * LDS + c] = sqrtf(fmaf(zz[u].x, zz[u].x, zz[u].y * zz[u].y));
         }
     } else
     for (int i = threadIdx.x; i < ROWS * COLS; i += HP_THREADS) {
@@ -147,7 +158,19 @@ __global__ void __launch_bounds__(HP_THREADS, 2) hpss_kernel(const float2* __res
     }
     __syncthreads();
     // phase 3: (S * mask) * exp(i angle(D)): phase = D / |D| (1 when |D| = 0); coalesced along bins
-    for (int o = threadIdx.x; o < TT * TF; o += HP_THREADS) {
+    constexpr int NOUT = TT * TF / HP_THREADS;
+    static_assert(NOUT * HP_THREADS == TT * TF, "output tile / threads");
+    float2 zo[NOUT];
+#pragma unroll
+    for (int u = 0; u < NOUT; ++u) {  // the tile's own D values again (L2): all loads first
+        const int o = threadIdx.x + u * HP_THREADS;
+        const int r = o / TF, c = o - r * TF;
+        const int t = t0 + r, f = f0 + c;
+        zo[u] = (t < n_frames && f < n_bins) ? __ldg(&D[((long long)clip * cap_frames + t) * ld + f]) : make_float2(0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < NOUT; ++u) {
+        const int o = threadIdx.x + u * HP_THREADS;
         const int r = o / TF, c = o - r * TF;
         const int t = t0 + r, f = f0 + c;
         if (t >= cap_frames || f >= n_bins) continue;
@@ -157,7 +180,7 @@ __global__ void __launch_bounds__(HP_THREADS, 2) hpss_kernel(const float2* __res
             if (out_p) out_p[idx] = make_float2(0.f, 0.f);
             continue;
         }
-        const float2 z = __ldg(&D[idx]);
+        const float2 z = zo[u];
         const float S = mag[(r + HALF) * LDS + c + HALF];
         float2 ph = make_float2(1.f, 0.f);
         if (S > 0.f) {
