@@ -11,6 +11,7 @@ namespace {
 
 constexpr int CQ_WARPS = 8;
 constexpr int MAX_CHROMA = 32;
+constexpr int CQ_LD = 8;  // row loads in flight per lane
 
 struct SplineTable {
     const float* knots;  // [n_knots]
@@ -75,9 +76,23 @@ __global__ void __launch_bounds__(CQ_WARPS * 32) chroma_quant_kernel(
     __syncthreads();
     for (long long row = (long long)blockIdx.x * CQ_WARPS + w; row < n_rows; row += (long long)gridDim.x * CQ_WARPS) {
         const float2* c = cqt + row * ldc;
-        for (int k = l; k < n_bins; k += 32) {
-            const float2 z = __ldg(c + k);
-            mags[k] = sqrtf(fmaf(z.x, z.x, z.y * z.y));
+        if (n_bins <= 32 * CQ_LD) {  // (252 bins) the lane's loads of a row are issued together
+            float2 zz[CQ_LD];
+#pragma unroll
+            for (int u = 0; u < CQ_LD; ++u) {
+                const int k = l + 32 * u;
+                zz[u] = k < n_bins ? __ldg(c + k) : make_float2(0.f, 0.f);
+            }
+#pragma unroll
+            for (int u = 0; u < CQ_LD; ++u) {
+                const int k = l + 32 * u;
+                if (k < n_bins) mags[k] = sqrtf(fmaf(zz[u].x, zz[u].x, zz[u].y * zz[u].y));
+            }
+        } else {
+            for (int k = l; k < n_bins; k += 32) {
+                const float2 z = __ldg(c + k);
+                mags[k] = sqrtf(fmaf(z.x, z.x, z.y * z.y));
+            }
         }
         __syncwarp();
         float v = 0.f;

@@ -117,17 +117,27 @@ __global__ void __launch_bounds__(HP_THREADS, 2) hpss_kernel(const float2* __res
             const int r = i / COLS, c = i - r * COLS;
             if (i < ROWS * COLS) mag[r * LDS + c] = sqrtf(fmaf(zz[u].x, zz[u].x, zz[u].y * zz[u].y));
         }
-    } else
-    for (int i = threadIdx.x; i < ROWS * COLS; i += HP_THREADS) {
-        const int r = i / COLS, c = i - r * COLS;
-        int t = t0 + r - HALF, f = f0 + c - HALF;
-        // reflect; tiles hanging over the far edge read clamped (unused) positions
-        t = (int)ssar_reflect(t, n_frames);
-        f = (int)ssar_reflect(f, n_bins);
-        t = min(max(t, 0), n_frames - 1);
-        f = min(max(f, 0), n_bins - 1);
-        const float2 z = __ldg(&Dc[(long long)t * ld + f]);
-        mag[r * LDS + c] = sqrtf(fmaf(z.x, z.x, z.y * z.y));
+    } else {  // edge tiles (3 of the 17 tile columns of a 1025-bin spectrum): same batching, reflected indices
+        constexpr int NLD = (ROWS * COLS + HP_THREADS - 1) / HP_THREADS;
+        float2 zz[NLD];
+#pragma unroll
+        for (int u = 0; u < NLD; ++u) {
+            const int i = threadIdx.x + u * HP_THREADS;
+            const int r = i / COLS, c = i - r * COLS;
+            int t = t0 + r - HALF, f = f0 + c - HALF;
+            // reflect; tiles hanging over the far edge read clamped (unused) positions
+            t = (int)ssar_reflect(t, n_frames);
+            f = (int)ssar_reflect(f, n_bins);
+            t = min(max(t, 0), n_frames - 1);
+            f = min(max(f, 0), n_bins - 1);
+            zz[u] = i < ROWS * COLS ? __ldg(&Dc[(long long)t * ld + f]) : make_float2(0.f, 0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < NLD; ++u) {
+            const int i = threadIdx.x + u * HP_THREADS;
+            const int r = i / COLS, c = i - r * COLS;
+            if (i < ROWS * COLS) mag[r * LDS + c] = sqrtf(fmaf(zz[u].x, zz[u].x, zz[u].y * zz[u].y));
+        }
     }
     __syncthreads();
 

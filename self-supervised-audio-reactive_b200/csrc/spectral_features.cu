@@ -81,15 +81,25 @@ __global__ void __launch_bounds__(256) onset_flux_mean128_kernel(const float* __
     float* __restrict__ oc = out + (long long)clip * T;
     float4 prev = make_float4(0.f, 0.f, 0.f, 0.f);
     int jprev = -2;  // flux index whose dB row `prev` holds
-    for (int t = t0; t < t0 + OF_RUN && t < T; ++t) {
+    // the run's OF_RUN + 1 mel rows are loaded up front (one exposed memory latency per run instead of one per frame)
+    float4 raw[OF_RUN + 1];
+#pragma unroll
+    for (int u = 0; u <= OF_RUN; ++u) {
+        const int jr = t0 - pad_width + u;
+        raw[u] = (jr >= 0 && jr < T) ? __ldg(rows + (long long)jr * 32) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < OF_RUN; ++u) {
+        const int t = t0 + u;
+        if (t >= T) break;
         const int j = t - pad_width;
         float result = 0.f;
         if (j >= 0 && j + 1 < T) {
             if (jprev != j) {
-                const float4 a = __ldg(rows + (long long)j * 32);
+                const float4 a = raw[u];
                 prev = make_float4(to_db(a.x, fl), to_db(a.y, fl), to_db(a.z, fl), to_db(a.w, fl));
             }
-            const float4 b = __ldg(rows + (long long)(j + 1) * 32);
+            const float4 b = raw[u + 1];
             const float4 cur = make_float4(to_db(b.x, fl), to_db(b.y, fl), to_db(b.z, fl), to_db(b.w, fl));
             const float d[4] = {fmaxf(0.f, cur.x - prev.x), fmaxf(0.f, cur.y - prev.y), fmaxf(0.f, cur.z - prev.z),
                                 fmaxf(0.f, cur.w - prev.w)};
