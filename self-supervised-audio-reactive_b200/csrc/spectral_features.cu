@@ -66,7 +66,7 @@ __global__ void mfcc_kernel(const float* __restrict__ mel, const uint32_t* __res
 // v1 of the mean-aggregated onset envelope for 128 bands: one warp walks OF_RUN consecutive frames, each lane keeps the
 // dB values of its 4 bands of the previous frame in registers, so every mel row is read (128-bit loads) and converted
 // to dB once; the band mean is a shuffle reduction.  (v0 spends one 128-thread CTA and two block barriers per frame.)
-constexpr int OF_RUN = 16;
+constexpr int OF_RUN_MEAN = 16, OF_RUN_MEDIAN = 4;  // the median's 31 serial select rounds per frame want more, shorter runs
 template <bool MEDIAN>
 __global__ void __launch_bounds__(256) onset_flux_mean128_kernel(const float* __restrict__ mel,
                                                                  const uint32_t* __restrict__ max_key, int T, int pad_width,
@@ -75,6 +75,7 @@ __global__ void __launch_bounds__(256) onset_flux_mean128_kernel(const float* __
     const long long wid = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int clip = blockIdx.y;
     if (wid >= runs_per_clip) return;
+    constexpr int OF_RUN = MEDIAN ? OF_RUN_MEDIAN : OF_RUN_MEAN;
     const int t0 = (int)wid * OF_RUN;
     const float fl = db_floor_from_key(max_key[clip], top_db);
     const float4* __restrict__ rows = reinterpret_cast<const float4*>(mel + (long long)clip * T * 128) + lane;
@@ -223,7 +224,7 @@ extern "C" int ssar_onset_flux(const float* mel, const uint32_t* max_key, int n_
     SSAR_REQUIRE(n_bands > 0 && n_bands <= 4096, "onset_flux: n_bands out of range");
     SSAR_REQUIRE(aggregate == 0 || aggregate == 1, "onset_flux: aggregate must be 0 (mean) or 1 (median)");
     if (n_bands == 128 && (reinterpret_cast<uintptr_t>(mel) & 15) == 0) {
-        const int runs = ssar_div_up(n_frames, OF_RUN);
+        const int runs = ssar_div_up(n_frames, aggregate == 0 ? OF_RUN_MEAN : OF_RUN_MEDIAN);
         if (aggregate == 0)
             onset_flux_mean128_kernel<false><<<dim3(ssar_div_up(runs, 8), n_clips), 256, 0, (cudaStream_t)stream>>>(
                 mel, max_key, n_frames, pad_width, top_db, out, runs);
